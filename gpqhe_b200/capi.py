@@ -1,0 +1,100 @@
+"""ctypes binding of the C ABI in include/gpqhe_b200.h.
+
+The product library is gpqhe_b200/libgpqhe_b200.so (hand-written CUDA, sm_100a, built
+by gpqhe_b200/csrc/Makefile).  There is no CPU fallback: if the library is missing,
+or no CUDA device is present when a context is created, this module raises.  Tests
+that run without a GPU pass the path of the emulated build (tests/emul/) explicitly;
+nothing in the package ever selects it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+DEFAULT_LIB = os.path.join(_HERE, "libgpqhe_b200.so")
+
+u64 = C.c_uint64
+u64p = C.POINTER(C.c_uint64)
+vp = C.c_void_p
+
+
+class GqInfo(C.Structure):
+    _fields_ = [(k, C.c_uint) for k in
+                ("logn", "n", "logp", "dimub", "has_he", "L", "dim", "dimevk", "W", "q_is_pow2")] + \
+               [("device", C.c_int)]
+
+
+class GpqheError(RuntimeError):
+    pass
+
+
+# name -> (restype, argtypes); every symbol include/gpqhe_b200.h declares
+SIGNATURES = {
+    "gq_last_error": (C.c_char_p, []),
+    "gq_abi_version": (C.c_int, []),
+    "gq_ctx_create": (C.c_int, [C.POINTER(vp), C.c_uint, u64p, C.c_uint, C.c_uint, u64, C.c_uint,
+                                C.c_uint, C.c_int, u64p, C.POINTER(u64p), C.POINTER(u64p)]),
+    "gq_ctx_destroy": (None, [vp]),
+    "gq_ctx_info": (C.c_int, [vp, C.POINTER(GqInfo)]),
+    "gq_ctx_primes": (C.c_int, [vp, u64p]),
+    "gq_ctx_prime_consts": (C.c_int, [vp, C.c_uint, u64p]),
+    "gq_ctx_dims": (C.c_int, [vp, C.c_uint, C.POINTER(C.c_uint), C.POINTER(C.c_uint)]),
+    "gq_ctx_sync": (C.c_int, [vp]),
+    "gq_ctx_launch_count": (C.c_ulonglong, [vp]),
+    "gq_ctx_stream": (vp, [vp]),
+    "gq_host_alloc": (C.c_int, [C.POINTER(vp), C.c_size_t]),
+    "gq_host_free": (None, [vp]),
+    "gq_ntt": (C.c_int, [vp, C.c_uint, vp]),
+    "gq_invntt": (C.c_int, [vp, C.c_uint, vp]),
+    "gq_poly_rns_add": (C.c_int, [vp, C.c_uint, vp, vp, vp]),
+    "gq_poly_rns_mul": (C.c_int, [vp, C.c_uint, vp, vp, vp]),
+    "gq_ntt_batch": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.c_int]),
+    "gq_rns_decompose": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, C.c_uint]),
+    "gq_poly_rns2mpi": (C.c_int, [vp, C.c_uint, vp, C.c_uint, vp, u64p, C.c_uint]),
+    "gq_poly_mul": (C.c_int, [vp, vp, C.c_uint, vp, vp, C.c_uint, C.c_uint, u64p, C.c_uint]),
+    "gq_poly_rot": (C.c_int, [vp, vp, vp, C.c_uint, u64]),
+    "gq_poly_conj": (C.c_int, [vp, vp, vp, C.c_uint]),
+    "gq_evk_create": (C.c_int, [vp, C.POINTER(vp), vp, vp]),
+    "gq_evk_create_dev": (C.c_int, [vp, C.POINTER(vp), vp, vp]),
+    "gq_evk_destroy": (None, [vp]),
+    "gq_he_mul": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp]),
+    "gq_he_mulpt": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp, vp]),
+    "gq_he_rs": (C.c_int, [vp, C.c_uint, vp, vp]),
+    "gq_he_moddown": (C.c_int, [vp, C.c_uint, vp, vp]),
+    "gq_he_rot": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp]),
+    "gq_he_conj": (C.c_int, [vp, C.c_uint, vp, vp, vp]),
+    "gq_ntt_batch_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.c_int, vp]),
+    "gq_poly_rns_mul_batch_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp]),
+    "gq_he_mul_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "gq_he_mulpt_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp]),
+    "gq_he_rs_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp]),
+    "gq_he_moddown_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp]),
+    "gq_he_rot_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp]),
+    "gq_he_conj_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp]),
+}
+
+_loaded: dict[str, C.CDLL] = {}
+
+
+def load(path: str | None = None) -> C.CDLL:
+    """Load the C-ABI library and attach prototypes.  Raises if it is not built."""
+    path = os.path.abspath(path or DEFAULT_LIB)
+    if path in _loaded:
+        return _loaded[path]
+    if not os.path.exists(path):
+        raise GpqheError(
+            f"{path} not found: build the CUDA extension first "
+            "(python -c 'import __graft_entry__ as g; g.build()' or make -C gpqhe_b200/csrc). "
+            "gpqhe_b200 has no CPU fallback.")
+    lib = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the library misses a symbol
+        fn.restype, fn.argtypes = res, args
+    _loaded[path] = lib
+    return lib
+
+
+def check(lib: C.CDLL, rc: int):
+    if rc != 0:
+        raise GpqheError(lib.gq_last_error().decode(errors="replace"))

@@ -1,0 +1,812 @@
+// gq_api.cu - the C ABI (include/gpqhe_b200.h): context construction (the host part of
+// src/precomp.c: prime search, roots, CRT constants, level table), table upload, and
+// the orchestration of the per-stage kernels for each reference entry point.
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/gpqhe_b200.h"
+#include "gq_context.h"
+
+// ------------------------------------------------------------------------------ errors
+static thread_local std::string g_err;
+void gq_set_error(const std::string &msg) { g_err = msg; }
+extern "C" const char *gq_last_error(void) { return g_err.c_str(); }
+extern "C" int gq_abi_version(void) { return 1; }
+
+#define GQ_FAIL(msg) do { gq_set_error(std::string(__func__) + ": " + (msg)); return 1; } while (0)
+#define GQ_CUDA(call)                                                                  \
+  do {                                                                                 \
+    cudaError_t e_ = (call);                                                           \
+    if (e_ != cudaSuccess) {                                                           \
+      gq_set_error(std::string(__func__) + ": " #call " -> " + cudaGetErrorString(e_)); \
+      return 1;                                                                        \
+    }                                                                                  \
+  } while (0)
+#define GQ_CHECK_LAUNCH(ctx)                                                           \
+  do {                                                                                 \
+    cudaError_t e_ = cudaGetLastError();                                               \
+    if (e_ != cudaSuccess) {                                                           \
+      gq_set_error(std::string(__func__) + ": kernel launch -> " + cudaGetErrorString(e_)); \
+      return 1;                                                                        \
+    }                                                                                  \
+  } while (0)
+
+// --------------------------------------------------- number theory (src/precomp.c:119-242)
+static uint64_t mulm(uint64_t a, uint64_t b, uint64_t m) { return (uint64_t)(((gq_u128)a * b) % m); }
+static uint64_t powm(uint64_t a, uint64_t e, uint64_t m) {
+  uint64_t r = 1 % m;
+  a %= m;
+  while (e) { if (e & 1) r = mulm(r, a, m); a = mulm(a, a, m); e >>= 1; }
+  return r;
+}
+// The reference runs 50 Miller-Rabin rounds with rand() witnesses (src/precomp.c:153-191);
+// the first 12 prime bases are a proof for every n < 3.3e24, so the same numbers pass.
+static bool is_prime(uint64_t p) {
+  static const uint64_t B[12] = {2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37};
+  if (p < 2) return false;
+  for (uint64_t b : B) { if (p == b) return true; if (p % b == 0) return false; }
+  uint64_t u = p - 1; int t = 0;
+  while (!(u & 1)) { u >>= 1; t++; }
+  for (uint64_t b : B) {
+    uint64_t x = powm(b, u, p);
+    if (x == 1 || x == p - 1) continue;
+    bool witness = true;
+    for (int r = 1; r < t && witness; r++) { x = mulm(x, x, p); if (x == p - 1) witness = false; }
+    if (witness) return false;
+  }
+  return true;
+}
+// smallest primitive root (src/precomp.c:205-225), then g^((p-1)/m) (:234-242)
+static uint64_t root_of_unity(uint64_t m, uint64_t p) {
+  uint64_t phi = p - 1, rest = phi;
+  std::vector<uint64_t> fac;
+  for (uint64_t f = 2; f * f <= rest; f++)
+    if (rest % f == 0) { fac.push_back(f); while (rest % f == 0) rest /= f; }
+  if (rest > 1) fac.push_back(rest);
+  for (uint64_t g = 2; g <= phi; g++) {
+    bool ok = true;
+    for (uint64_t f : fac) if (powm(g, phi / f, p) == 1) { ok = false; break; }
+    if (ok) return powm(g, phi / m, p);
+  }
+  return 0;
+}
+static uint32_t bitrev(uint32_t a, unsigned bits) {
+  uint32_t r = 0;
+  for (unsigned i = 0; i < bits; i++) r |= ((a >> i) & 1u) << (bits - 1 - i);
+  return r;
+}
+static unsigned std_logqub(unsigned logn) {   // src/precomp.c:52-61 (classical, 128 bit)
+  switch (logn) { case 10: return 27; case 11: return 54; case 12: return 109;
+                  case 13: return 218; case 14: return 438; case 15: return 881; }
+  return 0;
+}
+static unsigned round_wt(unsigned words) { return (words + 7) / 8 * 8; }
+
+// ------------------------------------------------------------------------ device helpers
+template <typename T>
+static int upload(T **dst, const T *src, size_t count) {
+  GQ_CUDA(cudaMalloc((void **)dst, count * sizeof(T) + 16));
+  GQ_CUDA(cudaMemcpy(*dst, src, count * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+static int ensure_slot(gq_ctx *c, int s, size_t bytes) {
+  if (c->slot_bytes[s] >= bytes) return 0;
+  if (c->slot[s]) { GQ_CUDA(cudaStreamSynchronize(c->stream)); GQ_CUDA(cudaFree(c->slot[s])); c->slot[s] = nullptr; }
+  size_t want = bytes + bytes / 4 + 256;
+  GQ_CUDA(cudaMalloc(&c->slot[s], want));
+  c->slot_bytes[s] = want;
+  return 0;
+}
+
+static int build_modulus(GqHostModulus &m, const BigU &q) {
+  m.q = q;
+  m.dev.is_pow2 = q.is_pow2() ? 1 : 0;
+  m.dev.k = q.bits() ? q.bits() - 1 : 0;
+  m.dev.nwords = (int)q.w.size();
+  std::vector<uint64_t> buf(2 * GQ_MAX_W, 0);
+  q.store(buf.data(), GQ_MAX_W);
+  q.shr(1).store(buf.data() + GQ_MAX_W, GQ_MAX_W);
+  uint64_t *d = nullptr;
+  if (upload(&d, buf.data(), buf.size())) return 1;
+  m.blob = d;
+  m.dev.q = d;
+  m.dev.qh = d + GQ_MAX_W;
+  return 0;
+}
+
+// CRT constants of the basis {p_0..p_{D-1}} (rns_init, src/precomp.c:266-293)
+static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
+  GqHostBasis &hb = c->basis[D - 1];
+  hb.P = P;
+  const unsigned bitsP = P.bits();
+  const unsigned WT = round_wt((bitsP + 1 + 63) / 64);
+  if (WT > GQ_MAX_W) GQ_FAIL("RNS basis wider than GQ_MAX_W words");
+  if (D > WT + WT / 8 + 2) GQ_FAIL("too many primes for the CRT tile");
+  std::vector<uint64_t> buf((size_t)(2 + D) * WT + 2 * D, 0);
+  uint64_t *hP = buf.data(), *hPh = hP + WT, *hphat = hPh + WT, *hinv = hphat + (size_t)D * WT,
+           *hinvsh = hinv + D;
+  P.store(hP, WT);
+  P.shr(1).store(hPh, WT);
+  for (unsigned d = 0; d < D; d++) {
+    const uint64_t pd = c->primes[d].p;
+    BigU phat = P.div_u64(pd);
+    phat.store(hphat + (size_t)d * WT, WT);
+    uint64_t inv = powm(phat.mod_u64(pd), pd - 2, pd);   // precomp.c:289
+    hinv[d] = inv;
+    hinvsh[d] = (uint64_t)(((gq_u128)inv << 64) / pd);
+  }
+  uint64_t *dv = nullptr;
+  if (upload(&dv, buf.data(), buf.size())) return 1;
+  hb.blob = dv;
+  GqCrtBasis &B = hb.dev;
+  B.D = (int)D; B.WT = (int)WT; B.bitsP = bitsP;
+  B.P = dv; B.Ph = dv + WT; B.phat = dv + 2 * WT; B.inv = B.phat + (size_t)D * WT; B.inv_sh = B.inv + D;
+  if (bitsP >= 58) {
+    B.sh = (int)bitsP - 58;
+    BigU top = P.shr((unsigned)B.sh);
+    uint64_t t1 = top.word(0) + 1;
+    gq_u128 num = (((gq_u128)1) << 120) - 1;
+    B.recip = (uint64_t)(num / t1);
+  } else {
+    B.sh = -1; B.recip = 0;
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------- create
+extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, unsigned q_words,
+                             unsigned slots, uint64_t Delta, unsigned logp, unsigned logqub,
+                             int device, const uint64_t *primes_in, const uint64_t *const *zetas_in,
+                             const uint64_t *const *zetas_inv_in) {
+  if (!out || !qw || q_words == 0) GQ_FAIL("null argument");
+  if (logn < 3 || logn > 17) GQ_FAIL("logn must be in [3,17]");
+  if (logp == 0) logp = 59;
+  if (logp < 8 || logp > 61) GQ_FAIL("logp must be in [8,61]");
+  int ndev = 0;
+  GQ_CUDA(cudaGetDeviceCount(&ndev));
+  if (ndev <= 0) GQ_FAIL("no CUDA device: gpqhe_b200 has no CPU path");
+  if (device < 0 || device >= ndev) GQ_FAIL("bad device index");
+  GQ_CUDA(cudaSetDevice(device));
+
+  gq_ctx *c = new gq_ctx();
+  c->device = device;
+  c->logn = logn; c->n = 1u << logn; c->logp = logp;
+  c->q = BigU(qw, q_words);
+  if (c->q.bits() < 2) { delete c; GQ_FAIL("modulus q too small"); }
+  const unsigned logq = c->q.bits() - 1;
+  if (logqub == 0) {                                   // precomp.c:338-340
+    logqub = std_logqub(logn);
+    if (logn < 10 || logn > 15) logqub = logq;
+  }
+  if (logq > logqub) { delete c; GQ_FAIL("The input modulus q is too large. Must guarantee log(q)<=log(qub)."); }
+  c->logqub = logqub;
+  c->dimub = (1 + logn + 4 * logqub) / logp + 1;       // precomp.c:357
+  if (c->dimub > GQ_MAX_PRIMES) { delete c; GQ_FAIL("dimub exceeds GQ_MAX_PRIMES"); }
+  GQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+
+  const unsigned n = c->n, K = c->dimub;
+  // primes: p = 2^logp + 1 + k*2N ascending (precomp.c:358-376), or the caller's
+  c->primes.resize(K);
+  uint64_t p = (1ull << logp) + 1;
+  for (unsigned d = 0; d < K; d++) {
+    if (primes_in) p = primes_in[d];
+    else do { p += 2ull * n; } while (!is_prime(p));
+    if ((p - 1) % (2ull * n) != 0 || !is_prime(p)) { delete c; GQ_FAIL("supplied modulus is not an NTT prime"); }
+    GqPrime &P = c->primes[d];
+    P.p = p;
+    P.bits = 64 - (unsigned)__builtin_clzll(p);
+    uint64_t inv = 1, sq = p;                              // montgomery_inv, reduce.c:36-49
+    for (int k = 0; k < 64; k++) { inv *= sq; sq *= sq; }
+    P.pinv_mont = inv;
+    P.pinv_barr = (2 * P.bits >= 128) ? 0 : (uint64_t)((((gq_u128)1) << (2 * P.bits)) / p);
+    P.barr_shift = (2 * P.bits >= 64) ? 2 * P.bits - 64 : 0;
+    P.ninv = powm(n, p - 2, p);
+    P.ninv_mont = (uint64_t)((((gq_u128)P.ninv) << 64) % p);
+    P.ninv_sh = (uint64_t)((((gq_u128)P.ninv) << 64) / p);
+  }
+  // twiddles: {w, floor(w*2^64/p)} indexed like zetas[] / zetas_inv[] (precomp.c:244-264)
+  {
+    std::vector<ulonglong2> fwd((size_t)K * n), inv((size_t)K * n), last(K);
+    for (unsigned d = 0; d < K; d++) {
+      const GqPrime &P = c->primes[d];
+      ulonglong2 *f = &fwd[(size_t)d * n], *iv = &inv[(size_t)d * n];
+      if (zetas_in && zetas_inv_in) {
+        for (unsigned k = 0; k < n; k++) {      // Montgomery form -> plain residue
+          uint64_t w = gq_mont_reduce(zetas_in[d][k], 0, P.p, P.pinv_mont);
+          uint64_t wi = gq_mont_reduce(zetas_inv_in[d][k], 0, P.p, P.pinv_mont);
+          f[k] = make_ulonglong2(w, (uint64_t)(((gq_u128)w << 64) / P.p));
+          iv[k] = make_ulonglong2(wi, (uint64_t)(((gq_u128)wi << 64) / P.p));
+        }
+      } else {
+        uint64_t root = root_of_unity(2ull * n, P.p), rinv = powm(root, P.p - 2, P.p);
+        uint64_t pw = 1, pwi = 1;
+        for (unsigned i = 0; i < n; i++) {
+          uint32_t j = bitrev(i, logn);
+          f[j] = make_ulonglong2(pw, (uint64_t)(((gq_u128)pw << 64) / P.p));
+          iv[j] = make_ulonglong2(pwi, (uint64_t)(((gq_u128)pwi << 64) / P.p));
+          pw = mulm(pw, root, P.p);
+          pwi = mulm(pwi, rinv, P.p);
+        }
+      }
+      uint64_t wl = mulm(iv[1].x, P.ninv, P.p);
+      last[d] = make_ulonglong2(wl, (uint64_t)(((gq_u128)wl << 64) / P.p));
+    }
+    if (upload(&c->d_tw_fwd, fwd.data(), fwd.size()) || upload(&c->d_tw_inv, inv.data(), inv.size()) ||
+        upload(&c->d_tw_inv_last, last.data(), last.size())) { gq_ctx_destroy(c); return 1; }
+  }
+  if (upload(&c->d_primes, c->primes.data(), K)) { gq_ctx_destroy(c); return 1; }
+  {   // decompose table: 2^(64w) mod p
+    std::vector<uint64_t> pw((size_t)K * GQ_DEC_W), t1(K);
+    for (unsigned d = 0; d < K; d++) {
+      const uint64_t pd = c->primes[d].p;
+      const uint64_t b = (uint64_t)((((gq_u128)1) << 64) % pd);
+      uint64_t v = 1 % pd;
+      for (unsigned w = 0; w < GQ_DEC_W; w++) { pw[(size_t)d * GQ_DEC_W + w] = v; v = mulm(v, b, pd); }
+      t1[d] = (uint64_t)(((gq_u128)b << 64) / pd);
+    }
+    if (upload(&c->d_pow64, pw.data(), pw.size()) || upload(&c->d_t1sh, t1.data(), t1.size())) {
+      gq_ctx_destroy(c); return 1;
+    }
+  }
+  // CRT constants for every prefix basis
+  c->basis.resize(K);
+  {
+    BigU P(1);
+    for (unsigned D = 1; D <= K; D++) {
+      P = P.mul_u64(c->primes[D - 1].p);
+      if (build_basis(c, D, P)) { gq_ctx_destroy(c); return 1; }
+    }
+  }
+  GQ_CUDA(cudaMalloc((void **)&c->d_adhoc, 2 * GQ_MAX_W * sizeof(uint64_t)));
+
+  // hectx_init / qtable_init (precomp.c:386-452)
+  if (Delta) {
+    if (slots == 0 || (slots & (slots - 1))) { gq_ctx_destroy(c); GQ_FAIL("The slots must be the power of 2."); }
+    if (slots > n / 2) { gq_ctx_destroy(c); GQ_FAIL("Must guarantee slots<=(n/2)."); }
+    c->has_he = 1; c->slots = slots; c->Delta = Delta;
+    const unsigned bitsD = 64 - (unsigned)__builtin_clzll(Delta);
+    const unsigned logDelta = bitsD - 1;
+    if (logDelta == 0) { gq_ctx_destroy(c); GQ_FAIL("Delta must be at least 2"); }
+    c->L = logq / logDelta;                               // precomp.c:391 (integer division)
+    c->ql.resize(c->L + 1); c->qh.resize(c->L + 1); c->qmod.resize(c->L + 1);
+    BigU q = c->q;
+    bool pow2 = (Delta & (Delta - 1)) == 0;
+    for (int l = (int)c->L; l >= 0; l--) {
+      c->ql[l] = q; c->qh[l] = q.shr(1);
+      if (q.is_zero()) { gq_ctx_destroy(c); GQ_FAIL("level modulus reached zero"); }
+      pow2 = pow2 && q.is_pow2();
+      if (build_modulus(c->qmod[l], q)) { gq_ctx_destroy(c); return 1; }
+      q = q.div_u64(Delta);
+    }
+    c->q_is_pow2 = pow2 ? 1 : 0;
+    c->logDelta = logDelta;
+    c->dim = (c->ql[c->L].bits() + logn) / logp + 1;      // precomp.c:401
+    if (c->dim > K) { gq_ctx_destroy(c); GQ_FAIL("hectx.dim exceeds dimub"); }
+    c->P = c->basis[c->dim - 1].P;
+    c->PqL = c->P.mul(c->q);
+    c->dimevk = (c->ql[c->L].bits() + c->PqL.bits() + logn) / logp + 1;   // precomp.c:407
+    // dimevk > dimub is not rejected here: the reference's hectx_init accepts it and only
+    // the key-switch entry points (which would walk off its prime list) fail.
+    c->W = (c->q.bits() + 63) / 64;
+    // P^-1 mod 2^(64*GQ_MAX_W) by word-serial exact division of 1 by P
+    {
+      std::vector<uint64_t> Pw(GQ_MAX_W), x(GQ_MAX_W, 0), pinv(GQ_MAX_W);
+      c->P.store(Pw.data(), GQ_MAX_W);
+      uint64_t inv0 = 1, sq = Pw[0];
+      for (int k = 0; k < 64; k++) { inv0 *= sq; sq *= sq; }
+      x[0] = 1;
+      for (int i = 0; i < GQ_MAX_W; i++) {
+        uint64_t qi = x[i] * inv0;
+        pinv[i] = qi;
+        uint64_t carry = 0, borrow = 0;          // x[i..] -= qi * P
+        for (int j = 0; i + j < GQ_MAX_W; j++) {
+          gq_u128 t = (gq_u128)qi * Pw[j] + carry;
+          uint64_t lo = (uint64_t)t; carry = (uint64_t)(t >> 64);
+          uint64_t a = x[i + j], dd = a - lo, b1 = a < lo, d2 = dd - borrow, b2 = dd < borrow;
+          x[i + j] = d2; borrow = b1 | b2;
+        }
+      }
+      std::vector<uint64_t> pp(2 * GQ_MAX_W);
+      c->P.store(pp.data(), GQ_MAX_W);
+      c->P.shr(1).store(pp.data() + GQ_MAX_W, GQ_MAX_W);
+      if (upload(&c->d_Pinv, pinv.data(), pinv.size()) || upload(&c->d_Pwords, pp.data(), pp.size())) {
+        gq_ctx_destroy(c); return 1;
+      }
+    }
+  } else {
+    c->W = (c->q.bits() + 63) / 64;
+  }
+  *out = c;
+  return 0;
+}
+
+extern "C" void gq_ctx_destroy(gq_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  cudaFree(c->d_primes); cudaFree(c->d_tw_fwd); cudaFree(c->d_tw_inv); cudaFree(c->d_tw_inv_last);
+  cudaFree(c->d_pow64); cudaFree(c->d_t1sh); cudaFree(c->d_Pinv); cudaFree(c->d_Pwords);
+  cudaFree(c->d_adhoc);
+  for (auto &b : c->basis) cudaFree(b.blob);
+  for (auto &m : c->qmod) cudaFree(m.blob);
+  for (int s = 0; s < GQ_SLOT_COUNT; s++) cudaFree(c->slot[s]);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+// ------------------------------------------------------------------------------ queries
+extern "C" int gq_ctx_info(const gq_ctx *c, gq_info *o) {
+  if (!c || !o) GQ_FAIL("null argument");
+  o->logn = c->logn; o->n = c->n; o->logp = c->logp; o->dimub = c->dimub; o->has_he = c->has_he;
+  o->L = c->L; o->dim = c->dim; o->dimevk = c->dimevk; o->W = c->W; o->q_is_pow2 = c->q_is_pow2;
+  o->device = c->device;
+  return 0;
+}
+extern "C" int gq_ctx_primes(const gq_ctx *c, uint64_t *out) {
+  if (!c || !out) GQ_FAIL("null argument");
+  for (unsigned d = 0; d < c->dimub; d++) out[d] = c->primes[d].p;
+  return 0;
+}
+extern "C" int gq_ctx_prime_consts(const gq_ctx *c, unsigned limb, uint64_t out[4]) {
+  if (!c || !out || limb >= c->dimub) GQ_FAIL("bad argument");
+  const GqPrime &P = c->primes[limb];
+  out[0] = P.p; out[1] = P.pinv_mont; out[2] = P.pinv_barr; out[3] = P.ninv_mont;
+  return 0;
+}
+static unsigned dim_tensor(const gq_ctx *c, unsigned l) {      // he-mult.c:99
+  return (c->ql[l].bits() * 2 + c->logn) / c->logp + 1;
+}
+static unsigned dim_ks(const gq_ctx *c, unsigned l) {          // he-mult.c:51
+  return (c->ql[l].bits() + c->PqL.bits() + c->logn) / c->logp + 1;
+}
+extern "C" int gq_ctx_dims(const gq_ctx *c, unsigned l, unsigned *dt, unsigned *dk) {
+  if (!c || !c->has_he || l > c->L) GQ_FAIL("bad argument");
+  if (dt) *dt = dim_tensor(c, l);
+  if (dk) *dk = dim_ks(c, l);
+  return 0;
+}
+extern "C" int gq_ctx_sync(gq_ctx *c) {
+  if (!c) GQ_FAIL("null context");
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+extern "C" unsigned long long gq_ctx_launch_count(const gq_ctx *c) { return c ? c->launches : 0; }
+extern "C" void *gq_ctx_stream(gq_ctx *c) { return c ? (void *)c->stream : nullptr; }
+extern "C" int gq_host_alloc(void **p, size_t bytes) {
+  if (!p) GQ_FAIL("null argument");
+  GQ_CUDA(cudaMallocHost(p, bytes));
+  return 0;
+}
+extern "C" void gq_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+static cudaStream_t pick(gq_ctx *c, void *s) { return s ? (cudaStream_t)s : c->stream; }
+static bool ntt_ok(const gq_ctx *c, unsigned limb0, unsigned nlimbs) {
+  if (limb0 + nlimbs > c->dimub || nlimbs == 0) return false;
+  for (unsigned d = limb0; d < limb0 + nlimbs; d++)
+    if (c->primes[d].bits < 32) return false;   // the reference aborts too (reduce.c:94-100)
+  return true;
+}
+
+// --------------------------------------------------------------------------- limb layer
+extern "C" int gq_ntt_batch_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys,
+                                uint64_t *data, int inverse, void *stream) {
+  if (!c || !data || npolys == 0) GQ_FAIL("bad argument");
+  if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
+  int r = gq_launch_ntt(c->ntt_tables(), data, (int)limb0, (int)nlimbs, (int)npolys, inverse != 0,
+                        pick(c, stream));
+  if (r < 0) GQ_FAIL("unsupported ring degree");
+  c->launches += (unsigned)r;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+
+extern "C" int gq_poly_rns_mul_batch_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys,
+                                         uint64_t *r, const uint64_t *a, const uint64_t *b,
+                                         void *stream) {
+  if (!c || !r || !a || !b || npolys == 0) GQ_FAIL("bad argument");
+  if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
+  gq_launch_binary(c->d_primes, (int)c->n, (int)limb0, (int)nlimbs, (int)npolys, true, r, a, b,
+                   pick(c, stream));
+  c->launches++;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+
+extern "C" int gq_ntt_batch(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys,
+                            uint64_t *data, int inverse) {
+  if (!c || !data) GQ_FAIL("bad argument");
+  const size_t bytes = (size_t)nlimbs * npolys * c->n * 8;
+  if (ensure_slot(c, GQ_SLOT_LIMB_A, bytes)) return 1;
+  uint64_t *d = (uint64_t *)c->slot[GQ_SLOT_LIMB_A];
+  GQ_CUDA(cudaMemcpyAsync(d, data, bytes, cudaMemcpyHostToDevice, c->stream));
+  if (gq_ntt_batch_dev(c, limb0, nlimbs, npolys, d, inverse, nullptr)) return 1;
+  GQ_CUDA(cudaMemcpyAsync(data, d, bytes, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+extern "C" int gq_ntt(gq_ctx *c, unsigned limb, uint64_t *a) { return gq_ntt_batch(c, limb, 1, 1, a, 0); }
+extern "C" int gq_invntt(gq_ctx *c, unsigned limb, uint64_t *a) { return gq_ntt_batch(c, limb, 1, 1, a, 1); }
+
+static int binary_host(gq_ctx *c, unsigned limb, uint64_t *r, const uint64_t *a, const uint64_t *b,
+                       bool mul) {
+  if (!c || !r || !a || !b) GQ_FAIL("bad argument");
+  if (!ntt_ok(c, limb, 1)) GQ_FAIL("limb invalid or modulus below 32 bits");
+  const size_t bytes = (size_t)c->n * 8;
+  if (ensure_slot(c, GQ_SLOT_LIMB_A, 3 * bytes)) return 1;
+  uint64_t *d = (uint64_t *)c->slot[GQ_SLOT_LIMB_A];
+  GQ_CUDA(cudaMemcpyAsync(d, a, bytes, cudaMemcpyHostToDevice, c->stream));
+  GQ_CUDA(cudaMemcpyAsync(d + c->n, b, bytes, cudaMemcpyHostToDevice, c->stream));
+  gq_launch_binary(c->d_primes, (int)c->n, (int)limb, 1, 1, mul, d + 2 * c->n, d, d + c->n, c->stream);
+  c->launches++;
+  GQ_CHECK_LAUNCH(c);
+  GQ_CUDA(cudaMemcpyAsync(r, d + 2 * c->n, bytes, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+extern "C" int gq_poly_rns_add(gq_ctx *c, unsigned limb, uint64_t *r, const uint64_t *a, const uint64_t *b) {
+  return binary_host(c, limb, r, a, b, false);
+}
+extern "C" int gq_poly_rns_mul(gq_ctx *c, unsigned limb, uint64_t *r, const uint64_t *a, const uint64_t *b) {
+  return binary_host(c, limb, r, a, b, true);
+}
+
+// ------------------------------------------------------------------- MPI <-> RNS (device)
+static GqPtrs4 ptrs(const uint64_t *a, const uint64_t *b = nullptr, const uint64_t *c2 = nullptr,
+                    const uint64_t *d = nullptr) {
+  GqPtrs4 p;
+  p.p[0] = (uint64_t *)a; p.p[1] = (uint64_t *)b; p.p[2] = (uint64_t *)c2; p.p[3] = (uint64_t *)d;
+  return p;
+}
+
+static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtrs4 &in, unsigned W,
+                         unsigned npolys, uint64_t *out, cudaStream_t st) {
+  if (limb0 + nlimbs > c->dimub) GQ_FAIL("limb range exceeds dimub");
+  if (W == 0 || W > GQ_MAX_W) GQ_FAIL("word count out of range");
+  if (gq_launch_decompose(c->dec_tables(), (int)c->n, (int)limb0, (int)nlimbs, in, (int)W, out,
+                          (int)npolys, st) < 0)
+    GQ_FAIL("no decompose kernel for this width");
+  c->launches++;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+
+static int reconstruct_dev(gq_ctx *c, unsigned D, const uint64_t *rhat, const GqModulus &q,
+                           const GqPtrs4 &out, unsigned Wout, unsigned npolys, cudaStream_t st) {
+  if (D == 0 || D > c->dimub) GQ_FAIL("basis size out of range");
+  if (gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)c->n, rhat, q, out, (int)Wout,
+                            (int)npolys, st) < 0)
+    GQ_FAIL("no reconstruct kernel for this width");
+  c->launches++;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+
+// ad-hoc modulus for poly_mul / poly_rns2mpi (the caller's q, any value)
+static int adhoc_modulus(gq_ctx *c, const uint64_t *qw, unsigned q_words, GqModulus *m) {
+  BigU q(qw, q_words);
+  if (q.is_zero()) GQ_FAIL("modulus is zero");
+  if (q.w.size() > GQ_MAX_W) GQ_FAIL("modulus wider than GQ_MAX_W words");
+  m->is_pow2 = q.is_pow2() ? 1 : 0;
+  m->k = q.bits() - 1;
+  m->nwords = (int)q.w.size();
+  m->q = c->d_adhoc; m->qh = c->d_adhoc + GQ_MAX_W;
+  if (!m->is_pow2) {
+    uint64_t buf[2 * GQ_MAX_W];
+    q.store(buf, GQ_MAX_W);
+    q.shr(1).store(buf + GQ_MAX_W, GQ_MAX_W);
+    GQ_CUDA(cudaStreamSynchronize(c->stream));
+    GQ_CUDA(cudaMemcpy(c->d_adhoc, buf, sizeof(buf), cudaMemcpyHostToDevice));
+  }
+  return 0;
+}
+
+extern "C" int gq_rns_decompose(gq_ctx *c, unsigned limb0, unsigned nlimbs, uint64_t *ahat,
+                                const uint64_t *a, unsigned W) {
+  if (!c || !ahat || !a || nlimbs == 0) GQ_FAIL("bad argument");
+  const size_t nb = (size_t)W * c->n * 8, ob = (size_t)nlimbs * c->n * 8;
+  if (ensure_slot(c, GQ_SLOT_IO, nb) || ensure_slot(c, GQ_SLOT_LIMB_A, ob)) return 1;
+  uint64_t *din = (uint64_t *)c->slot[GQ_SLOT_IO], *dout = (uint64_t *)c->slot[GQ_SLOT_LIMB_A];
+  GQ_CUDA(cudaMemcpyAsync(din, a, nb, cudaMemcpyHostToDevice, c->stream));
+  if (decompose_dev(c, limb0, nlimbs, ptrs(din), W, 1, dout, c->stream)) return 1;
+  GQ_CUDA(cudaMemcpyAsync(ahat, dout, ob, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int gq_poly_rns2mpi(gq_ctx *c, unsigned dim, uint64_t *r, unsigned Wr, const uint64_t *rhat,
+                               const uint64_t *qw, unsigned q_words) {
+  if (!c || !r || !rhat || !qw || Wr == 0) GQ_FAIL("bad argument");
+  GqModulus m;
+  if (adhoc_modulus(c, qw, q_words, &m)) return 1;
+  const size_t ib = (size_t)dim * c->n * 8, ob = (size_t)Wr * c->n * 8;
+  if (ensure_slot(c, GQ_SLOT_LIMB_A, ib) || ensure_slot(c, GQ_SLOT_IO, ob)) return 1;
+  uint64_t *din = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *dout = (uint64_t *)c->slot[GQ_SLOT_IO];
+  GQ_CUDA(cudaMemcpyAsync(din, rhat, ib, cudaMemcpyHostToDevice, c->stream));
+  if (reconstruct_dev(c, dim, din, m, ptrs(dout), Wr, 1, c->stream)) return 1;
+  GQ_CUDA(cudaMemcpyAsync(r, dout, ob, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int gq_poly_mul(gq_ctx *c, uint64_t *r, unsigned Wr, const uint64_t *a, const uint64_t *b,
+                           unsigned W, unsigned dim, const uint64_t *qw, unsigned q_words) {
+  if (!c || !r || !a || !b || !qw) GQ_FAIL("bad argument");
+  if (!ntt_ok(c, 0, dim)) GQ_FAIL("dim invalid or modulus below 32 bits");
+  GqModulus m;
+  if (adhoc_modulus(c, qw, q_words, &m)) return 1;
+  const size_t n = c->n, ib = (size_t)W * n * 8, ob = (size_t)Wr * n * 8;
+  if (ensure_slot(c, GQ_SLOT_IO, 2 * ib + ob) || ensure_slot(c, GQ_SLOT_LIMB_A, 2 * dim * n * 8) ||
+      ensure_slot(c, GQ_SLOT_LIMB_B, dim * n * 8)) return 1;
+  uint64_t *io = (uint64_t *)c->slot[GQ_SLOT_IO], *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A],
+           *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
+  uint64_t *da = io, *db = io + (size_t)W * n, *dr = io + 2 * (size_t)W * n;
+  cudaStream_t st = c->stream;
+  GQ_CUDA(cudaMemcpyAsync(da, a, ib, cudaMemcpyHostToDevice, st));
+  GQ_CUDA(cudaMemcpyAsync(db, b, ib, cudaMemcpyHostToDevice, st));
+  if (decompose_dev(c, 0, dim, ptrs(da, db), W, 2, A, st)) return 1;
+  if (gq_ntt_batch_dev(c, 0, dim, 2, A, 0, st)) return 1;
+  gq_launch_binary(c->d_primes, (int)n, 0, (int)dim, 1, true, B, A, A + (size_t)dim * n, st);
+  c->launches++;
+  if (gq_ntt_batch_dev(c, 0, dim, 1, B, 1, st)) return 1;
+  if (reconstruct_dev(c, dim, B, m, ptrs(dr), Wr, 1, st)) return 1;
+  GQ_CUDA(cudaMemcpyAsync(r, dr, ob, cudaMemcpyDeviceToHost, st));
+  GQ_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+static uint64_t galois_rot(const gq_ctx *c, uint64_t rot) {   // 5^rot mod 2n (poly.c:265-268)
+  uint64_t g = 1, m = 2ull * c->n;
+  uint64_t b = 5, e = rot;
+  while (e) { if (e & 1) g = (g * b) % m; b = (b * b) % m; e >>= 1; }
+  return g;
+}
+
+static int automorph_host(gq_ctx *c, uint64_t *r, const uint64_t *a, unsigned W, uint64_t g) {
+  if (!c || !r || !a || W == 0 || W > GQ_MAX_W) GQ_FAIL("bad argument");
+  const size_t nb = (size_t)W * c->n * 8;
+  if (ensure_slot(c, GQ_SLOT_IO, 2 * nb)) return 1;
+  uint64_t *din = (uint64_t *)c->slot[GQ_SLOT_IO], *dout = din + (size_t)W * c->n;
+  GQ_CUDA(cudaMemcpyAsync(din, a, nb, cudaMemcpyHostToDevice, c->stream));
+  gq_launch_automorph((int)c->n, (int)W, ptrs(dout), ptrs(din), 1, g, c->stream);
+  c->launches++;
+  GQ_CHECK_LAUNCH(c);
+  GQ_CUDA(cudaMemcpyAsync(r, dout, nb, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+extern "C" int gq_poly_rot(gq_ctx *c, uint64_t *r, const uint64_t *a, unsigned W, uint64_t rot) {
+  if (!c) GQ_FAIL("null context");
+  return automorph_host(c, r, a, W, galois_rot(c, rot));
+}
+extern "C" int gq_poly_conj(gq_ctx *c, uint64_t *r, const uint64_t *a, unsigned W) {
+  if (!c) GQ_FAIL("null context");
+  return automorph_host(c, r, a, W, 2ull * c->n - 1);
+}
+
+// ---------------------------------------------------------------------- evaluation keys
+extern "C" int gq_evk_create(gq_ctx *c, gq_evk **evk, const uint64_t *p0, const uint64_t *p1) {
+  if (!c || !evk || !p0 || !p1 || !c->has_he) GQ_FAIL("bad argument");
+  if (c->dimevk > c->dimub) GQ_FAIL("hectx.dimevk exceeds polyctx.dimub: no evaluation key exists for these parameters");
+  const size_t bytes = (size_t)c->dimevk * c->n * 8;
+  gq_evk *e = new gq_evk();
+  e->ctx = c;
+  GQ_CUDA(cudaMalloc((void **)&e->p0, bytes));
+  GQ_CUDA(cudaMalloc((void **)&e->p1, bytes));
+  GQ_CUDA(cudaMemcpy(e->p0, p0, bytes, cudaMemcpyHostToDevice));
+  GQ_CUDA(cudaMemcpy(e->p1, p1, bytes, cudaMemcpyHostToDevice));
+  *evk = e;
+  return 0;
+}
+extern "C" int gq_evk_create_dev(gq_ctx *c, gq_evk **evk, const uint64_t *p0, const uint64_t *p1) {
+  if (!c || !evk || !p0 || !p1 || !c->has_he) GQ_FAIL("bad argument");
+  gq_evk *e = new gq_evk();
+  e->ctx = c; e->p0 = (uint64_t *)p0; e->p1 = (uint64_t *)p1; e->owned = false;
+  *evk = e;
+  return 0;
+}
+extern "C" void gq_evk_destroy(gq_evk *e) {
+  if (!e) return;
+  if (e->owned) { cudaFree(e->p0); cudaFree(e->p1); }
+  delete e;
+}
+
+// ------------------------------------------------------------------ HE primitives (device)
+// Key switch shared by he_relin (he-mult.c:40-85) and he_swk (he-automorphism.c:40-85):
+//   out_k = smod_ql( rdiv(d * evk.p_k, P) + add_k ),  k = 0,1 ; add_k may be null.
+static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk *evk,
+                         const uint64_t *add0, const uint64_t *add1, uint64_t *c0, uint64_t *c1,
+                         cudaStream_t st) {
+  const unsigned D2 = dim_ks(c, l), n = c->n, W = c->W;
+  if (D2 > c->dimevk) GQ_FAIL("key-switch basis exceeds dimevk");
+  if (!ntt_ok(c, 0, D2)) GQ_FAIL("modulus below 32 bits");
+  if (ensure_slot(c, GQ_SLOT_LIMB_A, (size_t)4 * c->dimub * n * 8) ||
+      ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8)) return 1;
+  uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
+  if (decompose_dev(c, 0, D2, ptrs(d), W, 1, A, st)) return 1;
+  if (gq_ntt_batch_dev(c, 0, D2, 1, A, 0, st)) return 1;
+  gq_launch_mul_evk(c->d_primes, (int)n, (int)D2, B, A, evk->p0, evk->p1, st);
+  c->launches++;
+  if (gq_ntt_batch_dev(c, 0, D2, 2, B, 1, st)) return 1;
+  const GqHostModulus &qm = c->qmod[l];
+  int r;
+  if (qm.dev.is_pow2) {
+    r = gq_launch_ks_epilogue(c->basis[D2 - 1].dev, c->basis[c->dim - 1].dev, c->d_Pinv, c->d_primes,
+                              (int)n, B, qm.dev.k, ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st);
+  } else {
+    r = gq_launch_ks_epilogue_general(c->basis[D2 - 1].dev, c->d_Pwords, (int)c->P.w.size(),
+                                      c->d_Pwords + GQ_MAX_W, c->d_primes, (int)n, B, qm.dev,
+                                      ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st);
+  }
+  if (r < 0) GQ_FAIL("no key-switch epilogue kernel for these widths");
+  c->launches++;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+
+static int he_check(const gq_ctx *c, unsigned l) {
+  if (!c) GQ_FAIL("null context");
+  if (!c->has_he) GQ_FAIL("context was created without Delta (polyctx only)");
+  if (l > c->L) GQ_FAIL("level out of range");
+  return 0;
+}
+
+extern "C" int gq_he_mul_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                             const uint64_t *a1, const uint64_t *b0, const uint64_t *b1,
+                             const gq_evk *rlk, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !a0 || !a1 || !b0 || !b1 || !rlk) GQ_FAIL("null argument");
+  cudaStream_t st = pick(c, stream);
+  const unsigned D1 = dim_tensor(c, l), n = c->n, W = c->W;
+  if (D1 > c->dimub) GQ_FAIL("tensor basis exceeds dimub");
+  if (!ntt_ok(c, 0, D1)) GQ_FAIL("modulus below 32 bits");
+  if (ensure_slot(c, GQ_SLOT_LIMB_A, (size_t)4 * c->dimub * n * 8) ||
+      ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8) ||
+      ensure_slot(c, GQ_SLOT_BIG, (size_t)5 * W * n * 8)) return 1;
+  uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
+  uint64_t *big = (uint64_t *)c->slot[GQ_SLOT_BIG];
+  uint64_t *d0 = big, *d1 = big + (size_t)W * n, *d2 = big + 2 * (size_t)W * n;
+  // hot loop A (he-mult.c:116-138): decompose, forward NTT, tensor, inverse NTT
+  if (decompose_dev(c, 0, D1, ptrs(a0, a1, b0, b1), W, 4, A, st)) return 1;
+  if (gq_ntt_batch_dev(c, 0, D1, 4, A, 0, st)) return 1;
+  gq_launch_tensor(c->d_primes, (int)n, (int)D1, B, A, st);
+  c->launches++;
+  if (gq_ntt_batch_dev(c, 0, D1, 3, B, 1, st)) return 1;
+  // hot loop B (he-mult.c:139-141): d0, d1, d2 mod q_l
+  if (reconstruct_dev(c, D1, B, c->qmod[l].dev, ptrs(d0, d1, d2), W, 3, st)) return 1;
+  // he_relin (he-mult.c:143)
+  return keyswitch_dev(c, l, d2, rlk, d0, d1, c0, c1, st);
+}
+
+extern "C" int gq_he_mulpt_dev(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
+                               const uint64_t *a0, const uint64_t *a1, const uint64_t *m, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !a0 || !a1 || !m) GQ_FAIL("null argument");
+  if (dim == 0 || dim > c->dimub) GQ_FAIL("dim out of range");
+  if (!ntt_ok(c, 0, dim)) GQ_FAIL("modulus below 32 bits");
+  cudaStream_t st = pick(c, stream);
+  const unsigned n = c->n, W = c->W;
+  if (ensure_slot(c, GQ_SLOT_LIMB_A, (size_t)4 * c->dimub * n * 8) ||
+      ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8)) return 1;
+  uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
+  if (decompose_dev(c, 0, dim, ptrs(a0, a1, m), W, 3, A, st)) return 1;
+  if (gq_ntt_batch_dev(c, 0, dim, 3, A, 0, st)) return 1;
+  gq_launch_mul_pt(c->d_primes, (int)n, (int)dim, B, A, st);
+  c->launches++;
+  if (gq_ntt_batch_dev(c, 0, dim, 2, B, 1, st)) return 1;
+  return reconstruct_dev(c, dim, B, c->qmod[l].dev, ptrs(c0, c1), W, 2, st);
+}
+
+static int rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, bool divide, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (l == 0) GQ_FAIL("cannot go below level 0");
+  if (!c0 || !c1) GQ_FAIL("null argument");
+  cudaStream_t st = pick(c, stream);
+  const GqHostModulus &qm = c->qmod[l - 1];
+  const bool dpow2 = (c->Delta & (c->Delta - 1)) == 0;
+  if (qm.dev.is_pow2 && (dpow2 || !divide))
+    gq_launch_rescale_pow2((int)c->n, (int)c->W, ptrs(c0, c1), 2, divide ? c->logDelta : 0, qm.dev.k, st);
+  else
+    gq_launch_rescale_general((int)c->n, (int)c->W, ptrs(c0, c1), 2, divide ? c->Delta : 1, qm.dev, st);
+  c->launches++;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+extern "C" int gq_he_rs_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, void *s) {
+  return rescale_dev(c, l, c0, c1, true, s);
+}
+extern "C" int gq_he_moddown_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, void *s) {
+  return rescale_dev(c, l, c0, c1, false, s);
+}
+
+static int automorph_ks_dev(gq_ctx *c, unsigned l, uint64_t g, uint64_t *c0, uint64_t *c1,
+                            const gq_evk *swk, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !swk) GQ_FAIL("null argument");
+  cudaStream_t st = pick(c, stream);
+  const unsigned n = c->n, W = c->W;
+  if (ensure_slot(c, GQ_SLOT_BIG, (size_t)5 * W * n * 8)) return 1;
+  uint64_t *big = (uint64_t *)c->slot[GQ_SLOT_BIG];
+  uint64_t *d0 = big + 3 * (size_t)W * n, *d1 = big + 4 * (size_t)W * n;
+  gq_launch_automorph((int)n, (int)W, ptrs(d0, d1), ptrs(c0, c1), 2, g, st);
+  c->launches++;
+  // he_swk: only c0 receives the additive term (he-automorphism.c:73)
+  return keyswitch_dev(c, l, d1, swk, d0, nullptr, c0, c1, st);
+}
+extern "C" int gq_he_rot_dev(gq_ctx *c, unsigned l, unsigned rot, uint64_t *c0, uint64_t *c1,
+                             const gq_evk *rk, void *s) {
+  if (!c) GQ_FAIL("null context");
+  return automorph_ks_dev(c, l, galois_rot(c, rot), c0, c1, rk, s);
+}
+extern "C" int gq_he_conj_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const gq_evk *ck, void *s) {
+  if (!c) GQ_FAIL("null context");
+  return automorph_ks_dev(c, l, 2ull * c->n - 1, c0, c1, ck, s);
+}
+
+// -------------------------------------------------------------- HE primitives (host buffers)
+// stage up to 5 big polys in, run, copy up to 2 out
+struct HostIO {
+  gq_ctx *c; uint64_t *base; size_t poly;
+  uint64_t *in(int k) const { return base + (size_t)k * poly; }
+};
+static int io_begin(gq_ctx *c, HostIO *io, const uint64_t *const *src, int nsrc) {
+  io->c = c; io->poly = (size_t)c->W * c->n;
+  if (ensure_slot(c, GQ_SLOT_IO, 7 * io->poly * 8)) return 1;
+  io->base = (uint64_t *)c->slot[GQ_SLOT_IO];
+  for (int k = 0; k < nsrc; k++)
+    GQ_CUDA(cudaMemcpyAsync(io->in(k), src[k], io->poly * 8, cudaMemcpyHostToDevice, c->stream));
+  return 0;
+}
+static int io_end(HostIO *io, uint64_t *c0, uint64_t *c1, int k0, int k1) {
+  gq_ctx *c = io->c;
+  GQ_CUDA(cudaMemcpyAsync(c0, io->in(k0), io->poly * 8, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaMemcpyAsync(c1, io->in(k1), io->poly * 8, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int gq_he_mul(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                         const uint64_t *a1, const uint64_t *b0, const uint64_t *b1, const gq_evk *rlk) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !a0 || !a1 || !b0 || !b1) GQ_FAIL("null argument");
+  HostIO io; const uint64_t *src[4] = {a0, a1, b0, b1};
+  if (io_begin(c, &io, src, 4)) return 1;
+  if (gq_he_mul_dev(c, l, io.in(5), io.in(6), io.in(0), io.in(1), io.in(2), io.in(3), rlk, nullptr)) return 1;
+  return io_end(&io, c0, c1, 5, 6);
+}
+extern "C" int gq_he_mulpt(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
+                           const uint64_t *a0, const uint64_t *a1, const uint64_t *m) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !a0 || !a1 || !m) GQ_FAIL("null argument");
+  HostIO io; const uint64_t *src[3] = {a0, a1, m};
+  if (io_begin(c, &io, src, 3)) return 1;
+  if (gq_he_mulpt_dev(c, l, dim, io.in(5), io.in(6), io.in(0), io.in(1), io.in(2), nullptr)) return 1;
+  return io_end(&io, c0, c1, 5, 6);
+}
+static int inplace_host(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, int op, unsigned rot,
+                        const gq_evk *k) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1) GQ_FAIL("null argument");
+  HostIO io; const uint64_t *src[2] = {c0, c1};
+  if (io_begin(c, &io, src, 2)) return 1;
+  int r = 1;
+  switch (op) {
+    case 0: r = gq_he_rs_dev(c, l, io.in(0), io.in(1), nullptr); break;
+    case 1: r = gq_he_moddown_dev(c, l, io.in(0), io.in(1), nullptr); break;
+    case 2: r = gq_he_rot_dev(c, l, rot, io.in(0), io.in(1), k, nullptr); break;
+    case 3: r = gq_he_conj_dev(c, l, io.in(0), io.in(1), k, nullptr); break;
+  }
+  if (r) return 1;
+  return io_end(&io, c0, c1, 0, 1);
+}
+extern "C" int gq_he_rs(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1) { return inplace_host(c, l, c0, c1, 0, 0, nullptr); }
+extern "C" int gq_he_moddown(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1) { return inplace_host(c, l, c0, c1, 1, 0, nullptr); }
+extern "C" int gq_he_rot(gq_ctx *c, unsigned l, unsigned rot, uint64_t *c0, uint64_t *c1, const gq_evk *rk) {
+  return inplace_host(c, l, c0, c1, 2, rot, rk);
+}
+extern "C" int gq_he_conj(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const gq_evk *ck) {
+  return inplace_host(c, l, c0, c1, 3, 0, ck);
+}

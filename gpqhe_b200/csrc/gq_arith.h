@@ -1,0 +1,90 @@
+// gq_arith.h - 64-bit modular arithmetic for the RNS limb layer.
+//
+// Replaces src/reduce.c (montgomery_reduce :59, barrett_reduce :88).  The reference
+// keeps twiddles in Montgomery form and reduces every product with a 128-bit
+// Montgomery step; the outputs that matter are the *canonical residues* it stores.
+// We reach the same canonical residues with Shoup multiplication by precomputed
+// constants (w, floor(w*2^64/p)): one mulhi + two mullo on the integer pipe and a
+// shorter dependency chain than Montgomery.  Products of two variables use the
+// reference's own Barrett step so that poly_rns_mul/add agree for *any* input the
+// reference accepts (a < 2^(2*bits(p))).
+#pragma once
+#include "gq_platform.h"
+
+GQ_HD uint64_t gq_mulhi(uint64_t a, uint64_t b) {
+#if defined(__CUDA_ARCH__)
+  return __umul64hi(a, b);
+#else
+  return (uint64_t)(((gq_u128)a * b) >> 64);
+#endif
+}
+
+// Per-prime constants (device image of one struct rns_ctx node, src/poly.h:28-41).
+struct GqPrime {
+  uint64_t p;          // the prime
+  uint64_t pinv_mont;  // p^-1 mod 2^64                   (montgomery_inv, src/reduce.c:36)
+  uint64_t pinv_barr;  // floor(2^(2*bits(p)) / p)        (barrett_inv,    src/reduce.c:75)
+  uint64_t ninv_mont;  // N^-1 * 2^64 mod p               (ntt_init,       src/precomp.c:248)
+  uint64_t ninv;       // N^-1 mod p (plain)
+  uint64_t ninv_sh;    // floor(ninv * 2^64 / p)
+  uint32_t barr_shift; // 2*bits(p) - 64
+  uint32_t bits;       // bits(p)
+};
+
+// x*w mod p, canonical, for any x < 2^64, w < p < 2^63, wsh = floor(w*2^64/p).
+GQ_HD uint64_t gq_mul_shoup(uint64_t x, uint64_t w, uint64_t wsh, uint64_t p) {
+  uint64_t q = gq_mulhi(x, wsh);
+  uint64_t r = x * w - q * p;   // in [0, 2p)
+  return (r >= p) ? r - p : r;
+}
+
+// Same value as barrett_reduce(a, p, pinv_barr) of src/reduce.c:88-106 for a = hi:lo.
+GQ_HD uint64_t gq_barrett128(uint64_t lo, uint64_t hi, const GqPrime &P) {
+  // t = ((lo*mu)>>64) + hi*mu   (fits 128 bits for a < 2^(2k))
+  uint64_t t_lo = gq_mulhi(lo, P.pinv_barr);
+  uint64_t h_lo = hi * P.pinv_barr;
+  uint64_t h_hi = gq_mulhi(hi, P.pinv_barr);
+  uint64_t s_lo = t_lo + h_lo;
+  uint64_t s_hi = h_hi + (s_lo < t_lo ? 1u : 0u);
+  // t >>= shift  (0 <= shift < 64); only the low 64 bits of t*p are needed below
+  uint64_t t = (P.barr_shift == 0) ? s_lo : ((s_lo >> P.barr_shift) | (s_hi << (64 - P.barr_shift)));
+  uint64_t r = lo - t * P.p;
+  return (r < P.p) ? r : r - P.p;
+}
+
+GQ_HD uint64_t gq_mulmod_barrett(uint64_t a, uint64_t b, const GqPrime &P) {
+  return gq_barrett128(a * b, gq_mulhi(a, b), P);
+}
+
+GQ_HD uint64_t gq_addmod_barrett(uint64_t a, uint64_t b, const GqPrime &P) {
+  uint64_t lo = a + b;
+  uint64_t hi = (lo < a) ? 1u : 0u;
+  return gq_barrett128(lo, hi, P);
+}
+
+// montgomery_reduce of src/reduce.c:59-66 (used on the host to convert the
+// reference's Montgomery-form tables to plain residues).
+GQ_HD uint64_t gq_mont_reduce(uint64_t lo, uint64_t hi, uint64_t p, uint64_t pinv) {
+  uint64_t u = lo * pinv;
+  uint64_t t = gq_mulhi(u, p);
+  return (hi < t) ? hi - t + p : hi - t;
+}
+
+// Forward (Cooley-Tukey) butterfly with the reference's exact range rules
+// (src/ntt.c:46-48): the difference leg is canonical, the sum leg may hold p.
+GQ_HD void gq_bfly_fwd(uint64_t &x, uint64_t &y, uint64_t w, uint64_t wsh, uint64_t p) {
+  uint64_t t = gq_mul_shoup(y, w, wsh, p);
+  uint64_t d = (x >= t) ? x - t : x - t + p;
+  uint64_t s = (x <= p - t) ? x + t : x + t - p;
+  x = s;
+  y = d;
+}
+
+// Inverse (Gentleman-Sande) butterfly, src/ntt.c:63-67.
+GQ_HD void gq_bfly_inv(uint64_t &x, uint64_t &y, uint64_t w, uint64_t wsh, uint64_t p) {
+  uint64_t t = x, u = y;
+  uint64_t s = (u <= p - t) ? t + u : t + u - p;
+  uint64_t d = (u <= t) ? t - u : t - u + p;
+  x = s;
+  y = gq_mul_shoup(d, w, wsh, p);
+}

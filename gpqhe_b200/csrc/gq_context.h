@@ -1,0 +1,65 @@
+// gq_context.h - host-side context: the flattened, device-resident image of the
+// reference's process-global `polyctx` / `hectx` (src/precomp.c:38-47).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "gq_hostbig.h"
+#include "gq_kernels.h"
+
+struct GqHostBasis {
+  GqCrtBasis dev;   // device pointers
+  BigU P;
+  void *blob = nullptr;
+};
+
+struct GqHostModulus {
+  GqModulus dev;
+  BigU q;
+  void *blob = nullptr;
+};
+
+enum { GQ_SLOT_LIMB_A = 0, GQ_SLOT_LIMB_B, GQ_SLOT_BIG, GQ_SLOT_IO, GQ_SLOT_COUNT };
+
+struct gq_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  unsigned logn = 0, n = 0, logp = 59, dimub = 0, logqub = 0;
+  unsigned has_he = 0, L = 0, dim = 0, dimevk = 0, W = 0, q_is_pow2 = 0, slots = 0;
+  uint64_t Delta = 0;
+  unsigned logDelta = 0;      // valid when Delta is a power of two
+  BigU q, P, PqL;
+  std::vector<BigU> ql, qh;
+  std::vector<GqHostModulus> qmod;   // per level
+  std::vector<GqPrime> primes;
+  std::vector<GqHostBasis> basis;    // basis[D-1] for D = 1..dimub
+  // device tables
+  GqPrime *d_primes = nullptr;
+  ulonglong2 *d_tw_fwd = nullptr, *d_tw_inv = nullptr, *d_tw_inv_last = nullptr;
+  uint64_t *d_pow64 = nullptr, *d_t1sh = nullptr;
+  uint64_t *d_Pinv = nullptr;        // P^-1 mod 2^(64*GQ_MAX_W)
+  uint64_t *d_Pwords = nullptr;      // P and floor(P/2), GQ_MAX_W words each (general path)
+  uint64_t *d_adhoc = nullptr;       // scratch for an ad-hoc modulus (q, qh)
+  // growable device scratch
+  void *slot[GQ_SLOT_COUNT] = {nullptr, nullptr, nullptr, nullptr};
+  size_t slot_bytes[GQ_SLOT_COUNT] = {0, 0, 0, 0};
+  unsigned long long launches = 0;
+
+  GqNttTables ntt_tables() const {
+    GqNttTables t;
+    t.logn = (int)logn; t.n = (int)n; t.primes = d_primes;
+    t.tw_fwd = d_tw_fwd; t.tw_inv = d_tw_inv; t.tw_inv_last = d_tw_inv_last;
+    return t;
+  }
+  GqDecTables dec_tables() const {
+    GqDecTables t; t.primes = d_primes; t.pow64 = d_pow64; t.t1_sh = d_t1sh; return t;
+  }
+};
+
+struct gq_evk {
+  gq_ctx *ctx = nullptr;
+  uint64_t *p0 = nullptr, *p1 = nullptr;   // device, [dimevk][n] each
+  bool owned = true;
+};
+
+void gq_set_error(const std::string &msg);

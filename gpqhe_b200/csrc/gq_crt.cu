@@ -1,0 +1,441 @@
+// gq_crt.cu - the MPI <-> RNS crossings on the device.
+//   K4 k_decompose      rns_decompose                      src/rns.c:37-48
+//   K5 k_reconstruct    poly_rns2mpi = rns_reconstruct + 2x mpi_smod
+//                                                          src/rns.c:60-75, src/poly.c:109-120
+//   K6 k_ks_epilogue    poly_rns2mpi(P*q_l) + mpi_rdiv(P) + mpi_addm + mpi_smod
+//                                                          src/he-mult.c:67-77, src/he-automorphism.c:68-76
+// One thread owns one coefficient; multiword integers live in registers (compile-time
+// width WT, fully unrolled), CRT constants are staged in shared memory and read as
+// warp broadcasts, limb-poly reads / word-major writes are coalesced across threads.
+//
+// Exactness notes.
+//  * rns_reconstruct returns sum_d a_d*(phat_d*inv_d mod P) mod P in [0,P).  We compute
+//    y_d = a_d*inv_d mod p_d, S = sum_d y_d*phat_d (S == that sum mod P, S < D*P), then
+//    S mod P exactly: a 64-bit quotient estimate from the top bits that never
+//    overshoots, followed by exact compare-and-subtract.
+//  * Key switch: the reference reduces T = centred CRT value first to x = T smod (P*q_l),
+//    then takes rdiv(x,P) and reduces mod q_l.  x = T + m*P*q_l for an integer m, so
+//    floor(x/P) = floor(T/P) + m*q_l and x mod P = T mod P: the smod(P*q_l) step cannot
+//    change the final residue mod q_l and is skipped.  floor(T/P) = (T - r)/P with
+//    r = T mod P = CRT of the first `dim` residues; the division is exact, so modulo
+//    2^(64*WP) it is a multiplication by P^-1 mod 2^(64*WP).
+#include "gq_bigint.h"
+#include "gq_kernels.h"
+
+namespace {
+
+template <int WT> struct MaxD { static constexpr int v = WT + WT / 8 + 2; };
+
+template <int WT>
+struct CrtShared {
+  uint64_t phat[MaxD<WT>::v * WT];
+  uint64_t P[WT + 1];
+  uint64_t Ph[WT + 1];
+  uint64_t inv[MaxD<WT>::v];
+  uint64_t inv_sh[MaxD<WT>::v];
+  uint64_t p[MaxD<WT>::v];
+};
+
+template <int WT>
+GQ_DEV void crt_stage(CrtShared<WT> &S, const GqCrtBasis &B, const GqPrime *primes) {
+  for (int j = threadIdx.x; j < B.D * WT; j += blockDim.x) S.phat[j] = B.phat[j];
+  for (int j = threadIdx.x; j <= WT; j += blockDim.x) {
+    S.P[j] = (j < WT) ? B.P[j] : 0;
+    S.Ph[j] = (j < WT) ? B.Ph[j] : 0;
+  }
+  for (int j = threadIdx.x; j < B.D; j += blockDim.x) {
+    S.inv[j] = B.inv[j];
+    S.inv_sh[j] = B.inv_sh[j];
+    S.p[j] = primes[j].p;
+  }
+}
+
+// acc[0..WT) <- (sum_d rhat[d][i] * C_d) mod P, in [0,P)
+template <int WT>
+GQ_DEV void crt_mod_P(uint64_t *acc, const CrtShared<WT> &S, const GqCrtBasis &B,
+                      const uint64_t *__restrict__ rhat, int n, int i) {
+#pragma unroll
+  for (int w = 0; w <= WT; w++) acc[w] = 0;
+  for (int d = 0; d < B.D; d++) {
+    uint64_t y = gq_mul_shoup(rhat[(size_t)d * n + i], S.inv[d], S.inv_sh[d], S.p[d]);
+    mw_mac<WT>(acc, y, &S.phat[d * WT]);
+  }
+  if (B.sh >= 0) {
+    const int sw = B.sh >> 6, sb = B.sh & 63;
+    uint64_t lo = 0, hi = 0;
+#pragma unroll
+    for (int w = 0; w <= WT; w++) {   // mask-select: a compare-and-assign chain would be
+      lo |= acc[w] & (0 - (uint64_t)(w == sw));        // turned into a dynamic index and
+      hi |= acc[w] & (0 - (uint64_t)(w == sw + 1));    // push acc[] out of registers
+    }
+    uint64_t top = sb ? ((lo >> sb) | (hi << (64 - sb))) : lo;
+    uint64_t k = gq_mulhi(top, B.recip) >> 56;
+    mw_mulsub<WT + 1>(acc, k, S.P);
+  }
+  for (int it = 0; it < B.D + 2; it++) {
+    if (!mw_geq<WT + 1>(acc, S.P)) break;
+    mw_sub<WT + 1>(acc, acc, S.P);
+  }
+}
+
+// mpi_smod(acc, P, P/2): acc in [0,P) -> [-ceil(P/2), floor(P/2)), two's complement WT words
+template <int WT>
+GQ_DEV void crt_centre(uint64_t *acc, const CrtShared<WT> &S) {
+  if (mw_geq<WT>(acc, S.Ph)) mw_sub<WT>(acc, acc, S.P);
+}
+
+// signed acc (WT words) -> mpi_smod(acc, q, qh) for a general modulus (slow, exact)
+template <int WT>
+GQ_DEV void smod_general(uint64_t *acc, const GqModulus &q) {
+  uint64_t u[WT];
+  const bool neg = (acc[WT - 1] >> 63) != 0;
+#pragma unroll
+  for (int w = 0; w < WT; w++) u[w] = acc[w];
+  if (neg) mw_neg<WT>(u);
+  gq_divrem(u, WT, q.q, q.nwords, nullptr);   // u[0..nwords) = |acc| mod q
+  bool zero = true;
+  for (int w = 0; w < q.nwords; w++) zero = zero && (u[w] == 0);
+  uint64_t qq[WT], hh[WT];
+#pragma unroll
+  for (int w = 0; w < WT; w++) { qq[w] = (w < q.nwords) ? q.q[w] : 0; hh[w] = (w < q.nwords) ? q.qh[w] : 0; }
+  if (neg && !zero) mw_sub<WT>(u, qq, u);      // floor-mod of a negative value
+  if (mw_geq<WT>(u, hh)) mw_sub<WT>(u, u, qq);
+#pragma unroll
+  for (int w = 0; w < WT; w++) acc[w] = u[w];
+}
+
+template <int WT>
+GQ_DEV void store_words(uint64_t *__restrict__ out, int n, int i, int Wout, const uint64_t *acc) {
+  const uint64_t fill = (acc[WT - 1] >> 63) ? ~(uint64_t)0 : 0;
+#pragma unroll
+  for (int w = 0; w < WT; w++)
+    if (w < Wout) out[(size_t)w * n + i] = acc[w];
+  for (int w = WT; w < Wout; w++) out[(size_t)w * n + i] = fill;
+}
+
+// ---- K5 ---------------------------------------------------------------------------
+// batch: poly b reads rhat + b*D*n, writes out.p[b]
+template <int WT, bool POW2>
+__global__ void __launch_bounds__(128)
+k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
+              const uint64_t *__restrict__ rhat, GqModulus q, GqPtrs4 out, int Wout) {
+  __shared__ CrtShared<WT> S;
+  crt_stage<WT>(S, B, primes);
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = blockIdx.y;
+  uint64_t acc[WT + 1];
+  crt_mod_P<WT>(acc, S, B, rhat + (size_t)b * B.D * n, n, i);
+  crt_centre<WT>(acc, S);
+  if (POW2) {
+    if (q.k < 64u * WT) mw_smod_pow2<WT>(acc, q.k);
+  } else {
+    smod_general<WT>(acc, q);
+  }
+  store_words<WT>(out.p[b], n, i, Wout, acc);
+}
+
+// ---- K6 (power-of-two q_l fast path) ------------------------------------------------
+// B  : key-switch basis (D2 limbs), BP : basis of the special modulus P (`dim` limbs)
+// Pinv: P^-1 mod 2^(64*WP).  add.p[b]: additive big poly (Wadd words) or null.
+template <int WT, int WP>
+__global__ void __launch_bounds__(128)
+k_ks_epilogue(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
+              const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
+              unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout) {
+  __shared__ CrtShared<WT> S;
+  __shared__ CrtShared<WP> SP;
+  __shared__ uint64_t sPinv[WP];
+  crt_stage<WT>(S, B, primes);
+  crt_stage<WP>(SP, BP, primes);
+  for (int j = threadIdx.x; j < WP; j += blockDim.x) sPinv[j] = Pinv[j];
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = blockIdx.y;
+  const uint64_t *ch = chat + (size_t)b * B.D * n;
+  uint64_t T[WT + 1];
+  crt_mod_P<WT>(T, S, B, ch, n, i);
+  crt_centre<WT>(T, S);
+  uint64_t r[WP + 1];
+  crt_mod_P<WP>(r, SP, BP, ch, n, i);            // r = T mod P in [0,P)
+  const bool round_up = !mw_geq<WP>(SP.Ph, r);     // r > floor(P/2)
+  // low WP words of T - r
+  uint64_t x[WP];
+  {
+    uint64_t tl[WP];
+#pragma unroll
+    for (int w = 0; w < WP; w++) tl[w] = (w < WT) ? T[w] : ((T[WT - 1] >> 63) ? ~(uint64_t)0 : 0);
+    mw_sub<WP>(x, tl, r);
+  }
+  // Q = x * Pinv mod 2^(64*WP)  (exact quotient modulo 2^(64*WP))
+  uint64_t Q[WP];
+#pragma unroll
+  for (int w = 0; w < WP; w++) Q[w] = 0;
+#pragma unroll
+  for (int a = 0; a < WP; a++) {
+    uint64_t carry = 0;
+#pragma unroll
+    for (int c = 0; c + a < WP; c++) {
+      gq_u128 t = (gq_u128)x[a] * sPinv[c] + Q[a + c] + carry;
+      Q[a + c] = (uint64_t)t;
+      carry = (uint64_t)(t >> 64);
+    }
+  }
+  // + rounding + additive term (sign-extended to WP words)
+  uint64_t ad[WP];
+  if (add.p[b]) {
+    const uint64_t *ap = add.p[b];
+    uint64_t top = 0;
+#pragma unroll
+    for (int w = 0; w < WP; w++) {
+      if (w < Wadd) { ad[w] = ap[(size_t)w * n + i]; top = ad[w]; }
+    }
+    const uint64_t fill = (top >> 63) ? ~(uint64_t)0 : 0;
+#pragma unroll
+    for (int w = 0; w < WP; w++) if (w >= Wadd) ad[w] = fill;
+  } else {
+#pragma unroll
+    for (int w = 0; w < WP; w++) ad[w] = 0;
+  }
+  {
+    uint64_t carry = round_up ? 1u : 0u;
+#pragma unroll
+    for (int w = 0; w < WP; w++) {
+      gq_u128 t = (gq_u128)Q[w] + ad[w] + carry;
+      Q[w] = (uint64_t)t;
+      carry = (uint64_t)(t >> 64);
+    }
+  }
+  mw_smod_pow2<WP>(Q, k);
+  store_words<WP>(out.p[b], n, i, Wout, Q);
+}
+
+// ---- K6, general modulus: exact long division by P (slow path) -----------------------
+template <int WT>
+__global__ void __launch_bounds__(128)
+k_ks_epilogue_general(GqCrtBasis B, const uint64_t *__restrict__ Pw, int nP,
+                      const uint64_t *__restrict__ Phw, const GqPrime *__restrict__ primes, int n,
+                      const uint64_t *__restrict__ chat, GqModulus q, GqPtrs4 add, int Wadd,
+                      GqPtrs4 out, int Wout) {
+  __shared__ CrtShared<WT> S;
+  crt_stage<WT>(S, B, primes);
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = blockIdx.y;
+  uint64_t T[WT + 1];
+  crt_mod_P<WT>(T, S, B, chat + (size_t)b * B.D * n, n, i);
+  crt_centre<WT>(T, S);
+  const bool neg = (T[WT - 1] >> 63) != 0;
+  uint64_t u[WT], quot[WT + 1], Pl[WT], Phl[WT];
+#pragma unroll
+  for (int w = 0; w < WT; w++) {
+    u[w] = T[w]; quot[w] = 0;
+    Pl[w] = (w < nP) ? Pw[w] : 0;
+    Phl[w] = (w < nP) ? Phw[w] : 0;
+  }
+  quot[WT] = 0;
+  if (neg) mw_neg<WT>(u);
+  gq_divrem(u, WT, Pl, nP, quot);              // |T| = quot*P + u
+  for (int w = WT - nP + 1; w < WT; w++) quot[w] = 0;
+  bool zero = true;
+  for (int w = 0; w < nP; w++) zero = zero && (u[w] == 0);
+  if (neg && !zero) {                          // floor: -(quot+1), remainder P - u
+    uint64_t cy = 1;
+    for (int w = 0; w < WT && cy; w++) { quot[w] += 1; cy = (quot[w] == 0); }
+    mw_sub<WT>(u, Pl, u);
+  }
+  const bool up = !mw_geq<WT>(Phl, u);         // remainder > floor(P/2)
+  if (neg) mw_neg<WT>(quot);
+  uint64_t ad[WT];
+  if (add.p[b]) {
+    const uint64_t *ap = add.p[b];
+    uint64_t top = 0;
+#pragma unroll
+    for (int w = 0; w < WT; w++)
+      if (w < Wadd) { ad[w] = ap[(size_t)w * n + i]; top = ad[w]; }
+    const uint64_t fill = (top >> 63) ? ~(uint64_t)0 : 0;
+#pragma unroll
+    for (int w = 0; w < WT; w++) if (w >= Wadd) ad[w] = fill;
+  } else {
+#pragma unroll
+    for (int w = 0; w < WT; w++) ad[w] = 0;
+  }
+  uint64_t carry = up ? 1u : 0u;
+#pragma unroll
+  for (int w = 0; w < WT; w++) {
+    gq_u128 t = (gq_u128)quot[w] + ad[w] + carry;
+    quot[w] = (uint64_t)t;
+    carry = (uint64_t)(t >> 64);
+  }
+  if (q.is_pow2) {
+    if (q.k < 64u * WT) mw_smod_pow2<WT>(quot, q.k);
+  } else {
+    smod_general<WT>(quot, q);
+  }
+  store_words<WT>(out.p[b], n, i, Wout, quot);
+}
+
+// ---- K4 ---------------------------------------------------------------------------
+// (lo,hi) 128-bit value -> canonical residue mod p
+GQ_DEV uint64_t reduce128(uint64_t lo, uint64_t hi, const GqPrime &P, uint64_t T1, uint64_t T1sh) {
+  if (P.bits >= 32) {
+    uint64_t r1 = gq_mul_shoup(hi, T1, T1sh, P.p);
+    uint64_t r2 = gq_barrett128(lo, 0, P);
+    uint64_t s = r1 + r2;
+    return (s >= P.p) ? s - P.p : s;
+  }
+  gq_u128 v = ((gq_u128)hi << 64) | lo;
+  return (uint64_t)(v % P.p);
+}
+
+template <int W>
+__global__ void __launch_bounds__(256)
+k_decompose(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *__restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = blockIdx.y;
+  const uint64_t *src = in.p[b];
+  uint64_t *dst = out + (size_t)b * nlimbs * n;
+  uint64_t x[W];
+#pragma unroll
+  for (int w = 0; w < W; w++) x[w] = src[(size_t)w * n + i];
+  const bool neg = (x[W - 1] >> 63) != 0;
+  for (int d = 0; d < nlimbs; d++) {
+    const GqPrime P = dt.primes[limb0 + d];
+    const uint64_t *T = dt.pow64 + (size_t)(limb0 + d) * GQ_DEC_W;
+    const uint64_t T1 = __ldg(&T[1]), T1sh = __ldg(&dt.t1_sh[limb0 + d]);
+    // 192-bit accumulator of sum_w x_w * (2^(64w) mod p)
+    uint64_t a0 = x[0], a1 = 0, a2 = 0;
+#pragma unroll
+    for (int w = 1; w < W; w++) {
+      gq_u128 t = (gq_u128)x[w] * __ldg(&T[w]);
+      uint64_t tl = (uint64_t)t, th = (uint64_t)(t >> 64);
+      a0 += tl;
+      uint64_t c = a0 < tl;
+      a1 += c;
+      uint64_t c2 = a1 < c;
+      a1 += th;
+      c2 += a1 < th;
+      a2 += c2;
+    }
+    // fold: a0 + a1*T1 + a2*T2  < 2^125
+    gq_u128 v = (gq_u128)a1 * T1 + a0;
+    if (W > 2) v += (gq_u128)a2 * __ldg(&T[2]);
+    uint64_t r = reduce128((uint64_t)v, (uint64_t)(v >> 64), P, T1, T1sh);
+    if (neg) {
+      const uint64_t TW = __ldg(&T[W]);
+      r = (r >= TW) ? r - TW : r - TW + P.p;
+    }
+    dst[(size_t)d * n + i] = r;
+  }
+}
+
+}  // namespace
+
+// ---- launchers --------------------------------------------------------------------
+#define GQ_WT_SWITCH(WTV, STMT8, STMT16, STMT24, STMT32) \
+  switch (WTV) { case 8: STMT8; break; case 16: STMT16; break; case 24: STMT24; break; \
+                 case 32: STMT32; break; default: return -1; }
+
+int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
+                          const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
+                          cudaStream_t st) {
+  dim3 grid((n + 127) / 128, npolys), block(128);
+  if (q.is_pow2) {
+    GQ_WT_SWITCH(B.WT,
+      GQ_LAUNCH((k_reconstruct<8, true>), grid, block, st, B, primes, n, rhat, q, out, Wout),
+      GQ_LAUNCH((k_reconstruct<16, true>), grid, block, st, B, primes, n, rhat, q, out, Wout),
+      GQ_LAUNCH((k_reconstruct<24, true>), grid, block, st, B, primes, n, rhat, q, out, Wout),
+      GQ_LAUNCH((k_reconstruct<32, true>), grid, block, st, B, primes, n, rhat, q, out, Wout))
+  } else {
+    GQ_WT_SWITCH(B.WT,
+      GQ_LAUNCH((k_reconstruct<8, false>), grid, block, st, B, primes, n, rhat, q, out, Wout),
+      GQ_LAUNCH((k_reconstruct<16, false>), grid, block, st, B, primes, n, rhat, q, out, Wout),
+      GQ_LAUNCH((k_reconstruct<24, false>), grid, block, st, B, primes, n, rhat, q, out, Wout),
+      GQ_LAUNCH((k_reconstruct<32, false>), grid, block, st, B, primes, n, rhat, q, out, Wout))
+  }
+  return 1;
+}
+
+template <int WT>
+static int ks_dispatch_wp(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
+                          const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
+                          const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, dim3 grid,
+                          cudaStream_t st) {
+  dim3 block(128);
+  if (BP.WT > WT) return -1;
+  switch (BP.WT) {
+    case 8:
+      GQ_LAUNCH((k_ks_epilogue<WT, 8>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout);
+      return 1;
+    case 16:
+      if (WT >= 16) {
+        GQ_LAUNCH((k_ks_epilogue<WT, (WT >= 16 ? 16 : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout);
+        return 1;
+      }
+      return -1;
+    case 24:
+      if (WT >= 24) {
+        GQ_LAUNCH((k_ks_epilogue<WT, (WT >= 24 ? 24 : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout);
+        return 1;
+      }
+      return -1;
+    case 32:
+      if (WT >= 32) {
+        GQ_LAUNCH((k_ks_epilogue<WT, (WT >= 32 ? 32 : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout);
+        return 1;
+      }
+      return -1;
+  }
+  return -1;
+}
+
+int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
+                          const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
+                          const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
+                          cudaStream_t st) {
+  dim3 grid((n + 127) / 128, npolys);
+  switch (B.WT) {
+    case 8: return ks_dispatch_wp<8>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st);
+    case 16: return ks_dispatch_wp<16>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st);
+    case 24: return ks_dispatch_wp<24>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st);
+    case 32: return ks_dispatch_wp<32>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st);
+  }
+  return -1;
+}
+
+template <int W>
+static void dec_launch(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
+                       uint64_t *out, int npolys, cudaStream_t st) {
+  dim3 grid((n + 255) / 256, npolys), block(256);
+  GQ_LAUNCH(k_decompose<W>, grid, block, st, dt, n, limb0, nlimbs, in, out);
+}
+
+int gq_launch_decompose(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
+                        int W, uint64_t *out, int npolys, cudaStream_t st) {
+  switch (W) {
+#define GQ_CASE(V) case V: dec_launch<V>(dt, n, limb0, nlimbs, in, out, npolys, st); return 1;
+    GQ_CASE(1) GQ_CASE(2) GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8)
+    GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12) GQ_CASE(13) GQ_CASE(14) GQ_CASE(15) GQ_CASE(16)
+    GQ_CASE(17) GQ_CASE(18) GQ_CASE(19) GQ_CASE(20) GQ_CASE(21) GQ_CASE(22) GQ_CASE(23) GQ_CASE(24)
+    GQ_CASE(25) GQ_CASE(26) GQ_CASE(27) GQ_CASE(28) GQ_CASE(29) GQ_CASE(30) GQ_CASE(31) GQ_CASE(32)
+#undef GQ_CASE
+  }
+  return -1;
+}
+
+int gq_launch_ks_epilogue_general(const GqCrtBasis &B, const uint64_t *P, int nP, const uint64_t *Ph,
+                                  const GqPrime *primes, int n, const uint64_t *chat,
+                                  const GqModulus &q, const GqPtrs4 &add, int Wadd,
+                                  const GqPtrs4 &out, int Wout, int npolys, cudaStream_t st) {
+  dim3 grid((n + 127) / 128, npolys), block(128);
+  GQ_WT_SWITCH(B.WT,
+    GQ_LAUNCH(k_ks_epilogue_general<8>, grid, block, st, B, P, nP, Ph, primes, n, chat, q, add, Wadd, out, Wout),
+    GQ_LAUNCH(k_ks_epilogue_general<16>, grid, block, st, B, P, nP, Ph, primes, n, chat, q, add, Wadd, out, Wout),
+    GQ_LAUNCH(k_ks_epilogue_general<24>, grid, block, st, B, P, nP, Ph, primes, n, chat, q, add, Wadd, out, Wout),
+    GQ_LAUNCH(k_ks_epilogue_general<32>, grid, block, st, B, P, nP, Ph, primes, n, chat, q, add, Wadd, out, Wout))
+  return 1;
+}

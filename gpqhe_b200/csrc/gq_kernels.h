@@ -1,0 +1,47 @@
+// gq_kernels.h - host-side launchers of the device kernels (one per pipeline stage).
+#pragma once
+#include "gq_tables.h"
+
+struct GqPtrs4 { uint64_t *p[4]; };
+
+// K1/K2 (gq_ntt.cu): data[npolys][nlimbs][n] in place; returns kernels launched or <0
+int gq_launch_ntt(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
+                  bool inverse, cudaStream_t st);
+
+// K3 (gq_pointwise.cu)
+void gq_launch_binary(const GqPrime *primes, int n, int limb0, int nlimbs, int npolys, bool mul,
+                      uint64_t *r, const uint64_t *a, const uint64_t *b, cudaStream_t st);
+void gq_launch_tensor(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
+                      cudaStream_t st);
+void gq_launch_mul_evk(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
+                       const uint64_t *e0, const uint64_t *e1, cudaStream_t st);
+void gq_launch_mul_pt(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
+                      cudaStream_t st);
+
+// K4/K5/K6 (gq_crt.cu); return 1 on launch, <0 when no instantiation fits
+int gq_launch_decompose(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
+                        int W, uint64_t *out, int npolys, cudaStream_t st);
+int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
+                          const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
+                          cudaStream_t st);
+int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
+                          const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
+                          const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
+                          cudaStream_t st);
+// general-modulus key-switch epilogue (exact long division, slow path)
+int gq_launch_ks_epilogue_general(const GqCrtBasis &B, const uint64_t *P, int nP,
+                                  const uint64_t *Ph, const GqPrime *primes, int n,
+                                  const uint64_t *chat, const GqModulus &q, const GqPtrs4 &add,
+                                  int Wadd, const GqPtrs4 &out, int Wout, int npolys,
+                                  cudaStream_t st);
+
+// K7/K8 (gq_misc.cu)
+// in-place rounded division by 2^j (j == 0: none) then mpi_smod(2^k)
+void gq_launch_rescale_pow2(int n, int W, const GqPtrs4 &c, int npolys, unsigned j, unsigned k,
+                            cudaStream_t st);
+// general Delta / q
+void gq_launch_rescale_general(int n, int W, const GqPtrs4 &c, int npolys, uint64_t Delta,
+                               const GqModulus &q, cudaStream_t st);
+// out[(i*g mod 2n) mod n] = +-in[i]   (poly_rot: g = 5^rot mod 2n; poly_conj: g = 2n-1)
+void gq_launch_automorph(int n, int W, const GqPtrs4 &out, const GqPtrs4 &in, int npolys,
+                         uint64_t g, cudaStream_t st);

@@ -1,0 +1,51 @@
+// gq_tables.h - device-resident image of the reference's context tables
+// (struct rns_ctx list + struct he_ctx, src/poly.h:28-65, src/gpqhe.h:36-50),
+// flattened once per context by gq_context.cu and passed to kernels by value.
+#pragma once
+#include "gq_arith.h"
+
+#define GQ_MAX_PRIMES 64   // polyctx.dimub is 30 for the largest shipped ring
+#define GQ_MAX_W 32        // widest multiword integer kept in registers (2048 bits)
+#define GQ_DEC_W 33        // powers 2^(64w) mod p tabulated for w = 0..32
+
+// NTT view: everything kernels K1/K2/K3 need.
+struct GqNttTables {
+  int logn;
+  int n;
+  const GqPrime *primes;        // [nprimes]
+  const ulonglong2 *tw_fwd;     // [nprimes][n]  {w, floor(w*2^64/p)}, index as zetas[k]
+  const ulonglong2 *tw_inv;     // [nprimes][n]  same for zetas_inv[k]
+  const ulonglong2 *tw_inv_last;// [nprimes]     zetas_inv[1]*N^-1 mod p, folded final stage
+};
+
+// MPI -> RNS view (K4): pow64[d*GQ_DEC_W + w] = 2^(64w) mod p_d; t1_sh[d] is the Shoup
+// companion of pow64[d][1].
+struct GqDecTables {
+  const GqPrime *primes;
+  const uint64_t *pow64;
+  const uint64_t *t1_sh;
+};
+
+// CRT basis {p_0..p_{D-1}} (the `rns` node with dim == D, src/precomp.c:266-293).
+// All multiword constants are zero-padded to WT words, WT = template width.
+struct GqCrtBasis {
+  int D;
+  int WT;                 // multiple of 4, >= words(bits(P)+1)
+  unsigned bitsP;
+  int sh;                 // bitsP - 58 (>= 0) : window used for the quotient estimate
+  uint64_t recip;         // floor((2^120-1) / ((P >> sh) + 1))
+  const uint64_t *P;      // [WT]
+  const uint64_t *Ph;     // [WT] floor(P/2)
+  const uint64_t *phat;   // [D][WT]   P / p_d
+  const uint64_t *inv;    // [D]       (P/p_d)^-1 mod p_d          (phat_invmp)
+  const uint64_t *inv_sh; // [D]       Shoup companion
+};
+
+// a modulus q used by mpi_smod (src/types.c:108): power-of-two fast path or general
+struct GqModulus {
+  int is_pow2;
+  unsigned k;             // q == 2^k when is_pow2
+  int nwords;             // significant words of q (general path)
+  const uint64_t *q;      // [GQ_MAX_W] zero padded
+  const uint64_t *qh;     // [GQ_MAX_W] floor(q/2)
+};

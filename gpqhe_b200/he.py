@@ -1,0 +1,322 @@
+"""Host-side mirror of the reference interface for the RNS polynomial hot path.
+
+Same names, argument meaning and error behaviour as the reference's C functions
+(file:line cited per function, GPQHE commit 5e70953c), on numpy arrays instead of
+libgcrypt MPIs.  Everything computes on the GPU through the C ABI
+(include/gpqhe_b200.h); there is no CPU path here.
+
+Representation
+  limb-poly / poly_rns : np.uint64 [n] / [dim, n]
+  big poly (poly_mpi)  : np.uint64 [W, n], word-major two's complement
+  HeCt                 : l, nu, B, c0, c1   (struct he_ct, src/gpqhe.h:84-91)
+  HeEvk                : device-resident key handle built from (p0, p1) uint64 [dimevk, n]
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import capi
+from .capi import GpqheError
+
+LOGP = 59  # GPQHE_LOGP, src/params.h:27
+SIGMA = 3.1915382432114616  # GPQHE_SIGMA, src/params.h:56
+BLKSIZ = 64  # GPQHE_BLKSIZ, src/params.h:48
+
+
+def int_to_words(x: int, nwords: int | None = None) -> np.ndarray:
+    nwords = nwords or max(1, (x.bit_length() + 63) // 64)
+    return np.frombuffer(x.to_bytes(8 * nwords, "little"), dtype="<u8").astype(np.uint64)
+
+
+def ints_to_big(a, W: int) -> np.ndarray:
+    """list of Python ints -> word-major two's complement [W, n]."""
+    mask = (1 << (64 * W)) - 1
+    buf = b"".join((int(x) & mask).to_bytes(8 * W, "little") for x in a)
+    return np.ascontiguousarray(np.frombuffer(buf, dtype="<u8").reshape(len(a), W).T).astype(np.uint64)
+
+
+def big_to_ints(w: np.ndarray) -> list[int]:
+    W, n = w.shape
+    raw = np.ascontiguousarray(w.T).astype("<u8").tobytes()
+    half, full = 1 << (64 * W - 1), 1 << (64 * W)
+    out = []
+    for i in range(n):
+        x = int.from_bytes(raw[i * 8 * W:(i + 1) * 8 * W], "little")
+        out.append(x - full if x >= half else x)
+    return out
+
+
+def _ptr(a: np.ndarray):
+    assert a.dtype == np.uint64 and a.flags["C_CONTIGUOUS"], "need contiguous uint64"
+    return a.ctypes.data
+
+
+def _c(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.uint64)
+
+
+@dataclass
+class HeCt:
+    """struct he_ct (src/gpqhe.h:84-91)."""
+    l: int
+    c0: np.ndarray
+    c1: np.ndarray
+    nu: float = 1.0
+    B: float = 0.0
+
+    def copy(self) -> "HeCt":   # he_copy_ct, src/he-mem.c:88-97
+        return HeCt(self.l, self.c0.copy(), self.c1.copy(), self.nu, self.B)
+
+
+@dataclass
+class HePt:
+    """struct he_pt (src/gpqhe.h:93-97)."""
+    m: np.ndarray
+    nu: float = 1.0
+
+
+class HeEvk:
+    """he_evk_t (src/gpqhe.h:78-82) uploaded once and kept on the device."""
+
+    def __init__(self, ctx: "HeContext", p0: np.ndarray, p1: np.ndarray):
+        p0, p1 = _c(p0).reshape(-1), _c(p1).reshape(-1)
+        want = ctx.dimevk * ctx.n
+        if p0.size != want or p1.size != want:
+            raise GpqheError(f"evk must be 2 x [dimevk={ctx.dimevk}, n={ctx.n}] uint64")
+        self._lib, self._h = ctx._lib, C.c_void_p()
+        capi.check(self._lib, self._lib.gq_evk_create(ctx._h, C.byref(self._h), _ptr(p0), _ptr(p1)))
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._lib.gq_evk_destroy(self._h)
+            self._h = C.c_void_p()
+
+
+class HeContext:
+    """hectx_init(logn, q, slots, Delta) (src/precomp.c:431-452); with Delta=None only
+    polyctx_init(logn, q) (src/precomp.c:328-384).  Errors the reference reports by
+    abort() are raised as GpqheError with the same message."""
+
+    def __init__(self, logn: int, q: int, slots: int | None = None, Delta: int | None = None, *,
+                 device: int = 0, logp: int = LOGP, logqub: int = 0, lib_path: str | None = None,
+                 ref_tables=None):
+        self._lib = capi.load(lib_path)
+        self._h = C.c_void_p()
+        qw = int_to_words(q)
+        primes = zet = zin = None
+        if ref_tables is not None:   # (primes[K], zetas[K][n], zetas_inv[K][n]) in Montgomery form
+            pr, z, zi = ref_tables
+            self._keep = (_c(pr), [_c(x) for x in z], [_c(x) for x in zi])
+            K = len(self._keep[1])
+            primes = self._keep[0].ctypes.data_as(capi.u64p)
+            zet = (capi.u64p * K)(*[x.ctypes.data_as(capi.u64p) for x in self._keep[1]])
+            zin = (capi.u64p * K)(*[x.ctypes.data_as(capi.u64p) for x in self._keep[2]])
+        capi.check(self._lib, self._lib.gq_ctx_create(
+            C.byref(self._h), logn, qw.ctypes.data_as(capi.u64p), qw.size, slots or 0, Delta or 0,
+            logp, logqub, device, primes, zet, zin))
+        info = capi.GqInfo()
+        capi.check(self._lib, self._lib.gq_ctx_info(self._h, C.byref(info)))
+        self.info = info
+        self.logn, self.n, self.logp, self.dimub = info.logn, info.n, info.logp, info.dimub
+        self.L, self.dim, self.dimevk, self.W = info.L, info.dim, info.dimevk, info.W
+        self.q, self.slots, self.Delta = q, slots, Delta
+        pr = np.zeros(self.dimub, dtype=np.uint64)
+        capi.check(self._lib, self._lib.gq_ctx_primes(self._h, pr.ctypes.data_as(capi.u64p)))
+        self.primes = [int(x) for x in pr]
+        if Delta:
+            self.ql = [0] * (self.L + 1)
+            t = q
+            for l in range(self.L, -1, -1):   # qtable_init, src/precomp.c:394-400
+                self.ql[l] = t
+                t //= Delta
+            self._bounds_init()
+
+    def close(self):
+        if self._h.value:
+            self._lib.gq_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- metadata helpers -------------------------------------------------------
+    def _bounds_init(self):
+        """bounds_init, src/precomp.c:411-429 (host metadata only; plain doubles here)."""
+        n, h, s = self.n, BLKSIZ, SIGMA
+        self.Bclean = 8 * math.sqrt(2) * s * n + 6 * s * math.sqrt(n) + 16 * s * math.sqrt(h * n)
+        self.Brs = math.sqrt(n / 3.0) * (3 + 8 * math.sqrt(h))
+        self.Bks = 8 * s * n / math.sqrt(3)
+        pinv = 1.0
+        for p in self.primes:
+            pinv *= 1.0 / p
+        x = pinv * float(self.ql[0])
+        self.Bmult = []
+        for l in range(self.L + 1):
+            self.Bmult.append(x * self.Bks + self.Brs)
+            x *= float(self.Delta)
+
+    def dims(self, l: int) -> tuple[int, int]:
+        """(tensor limbs, key-switch limbs) at level l: he-mult.c:99 and :51."""
+        a, b = C.c_uint(), C.c_uint()
+        capi.check(self._lib, self._lib.gq_ctx_dims(self._h, l, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def prime_consts(self, limb: int):
+        out = np.zeros(4, dtype=np.uint64)
+        capi.check(self._lib, self._lib.gq_ctx_prime_consts(self._h, limb, out.ctypes.data_as(capi.u64p)))
+        return [int(x) for x in out]
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.gq_ctx_launch_count(self._h))
+
+    def sync(self):
+        capi.check(self._lib, self._lib.gq_ctx_sync(self._h))
+
+    # ---- limb layer ---------------------------------------------------------------
+    def ntt(self, a: np.ndarray, limb: int) -> np.ndarray:
+        """ntt(a, rns) (src/ntt.c:37-52); `limb` = index of the rns list node."""
+        a = _c(a).copy()
+        capi.check(self._lib, self._lib.gq_ntt(self._h, limb, _ptr(a)))
+        return a
+
+    def invntt(self, a: np.ndarray, limb: int) -> np.ndarray:
+        """invntt(a, rns) (src/ntt.c:54-73)."""
+        a = _c(a).copy()
+        capi.check(self._lib, self._lib.gq_invntt(self._h, limb, _ptr(a)))
+        return a
+
+    def ntt_batch(self, data: np.ndarray, limb0: int = 0, inverse: bool = False) -> np.ndarray:
+        """data[npolys, nlimbs, n]: every limb-poly transformed with its own prime."""
+        d = _c(data).copy()
+        npolys, nlimbs, n = d.shape
+        capi.check(self._lib, self._lib.gq_ntt_batch(self._h, limb0, nlimbs, npolys, _ptr(d), int(inverse)))
+        return d
+
+    def poly_rns_add(self, a, b, limb: int) -> np.ndarray:
+        """poly_rns_add (src/poly.c:71-76)."""
+        a, b = _c(a), _c(b)
+        r = np.empty_like(a)
+        capi.check(self._lib, self._lib.gq_poly_rns_add(self._h, limb, _ptr(r), _ptr(a), _ptr(b)))
+        return r
+
+    def poly_rns_mul(self, a, b, limb: int) -> np.ndarray:
+        """poly_rns_mul (src/poly.c:77-82)."""
+        a, b = _c(a), _c(b)
+        r = np.empty_like(a)
+        capi.check(self._lib, self._lib.gq_poly_rns_mul(self._h, limb, _ptr(r), _ptr(a), _ptr(b)))
+        return r
+
+    # ---- MPI <-> RNS ----------------------------------------------------------------
+    def rns_decompose(self, a: np.ndarray, limb0: int = 0, nlimbs: int = 1) -> np.ndarray:
+        """rns_decompose (src/rns.c:37-48) for limbs limb0..limb0+nlimbs-1; a is [W, n]."""
+        a = _c(a)
+        out = np.empty((nlimbs, self.n), dtype=np.uint64)
+        capi.check(self._lib, self._lib.gq_rns_decompose(self._h, limb0, nlimbs, _ptr(out), _ptr(a), a.shape[0]))
+        return out
+
+    def poly_rns2mpi(self, rhat: np.ndarray, dim: int, q: int, W: int | None = None) -> np.ndarray:
+        """poly_rns2mpi(r, rhat, rns[dim-1], q) (src/poly.c:109-120)."""
+        rhat = _c(rhat)
+        W = W or max(1, (q.bit_length() + 63) // 64)
+        out = np.empty((W, self.n), dtype=np.uint64)
+        qw = int_to_words(q)
+        capi.check(self._lib, self._lib.gq_poly_rns2mpi(self._h, dim, _ptr(out), W, _ptr(rhat),
+                                                        qw.ctypes.data_as(capi.u64p), qw.size))
+        return out
+
+    def poly_mul(self, a: np.ndarray, b: np.ndarray, dim: int, q: int, W: int | None = None) -> np.ndarray:
+        """poly_mul(r, a, b, dim, q) (src/poly.c:84-107)."""
+        a, b = _c(a), _c(b)
+        W = W or max(1, (q.bit_length() + 63) // 64)
+        out = np.empty((W, self.n), dtype=np.uint64)
+        qw = int_to_words(q)
+        capi.check(self._lib, self._lib.gq_poly_mul(self._h, _ptr(out), W, _ptr(a), _ptr(b), a.shape[0], dim,
+                                                    qw.ctypes.data_as(capi.u64p), qw.size))
+        return out
+
+    def poly_rot(self, a: np.ndarray, rot: int) -> np.ndarray:
+        """poly_rot (src/poly.c:263-276)."""
+        a = _c(a)
+        out = np.empty_like(a)
+        capi.check(self._lib, self._lib.gq_poly_rot(self._h, _ptr(out), _ptr(a), a.shape[0], rot))
+        return out
+
+    def poly_conj(self, a: np.ndarray) -> np.ndarray:
+        """poly_conj (src/poly.c:278-283)."""
+        a = _c(a)
+        out = np.empty_like(a)
+        capi.check(self._lib, self._lib.gq_poly_conj(self._h, _ptr(out), _ptr(a), a.shape[0]))
+        return out
+
+    # ---- HE primitives ----------------------------------------------------------------
+    def genevk(self, p0: np.ndarray, p1: np.ndarray) -> HeEvk:
+        return HeEvk(self, p0, p1)
+
+    def he_mul(self, ct1: HeCt, ct2: HeCt, rlk: HeEvk) -> HeCt:
+        """he_mul(ct, ct1, ct2, rlk) (src/he-mult.c:88-156)."""
+        if ct1.l != ct2.l:
+            raise GpqheError("he_mul: ct1->l != ct2->l")   # assert at he-mult.c:90
+        l = ct1.l
+        c0 = np.empty((self.W, self.n), dtype=np.uint64)
+        c1 = np.empty_like(c0)
+        capi.check(self._lib, self._lib.gq_he_mul(self._h, l, _ptr(c0), _ptr(c1), _ptr(_c(ct1.c0)),
+                                                  _ptr(_c(ct1.c1)), _ptr(_c(ct2.c0)), _ptr(_c(ct2.c1)), rlk._h))
+        nu = ct1.nu * ct2.nu                                  # he-mult.c:93-95
+        B = ct1.nu * ct2.B + ct2.nu * ct1.B + ct1.B * ct2.B + self.Bmult[l]
+        return HeCt(l, c0, c1, nu, B)
+
+    def mulpt_dim(self, l: int, nu: float) -> int:
+        """limb count of he_mulpt, double arithmetic truncated (src/he-mult.c:168)."""
+        return int((self.ql[l].bit_length() + math.log2(nu) + self.logn) / self.logp + 1)
+
+    def he_mulpt(self, ct: HeCt, pt: HePt) -> HeCt:
+        """he_mulpt(dest, src, pt) (src/he-mult.c:159-196)."""
+        dim = self.mulpt_dim(ct.l, pt.nu)
+        c0 = np.empty((self.W, self.n), dtype=np.uint64)
+        c1 = np.empty_like(c0)
+        capi.check(self._lib, self._lib.gq_he_mulpt(self._h, ct.l, dim, _ptr(c0), _ptr(c1), _ptr(_c(ct.c0)),
+                                                    _ptr(_c(ct.c1)), _ptr(_c(pt.m))))
+        return HeCt(ct.l, c0, c1, ct.nu * pt.nu, ct.B * pt.nu)
+
+    def he_rs(self, ct: HeCt) -> HeCt:
+        """he_rs(ct) (src/he-rescale.c:33-54); returns the rescaled ciphertext."""
+        c0, c1 = _c(ct.c0).copy(), _c(ct.c1).copy()
+        capi.check(self._lib, self._lib.gq_he_rs(self._h, ct.l, _ptr(c0), _ptr(c1)))
+        return HeCt(ct.l - 1, c0, c1, ct.nu / float(self.Delta), ct.B / float(self.Delta) + self.Brs)
+
+    def he_moddown(self, ct: HeCt) -> HeCt:
+        """he_moddown(ct) (src/he-rescale.c:56-70)."""
+        c0, c1 = _c(ct.c0).copy(), _c(ct.c1).copy()
+        capi.check(self._lib, self._lib.gq_he_moddown(self._h, ct.l, _ptr(c0), _ptr(c1)))
+        return HeCt(ct.l - 1, c0, c1, ct.nu, ct.B)
+
+    def he_rot(self, ct: HeCt, rot: int, rk) -> HeCt:
+        """he_rot(ct, rot, rk) (src/he-automorphism.c:102-115); `rk` is the key array
+        indexed by rot (a dict or list of HeEvk)."""
+        c0, c1 = _c(ct.c0).copy(), _c(ct.c1).copy()
+        capi.check(self._lib, self._lib.gq_he_rot(self._h, ct.l, rot, _ptr(c0), _ptr(c1), rk[rot]._h))
+        return HeCt(ct.l, c0, c1, ct.nu, ct.B)
+
+    def he_conj(self, ct: HeCt, ck: HeEvk) -> HeCt:
+        """he_conj(ct, ck) (src/he-automorphism.c:87-100)."""
+        c0, c1 = _c(ct.c0).copy(), _c(ct.c1).copy()
+        capi.check(self._lib, self._lib.gq_he_conj(self._h, ct.l, _ptr(c0), _ptr(c1), ck._h))
+        return HeCt(ct.l, c0, c1, ct.nu, ct.B)
+
+
+def hectx_init(logn: int, q: int, slots: int, Delta: int, **kw) -> HeContext:
+    """hectx_init (src/precomp.c:431)."""
+    return HeContext(logn, q, slots, Delta, **kw)
+
+
+def polyctx_init(logn: int, q: int, **kw) -> HeContext:
+    """polyctx_init (src/precomp.c:328)."""
+    return HeContext(logn, q, None, None, **kw)

@@ -1,0 +1,159 @@
+/*
+ * gpqhe_b200.h - C ABI of the B200-native RNS polynomial hot path of GPQHE.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no CUDA or torch types.
+ * Every entry point names the reference function it replaces (file:line relative
+ * to the GPQHE tree, commit 5e70953c).  dropin/ shows the C shim that binds the
+ * reference's own symbols (ntt, poly_mul, he_mul, ...) to these calls; the Python
+ * mirror in gpqhe_b200/ binds them with ctypes.
+ *
+ * Data formats
+ *   limb-poly   uint64_t[n]          one polynomial modulo one prime p_d, values in
+ *                                    [0,p_d] (the reference's ntt() may emit p_d for 0)
+ *   poly_rns    uint64_t[dim][n]     limb-major, as struct poly_rns (src/poly.h:74-77)
+ *   big poly    uint64_t[W][n]       WORD-MAJOR two's-complement integers: word w of
+ *                                    coefficient i is at [w*n + i]; this stands in for
+ *                                    struct poly_mpi (src/poly.h:69-72), the MPI <-> words
+ *                                    conversion staying on the host side (dropin/)
+ *   evk         2 x uint64_t[dimevk][n], already in ntt() output order, exactly what
+ *                                    he_genswk stores (src/he-kem.c:103-110)
+ *
+ * Host entry points take HOST pointers and include the host<->device copies;
+ * the *_dev entry points take DEVICE pointers plus a CUDA stream handle
+ * (cudaStream_t passed as void*, NULL = the context's own stream) and only
+ * enqueue work.  All functions return 0 on success, non-zero on error;
+ * gq_last_error() describes the last failure.  The reference aborts on error
+ * (SURVEY 8b); the dropin shim turns a non-zero return into the same abort().
+ * One context is bound to one device; calls on one context must be serialised
+ * by the caller (the reference is single-threaded, process-global state).
+ */
+#ifndef GPQHE_B200_H
+#define GPQHE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+typedef struct gq_ctx gq_ctx;
+typedef struct gq_evk gq_evk;
+
+typedef struct gq_info {
+  unsigned logn, n;
+  unsigned logp;      /* GPQHE_LOGP (src/params.h:27), 59 unless TEST_CRT */
+  unsigned dimub;     /* polyctx.dimub, src/precomp.c:357 */
+  unsigned has_he;    /* 0 when created with Delta == 0 (polyctx_init only) */
+  unsigned L;         /* hectx.L,      src/precomp.c:391 */
+  unsigned dim;       /* hectx.dim,    src/precomp.c:401 */
+  unsigned dimevk;    /* hectx.dimevk, src/precomp.c:407 */
+  unsigned W;         /* words per ciphertext coefficient: holds [-q_L/2, q_L/2) */
+  unsigned q_is_pow2; /* every q_l and Delta is a power of two (fast path) */
+  int device;
+} gq_info;
+
+const char *gq_last_error(void);
+int gq_abi_version(void);
+
+/* ---- context: polyctx_init + hectx_init (src/precomp.c:328-384, 431-452) ----------
+ * q: little-endian words of the top modulus.  Delta == 0 builds the polynomial context
+ * only (polyctx_init).  primes/zetas/zetas_inv may be NULL: the library then runs the
+ * reference's prime search and root selection itself (src/precomp.c:153-264,370-376).
+ * When given, they are the reference's own tables (struct rns_ctx .p, .zetas,
+ * .zetas_inv in Montgomery form, one pointer per list node) and are uploaded as is.
+ * logqub == 0 applies the reference's security table (src/precomp.c:52-117,339-340). */
+int gq_ctx_create(gq_ctx **ctx, unsigned logn, const uint64_t *q, unsigned q_words,
+                  unsigned slots, uint64_t Delta, unsigned logp, unsigned logqub,
+                  int device, const uint64_t *primes, const uint64_t *const *zetas,
+                  const uint64_t *const *zetas_inv);
+void gq_ctx_destroy(gq_ctx *ctx);
+int gq_ctx_info(const gq_ctx *ctx, gq_info *out);
+int gq_ctx_primes(const gq_ctx *ctx, uint64_t *out /* [dimub] */);
+/* per-prime scalars of struct rns_ctx: out = {p, pinv_mont, pinv_barr, ninv} */
+int gq_ctx_prime_consts(const gq_ctx *ctx, unsigned limb, uint64_t out[4]);
+/* limb counts at level l: he-mult.c:99 (tensor) and he-mult.c:51 (key switch) */
+int gq_ctx_dims(const gq_ctx *ctx, unsigned l, unsigned *dim_tensor, unsigned *dim_ks);
+int gq_ctx_sync(gq_ctx *ctx);
+/* kernels launched by this context since creation (bench.py's gpu_launches) */
+unsigned long long gq_ctx_launch_count(const gq_ctx *ctx);
+void *gq_ctx_stream(gq_ctx *ctx); /* the context's cudaStream_t */
+
+/* pinned host memory for callers that want fast copies */
+int gq_host_alloc(void **p, size_t bytes);
+void gq_host_free(void *p);
+
+/* ---- limb layer (host pointers) ------------------------------------------------- */
+int gq_ntt(gq_ctx *ctx, unsigned limb, uint64_t *a);    /* ntt(),    src/ntt.c:37-52 */
+int gq_invntt(gq_ctx *ctx, unsigned limb, uint64_t *a); /* invntt(), src/ntt.c:54-73 */
+/* poly_rns_add / poly_rns_mul, src/poly.c:71-82; r may alias a or b */
+int gq_poly_rns_add(gq_ctx *ctx, unsigned limb, uint64_t *r, const uint64_t *a, const uint64_t *b);
+int gq_poly_rns_mul(gq_ctx *ctx, unsigned limb, uint64_t *r, const uint64_t *a, const uint64_t *b);
+/* batched transforms: data[npolys][nlimbs][n], limb d uses prime limb0+d */
+int gq_ntt_batch(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsigned npolys, uint64_t *data,
+                 int inverse);
+
+/* ---- MPI <-> RNS (host pointers) --------------------------------------------------- */
+/* rns_decompose, src/rns.c:37-48, for limbs limb0..limb0+nlimbs-1 at once */
+int gq_rns_decompose(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, uint64_t *ahat,
+                     const uint64_t *a, unsigned W);
+/* poly_rns2mpi, src/poly.c:109-120: CRT over the first `dim` primes, centre mod P, centre mod q */
+int gq_poly_rns2mpi(gq_ctx *ctx, unsigned dim, uint64_t *r, unsigned Wr, const uint64_t *rhat,
+                    const uint64_t *q, unsigned q_words);
+/* poly_mul, src/poly.c:84-107 */
+int gq_poly_mul(gq_ctx *ctx, uint64_t *r, unsigned Wr, const uint64_t *a, const uint64_t *b,
+                unsigned W, unsigned dim, const uint64_t *q, unsigned q_words);
+/* poly_rot / poly_conj, src/poly.c:263-283 */
+int gq_poly_rot(gq_ctx *ctx, uint64_t *r, const uint64_t *a, unsigned W, uint64_t rot);
+int gq_poly_conj(gq_ctx *ctx, uint64_t *r, const uint64_t *a, unsigned W);
+
+/* ---- evaluation keys ------------------------------------------------------------- */
+/* upload a key laid out as he_evk_t (src/gpqhe.h:78-82): p0, p1 = uint64_t[dimevk][n] */
+int gq_evk_create(gq_ctx *ctx, gq_evk **evk, const uint64_t *p0, const uint64_t *p1);
+int gq_evk_create_dev(gq_ctx *ctx, gq_evk **evk, const uint64_t *p0_dev, const uint64_t *p1_dev);
+void gq_evk_destroy(gq_evk *evk);
+
+/* ---- HE primitives, host pointers; every big poly is uint64_t[W][n], W = gq_info.W - */
+/* he_mul (mult + relinearise), src/he-mult.c:88-156; `l` = ct1->l = ct2->l; outputs may alias inputs */
+int gq_he_mul(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+              const uint64_t *a1, const uint64_t *b0, const uint64_t *b1, const gq_evk *rlk);
+/* he_mulpt, src/he-mult.c:159-196; `dim` is the limb count the caller derives from pt->nu (:168) */
+int gq_he_mulpt(gq_ctx *ctx, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
+                const uint64_t *a0, const uint64_t *a1, const uint64_t *m);
+/* he_rs / he_moddown, src/he-rescale.c:33-70; in place; `l` is the level BEFORE the call */
+int gq_he_rs(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1);
+int gq_he_moddown(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1);
+/* he_rot / he_conj, src/he-automorphism.c:87-115; in place; `rk_rot` is &rk[rot] */
+int gq_he_rot(gq_ctx *ctx, unsigned l, unsigned rot, uint64_t *c0, uint64_t *c1, const gq_evk *rk_rot);
+int gq_he_conj(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const gq_evk *ck);
+
+/* ---- device-resident variants: DEVICE pointers, enqueue only -------------------- */
+int gq_ntt_batch_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsigned npolys,
+                     uint64_t *data_dev, int inverse, void *stream);
+int gq_poly_rns_mul_batch_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsigned npolys,
+                              uint64_t *r_dev, const uint64_t *a_dev, const uint64_t *b_dev,
+                              void *stream);
+int gq_he_mul_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                  const uint64_t *a1, const uint64_t *b0, const uint64_t *b1, const gq_evk *rlk,
+                  void *stream);
+int gq_he_mulpt_dev(gq_ctx *ctx, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
+                    const uint64_t *a0, const uint64_t *a1, const uint64_t *m, void *stream);
+int gq_he_rs_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, void *stream);
+int gq_he_moddown_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, void *stream);
+int gq_he_rot_dev(gq_ctx *ctx, unsigned l, unsigned rot, uint64_t *c0, uint64_t *c1,
+                  const gq_evk *rk_rot, void *stream);
+int gq_he_conj_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const gq_evk *ck,
+                   void *stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPQHE_B200_H */
