@@ -396,8 +396,10 @@ extern "C" int gq_ntt_batch_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsi
                                 uint64_t *data, int inverse, void *stream) {
   if (!c || !data || npolys == 0) GQ_FAIL("bad argument");
   if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
-  int r = gq_launch_ntt(c->ntt_tables(), data, (int)limb0, (int)nlimbs, (int)npolys, inverse != 0,
-                        pick(c, stream));
+  // inverse: bit 0 = inverse transform; bits 1,2 = profiling only (run just the tile /
+  // just the strided kernel of a two-kernel transform; the output is then not an NTT)
+  int r = gq_launch_ntt(c->ntt_tables(), data, (int)limb0, (int)nlimbs, (int)npolys, (inverse & 1) != 0,
+                        pick(c, stream), (inverse >> 1) & 3);
   if (r < 0) GQ_FAIL("unsupported ring degree");
   c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);

@@ -6,7 +6,7 @@ struct GqPtrs4 { uint64_t *p[4]; };
 
 // K1/K2 (gq_ntt.cu): data[npolys][nlimbs][n] in place; returns kernels launched or <0
 int gq_launch_ntt(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
-                  bool inverse, cudaStream_t st);
+                  bool inverse, cudaStream_t st, int only = 0);
 
 // K3 (gq_pointwise.cu)
 void gq_launch_binary(const GqPrime *primes, int n, int limb0, int nlimbs, int npolys, bool mul,

@@ -284,10 +284,26 @@ void launch_inv_strided(const GqNttTables &tb, uint64_t *data, int limb0, int nl
 }  // namespace
 
 int gq_launch_ntt(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
-                  bool inverse, cudaStream_t st) {
+                  bool inverse, cudaStream_t st, int only) {
+  // only: 0 = whole transform; 1 = tile kernel only, 2 = strided kernel only (profiling)
   const int logn = tb.logn;
   if (logn < 3 || logn > 17) return -1;
   int launches = 0;
+  if (only && logn > 12) {
+    if (only == 1) {
+      if (inverse) launch_inv_tile<12, false>(tb, data, limb0, nlimbs, npolys, st);
+      else launch_fwd_tile<12>(tb, data, limb0, nlimbs, npolys, st);
+    } else if (logn == 16) {
+      if (inverse) launch_inv_strided<4>(tb, data, limb0, nlimbs, npolys, st);
+      else launch_fwd_strided<4>(tb, data, limb0, nlimbs, npolys, st);
+    } else if (logn == 14) {
+      if (inverse) launch_inv_strided<2>(tb, data, limb0, nlimbs, npolys, st);
+      else launch_fwd_strided<2>(tb, data, limb0, nlimbs, npolys, st);
+    } else {
+      return -1;
+    }
+    return 1;
+  }
   if (!inverse) {
     if (logn > 12) {
       switch (logn - 12) {

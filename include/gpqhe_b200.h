@@ -132,6 +132,8 @@ int gq_he_rot(gq_ctx *ctx, unsigned l, unsigned rot, uint64_t *c0, uint64_t *c1,
 int gq_he_conj(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const gq_evk *ck);
 
 /* ---- device-resident variants: DEVICE pointers, enqueue only -------------------- */
+/* inverse: 0 forward, 1 inverse.  Profiling only: +2 runs just the 4096-point tile kernel,
+ * +4 just the strided kernel of a two-kernel transform (the result is then not an NTT). */
 int gq_ntt_batch_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsigned npolys,
                      uint64_t *data_dev, int inverse, void *stream);
 int gq_poly_rns_mul_batch_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsigned npolys,

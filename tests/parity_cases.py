@@ -1,0 +1,174 @@
+"""Parity checks shared by the CPU tier (library compiled against tests/emul) and the GPU
+tier (the real sm_100a library).  Every check goes through the C ABI via gpqhe_b200.he."""
+import os
+import random
+
+import numpy as np
+
+import gpqhe_b200 as g
+from oracle import pyoracle as o
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+GOLDEN_CASES = ["pow2_n256_q120", "pow2_n64_q438", "general_n128"]
+
+
+def words_to_int(w):
+    return int.from_bytes(np.asarray(w, dtype="<u8").tobytes(), "little")
+
+
+def load_golden(name):
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    return z, int(z["logn"]), words_to_int(z["q"]), int(z["slots"]), int(z["Delta"])
+
+
+def eq(a, b, what):
+    assert np.array_equal(np.asarray(a, dtype=np.uint64), np.asarray(b, dtype=np.uint64)), what
+
+
+def check_golden(lib_path, name):
+    """Product vs the outputs the unmodified reference produced (tests/golden/*.npz)."""
+    z, logn, q, slots, Delta = load_golden(name)
+    ctx = g.HeContext(logn, q, slots, Delta, lib_path=lib_path)
+    try:
+        W, n = ctx.W, ctx.n
+        assert (ctx.L, ctx.dim, ctx.dimevk, ctx.dimub, W) == tuple(int(z[k]) for k in ("L", "dim", "dimevk", "dimub", "W"))
+        eq(ctx.primes, z["primes"], "primes")
+        for d in range(ctx.dimub):
+            eq(ctx.prime_consts(d), z["prime_consts"][d][:4], f"prime consts {d}")
+        for tag in ("a", "b"):
+            d = int(z[f"limb_{tag}"])
+            x, y = z[f"x_{tag}"], z[f"y_{tag}"]
+            eq(ctx.ntt(x, d), z[f"ntt_{tag}"], "ntt")
+            eq(ctx.invntt(y, d), z[f"invntt_{tag}"], "invntt")
+            eq(ctx.poly_rns_mul(x, y, d), z[f"mul_{tag}"], "poly_rns_mul")
+            eq(ctx.poly_rns_add(x, y, d), z[f"add_{tag}"], "poly_rns_add")
+            eq(ctx.ntt(z[f"hz_{tag}"], d), z[f"hzntt_{tag}"], "ntt non-canonical q vector")
+            assert int((z[f"hzntt_{tag}"] == z["primes"][d]).sum()) > 0
+            eq(ctx.invntt(z[f"hzntt_{tag}"], d), z[f"hzinv_{tag}"], "invntt of non-canonical input")
+        eq(ctx.rns_decompose(z["big_a"], 0, ctx.dimub), z["decompose_a"], "rns_decompose")
+        q2 = words_to_int(z["rns2mpi_q2"])
+        eq(ctx.poly_rns2mpi(z["rns2mpi_in"], ctx.dimub, q, W), z["rns2mpi_full"], "poly_rns2mpi full")
+        eq(ctx.poly_rns2mpi(z["rns2mpi_in"][:ctx.dim * n], ctx.dim, q2, W), z["rns2mpi_dim"], "poly_rns2mpi dim")
+        eq(ctx.poly_mul(z["big_a"], z["big_b"], ctx.dimub, q, W), z["poly_mul"], "poly_mul")
+        for rot in (1, 5):
+            eq(ctx.poly_rot(z["big_a"], rot), z[f"poly_rot{rot}"], "poly_rot")
+        eq(ctx.poly_conj(z["big_a"]), z["poly_conj"], "poly_conj")
+        evk = ctx.genevk(z["evk_p0"], z["evk_p1"])
+        for l in [int(v) for v in z["levels"]]:
+            ct1 = g.HeCt(l, z[f"l{l}_a0"], z[f"l{l}_a1"])
+            ct2 = g.HeCt(l, z[f"l{l}_b0"], z[f"l{l}_b1"])
+            r = ctx.he_mul(ct1, ct2, evk)
+            eq(r.c0, z[f"l{l}_mul_c0"], f"he_mul c0 l={l}"); eq(r.c1, z[f"l{l}_mul_c1"], f"he_mul c1 l={l}")
+            r = ctx.he_rs(r)
+            assert r.l == l - 1
+            eq(r.c0, z[f"l{l}_mulrs_c0"], "he_rs c0"); eq(r.c1, z[f"l{l}_mulrs_c1"], "he_rs c1")
+            r = ctx.he_moddown(ct1)
+            eq(r.c0, z[f"l{l}_moddown_c0"], "he_moddown"); eq(r.c1, z[f"l{l}_moddown_c1"], "he_moddown")
+            for rot in (0, 3):
+                r = ctx.he_rot(ct1, rot, {rot: evk})
+                eq(r.c0, z[f"l{l}_rot{rot}_c0"], f"he_rot {rot}"); eq(r.c1, z[f"l{l}_rot{rot}_c1"], f"he_rot {rot}")
+            r = ctx.he_conj(ct1, evk)
+            eq(r.c0, z[f"l{l}_conj_c0"], "he_conj"); eq(r.c1, z[f"l{l}_conj_c1"], "he_conj")
+            r = ctx.he_mulpt(ct1, g.HePt(z[f"l{l}_pt_m"], nu=float(1 << 40)))
+            eq(r.c0, z[f"l{l}_mulpt_c0"], "he_mulpt"); eq(r.c1, z[f"l{l}_mulpt_c1"], "he_mulpt")
+    finally:
+        ctx.close()
+
+
+def rlimbs(rng, primes, n, count):
+    return np.concatenate([np.array([rng.randrange(primes[d]) for _ in range(n)], dtype=np.uint64)
+                           for d in range(count)])
+
+
+def check_limb_layer_vs_oracle(lib_path, logn, q, seed=0, limbs=None, logp=59):
+    """ntt / invntt / poly_rns_mul / poly_rns_add vs oracle.c on seeded inputs + edge vectors."""
+    rng = random.Random(seed)
+    ctx = g.HeContext(logn, q, lib_path=lib_path, logp=logp)
+    oc = o.Ctx(logn, q, logp=logp)
+    try:
+        n = ctx.n
+        assert ctx.primes == oc.primes
+        for d in (limbs or (0, ctx.dimub - 1)):
+            nd = oc.rns[d]
+            p = nd.p
+            assert ctx.prime_consts(d) == [nd.p, nd.pinv_mont, nd.pinv_barr, nd.ninv]
+            a = np.array([rng.randrange(p) for _ in range(n)], dtype=np.uint64)
+            b = np.array([rng.randrange(p) for _ in range(n)], dtype=np.uint64)
+            f = ctx.ntt(a, d)
+            eq(f, o.ntt(a, nd), f"ntt logn={logn} limb={d}")
+            eq(ctx.invntt(f, d), a, "invntt(ntt(a)) == a")
+            eq(ctx.invntt(b, d), o.invntt(b, nd), "invntt")
+            eq(ctx.poly_rns_mul(a, b, d), o.poly_rns_mul(a, b, nd), "poly_rns_mul")
+            eq(ctx.poly_rns_add(a, b, d), o.poly_rns_add(a, b, nd), "poly_rns_add")
+            # edge vectors: all zero, all p-1, unit impulses, and the non-canonical-q case
+            for v in (np.zeros(n, dtype=np.uint64), np.full(n, p - 1, dtype=np.uint64)):
+                eq(ctx.ntt(v, d), o.ntt(v, nd), "ntt edge")
+                eq(ctx.invntt(v, d), o.invntt(v, nd), "invntt edge")
+            e = np.zeros(n, dtype=np.uint64); e[n - 1] = 1
+            eq(ctx.ntt(e, d), o.ntt(e, nd), "ntt impulse")
+            zplain = (int(nd.zetas[1]) * pow(1 << 64, -1, p)) % p
+            h = np.zeros(n, dtype=np.uint64); h[n // 2] = 1; h[0] = p - zplain
+            hf = o.ntt(h, nd)
+            assert int((hf == p).sum()) > 0, "hazard vector must produce the value p"
+            eq(ctx.ntt(h, d), hf, "ntt keeps q (not 0) on the + leg")
+            eq(ctx.invntt(hf, d), o.invntt(hf, nd), "invntt accepts q")
+    finally:
+        ctx.close()
+
+
+def rpoly(rng, qq, n):
+    return [rng.randrange(qq) - qq // 2 for _ in range(n)]
+
+
+def check_he_vs_oracle(lib_path, logn, q, slots, Delta, seed=0, levels=None, rots=(0, 3)):
+    """MPI layer + he_mul / he_rs / he_moddown / he_rot / he_conj / he_mulpt vs pyoracle."""
+    rng = random.Random(seed)
+    ctx = g.HeContext(logn, q, slots, Delta, lib_path=lib_path)
+    oc = o.Ctx(logn, q, slots, Delta)
+    try:
+        n, W = ctx.n, ctx.W
+        assert (ctx.L, ctx.dim, ctx.dimevk, ctx.dimub) == (oc.L, oc.dim, oc.dimevk, oc.dimub)
+        a = rpoly(rng, q, n); aw = g.ints_to_big(a, W)
+        b = rpoly(rng, q, n); bw = g.ints_to_big(b, W)
+        dec = ctx.rns_decompose(aw, 0, ctx.dimub)
+        for d in range(ctx.dimub):
+            eq(dec[d], o.rns_decompose(a, oc.rns[d]), f"rns_decompose limb {d}")
+        for dim in sorted({1, ctx.dim, ctx.dimub}):
+            rh = rlimbs(rng, oc.primes, n, dim)
+            for qq in (q, oc.rns[dim - 1].P * 3 + 1, 12345):
+                Wr = max(1, (qq.bit_length() + 63) // 64)
+                got = g.big_to_ints(ctx.poly_rns2mpi(rh, dim, qq, Wr))
+                assert got == o.poly_rns2mpi(rh, oc.rns[dim - 1], qq, n), ("poly_rns2mpi", dim)
+        assert g.big_to_ints(ctx.poly_mul(aw, bw, ctx.dimub, q)) == o.poly_mul(oc, a, b, oc.dimub, q)
+        for rot in (0, 1, 7):
+            assert g.big_to_ints(ctx.poly_rot(aw, rot)) == o.poly_rot(a, rot, n)
+        assert g.big_to_ints(ctx.poly_conj(aw)) == o.poly_conj(a, n)
+        p0, p1 = rlimbs(rng, oc.primes, n, oc.dimevk), rlimbs(rng, oc.primes, n, oc.dimevk)
+        evk = ctx.genevk(p0, p1)
+        for l in (levels or range(oc.L, 0, -1)):
+            ql = oc.ql[l]
+            a0, a1, b0, b1 = (rpoly(rng, ql, n) for _ in range(4))
+            c1 = g.HeCt(l, g.ints_to_big(a0, W), g.ints_to_big(a1, W))
+            c2 = g.HeCt(l, g.ints_to_big(b0, W), g.ints_to_big(b1, W))
+            d1, d2 = {"l": l, "c0": a0, "c1": a1}, {"l": l, "c0": b0, "c1": b1}
+            r, e = ctx.he_mul(c1, c2, evk), o.he_mul(oc, d1, d2, (p0, p1))
+            assert g.big_to_ints(r.c0) == e["c0"] and g.big_to_ints(r.c1) == e["c1"], ("he_mul", l)
+            r2, e2 = ctx.he_rs(r), o.he_rs(oc, e)
+            assert r2.l == e2["l"] and g.big_to_ints(r2.c0) == e2["c0"] and g.big_to_ints(r2.c1) == e2["c1"], ("he_rs", l)
+            r3, e3 = ctx.he_moddown(c1), o.he_moddown(oc, d1)
+            assert g.big_to_ints(r3.c0) == e3["c0"] and g.big_to_ints(r3.c1) == e3["c1"], ("he_moddown", l)
+            for rot in rots:
+                r4, e4 = ctx.he_rot(c1, rot, {rot: evk}), o.he_rot(oc, d1, rot, (p0, p1))
+                assert g.big_to_ints(r4.c0) == e4["c0"] and g.big_to_ints(r4.c1) == e4["c1"], ("he_rot", l, rot)
+            r5, e5 = ctx.he_conj(c1, evk), o.he_conj(oc, d1, (p0, p1))
+            assert g.big_to_ints(r5.c0) == e5["c0"] and g.big_to_ints(r5.c1) == e5["c1"], ("he_conj", l)
+            m = [rng.randrange(1 << 40) - (1 << 39) for _ in range(n)]
+            pt = g.HePt(g.ints_to_big(m, W), nu=float(1 << 40))
+            r6, e6 = ctx.he_mulpt(c1, pt), o.he_mulpt(oc, d1, m, ctx.mulpt_dim(l, pt.nu))
+            assert g.big_to_ints(r6.c0) == e6["c0"] and g.big_to_ints(r6.c1) == e6["c1"], ("he_mulpt", l)
+            # aliasing contract: he_mul(&x,&x,&x) == he_mul with distinct buffers
+            r7 = ctx.he_mul(c1, c1, evk)
+            e7 = o.he_mul(oc, d1, d1, (p0, p1))
+            assert g.big_to_ints(r7.c0) == e7["c0"], "he_mul(x,x)"
+    finally:
+        ctx.close()

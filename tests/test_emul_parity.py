@@ -1,0 +1,73 @@
+"""CPU tier: host logic + kernel index arithmetic.  The library sources are compiled
+against the fibre-based CUDA stand-in in tests/emul (test infrastructure, not a product
+path) and driven through the same C ABI and the same checks as the GPU tier."""
+import pytest
+
+import gpqhe_b200 as g
+import parity_cases as pc
+
+
+@pytest.mark.parametrize("name", pc.GOLDEN_CASES)
+def test_golden(emul_lib, name):
+    pc.check_golden(emul_lib, name)
+
+
+@pytest.mark.parametrize("logn,logq", [(3, 61), (4, 61), (5, 61), (7, 61), (9, 100), (10, 27), (12, 100),
+                                       (13, 120), (14, 120)])
+def test_limb_layer(emul_lib, logn, logq):
+    pc.check_limb_layer_vs_oracle(emul_lib, logn, 1 << logq, seed=logn)
+
+
+@pytest.mark.parametrize("logn,q,Delta,levels", [
+    (8, 1 << 120, 1 << 40, None),                 # power-of-two fast path, every level incl. q_0 = 1
+    (5, 1 << 438, 1 << 50, [8, 4, 1]),            # the KAT modulus chain (24 key-switch limbs)
+    (6, (1 << 119) + 12345, (1 << 40) + 7, None),  # arbitrary q and Delta: exact slow path
+    (4, 3 ** 75, 1 << 40, None),                  # arbitrary q, power-of-two Delta
+])
+def test_he_ops(emul_lib, logn, q, Delta, levels):
+    pc.check_he_vs_oracle(emul_lib, logn, q, 4, Delta, seed=logn, levels=levels)
+
+
+def test_error_behaviour(emul_lib):
+    """The reference abort()s with these messages (src/precomp.c:344-350,434-445)."""
+    with pytest.raises(g.GpqheError, match="too large"):
+        g.HeContext(12, 1 << 120, 4, 1 << 40, lib_path=emul_lib)
+    with pytest.raises(g.GpqheError, match="power of 2"):
+        g.HeContext(8, 1 << 120, 3, 1 << 40, lib_path=emul_lib)
+    with pytest.raises(g.GpqheError, match="slots"):
+        g.HeContext(4, 1 << 120, 16, 1 << 40, lib_path=emul_lib)
+    ctx = g.HeContext(8, 1 << 120, 4, 1 << 40, lib_path=emul_lib)
+    import numpy as np
+    z = np.zeros((ctx.W, ctx.n), dtype=np.uint64)
+    evk = ctx.genevk(np.zeros((ctx.dimevk, ctx.n), dtype=np.uint64), np.zeros((ctx.dimevk, ctx.n), dtype=np.uint64))
+    with pytest.raises(g.GpqheError):            # assert(ct1->l==ct2->l), src/he-mult.c:90
+        ctx.he_mul(g.HeCt(3, z, z), g.HeCt(2, z, z), evk)
+    with pytest.raises(g.GpqheError):
+        ctx.he_rs(g.HeCt(0, z, z))
+    ctx.close()
+
+
+def test_small_primes_crt(emul_lib):
+    """tests/crt.c: -DTEST_CRT rings (9-bit primes): decompose -> reconstruct round trip at
+    every basis size; NTT entry points refuse (the reference aborts, src/reduce.c:94-100)."""
+    import random
+    import numpy as np
+    from oracle import pyoracle as o
+    ctx = g.HeContext(4, 1 << 10, lib_path=emul_lib, logp=9)
+    oc = o.Ctx(4, 1 << 10, logp=9)
+    assert ctx.primes == oc.primes
+    rng = random.Random(5)
+    n = ctx.n
+    for dim in range(ctx.dimub, 1, -1):
+        P = oc.rns[dim - 1].P
+        a = [rng.randrange(P) - P // 2 for _ in range(n)]
+        W = (P.bit_length() + 63) // 64
+        dec = ctx.rns_decompose(g.ints_to_big(a, W), 0, dim)
+        for d in range(dim):
+            pc.eq(dec[d], o.rns_decompose(a, oc.rns[d]), "decompose")
+        back = g.big_to_ints(ctx.poly_rns2mpi(dec.reshape(-1), dim, P, W))
+        assert back == o.poly_rns2mpi(dec.reshape(-1), oc.rns[dim - 1], P, n)
+        assert all((x - y) % P == 0 for x, y in zip(back, a))
+    with pytest.raises(g.GpqheError):
+        ctx.ntt(np.zeros(n, dtype=np.uint64), 0)
+    ctx.close()

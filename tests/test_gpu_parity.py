@@ -1,0 +1,96 @@
+"""GPU tier: the real sm_100a library through the C ABI vs golden fixtures and the oracle."""
+import random
+
+import numpy as np
+import pytest
+
+import gpqhe_b200 as g
+import parity_cases as pc
+from oracle import pyoracle as o
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", pc.GOLDEN_CASES)
+def test_golden(real_lib, name):
+    pc.check_golden(real_lib, name)
+
+
+@pytest.mark.parametrize("logn,logq", [(3, 61), (4, 61), (6, 61), (7, 61), (8, 61), (9, 100), (10, 27), (11, 54),
+                                       (12, 100), (13, 120), (14, 438), (15, 120), (16, 438), (17, 120)])
+def test_limb_layer(real_lib, logn, logq):
+    pc.check_limb_layer_vs_oracle(real_lib, logn, 1 << logq, seed=logn, limbs=(0, 1))
+
+
+@pytest.mark.parametrize("logn,q,Delta,levels", [
+    (8, 1 << 120, 1 << 40, None),
+    (10, 1 << 438, 1 << 50, [8, 5, 1]),
+    (12, 1 << 109, 1 << 30, None),
+    (7, (1 << 119) + 12345, (1 << 40) + 7, None),
+    (6, 3 ** 75, 1 << 40, None),
+])
+def test_he_ops(real_lib, logn, q, Delta, levels):
+    import gpqhe_b200.capi as capi
+    pc.check_he_vs_oracle(real_lib, logn, q, 4, Delta, seed=logn, levels=levels)
+
+
+def test_kat_ring_n14_he_mul_rs(real_lib):
+    """config[0] ring (logn=14, logq=438, Delta=2^50, tests/gpqhe.c:1296-1299): he_mul+he_rs and
+    he_rot at the top level, bit-exact vs the oracle."""
+    pc.check_he_vs_oracle(real_lib, 14, 1 << 438, 16, 1 << 50, seed=14, levels=[8], rots=(1,))
+
+
+def test_batched_ntt_n16_all_limbs(real_lib):
+    """config[1]: batched forward/inverse NTT + pointwise mul over 24 limbs at N=2^16."""
+    rng = np.random.default_rng(16)
+    ctx = g.HeContext(16, 1 << 438, 16, 1 << 50, lib_path=real_lib)
+    oc = o.Ctx(16, 1 << 438, 16, 1 << 50)
+    try:
+        assert ctx.primes == oc.primes and ctx.dimevk == 24
+        n, D = ctx.n, 24
+        x = np.stack([rng.integers(0, oc.primes[d], size=n, dtype=np.uint64) for d in range(D)])[None]
+        f = ctx.ntt_batch(x, 0, inverse=False)
+        for d in range(D):
+            pc.eq(f[0, d], o.ntt(x[0, d], oc.rns[d]), f"batched ntt limb {d}")
+        pc.eq(ctx.ntt_batch(f, 0, inverse=True), x, "inverse of forward")
+        y = np.stack([rng.integers(0, oc.primes[d], size=n, dtype=np.uint64) for d in range(D)])[None]
+        iv = ctx.ntt_batch(y, 0, inverse=True)
+        for d in (0, 7, 23):
+            pc.eq(iv[0, d], o.invntt(y[0, d], oc.rns[d]), f"batched invntt limb {d}")
+            pc.eq(ctx.poly_rns_mul(x[0, d], y[0, d], d), o.poly_rns_mul(x[0, d], y[0, d], oc.rns[d]), "mul")
+    finally:
+        ctx.close()
+
+
+def test_full_size_n16_he_mul_rs_rot(real_lib):
+    """config[2]/[3] at full size (N=2^16, 16 tensor limbs, 24 key-switch limbs): he_mul + he_rs
+    and he_rot vs the oracle, plus size-independent properties."""
+    rng = random.Random(2016)
+    logn, q, Delta = 16, 1 << 438, 1 << 50
+    ctx = g.HeContext(logn, q, 16, Delta, lib_path=real_lib)
+    oc = o.Ctx(logn, q, 16, Delta)
+    try:
+        n, W, l = ctx.n, ctx.W, ctx.L
+        nr = np.random.default_rng(7)
+        p0 = np.concatenate([nr.integers(0, oc.primes[d], size=n, dtype=np.uint64) for d in range(oc.dimevk)])
+        p1 = np.concatenate([nr.integers(0, oc.primes[d], size=n, dtype=np.uint64) for d in range(oc.dimevk)])
+        evk = ctx.genevk(p0, p1)
+        ql = oc.ql[l]
+        a0, a1, b0, b1 = (pc.rpoly(rng, ql, n) for _ in range(4))
+        c1 = g.HeCt(l, g.ints_to_big(a0, W), g.ints_to_big(a1, W))
+        c2 = g.HeCt(l, g.ints_to_big(b0, W), g.ints_to_big(b1, W))
+        r = ctx.he_mul(c1, c2, evk)
+        e = o.he_mul(oc, {"l": l, "c0": a0, "c1": a1}, {"l": l, "c0": b0, "c1": b1}, (p0, p1))
+        assert g.big_to_ints(r.c0) == e["c0"] and g.big_to_ints(r.c1) == e["c1"], "he_mul N=2^16"
+        r2, e2 = ctx.he_rs(r), o.he_rs(oc, e)
+        assert g.big_to_ints(r2.c0) == e2["c0"] and g.big_to_ints(r2.c1) == e2["c1"], "he_rs N=2^16"
+        r3 = ctx.he_rot(c1, 5, {5: evk})
+        e3 = o.he_rot(oc, {"l": l, "c0": a0, "c1": a1}, 5, (p0, p1))
+        assert g.big_to_ints(r3.c0) == e3["c0"] and g.big_to_ints(r3.c1) == e3["c1"], "he_rot N=2^16"
+        # properties: commutativity of he_mul; outputs centred mod q_l; rot then level check
+        rs = ctx.he_mul(c2, c1, evk)
+        pc.eq(rs.c0, r.c0, "he_mul commutes"); pc.eq(rs.c1, r.c1, "he_mul commutes")
+        top = np.asarray(r.c0[W - 1], dtype=np.uint64).astype(np.int64) >> 53   # bits >= 437 are sign
+        assert set(np.unique(top).tolist()) <= {0, -1}, "centred range of q_L"
+    finally:
+        ctx.close()
