@@ -124,8 +124,12 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
   hb.P = P;
   const unsigned bitsP = P.bits();
   const unsigned WT = round_wt((bitsP + 1 + 63) / 64);
-  if (WT > GQ_MAX_W) GQ_FAIL("RNS basis wider than GQ_MAX_W words");
-  if (D > WT + WT / 8 + 2) GQ_FAIL("too many primes for the CRT tile");
+  if (WT > GQ_MAX_W || D > WT + WT / 8 + 2) {
+    // wider than the register-resident CRT kernels support (2048 bits): the context is still
+    // usable for the limb layer and for narrower bases; CRT over this basis fails loudly.
+    hb.dev.D = (int)D; hb.dev.WT = 0;
+    return 0;
+  }
   std::vector<uint64_t> buf((size_t)(2 + D) * WT + 2 * D, 0);
   uint64_t *hP = buf.data(), *hPh = hP + WT, *hphat = hPh + WT, *hinv = hphat + (size_t)D * WT,
            *hinvsh = hinv + D;
@@ -479,6 +483,7 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
 static int reconstruct_dev(gq_ctx *c, unsigned D, const uint64_t *rhat, const GqModulus &q,
                            const GqPtrs4 &out, unsigned Wout, unsigned npolys, cudaStream_t st) {
   if (D == 0 || D > c->dimub) GQ_FAIL("basis size out of range");
+  if (c->basis[D - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
   if (gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)c->n, rhat, q, out, (int)Wout,
                             (int)npolys, st) < 0)
     GQ_FAIL("no reconstruct kernel for this width");
@@ -625,6 +630,7 @@ static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk 
   const unsigned D2 = dim_ks(c, l), n = c->n, W = c->W;
   if (D2 > c->dimevk) GQ_FAIL("key-switch basis exceeds dimevk");
   if (!ntt_ok(c, 0, D2)) GQ_FAIL("modulus below 32 bits");
+  if (c->basis[D2 - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
   if (ensure_slot(c, GQ_SLOT_LIMB_A, (size_t)4 * c->dimub * n * 8) ||
       ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8)) return 1;
   uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
