@@ -120,11 +120,11 @@ def rpoly(rng, qq, n):
     return [rng.randrange(qq) - qq // 2 for _ in range(n)]
 
 
-def check_he_vs_oracle(lib_path, logn, q, slots, Delta, seed=0, levels=None, rots=(0, 3)):
+def check_he_vs_oracle(lib_path, logn, q, slots, Delta, seed=0, levels=None, rots=(0, 3), logqub=0):
     """MPI layer + he_mul / he_rs / he_moddown / he_rot / he_conj / he_mulpt vs pyoracle."""
     rng = random.Random(seed)
-    ctx = g.HeContext(logn, q, slots, Delta, lib_path=lib_path)
-    oc = o.Ctx(logn, q, slots, Delta)
+    ctx = g.HeContext(logn, q, slots, Delta, lib_path=lib_path, logqub=logqub)
+    oc = o.Ctx(logn, q, slots, Delta, logqub=logqub)
     try:
         n, W = ctx.n, ctx.W
         assert (ctx.L, ctx.dim, ctx.dimevk, ctx.dimub) == (oc.L, oc.dim, oc.dimevk, oc.dimub)

@@ -1,0 +1,133 @@
+"""The drop-in libgpqhe.so (dropin/): the reference's own host C + our hot symbols over the C ABI.
+
+CPU tier: the drop-in is linked at run time against the emulated build of the device library
+(tests/emul) and compared, in one process, with the reference's own CPU definitions that stay in
+the same library as gpqhe_ref_<name> (tests/dropin_diff.c), and the reference's UNMODIFIED test
+programs are run against it.  GPU tier: the same programs against the real sm_100a library at the
+KAT ring (N=2^14) and at N=2^16.
+"""
+import os
+import re
+import shutil
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BUILD = os.path.join(ROOT, "dropin", "_build")
+REF_PRESENT = os.path.isdir("/root/reference/src")
+
+
+def _have_gcrypt():
+    import ctypes
+    try:
+        ctypes.CDLL("libgcrypt.so.20")
+        return True
+    except OSError:
+        return False
+
+
+def _build_dropin():
+    if REF_PRESENT:
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "gpqhe_b200", "csrc"), "-j8"])
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "dropin"), "-j8"])
+    if not os.path.exists(os.path.join(BUILD, "libgpqhe.so")):
+        pytest.skip("dropin/_build is not built and /root/reference is not mounted here")
+    if not _have_gcrypt():
+        pytest.skip("libgcrypt.so.20 is not installed on this machine")
+
+
+@pytest.fixture(scope="module")
+def emul_env(emul_lib):
+    """LD_LIBRARY_PATH that makes dropin/_build/libgpqhe.so resolve libgpqhe_b200.so to the
+    emulated build (LD_LIBRARY_PATH is searched before the library's RUNPATH)."""
+    _build_dropin()
+    d = os.path.join(ROOT, "tests", "emul", "_as_real")
+    os.makedirs(d, exist_ok=True)
+    shutil.copyfile(emul_lib, os.path.join(d, "libgpqhe_b200.so"))
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = d + os.pathsep + env.get("LD_LIBRARY_PATH", "")
+    return env
+
+
+def _run(cmd, env=None, timeout=900, cwd=None):
+    p = subprocess.run(cmd, env=env, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout)
+    return p.returncode, p.stdout
+
+
+def _diffs(out):
+    return re.findall(r"diff = (\S+)", out)
+
+
+@pytest.mark.parametrize("args", [("7", "120", "4", "40"), ("6", "438", "4", "50"), ("5", "100", "2", "30")])
+def test_dropin_diff_emulated(emul_env, args):
+    rc, out = _run([os.path.join(BUILD, "dropin_diff"), *args], env=emul_env)
+    assert rc == 0 and "PASS" in out, out[-2000:]
+    assert "direct-limb" in out
+
+
+def test_dropin_diff_emulated_portable_mpi_path(emul_env):
+    env = dict(emul_env, GPQHE_DROPIN_SLOW_MPI="1")
+    rc, out = _run([os.path.join(BUILD, "dropin_diff"), "6", "120", "4", "40"], env=env)
+    assert rc == 0 and "PASS" in out and "gcry_mpi_print/scan" in out, out[-2000:]
+
+
+def test_dropin_exports_reference_symbols():
+    """the drop-in must export everything the reference library exports."""
+    _build_dropin()
+    ref = os.path.join(ROOT, "oracle", "_ref", "libgpqhe.so")
+    if not os.path.exists(ref):
+        pytest.skip("reference build absent")
+
+    def syms(path):
+        out = subprocess.check_output(["nm", "-D", "--defined-only", path], text=True)
+        return {l.split()[-1] for l in out.splitlines() if l.split()[1] in "TBDR"}
+    missing = syms(ref) - syms(os.path.join(BUILD, "libgpqhe.so"))
+    assert not missing, sorted(missing)
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "test-gpqhe")), reason="reference build absent")
+@pytest.mark.parametrize("op", ["mul", "rot", "conj"])
+def test_reference_test_program_same_output_emulated(emul_env, op):
+    """The reference's unmodified tests/gpqhe.c prints `diff = ...` per case; against the drop-in
+    it must print the very same numbers as against the reference library (bit-exact ciphertexts
+    decrypt to identical doubles)."""
+    args = [op, "pk", "--logn=7", "--logq=120", "--slots=4", "--logDelta=40"]
+    _, ours = _run([os.path.join(BUILD, "test-gpqhe"), *args], env=emul_env)
+    _, ref = _run([os.path.join(ROOT, "oracle", "_ref", "test-gpqhe"), *args])
+    assert _diffs(ours) and _diffs(ours) == _diffs(ref), (ours[-1500:], ref[-1500:])
+
+
+def test_reference_polymul_program_emulated(emul_env):
+    """tests/polymul.c (N=2^7, the polynomial tests/polymul.gp computes): same printout."""
+    _, ours = _run([os.path.join(BUILD, "test-polymul")], env=emul_env)
+    ref_bin = os.path.join(ROOT, "oracle", "_ref", "test-polymul")
+    if not os.path.exists(ref_bin):
+        pytest.skip("reference build absent")
+    _, ref = _run([ref_bin])
+    strip = lambda s: [re.sub(r"\x1b\[[0-9;]*m", "", l) for l in s.splitlines() if "us " not in l and "ms " not in l and "Kb used" not in l]
+    assert strip(ours) == strip(ref)
+
+
+# ------------------------------------------------------------------------------- GPU tier
+@pytest.mark.gpu
+@pytest.mark.parametrize("args", [("14", "438", "16", "50", "3"), ("16", "438", "16", "50", "2"), ("12", "109", "4", "30", "4")])
+def test_dropin_diff_gpu(args):
+    _build_dropin()
+    rc, out = _run([os.path.join(BUILD, "dropin_diff"), *args], timeout=1800)
+    assert rc == 0 and "PASS" in out, out[-3000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("op", ["mul", "rot", "conj"])
+def test_reference_kat_program_gpu(op):
+    """configs[0]: ./test-gpqhe <op> pk at the default params.h ring (N=2^14, logq=438, Delta=2^50,
+    -DSUPERCOP stream), the reference's unmodified test program on the GPU library."""
+    _build_dropin()
+    rc, out = _run([os.path.join(BUILD, "test-gpqhe"), op, "pk"], timeout=1800)
+    clean = re.sub(r"\x1b\[[0-9;]*m", "", out)
+    assert "PASSED" in clean and "FAILED" not in clean, clean[-3000:]
+    ref_bin = os.path.join(ROOT, "oracle", "_ref", "test-gpqhe")
+    if op == "mul" and os.path.exists(ref_bin) and _have_gcrypt():
+        _, ref = _run([ref_bin, op, "pk"], timeout=1800)
+        assert _diffs(out) == _diffs(ref), "decoded results differ from the reference run"

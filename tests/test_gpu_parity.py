@@ -22,16 +22,15 @@ def test_limb_layer(real_lib, logn, logq):
     pc.check_limb_layer_vs_oracle(real_lib, logn, 1 << logq, seed=logn, limbs=(0, 1))
 
 
-@pytest.mark.parametrize("logn,q,Delta,levels", [
-    (8, 1 << 120, 1 << 40, None),
-    (10, 1 << 438, 1 << 50, [8, 5, 1]),
-    (12, 1 << 109, 1 << 30, None),
-    (7, (1 << 119) + 12345, (1 << 40) + 7, None),
-    (6, 3 ** 75, 1 << 40, None),
+@pytest.mark.parametrize("logn,q,Delta,levels,logqub", [
+    (8, 1 << 120, 1 << 40, None, 0),
+    (10, 1 << 438, 1 << 50, [8, 5, 1], 438),      # logn in [10,15] consults the security table
+    (12, 1 << 109, 1 << 30, None, 0),
+    (7, (1 << 119) + 12345, (1 << 40) + 7, None, 0),
+    (6, 3 ** 75, 1 << 40, None, 0),
 ])
-def test_he_ops(real_lib, logn, q, Delta, levels):
-    import gpqhe_b200.capi as capi
-    pc.check_he_vs_oracle(real_lib, logn, q, 4, Delta, seed=logn, levels=levels)
+def test_he_ops(real_lib, logn, q, Delta, levels, logqub):
+    pc.check_he_vs_oracle(real_lib, logn, q, 4, Delta, seed=logn, levels=levels, logqub=logqub)
 
 
 def test_kat_ring_n14_he_mul_rs(real_lib):
