@@ -124,7 +124,7 @@ def check_he_vs_oracle(lib_path, logn, q, slots, Delta, seed=0, levels=None, rot
     """MPI layer + he_mul / he_rs / he_moddown / he_rot / he_conj / he_mulpt vs pyoracle."""
     rng = random.Random(seed)
     ctx = g.HeContext(logn, q, slots, Delta, lib_path=lib_path, logqub=logqub)
-    oc = o.Ctx(logn, q, slots, Delta, logqub=logqub)
+    oc = o.Ctx(logn, q, slots, Delta, logqub=logqub or None)
     try:
         n, W = ctx.n, ctx.W
         assert (ctx.L, ctx.dim, ctx.dimevk, ctx.dimub) == (oc.L, oc.dim, oc.dimevk, oc.dimub)

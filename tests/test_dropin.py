@@ -59,7 +59,13 @@ def _diffs(out):
     return re.findall(r"diff = (\S+)", out)
 
 
-@pytest.mark.parametrize("args", [("7", "120", "4", "40"), ("6", "438", "4", "50"), ("5", "100", "2", "30")])
+def _verdicts(out):
+    """pass/fail markers libpmu prints per case, without the timings"""
+    clean = re.sub(r"\x1b\[[0-9;]*m", "", out)
+    return re.findall(r"\b(OK|FAILED|PASSED)\]", clean) + re.findall(r"(\d+/\d+) subtask", clean)
+
+
+@pytest.mark.parametrize("args", [("7", "120", "4", "40"), ("6", "438", "4", "50"), ("8", "200", "8", "40")])
 def test_dropin_diff_emulated(emul_env, args):
     rc, out = _run([os.path.join(BUILD, "dropin_diff"), *args], env=emul_env)
     assert rc == 0 and "PASS" in out, out[-2000:]
@@ -95,7 +101,8 @@ def test_reference_test_program_same_output_emulated(emul_env, op):
     args = [op, "pk", "--logn=7", "--logq=120", "--slots=4", "--logDelta=40"]
     _, ours = _run([os.path.join(BUILD, "test-gpqhe"), *args], env=emul_env)
     _, ref = _run([os.path.join(ROOT, "oracle", "_ref", "test-gpqhe"), *args])
-    assert _diffs(ours) and _diffs(ours) == _diffs(ref), (ours[-1500:], ref[-1500:])
+    assert _verdicts(ours) and _verdicts(ours) == _verdicts(ref), (ours[-1500:], ref[-1500:])
+    assert _diffs(ours) == _diffs(ref), (ours[-1500:], ref[-1500:])
 
 
 def test_reference_polymul_program_emulated(emul_env):
@@ -105,7 +112,8 @@ def test_reference_polymul_program_emulated(emul_env):
     if not os.path.exists(ref_bin):
         pytest.skip("reference build absent")
     _, ref = _run([ref_bin])
-    strip = lambda s: [re.sub(r"\x1b\[[0-9;]*m", "", l) for l in s.splitlines() if "us " not in l and "ms " not in l and "Kb used" not in l]
+    strip = lambda s: [re.sub(r"\d\d:\d\d:\d\d", "", re.sub(r"\x1b\[[0-9;]*m", "", l)) for l in s.splitlines()
+                       if "us " not in l and "ms " not in l and "Kb used" not in l]
     assert strip(ours) == strip(ref)
 
 
