@@ -2,6 +2,7 @@
 // src/precomp.c: prime search, roots, CRT constants, level table), table upload, and
 // the orchestration of the per-stage kernels for each reference entry point.
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -191,6 +192,7 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
   c->dimub = (1 + logn + 4 * logqub) / logp + 1;       // precomp.c:357
   if (c->dimub > GQ_MAX_PRIMES) { delete c; GQ_FAIL("dimub exceeds GQ_MAX_PRIMES"); }
   GQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  c->lazy_ntt = getenv("GPQHE_B200_EXACT_NTT") == nullptr;   // A/B switch for tests and profiling
 
   const unsigned n = c->n, K = c->dimub;
   // primes: p = 2^logp + 1 + k*2N ascending (precomp.c:358-376), or the caller's
@@ -410,6 +412,26 @@ extern "C" int gq_ntt_batch_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsi
   return 0;
 }
 
+// NTT of the internal pipelines: canonical in / canonical out is all they need, so the lazy
+// kernels are used whenever every prime of the range has the shape they assume.
+static int ntt_internal(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys, uint64_t *data,
+                        bool inverse, cudaStream_t st) {
+  bool lazy = c->lazy_ntt;
+  for (unsigned d = limb0; lazy && d < limb0 + nlimbs; d++) {
+    const GqPrime &P = c->primes[d];
+    if (P.bits < 33 || P.bits > 60) { lazy = false; break; }
+    const uint64_t top = 1ull << (P.bits - 1), cc = P.p - top;
+    if (cc >= (top >> 4)) lazy = false;
+  }
+  if (!lazy) return gq_ntt_batch_dev(c, limb0, nlimbs, npolys, data, inverse ? 1 : 0, (void *)st);
+  if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
+  int r = gq_launch_ntt_lazy(c->ntt_tables(), data, (int)limb0, (int)nlimbs, (int)npolys, inverse, st);
+  if (r < 0) GQ_FAIL("unsupported ring degree");
+  c->launches += (unsigned)r;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+
 extern "C" int gq_poly_rns_mul_batch_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys,
                                          uint64_t *r, const uint64_t *a, const uint64_t *b,
                                          void *stream) {
@@ -555,10 +577,10 @@ extern "C" int gq_poly_mul(gq_ctx *c, uint64_t *r, unsigned Wr, const uint64_t *
   GQ_CUDA(cudaMemcpyAsync(da, a, ib, cudaMemcpyHostToDevice, st));
   GQ_CUDA(cudaMemcpyAsync(db, b, ib, cudaMemcpyHostToDevice, st));
   if (decompose_dev(c, 0, dim, ptrs(da, db), W, 2, A, st)) return 1;
-  if (gq_ntt_batch_dev(c, 0, dim, 2, A, 0, st)) return 1;
+  if (ntt_internal(c, 0, dim, 2, A, false, st)) return 1;
   gq_launch_binary(c->d_primes, (int)n, 0, (int)dim, 1, true, B, A, A + (size_t)dim * n, st);
   c->launches++;
-  if (gq_ntt_batch_dev(c, 0, dim, 1, B, 1, st)) return 1;
+  if (ntt_internal(c, 0, dim, 1, B, true, st)) return 1;
   if (reconstruct_dev(c, dim, B, m, ptrs(dr), Wr, 1, st)) return 1;
   GQ_CUDA(cudaMemcpyAsync(r, dr, ob, cudaMemcpyDeviceToHost, st));
   GQ_CUDA(cudaStreamSynchronize(st));
@@ -635,10 +657,10 @@ static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk 
       ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8)) return 1;
   uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
   if (decompose_dev(c, 0, D2, ptrs(d), W, 1, A, st)) return 1;
-  if (gq_ntt_batch_dev(c, 0, D2, 1, A, 0, st)) return 1;
+  if (ntt_internal(c, 0, D2, 1, A, false, st)) return 1;
   gq_launch_mul_evk(c->d_primes, (int)n, (int)D2, B, A, evk->p0, evk->p1, st);
   c->launches++;
-  if (gq_ntt_batch_dev(c, 0, D2, 2, B, 1, st)) return 1;
+  if (ntt_internal(c, 0, D2, 2, B, true, st)) return 1;
   const GqHostModulus &qm = c->qmod[l];
   int r;
   if (qm.dev.is_pow2) {
@@ -679,10 +701,10 @@ extern "C" int gq_he_mul_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, 
   uint64_t *d0 = big, *d1 = big + (size_t)W * n, *d2 = big + 2 * (size_t)W * n;
   // hot loop A (he-mult.c:116-138): decompose, forward NTT, tensor, inverse NTT
   if (decompose_dev(c, 0, D1, ptrs(a0, a1, b0, b1), W, 4, A, st)) return 1;
-  if (gq_ntt_batch_dev(c, 0, D1, 4, A, 0, st)) return 1;
+  if (ntt_internal(c, 0, D1, 4, A, false, st)) return 1;
   gq_launch_tensor(c->d_primes, (int)n, (int)D1, B, A, st);
   c->launches++;
-  if (gq_ntt_batch_dev(c, 0, D1, 3, B, 1, st)) return 1;
+  if (ntt_internal(c, 0, D1, 3, B, true, st)) return 1;
   // hot loop B (he-mult.c:139-141): d0, d1, d2 mod q_l
   if (reconstruct_dev(c, D1, B, c->qmod[l].dev, ptrs(d0, d1, d2), W, 3, st)) return 1;
   // he_relin (he-mult.c:143)
@@ -701,10 +723,10 @@ extern "C" int gq_he_mulpt_dev(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0
       ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8)) return 1;
   uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
   if (decompose_dev(c, 0, dim, ptrs(a0, a1, m), W, 3, A, st)) return 1;
-  if (gq_ntt_batch_dev(c, 0, dim, 3, A, 0, st)) return 1;
+  if (ntt_internal(c, 0, dim, 3, A, false, st)) return 1;
   gq_launch_mul_pt(c->d_primes, (int)n, (int)dim, B, A, st);
   c->launches++;
-  if (gq_ntt_batch_dev(c, 0, dim, 2, B, 1, st)) return 1;
+  if (ntt_internal(c, 0, dim, 2, B, true, st)) return 1;
   return reconstruct_dev(c, dim, B, c->qmod[l].dev, ptrs(c0, c1), W, 2, st);
 }
 

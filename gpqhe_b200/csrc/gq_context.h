@@ -44,6 +44,7 @@ struct gq_ctx {
   void *slot[GQ_SLOT_COUNT] = {nullptr, nullptr, nullptr, nullptr};
   size_t slot_bytes[GQ_SLOT_COUNT] = {0, 0, 0, 0};
   unsigned long long launches = 0;
+  bool lazy_ntt = true;          // internal pipelines use gq_ntt_lazy.cu when every prime allows it
 
   GqNttTables ntt_tables() const {
     GqNttTables t;

@@ -1,0 +1,335 @@
+// gq_ntt_lazy.cu - K1/K2 for the INTERNAL pipelines (poly_mul, he_mul, he_mulpt, key switch):
+// the same transforms as gq_ntt.cu, with lazy (Harvey) butterflies.
+//
+// Why two sets.  ntt() of the reference may store p instead of 0 on the sum leg
+// (src/ntt.c:48); the public gq_ntt / gq_ntt_batch entry points reproduce that bit for bit
+// with the exact butterflies of gq_ntt.cu.  Inside a polynomial product the forward NTT only
+// feeds poly_rns_mul, whose Barrett step maps 0 and p to the same canonical residue
+// (src/poly.c:77-82), and invntt() always ends canonical (src/ntt.c:71-72).  So the internal
+// transforms only have to be right modulo p at their boundaries:
+//   forward : canonical in  -> canonical out   (intermediate values < 14p)
+//   inverse : canonical in  -> canonical out   (intermediate values < 2p, N^-1 folded in)
+// which removes two of the three compare/select pairs of every butterfly (ncu of the exact
+// kernels: ALU pipe 59 %, math-pipe throttle the top stall - instruction count is the bound).
+//
+// Ranges (p < 2^64/15 is checked on the host, else the exact kernels are used):
+//   forward CT butterfly: t = y*w - hi(y*wsh)*p in [0,2p) for ANY y < 2^64;
+//     x' = x + t, y' = x - t + 2p: bounds grow by 2p per stage, no reduction inside a round;
+//     one conditional subtraction of 8p per value per radix-8 round keeps round inputs < 8p
+//     (8p + 3*2p = 14p < 2^64); the last round ends with an exact reduction to [0,p).
+//   inverse GS butterfly: s = x + y (- 2p if >= 2p), d = x - y + 2p, y' = lazy d*w in [0,2p).
+#include "gq_kernels.h"
+
+namespace {
+
+GQ_DEV int swz(int i) { return i ^ ((i >> 4) & 7); }
+GQ_DEV int idx8(int t, int lo) { return ((t >> lo) << (lo + 3)) | (t & ((1 << lo) - 1)); }
+
+GQ_DEV uint64_t csub(uint64_t x, uint64_t m) { return (x >= m) ? x - m : x; }
+
+// x*w mod p in [0,2p), any x
+GQ_DEV uint64_t mul_lazy(uint64_t x, uint64_t w, uint64_t wsh, uint64_t p) {
+  return x * w - gq_mulhi(x, wsh) * p;
+}
+
+GQ_DEV void bf_fwd(uint64_t &x, uint64_t &y, uint64_t w, uint64_t wsh, uint64_t p, uint64_t p2) {
+  const uint64_t t = mul_lazy(y, w, wsh, p);
+  y = x - t + p2;
+  x = x + t;
+}
+GQ_DEV void bf_inv(uint64_t &x, uint64_t &y, uint64_t w, uint64_t wsh, uint64_t p, uint64_t p2) {
+  const uint64_t s = csub(x + y, p2);
+  const uint64_t d = x - y + p2;
+  x = s;
+  y = mul_lazy(d, w, wsh, p);
+}
+// v < 15p  ->  v mod p.  p = 2^sh + c with 16c < 2^sh, so k = v >> sh is floor(v/p) or one more.
+GQ_DEV uint64_t full_reduce(uint64_t v, uint64_t p, int sh) {
+  const uint64_t k = v >> sh;
+  const uint64_t r = v - k * p;
+  return ((int64_t)r < 0) ? r + p : r;
+}
+
+struct PC { uint64_t p, p2, p8; int sh; };
+GQ_DEV PC load_pc(const GqPrime &P) {
+  PC c; c.p = P.p; c.p2 = 2 * P.p; c.p8 = 8 * P.p; c.sh = (int)P.bits - 1; return c;
+}
+
+template <int NB>
+GQ_DEV void fwd_round(uint64_t *v, int lo, int kq, const ulonglong2 *__restrict__ tw, const PC &c) {
+  {
+    const ulonglong2 w = __ldg(&tw[kq >> (lo + 3)]);
+#pragma unroll
+    for (int e = 0; e < 4; e++) bf_fwd(v[e], v[e + 4], w.x, w.y, c.p, c.p2);
+  }
+  if (NB >= 2) {
+    const int kb = kq >> (lo + 2);
+#pragma unroll
+    for (int g = 0; g < 2; g++) {
+      const ulonglong2 w = __ldg(&tw[kb + g]);
+      bf_fwd(v[4 * g + 0], v[4 * g + 2], w.x, w.y, c.p, c.p2);
+      bf_fwd(v[4 * g + 1], v[4 * g + 3], w.x, w.y, c.p, c.p2);
+    }
+  }
+  if (NB >= 3) {
+    const int kb = kq >> (lo + 1);
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+      const ulonglong2 w = __ldg(&tw[kb + g]);
+      bf_fwd(v[2 * g], v[2 * g + 1], w.x, w.y, c.p, c.p2);
+    }
+  }
+}
+
+template <int NB, bool LAST>
+GQ_DEV void inv_round(uint64_t *v, int lo, int kq, const ulonglong2 *__restrict__ tw, const PC &c,
+                      ulonglong2 wlast, uint64_t ninv, uint64_t ninv_sh) {
+  if (NB >= 3) {
+    const int kb = kq >> (lo + 1);
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+      const ulonglong2 w = __ldg(&tw[kb + g]);
+      bf_inv(v[2 * g], v[2 * g + 1], w.x, w.y, c.p, c.p2);
+    }
+  }
+  if (NB >= 2) {
+    const int kb = kq >> (lo + 2);
+#pragma unroll
+    for (int g = 0; g < 2; g++) {
+      const ulonglong2 w = __ldg(&tw[kb + g]);
+      bf_inv(v[4 * g + 0], v[4 * g + 2], w.x, w.y, c.p, c.p2);
+      bf_inv(v[4 * g + 1], v[4 * g + 3], w.x, w.y, c.p, c.p2);
+    }
+  }
+  if (LAST) {   // final stage: N^-1 folded into both legs, canonical out
+#pragma unroll
+    for (int e = 0; e < 4; e++) {
+      const uint64_t s = v[e] + v[e + 4], d = v[e] - v[e + 4] + c.p2;
+      v[e] = csub(mul_lazy(s, ninv, ninv_sh, c.p), c.p);
+      v[e + 4] = csub(mul_lazy(d, wlast.x, wlast.y, c.p), c.p);
+    }
+  } else {
+    const ulonglong2 w = __ldg(&tw[kq >> (lo + 3)]);
+#pragma unroll
+    for (int e = 0; e < 4; e++) bf_inv(v[e], v[e + 4], w.x, w.y, c.p, c.p2);
+  }
+}
+
+template <int LOGT>
+struct TileCfg {
+  static constexpr int T = 1 << LOGT;
+  static constexpr int NT = T / 8;
+  static constexpr int NB0 = (LOGT % 3 == 0) ? 3 : (LOGT % 3);
+  static constexpr int NFULL = (LOGT - NB0) / 3;
+};
+
+// ---- forward tile kernel: 2^LOGT contiguous elements, the last LOGT stages ----------
+// PRE: inputs may be as large as 11p (they come from the strided kernel): reduce below 8p first.
+template <int LOGT, bool PRE>
+__global__ void __launch_bounds__(TileCfg<LOGT>::NT, (TileCfg<LOGT>::NT >= 512 ? 2 : 1))
+k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+  typedef TileCfg<LOGT> C;
+  __shared__ uint64_t sm[C::T];
+  const int t = threadIdx.x;
+  const int m = blockIdx.y;
+  const int d = limb0 + m % nlimbs;
+  const PC c = load_pc(tb.primes[d]);
+  const ulonglong2 *tw = tb.tw_fwd + (size_t)d * tb.n;
+  uint64_t *a = data + (size_t)m * tb.n + (size_t)blockIdx.x * C::T;
+  const int jbase = tb.n + blockIdx.x * C::T;
+  uint64_t v[8];
+#pragma unroll
+  for (int e = 0; e < 8; e++) v[e] = a[e * C::NT + t];
+  if (PRE) {
+#pragma unroll
+    for (int e = 0; e < 8; e++) v[e] = csub(v[e], c.p8);
+  }
+  fwd_round<C::NB0>(v, LOGT - 3, jbase + t, tw, c);
+  if (C::NFULL > 0) {
+#pragma unroll
+    for (int e = 0; e < 8; e++) sm[swz(e * C::NT + t)] = v[e];
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < C::NFULL; r++) {
+      const int lo = LOGT - C::NB0 - 3 * (r + 1);
+      const int base = idx8(t, lo);
+#pragma unroll
+      for (int e = 0; e < 8; e++) v[e] = csub(sm[swz(base | (e << lo))], c.p8);
+      fwd_round<3>(v, lo, jbase + base, tw, c);
+      if (r == C::NFULL - 1) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) v[e] = full_reduce(v[e], c.p, c.sh);
+      }
+#pragma unroll
+      for (int e = 0; e < 8; e++) sm[swz(base | (e << lo))] = v[e];
+      __syncthreads();
+    }
+#pragma unroll
+    for (int e = 0; e < 8; e++) a[e * C::NT + t] = sm[swz(e * C::NT + t)];
+  } else {
+#pragma unroll
+    for (int e = 0; e < 8; e++) a[e * C::NT + t] = full_reduce(v[e], c.p, c.sh);
+  }
+}
+
+// ---- inverse tile kernel: the first LOGT stages; WHOLE: also the final one ------------
+template <int LOGT, bool WHOLE>
+__global__ void __launch_bounds__(TileCfg<LOGT>::NT, (TileCfg<LOGT>::NT >= 512 ? 2 : 1))
+k_nttl_inv_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+  typedef TileCfg<LOGT> C;
+  __shared__ uint64_t sm[C::T];
+  const int t = threadIdx.x;
+  const int m = blockIdx.y;
+  const int d = limb0 + m % nlimbs;
+  const GqPrime pr = tb.primes[d];
+  const PC c = load_pc(pr);
+  const ulonglong2 *tw = tb.tw_inv + (size_t)d * tb.n;
+  const ulonglong2 wlast = tb.tw_inv_last[d];
+  uint64_t *a = data + (size_t)m * tb.n + (size_t)blockIdx.x * C::T;
+  const int jbase = tb.n + blockIdx.x * C::T;
+  uint64_t v[8];
+  if (C::NFULL > 0) {
+#pragma unroll
+    for (int e = 0; e < 8; e++) sm[swz(e * C::NT + t)] = a[e * C::NT + t];
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < C::NFULL; r++) {
+      const int lo = 3 * r;
+      const int base = idx8(t, lo);
+#pragma unroll
+      for (int e = 0; e < 8; e++) v[e] = sm[swz(base | (e << lo))];
+      inv_round<3, false>(v, lo, jbase + base, tw, c, wlast, pr.ninv, pr.ninv_sh);
+#pragma unroll
+      for (int e = 0; e < 8; e++) sm[swz(base | (e << lo))] = v[e];
+      __syncthreads();
+    }
+#pragma unroll
+    for (int e = 0; e < 8; e++) v[e] = sm[swz(e * C::NT + t)];
+  } else {
+#pragma unroll
+    for (int e = 0; e < 8; e++) v[e] = a[e * C::NT + t];
+  }
+  inv_round<C::NB0, WHOLE>(v, LOGT - 3, jbase + t, tw, c, wlast, pr.ninv, pr.ninv_sh);
+#pragma unroll
+  for (int e = 0; e < 8; e++) a[e * C::NT + t] = v[e];
+}
+
+// ---- strided register kernels ------------------------------------------------------
+template <int SA>
+__global__ void __launch_bounds__(256)
+k_nttl_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+  constexpr int R = 1 << SA;
+  const int cols = tb.n >> SA;
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= cols) return;
+  const int m = blockIdx.y;
+  const int d = limb0 + m % nlimbs;
+  const PC c = load_pc(tb.primes[d]);
+  const ulonglong2 *tw = tb.tw_fwd + (size_t)d * tb.n;
+  uint64_t *a = data + (size_t)m * tb.n + col;
+  uint64_t v[R];
+#pragma unroll
+  for (int r = 0; r < R; r++) v[r] = a[(size_t)r * cols];
+#pragma unroll
+  for (int s = 0; s < SA; s++) {       // canonical in: bound 1 + 2*SA <= 11 p, no reduction
+    const int mb = SA - 1 - s;
+#pragma unroll
+    for (int g = 0; g < (1 << s); g++) {
+      const ulonglong2 w = __ldg(&tw[(1 << s) + g]);
+#pragma unroll
+      for (int i = 0; i < (1 << mb); i++) {
+        const int r = (g << (mb + 1)) | i;
+        bf_fwd(v[r], v[r | (1 << mb)], w.x, w.y, c.p, c.p2);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; r++) a[(size_t)r * cols] = v[r];
+}
+
+template <int SA>
+__global__ void __launch_bounds__(256)
+k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+  constexpr int R = 1 << SA;
+  const int cols = tb.n >> SA;
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= cols) return;
+  const int m = blockIdx.y;
+  const int d = limb0 + m % nlimbs;
+  const GqPrime pr = tb.primes[d];
+  const PC c = load_pc(pr);
+  const ulonglong2 *tw = tb.tw_inv + (size_t)d * tb.n;
+  const ulonglong2 wlast = tb.tw_inv_last[d];
+  uint64_t *a = data + (size_t)m * tb.n + col;
+  uint64_t v[R];
+#pragma unroll
+  for (int r = 0; r < R; r++) v[r] = a[(size_t)r * cols];
+#pragma unroll
+  for (int s = SA - 1; s >= 1; s--) {
+    const int mb = SA - 1 - s;
+#pragma unroll
+    for (int g = 0; g < (1 << s); g++) {
+      const ulonglong2 w = __ldg(&tw[(1 << s) + g]);
+#pragma unroll
+      for (int i = 0; i < (1 << mb); i++) {
+        const int r = (g << (mb + 1)) | i;
+        bf_inv(v[r], v[r | (1 << mb)], w.x, w.y, c.p, c.p2);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R / 2; r++) {
+    const uint64_t s = v[r] + v[r + R / 2], dd = v[r] - v[r + R / 2] + c.p2;
+    v[r] = csub(mul_lazy(s, pr.ninv, pr.ninv_sh, c.p), c.p);
+    v[r + R / 2] = csub(mul_lazy(dd, wlast.x, wlast.y, c.p), c.p);
+  }
+#pragma unroll
+  for (int r = 0; r < R; r++) a[(size_t)r * cols] = v[r];
+}
+
+}  // namespace
+
+// Same contract as gq_launch_ntt, canonical in / canonical out only.
+int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
+                       bool inverse, cudaStream_t st) {
+  const int logn = tb.logn;
+  if (logn < 3 || logn > 17) return -1;
+  const int lt = logn > 12 ? 12 : logn, sa = logn - lt;
+  const dim3 gt(tb.n >> lt, nlimbs * npolys), gs(((tb.n >> (sa ? sa : 1)) + 255) / 256, nlimbs * npolys);
+  int launches = 0;
+#define GQ_STRIDED(K) \
+  switch (sa) { \
+    case 1: GQ_LAUNCH(K<1>, gs, dim3(256), st, tb, data, limb0, nlimbs); break; \
+    case 2: GQ_LAUNCH(K<2>, gs, dim3(256), st, tb, data, limb0, nlimbs); break; \
+    case 3: GQ_LAUNCH(K<3>, gs, dim3(256), st, tb, data, limb0, nlimbs); break; \
+    case 4: GQ_LAUNCH(K<4>, gs, dim3(256), st, tb, data, limb0, nlimbs); break; \
+    case 5: GQ_LAUNCH(K<5>, gs, dim3(256), st, tb, data, limb0, nlimbs); break; \
+  }
+  if (!inverse) {
+    if (sa) {
+      GQ_STRIDED(k_nttl_fwd_strided)
+      GQ_LAUNCH((k_nttl_fwd_tile<12, true>), gt, dim3(TileCfg<12>::NT), st, tb, data, limb0, nlimbs);
+      return 2;
+    }
+    switch (lt) {
+#define GQ_CASE(L) case L: GQ_LAUNCH((k_nttl_fwd_tile<L, false>), gt, dim3(TileCfg<L>::NT), st, tb, data, limb0, nlimbs); break;
+      GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8) GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12)
+#undef GQ_CASE
+    }
+    launches = 1;
+  } else {
+    if (sa) {
+      GQ_LAUNCH((k_nttl_inv_tile<12, false>), gt, dim3(TileCfg<12>::NT), st, tb, data, limb0, nlimbs);
+      GQ_STRIDED(k_nttl_inv_strided)
+      return 2;
+    }
+    switch (lt) {
+#define GQ_CASE(L) case L: GQ_LAUNCH((k_nttl_inv_tile<L, true>), gt, dim3(TileCfg<L>::NT), st, tb, data, limb0, nlimbs); break;
+      GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8) GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12)
+#undef GQ_CASE
+    }
+    launches = 1;
+  }
+#undef GQ_STRIDED
+  return launches;
+}

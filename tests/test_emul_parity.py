@@ -71,3 +71,33 @@ def test_small_primes_crt(emul_lib):
     with pytest.raises(g.GpqheError):
         ctx.ntt(np.zeros(n, dtype=np.uint64), 0)
     ctx.close()
+
+
+@pytest.mark.parametrize("logn", [9, 13, 14])
+def test_poly_mul_lazy_ntt_two_kernel_path(emul_lib, logn):
+    """poly_mul runs the lazy (Harvey) NTT kernels of gq_ntt_lazy.cu; above 2^12 that is the
+    strided + tile pair.  Bit-exact vs the oracle, and identical to the exact-NTT pipeline
+    (GPQHE_B200_EXACT_NTT=1 selects the kernels of gq_ntt.cu for the internal transforms)."""
+    import os
+    import random
+    from oracle import pyoracle as o
+    q = 1 << 100
+    rng = random.Random(logn)
+    oc = o.Ctx(logn, q, logqub=100)
+    n = oc.n
+    a = [rng.randrange(q) - q // 2 for _ in range(n)]
+    b = [rng.randrange(q) - q // 2 for _ in range(n)]
+    a[0], a[1], b[0] = 0, q // 2 - 1, -(q // 2)
+    want = o.poly_mul(oc, a, b, 3, q)
+    got = []
+    for exact in (False, True):
+        if exact:
+            os.environ["GPQHE_B200_EXACT_NTT"] = "1"
+        try:
+            ctx = g.HeContext(logn, q, lib_path=emul_lib, logqub=100)
+            W = ctx.W
+            got.append(g.big_to_ints(ctx.poly_mul(g.ints_to_big(a, W), g.ints_to_big(b, W), 3, q)))
+            ctx.close()
+        finally:
+            os.environ.pop("GPQHE_B200_EXACT_NTT", None)
+    assert got[0] == want and got[1] == want
