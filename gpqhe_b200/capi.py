@@ -43,6 +43,7 @@ SIGNATURES = {
     "gq_ctx_sync": (C.c_int, [vp]),
     "gq_ctx_launch_count": (C.c_ulonglong, [vp]),
     "gq_ctx_stream": (vp, [vp]),
+    "gq_ctx_crt_fixups": (C.c_longlong, [vp]),
     "gq_host_alloc": (C.c_int, [C.POINTER(vp), C.c_size_t]),
     "gq_host_free": (None, [vp]),
     "gq_ntt": (C.c_int, [vp, C.c_uint, vp]),

@@ -131,9 +131,9 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
     hb.dev.D = (int)D; hb.dev.WT = 0;
     return 0;
   }
-  std::vector<uint64_t> buf((size_t)(2 + D) * WT + 2 * D, 0);
+  std::vector<uint64_t> buf((size_t)(2 + D) * WT + 4 * D + 2, 0);
   uint64_t *hP = buf.data(), *hPh = hP + WT, *hphat = hPh + WT, *hinv = hphat + (size_t)D * WT,
-           *hinvsh = hinv + D;
+           *hinvsh = hinv + D, *hu = hinvsh + D, *hhc = hu + 2 * D;
   P.store(hP, WT);
   P.shr(1).store(hPh, WT);
   for (unsigned d = 0; d < D; d++) {
@@ -143,6 +143,15 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
     uint64_t inv = powm(phat.mod_u64(pd), pd - 2, pd);   // precomp.c:289
     hinv[d] = inv;
     hinvsh[d] = (uint64_t)(((gq_u128)inv << 64) / pd);
+    const uint64_t one128[3] = {0, 0, 1};
+    BigU(one128, 3).div_u64(pd).store(hu + 2 * d, 2);           // floor(2^128 / p_d) < 2^128
+  }
+  {   // floor(2^128 * ceil(P/2) / P); P is odd, so ceil(P/2) = floor(P/2) + 1
+    BigU half = P.shr(1);
+    std::vector<uint64_t> num(half.w.size() + 3, 0);
+    uint64_t cy = 1;
+    for (size_t i = 0; i < half.w.size() + 1; i++) { uint64_t t = half.word(i) + cy; cy = (cy && t == 0); num[i + 2] = t; }
+    BigU(num.data(), num.size()).div(P).store(hhc, 2);
   }
   uint64_t *dv = nullptr;
   if (upload(&dv, buf.data(), buf.size())) return 1;
@@ -150,6 +159,7 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
   GqCrtBasis &B = hb.dev;
   B.D = (int)D; B.WT = (int)WT; B.bitsP = bitsP;
   B.P = dv; B.Ph = dv + WT; B.phat = dv + 2 * WT; B.inv = B.phat + (size_t)D * WT; B.inv_sh = B.inv + D;
+  B.u = B.inv_sh + D; B.hc = B.u + 2 * D;
   if (bitsP >= 58) {
     B.sh = (int)bitsP - 58;
     BigU top = P.shr((unsigned)B.sh);
@@ -268,6 +278,9 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
     }
   }
   GQ_CUDA(cudaMalloc((void **)&c->d_adhoc, 2 * GQ_MAX_W * sizeof(uint64_t)));
+  GQ_CUDA(cudaMalloc((void **)&c->d_fix, (4 + 4 * (size_t)n) * sizeof(int)));
+  GQ_CUDA(cudaMemset(c->d_fix, 0, 4 * sizeof(int)));
+  c->fast_crt = getenv("GPQHE_B200_EXACT_CRT") == nullptr;    // A/B switch for tests and profiling
 
   // hectx_init / qtable_init (precomp.c:386-452)
   if (Delta) {
@@ -336,7 +349,7 @@ extern "C" void gq_ctx_destroy(gq_ctx *c) {
   if (c->stream) cudaStreamSynchronize(c->stream);
   cudaFree(c->d_primes); cudaFree(c->d_tw_fwd); cudaFree(c->d_tw_inv); cudaFree(c->d_tw_inv_last);
   cudaFree(c->d_pow64); cudaFree(c->d_t1sh); cudaFree(c->d_Pinv); cudaFree(c->d_Pwords);
-  cudaFree(c->d_adhoc);
+  cudaFree(c->d_adhoc); cudaFree(c->d_fix);
   for (auto &b : c->basis) cudaFree(b.blob);
   for (auto &m : c->qmod) cudaFree(m.blob);
   for (int s = 0; s < GQ_SLOT_COUNT; s++) cudaFree(c->slot[s]);
@@ -381,6 +394,13 @@ extern "C" int gq_ctx_sync(gq_ctx *c) {
   return 0;
 }
 extern "C" unsigned long long gq_ctx_launch_count(const gq_ctx *c) { return c ? c->launches : 0; }
+extern "C" long long gq_ctx_crt_fixups(gq_ctx *c) {
+  if (!c || !c->d_fix) return -1;
+  int v[2] = {0, 0};
+  if (cudaStreamSynchronize(c->stream) != cudaSuccess) return -1;
+  if (cudaMemcpy(v, c->d_fix, sizeof v, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  return v[1];
+}
 extern "C" void *gq_ctx_stream(gq_ctx *c) { return c ? (void *)c->stream : nullptr; }
 extern "C" int gq_host_alloc(void **p, size_t bytes) {
   if (!p) GQ_FAIL("null argument");
@@ -506,10 +526,11 @@ static int reconstruct_dev(gq_ctx *c, unsigned D, const uint64_t *rhat, const Gq
                            const GqPtrs4 &out, unsigned Wout, unsigned npolys, cudaStream_t st) {
   if (D == 0 || D > c->dimub) GQ_FAIL("basis size out of range");
   if (c->basis[D - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
-  if (gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)c->n, rhat, q, out, (int)Wout,
-                            (int)npolys, st) < 0)
-    GQ_FAIL("no reconstruct kernel for this width");
-  c->launches++;
+  if (npolys > 4) GQ_FAIL("at most 4 polynomials per reconstruct launch");
+  const int r = gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)c->n, rhat, q, out, (int)Wout,
+                                      (int)npolys, st, c->fast_crt ? c->d_fix : nullptr);
+  if (r < 0) GQ_FAIL("no reconstruct kernel for this width");
+  c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);
   return 0;
 }
@@ -665,14 +686,15 @@ static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk 
   int r;
   if (qm.dev.is_pow2) {
     r = gq_launch_ks_epilogue(c->basis[D2 - 1].dev, c->basis[c->dim - 1].dev, c->d_Pinv, c->d_primes,
-                              (int)n, B, qm.dev.k, ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st);
+                              (int)n, B, qm.dev.k, ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st,
+                              c->fast_crt ? c->d_fix : nullptr);
   } else {
     r = gq_launch_ks_epilogue_general(c->basis[D2 - 1].dev, c->d_Pwords, (int)c->P.w.size(),
                                       c->d_Pwords + GQ_MAX_W, c->d_primes, (int)n, B, qm.dev,
                                       ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st);
   }
   if (r < 0) GQ_FAIL("no key-switch epilogue kernel for these widths");
-  c->launches++;
+  c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);
   return 0;
 }

@@ -23,6 +23,19 @@ GQ_HD void mw_mac(uint64_t *r, uint64_t y, const uint64_t *c) {
   r[W] += carry;
 }
 
+// r += y * c over the low W words only (mod 2^(64W)); the last column needs no high product
+template <int W>
+GQ_HD void mw_mac_low(uint64_t *r, uint64_t y, const uint64_t *c) {
+  uint64_t carry = 0;
+#pragma unroll
+  for (int w = 0; w < W - 1; w++) {
+    gq_u128 t = (gq_u128)y * c[w] + r[w] + carry;
+    r[w] = (uint64_t)t;
+    carry = (uint64_t)(t >> 64);
+  }
+  r[W - 1] += y * c[W - 1] + carry;
+}
+
 // r -= k * c  over W words (mod 2^(64W)); returns nothing
 template <int W>
 GQ_HD void mw_mulsub(uint64_t *r, uint64_t k, const uint64_t *c) {

@@ -39,6 +39,8 @@ struct gq_ctx {
   uint64_t *d_pow64 = nullptr, *d_t1sh = nullptr;
   uint64_t *d_Pinv = nullptr;        // P^-1 mod 2^(64*GQ_MAX_W)
   uint64_t *d_Pwords = nullptr;      // P and floor(P/2), GQ_MAX_W words each (general path)
+  int *d_fix = nullptr;              // {count, pad x3, list[4n]} of the fast CRT kernels
+  bool fast_crt = true;
   uint64_t *d_adhoc = nullptr;       // scratch for an ad-hoc modulus (q, qh)
   // growable device scratch
   void *slot[GQ_SLOT_COUNT] = {nullptr, nullptr, nullptr, nullptr};

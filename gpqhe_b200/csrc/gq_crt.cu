@@ -116,15 +116,9 @@ GQ_DEV void store_words(uint64_t *__restrict__ out, int n, int i, int Wout, cons
 // ---- K5 ---------------------------------------------------------------------------
 // batch: poly b reads rhat + b*D*n, writes out.p[b]
 template <int WT, bool POW2>
-__global__ void __launch_bounds__(128)
-k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
-              const uint64_t *__restrict__ rhat, GqModulus q, GqPtrs4 out, int Wout) {
-  __shared__ CrtShared<WT> S;
-  crt_stage<WT>(S, B, primes);
-  __syncthreads();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int b = blockIdx.y;
+GQ_DEV void reconstruct_one(const CrtShared<WT> &S, const GqCrtBasis &B, int n,
+                            const uint64_t *__restrict__ rhat, const GqModulus &q, const GqPtrs4 &out,
+                            int Wout, int b, int i) {
   uint64_t acc[WT + 1];
   crt_mod_P<WT>(acc, S, B, rhat + (size_t)b * B.D * n, n, i);
   crt_centre<WT>(acc, S);
@@ -136,24 +130,40 @@ k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
   store_words<WT>(out.p[b], n, i, Wout, acc);
 }
 
+// fix_list == null: one thread per coefficient, blockIdx.y = poly.  Otherwise (one block) the
+// coefficients b*n+i that the fast kernel could not decide are taken from the list, which is
+// then emptied for the next call.
+template <int WT, bool POW2>
+__global__ void __launch_bounds__(128)
+k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
+              const uint64_t *__restrict__ rhat, GqModulus q, GqPtrs4 out, int Wout,
+              int *fix_count, const int *__restrict__ fix_list) {
+  __shared__ CrtShared<WT> S;
+  if (fix_list) {
+    const int cnt = *fix_count;
+    if (cnt == 0) return;
+    crt_stage<WT>(S, B, primes);
+    __syncthreads();
+    for (int e = threadIdx.x; e < cnt; e += blockDim.x)
+      reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, fix_list[e] / n, fix_list[e] % n);
+    __syncthreads();
+    if (threadIdx.x == 0) *fix_count = 0;
+    return;
+  }
+  crt_stage<WT>(S, B, primes);
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, blockIdx.y, i);
+}
+
 // ---- K6 (power-of-two q_l fast path) ------------------------------------------------
 // B  : key-switch basis (D2 limbs), BP : basis of the special modulus P (`dim` limbs)
 // Pinv: P^-1 mod 2^(64*WP).  add.p[b]: additive big poly (Wadd words) or null.
 template <int WT, int WP>
-__global__ void __launch_bounds__(128)
-k_ks_epilogue(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
-              const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
-              unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout) {
-  __shared__ CrtShared<WT> S;
-  __shared__ CrtShared<WP> SP;
-  __shared__ uint64_t sPinv[WP];
-  crt_stage<WT>(S, B, primes);
-  crt_stage<WP>(SP, BP, primes);
-  for (int j = threadIdx.x; j < WP; j += blockDim.x) sPinv[j] = Pinv[j];
-  __syncthreads();
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int b = blockIdx.y;
+GQ_DEV void ks_one(const CrtShared<WT> &S, const CrtShared<WP> &SP, const uint64_t *sPinv,
+                   const GqCrtBasis &B, const GqCrtBasis &BP, int n, const uint64_t *__restrict__ chat,
+                   unsigned k, const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int b, int i) {
   const uint64_t *ch = chat + (size_t)b * B.D * n;
   uint64_t T[WT + 1];
   crt_mod_P<WT>(T, S, B, ch, n, i);
@@ -210,6 +220,33 @@ k_ks_epilogue(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
   }
   mw_smod_pow2<WP>(Q, k);
   store_words<WP>(out.p[b], n, i, Wout, Q);
+}
+
+template <int WT, int WP>
+__global__ void __launch_bounds__(128)
+k_ks_epilogue(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
+              const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
+              unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout,
+              int *fix_count, const int *__restrict__ fix_list) {
+  __shared__ CrtShared<WT> S;
+  __shared__ CrtShared<WP> SP;
+  __shared__ uint64_t sPinv[WP];
+  if (fix_list && *fix_count == 0) return;
+  crt_stage<WT>(S, B, primes);
+  crt_stage<WP>(SP, BP, primes);
+  for (int j = threadIdx.x; j < WP; j += blockDim.x) sPinv[j] = Pinv[j];
+  __syncthreads();
+  if (fix_list) {   // one block: the coefficients the fast kernel left undecided
+    const int cnt = *fix_count;
+    for (int e = threadIdx.x; e < cnt; e += blockDim.x)
+      ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, fix_list[e] / n, fix_list[e] % n);
+    __syncthreads();
+    if (threadIdx.x == 0) *fix_count = 0;
+    return;
+  }
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, blockIdx.y, i);
 }
 
 // ---- K6, general modulus: exact long division by P (slow path) -----------------------
@@ -278,6 +315,155 @@ k_ks_epilogue_general(GqCrtBasis B, const uint64_t *__restrict__ Pw, int nP,
   store_words<WT>(out.p[b], n, i, Wout, quot);
 }
 
+// ---- fast K5 / K6 (power-of-two q): low words only --------------------------------------
+// The results above are only needed modulo q = 2^k (k <= 64*W), and the centred CRT value is
+//   T = S - M*P,   S = sum_d y_d * (P/p_d),   M = floor((S + ceil(P/2)) / P)
+// (M counts the multiples of P removed by "mod P" plus the one removed by centring).  Modulo
+// 2^(64W) only the low W words of every P/p_d and of P enter, so the D x WT multiply-accumulate
+// shrinks to D x W - provided M is known exactly.  (S + ceil(P/2))/P = sum_d y_d/p_d + ceil(P/2)/P
+// is evaluated in fixed point with 128 fractional bits from below: est <= true < est + D*2^-67.
+// If the fraction of est is not within 2^-56 of 1 the integer part IS M.  Otherwise (the value
+// sits within 2^-56 of the +P/2 edge; never for honest ciphertexts) the coefficient index is put
+// on a list and recomputed by the exact full-width kernel above in list mode.
+template <int W>
+struct CrtSharedLow {
+  uint64_t phat[GQ_MAX_PRIMES * W];
+  uint64_t P[W];
+  uint64_t inv[GQ_MAX_PRIMES], inv_sh[GQ_MAX_PRIMES], p[GQ_MAX_PRIMES];
+  uint64_t u0[GQ_MAX_PRIMES], u1[GQ_MAX_PRIMES];
+  uint64_t hc[2];
+};
+
+template <int W>
+GQ_DEV void crt_low_stage(CrtSharedLow<W> &S, const GqCrtBasis &B, const GqPrime *primes) {
+  for (int j = threadIdx.x; j < B.D * W; j += blockDim.x) {
+    const int d = j / W, w = j % W;
+    S.phat[j] = (w < B.WT) ? B.phat[d * B.WT + w] : 0;
+  }
+  for (int j = threadIdx.x; j < W; j += blockDim.x) S.P[j] = (j < B.WT) ? B.P[j] : 0;
+  for (int j = threadIdx.x; j < B.D; j += blockDim.x) {
+    S.inv[j] = B.inv[j]; S.inv_sh[j] = B.inv_sh[j]; S.p[j] = primes[j].p;
+    S.u0[j] = B.u[2 * j]; S.u1[j] = B.u[2 * j + 1];
+  }
+  if (threadIdx.x < 2) S.hc[threadIdx.x] = B.hc[threadIdx.x];
+}
+
+// acc[0..W) = low words of the centred CRT value; false if M could not be decided
+template <int W>
+GQ_DEV bool crt_low(uint64_t *acc, const CrtSharedLow<W> &S, int D, const uint64_t *__restrict__ rhat,
+                    int n, int i) {
+#pragma unroll
+  for (int w = 0; w < W; w++) acc[w] = 0;
+  uint64_t e0 = S.hc[0], e1 = S.hc[1], e2 = 0;
+  for (int d = 0; d < D; d++) {
+    const uint64_t y = gq_mul_shoup(rhat[(size_t)d * n + i], S.inv[d], S.inv_sh[d], S.p[d]);
+    mw_mac_low<W>(acc, y, &S.phat[d * W]);
+    // est += y * (u1:u0); only the carry out of the lowest column of y*u0 matters below 2^64
+    const uint64_t h0 = gq_mulhi(y, S.u0[d]), l0 = y * S.u0[d];
+    const uint64_t l1 = y * S.u1[d], h1 = gq_mulhi(y, S.u1[d]);
+    uint64_t t = e0 + l0; uint64_t c = t < l0; e0 = t;
+    t = e1 + h0; uint64_t c1 = t < h0; t += c; c1 += t < c; uint64_t t2 = t + l1; c1 += t2 < l1; e1 = t2;
+    e2 += h1 + c1;
+  }
+  if (e1 >= ~(uint64_t)0 - 255) return false;
+  // acc -= M * P  (low words)
+  const uint64_t M = e2;
+  uint64_t carry = 0, borrow = 0;
+#pragma unroll
+  for (int w = 0; w < W; w++) {
+    gq_u128 t = (gq_u128)M * S.P[w] + carry;
+    const uint64_t lo = (uint64_t)t;
+    carry = (uint64_t)(t >> 64);
+    const uint64_t a = acc[w], dd = a - lo, b1 = a < lo, d2 = dd - borrow, b2 = dd < borrow;
+    acc[w] = d2;
+    borrow = b1 | b2;
+  }
+  return true;
+}
+
+GQ_DEV void fix_push(int *fix_count, int *fix_list, int entry) {
+#ifdef GQ_EMULATE
+  fix_list[(*fix_count)++] = entry;
+  fix_count[1]++;
+#else
+  fix_list[atomicAdd(fix_count, 1)] = entry;
+  atomicAdd(fix_count + 1, 1);          // lifetime total, read by gq_ctx_crt_fixups()
+#endif
+}
+
+template <int W>
+__global__ void __launch_bounds__(256)
+k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
+                   const uint64_t *__restrict__ rhat, unsigned k, GqPtrs4 out, int Wout,
+                   int *fix_count, int *fix_list) {
+  __shared__ CrtSharedLow<W> S;
+  crt_low_stage<W>(S, B, primes);
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = blockIdx.y;
+  uint64_t acc[W];
+  if (!crt_low<W>(acc, S, B.D, rhat + (size_t)b * B.D * n, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
+  mw_smod_pow2<W>(acc, k);
+  store_words<W>(out.p[b], n, i, Wout, acc);
+}
+
+// key-switch epilogue: T low WP words by crt_low over the D2 basis, r = T mod P exactly over the
+// first `dim` limbs (full width WP, cheap), then the same exact quotient as ks_one.
+template <int WP>
+__global__ void __launch_bounds__(128)
+k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
+                   const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
+                   unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout, int *fix_count, int *fix_list) {
+  __shared__ CrtSharedLow<WP> S;
+  __shared__ CrtShared<WP> SP;
+  __shared__ uint64_t sPinv[WP];
+  crt_low_stage<WP>(S, B, primes);
+  crt_stage<WP>(SP, BP, primes);
+  for (int j = threadIdx.x; j < WP; j += blockDim.x) sPinv[j] = Pinv[j];
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = blockIdx.y;
+  const uint64_t *ch = chat + (size_t)b * B.D * n;
+  uint64_t x[WP];
+  if (!crt_low<WP>(x, S, B.D, ch, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
+  bool round_up;
+  {
+    uint64_t r[WP + 1];
+    crt_mod_P<WP>(r, SP, BP, ch, n, i);            // r = T mod P in [0,P)
+    round_up = !mw_geq<WP>(SP.Ph, r);              // r > floor(P/2)
+    mw_sub<WP>(x, x, r);                           // low words of T - r
+  }
+  uint64_t Q[WP];                                  // (T - r) * P^-1 mod 2^(64*WP): the exact quotient
+#pragma unroll
+  for (int w = 0; w < WP; w++) Q[w] = 0;
+#pragma unroll
+  for (int a = 0; a < WP; a++) {
+    uint64_t carry = 0;
+#pragma unroll
+    for (int c = 0; c + a < WP; c++) {
+      gq_u128 t = (gq_u128)x[a] * sPinv[c] + Q[a + c] + carry;
+      Q[a + c] = (uint64_t)t;
+      carry = (uint64_t)(t >> 64);
+    }
+  }
+  {
+    const uint64_t *ap = add.p[b];
+    uint64_t carry = round_up ? 1u : 0u, top = 0;
+#pragma unroll
+    for (int w = 0; w < WP; w++) {
+      uint64_t ad = 0;
+      if (ap) { if (w < Wadd) { ad = ap[(size_t)w * n + i]; top = ad; } else ad = (top >> 63) ? ~(uint64_t)0 : 0; }
+      gq_u128 t = (gq_u128)Q[w] + ad + carry;
+      Q[w] = (uint64_t)t;
+      carry = (uint64_t)(t >> 64);
+    }
+  }
+  mw_smod_pow2<WP>(Q, k);
+  store_words<WP>(out.p[b], n, i, Wout, Q);
+}
+
 // ---- K4 ---------------------------------------------------------------------------
 // (lo,hi) 128-bit value -> canonical residue mod p
 GQ_DEV uint64_t reduce128(uint64_t lo, uint64_t hi, const GqPrime &P, uint64_t T1, uint64_t T1sh) {
@@ -340,71 +526,87 @@ k_decompose(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *
   switch (WTV) { case 8: STMT8; break; case 16: STMT16; break; case 24: STMT24; break; \
                  case 32: STMT32; break; default: return -1; }
 
+// fix: {count, list} scratch of the context; non-null selects the fast low-word kernel followed
+// by the exact kernel in list mode (power-of-two q only).  Returns kernels launched.
 int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st) {
+                          cudaStream_t st, int *fix) {
   dim3 grid((n + 127) / 128, npolys), block(128);
+  int *fc = nullptr, *fl = nullptr;
+  int launches = 1;
+  if (fix && q.is_pow2 && q.k >= 1 && q.k <= 64u * GQ_MAX_W) {
+    fc = fix; fl = fix + 4;
+    const int W = (int)((q.k + 63) / 64);
+    dim3 g2((n + 255) / 256, npolys), b2(256);
+#define GQ_RF(V) GQ_LAUNCH(k_reconstruct_fast<V>, g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl)
+    if (W <= 1) GQ_RF(1); else if (W <= 2) GQ_RF(2); else if (W <= 3) GQ_RF(3); else if (W <= 4) GQ_RF(4);
+    else if (W <= 5) GQ_RF(5); else if (W <= 6) GQ_RF(6); else if (W <= 7) GQ_RF(7); else if (W <= 8) GQ_RF(8);
+    else if (W <= 12) GQ_RF(12); else if (W <= 16) GQ_RF(16); else if (W <= 24) GQ_RF(24); else GQ_RF(32);
+#undef GQ_RF
+    grid = dim3(1, 1);
+    launches = 2;
+  }
   if (q.is_pow2) {
     GQ_WT_SWITCH(B.WT,
-      GQ_LAUNCH((k_reconstruct<8, true>), grid, block, st, B, primes, n, rhat, q, out, Wout),
-      GQ_LAUNCH((k_reconstruct<16, true>), grid, block, st, B, primes, n, rhat, q, out, Wout),
-      GQ_LAUNCH((k_reconstruct<24, true>), grid, block, st, B, primes, n, rhat, q, out, Wout),
-      GQ_LAUNCH((k_reconstruct<32, true>), grid, block, st, B, primes, n, rhat, q, out, Wout))
+      GQ_LAUNCH((k_reconstruct<8, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
+      GQ_LAUNCH((k_reconstruct<16, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
+      GQ_LAUNCH((k_reconstruct<24, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
+      GQ_LAUNCH((k_reconstruct<32, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl))
   } else {
     GQ_WT_SWITCH(B.WT,
-      GQ_LAUNCH((k_reconstruct<8, false>), grid, block, st, B, primes, n, rhat, q, out, Wout),
-      GQ_LAUNCH((k_reconstruct<16, false>), grid, block, st, B, primes, n, rhat, q, out, Wout),
-      GQ_LAUNCH((k_reconstruct<24, false>), grid, block, st, B, primes, n, rhat, q, out, Wout),
-      GQ_LAUNCH((k_reconstruct<32, false>), grid, block, st, B, primes, n, rhat, q, out, Wout))
+      GQ_LAUNCH((k_reconstruct<8, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
+      GQ_LAUNCH((k_reconstruct<16, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
+      GQ_LAUNCH((k_reconstruct<24, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
+      GQ_LAUNCH((k_reconstruct<32, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl))
   }
-  return 1;
+  return launches;
 }
 
 template <int WT>
 static int ks_dispatch_wp(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, dim3 grid,
-                          cudaStream_t st) {
+                          cudaStream_t st, int *fc, int *fl) {
   dim3 block(128);
   if (BP.WT > WT) return -1;
+#define GQ_KS(WPV) GQ_LAUNCH((k_ks_epilogue<WT, (WT >= WPV ? WPV : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl)
   switch (BP.WT) {
-    case 8:
-      GQ_LAUNCH((k_ks_epilogue<WT, 8>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout);
-      return 1;
-    case 16:
-      if (WT >= 16) {
-        GQ_LAUNCH((k_ks_epilogue<WT, (WT >= 16 ? 16 : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout);
-        return 1;
-      }
-      return -1;
-    case 24:
-      if (WT >= 24) {
-        GQ_LAUNCH((k_ks_epilogue<WT, (WT >= 24 ? 24 : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout);
-        return 1;
-      }
-      return -1;
-    case 32:
-      if (WT >= 32) {
-        GQ_LAUNCH((k_ks_epilogue<WT, (WT >= 32 ? 32 : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout);
-        return 1;
-      }
-      return -1;
+    case 8: GQ_KS(8); return 1;
+    case 16: if (WT >= 16) { GQ_KS(16); return 1; } return -1;
+    case 24: if (WT >= 24) { GQ_KS(24); return 1; } return -1;
+    case 32: if (WT >= 32) { GQ_KS(32); return 1; } return -1;
   }
+#undef GQ_KS
   return -1;
 }
 
 int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st) {
+                          cudaStream_t st, int *fix) {
   dim3 grid((n + 127) / 128, npolys);
-  switch (B.WT) {
-    case 8: return ks_dispatch_wp<8>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st);
-    case 16: return ks_dispatch_wp<16>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st);
-    case 24: return ks_dispatch_wp<24>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st);
-    case 32: return ks_dispatch_wp<32>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st);
+  int *fc = nullptr, *fl = nullptr;
+  int launches = 1;
+  if (fix && k >= 1 && BP.WT <= B.WT) {
+    fc = fix; fl = fix + 4;
+    dim3 block(128);
+    switch (BP.WT) {
+#define GQ_KF(V) case V: GQ_LAUNCH(k_ks_epilogue_fast<V>, grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl); break;
+      GQ_KF(8) GQ_KF(16) GQ_KF(24) GQ_KF(32)
+#undef GQ_KF
+      default: return -1;
+    }
+    grid = dim3(1, 1);
+    launches = 2;
   }
-  return -1;
+  int r = -1;
+  switch (B.WT) {
+    case 8: r = ks_dispatch_wp<8>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl); break;
+    case 16: r = ks_dispatch_wp<16>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl); break;
+    case 24: r = ks_dispatch_wp<24>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl); break;
+    case 32: r = ks_dispatch_wp<32>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl); break;
+  }
+  return r < 0 ? r : launches;
 }
 
 template <int W>

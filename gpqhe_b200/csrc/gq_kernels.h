@@ -23,16 +23,17 @@ void gq_launch_mul_evk(const GqPrime *primes, int n, int D, uint64_t *y, const u
 void gq_launch_mul_pt(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
                       cudaStream_t st);
 
-// K4/K5/K6 (gq_crt.cu); return 1 on launch, <0 when no instantiation fits
+// K4/K5/K6 (gq_crt.cu); return the number of kernels launched, <0 when no instantiation fits.
+// fix = device scratch {int count (16-byte slot), int list[4n]}: enables the fast low-word kernels
 int gq_launch_decompose(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
                         int W, uint64_t *out, int npolys, cudaStream_t st);
 int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st);
+                          cudaStream_t st, int *fix = nullptr);
 int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st);
+                          cudaStream_t st, int *fix = nullptr);
 // general-modulus key-switch epilogue (exact long division, slow path)
 int gq_launch_ks_epilogue_general(const GqCrtBasis &B, const uint64_t *P, int nP,
                                   const uint64_t *Ph, const GqPrime *primes, int n,

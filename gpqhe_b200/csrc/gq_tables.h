@@ -39,6 +39,10 @@ struct GqCrtBasis {
   const uint64_t *phat;   // [D][WT]   P / p_d
   const uint64_t *inv;    // [D]       (P/p_d)^-1 mod p_d          (phat_invmp)
   const uint64_t *inv_sh; // [D]       Shoup companion
+  // fixed-point image of 1/p_d and of ceil(P/2)/P with 128 fractional bits: lets the fast CRT
+  // kernels find the overflow count floor((S + ceil(P/2))/P) without the high words of S
+  const uint64_t *u;      // [D][2]    floor(2^128 / p_d)
+  const uint64_t *hc;     // [2]       floor(2^128 * ceil(P/2) / P)
 };
 
 // a modulus q used by mpi_smod (src/types.c:108): power-of-two fast path or general

@@ -177,6 +177,11 @@ class HeContext:
     def launch_count(self) -> int:
         return int(self._lib.gq_ctx_launch_count(self._h))
 
+    @property
+    def crt_fixups(self) -> int:
+        """coefficients the fast CRT kernels passed on to the exact full-width kernel"""
+        return int(self._lib.gq_ctx_crt_fixups(self._h))
+
     def sync(self):
         capi.check(self._lib, self._lib.gq_ctx_sync(self._h))
 

@@ -82,6 +82,9 @@ int gq_ctx_sync(gq_ctx *ctx);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 unsigned long long gq_ctx_launch_count(const gq_ctx *ctx);
 void *gq_ctx_stream(gq_ctx *ctx); /* the context's cudaStream_t */
+/* coefficients the fast CRT kernels handed to the exact full-width kernel since creation
+ * (values within 2^-56 of the +P/2 edge; diagnostics for the edge-case tests), -1 on error */
+long long gq_ctx_crt_fixups(gq_ctx *ctx);
 
 /* pinned host memory for callers that want fast copies */
 int gq_host_alloc(void **p, size_t bytes);

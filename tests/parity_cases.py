@@ -172,3 +172,52 @@ def check_he_vs_oracle(lib_path, logn, q, slots, Delta, seed=0, levels=None, rot
             assert g.big_to_ints(r7.c0) == e7["c0"], "he_mul(x,x)"
     finally:
         ctx.close()
+
+
+def check_crt_edges(lib_path, logn=5, q=1 << 438, Delta=1 << 50, logqub=438):
+    """Edge values of the centred CRT range (the +P/2 boundary, 0, -1 ...) through poly_rns2mpi and,
+    with a crafted switching key, through the key-switch epilogue: these are the inputs on which
+    the fast low-word CRT kernels cannot decide the overflow count and must hand the coefficient
+    to the exact full-width kernel.  Bit-exact vs the oracle, and the hand-over must have happened."""
+    ctx = g.HeContext(logn, q, 4, Delta, lib_path=lib_path, logqub=logqub)
+    oc = o.Ctx(logn, q, 4, Delta, logqub=logqub)
+    try:
+        n, W = ctx.n, ctx.W
+        before = ctx.crt_fixups
+        for dim in sorted({2, ctx.dim, ctx.dimevk}):
+            P = oc.rns[dim - 1].P
+            Ph = P // 2
+            edge = [Ph - 1, Ph, Ph + 1, 0, 1, P - 1, Ph - 2, Ph + 2, P - Ph, 12345, P - 12345, Ph - (1 << 64)]
+            vals = [edge[i % len(edge)] for i in range(n)]
+            rh = np.stack([np.array([v % oc.primes[d] for v in vals], dtype=np.uint64) for d in range(dim)]).reshape(-1)
+            for qq in (q, 1 << 64, 1 << 65, 2):
+                Wr = max(1, (qq.bit_length() + 63) // 64)
+                got = g.big_to_ints(ctx.poly_rns2mpi(rh, dim, qq, Wr))
+                assert got == o.poly_rns2mpi(rh, oc.rns[dim - 1], qq, n), ("poly_rns2mpi edge", dim, qq.bit_length())
+        assert ctx.crt_fixups > before, "edge values must take the exact list path"
+        # key switch: c1 = 1 (constant), evk = NTT(residues of Z): the epilogue then sees exactly Z
+        before = ctx.crt_fixups
+        l = oc.L
+        D2 = ctx.dims(l)[1]
+        PB = oc.rns[D2 - 1].P
+        Ph = PB // 2
+        edge = [Ph - 1, Ph, Ph + 1, 0, PB - 1, 1, Ph - 5, 7]
+        z0 = [edge[i % len(edge)] for i in range(n)]
+        z1 = [edge[(i + 3) % len(edge)] for i in range(n)]
+
+        def key(z):
+            out = np.zeros((oc.dimevk, n), dtype=np.uint64)
+            for d in range(oc.dimevk):
+                out[d] = o.ntt(np.array([v % oc.primes[d] for v in z], dtype=np.uint64), oc.rns[d])
+            return out.reshape(-1)
+        p0, p1 = key(z0), key(z1)
+        evk = ctx.genevk(p0, p1)
+        one = [1] + [0] * (n - 1)
+        c0 = [((i * 977) % 1000) - 500 for i in range(n)]
+        ct = g.HeCt(l, g.ints_to_big(c0, W), g.ints_to_big(one, W))
+        r = ctx.he_rot(ct, 0, {0: evk})
+        e = o.he_rot(oc, {"l": l, "c0": c0, "c1": one}, 0, (p0, p1))
+        assert g.big_to_ints(r.c0) == e["c0"] and g.big_to_ints(r.c1) == e["c1"], "key-switch epilogue at the P/2 edge"
+        assert ctx.crt_fixups > before, "edge values must take the exact list path (key switch)"
+    finally:
+        ctx.close()

@@ -101,3 +101,7 @@ def test_poly_mul_lazy_ntt_two_kernel_path(emul_lib, logn):
         finally:
             os.environ.pop("GPQHE_B200_EXACT_NTT", None)
     assert got[0] == want and got[1] == want
+
+
+def test_crt_edge_values_take_exact_path(emul_lib):
+    pc.check_crt_edges(emul_lib)

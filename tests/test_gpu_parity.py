@@ -93,3 +93,8 @@ def test_full_size_n16_he_mul_rs_rot(real_lib):
         assert set(np.unique(top).tolist()) <= {0, -1}, "centred range of q_L"
     finally:
         ctx.close()
+
+
+def test_crt_edge_values_take_exact_path(real_lib):
+    pc.check_crt_edges(real_lib)
+    pc.check_crt_edges(real_lib, logn=12, q=1 << 109, Delta=1 << 30, logqub=109)
