@@ -264,7 +264,16 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
       for (unsigned w = 0; w < GQ_DEC_W; w++) { pw[(size_t)d * GQ_DEC_W + w] = v; v = mulm(v, b, pd); }
       t1[d] = (uint64_t)(((gq_u128)b << 64) / pd);
     }
-    if (upload(&c->d_pow64, pw.data(), pw.size()) || upload(&c->d_t1sh, t1.data(), t1.size())) {
+    std::vector<uint64_t> p32((size_t)K * GQ_DEC32), osh(K);
+    for (unsigned d = 0; d < K; d++) {
+      const uint64_t pd = c->primes[d].p;
+      uint64_t v = 1 % pd;
+      const uint64_t b32 = (1ull << 32) % pd;
+      for (unsigned j = 0; j < GQ_DEC32; j++) { p32[(size_t)d * GQ_DEC32 + j] = v; v = mulm(v, b32, pd); }
+      osh[d] = (uint64_t)((((gq_u128)1) << 64) / pd);
+    }
+    if (upload(&c->d_pow64, pw.data(), pw.size()) || upload(&c->d_t1sh, t1.data(), t1.size()) ||
+        upload(&c->d_pow32, p32.data(), p32.size()) || upload(&c->d_onesh, osh.data(), osh.size())) {
       gq_ctx_destroy(c); return 1;
     }
   }
@@ -348,7 +357,7 @@ extern "C" void gq_ctx_destroy(gq_ctx *c) {
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   cudaFree(c->d_primes); cudaFree(c->d_tw_fwd); cudaFree(c->d_tw_inv); cudaFree(c->d_tw_inv_last);
-  cudaFree(c->d_pow64); cudaFree(c->d_t1sh); cudaFree(c->d_Pinv); cudaFree(c->d_Pwords);
+  cudaFree(c->d_pow64); cudaFree(c->d_t1sh); cudaFree(c->d_pow32); cudaFree(c->d_onesh); cudaFree(c->d_Pinv); cudaFree(c->d_Pwords);
   cudaFree(c->d_adhoc); cudaFree(c->d_fix);
   for (auto &b : c->basis) cudaFree(b.blob);
   for (auto &m : c->qmod) cudaFree(m.blob);
@@ -514,8 +523,11 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
                          unsigned npolys, uint64_t *out, cudaStream_t st) {
   if (limb0 + nlimbs > c->dimub) GQ_FAIL("limb range exceeds dimub");
   if (W == 0 || W > GQ_MAX_W) GQ_FAIL("word count out of range");
+  bool digits = c->fast_crt && W <= 8;      // A1 of k_decompose32 stays below 2^64 for <= 15 digits
+  for (unsigned d = limb0; digits && d < limb0 + nlimbs; d++)
+    digits = c->primes[d].bits >= 33 && c->primes[d].bits <= 60;
   if (gq_launch_decompose(c->dec_tables(), (int)c->n, (int)limb0, (int)nlimbs, in, (int)W, out,
-                          (int)npolys, st) < 0)
+                          (int)npolys, st, digits) < 0)
     GQ_FAIL("no decompose kernel for this width");
   c->launches++;
   GQ_CHECK_LAUNCH(c);

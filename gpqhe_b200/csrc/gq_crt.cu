@@ -477,6 +477,63 @@ GQ_DEV uint64_t reduce128(uint64_t lo, uint64_t hi, const GqPrime &P, uint64_t T
   return (uint64_t)(v % P.p);
 }
 
+// K4, digit form (primes of at least 33 bits).  The coefficient is read as 2W 32-bit digits x_j;
+//   sum_j x_j * (2^(32j) mod p)  =  A0 + 2^32 * A1,   A0 = sum x_j * lo32(U_j) (< 2^70),
+//                                                      A1 = sum x_j * hi32(U_j) (< 2^64 for p < 2^61)
+// costs two 32x32 multiply-adds per digit instead of a 64x64 product plus a 192-bit add per
+// word; the 100-bit total is folded once with two lazy Shoup products (by 2^64 mod p and by 1).
+template <int W>
+__global__ void __launch_bounds__(256)
+k_decompose32(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *__restrict__ out) {
+  __shared__ uint64_t sU[GQ_MAX_PRIMES * 2 * W];
+  __shared__ uint64_t sC[GQ_MAX_PRIMES * 6];      // p, T1, T1sh, one_sh, TW, pad
+  for (int j = threadIdx.x; j < nlimbs * 2 * W; j += blockDim.x)
+    sU[j] = dt.pow32[(size_t)(limb0 + j / (2 * W)) * GQ_DEC32 + j % (2 * W)];
+  for (int d = threadIdx.x; d < nlimbs; d += blockDim.x) {
+    sC[6 * d + 0] = dt.primes[limb0 + d].p;
+    sC[6 * d + 1] = dt.pow64[(size_t)(limb0 + d) * GQ_DEC_W + 1];
+    sC[6 * d + 2] = dt.t1_sh[limb0 + d];
+    sC[6 * d + 3] = dt.one_sh[limb0 + d];
+    sC[6 * d + 4] = dt.pow64[(size_t)(limb0 + d) * GQ_DEC_W + W];
+  }
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = blockIdx.y;
+  const uint64_t *src = (b == 0) ? in.p[0] : (b == 1) ? in.p[1] : (b == 2) ? in.p[2] : in.p[3];
+  uint64_t *dst = out + (size_t)b * nlimbs * n;
+  uint32_t x[2 * W];
+#pragma unroll
+  for (int w = 0; w < W; w++) {
+    const uint64_t v = src[(size_t)w * n + i];
+    x[2 * w] = (uint32_t)v; x[2 * w + 1] = (uint32_t)(v >> 32);
+  }
+  const bool neg = (x[2 * W - 1] >> 31) != 0;
+  for (int d = 0; d < nlimbs; d++) {
+    const uint64_t *U = &sU[d * 2 * W];
+    const uint64_t p = sC[6 * d], T1 = sC[6 * d + 1], T1sh = sC[6 * d + 2], osh = sC[6 * d + 3];
+    gq_u128 A0 = x[0];
+    uint64_t A1 = 0;
+#pragma unroll
+    for (int j = 1; j < 2 * W; j++) {
+      const uint64_t u = U[j];
+      A0 += (uint64_t)x[j] * (uint32_t)u;
+      A1 += (uint64_t)x[j] * (uint32_t)(u >> 32);
+    }
+    const gq_u128 V = A0 + ((gq_u128)A1 << 32);
+    const uint64_t vlo = (uint64_t)V, vhi = (uint64_t)(V >> 64);
+    // vhi*2^64 + vlo  ==  vhi*T1 + vlo*1 (mod p), each lazy product in [0,2p)
+    uint64_t r = (vhi * T1 - gq_mulhi(vhi, T1sh) * p) + (vlo - gq_mulhi(vlo, osh) * p);
+    r = (r >= 2 * p) ? r - 2 * p : r;
+    r = (r >= p) ? r - p : r;
+    if (neg) {
+      const uint64_t TW = sC[6 * d + 4];
+      r = (r >= TW) ? r - TW : r - TW + p;
+    }
+    dst[(size_t)d * n + i] = r;
+  }
+}
+
 template <int W>
 __global__ void __launch_bounds__(256)
 k_decompose(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *__restrict__ out) {
@@ -611,15 +668,16 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
 
 template <int W>
 static void dec_launch(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
-                       uint64_t *out, int npolys, cudaStream_t st) {
+                       uint64_t *out, int npolys, cudaStream_t st, bool digits) {
   dim3 grid((n + 255) / 256, npolys), block(256);
-  GQ_LAUNCH(k_decompose<W>, grid, block, st, dt, n, limb0, nlimbs, in, out);
+  if (digits) GQ_LAUNCH(k_decompose32<W>, grid, block, st, dt, n, limb0, nlimbs, in, out);
+  else GQ_LAUNCH(k_decompose<W>, grid, block, st, dt, n, limb0, nlimbs, in, out);
 }
 
 int gq_launch_decompose(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
-                        int W, uint64_t *out, int npolys, cudaStream_t st) {
+                        int W, uint64_t *out, int npolys, cudaStream_t st, bool digits) {
   switch (W) {
-#define GQ_CASE(V) case V: dec_launch<V>(dt, n, limb0, nlimbs, in, out, npolys, st); return 1;
+#define GQ_CASE(V) case V: dec_launch<V>(dt, n, limb0, nlimbs, in, out, npolys, st, digits); return 1;
     GQ_CASE(1) GQ_CASE(2) GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8)
     GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12) GQ_CASE(13) GQ_CASE(14) GQ_CASE(15) GQ_CASE(16)
     GQ_CASE(17) GQ_CASE(18) GQ_CASE(19) GQ_CASE(20) GQ_CASE(21) GQ_CASE(22) GQ_CASE(23) GQ_CASE(24)

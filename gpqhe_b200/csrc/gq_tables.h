@@ -20,8 +20,13 @@ struct GqNttTables {
 
 // MPI -> RNS view (K4): pow64[d*GQ_DEC_W + w] = 2^(64w) mod p_d; t1_sh[d] is the Shoup
 // companion of pow64[d][1].
+// pow32[d*GQ_DEC32 + j] = 2^(32j) mod p_d for j = 0..2*GQ_MAX_W-1 (digit form of the same table);
+// one_sh[d] = floor(2^64 / p_d), the Shoup companion of the constant 1.
+#define GQ_DEC32 (2 * GQ_MAX_W)
 struct GqDecTables {
   const GqPrime *primes;
+  const uint64_t *pow32;
+  const uint64_t *one_sh;
   const uint64_t *pow64;
   const uint64_t *t1_sh;
 };
