@@ -73,6 +73,13 @@ SIGNATURES = {
     "gq_he_moddown_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp]),
     "gq_he_rot_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp]),
     "gq_he_conj_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp]),
+    "gq_stage_decompose_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.POINTER(vp), C.c_uint, C.c_uint, vp, vp]),
+    "gq_stage_ntt_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.c_int, vp]),
+    "gq_stage_tensor_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp]),
+    "gq_stage_mul_evk_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp]),
+    "gq_stage_reconstruct_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.POINTER(vp), C.c_uint, vp]),
+    "gq_stage_ks_epilogue_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, vp]),
+    "gq_stage_rescale_dev": (C.c_int, [vp, C.c_uint, vp, vp, C.c_int, C.c_uint, vp]),
 }
 
 _loaded: dict[str, C.CDLL] = {}

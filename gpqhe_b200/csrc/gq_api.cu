@@ -444,7 +444,7 @@ extern "C" int gq_ntt_batch_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsi
 // NTT of the internal pipelines: canonical in / canonical out is all they need, so the lazy
 // kernels are used whenever every prime of the range has the shape they assume.
 static int ntt_internal(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys, uint64_t *data,
-                        bool inverse, cudaStream_t st) {
+                        bool inverse, cudaStream_t st, int only = 0) {
   bool lazy = c->lazy_ntt;
   for (unsigned d = limb0; lazy && d < limb0 + nlimbs; d++) {
     const GqPrime &P = c->primes[d];
@@ -452,9 +452,9 @@ static int ntt_internal(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npo
     const uint64_t top = 1ull << (P.bits - 1), cc = P.p - top;
     if (cc >= (top >> 4)) lazy = false;
   }
-  if (!lazy) return gq_ntt_batch_dev(c, limb0, nlimbs, npolys, data, inverse ? 1 : 0, (void *)st);
+  if (!lazy) return gq_ntt_batch_dev(c, limb0, nlimbs, npolys, data, (inverse ? 1 : 0) | (only << 1), (void *)st);
   if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
-  int r = gq_launch_ntt_lazy(c->ntt_tables(), data, (int)limb0, (int)nlimbs, (int)npolys, inverse, st);
+  int r = gq_launch_ntt_lazy(c->ntt_tables(), data, (int)limb0, (int)nlimbs, (int)npolys, inverse, st, only);
   if (r < 0) GQ_FAIL("unsupported ring degree");
   c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);
@@ -519,14 +519,17 @@ static GqPtrs4 ptrs(const uint64_t *a, const uint64_t *b = nullptr, const uint64
   return p;
 }
 
+// ncoef: coefficients per polynomial in this call (0 = the whole ring); the coefficient-local
+// stages work on any slice because one thread owns one coefficient
 static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtrs4 &in, unsigned W,
-                         unsigned npolys, uint64_t *out, cudaStream_t st) {
+                         unsigned npolys, uint64_t *out, cudaStream_t st, unsigned ncoef = 0) {
+  if (ncoef == 0) ncoef = c->n;
   if (limb0 + nlimbs > c->dimub) GQ_FAIL("limb range exceeds dimub");
   if (W == 0 || W > GQ_MAX_W) GQ_FAIL("word count out of range");
   bool digits = c->fast_crt && W <= 8;      // A1 of k_decompose32 stays below 2^64 for <= 15 digits
   for (unsigned d = limb0; digits && d < limb0 + nlimbs; d++)
     digits = c->primes[d].bits >= 33 && c->primes[d].bits <= 60;
-  if (gq_launch_decompose(c->dec_tables(), (int)c->n, (int)limb0, (int)nlimbs, in, (int)W, out,
+  if (gq_launch_decompose(c->dec_tables(), (int)ncoef, (int)limb0, (int)nlimbs, in, (int)W, out,
                           (int)npolys, st, digits) < 0)
     GQ_FAIL("no decompose kernel for this width");
   c->launches++;
@@ -535,11 +538,13 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
 }
 
 static int reconstruct_dev(gq_ctx *c, unsigned D, const uint64_t *rhat, const GqModulus &q,
-                           const GqPtrs4 &out, unsigned Wout, unsigned npolys, cudaStream_t st) {
+                           const GqPtrs4 &out, unsigned Wout, unsigned npolys, cudaStream_t st,
+                           unsigned ncoef = 0) {
+  if (ncoef == 0) ncoef = c->n;
   if (D == 0 || D > c->dimub) GQ_FAIL("basis size out of range");
   if (c->basis[D - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
   if (npolys > 4) GQ_FAIL("at most 4 polynomials per reconstruct launch");
-  const int r = gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)c->n, rhat, q, out, (int)Wout,
+  const int r = gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)ncoef, rhat, q, out, (int)Wout,
                                       (int)npolys, st, c->fast_crt ? c->d_fix : nullptr);
   if (r < 0) GQ_FAIL("no reconstruct kernel for this width");
   c->launches += (unsigned)r;
@@ -677,6 +682,30 @@ extern "C" void gq_evk_destroy(gq_evk *e) {
 }
 
 // ------------------------------------------------------------------ HE primitives (device)
+// K6 on a coefficient slice: chat[2][D2][ncoef] -> c0, c1 (W words each), + add0/add1 (may be null)
+static int ks_epilogue_dev(gq_ctx *c, unsigned l, unsigned D2, const uint64_t *B, const uint64_t *add0,
+                           const uint64_t *add1, uint64_t *c0, uint64_t *c1, unsigned ncoef,
+                           cudaStream_t st) {
+  if (ncoef == 0) ncoef = c->n;
+  const unsigned n = ncoef, W = c->W;
+  if (D2 == 0 || D2 > c->dimub || c->basis[D2 - 1].dev.WT == 0) GQ_FAIL("key-switch basis not supported");
+  const GqHostModulus &qm = c->qmod[l];
+  int r;
+  if (qm.dev.is_pow2) {
+    r = gq_launch_ks_epilogue(c->basis[D2 - 1].dev, c->basis[c->dim - 1].dev, c->d_Pinv, c->d_primes,
+                              (int)n, B, qm.dev.k, ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st,
+                              c->fast_crt ? c->d_fix : nullptr);
+  } else {
+    r = gq_launch_ks_epilogue_general(c->basis[D2 - 1].dev, c->d_Pwords, (int)c->P.w.size(),
+                                      c->d_Pwords + GQ_MAX_W, c->d_primes, (int)n, B, qm.dev,
+                                      ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st);
+  }
+  if (r < 0) GQ_FAIL("no key-switch epilogue kernel for these widths");
+  c->launches += (unsigned)r;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+
 // Key switch shared by he_relin (he-mult.c:40-85) and he_swk (he-automorphism.c:40-85):
 //   out_k = smod_ql( rdiv(d * evk.p_k, P) + add_k ),  k = 0,1 ; add_k may be null.
 static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk *evk,
@@ -694,21 +723,7 @@ static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk 
   gq_launch_mul_evk(c->d_primes, (int)n, (int)D2, B, A, evk->p0, evk->p1, st);
   c->launches++;
   if (ntt_internal(c, 0, D2, 2, B, true, st)) return 1;
-  const GqHostModulus &qm = c->qmod[l];
-  int r;
-  if (qm.dev.is_pow2) {
-    r = gq_launch_ks_epilogue(c->basis[D2 - 1].dev, c->basis[c->dim - 1].dev, c->d_Pinv, c->d_primes,
-                              (int)n, B, qm.dev.k, ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st,
-                              c->fast_crt ? c->d_fix : nullptr);
-  } else {
-    r = gq_launch_ks_epilogue_general(c->basis[D2 - 1].dev, c->d_Pwords, (int)c->P.w.size(),
-                                      c->d_Pwords + GQ_MAX_W, c->d_primes, (int)n, B, qm.dev,
-                                      ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st);
-  }
-  if (r < 0) GQ_FAIL("no key-switch epilogue kernel for these widths");
-  c->launches += (unsigned)r;
-  GQ_CHECK_LAUNCH(c);
-  return 0;
+  return ks_epilogue_dev(c, l, D2, B, add0, add1, c0, c1, 0, st);
 }
 
 static int he_check(const gq_ctx *c, unsigned l) {
@@ -764,7 +779,9 @@ extern "C" int gq_he_mulpt_dev(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0
   return reconstruct_dev(c, dim, B, c->qmod[l].dev, ptrs(c0, c1), W, 2, st);
 }
 
-static int rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, bool divide, void *stream) {
+static int rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, bool divide, void *stream,
+                       unsigned ncoef = 0) {
+  if (c && ncoef == 0) ncoef = c->n;
   if (he_check(c, l)) return 1;
   if (l == 0) GQ_FAIL("cannot go below level 0");
   if (!c0 || !c1) GQ_FAIL("null argument");
@@ -772,9 +789,9 @@ static int rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, bool d
   const GqHostModulus &qm = c->qmod[l - 1];
   const bool dpow2 = (c->Delta & (c->Delta - 1)) == 0;
   if (qm.dev.is_pow2 && (dpow2 || !divide))
-    gq_launch_rescale_pow2((int)c->n, (int)c->W, ptrs(c0, c1), 2, divide ? c->logDelta : 0, qm.dev.k, st);
+    gq_launch_rescale_pow2((int)ncoef, (int)c->W, ptrs(c0, c1), 2, divide ? c->logDelta : 0, qm.dev.k, st);
   else
-    gq_launch_rescale_general((int)c->n, (int)c->W, ptrs(c0, c1), 2, divide ? c->Delta : 1, qm.dev, st);
+    gq_launch_rescale_general((int)ncoef, (int)c->W, ptrs(c0, c1), 2, divide ? c->Delta : 1, qm.dev, st);
   c->launches++;
   GQ_CHECK_LAUNCH(c);
   return 0;
@@ -873,4 +890,74 @@ extern "C" int gq_he_rot(gq_ctx *c, unsigned l, unsigned rot, uint64_t *c0, uint
 }
 extern "C" int gq_he_conj(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const gq_evk *ck) {
   return inplace_host(c, l, c0, c1, 3, 0, ck);
+}
+
+// -------------------------------------------------- stage-level entry points (device pointers)
+// One call = one pipeline stage on a limb range (NTT domain) or on a coefficient slice (big-integer
+// domain).  They exist for the limb-sharded multi-GPU pipeline (gpqhe_b200/sharded.py): every GPU
+// runs the limb-local stages on the limbs it owns and the coefficient-local stages on its
+// coefficient slice, with an all-to-all between the two domains.
+extern "C" int gq_stage_decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys,
+                                      const uint64_t *const *in, unsigned W, unsigned ncoef,
+                                      uint64_t *out, void *stream) {
+  if (!c || !in || !out || npolys == 0 || npolys > 4 || nlimbs == 0) GQ_FAIL("bad argument");
+  if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
+  GqPtrs4 p = ptrs(in[0], npolys > 1 ? in[1] : nullptr, npolys > 2 ? in[2] : nullptr, npolys > 3 ? in[3] : nullptr);
+  return decompose_dev(c, limb0, nlimbs, p, W, npolys, out, pick(c, stream), ncoef);
+}
+
+extern "C" int gq_stage_ntt_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys,
+                                uint64_t *data, int inverse, void *stream) {
+  if (!c || !data || npolys == 0) GQ_FAIL("bad argument");
+  // inverse: bit 0 = inverse transform; +2 / +4 = profiling only (just the tile / just the strided
+  // kernel of a two-kernel transform)
+  return ntt_internal(c, limb0, nlimbs, npolys, data, (inverse & 1) != 0, pick(c, stream), (inverse >> 1) & 3);
+}
+
+extern "C" int gq_stage_tensor_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, uint64_t *y,
+                                   const uint64_t *x, void *stream) {
+  if (!c || !y || !x) GQ_FAIL("bad argument");
+  if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
+  gq_launch_tensor(c->d_primes + limb0, (int)c->n, (int)nlimbs, y, x, pick(c, stream));
+  c->launches++;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+
+extern "C" int gq_stage_mul_evk_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, uint64_t *y,
+                                    const uint64_t *x, const gq_evk *evk, void *stream) {
+  if (!c || !y || !x || !evk) GQ_FAIL("bad argument");
+  if (limb0 + nlimbs > c->dimevk || !ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid");
+  const size_t off = (size_t)limb0 * c->n;
+  gq_launch_mul_evk(c->d_primes + limb0, (int)c->n, (int)nlimbs, y, x, evk->p0 + off, evk->p1 + off,
+                    pick(c, stream));
+  c->launches++;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+
+extern "C" int gq_stage_reconstruct_dev(gq_ctx *c, unsigned D, unsigned l, unsigned npolys,
+                                        const uint64_t *rhat, uint64_t *const *out, unsigned ncoef,
+                                        void *stream) {
+  if (he_check(c, l)) return 1;
+  if (!rhat || !out || npolys == 0 || npolys > 4) GQ_FAIL("bad argument");
+  if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
+  GqPtrs4 p = ptrs(out[0], npolys > 1 ? out[1] : nullptr, npolys > 2 ? out[2] : nullptr, npolys > 3 ? out[3] : nullptr);
+  return reconstruct_dev(c, D, rhat, c->qmod[l].dev, p, c->W, npolys, pick(c, stream), ncoef);
+}
+
+extern "C" int gq_stage_ks_epilogue_dev(gq_ctx *c, unsigned l, const uint64_t *chat,
+                                        const uint64_t *add0, const uint64_t *add1, uint64_t *c0,
+                                        uint64_t *c1, unsigned ncoef, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (!chat || !c0 || !c1) GQ_FAIL("null argument");
+  if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
+  return ks_epilogue_dev(c, l, dim_ks(c, l), chat, add0, add1, c0, c1, ncoef, pick(c, stream));
+}
+
+extern "C" int gq_stage_rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, int divide,
+                                    unsigned ncoef, void *stream) {
+  if (!c) GQ_FAIL("null context");
+  if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
+  return rescale_dev(c, l, c0, c1, divide != 0, stream, ncoef);
 }

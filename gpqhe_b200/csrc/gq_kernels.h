@@ -11,7 +11,7 @@ int gq_launch_ntt(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, 
 // K1/K2 lazy variants for the internal pipelines (gq_ntt_lazy.cu): canonical in, canonical out;
 // valid only for primes p = 2^b + c, b <= 59, 16c < 2^b (checked by the caller)
 int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
-                       bool inverse, cudaStream_t st);
+                       bool inverse, cudaStream_t st, int only = 0);
 
 // K3 (gq_pointwise.cu)
 void gq_launch_binary(const GqPrime *primes, int n, int limb0, int nlimbs, int npolys, bool mul,

@@ -291,9 +291,12 @@ k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
 
 // Same contract as gq_launch_ntt, canonical in / canonical out only.
 int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
-                       bool inverse, cudaStream_t st) {
+                       bool inverse, cudaStream_t st, int only) {
+  // only: 0 = whole transform; 1 = tile kernel only, 2 = strided kernel only (profiling: the
+  // output is then not a transform)
   const int logn = tb.logn;
   if (logn < 3 || logn > 17) return -1;
+  if (only && logn <= 12) return -1;
   const int lt = logn > 12 ? 12 : logn, sa = logn - lt;
   const dim3 gt(tb.n >> lt, nlimbs * npolys), gs(((tb.n >> (sa ? sa : 1)) + 255) / 256, nlimbs * npolys);
   int launches = 0;
@@ -307,9 +310,9 @@ int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nli
   }
   if (!inverse) {
     if (sa) {
-      GQ_STRIDED(k_nttl_fwd_strided)
-      GQ_LAUNCH((k_nttl_fwd_tile<12, true>), gt, dim3(TileCfg<12>::NT), st, tb, data, limb0, nlimbs);
-      return 2;
+      if (only != 1) { GQ_STRIDED(k_nttl_fwd_strided) }
+      if (only != 2) GQ_LAUNCH((k_nttl_fwd_tile<12, true>), gt, dim3(TileCfg<12>::NT), st, tb, data, limb0, nlimbs);
+      return only ? 1 : 2;
     }
     switch (lt) {
 #define GQ_CASE(L) case L: GQ_LAUNCH((k_nttl_fwd_tile<L, false>), gt, dim3(TileCfg<L>::NT), st, tb, data, limb0, nlimbs); break;
@@ -319,9 +322,9 @@ int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nli
     launches = 1;
   } else {
     if (sa) {
-      GQ_LAUNCH((k_nttl_inv_tile<12, false>), gt, dim3(TileCfg<12>::NT), st, tb, data, limb0, nlimbs);
-      GQ_STRIDED(k_nttl_inv_strided)
-      return 2;
+      if (only != 2) GQ_LAUNCH((k_nttl_inv_tile<12, false>), gt, dim3(TileCfg<12>::NT), st, tb, data, limb0, nlimbs);
+      if (only != 1) { GQ_STRIDED(k_nttl_inv_strided) }
+      return only ? 1 : 2;
     }
     switch (lt) {
 #define GQ_CASE(L) case L: GQ_LAUNCH((k_nttl_inv_tile<L, true>), gt, dim3(TileCfg<L>::NT), st, tb, data, limb0, nlimbs); break;

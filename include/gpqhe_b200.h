@@ -154,6 +154,35 @@ int gq_he_rot_dev(gq_ctx *ctx, unsigned l, unsigned rot, uint64_t *c0, uint64_t 
 int gq_he_conj_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const gq_evk *ck,
                    void *stream);
 
+/* ---- stage-level entry points (DEVICE pointers, enqueue only) ------------------------
+ * One call = one stage of the pipelines above on a limb range [limb0, limb0+nlimbs) (NTT domain,
+ * limb-polys of the full ring degree n) or on a slice of `ncoef` coefficients (big-integer domain:
+ * big polys are uint64_t[W][ncoef], residues uint64_t[npolys][nlimbs][ncoef]).  The limb-sharded
+ * multi-GPU pipeline is built from them with an all-to-all between the two domains.
+ *   decompose    rns_decompose (src/rns.c:37-48) of npolys (<= 4) big polys: out[npolys][nlimbs][ncoef]
+ *   ntt          the internal transforms (canonical in / out), data[npolys][nlimbs][n]
+ *   tensor       he-mult.c:125-136: x[4][nlimbs][n] -> y[3][nlimbs][n]
+ *   mul_evk      he-mult.c:61-64:   x[nlimbs][n] -> y[2][nlimbs][n] with the key's limbs limb0..
+ *   reconstruct  poly_rns2mpi(q_l) (src/poly.c:109-120) over the first D primes: rhat[npolys][D][ncoef]
+ *   ks_epilogue  he-mult.c:67-77 / he-automorphism.c:68-76: chat[2][D2(l)][ncoef], add may be NULL
+ *   rescale      he_rs (divide != 0) / he_moddown on a slice; l = level before the call */
+int gq_stage_decompose_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsigned npolys,
+                           const uint64_t *const *in_dev, unsigned W, unsigned ncoef, uint64_t *out_dev,
+                           void *stream);
+int gq_stage_ntt_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsigned npolys, uint64_t *data_dev,
+                     int inverse, void *stream);
+int gq_stage_tensor_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, uint64_t *y_dev,
+                        const uint64_t *x_dev, void *stream);
+int gq_stage_mul_evk_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, uint64_t *y_dev,
+                         const uint64_t *x_dev, const gq_evk *evk, void *stream);
+int gq_stage_reconstruct_dev(gq_ctx *ctx, unsigned D, unsigned l, unsigned npolys, const uint64_t *rhat_dev,
+                             uint64_t *const *out_dev, unsigned ncoef, void *stream);
+int gq_stage_ks_epilogue_dev(gq_ctx *ctx, unsigned l, const uint64_t *chat_dev, const uint64_t *add0_dev,
+                             const uint64_t *add1_dev, uint64_t *c0_dev, uint64_t *c1_dev, unsigned ncoef,
+                             void *stream);
+int gq_stage_rescale_dev(gq_ctx *ctx, unsigned l, uint64_t *c0_dev, uint64_t *c1_dev, int divide,
+                         unsigned ncoef, void *stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -1,0 +1,103 @@
+"""Limb-sharded multi-rank pipeline (gpqhe_b200/sharded.py).
+
+CPU tier: world_size 2 and 4 over gloo, every rank driving the emulated build of the device
+library; the sharded he_mul + he_rs must equal the single-rank C-ABI result and the oracle bit
+for bit.  GPU tier: the same check on one GPU with world_size 1 (the exchange degenerates to
+the identity but every gq_stage_* kernel path runs on the real library)."""
+import os
+import random
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _case(lib_path, logn, q, Delta, logqub, device):
+    """runs on every rank: returns (sharded result gathered, single-rank result, oracle result)"""
+    import gpqhe_b200 as g
+    from gpqhe_b200.sharded import ShardedHe
+    from oracle import pyoracle as o
+    ctx = g.HeContext(logn, q, 4, Delta, lib_path=lib_path, logqub=logqub)
+    oc = o.Ctx(logn, q, 4, Delta, logqub=logqub or None)
+    rng = random.Random(99)                       # same inputs on every rank
+    n, W, l = ctx.n, ctx.W, ctx.L
+    ql = oc.ql[l]
+    polys = [[rng.randrange(ql) - ql // 2 for _ in range(n)] for _ in range(4)]
+    nr = np.random.default_rng(5)
+    p0 = np.concatenate([nr.integers(0, oc.primes[d], size=n, dtype=np.uint64) for d in range(oc.dimevk)])
+    p1 = np.concatenate([nr.integers(0, oc.primes[d], size=n, dtype=np.uint64) for d in range(oc.dimevk)])
+    evk = ctx.genevk(p0, p1)
+    big = [g.ints_to_big(p, W) for p in polys]
+    sh = ShardedHe(ctx, device=device)
+    sl = [sh.shard(torch.from_numpy(b.view(np.int64)).to(device)) for b in big]
+    c0, c1 = sh.he_mul(l, sl[0], sl[1], sl[2], sl[3], evk)
+    c0, c1 = sh.he_rs(l, c0, c1)
+    ctx.sync()
+    got = [g.big_to_ints(sh.gather(c).cpu().numpy().view(np.uint64)) for c in (c0, c1)]
+    one = ctx.he_rs(ctx.he_mul(g.HeCt(l, big[0], big[1]), g.HeCt(l, big[2], big[3]), evk))
+    single = [g.big_to_ints(one.c0), g.big_to_ints(one.c1)]
+    e = o.he_rs(oc, o.he_mul(oc, {"l": l, "c0": polys[0], "c1": polys[1]}, {"l": l, "c0": polys[2], "c1": polys[3]}, (p0, p1)))
+    stats = (sh.exchanges, sh.exchanged_bytes)
+    ctx.close()
+    return got, single, [e["c0"], e["c1"]], stats
+
+
+def _worker(rank, world, port, lib_path, params, q_out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        got, single, want, stats = _case(lib_path, *params, device="cpu")
+        ok = got == want and single == want
+        q_out.put((rank, ok, stats))
+    except Exception as ex:  # pragma: no cover - reported to the parent
+        q_out.put((rank, False, repr(ex)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,logn,logq,logDelta", [(2, 6, 438, 50), (4, 7, 438, 50), (2, 8, 120, 40)])
+def test_sharded_he_mul_rs_gloo(emul_lib, world, logn, logq, logDelta):
+    params = (logn, 1 << logq, 1 << logDelta, logq)
+    ctxm = mp.get_context("spawn")
+    q_out = ctxm.Queue()
+    port = _free_port()
+    procs = [ctxm.Process(target=_worker, args=(r, world, port, emul_lib, params, q_out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q_out.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok, _ in res), res
+    # four all-to-alls per he_mul, none for he_rs
+    assert all(st[0] == 4 for _, _, st in res), res
+
+
+@pytest.mark.gpu
+def test_sharded_stage_entry_points_gpu(real_lib):
+    """world_size 1 on the real library: the gq_stage_* kernels on limb ranges / coefficient
+    slices give the same bits as the fused single-call path and the oracle at N=2^12."""
+    dev = torch.device("cuda", 0)
+    import gpqhe_b200 as g
+    ctx = g.HeContext(12, 1 << 109, 4, 1 << 30, lib_path=real_lib)
+    ext = torch.cuda.ExternalStream(ctx._lib.gq_ctx_stream(ctx._h), device=dev)
+    ctx.close()
+    with torch.cuda.stream(ext):
+        got, single, want, _ = _case(real_lib, 12, 1 << 109, 1 << 30, 0, dev)
+    assert got == want and single == want
