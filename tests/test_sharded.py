@@ -45,11 +45,16 @@ def _case(lib_path, logn, q, Delta, logqub, device):
     evk = ctx.genevk(p0, p1)
     big = [g.ints_to_big(p, W) for p in polys]
     sh = ShardedHe(ctx, device=device)
-    sl = [sh.shard(torch.from_numpy(b.view(np.int64)).to(device)) for b in big]
-    c0, c1 = sh.he_mul(l, sl[0], sl[1], sl[2], sl[3], evk)
-    c0, c1 = sh.he_rs(l, c0, c1)
-    ctx.sync()
-    got = [g.big_to_ints(sh.gather(c).cpu().numpy().view(np.uint64)) for c in (c0, c1)]
+    import contextlib
+    on_ctx_stream = contextlib.nullcontext()
+    if torch.device(device).type == "cuda":   # torch work must be ordered with the context's stream
+        on_ctx_stream = torch.cuda.stream(torch.cuda.ExternalStream(ctx._lib.gq_ctx_stream(ctx._h), device=device))
+    with on_ctx_stream:
+        sl = [sh.shard(torch.from_numpy(b.view(np.int64)).to(device)) for b in big]
+        c0, c1 = sh.he_mul(l, sl[0], sl[1], sl[2], sl[3], evk)
+        c0, c1 = sh.he_rs(l, c0, c1)
+        ctx.sync()
+        got = [g.big_to_ints(sh.gather(c).cpu().numpy().view(np.uint64)) for c in (c0, c1)]
     one = ctx.he_rs(ctx.he_mul(g.HeCt(l, big[0], big[1]), g.HeCt(l, big[2], big[3]), evk))
     single = [g.big_to_ints(one.c0), g.big_to_ints(one.c1)]
     e = o.he_rs(oc, o.he_mul(oc, {"l": l, "c0": polys[0], "c1": polys[1]}, {"l": l, "c0": polys[2], "c1": polys[3]}, (p0, p1)))
@@ -94,10 +99,5 @@ def test_sharded_stage_entry_points_gpu(real_lib):
     """world_size 1 on the real library: the gq_stage_* kernels on limb ranges / coefficient
     slices give the same bits as the fused single-call path and the oracle at N=2^12."""
     dev = torch.device("cuda", 0)
-    import gpqhe_b200 as g
-    ctx = g.HeContext(12, 1 << 109, 4, 1 << 30, lib_path=real_lib)
-    ext = torch.cuda.ExternalStream(ctx._lib.gq_ctx_stream(ctx._h), device=dev)
-    ctx.close()
-    with torch.cuda.stream(ext):
-        got, single, want, _ = _case(real_lib, 12, 1 << 109, 1 << 30, 0, dev)
+    got, single, want, _ = _case(real_lib, 12, 1 << 109, 1 << 30, 0, dev)
     assert got == want and single == want
