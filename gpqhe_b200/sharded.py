@@ -170,3 +170,148 @@ class ShardedHe:
     def he_moddown(self, l: int, c0, c1):
         self._ck(self._lib.gq_stage_rescale_dev(self._h, l, c0.data_ptr(), c1.data_ptr(), 0, self.n_loc, None))
         return c0, c1
+
+
+class MulPlan:
+    """he_mul (+ he_rs) at one level with every buffer allocated once and the work between two
+    exchanges recorded as ONE CUDA graph (five graphs, four eager all-to-alls per op).
+
+    The eager path of ShardedHe issues ~15 small launches per exchange from Python and is
+    launch-bound at N=2^16; replaying five graphs makes the op GPU- and link-bound instead.  The
+    collectives stay outside the graphs on purpose (capturing NCCL work needs cross-rank care and
+    buys nothing here: they are four launches)."""
+
+    def __init__(self, sh: ShardedHe, l: int, rlk: HeEvk, rescale: bool = True, graphs: bool | None = None):
+        self.sh, self.l, self.rlk, self.rescale = sh, l, rlk, rescale
+        G, n, nl, W = sh.G, sh.n, sh.n_loc, sh.W
+        self.D1, self.D2 = sh.ctx.dims(l)
+        self.off1, self.off2 = sh._offsets(self.D1), sh._offsets(self.D2)
+        r = sh.rank
+        self.lo1, self.D1l = self.off1[r], self.off1[r + 1] - self.off1[r]
+        self.lo2, self.D2l = self.off2[r], self.off2[r + 1] - self.off2[r]
+        E = sh._empty
+        self.inp = E(4, W, nl)                         # a0, a1, b0, b1 slices (copy inputs here)
+        self.xc, self.xl = E(4, self.D1, nl), E(4, self.D1l, n)
+        self.yl, self.rh = E(3, self.D1l, n), E(3, self.D1, nl)
+        self.d = E(3, W, nl)
+        self.x2c, self.x2l = E(1, self.D2, nl), E(1, self.D2l, n)
+        self.y2l, self.ch = E(2, self.D2l, n), E(2, self.D2, nl)
+        self.out = E(2, W, nl)                         # c0, c1 slices
+        # flat exchange buffers: (send, recv, in_splits, out_splits) per exchange
+        self.ex = [self._xbuf(4, self.off1, True), self._xbuf(3, self.off1, False),
+                   self._xbuf(1, self.off2, True), self._xbuf(2, self.off2, False)]
+        self.segs = [self._seg0, self._seg1, self._seg2, self._seg3, self._seg4]
+        self.graphs = None
+        want = (sh.device.type == "cuda") if graphs is None else graphs
+        if want:
+            self._capture()
+
+    # -- exchange buffers ------------------------------------------------------------
+    def _xbuf(self, P, off, coef_to_limb):
+        sh = self.sh
+        G, nl, r = sh.G, sh.n_loc, sh.rank
+        Dl = off[r + 1] - off[r]
+        ragged = [P * (off[s + 1] - off[s]) * nl for s in range(G)]
+        even = [P * Dl * nl] * G
+        ins, outs = (ragged, even) if coef_to_limb else (even, ragged)
+        send = torch.empty(sum(ins), dtype=torch.int64, device=sh.device)
+        recv = torch.empty(sum(outs), dtype=torch.int64, device=sh.device)
+        return send, recv, ins, outs
+
+    def _pack_c2l(self, k, x, off):           # x[P, D, n_loc] -> send blocks by destination limb range
+        send, _, ins, _ = self.ex[k]
+        P, pos = x.shape[0], 0
+        for s in range(self.sh.G):
+            send[pos:pos + ins[s]].view(P, off[s + 1] - off[s], self.sh.n_loc).copy_(x[:, off[s]:off[s + 1], :])
+            pos += ins[s]
+
+    def _unpack_c2l(self, k, xl):             # recv[G][P][Dl][n_loc] -> xl[P, Dl, n]
+        _, recv, _, _ = self.ex[k]
+        P, Dl = xl.shape[0], xl.shape[1]
+        xl.view(P, Dl, self.sh.G, self.sh.n_loc).copy_(recv.view(self.sh.G, P, Dl, self.sh.n_loc).permute(1, 2, 0, 3))
+
+    def _pack_l2c(self, k, yl):               # yl[P, Dl, n] -> send[G][P][Dl][n_loc]
+        send, _, _, _ = self.ex[k]
+        P, Dl = yl.shape[0], yl.shape[1]
+        send.view(self.sh.G, P, Dl, self.sh.n_loc).copy_(yl.view(P, Dl, self.sh.G, self.sh.n_loc).permute(2, 0, 1, 3))
+
+    def _unpack_l2c(self, k, out, off):       # recv blocks by source limb range -> out[P, D, n_loc]
+        _, recv, _, outs = self.ex[k]
+        P, pos = out.shape[0], 0
+        for s in range(self.sh.G):
+            out[:, off[s]:off[s + 1], :].copy_(recv[pos:pos + outs[s]].view(P, off[s + 1] - off[s], self.sh.n_loc))
+            pos += outs[s]
+
+    def _exchange(self, k):
+        sh = self.sh
+        send, recv, ins, outs = self.ex[k]
+        if sh.G == 1:
+            recv.copy_(send)
+            return
+        dist.all_to_all_single(recv, send, output_split_sizes=outs, input_split_sizes=ins, group=sh.group)
+        sh.exchanges += 1
+        sh.exchanged_bytes += (send.numel() - ins[sh.rank]) * 8
+
+    # -- the five compute segments ----------------------------------------------------
+    def _seg0(self):
+        sh = self.sh
+        arr = (C.c_void_p * 4)(*[self.inp[k].data_ptr() for k in range(4)])
+        sh._ck(sh._lib.gq_stage_decompose_dev(sh._h, 0, self.D1, 4, arr, sh.W, sh.n_loc, self.xc.data_ptr(), None))
+        self._pack_c2l(0, self.xc, self.off1)
+
+    def _seg1(self):
+        sh, lib, h = self.sh, self.sh._lib, self.sh._h
+        self._unpack_c2l(0, self.xl)
+        sh._ck(lib.gq_stage_ntt_dev(h, self.lo1, self.D1l, 4, self.xl.data_ptr(), 0, None))
+        sh._ck(lib.gq_stage_tensor_dev(h, self.lo1, self.D1l, self.yl.data_ptr(), self.xl.data_ptr(), None))
+        sh._ck(lib.gq_stage_ntt_dev(h, self.lo1, self.D1l, 3, self.yl.data_ptr(), 1, None))
+        self._pack_l2c(1, self.yl)
+
+    def _seg2(self):
+        sh, lib, h = self.sh, self.sh._lib, self.sh._h
+        self._unpack_l2c(1, self.rh, self.off1)
+        outs = (C.c_void_p * 3)(*[self.d[k].data_ptr() for k in range(3)])
+        sh._ck(lib.gq_stage_reconstruct_dev(h, self.D1, self.l, 3, self.rh.data_ptr(), outs, sh.n_loc, None))
+        arr = (C.c_void_p * 1)(self.d[2].data_ptr())
+        sh._ck(lib.gq_stage_decompose_dev(h, 0, self.D2, 1, arr, sh.W, sh.n_loc, self.x2c.data_ptr(), None))
+        self._pack_c2l(2, self.x2c, self.off2)
+
+    def _seg3(self):
+        sh, lib, h = self.sh, self.sh._lib, self.sh._h
+        self._unpack_c2l(2, self.x2l)
+        sh._ck(lib.gq_stage_ntt_dev(h, self.lo2, self.D2l, 1, self.x2l.data_ptr(), 0, None))
+        sh._ck(lib.gq_stage_mul_evk_dev(h, self.lo2, self.D2l, self.y2l.data_ptr(), self.x2l.data_ptr(), self.rlk._h, None))
+        sh._ck(lib.gq_stage_ntt_dev(h, self.lo2, self.D2l, 2, self.y2l.data_ptr(), 1, None))
+        self._pack_l2c(3, self.y2l)
+
+    def _seg4(self):
+        sh, lib, h = self.sh, self.sh._lib, self.sh._h
+        self._unpack_l2c(3, self.ch, self.off2)
+        sh._ck(lib.gq_stage_ks_epilogue_dev(h, self.l, self.ch.data_ptr(), self.d[0].data_ptr(), self.d[1].data_ptr(),
+                                            self.out[0].data_ptr(), self.out[1].data_ptr(), sh.n_loc, None))
+        if self.rescale:
+            sh._ck(lib.gq_stage_rescale_dev(h, self.l, self.out[0].data_ptr(), self.out[1].data_ptr(), 1, sh.n_loc, None))
+
+    def _capture(self):
+        """record each segment once; must be called with the context's stream current"""
+        self.run()                                   # warm-up: allocations, lazy inits
+        torch.cuda.current_stream().synchronize()
+        stream = torch.cuda.current_stream()
+        graphs = []
+        for seg in self.segs:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=stream, capture_error_mode="thread_local"):
+                seg()
+            graphs.append(g)
+        self.graphs = graphs
+
+    def run(self):
+        """one he_mul (+ he_rs) on self.inp -> self.out"""
+        for k in range(5):
+            if self.graphs is not None:
+                self.graphs[k].replay()
+            else:
+                self.segs[k]()
+            if k < 4:
+                self._exchange(k)
+        return self.out[0], self.out[1]

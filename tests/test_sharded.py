@@ -55,6 +55,16 @@ def _case(lib_path, logn, q, Delta, logqub, device):
         c0, c1 = sh.he_rs(l, c0, c1)
         ctx.sync()
         got = [g.big_to_ints(sh.gather(c).cpu().numpy().view(np.uint64)) for c in (c0, c1)]
+        # the planned variant (static buffers, CUDA graphs between the exchanges on a GPU)
+        from gpqhe_b200.sharded import MulPlan
+        plan = MulPlan(sh, l, evk, rescale=True)
+        for k in range(4):
+            plan.inp[k].copy_(sl[k])
+        for _ in range(2):                       # twice: replays must not depend on stale state
+            p0_, p1_ = plan.run()
+        ctx.sync()
+        got_plan = [g.big_to_ints(sh.gather(c).cpu().numpy().view(np.uint64)) for c in (p0_, p1_)]
+        assert got_plan == got, "MulPlan differs from the eager sharded path"
     one = ctx.he_rs(ctx.he_mul(g.HeCt(l, big[0], big[1]), g.HeCt(l, big[2], big[3]), evk))
     single = [g.big_to_ints(one.c0), g.big_to_ints(one.c1)]
     e = o.he_rs(oc, o.he_mul(oc, {"l": l, "c0": polys[0], "c1": polys[1]}, {"l": l, "c0": polys[2], "c1": polys[3]}, (p0, p1)))
@@ -91,7 +101,7 @@ def test_sharded_he_mul_rs_gloo(emul_lib, world, logn, logq, logDelta):
         p.join(timeout=60)
     assert all(ok for _, ok, _ in res), res
     # four all-to-alls per he_mul, none for he_rs
-    assert all(st[0] == 4 for _, _, st in res), res
+    assert all(st[0] == 12 for _, _, st in res), res    # eager op + two planned ops
 
 
 @pytest.mark.gpu
