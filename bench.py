@@ -282,6 +282,22 @@ def run_ours(args):
            "kernels": "lazy (internal pipelines); exact_* = the ntt()-semantics kernels"}
     del dn
 
+    # ---- configs[3]: rotation sweep, he_rot = Galois permutation + key switch, rot = 0..NROT-1 with
+    # one switching key per rotation (the he_gemv workload: slots=16 rotations)
+    NROT = 16
+    rks = [ctx.genevk(synth_evk(rng, ctx.primes, n, ctx.dimevk), synth_evk(rng, ctx.primes, n, ctx.dimevk))
+           for _ in range(NROT)]
+    drot = dpool[:, :2].clone()                       # [POOL][2][W][n] ciphertexts rotated in place
+
+    def rot_step(i):
+        b = drot.data_ptr() + (i % POOL) * 2 * poly
+        ck(lib.gq_he_rot_dev(h, L, i % NROT, b, b + poly, rks[i % NROT]._h, None))
+    nrot = max(args.steps, NROT)
+    ms_rot = timed(rot_step, nrot, args.warmup)
+    rot_sweep = {"he_rot_per_s": world * nrot / (ms_rot * 1e-3), "ms_per_rot": ms_rot / nrot, "rotations": NROT,
+                 "keyswitch_limbs": D2, "note": "he_rot at l=L, 16 distinct rotation keys (384 MiB) cycled"}
+    del rks, drot
+
     # ---- limb-sharded single-stream pipeline: all ranks cooperate on ONE he_mul+he_rs;
     # ciphertexts stay coefficient-sharded, four all-to-alls per op (gpqhe_b200/sharded.py)
     sharded = None
@@ -363,7 +379,7 @@ def run_ours(args):
                            "l2": f"inputs rotate over a pool of {POOL} ciphertext pairs ({POOL * 4 * poly / 2**20:.0f} MiB) and the "
                                  f"per-op scratch + key is {ws_mib:.0f} MiB: working set > 126 MB L2"},
                 "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "ntt": ntt,
-                "sharded": sharded, "cpu_baseline": cpu}
+                "rot_sweep": rot_sweep, "sharded": sharded, "cpu_baseline": cpu}
         sys.stdout.flush()
         os.write(real_stdout, (json.dumps(line) + "\n").encode())
     ctx.close()
