@@ -441,6 +441,18 @@ extern "C" int gq_ntt_batch_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsi
   return 0;
 }
 
+// every prime of the range is 2^s + c, c < 2^28, 33 <= s <= 59: the pseudo-Mersenne pointwise kernels apply
+static bool pm_ok(const gq_ctx *c, unsigned limb0, unsigned nlimbs) {
+  if (!c->lazy_ntt) return false;
+  for (unsigned d = limb0; d < limb0 + nlimbs; d++) {
+    const GqPrime &P = c->primes[d];
+    if (P.bits < 34 || P.bits > 60) return false;
+    const unsigned sh = P.bits - 1, cb = (sh - 31 < 28) ? sh - 31 : 28;   // c*uh (uh < 2^31) must stay below 2^s
+    if (P.p - (1ull << sh) >= (1ull << cb)) return false;
+  }
+  return true;
+}
+
 // NTT of the internal pipelines: canonical in / canonical out is all they need, so the lazy
 // kernels are used whenever every prime of the range has the shape they assume.
 static int ntt_internal(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys, uint64_t *data,
@@ -616,7 +628,7 @@ extern "C" int gq_poly_mul(gq_ctx *c, uint64_t *r, unsigned Wr, const uint64_t *
   GQ_CUDA(cudaMemcpyAsync(db, b, ib, cudaMemcpyHostToDevice, st));
   if (decompose_dev(c, 0, dim, ptrs(da, db), W, 2, A, st)) return 1;
   if (ntt_internal(c, 0, dim, 2, A, false, st)) return 1;
-  gq_launch_binary(c->d_primes, (int)n, 0, (int)dim, 1, true, B, A, A + (size_t)dim * n, st);
+  gq_launch_binary(c->d_primes, (int)n, 0, (int)dim, 1, true, B, A, A + (size_t)dim * n, st);   // poly_mul: Barrett as is
   c->launches++;
   if (ntt_internal(c, 0, dim, 1, B, true, st)) return 1;
   if (reconstruct_dev(c, dim, B, m, ptrs(dr), Wr, 1, st)) return 1;
@@ -720,7 +732,7 @@ static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk 
   uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
   if (decompose_dev(c, 0, D2, ptrs(d), W, 1, A, st)) return 1;
   if (ntt_internal(c, 0, D2, 1, A, false, st)) return 1;
-  gq_launch_mul_evk(c->d_primes, (int)n, (int)D2, B, A, evk->p0, evk->p1, st);
+  gq_launch_mul_evk(c->d_primes, (int)n, (int)D2, B, A, evk->p0, evk->p1, st, pm_ok(c, 0, D2));
   c->launches++;
   if (ntt_internal(c, 0, D2, 2, B, true, st)) return 1;
   return ks_epilogue_dev(c, l, D2, B, add0, add1, c0, c1, 0, st);
@@ -751,7 +763,7 @@ extern "C" int gq_he_mul_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, 
   // hot loop A (he-mult.c:116-138): decompose, forward NTT, tensor, inverse NTT
   if (decompose_dev(c, 0, D1, ptrs(a0, a1, b0, b1), W, 4, A, st)) return 1;
   if (ntt_internal(c, 0, D1, 4, A, false, st)) return 1;
-  gq_launch_tensor(c->d_primes, (int)n, (int)D1, B, A, st);
+  gq_launch_tensor(c->d_primes, (int)n, (int)D1, B, A, st, pm_ok(c, 0, D1));
   c->launches++;
   if (ntt_internal(c, 0, D1, 3, B, true, st)) return 1;
   // hot loop B (he-mult.c:139-141): d0, d1, d2 mod q_l
@@ -773,7 +785,7 @@ extern "C" int gq_he_mulpt_dev(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0
   uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
   if (decompose_dev(c, 0, dim, ptrs(a0, a1, m), W, 3, A, st)) return 1;
   if (ntt_internal(c, 0, dim, 3, A, false, st)) return 1;
-  gq_launch_mul_pt(c->d_primes, (int)n, (int)dim, B, A, st);
+  gq_launch_mul_pt(c->d_primes, (int)n, (int)dim, B, A, st, pm_ok(c, 0, dim));
   c->launches++;
   if (ntt_internal(c, 0, dim, 2, B, true, st)) return 1;
   return reconstruct_dev(c, dim, B, c->qmod[l].dev, ptrs(c0, c1), W, 2, st);
@@ -918,7 +930,7 @@ extern "C" int gq_stage_tensor_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, u
                                    const uint64_t *x, void *stream) {
   if (!c || !y || !x) GQ_FAIL("bad argument");
   if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
-  gq_launch_tensor(c->d_primes + limb0, (int)c->n, (int)nlimbs, y, x, pick(c, stream));
+  gq_launch_tensor(c->d_primes + limb0, (int)c->n, (int)nlimbs, y, x, pick(c, stream), pm_ok(c, limb0, nlimbs));
   c->launches++;
   GQ_CHECK_LAUNCH(c);
   return 0;
@@ -930,7 +942,7 @@ extern "C" int gq_stage_mul_evk_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, 
   if (limb0 + nlimbs > c->dimevk || !ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid");
   const size_t off = (size_t)limb0 * c->n;
   gq_launch_mul_evk(c->d_primes + limb0, (int)c->n, (int)nlimbs, y, x, evk->p0 + off, evk->p1 + off,
-                    pick(c, stream));
+                    pick(c, stream), pm_ok(c, limb0, nlimbs));
   c->launches++;
   GQ_CHECK_LAUNCH(c);
   return 0;

@@ -88,3 +88,43 @@ GQ_HD void gq_bfly_inv(uint64_t &x, uint64_t &y, uint64_t w, uint64_t wsh, uint6
   x = s;
   y = gq_mul_shoup(d, w, wsh, p);
 }
+
+// ---- products of two variables for primes p = 2^s + c with c < 2^28 (every GPQHE prime is
+// 2^59 + 1 + k*2N).  2^s == -c (mod p), so a 2s+3-bit value z = zh*2^s + zl folds as
+//   z == zl - c*zh,   c*zh = uh*2^s + ul   ==>   z == zl - ul + c*uh   in (-2^s, 2^(s+1))
+// with three 32x32 products instead of Barrett's ~14; the result is then made canonical.
+// Same canonical residue as barrett_reduce (src/reduce.c:88-106); used by the internal pointwise
+// kernels only (the public poly_rns_mul keeps the reference's Barrett domain).
+struct GqWide { uint64_t lo, hi; };
+
+GQ_HD GqWide gq_mul_wide(uint64_t a, uint64_t b) {
+  const uint32_t a0 = (uint32_t)a, a1 = (uint32_t)(a >> 32), b0 = (uint32_t)b, b1 = (uint32_t)(b >> 32);
+  const uint64_t p00 = (uint64_t)a0 * b0, p01 = (uint64_t)a0 * b1, p10 = (uint64_t)a1 * b0,
+                 p11 = (uint64_t)a1 * b1;
+  const uint64_t mid = (p00 >> 32) + (uint32_t)p01 + (uint32_t)p10;      // < 3 * 2^32
+  GqWide r;
+  r.lo = (mid << 32) | (uint32_t)p00;
+  r.hi = p11 + (p01 >> 32) + (p10 >> 32) + (mid >> 32);
+  return r;
+}
+GQ_HD GqWide gq_add_wide(GqWide x, GqWide y) {
+  GqWide r;
+  r.lo = x.lo + y.lo;
+  r.hi = x.hi + y.hi + (r.lo < x.lo ? 1u : 0u);
+  return r;
+}
+// z < 2^(2s+3), s = bits(p)-1 in [33,60], c = p - 2^s < 2^28  ->  z mod p, canonical
+GQ_HD uint64_t gq_reduce_pm(GqWide z, uint64_t p, uint32_t c, int s) {
+  const uint64_t mask = (((uint64_t)1) << s) - 1;
+  const uint64_t zl = z.lo & mask;
+  const uint64_t zh = (z.lo >> s) | (z.hi << (64 - s));                  // < 2^(s+3) <= 2^63
+  const uint64_t u0 = (uint64_t)c * (uint32_t)zh, u1 = (uint64_t)c * (uint32_t)(zh >> 32);
+  // u = u0 + u1*2^32 < 2^91
+  const uint64_t ulo = u0 + (u1 << 32);
+  const uint64_t uhi = (u1 >> 32) + (ulo < u0 ? 1u : 0u);
+  const uint64_t ul = ulo & mask;
+  const uint64_t uh = (ulo >> s) | (uhi << (64 - s));                    // < 2^31
+  uint64_t r = zl - ul + (uint64_t)c * (uint32_t)uh;                     // in (-2^s, 2^(s+1)) as signed
+  r = ((int64_t)r < 0) ? r + p : r;
+  return (r >= p) ? r - p : r;
+}

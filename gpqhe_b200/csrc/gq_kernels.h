@@ -16,12 +16,13 @@ int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nli
 // K3 (gq_pointwise.cu)
 void gq_launch_binary(const GqPrime *primes, int n, int limb0, int nlimbs, int npolys, bool mul,
                       uint64_t *r, const uint64_t *a, const uint64_t *b, cudaStream_t st);
+// pm: every prime of the range is 2^s + c with c < 2^28, 33 <= s <= 59 (gq_reduce_pm kernels)
 void gq_launch_tensor(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
-                      cudaStream_t st);
+                      cudaStream_t st, bool pm = false);
 void gq_launch_mul_evk(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
-                       const uint64_t *e0, const uint64_t *e1, cudaStream_t st);
+                       const uint64_t *e0, const uint64_t *e1, cudaStream_t st, bool pm = false);
 void gq_launch_mul_pt(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
-                      cudaStream_t st);
+                      cudaStream_t st, bool pm = false);
 
 // K4/K5/K6 (gq_crt.cu); return the number of kernels launched, <0 when no instantiation fits.
 // fix = device scratch {int count (16-byte slot), int list[4n]}: enables the fast low-word kernels

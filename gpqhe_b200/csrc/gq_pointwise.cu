@@ -108,6 +108,75 @@ k_mul_pt(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict_
   }
 }
 
+// ---- the same three internal kernels for primes 2^s + c, c < 2^28 (gq_reduce_pm) -------------
+struct PM { uint64_t p; uint32_t c; int s; };
+GQ_DEV PM load_pm(const GqPrime &P) {
+  PM m; m.p = P.p; m.s = (int)P.bits - 1; m.c = (uint32_t)(P.p - (((uint64_t)1) << m.s)); return m;
+}
+GQ_DEV uint64_t mulm_pm(uint64_t a, uint64_t b, const PM &m) { return gq_reduce_pm(gq_mul_wide(a, b), m.p, m.c, m.s); }
+GQ_DEV uint64_t mul2add_pm(uint64_t a, uint64_t b, uint64_t c2, uint64_t d, const PM &m) {
+  return gq_reduce_pm(gq_add_wide(gq_mul_wide(a, b), gq_mul_wide(c2, d)), m.p, m.c, m.s);
+}
+
+__global__ void __launch_bounds__(256)
+k_tensor_pm(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict__ y,
+            const uint64_t *__restrict__ x) {
+  const int half = n >> 1;
+  const long long per = (long long)D * half;
+  const size_t stride = (size_t)D * n;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < per;
+       i += (long long)gridDim.x * blockDim.x) {
+    const PM m = load_pm(primes[(int)(i / half)]);
+    const ulonglong2 a0 = ld2(x + 2 * i), a1 = ld2(x + stride + 2 * i);
+    const ulonglong2 b0 = ld2(x + 2 * stride + 2 * i), b1 = ld2(x + 3 * stride + 2 * i);
+    ulonglong2 d0, d1, d2;
+    d0.x = mulm_pm(a0.x, b0.x, m); d0.y = mulm_pm(a0.y, b0.y, m);
+    d2.x = mulm_pm(a1.x, b1.x, m); d2.y = mulm_pm(a1.y, b1.y, m);
+    d1.x = mul2add_pm(a0.x, b1.x, a1.x, b0.x, m);
+    d1.y = mul2add_pm(a0.y, b1.y, a1.y, b0.y, m);
+    st2(y + 2 * i, d0);
+    st2(y + stride + 2 * i, d1);
+    st2(y + 2 * stride + 2 * i, d2);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_mul_evk_pm(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict__ y,
+             const uint64_t *__restrict__ x, const uint64_t *__restrict__ e0,
+             const uint64_t *__restrict__ e1) {
+  const int half = n >> 1;
+  const long long per = (long long)D * half;
+  const size_t stride = (size_t)D * n;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < per;
+       i += (long long)gridDim.x * blockDim.x) {
+    const PM m = load_pm(primes[(int)(i / half)]);
+    const ulonglong2 a = ld2(x + 2 * i), k0 = ld2(e0 + 2 * i), k1 = ld2(e1 + 2 * i);
+    ulonglong2 r0, r1;
+    r0.x = mulm_pm(a.x, k0.x, m); r0.y = mulm_pm(a.y, k0.y, m);
+    r1.x = mulm_pm(a.x, k1.x, m); r1.y = mulm_pm(a.y, k1.y, m);
+    st2(y + 2 * i, r0);
+    st2(y + stride + 2 * i, r1);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_mul_pt_pm(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict__ y,
+            const uint64_t *__restrict__ x) {
+  const int half = n >> 1;
+  const long long per = (long long)D * half;
+  const size_t stride = (size_t)D * n;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < per;
+       i += (long long)gridDim.x * blockDim.x) {
+    const PM m = load_pm(primes[(int)(i / half)]);
+    const ulonglong2 c0 = ld2(x + 2 * i), c1 = ld2(x + stride + 2 * i), mm = ld2(x + 2 * stride + 2 * i);
+    ulonglong2 r0, r1;
+    r0.x = mulm_pm(c0.x, mm.x, m); r0.y = mulm_pm(c0.y, mm.y, m);
+    r1.x = mulm_pm(c1.x, mm.x, m); r1.y = mulm_pm(c1.y, mm.y, m);
+    st2(y + 2 * i, r0);
+    st2(y + stride + 2 * i, r1);
+  }
+}
+
 inline int grid_for(long long work_items, int block) {
   long long blocks = (work_items + block - 1) / block;
   long long cap = (long long)GQ_NUM_SMS * 8;
@@ -129,17 +198,20 @@ void gq_launch_binary(const GqPrime *primes, int n, int limb0, int nlimbs, int n
 }
 
 void gq_launch_tensor(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
-                      cudaStream_t st) {
+                      cudaStream_t st, bool pm) {
+  if (pm) { GQ_LAUNCH(k_tensor_pm, dim3(grid_for((long long)D * (n >> 1), 256)), dim3(256), st, primes, n, D, y, x); return; }
   GQ_LAUNCH(k_tensor, dim3(grid_for((long long)D * (n >> 1), 256)), dim3(256), st, primes, n, D, y, x);
 }
 
 void gq_launch_mul_evk(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
-                       const uint64_t *e0, const uint64_t *e1, cudaStream_t st) {
+                       const uint64_t *e0, const uint64_t *e1, cudaStream_t st, bool pm) {
+  if (pm) { GQ_LAUNCH(k_mul_evk_pm, dim3(grid_for((long long)D * (n >> 1), 256)), dim3(256), st, primes, n, D, y, x, e0, e1); return; }
   GQ_LAUNCH(k_mul_evk, dim3(grid_for((long long)D * (n >> 1), 256)), dim3(256), st, primes, n, D, y, x,
             e0, e1);
 }
 
 void gq_launch_mul_pt(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
-                      cudaStream_t st) {
+                      cudaStream_t st, bool pm) {
+  if (pm) { GQ_LAUNCH(k_mul_pt_pm, dim3(grid_for((long long)D * (n >> 1), 256)), dim3(256), st, primes, n, D, y, x); return; }
   GQ_LAUNCH(k_mul_pt, dim3(grid_for((long long)D * (n >> 1), 256)), dim3(256), st, primes, n, D, y, x);
 }
