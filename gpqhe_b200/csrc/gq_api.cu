@@ -143,15 +143,21 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
     uint64_t inv = powm(phat.mod_u64(pd), pd - 2, pd);   // precomp.c:289
     hinv[d] = inv;
     hinvsh[d] = (uint64_t)(((gq_u128)inv << 64) / pd);
-    const uint64_t one128[3] = {0, 0, 1};
-    BigU(one128, 3).div_u64(pd).store(hu + 2 * d, 2);           // floor(2^128 / p_d) < 2^128
   }
-  {   // floor(2^128 * ceil(P/2) / P); P is odd, so ceil(P/2) = floor(P/2) + 1
+  // fixed point for the fast CRT kernels: F = 64 + bits(p) - 1 when every prime has the same length
+  int F = 64 + (int)c->primes[0].bits - 1;
+  for (unsigned d = 0; d < D; d++) if (c->primes[d].bits != c->primes[0].bits) F = 0;
+  if (F > 126 || c->primes[0].bits < 33) F = 0;
+  if (F) {
+    std::vector<uint64_t> pw(3, 0);
+    pw[F / 64] = 1ull << (F % 64);
+    for (unsigned d = 0; d < D; d++) BigU(pw.data(), 3).div_u64(c->primes[d].p).store(hu + 2 * d, 2);
+    // floor(2^F * ceil(P/2) / P); P is odd, so ceil(P/2) = floor(P/2) + 1
     BigU half = P.shr(1);
-    std::vector<uint64_t> num(half.w.size() + 3, 0);
+    std::vector<uint64_t> hv(half.w.size() + 1, 0);
     uint64_t cy = 1;
-    for (size_t i = 0; i < half.w.size() + 1; i++) { uint64_t t = half.word(i) + cy; cy = (cy && t == 0); num[i + 2] = t; }
-    BigU(num.data(), num.size()).div(P).store(hhc, 2);
+    for (size_t i = 0; i < hv.size(); i++) { uint64_t t = half.word(i) + cy; cy = (cy && t == 0); hv[i] = t; }
+    BigU(hv.data(), hv.size()).mul(BigU(pw.data(), 3)).div(P).store(hhc, 2);
   }
   uint64_t *dv = nullptr;
   if (upload(&dv, buf.data(), buf.size())) return 1;
@@ -159,7 +165,7 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
   GqCrtBasis &B = hb.dev;
   B.D = (int)D; B.WT = (int)WT; B.bitsP = bitsP;
   B.P = dv; B.Ph = dv + WT; B.phat = dv + 2 * WT; B.inv = B.phat + (size_t)D * WT; B.inv_sh = B.inv + D;
-  B.u = B.inv_sh + D; B.hc = B.u + 2 * D;
+  B.u = B.inv_sh + D; B.hc = B.u + 2 * D; B.F = F;
   if (bitsP >= 58) {
     B.sh = (int)bitsP - 58;
     BigU top = P.shr((unsigned)B.sh);

@@ -56,8 +56,12 @@ GQ_DEV void crt_mod_P(uint64_t *acc, const CrtShared<WT> &S, const GqCrtBasis &B
                       const uint64_t *__restrict__ rhat, int n, int i) {
 #pragma unroll
   for (int w = 0; w <= WT; w++) acc[w] = 0;
+  uint64_t a0 = rhat[i], a1 = (B.D > 1) ? rhat[(size_t)n + i] : 0;
   for (int d = 0; d < B.D; d++) {
-    uint64_t y = gq_mul_shoup(rhat[(size_t)d * n + i], S.inv[d], S.inv_sh[d], S.p[d]);
+    const uint64_t a = a0;
+    a0 = a1;
+    a1 = (d + 2 < B.D) ? rhat[(size_t)(d + 2) * n + i] : 0;
+    uint64_t y = gq_mul_shoup(a, S.inv[d], S.inv_sh[d], S.p[d]);
     mw_mac<WT>(acc, y, &S.phat[d * WT]);
   }
   if (B.sh >= 0) {
@@ -321,16 +325,16 @@ k_ks_epilogue_general(GqCrtBasis B, const uint64_t *__restrict__ Pw, int nP,
 // (M counts the multiples of P removed by "mod P" plus the one removed by centring).  Modulo
 // 2^(64W) only the low W words of every P/p_d and of P enter, so the D x WT multiply-accumulate
 // shrinks to D x W - provided M is known exactly.  (S + ceil(P/2))/P = sum_d y_d/p_d + ceil(P/2)/P
-// is evaluated in fixed point with 128 fractional bits from below: est <= true < est + D*2^-67.
-// If the fraction of est is not within 2^-56 of 1 the integer part IS M.  Otherwise (the value
-// sits within 2^-56 of the +P/2 edge; never for honest ciphertexts) the coefficient index is put
+// is evaluated in fixed point with F = 64 + bits(p) - 1 fractional bits from below (floor(2^F/p_d)
+// fits one word): est <= true < est + D*2^-63.  If the fraction of est is not within 2^-54 of 1
+// the integer part IS M.  Otherwise (the value sits on the +P/2 edge; never for honest ciphertexts) the coefficient index is put
 // on a list and recomputed by the exact full-width kernel above in list mode.
 template <int W>
 struct CrtSharedLow {
   uint64_t phat[GQ_MAX_PRIMES * W];
   uint64_t P[W];
   uint64_t inv[GQ_MAX_PRIMES], inv_sh[GQ_MAX_PRIMES], p[GQ_MAX_PRIMES];
-  uint64_t u0[GQ_MAX_PRIMES], u1[GQ_MAX_PRIMES];
+  uint64_t u0[GQ_MAX_PRIMES];
   uint64_t hc[2];
 };
 
@@ -343,31 +347,42 @@ GQ_DEV void crt_low_stage(CrtSharedLow<W> &S, const GqCrtBasis &B, const GqPrime
   for (int j = threadIdx.x; j < W; j += blockDim.x) S.P[j] = (j < B.WT) ? B.P[j] : 0;
   for (int j = threadIdx.x; j < B.D; j += blockDim.x) {
     S.inv[j] = B.inv[j]; S.inv_sh[j] = B.inv_sh[j]; S.p[j] = primes[j].p;
-    S.u0[j] = B.u[2 * j]; S.u1[j] = B.u[2 * j + 1];
+    S.u0[j] = B.u[2 * j];
   }
   if (threadIdx.x < 2) S.hc[threadIdx.x] = B.hc[threadIdx.x];
 }
 
 // acc[0..W) = low words of the centred CRT value; false if M could not be decided
 template <int W>
-GQ_DEV bool crt_low(uint64_t *acc, const CrtSharedLow<W> &S, int D, const uint64_t *__restrict__ rhat,
-                    int n, int i) {
+GQ_DEV bool crt_low(uint64_t *acc, const CrtSharedLow<W> &S, int D, int fs,
+                    const uint64_t *__restrict__ rhat, int n, int i) {
 #pragma unroll
   for (int w = 0; w < W; w++) acc[w] = 0;
   uint64_t e0 = S.hc[0], e1 = S.hc[1], e2 = 0;
+  // residue loads run two limbs ahead of the arithmetic (long-scoreboard was the top stall)
+  uint64_t a0 = rhat[i], a1 = (D > 1) ? rhat[(size_t)n + i] : 0;
   for (int d = 0; d < D; d++) {
-    const uint64_t y = gq_mul_shoup(rhat[(size_t)d * n + i], S.inv[d], S.inv_sh[d], S.p[d]);
+    const uint64_t a = a0;
+    a0 = a1;
+    a1 = (d + 2 < D) ? rhat[(size_t)(d + 2) * n + i] : 0;
+    const uint64_t y = gq_mul_shoup(a, S.inv[d], S.inv_sh[d], S.p[d]);
     mw_mac_low<W>(acc, y, &S.phat[d * W]);
-    // est += y * (u1:u0); only the carry out of the lowest column of y*u0 matters below 2^64
+    // est += y * floor(2^F / p_d)   (one 64x64 product, 192-bit accumulator)
     const uint64_t h0 = gq_mulhi(y, S.u0[d]), l0 = y * S.u0[d];
-    const uint64_t l1 = y * S.u1[d], h1 = gq_mulhi(y, S.u1[d]);
-    uint64_t t = e0 + l0; uint64_t c = t < l0; e0 = t;
-    t = e1 + h0; uint64_t c1 = t < h0; t += c; c1 += t < c; uint64_t t2 = t + l1; c1 += t2 < l1; e1 = t2;
-    e2 += h1 + c1;
+    const uint64_t t = e0 + l0;
+    const uint64_t c0 = t < l0;
+    e0 = t;
+    const uint64_t t1 = e1 + h0;
+    uint64_t c1 = t1 < h0;
+    e1 = t1 + c0;
+    c1 += e1 < c0;
+    e2 += c1;
   }
-  if (e1 >= ~(uint64_t)0 - 255) return false;
+  // est = M * 2^F + fraction; F = 64 + fs, 32 <= fs <= 62
+  const uint64_t frac = (e0 >> fs) | (e1 << (64 - fs));
+  if (frac >= ~(uint64_t)0 - 1023) return false;
+  const uint64_t M = (e1 >> fs) | (e2 << (64 - fs));
   // acc -= M * P  (low words)
-  const uint64_t M = e2;
   uint64_t carry = 0, borrow = 0;
 #pragma unroll
   for (int w = 0; w < W; w++) {
@@ -403,7 +418,7 @@ k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
   if (i >= n) return;
   const int b = blockIdx.y;
   uint64_t acc[W];
-  if (!crt_low<W>(acc, S, B.D, rhat + (size_t)b * B.D * n, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
+  if (!crt_low<W>(acc, S, B.D, B.F - 64, rhat + (size_t)b * B.D * n, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
   mw_smod_pow2<W>(acc, k);
   store_words<W>(out.p[b], n, i, Wout, acc);
 }
@@ -427,7 +442,7 @@ k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pin
   const int b = blockIdx.y;
   const uint64_t *ch = chat + (size_t)b * B.D * n;
   uint64_t x[WP];
-  if (!crt_low<WP>(x, S, B.D, ch, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
+  if (!crt_low<WP>(x, S, B.D, B.F - 64, ch, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
   bool round_up;
   {
     uint64_t r[WP + 1];
@@ -591,7 +606,7 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
   dim3 grid((n + 127) / 128, npolys), block(128);
   int *fc = nullptr, *fl = nullptr;
   int launches = 1;
-  if (fix && q.is_pow2 && q.k >= 1 && q.k <= 64u * GQ_MAX_W) {
+  if (fix && B.F && q.is_pow2 && q.k >= 1 && q.k <= 64u * GQ_MAX_W) {
     fc = fix; fl = fix + 4;
     const int W = (int)((q.k + 63) / 64);
     dim3 g2((n + 255) / 256, npolys), b2(256);
@@ -644,7 +659,7 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
   dim3 grid((n + 127) / 128, npolys);
   int *fc = nullptr, *fl = nullptr;
   int launches = 1;
-  if (fix && k >= 1 && BP.WT <= B.WT) {
+  if (fix && B.F && k >= 1 && BP.WT <= B.WT) {
     fc = fix; fl = fix + 4;
     dim3 block(128);
     switch (BP.WT) {

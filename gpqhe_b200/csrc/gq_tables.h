@@ -46,8 +46,11 @@ struct GqCrtBasis {
   const uint64_t *inv_sh; // [D]       Shoup companion
   // fixed-point image of 1/p_d and of ceil(P/2)/P with 128 fractional bits: lets the fast CRT
   // kernels find the overflow count floor((S + ceil(P/2))/P) without the high words of S
-  const uint64_t *u;      // [D][2]    floor(2^128 / p_d)
-  const uint64_t *hc;     // [2]       floor(2^128 * ceil(P/2) / P)
+  // F = 64 + bits(p) - 1 fractional bits (all primes of the basis have the same bit length, else
+  // F = 0 and only the exact kernels are used): floor(2^F / p_d) then fits one word
+  int F;
+  const uint64_t *u;      // [D][2]    floor(2^F / p_d) (second word 0)
+  const uint64_t *hc;     // [2]       floor(2^F * ceil(P/2) / P)
 };
 
 // a modulus q used by mpi_smod (src/types.c:108): power-of-two fast path or general
