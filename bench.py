@@ -284,19 +284,19 @@ def run_ours(args):
 
     # ---- configs[3]: rotation sweep, he_rot = Galois permutation + key switch, rot = 0..NROT-1 with
     # one switching key per rotation (the he_gemv workload: slots=16 rotations)
-    NROT = 16
-    rks = [ctx.genevk(synth_evk(rng, ctx.primes, n, ctx.dimevk), synth_evk(rng, ctx.primes, n, ctx.dimevk))
-           for _ in range(NROT)]
-    drot = dpool[:, :2].clone()                       # [POOL][2][W][n] ciphertexts rotated in place
+    def rotation_sweep(NROT=16):
+        rks = [ctx.genevk(synth_evk(rng, ctx.primes, n, ctx.dimevk), synth_evk(rng, ctx.primes, n, ctx.dimevk))
+               for _ in range(NROT)]
+        drot = dpool[:, :2].clone()                   # [POOL][2][W][n] ciphertexts rotated in place
 
-    def rot_step(i):
-        b = drot.data_ptr() + (i % POOL) * 2 * poly
-        ck(lib.gq_he_rot_dev(h, L, i % NROT, b, b + poly, rks[i % NROT]._h, None))
-    nrot = max(args.steps, NROT)
-    ms_rot = timed(rot_step, nrot, args.warmup)
-    rot_sweep = {"he_rot_per_s": world * nrot / (ms_rot * 1e-3), "ms_per_rot": ms_rot / nrot, "rotations": NROT,
-                 "keyswitch_limbs": D2, "note": "he_rot at l=L, 16 distinct rotation keys (384 MiB) cycled"}
-    del rks, drot
+        def rot_step(i):
+            b = drot.data_ptr() + (i % POOL) * 2 * poly
+            ck(lib.gq_he_rot_dev(h, L, i % NROT, b, b + poly, rks[i % NROT]._h, None))
+        nrot = max(args.steps, NROT)
+        ms_rot = timed(rot_step, nrot, args.warmup)
+        return {"he_rot_per_s": world * nrot / (ms_rot * 1e-3), "ms_per_rot": ms_rot / nrot, "rotations": NROT,
+                "keyswitch_limbs": D2, "note": "he_rot at l=L, 16 distinct rotation keys (384 MiB) cycled"}
+    rot_sweep = None if args.no_rot else rotation_sweep()
 
     # ---- limb-sharded single-stream pipeline: all ranks cooperate on ONE he_mul+he_rs;
     # ciphertexts stay coefficient-sharded, four all-to-alls per op (gpqhe_b200/sharded.py)
@@ -394,6 +394,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-rot", action="store_true", help="skip the rotation sweep leg")
     ap.add_argument("--no-sharded", action="store_true", help="skip the limb-sharded single-stream leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
