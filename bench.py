@@ -338,6 +338,52 @@ def run_ours(args):
                    "note": "one ciphertext stream sharded by RNS limb (NTT domain) and by coefficient (CRT domain); "
                            "NCCL all_to_all_single between the domains"}
 
+        # peer-to-peer variant: the re-layouts are scatter kernels writing into the peers' slabs over
+        # NVLink (gq_p2p.cu), epoch flags instead of NCCL, the whole op one CUDA graph per rank
+        def all_ok(flag):
+            if world == 1:
+                return bool(flag)
+            t = torch.tensor([1 if flag else 0], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            return bool(t.item())
+        if not args.no_p2p:
+            from gpqhe_b200.sharded import P2PPlan
+            pp, ok, match = None, True, False
+            try:
+                with torch.cuda.stream(ext):
+                    pp = P2PPlan.build(sh, L, evk_s, rescale=True)
+                    for k in range(4):
+                        pp.inp[k].copy_(sl[k])
+                    pp.run()
+                    ctx.sync()
+                    want0, want1 = plan.out[0], plan.out[1]
+                    match = bool(torch.equal(pp.out[0], want0) and torch.equal(pp.out[1], want1)) and not pp.failed()
+            except Exception as ex:
+                print(f"bench.py: p2p plan failed: {ex!r}", file=sys.stderr)
+                ok = False
+            if all_ok(ok):
+                ms_pe = timed(lambda i: pp.run(), args.steps, args.warmup)
+                p2p = {"bit_exact_vs_nccl_plan": all_ok(match), "eager_ms_per_op": ms_pe / args.steps}
+                okc = True
+                try:
+                    with torch.cuda.stream(ext):
+                        pp.capture()
+                except Exception as ex:
+                    print(f"bench.py: p2p graph capture failed: {ex!r}", file=sys.stderr)
+                    okc = False
+                if all_ok(okc):
+                    ms_pg = timed(lambda i: pp.run(), args.steps, args.warmup)
+                    with torch.cuda.stream(ext):
+                        ctx.sync()
+                        same = bool(torch.equal(pp.out[0], plan.out[0]) and torch.equal(pp.out[1], plan.out[1]))
+                    p2p.update({"ms_per_op": ms_pg / args.steps, "ops_per_s": args.steps / (ms_pg * 1e-3),
+                                "one_graph_per_op": True, "bit_exact_after_replays": all_ok(same and not pp.failed())})
+                else:
+                    pp.graph = None
+                sharded["p2p"] = p2p
+            else:
+                sharded["p2p"] = {"error": "plan construction failed on some rank (see stderr)"}
+
     # ---- end to end through the host C ABI: pinned host buffers, copies inside the timed region ----
     hout = torch.empty((2, W, n), dtype=torch.int64).pin_memory()
 
@@ -395,6 +441,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-rot", action="store_true", help="skip the rotation sweep leg")
+    ap.add_argument("--no-p2p", action="store_true", help="skip the peer-to-peer variant of the sharded leg")
     ap.add_argument("--no-sharded", action="store_true", help="skip the limb-sharded single-stream leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -80,6 +80,15 @@ SIGNATURES = {
     "gq_stage_reconstruct_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.POINTER(vp), C.c_uint, vp]),
     "gq_stage_ks_epilogue_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, vp]),
     "gq_stage_rescale_dev": (C.c_int, [vp, C.c_uint, vp, vp, C.c_int, C.c_uint, vp]),
+    "gq_p2p_alloc": (C.c_int, [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]),
+    "gq_p2p_open": (C.c_int, [vp, C.c_char_p, C.POINTER(vp)]),
+    "gq_p2p_close": (C.c_int, [vp, vp]),
+    "gq_p2p_free": (C.c_int, [vp, vp]),
+    "gq_p2p_scatter_c2l_dev": (C.c_int, [vp, vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(vp), C.POINTER(C.c_int), vp]),
+    "gq_p2p_scatter_l2c_dev": (C.c_int, [vp, vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(vp), C.POINTER(C.c_int), vp]),
+    "gq_p2p_bump_dev": (C.c_int, [vp, vp, vp]),
+    "gq_p2p_signal_dev": (C.c_int, [vp, C.POINTER(vp), C.c_uint, C.c_uint, C.c_uint, vp, vp]),
+    "gq_p2p_wait_dev": (C.c_int, [vp, vp, C.c_uint, C.c_uint, vp, vp, vp]),
 }
 
 _loaded: dict[str, C.CDLL] = {}

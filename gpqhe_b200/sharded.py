@@ -315,3 +315,190 @@ class MulPlan:
             if k < 4:
                 self._exchange(k)
         return self.out[0], self.out[1]
+
+
+class P2PPlan:
+    """he_mul (+ he_rs) sharded over G ranks with the re-layouts written straight into the peers'
+    memory (gq_p2p.cu): per exchange one scatter kernel + an epoch signal on the producer and a flag
+    wait on the consumer; no NCCL, no pack/unpack copies.  The whole op on one rank is ONE CUDA graph
+    (the epoch is read from device memory).
+
+    `slabs[s]` is rank s's receive slab as mapped in this process.  build() wires real ranks through
+    CUDA IPC handles exchanged over torch.distributed; loopback() builds G virtual ranks inside one
+    process (single GPU or the emulated library), run stage by stage in lockstep - the CPU tier uses
+    that to check every index of the scatter kernels."""
+
+    SLOTS = 8
+
+    def __init__(self, ctx: HeContext, G: int, rank: int, l: int, rlk: HeEvk, slabs, rescale=True,
+                 device="cpu"):
+        self.ctx, self.G, self.rank, self.l, self.rlk, self.rescale = ctx, G, rank, l, rlk, rescale
+        self._lib, self._h = ctx._lib, ctx._h
+        self.n, self.W, self.nl = ctx.n, ctx.W, ctx.n // G
+        self.device = torch.device(device)
+        self.D1, self.D2 = ctx.dims(l)
+        self.off1, self.off2 = self._offsets(self.D1), self._offsets(self.D2)
+        self.lo1, self.D1l = self.off1[rank], self.off1[rank + 1] - self.off1[rank]
+        self.lo2, self.D2l = self.off2[rank], self.off2[rank + 1] - self.off2[rank]
+        lay = self.layout(ctx, G, l)
+        self.lay = lay
+        self.slab = slabs[rank]
+        E = lambda *shape: torch.empty(shape, dtype=torch.int64, device=self.device)
+        self.inp, self.out = E(4, self.W, self.nl), E(2, self.W, self.nl)
+        self.xc, self.yl = E(4, self.D1, self.nl), E(3, max(self.D1l, 1), self.n)
+        self.d, self.x2c = E(3, self.W, self.nl), E(1, self.D2, self.nl)
+        self.y2l = E(2, max(self.D2l, 1), self.n)
+        self.epoch = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self.err = torch.zeros(1, dtype=torch.int32, device=self.device)
+        ptrs = lambda key: (C.c_void_p * G)(*[slabs[s] + 8 * lay[key] for s in range(G)])
+        self.p_flags, self.p_xl1, self.p_rh = ptrs("flags"), ptrs("xl1"), ptrs("rh")
+        self.p_xl2, self.p_ch = ptrs("xl2"), ptrs("ch")
+        self.c_off1 = (C.c_int * (G + 1))(*self.off1)
+        self.c_off2 = (C.c_int * (G + 1))(*self.off2)
+        self.graph = None
+
+    def _offsets(self, D):
+        base, extra = divmod(D, self.G)
+        off = [0]
+        for r in range(self.G):
+            off.append(off[-1] + base + (1 if r < extra else 0))
+        return off
+
+    @staticmethod
+    def layout(ctx: HeContext, G: int, l: int):
+        """word offsets of the sub-buffers inside a slab (identical on every rank)"""
+        n, nl = ctx.n, ctx.n // G
+        D1, D2 = ctx.dims(l)
+        m1, m2 = -(-D1 // G), -(-D2 // G)
+        lay, pos = {}, 0
+        for key, words in (("flags", 256), ("xl1", 4 * m1 * n), ("rh", 3 * D1 * nl), ("xl2", m2 * n),
+                           ("ch", 2 * D2 * nl)):
+            lay[key] = pos
+            pos += (words + 31) // 32 * 32
+        lay["words"] = pos
+        return lay
+
+    def _ck(self, rc):
+        capi.check(self._lib, rc)
+
+    def _loc(self, key):
+        return self.slab + 8 * self.lay[key]
+
+    # -- exchange primitives ---------------------------------------------------------------
+    def _c2l(self, src, P, D, dst, off, slot):
+        lib, h = self._lib, self._h
+        self._ck(lib.gq_p2p_scatter_c2l_dev(h, src.data_ptr(), P, D, self.nl, self.G, self.rank, dst, off, None))
+        self._ck(lib.gq_p2p_signal_dev(h, self.p_flags, slot, self.G, self.rank, self.epoch.data_ptr(), None))
+
+    def _l2c(self, src, P, Dl, D, dst, off, slot):
+        lib, h = self._lib, self._h
+        self._ck(lib.gq_p2p_scatter_l2c_dev(h, src.data_ptr(), P, Dl, D, self.nl, self.G, self.rank, dst, off, None))
+        self._ck(lib.gq_p2p_signal_dev(h, self.p_flags, slot, self.G, self.rank, self.epoch.data_ptr(), None))
+
+    def _wait(self, slot):
+        self._ck(self._lib.gq_p2p_wait_dev(self._h, self._loc("flags"), slot, self.G, self.epoch.data_ptr(),
+                                           self.err.data_ptr(), None))
+
+    # -- the five segments (producer side ends with scatter + signal, consumer side starts with wait)
+    def seg(self, k):
+        lib, h, W, nl = self._lib, self._h, self.W, self.nl
+        if k == 0:
+            self._ck(lib.gq_p2p_bump_dev(h, self.epoch.data_ptr(), None))
+            arr = (C.c_void_p * 4)(*[self.inp[j].data_ptr() for j in range(4)])
+            self._ck(lib.gq_stage_decompose_dev(h, 0, self.D1, 4, arr, W, nl, self.xc.data_ptr(), None))
+            self._c2l(self.xc, 4, self.D1, self.p_xl1, self.c_off1, 0)
+        elif k == 1:
+            self._wait(0)
+            if self.D1l:
+                xl = self._loc("xl1")
+                self._ck(lib.gq_stage_ntt_dev(h, self.lo1, self.D1l, 4, xl, 0, None))
+                self._ck(lib.gq_stage_tensor_dev(h, self.lo1, self.D1l, self.yl.data_ptr(), xl, None))
+                self._ck(lib.gq_stage_ntt_dev(h, self.lo1, self.D1l, 3, self.yl.data_ptr(), 1, None))
+            self._l2c(self.yl, 3, self.D1l, self.D1, self.p_rh, self.c_off1, 1)
+        elif k == 2:
+            self._wait(1)
+            outs = (C.c_void_p * 3)(*[self.d[j].data_ptr() for j in range(3)])
+            self._ck(lib.gq_stage_reconstruct_dev(h, self.D1, self.l, 3, self._loc("rh"), outs, nl, None))
+            arr = (C.c_void_p * 1)(self.d[2].data_ptr())
+            self._ck(lib.gq_stage_decompose_dev(h, 0, self.D2, 1, arr, W, nl, self.x2c.data_ptr(), None))
+            self._c2l(self.x2c, 1, self.D2, self.p_xl2, self.c_off2, 2)
+        elif k == 3:
+            self._wait(2)
+            if self.D2l:
+                xl = self._loc("xl2")
+                self._ck(lib.gq_stage_ntt_dev(h, self.lo2, self.D2l, 1, xl, 0, None))
+                self._ck(lib.gq_stage_mul_evk_dev(h, self.lo2, self.D2l, self.y2l.data_ptr(), xl, self.rlk._h, None))
+                self._ck(lib.gq_stage_ntt_dev(h, self.lo2, self.D2l, 2, self.y2l.data_ptr(), 1, None))
+            self._l2c(self.y2l, 2, self.D2l, self.D2, self.p_ch, self.c_off2, 3)
+        else:
+            self._wait(3)
+            self._ck(lib.gq_stage_ks_epilogue_dev(h, self.l, self._loc("ch"), self.d[0].data_ptr(),
+                                                  self.d[1].data_ptr(), self.out[0].data_ptr(),
+                                                  self.out[1].data_ptr(), nl, None))
+            if self.rescale:
+                self._ck(lib.gq_stage_rescale_dev(h, self.l, self.out[0].data_ptr(), self.out[1].data_ptr(), 1, nl, None))
+
+    def run(self):
+        """one he_mul (+ he_rs): self.inp -> self.out (real multi-rank use; every rank calls it)"""
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            for k in range(5):
+                self.seg(k)
+        return self.out[0], self.out[1]
+
+    def capture(self):
+        """record the whole op as one CUDA graph (call with the context's stream current, after a
+        warm-up run on every rank)"""
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=torch.cuda.current_stream(), capture_error_mode="thread_local"):
+            for k in range(5):
+                self.seg(k)
+        self.graph = g
+
+    def failed(self) -> bool:
+        return bool(self.err.item())
+
+    # -- wiring ----------------------------------------------------------------------------
+    @classmethod
+    def build(cls, sh: ShardedHe, l: int, rlk: HeEvk, rescale=True):
+        """real ranks: allocate my slab, exchange IPC handles over torch.distributed, map the peers"""
+        ctx, G, r = sh.ctx, sh.G, sh.rank
+        lay = cls.layout(ctx, G, l)
+        mine, handle = C.c_void_p(), C.create_string_buffer(64)
+        capi.check(ctx._lib, ctx._lib.gq_p2p_alloc(ctx._h, 8 * lay["words"], C.byref(mine), handle))
+        handles = [None] * G
+        if G > 1:
+            dist.all_gather_object(handles, handle.raw, group=sh.group)
+        else:
+            handles[0] = handle.raw
+        slabs = []
+        for s in range(G):
+            if s == r:
+                slabs.append(mine.value)
+            else:
+                p = C.c_void_p()
+                capi.check(ctx._lib, ctx._lib.gq_p2p_open(ctx._h, handles[s], C.byref(p)))
+                slabs.append(p.value)
+        plan = cls(ctx, G, r, l, rlk, slabs, rescale, sh.device)
+        plan._owned = mine.value
+        if G > 1:
+            dist.barrier(group=sh.group)     # every slab is zeroed and mapped before anyone signals
+        return plan
+
+    @classmethod
+    def loopback(cls, ctx: HeContext, G: int, l: int, rlk: HeEvk, rescale=True, device="cpu"):
+        """G virtual ranks in one process (tests): returns the list of plans"""
+        lay = cls.layout(ctx, G, l)
+        slabs = []
+        for _ in range(G):
+            p, hd = C.c_void_p(), C.create_string_buffer(64)
+            capi.check(ctx._lib, ctx._lib.gq_p2p_alloc(ctx._h, 8 * lay["words"], C.byref(p), hd))
+            slabs.append(p.value)
+        return [cls(ctx, G, r, l, rlk, slabs, rescale, device) for r in range(G)]
+
+    @staticmethod
+    def run_lockstep(plans):
+        for k in range(5):
+            for p in plans:
+                p.seg(k)

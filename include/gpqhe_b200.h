@@ -183,6 +183,28 @@ int gq_stage_ks_epilogue_dev(gq_ctx *ctx, unsigned l, const uint64_t *chat_dev, 
 int gq_stage_rescale_dev(gq_ctx *ctx, unsigned l, uint64_t *c0_dev, uint64_t *c1_dev, int divide,
                          unsigned ncoef, void *stream);
 
+/* ---- peer-to-peer re-layout for the sharded pipeline (gq_p2p.cu) ----------------------------
+ * One receive slab per rank, exported / mapped with CUDA IPC (one process per GPU, same node).
+ * scatter_c2l: src[P][D][nloc] -> owner of each limb, scatter_l2c: src[P][Dl][n] -> owner of each
+ * coefficient; dst[s] is rank s's destination buffer as mapped in THIS process, off[G+1] the limb
+ * ownership.  signal/wait: per-exchange epoch flags in the peers' slabs (slot < 8); the epoch is
+ * read from device memory (bump increments it) so the launches can be replayed from a CUDA graph.
+ * err_dev is set non-zero when a peer does not show up within a few seconds. */
+int gq_p2p_alloc(gq_ctx *ctx, size_t bytes, void **ptr_dev, unsigned char handle[64]);
+int gq_p2p_open(gq_ctx *ctx, const unsigned char handle[64], void **peer_ptr_dev);
+int gq_p2p_close(gq_ctx *ctx, void *peer_ptr_dev);
+int gq_p2p_free(gq_ctx *ctx, void *ptr_dev);
+int gq_p2p_scatter_c2l_dev(gq_ctx *ctx, const uint64_t *src_dev, unsigned P, unsigned D, unsigned nloc,
+                           unsigned G, unsigned me, const uint64_t *const *dst, const int *off, void *stream);
+int gq_p2p_scatter_l2c_dev(gq_ctx *ctx, const uint64_t *src_dev, unsigned P, unsigned Dl, unsigned D,
+                           unsigned nloc, unsigned G, unsigned me, const uint64_t *const *dst, const int *off,
+                           void *stream);
+int gq_p2p_bump_dev(gq_ctx *ctx, unsigned long long *epoch_dev, void *stream);
+int gq_p2p_signal_dev(gq_ctx *ctx, const uint64_t *const *flags, unsigned slot, unsigned G, unsigned me,
+                      const unsigned long long *epoch_dev, void *stream);
+int gq_p2p_wait_dev(gq_ctx *ctx, const uint64_t *flags_local_dev, unsigned slot, unsigned G,
+                    const unsigned long long *epoch_dev, int *err_dev, void *stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

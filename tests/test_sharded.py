@@ -111,3 +111,52 @@ def test_sharded_stage_entry_points_gpu(real_lib):
     dev = torch.device("cuda", 0)
     got, single, want, _ = _case(real_lib, 12, 1 << 109, 1 << 30, 0, dev)
     assert got == want and single == want
+
+
+def _loopback_case(lib_path, logn, q, Delta, logqub, G, device):
+    """G virtual ranks in ONE process through the peer-to-peer plan (scatter kernels + flags)."""
+    import gpqhe_b200 as g
+    from gpqhe_b200.sharded import P2PPlan
+    from oracle import pyoracle as o
+    ctx = g.HeContext(logn, q, 4, Delta, lib_path=lib_path, logqub=logqub)
+    oc = o.Ctx(logn, q, 4, Delta, logqub=logqub or None)
+    rng = random.Random(7)
+    n, W, l = ctx.n, ctx.W, ctx.L
+    ql = oc.ql[l]
+    polys = [[rng.randrange(ql) - ql // 2 for _ in range(n)] for _ in range(4)]
+    nr = np.random.default_rng(11)
+    p0 = np.concatenate([nr.integers(0, oc.primes[d], size=n, dtype=np.uint64) for d in range(oc.dimevk)])
+    p1 = np.concatenate([nr.integers(0, oc.primes[d], size=n, dtype=np.uint64) for d in range(oc.dimevk)])
+    evk = ctx.genevk(p0, p1)
+    big = [torch.from_numpy(g.ints_to_big(p, W).view(np.int64)).to(device) for p in polys]
+    import contextlib
+    cm = contextlib.nullcontext()
+    if torch.device(device).type == "cuda":
+        cm = torch.cuda.stream(torch.cuda.ExternalStream(ctx._lib.gq_ctx_stream(ctx._h), device=device))
+    with cm:
+        plans = P2PPlan.loopback(ctx, G, l, evk, rescale=True, device=device)
+        nl = n // G
+        for r, pl in enumerate(plans):
+            for k in range(4):
+                pl.inp[k].copy_(big[k][:, r * nl:(r + 1) * nl])
+        for _ in range(2):                               # epochs must advance correctly
+            P2PPlan.run_lockstep(plans)
+        ctx.sync()
+        assert not any(pl.failed() for pl in plans), "a flag wait timed out"
+        got = [g.big_to_ints(torch.cat([pl.out[k] for pl in plans], dim=1).cpu().numpy().view(np.uint64)) for k in range(2)]
+    e = o.he_rs(oc, o.he_mul(oc, {"l": l, "c0": polys[0], "c1": polys[1]}, {"l": l, "c0": polys[2], "c1": polys[3]}, (p0, p1)))
+    ctx.close()
+    assert got == [e["c0"], e["c1"]]
+
+
+@pytest.mark.parametrize("G,logn,logq,logDelta", [(2, 6, 438, 50), (4, 7, 438, 50), (8, 8, 120, 40), (3, 6, 120, 40)])
+def test_p2p_plan_loopback_emulated(emul_lib, G, logn, logq, logDelta):
+    if (1 << logn) % G:
+        pytest.skip("ring degree not divisible")
+    _loopback_case(emul_lib, logn, 1 << logq, 1 << logDelta, logq, G, "cpu")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("G", [1, 4, 8])
+def test_p2p_plan_loopback_gpu(real_lib, G):
+    _loopback_case(real_lib, 12, 1 << 109, 1 << 30, 0, G, torch.device("cuda", 0))
