@@ -322,7 +322,7 @@ def run_ours(args):
         # the eager pipeline is launch-bound (about 15 small launches per exchange from Python):
         # MulPlan records the work between two exchanges as one CUDA graph (5 graphs + 4 eager
         # all-to-alls per op, static buffers)
-        ms_s, graphed = ms_eager, False
+        ms_s, graphed, plan = ms_eager, False, None
         try:
             barrier()
             with torch.cuda.stream(ext):
@@ -346,7 +346,7 @@ def run_ours(args):
             t = torch.tensor([1 if flag else 0], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MIN)
             return bool(t.item())
-        if not args.no_p2p:
+        if not args.no_p2p and plan is not None:
             from gpqhe_b200.sharded import P2PPlan
             pp, ok, match = None, True, False
             try:
