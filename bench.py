@@ -404,9 +404,49 @@ def run_ours(args):
         t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-    e2e = {"value": world * args.steps / e2e_s, "unit": "ops/s", "h2d_bytes_per_step": 6 * poly,
-           "d2h_bytes_per_step": 4 * poly, "ms_per_step": e2e_s / args.steps * 1e3,
-           "api": "gq_he_mul + gq_he_rs (host pointers, pinned), one crossing per reference call"}
+    def wall(fn):
+        barrier()
+        t0 = time.perf_counter()
+        fn()
+        barrier()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        return dt
+    two_calls_s = e2e_s
+    # one crossing per product (gq_he_mul_rs), still one synchronous call per op
+    def fused_steps(k0, cnt):
+        for i in range(k0, k0 + cnt):
+            b = host_pool.data_ptr() + (i % POOL) * 4 * poly
+            ck(lib.gq_he_mul_rs(h, L, hout.data_ptr(), hout.data_ptr() + poly, b, b + poly, b + 2 * poly, b + 3 * poly, evk._h))
+    fused_steps(0, args.warmup)
+    fused_s = wall(lambda: fused_steps(args.warmup, args.steps))
+    # the batched entry point: `steps` products in one call, uploads / kernels / downloads pipelined
+    houts = torch.empty((POOL, 2, W, n), dtype=torch.int64).pin_memory()
+
+    def batch_call(k0, cnt):
+        VP = C.c_void_p * cnt
+        ins = [VP(*[host_pool.data_ptr() + ((k0 + i) % POOL) * 4 * poly + j * poly for i in range(cnt)]) for j in range(4)]
+        outs = [VP(*[houts.data_ptr() + ((k0 + i) % POOL) * 2 * poly + j * poly for i in range(cnt)]) for j in range(2)]
+        ck(lib.gq_he_mul_batch(h, L, cnt, outs[0], outs[1], ins[0], ins[1], ins[2], ins[3], evk._h, 1))
+    batch_call(0, max(args.warmup, 3))
+    batch_s = wall(lambda: batch_call(args.warmup, args.steps))
+    ctx.sync()
+    same = bool(torch.equal(houts[(args.warmup + args.steps - 1) % POOL].reshape(-1), hout.reshape(-1)))
+    e2e = {"value": world * args.steps / batch_s, "unit": "ops/s", "h2d_bytes_per_step": 4 * poly,
+           "d2h_bytes_per_step": 2 * poly, "ms_per_step": batch_s / args.steps * 1e3,
+           "api": f"gq_he_mul_batch(count={args.steps}, rescale=1): host pointers (page-locked), every product's "
+                  "4 input polys uploaded and 2 result polys downloaded inside the timed call; uploads, kernels and "
+                  "downloads of neighbouring products overlap on the two copy engines",
+           "batch_equals_single_call_result": same,
+           "single_call": {"gq_he_mul_rs": {"ops_per_s": world * args.steps / fused_s, "ms_per_step": fused_s / args.steps * 1e3,
+                                            "h2d_bytes_per_step": 4 * poly, "d2h_bytes_per_step": 2 * poly},
+                           "gq_he_mul+gq_he_rs": {"ops_per_s": world * args.steps / two_calls_s,
+                                                  "ms_per_step": two_calls_s / args.steps * 1e3,
+                                                  "h2d_bytes_per_step": 6 * poly, "d2h_bytes_per_step": 4 * poly,
+                                                  "note": "one crossing per reference call, as the drop-in issues them"}}}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

@@ -368,6 +368,9 @@ extern "C" void gq_ctx_destroy(gq_ctx *c) {
   for (auto &b : c->basis) cudaFree(b.blob);
   for (auto &m : c->qmod) cudaFree(m.blob);
   for (int s = 0; s < GQ_SLOT_COUNT; s++) cudaFree(c->slot[s]);
+  for (auto &e : c->ev_pipe) if (e) cudaEventDestroy(e);
+  if (c->s_in) cudaStreamDestroy(c->s_in);
+  if (c->s_out) cudaStreamDestroy(c->s_out);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -876,6 +879,74 @@ extern "C" int gq_he_mul(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, cons
   if (gq_he_mul_dev(c, l, io.in(5), io.in(6), io.in(0), io.in(1), io.in(2), io.in(3), rlk, nullptr)) return 1;
   return io_end(&io, c0, c1, 5, 6);
 }
+// he_mul followed by he_rs on its result in ONE crossing (the pair every CKKS product makes:
+// src/he-mult.c:100-150 then src/he-rescale.c:30-60)
+extern "C" int gq_he_mul_rs(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                            const uint64_t *a1, const uint64_t *b0, const uint64_t *b1, const gq_evk *rlk) {
+  if (he_check(c, l)) return 1;
+  if (l == 0) GQ_FAIL("cannot go below level 0");
+  if (!c0 || !c1 || !a0 || !a1 || !b0 || !b1) GQ_FAIL("null argument");
+  HostIO io; const uint64_t *src[4] = {a0, a1, b0, b1};
+  if (io_begin(c, &io, src, 4)) return 1;
+  if (gq_he_mul_dev(c, l, io.in(5), io.in(6), io.in(0), io.in(1), io.in(2), io.in(3), rlk, nullptr)) return 1;
+  if (rescale_dev(c, l, io.in(5), io.in(6), true, nullptr)) return 1;
+  return io_end(&io, c0, c1, 5, 6);
+}
+
+// `count` independent products (the row loop of he_gemv / a batch of ciphertext pairs), software
+// pipelined over the two copy engines: the upload of product i+1 and the download of product i-1
+// overlap the kernels of product i.  Two staging buffers per direction; host buffers should be
+// page-locked (gq_host_alloc) for the copies to be asynchronous.  Synchronous for the caller.
+static int pipe_init(gq_ctx *c) {
+  if (c->s_in) return 0;
+  GQ_CUDA(cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
+  GQ_CUDA(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
+  for (auto &e : c->ev_pipe) GQ_CUDA(cudaEventCreate(&e));
+  return 0;
+}
+extern "C" int gq_he_mul_batch(gq_ctx *c, unsigned l, unsigned count, uint64_t *const *c0, uint64_t *const *c1,
+                               const uint64_t *const *a0, const uint64_t *const *a1,
+                               const uint64_t *const *b0, const uint64_t *const *b1, const gq_evk *rlk,
+                               int rescale) {
+  if (he_check(c, l)) return 1;
+  if (rescale && l == 0) GQ_FAIL("cannot go below level 0");
+  if (!c0 || !c1 || !a0 || !a1 || !b0 || !b1 || !rlk) GQ_FAIL("null argument");
+  for (unsigned i = 0; i < count; i++)
+    if (!c0[i] || !c1[i] || !a0[i] || !a1[i] || !b0[i] || !b1[i]) GQ_FAIL("null polynomial pointer");
+  if (count == 0) return 0;
+  GQ_CUDA(cudaSetDevice(c->device));
+  if (pipe_init(c)) return 1;
+  const size_t poly = (size_t)c->W * c->n;
+  if (ensure_slot(c, GQ_SLOT_PIPE, 12 * poly * 8)) return 1;
+  uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_PIPE];
+  cudaEvent_t *ev = c->ev_pipe;      // [4*k + {0: in_ready, 1: in_free, 2: out_ready, 3: out_free}]
+  int rc = 0;
+  for (unsigned i = 0; i < count && !rc; i++) {
+    const int k = (int)(i & 1);
+    uint64_t *in = base + (size_t)k * 6 * poly, *out = in + 4 * poly;
+    const uint64_t *src[4] = {a0[i], a1[i], b0[i], b1[i]};
+    if (i >= 2) GQ_CUDA(cudaStreamWaitEvent(c->s_in, ev[4 * k + 1], 0));
+    for (int j = 0; j < 4; j++)
+      GQ_CUDA(cudaMemcpyAsync(in + j * poly, src[j], poly * 8, cudaMemcpyHostToDevice, c->s_in));
+    GQ_CUDA(cudaEventRecord(ev[4 * k + 0], c->s_in));
+    GQ_CUDA(cudaStreamWaitEvent(c->stream, ev[4 * k + 0], 0));
+    if (i >= 2) GQ_CUDA(cudaStreamWaitEvent(c->stream, ev[4 * k + 3], 0));
+    rc = gq_he_mul_dev(c, l, out, out + poly, in, in + poly, in + 2 * poly, in + 3 * poly, rlk, nullptr);
+    if (!rc && rescale) rc = rescale_dev(c, l, out, out + poly, true, nullptr);
+    if (rc) break;
+    GQ_CUDA(cudaEventRecord(ev[4 * k + 1], c->stream));
+    GQ_CUDA(cudaEventRecord(ev[4 * k + 2], c->stream));
+    GQ_CUDA(cudaStreamWaitEvent(c->s_out, ev[4 * k + 2], 0));
+    GQ_CUDA(cudaMemcpyAsync(c0[i], out, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
+    GQ_CUDA(cudaMemcpyAsync(c1[i], out + poly, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
+    GQ_CUDA(cudaEventRecord(ev[4 * k + 3], c->s_out));
+  }
+  cudaStreamSynchronize(c->s_in);
+  cudaStreamSynchronize(c->stream);
+  GQ_CUDA(cudaStreamSynchronize(c->s_out));
+  return rc;
+}
+
 extern "C" int gq_he_mulpt(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
                            const uint64_t *a0, const uint64_t *a1, const uint64_t *m) {
   if (he_check(c, l)) return 1;

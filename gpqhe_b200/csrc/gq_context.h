@@ -19,7 +19,7 @@ struct GqHostModulus {
   void *blob = nullptr;
 };
 
-enum { GQ_SLOT_LIMB_A = 0, GQ_SLOT_LIMB_B, GQ_SLOT_BIG, GQ_SLOT_IO, GQ_SLOT_COUNT };
+enum { GQ_SLOT_LIMB_A = 0, GQ_SLOT_LIMB_B, GQ_SLOT_BIG, GQ_SLOT_IO, GQ_SLOT_PIPE, GQ_SLOT_COUNT };
 
 struct gq_ctx {
   int device = 0;
@@ -43,8 +43,11 @@ struct gq_ctx {
   bool fast_crt = true;
   uint64_t *d_adhoc = nullptr;       // scratch for an ad-hoc modulus (q, qh)
   // growable device scratch
-  void *slot[GQ_SLOT_COUNT] = {nullptr, nullptr, nullptr, nullptr};
-  size_t slot_bytes[GQ_SLOT_COUNT] = {0, 0, 0, 0};
+  void *slot[GQ_SLOT_COUNT] = {};
+  size_t slot_bytes[GQ_SLOT_COUNT] = {};
+  // copy engines of the batched host entry points (created on first use)
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ev_pipe[8] = {};       // {in_ready, in_free, out_ready, out_free} x 2 buffers
   unsigned long long launches = 0;
   bool lazy_ntt = true;          // internal pipelines use gq_ntt_lazy.cu when every prime allows it
 

@@ -278,6 +278,43 @@ class HeContext:
         B = ct1.nu * ct2.B + ct2.nu * ct1.B + ct1.B * ct2.B + self.Bmult[l]
         return HeCt(l, c0, c1, nu, B)
 
+    def he_mul_rs(self, ct1: HeCt, ct2: HeCt, rlk: HeEvk) -> HeCt:
+        """he_mul then he_rs on the product, one crossing (gq_he_mul_rs)."""
+        return self.he_mul_batch([(ct1, ct2)], rlk, rescale=True, fused_single=True)[0]
+
+    def he_mul_batch(self, pairs, rlk: HeEvk, rescale: bool = True, fused_single: bool = False):
+        """[he_mul(a, b) (+ he_rs) for a, b in pairs] through the pipelined batch entry point
+        (gq_he_mul_batch); metadata follows he-mult.c:93-95 and he-rescale.c:40-44."""
+        if not pairs:
+            return []
+        l = pairs[0][0].l
+        for a, b in pairs:
+            if a.l != l or b.l != l:
+                raise GpqheError("he_mul_batch: every ciphertext must be at the same level")
+        k = len(pairs)
+        hold = [[_c(a.c0), _c(a.c1), _c(b.c0), _c(b.c1)] for a, b in pairs]
+        outs = [(np.empty((self.W, self.n), dtype=np.uint64), np.empty((self.W, self.n), dtype=np.uint64))
+                for _ in range(k)]
+        if fused_single and k == 1:
+            h = hold[0]
+            capi.check(self._lib, self._lib.gq_he_mul_rs(self._h, l, _ptr(outs[0][0]), _ptr(outs[0][1]),
+                                                         _ptr(h[0]), _ptr(h[1]), _ptr(h[2]), _ptr(h[3]), rlk._h))
+        else:
+            arr = lambda xs: (C.c_void_p * k)(*[x.ctypes.data for x in xs])
+            capi.check(self._lib, self._lib.gq_he_mul_batch(
+                self._h, l, k, arr([o[0] for o in outs]), arr([o[1] for o in outs]),
+                arr([h[0] for h in hold]), arr([h[1] for h in hold]), arr([h[2] for h in hold]),
+                arr([h[3] for h in hold]), rlk._h, 1 if rescale else 0))
+        res = []
+        for (a, b), (c0, c1) in zip(pairs, outs):
+            nu = a.nu * b.nu
+            B = a.nu * b.B + b.nu * a.B + a.B * b.B + self.Bmult[l]
+            if rescale:
+                res.append(HeCt(l - 1, c0, c1, nu / float(self.Delta), B / float(self.Delta) + self.Brs))
+            else:
+                res.append(HeCt(l, c0, c1, nu, B))
+        return res
+
     def mulpt_dim(self, l: int, nu: float) -> int:
         """limb count of he_mulpt, double arithmetic truncated (src/he-mult.c:168)."""
         return int((self.ql[l].bit_length() + math.log2(nu) + self.logn) / self.logp + 1)

@@ -124,6 +124,16 @@ void gq_evk_destroy(gq_evk *evk);
 /* he_mul (mult + relinearise), src/he-mult.c:88-156; `l` = ct1->l = ct2->l; outputs may alias inputs */
 int gq_he_mul(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
               const uint64_t *a1, const uint64_t *b0, const uint64_t *b1, const gq_evk *rlk);
+/* he_mul immediately followed by he_rs on the product (src/he-mult.c:88-156 then
+   src/he-rescale.c:33-50) in one host<->device crossing; the result is at level l-1 */
+int gq_he_mul_rs(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                 const uint64_t *a1, const uint64_t *b0, const uint64_t *b1, const gq_evk *rlk);
+/* `count` independent he_mul (+ he_rs when `rescale`) at level l with one relinearisation key - the
+   row loop of he_gemv (src/he-linear.c) - pipelined over both copy engines; arrays of `count` poly
+   pointers; page-locked host memory (gq_host_alloc) makes the copies overlap the kernels */
+int gq_he_mul_batch(gq_ctx *ctx, unsigned l, unsigned count, uint64_t *const *c0, uint64_t *const *c1,
+                    const uint64_t *const *a0, const uint64_t *const *a1, const uint64_t *const *b0,
+                    const uint64_t *const *b1, const gq_evk *rlk, int rescale);
 /* he_mulpt, src/he-mult.c:159-196; `dim` is the limb count the caller derives from pt->nu (:168) */
 int gq_he_mulpt(gq_ctx *ctx, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
                 const uint64_t *a0, const uint64_t *a1, const uint64_t *m);

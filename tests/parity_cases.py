@@ -155,6 +155,16 @@ def check_he_vs_oracle(lib_path, logn, q, slots, Delta, seed=0, levels=None, rot
             assert g.big_to_ints(r.c0) == e["c0"] and g.big_to_ints(r.c1) == e["c1"], ("he_mul", l)
             r2, e2 = ctx.he_rs(r), o.he_rs(oc, e)
             assert r2.l == e2["l"] and g.big_to_ints(r2.c0) == e2["c0"] and g.big_to_ints(r2.c1) == e2["c1"], ("he_rs", l)
+            # one-crossing he_mul+he_rs and the pipelined batch (3 products: both staging buffers reused)
+            rf = ctx.he_mul_rs(c1, c2, evk)
+            assert rf.l == e2["l"] and g.big_to_ints(rf.c0) == e2["c0"] and g.big_to_ints(rf.c1) == e2["c1"], ("he_mul_rs", l)
+            eb = o.he_rs(oc, o.he_mul(oc, d2, d2, (p0, p1)))
+            for resc, want in ((True, [e2, eb, e2]), (False, [e, None, e])):
+                rb = ctx.he_mul_batch([(c1, c2), (c2, c2), (c2, c1)], evk, rescale=resc)
+                for got_ct, w in zip(rb, want):
+                    if w is not None:
+                        assert got_ct.l == w["l"] and g.big_to_ints(got_ct.c0) == w["c0"] and \
+                            g.big_to_ints(got_ct.c1) == w["c1"], ("he_mul_batch", l, resc)
             r3, e3 = ctx.he_moddown(c1), o.he_moddown(oc, d1)
             assert g.big_to_ints(r3.c0) == e3["c0"] and g.big_to_ints(r3.c1) == e3["c1"], ("he_moddown", l)
             for rot in rots:
