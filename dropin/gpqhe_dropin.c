@@ -471,6 +471,61 @@ void he_moddown(he_ct_t *ct)
 void he_rot(he_ct_t *ct, const int rot, const he_evk_t *rk) { ct_inplace(ct, 2, (unsigned)rot, &rk[rot], __func__); }
 void he_conj(he_ct_t *ct, const he_evk_t *ck) { ct_inplace(ct, 3, 0, ck, __func__); }
 
+/* ---- coefficient-local ops: src/he-add.c:32-146 ------------------------------- */
+static void ct_linear(he_ct_t *ct, const he_ct_t *a, const poly_mpi_t *b0, const poly_mpi_t *b1, int op,
+                      unsigned l, const char *who)
+{
+  const unsigned n = polyctx.n, W = G.info.W;
+  const size_t poly = (size_t)W * n;
+  uint64_t *s = stage(6 * poly);
+  poly_in(s, &a->c0, W, who);
+  poly_in(s + poly, &a->c1, W, who);
+  if (b0) poly_in(s + 2 * poly, b0, W, who);
+  if (b1) poly_in(s + 3 * poly, b1, W, who);
+  uint64_t *o0 = s + 4 * poly, *o1 = s + 5 * poly;
+  switch (op) {
+    case 0: CK(gq_he_add(ctx(), l, o0, o1, s, s + poly, s + 2 * poly, s + 3 * poly)); break;
+    case 1: CK(gq_he_sub(ctx(), l, o0, o1, s, s + poly, s + 2 * poly, s + 3 * poly)); break;
+    case 2: CK(gq_he_addpt(ctx(), l, o0, o1, s, s + poly, s + 2 * poly)); break;
+    case 3: CK(gq_he_subpt(ctx(), l, o0, o1, s, s + poly, s + 2 * poly)); break;
+    case 4: memcpy(o0, s, 2 * poly * sizeof(uint64_t)); CK(gq_he_neg(ctx(), l, o0, o1)); break;
+  }
+  poly_out(&ct->c0, o0, W);
+  poly_out(&ct->c1, o1, W);
+}
+
+void he_add(he_ct_t *ct, const he_ct_t *ct1, const he_ct_t *ct2)
+{
+  assert(ct1->l == ct2->l);
+  ct->l = ct1->l;                                                       /* he-add.c:36-38, in order */
+  ct->nu = (ct1->nu >= ct2->nu) ? ct1->nu : ct2->nu;
+  ct->B = ct1->B + ct2->B;
+  ct_linear(ct, ct1, &ct2->c0, &ct2->c1, 0, ct->l, __func__);
+}
+void he_sub(he_ct_t *ct, const he_ct_t *ct1, const he_ct_t *ct2)
+{
+  assert(ct1->l == ct2->l);
+  ct->l = ct1->l;                                                       /* he-add.c:61-63 */
+  ct->nu = (ct1->nu >= ct2->nu) ? ct1->nu : ct2->nu;
+  ct->B = ct1->B + ct2->B;
+  ct_linear(ct, ct1, &ct2->c0, &ct2->c1, 1, ct->l, __func__);
+}
+void he_addpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt)
+{
+  dest->l = src->l;                                                     /* he-add.c:85-87 */
+  dest->nu = (src->nu >= pt->nu) ? src->nu : pt->nu;
+  dest->B = src->B;
+  ct_linear(dest, src, &pt->m, NULL, 2, dest->l, __func__);
+}
+void he_subpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt)
+{
+  dest->l = src->l;                                                     /* he-add.c:109-111 */
+  dest->nu = (src->nu >= pt->nu) ? src->nu : pt->nu;
+  dest->B = src->B;
+  ct_linear(dest, src, &pt->m, NULL, 3, dest->l, __func__);
+}
+void he_neg(he_ct_t *ct) { ct_linear(ct, ct, NULL, NULL, 4, ct->l, __func__); }
+
 /* diagnostics for tests: coefficients marshalled in / out since load, and whether the direct
  * limb path is active */
 void gpqhe_dropin_stats(unsigned long long *in, unsigned long long *out, int *fast_mpi)

@@ -60,6 +60,16 @@ SIGNATURES = {
     "gq_evk_create_dev": (C.c_int, [vp, C.POINTER(vp), vp, vp]),
     "gq_evk_destroy": (None, [vp]),
     "gq_he_mul": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp]),
+    "gq_he_add": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp]),
+    "gq_he_sub": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp]),
+    "gq_he_addpt": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp]),
+    "gq_he_subpt": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp]),
+    "gq_he_neg": (C.c_int, [vp, C.c_uint, vp, vp]),
+    "gq_he_add_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp]),
+    "gq_he_sub_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp]),
+    "gq_he_addpt_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp]),
+    "gq_he_subpt_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp]),
+    "gq_he_neg_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp]),
     "gq_he_mul_rs": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp]),
     "gq_he_mul_batch": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, vp, C.c_int]),
     "gq_he_mulpt": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp, vp]),

@@ -824,6 +824,37 @@ extern "C" int gq_he_moddown_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *
   return rescale_dev(c, l, c0, c1, false, s);
 }
 
+// he_add / he_sub / he_addpt / he_subpt / he_neg (src/he-add.c:32-142): coefficient-local, one launch
+static int linear_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                      const uint64_t *b0, const uint64_t *b1, int op0, int op1, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !a0 || !a1 || (op0 < 2 && !b0) || (op1 < 2 && !b1)) GQ_FAIL("null argument");
+  gq_launch_linear((int)c->n, (int)c->W, ptrs(c0, c1), ptrs(a0, a1), ptrs(b0 ? b0 : a0, b1 ? b1 : a1), 2,
+                   op0, op1, c->qmod[l].dev, pick(c, stream));
+  c->launches++;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+extern "C" int gq_he_add_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                             const uint64_t *a1, const uint64_t *b0, const uint64_t *b1, void *s) {
+  return linear_dev(c, l, c0, c1, a0, a1, b0, b1, 0, 0, s);
+}
+extern "C" int gq_he_sub_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                             const uint64_t *a1, const uint64_t *b0, const uint64_t *b1, void *s) {
+  return linear_dev(c, l, c0, c1, a0, a1, b0, b1, 1, 1, s);
+}
+extern "C" int gq_he_addpt_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                               const uint64_t *a1, const uint64_t *m, void *s) {
+  return linear_dev(c, l, c0, c1, a0, a1, m, nullptr, 0, 3, s);
+}
+extern "C" int gq_he_subpt_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                               const uint64_t *a1, const uint64_t *m, void *s) {
+  return linear_dev(c, l, c0, c1, a0, a1, m, nullptr, 1, 3, s);
+}
+extern "C" int gq_he_neg_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, void *s) {
+  return linear_dev(c, l, c0, c1, c0, c1, nullptr, nullptr, 2, 2, s);
+}
+
 static int automorph_ks_dev(gq_ctx *c, unsigned l, uint64_t g, uint64_t *c0, uint64_t *c1,
                             const gq_evk *swk, void *stream) {
   if (he_check(c, l)) return 1;
@@ -956,6 +987,31 @@ extern "C" int gq_he_mulpt(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0, ui
   if (gq_he_mulpt_dev(c, l, dim, io.in(5), io.in(6), io.in(0), io.in(1), io.in(2), nullptr)) return 1;
   return io_end(&io, c0, c1, 5, 6);
 }
+static int linear_host(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                       const uint64_t *b0, const uint64_t *b1, int op0, int op1) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !a0 || !a1 || (op0 < 2 && !b0) || (op1 < 2 && !b1)) GQ_FAIL("null argument");
+  HostIO io; const uint64_t *src[4] = {a0, a1, b0, b1};
+  int nsrc = 2;
+  if (b0) { src[2] = b0; nsrc = 3; }
+  if (b1) { src[3] = b1; nsrc = 4; }
+  if (io_begin(c, &io, src, nsrc)) return 1;
+  if (linear_dev(c, l, io.in(5), io.in(6), io.in(0), io.in(1), b0 ? io.in(2) : nullptr, b1 ? io.in(3) : nullptr,
+                 op0, op1, nullptr)) return 1;
+  return io_end(&io, c0, c1, 5, 6);
+}
+extern "C" int gq_he_add(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                         const uint64_t *b0, const uint64_t *b1) { return linear_host(c, l, c0, c1, a0, a1, b0, b1, 0, 0); }
+extern "C" int gq_he_sub(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                         const uint64_t *b0, const uint64_t *b1) { return linear_host(c, l, c0, c1, a0, a1, b0, b1, 1, 1); }
+extern "C" int gq_he_addpt(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                           const uint64_t *m) { return linear_host(c, l, c0, c1, a0, a1, m, nullptr, 0, 3); }
+extern "C" int gq_he_subpt(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                           const uint64_t *m) { return linear_host(c, l, c0, c1, a0, a1, m, nullptr, 1, 3); }
+extern "C" int gq_he_neg(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1) {
+  return linear_host(c, l, c0, c1, c0, c1, nullptr, nullptr, 2, 2);
+}
+
 static int inplace_host(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, int op, unsigned rot,
                         const gq_evk *k) {
   if (he_check(c, l)) return 1;

@@ -50,6 +50,9 @@ void gq_launch_rescale_pow2(int n, int W, const GqPtrs4 &c, int npolys, unsigned
 // general Delta / q
 void gq_launch_rescale_general(int n, int W, const GqPtrs4 &c, int npolys, uint64_t Delta,
                                const GqModulus &q, cudaStream_t st);
+// out[y] = smod_q(a[y] op_y b[y]); op: 0 add, 1 sub, 2 negate a, 3 reduce a  (src/he-add.c:32-142)
+void gq_launch_linear(int n, int W, const GqPtrs4 &out, const GqPtrs4 &a, const GqPtrs4 &b, int npolys,
+                      int op0, int op1, const GqModulus &q, cudaStream_t st);
 // out[(i*g mod 2n) mod n] = +-in[i]   (poly_rot: g = 5^rot mod 2n; poly_conj: g = 2n-1)
 void gq_launch_automorph(int n, int W, const GqPtrs4 &out, const GqPtrs4 &in, int npolys,
                          uint64_t g, cudaStream_t st);

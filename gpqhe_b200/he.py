@@ -278,6 +278,44 @@ class HeContext:
         B = ct1.nu * ct2.B + ct2.nu * ct1.B + ct1.B * ct2.B + self.Bmult[l]
         return HeCt(l, c0, c1, nu, B)
 
+    def _linear(self, name, a: HeCt, b0, b1):
+        c0 = np.empty((self.W, self.n), dtype=np.uint64)
+        c1 = np.empty_like(c0)
+        args = [self._h, a.l, _ptr(c0), _ptr(c1), _ptr(_c(a.c0)), _ptr(_c(a.c1))]
+        args += [_ptr(_c(x)) for x in (b0, b1) if x is not None]
+        capi.check(self._lib, getattr(self._lib, name)(*args))
+        return c0, c1
+
+    def he_add(self, ct1: HeCt, ct2: HeCt) -> HeCt:
+        """he_add(ct, ct1, ct2) (src/he-add.c:32-54): nu = max, B = sum."""
+        if ct1.l != ct2.l:
+            raise GpqheError("he_add: ct1->l != ct2->l")
+        c0, c1 = self._linear("gq_he_add", ct1, ct2.c0, ct2.c1)
+        return HeCt(ct1.l, c0, c1, max(ct1.nu, ct2.nu), ct1.B + ct2.B)
+
+    def he_sub(self, ct1: HeCt, ct2: HeCt) -> HeCt:
+        """he_sub(ct, ct1, ct2) (src/he-add.c:57-79)."""
+        if ct1.l != ct2.l:
+            raise GpqheError("he_sub: ct1->l != ct2->l")
+        c0, c1 = self._linear("gq_he_sub", ct1, ct2.c0, ct2.c1)
+        return HeCt(ct1.l, c0, c1, max(ct1.nu, ct2.nu), ct1.B + ct2.B)
+
+    def he_addpt(self, ct: HeCt, pt: HePt) -> HeCt:
+        """he_addpt(dest, src, pt) (src/he-add.c:82-103)."""
+        c0, c1 = self._linear("gq_he_addpt", ct, pt.m, None)
+        return HeCt(ct.l, c0, c1, max(ct.nu, pt.nu), ct.B)
+
+    def he_subpt(self, ct: HeCt, pt: HePt) -> HeCt:
+        """he_subpt(dest, src, pt) (src/he-add.c:106-127)."""
+        c0, c1 = self._linear("gq_he_subpt", ct, pt.m, None)
+        return HeCt(ct.l, c0, c1, max(ct.nu, pt.nu), ct.B)
+
+    def he_neg(self, ct: HeCt) -> HeCt:
+        """he_neg(ct) (src/he-add.c:130-146); returns the negated ciphertext."""
+        c0, c1 = _c(ct.c0).copy(), _c(ct.c1).copy()
+        capi.check(self._lib, self._lib.gq_he_neg(self._h, ct.l, _ptr(c0), _ptr(c1)))
+        return HeCt(ct.l, c0, c1, ct.nu, ct.B)
+
     def he_mul_rs(self, ct1: HeCt, ct2: HeCt, rlk: HeEvk) -> HeCt:
         """he_mul then he_rs on the product, one crossing (gq_he_mul_rs)."""
         return self.he_mul_batch([(ct1, ct2)], rlk, rescale=True, fused_single=True)[0]

@@ -140,6 +140,17 @@ int gq_he_mulpt(gq_ctx *ctx, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c
 /* he_rs / he_moddown, src/he-rescale.c:33-70; in place; `l` is the level BEFORE the call */
 int gq_he_rs(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1);
 int gq_he_moddown(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1);
+/* he_add / he_sub (src/he-add.c:32-76), he_addpt / he_subpt (:79-120: only c0 meets the plaintext,
+   c1 is reduced), he_neg (:123-140, in place): out = smod_{q_l}(a op b); outputs may alias inputs */
+int gq_he_add(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+              const uint64_t *b0, const uint64_t *b1);
+int gq_he_sub(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+              const uint64_t *b0, const uint64_t *b1);
+int gq_he_addpt(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                const uint64_t *m);
+int gq_he_subpt(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                const uint64_t *m);
+int gq_he_neg(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1);
 /* he_rot / he_conj, src/he-automorphism.c:87-115; in place; `rk_rot` is &rk[rot] */
 int gq_he_rot(gq_ctx *ctx, unsigned l, unsigned rot, uint64_t *c0, uint64_t *c1, const gq_evk *rk_rot);
 int gq_he_conj(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const gq_evk *ck);
@@ -163,6 +174,15 @@ int gq_he_rot_dev(gq_ctx *ctx, unsigned l, unsigned rot, uint64_t *c0, uint64_t 
                   const gq_evk *rk_rot, void *stream);
 int gq_he_conj_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const gq_evk *ck,
                    void *stream);
+int gq_he_add_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                  const uint64_t *b0, const uint64_t *b1, void *stream);
+int gq_he_sub_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                  const uint64_t *b0, const uint64_t *b1, void *stream);
+int gq_he_addpt_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                    const uint64_t *a1, const uint64_t *m, void *stream);
+int gq_he_subpt_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                    const uint64_t *a1, const uint64_t *m, void *stream);
+int gq_he_neg_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, void *stream);
 
 /* ---- stage-level entry points (DEVICE pointers, enqueue only) ------------------------
  * One call = one stage of the pipelines above on a limb range [limb0, limb0+nlimbs) (NTT domain,

@@ -399,6 +399,37 @@ def he_conj(ctx: Ctx, ct: dict, ck) -> dict:
     return he_swk(ctx, ct["l"], poly_conj(ct["c0"], n), poly_conj(ct["c1"], n), ck)
 
 
+def he_add(ctx: Ctx, ct1: dict, ct2: dict) -> dict:
+    """src/he-add.c:32-54: mpi_addm then mpi_smod per coefficient."""
+    l = ct1["l"]
+    q, qh = ctx.ql[l], ctx.qh[l]
+    return {"l": l, "c0": [mpi_smod((x + y) % q, q, qh) for x, y in zip(ct1["c0"], ct2["c0"])],
+            "c1": [mpi_smod((x + y) % q, q, qh) for x, y in zip(ct1["c1"], ct2["c1"])]}
+
+
+def he_sub(ctx: Ctx, ct1: dict, ct2: dict) -> dict:
+    """src/he-add.c:57-79: mpi_subm then mpi_smod."""
+    l = ct1["l"]
+    q, qh = ctx.ql[l], ctx.qh[l]
+    return {"l": l, "c0": [mpi_smod((x - y) % q, q, qh) for x, y in zip(ct1["c0"], ct2["c0"])],
+            "c1": [mpi_smod((x - y) % q, q, qh) for x, y in zip(ct1["c1"], ct2["c1"])]}
+
+
+def he_addpt(ctx: Ctx, ct: dict, m: list[int], sign: int = 1) -> dict:
+    """src/he-add.c:82-103 (sign=+1) and :106-127 (he_subpt, sign=-1): c0 +- m, c1 only reduced."""
+    l = ct["l"]
+    q, qh = ctx.ql[l], ctx.qh[l]
+    return {"l": l, "c0": [mpi_smod((x + sign * y) % q, q, qh) for x, y in zip(ct["c0"], m)],
+            "c1": [mpi_smod(x % q, q, qh) for x in ct["c1"]]}
+
+
+def he_neg(ctx: Ctx, ct: dict) -> dict:
+    """src/he-add.c:130-146."""
+    l = ct["l"]
+    q, qh = ctx.ql[l], ctx.qh[l]
+    return {"l": l, "c0": [mpi_smod(-x, q, qh) for x in ct["c0"]], "c1": [mpi_smod(-x, q, qh) for x in ct["c1"]]}
+
+
 # --------------------------------------------------------------------------- #
 # packed-word interchange format used at the C-ABI (include/gpqhe_b200.h):
 # word-major two's complement, words[w, i] = bits 64w..64w+63 of coefficient i

@@ -43,6 +43,11 @@ void gpqhe_ref_he_rs(he_ct_t *ct);
 void gpqhe_ref_he_moddown(he_ct_t *ct);
 void gpqhe_ref_he_rot(he_ct_t *ct, const int rot, const he_evk_t *rk);
 void gpqhe_ref_he_conj(he_ct_t *ct, const he_evk_t *ck);
+void gpqhe_ref_he_add(he_ct_t *ct, const he_ct_t *ct1, const he_ct_t *ct2);
+void gpqhe_ref_he_sub(he_ct_t *ct, const he_ct_t *ct1, const he_ct_t *ct2);
+void gpqhe_ref_he_addpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt);
+void gpqhe_ref_he_subpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt);
+void gpqhe_ref_he_neg(he_ct_t *ct);
 void gpqhe_dropin_stats(unsigned long long *in, unsigned long long *out, int *fast_mpi);
 
 static unsigned npass, nfail;
@@ -177,6 +182,20 @@ int main(int argc, char **argv)
   he_copy_ct(&g, &c2); he_copy_ct(&r, &c2);
   he_conj(&g, &ck); gpqhe_ref_he_conj(&r, &ck);
   report("he_conj", eq_ct(&g, &r));
+
+  /* ---- coefficient-local ops (src/he-add.c), aliased forms included */
+  he_add(&g, &c1, &c2); gpqhe_ref_he_add(&r, &c1, &c2);
+  report("he_add", eq_ct(&g, &r));
+  he_sub(&g, &g, &c1); gpqhe_ref_he_sub(&r, &r, &c1);            /* dest aliases ct1 */
+  report("he_sub (in place)", eq_ct(&g, &r));
+  he_add(&g, &g, &g); gpqhe_ref_he_add(&r, &r, &r);              /* x + x: wraps past q/2 */
+  report("he_add (x,x,x)", eq_ct(&g, &r));
+  he_neg(&g); gpqhe_ref_he_neg(&r);
+  report("he_neg", eq_ct(&g, &r));
+  he_addpt(&g, &c2, &pt2); gpqhe_ref_he_addpt(&r, &c2, &pt2);
+  report("he_addpt", eq_ct(&g, &r));
+  he_subpt(&g, &g, &pt2); gpqhe_ref_he_subpt(&r, &r, &pt2);
+  report("he_subpt (in place)", eq_ct(&g, &r));
 
   unsigned long long in = 0, out = 0;
   gpqhe_dropin_stats(&in, &out, NULL);

@@ -176,6 +176,20 @@ def check_he_vs_oracle(lib_path, logn, q, slots, Delta, seed=0, levels=None, rot
             pt = g.HePt(g.ints_to_big(m, W), nu=float(1 << 40))
             r6, e6 = ctx.he_mulpt(c1, pt), o.he_mulpt(oc, d1, m, ctx.mulpt_dim(l, pt.nu))
             assert g.big_to_ints(r6.c0) == e6["c0"] and g.big_to_ints(r6.c1) == e6["c1"], ("he_mulpt", l)
+            # coefficient-local ops (src/he-add.c); edge values of the centred range included
+            edge = [-(ql // 2) - (ql & 1), ql // 2 - 1, 0, -1, 1, ql // 2 - 1, -(ql // 2) - (ql & 1), ql // 3]
+            x0, x1 = list(a0), list(a1)
+            y0, y1 = list(b0), list(b1)
+            x0[:8], y0[:8] = edge, edge[::-1]
+            x1[:8], y1[:8] = edge, edge
+            cx, cy = g.HeCt(l, g.ints_to_big(x0, W), g.ints_to_big(x1, W)), g.HeCt(l, g.ints_to_big(y0, W), g.ints_to_big(y1, W))
+            dx, dy = {"l": l, "c0": x0, "c1": x1}, {"l": l, "c0": y0, "c1": y1}
+            for name, got_ct, w in (("he_add", ctx.he_add(cx, cy), o.he_add(oc, dx, dy)),
+                                    ("he_sub", ctx.he_sub(cx, cy), o.he_sub(oc, dx, dy)),
+                                    ("he_neg", ctx.he_neg(cx), o.he_neg(oc, dx)),
+                                    ("he_addpt", ctx.he_addpt(cx, pt), o.he_addpt(oc, dx, m, 1)),
+                                    ("he_subpt", ctx.he_subpt(cx, pt), o.he_addpt(oc, dx, m, -1))):
+                assert g.big_to_ints(got_ct.c0) == w["c0"] and g.big_to_ints(got_ct.c1) == w["c1"], (name, l)
             # aliasing contract: he_mul(&x,&x,&x) == he_mul with distinct buffers
             r7 = ctx.he_mul(c1, c1, evk)
             e7 = o.he_mul(oc, d1, d1, (p0, p1))
