@@ -275,6 +275,18 @@ def run_ours(args):
                 "algorithmic_bytes_per_launch": ntt_bytes, "kernel_ms_per_launch": ms_tile,
                 "note": "this kernel is bound by the integer-multiply pipe, not HBM: ncu shows sm__pipe_fmaheavy_cycles_active "
                         "61 % / alu 48 % / dram 12 % (profiles/r01_call5_full.md); the HBM fraction is reported as the contract asks"}
+    # integer-pipe roofline: what the tile kernel achieves in butterflies/s against the measured
+    # register-resident butterfly rate of this GPU (gq_peak.cu)
+    bf_peak, mw_peak = C.c_double(0), C.c_double(0)
+    ck(lib.gq_bench_intpipe(h, C.byref(bf_peak), C.byref(mw_peak)))
+    tile_bf = nlp * (n // 2) * 12 / (ms_tile * 1e-3)
+    roofline["int_pipe"] = {"bound": "integer multiply pipe (fmaheavy)", "unit": "Gbutterfly/s",
+                            "achieved": tile_bf / 1e9, "peak": bf_peak.value / 1e9,
+                            "frac": tile_bf / bf_peak.value if bf_peak.value else None,
+                            "madwide_peak_Gops": mw_peak.value / 1e9,
+                            "peak_source": "measured in this run: k_peak_butterfly (lazy Shoup butterfly, operands in "
+                                           "registers, 4 chains per thread, no memory)",
+                            "algorithmic_butterflies_per_launch": nlp * (n // 2) * 12}
     ntt = {"fwd_limb_ntt_per_s": world * nlp / (ms_f * 1e-3), "inv_limb_ntt_per_s": world * nlp / (ms_i * 1e-3),
            "fwd_ms_per_batch": ms_f, "inv_ms_per_batch": ms_i, "tile_kernel_ms_per_batch": ms_tile,
            "exact_fwd_limb_ntt_per_s": world * nlp / (ms_fx * 1e-3),

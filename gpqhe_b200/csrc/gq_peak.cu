@@ -1,0 +1,108 @@
+// gq_peak.cu - measured integer-pipe ceilings for the roofline of the NTT / CRT kernels (SURVEY 8d:
+// "measure the IMAD peak on the box with a dependent-free IMAD microbenchmark").
+//   k_peak_butterfly : the lazy Harvey butterfly of gq_ntt_lazy.cu (one Shoup multiplication by a
+//                      fixed twiddle + add / sub), operands in registers, 4 independent chains per
+//                      thread, no memory traffic: the speed of light of a butterfly on the SM.
+//   k_peak_madwide   : dependent-free 32x32+64 multiply-adds (IMAD.WIDE.U32), the raw multiplier rate.
+// Both report operations per second over the whole GPU; bench.py divides what the NTT kernels achieve
+// by the first one.
+#include <string>
+
+#include "../../include/gpqhe_b200.h"
+#include "gq_arith.h"
+#include "gq_context.h"
+
+namespace {
+
+__global__ void __launch_bounds__(256)
+k_peak_butterfly(uint64_t *sink, uint64_t p, uint64_t w, uint64_t wsh, int iters) {
+  const uint64_t p2 = 2 * p;
+  uint64_t x[4], y[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    x[k] = (uint64_t)(threadIdx.x + 1) * 0x9E3779B97F4A7C15ull % p;
+    y[k] = (uint64_t)(blockIdx.x + k + 1) * 0xD1B54A32D192ED03ull % p;
+  }
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      // forward lazy butterfly: t = y*w in [0,2p); x' = x + t; y' = x - t + 2p; then the conditional
+      // subtraction the radix-8 round amortises over three stages is done every time here
+      const uint64_t q = gq_mulhi(y[k], wsh);
+      const uint64_t t = y[k] * w - q * p;
+      uint64_t a = x[k] + t, b = x[k] - t + p2;
+      x[k] = (a >= p2) ? a - p2 : a;
+      y[k] = (b >= p2) ? b - p2 : b;
+    }
+  }
+  uint64_t acc = 0;
+#pragma unroll
+  for (int k = 0; k < 4; k++) acc ^= x[k] ^ y[k];
+  if (acc == 0x1234567) sink[0] = acc;   // keeps the loop alive, practically never taken
+}
+
+__global__ void __launch_bounds__(256)
+k_peak_madwide(uint64_t *sink, uint32_t m, int iters) {
+  uint64_t a[8];
+  uint32_t b[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) { a[k] = threadIdx.x + k; b[k] = (uint32_t)(blockIdx.x * 8 + k) | 1u; }
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int k = 0; k < 8; k++) a[k] = (uint64_t)b[k] * m + a[k];   // IMAD.WIDE.U32
+  }
+  uint64_t acc = 0;
+#pragma unroll
+  for (int k = 0; k < 8; k++) acc ^= a[k];
+  if (acc == 0x1234567) sink[0] = acc;
+}
+
+}  // namespace
+
+#define PK_CUDA(call)                                                                   \
+  do {                                                                                  \
+    cudaError_t e_ = (call);                                                            \
+    if (e_ != cudaSuccess) {                                                            \
+      gq_set_error(std::string(__func__) + ": " #call " -> " + cudaGetErrorString(e_)); \
+      return 1;                                                                         \
+    }                                                                                   \
+  } while (0)
+
+extern "C" int gq_bench_intpipe(gq_ctx *c, double *butterflies_per_s, double *madwide_per_s) {
+  if (!c || !butterflies_per_s || !madwide_per_s) { gq_set_error("gq_bench_intpipe: null argument"); return 1; }
+  if (c->primes.empty()) { gq_set_error("gq_bench_intpipe: context has no primes"); return 1; }
+  PK_CUDA(cudaSetDevice(c->device));
+  uint64_t *sink = nullptr;
+  PK_CUDA(cudaMalloc(&sink, 8));
+  const uint64_t p = c->primes[0].p, w = c->primes[0].ninv, wsh = c->primes[0].ninv_sh;
+  const int blocks = GQ_NUM_SMS * 8, threads = 256;
+  cudaEvent_t e0, e1;
+  PK_CUDA(cudaEventCreate(&e0));
+  PK_CUDA(cudaEventCreate(&e1));
+  float ms = 0.f;
+  int iters = 2000;
+#ifdef GQ_EMULATE
+  iters = 2;
+#endif
+  for (int rep = 0; rep < 2; rep++) {   // first pass warms up
+    PK_CUDA(cudaEventRecord(e0, c->stream));
+    GQ_LAUNCH(k_peak_butterfly, dim3(blocks), dim3(threads), c->stream, sink, p, w, wsh, iters);
+    PK_CUDA(cudaEventRecord(e1, c->stream));
+    PK_CUDA(cudaEventSynchronize(e1));
+    PK_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  }
+  *butterflies_per_s = (double)blocks * threads * 4.0 * iters / ((ms > 0.f ? ms : 1e-3) * 1e-3);
+  for (int rep = 0; rep < 2; rep++) {
+    PK_CUDA(cudaEventRecord(e0, c->stream));
+    GQ_LAUNCH(k_peak_madwide, dim3(blocks), dim3(threads), c->stream, sink, 0x9E3779B1u, iters * 4);
+    PK_CUDA(cudaEventRecord(e1, c->stream));
+    PK_CUDA(cudaEventSynchronize(e1));
+    PK_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  }
+  *madwide_per_s = (double)blocks * threads * 8.0 * iters * 4 / ((ms > 0.f ? ms : 1e-3) * 1e-3);
+  c->launches += 4;
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(sink);
+  return 0;
+}

@@ -184,6 +184,11 @@ int gq_he_subpt_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const u
                     const uint64_t *a1, const uint64_t *m, void *stream);
 int gq_he_neg_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, void *stream);
 
+/* measured integer-pipe ceilings of this GPU (no reference counterpart; roofline denominators of the
+   NTT / CRT kernels): lazy Shoup butterflies per second with operands in registers, and raw
+   32x32+64 multiply-adds per second.  Runs two short kernels on the context's stream and waits. */
+int gq_bench_intpipe(gq_ctx *ctx, double *butterflies_per_s, double *madwide_per_s);
+
 /* ---- stage-level entry points (DEVICE pointers, enqueue only) ------------------------
  * One call = one stage of the pipelines above on a limb range [limb0, limb0+nlimbs) (NTT domain,
  * limb-polys of the full ring degree n) or on a slice of `ncoef` coefficients (big-integer domain:
