@@ -49,7 +49,7 @@ k_peak_madwide(uint64_t *sink, uint32_t m, int iters) {
   for (int k = 0; k < 8; k++) { a[k] = threadIdx.x + k; b[k] = (uint32_t)(blockIdx.x * 8 + k) | 1u; }
   for (int it = 0; it < iters; it++) {
 #pragma unroll
-    for (int k = 0; k < 8; k++) a[k] = (uint64_t)b[k] * m + a[k];   // IMAD.WIDE.U32
+    for (int k = 0; k < 8; k++) a[k] = (uint64_t)((uint32_t)a[k] ^ b[k]) * m + a[k];   // IMAD.WIDE.U32 (+ one LOP3)
   }
   uint64_t acc = 0;
 #pragma unroll
