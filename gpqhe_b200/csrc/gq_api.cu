@@ -879,6 +879,42 @@ extern "C" int gq_he_conj_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1,
   return automorph_ks_dev(c, l, 2ull * c->n - 1, c0, c1, ck, s);
 }
 
+// Several rotations of ONE ciphertext (the baby steps of he_gemv, src/he-algo.c:62-66): identical bits
+// to `count` separate he_rot calls, with decompose + forward NTT of c1 done once (gq_pointwise.cu,
+// k_mul_evk_perm).  Outputs must not overlap the inputs.
+extern "C" int gq_he_rot_hoisted_dev(gq_ctx *c, unsigned l, unsigned count, const unsigned *rots,
+                                     uint64_t *const *c0_out, uint64_t *const *c1_out, const uint64_t *c0,
+                                     const uint64_t *c1, const gq_evk *const *rk, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (!rots || !c0_out || !c1_out || !c0 || !c1 || !rk) GQ_FAIL("null argument");
+  for (unsigned k = 0; k < count; k++)
+    if (!c0_out[k] || !c1_out[k] || !rk[k] || c0_out[k] == c0 || c1_out[k] == c1 || c0_out[k] == c1 || c1_out[k] == c0)
+      GQ_FAIL("null or aliased output");
+  if (count == 0) return 0;
+  cudaStream_t st = pick(c, stream);
+  const unsigned D2 = dim_ks(c, l), n = c->n, W = c->W;
+  if (D2 > c->dimevk) GQ_FAIL("key-switch basis exceeds dimevk");
+  if (!ntt_ok(c, 0, D2)) GQ_FAIL("modulus below 32 bits");
+  if (c->basis[D2 - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
+  if (ensure_slot(c, GQ_SLOT_LIMB_A, (size_t)4 * c->dimub * n * 8) ||
+      ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8) ||
+      ensure_slot(c, GQ_SLOT_BIG, (size_t)5 * W * n * 8)) return 1;
+  uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
+  uint64_t *d0 = (uint64_t *)c->slot[GQ_SLOT_BIG] + 3 * (size_t)W * n;
+  if (decompose_dev(c, 0, D2, ptrs(c1), W, 1, A, st)) return 1;
+  if (ntt_internal(c, 0, D2, 1, A, false, st)) return 1;
+  for (unsigned k = 0; k < count; k++) {
+    const uint64_t g = galois_rot(c, rots[k]);
+    gq_launch_mul_evk_perm(c->d_primes, (int)n, (int)c->logn, (int)D2, B, A, rk[k]->p0, rk[k]->p1, g, st,
+                           pm_ok(c, 0, D2));
+    gq_launch_automorph((int)n, (int)W, ptrs(d0), ptrs(c0), 1, g, st);
+    c->launches += 2;
+    if (ntt_internal(c, 0, D2, 2, B, true, st)) return 1;
+    if (ks_epilogue_dev(c, l, D2, B, d0, nullptr, c0_out[k], c1_out[k], 0, st)) return 1;
+  }
+  return 0;
+}
+
 // -------------------------------------------------------------- HE primitives (host buffers)
 // stage up to 5 big polys in, run, copy up to 2 out
 struct HostIO {
@@ -987,6 +1023,29 @@ extern "C" int gq_he_mulpt(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0, ui
   if (gq_he_mulpt_dev(c, l, dim, io.in(5), io.in(6), io.in(0), io.in(1), io.in(2), nullptr)) return 1;
   return io_end(&io, c0, c1, 5, 6);
 }
+extern "C" int gq_he_rot_hoisted(gq_ctx *c, unsigned l, unsigned count, const unsigned *rots,
+                                 uint64_t *const *c0_out, uint64_t *const *c1_out, const uint64_t *c0,
+                                 const uint64_t *c1, const gq_evk *const *rk) {
+  if (he_check(c, l)) return 1;
+  if (!rots || !c0_out || !c1_out || !c0 || !c1 || !rk) GQ_FAIL("null argument");
+  if (count == 0) return 0;
+  const size_t poly = (size_t)c->W * c->n;
+  if (ensure_slot(c, GQ_SLOT_PIPE, (2 + 2 * (size_t)count) * poly * 8)) return 1;
+  uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_PIPE];
+  GQ_CUDA(cudaMemcpyAsync(base, c0, poly * 8, cudaMemcpyHostToDevice, c->stream));
+  GQ_CUDA(cudaMemcpyAsync(base + poly, c1, poly * 8, cudaMemcpyHostToDevice, c->stream));
+  std::vector<uint64_t *> o0(count), o1(count);
+  for (unsigned k = 0; k < count; k++) { o0[k] = base + (2 + 2 * (size_t)k) * poly; o1[k] = o0[k] + poly; }
+  if (gq_he_rot_hoisted_dev(c, l, count, rots, o0.data(), o1.data(), base, base + poly, rk, nullptr)) return 1;
+  for (unsigned k = 0; k < count; k++) {
+    if (!c0_out[k] || !c1_out[k]) GQ_FAIL("null output");
+    GQ_CUDA(cudaMemcpyAsync(c0_out[k], o0[k], poly * 8, cudaMemcpyDeviceToHost, c->stream));
+    GQ_CUDA(cudaMemcpyAsync(c1_out[k], o1[k], poly * 8, cudaMemcpyDeviceToHost, c->stream));
+  }
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
 static int linear_host(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
                        const uint64_t *b0, const uint64_t *b1, int op0, int op1) {
   if (he_check(c, l)) return 1;

@@ -21,6 +21,9 @@ void gq_launch_tensor(const GqPrime *primes, int n, int D, uint64_t *y, const ui
                       cudaStream_t st, bool pm = false);
 void gq_launch_mul_evk(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
                        const uint64_t *e0, const uint64_t *e1, cudaStream_t st, bool pm = false);
+// the same with x read through the evaluation-point permutation of the Galois map g (hoisted rotations)
+void gq_launch_mul_evk_perm(const GqPrime *primes, int n, int logn, int D, uint64_t *y, const uint64_t *x,
+                            const uint64_t *e0, const uint64_t *e1, uint64_t g, cudaStream_t st, bool pm);
 void gq_launch_mul_pt(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,
                       cudaStream_t st, bool pm = false);
 

@@ -177,6 +177,41 @@ k_mul_pt_pm(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restri
   }
 }
 
+// Hoisted rotations: the key switch of sigma_g(d) from xhat = NTT(decompose(d)) computed ONCE.
+// sigma_g commutes with the coefficient-wise floor-mod (it only moves and negates coefficients) and
+// acts on the evaluation vector as a pure permutation: slot j of ntt()'s output holds the value at
+// psi^(2*brv(j)+1), and (sigma_g a)(psi^e) = a(psi^(e*g)).  So
+//   NTT(decompose(sigma_g d))[j] = xhat[pi(j)],  2*brv(pi(j))+1 = (2*brv(j)+1)*g mod 2n,
+// exactly (canonical residues on both sides), and y_k[j] = xhat[pi(j)] * evk.p_k[j] as in k_mul_evk.
+GQ_DEV unsigned gq_brev(unsigned x, int bits) { return __brev(x) >> (32 - bits); }
+
+template <bool PMODE>
+__global__ void __launch_bounds__(256)
+k_mul_evk_perm(const GqPrime *__restrict__ primes, int n, int logn, int D, uint64_t *__restrict__ y,
+               const uint64_t *__restrict__ x, const uint64_t *__restrict__ e0,
+               const uint64_t *__restrict__ e1, unsigned g) {
+  const long long per = (long long)D * n;
+  const size_t stride = (size_t)D * n;
+  const unsigned mask2n = 2u * (unsigned)n - 1u;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < per;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int d = (int)(i >> logn);
+    const unsigned j = (unsigned)(i & (n - 1));
+    const unsigned e = ((2u * gq_brev(j, logn) + 1u) * g) & mask2n;
+    const unsigned src = gq_brev((e - 1u) >> 1, logn);
+    const uint64_t a = x[(size_t)d * n + src], k0 = e0[i], k1 = e1[i];
+    if (PMODE) {
+      const PM m = load_pm(primes[d]);
+      y[i] = mulm_pm(a, k0, m);
+      y[stride + i] = mulm_pm(a, k1, m);
+    } else {
+      const GqPrime P = primes[d];
+      y[i] = gq_mulmod_barrett(a, k0, P);
+      y[stride + i] = gq_mulmod_barrett(a, k1, P);
+    }
+  }
+}
+
 inline int grid_for(long long work_items, int block) {
   long long blocks = (work_items + block - 1) / block;
   long long cap = (long long)GQ_NUM_SMS * 8;
@@ -208,6 +243,13 @@ void gq_launch_mul_evk(const GqPrime *primes, int n, int D, uint64_t *y, const u
   if (pm) { GQ_LAUNCH(k_mul_evk_pm, dim3(grid_for((long long)D * (n >> 1), 256)), dim3(256), st, primes, n, D, y, x, e0, e1); return; }
   GQ_LAUNCH(k_mul_evk, dim3(grid_for((long long)D * (n >> 1), 256)), dim3(256), st, primes, n, D, y, x,
             e0, e1);
+}
+
+void gq_launch_mul_evk_perm(const GqPrime *primes, int n, int logn, int D, uint64_t *y, const uint64_t *x,
+                            const uint64_t *e0, const uint64_t *e1, uint64_t g, cudaStream_t st, bool pm) {
+  const dim3 grid(grid_for((long long)D * n, 256));
+  if (pm) GQ_LAUNCH(k_mul_evk_perm<true>, grid, dim3(256), st, primes, n, logn, D, y, x, e0, e1, (unsigned)g);
+  else GQ_LAUNCH(k_mul_evk_perm<false>, grid, dim3(256), st, primes, n, logn, D, y, x, e0, e1, (unsigned)g);
 }
 
 void gq_launch_mul_pt(const GqPrime *primes, int n, int D, uint64_t *y, const uint64_t *x,

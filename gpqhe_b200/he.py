@@ -316,6 +316,20 @@ class HeContext:
         capi.check(self._lib, self._lib.gq_he_neg(self._h, ct.l, _ptr(c0), _ptr(c1)))
         return HeCt(ct.l, c0, c1, ct.nu, ct.B)
 
+    def he_rot_hoisted(self, ct: HeCt, rots, rk) -> list:
+        """[he_rot(copy of ct, r, rk) for r in rots] (src/he-automorphism.c:102-115) with the
+        decomposition and forward NTT of c1 shared between the rotations (gq_he_rot_hoisted)."""
+        rots = list(rots)
+        k = len(rots)
+        outs = [(np.empty((self.W, self.n), dtype=np.uint64), np.empty((self.W, self.n), dtype=np.uint64))
+                for _ in range(k)]
+        c0, c1 = _c(ct.c0), _c(ct.c1)
+        arr = lambda xs: (C.c_void_p * k)(*xs)
+        capi.check(self._lib, self._lib.gq_he_rot_hoisted(
+            self._h, ct.l, k, (C.c_uint * k)(*rots), arr([o[0].ctypes.data for o in outs]),
+            arr([o[1].ctypes.data for o in outs]), _ptr(c0), _ptr(c1), arr([rk[r]._h for r in rots])))
+        return [HeCt(ct.l, o0, o1, ct.nu, ct.B) for o0, o1 in outs]
+
     def he_mul_rs(self, ct1: HeCt, ct2: HeCt, rlk: HeEvk) -> HeCt:
         """he_mul then he_rs on the product, one crossing (gq_he_mul_rs)."""
         return self.he_mul_batch([(ct1, ct2)], rlk, rescale=True, fused_single=True)[0]

@@ -140,6 +140,11 @@ int gq_he_mulpt(gq_ctx *ctx, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c
 /* he_rs / he_moddown, src/he-rescale.c:33-70; in place; `l` is the level BEFORE the call */
 int gq_he_rs(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1);
 int gq_he_moddown(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1);
+/* `count` rotations rots[k] of one ciphertext with rns_decompose + ntt of c1 shared (see
+   gq_he_rot_hoisted_dev); host pointers, outputs are separate polynomials */
+int gq_he_rot_hoisted(gq_ctx *ctx, unsigned l, unsigned count, const unsigned *rots,
+                      uint64_t *const *c0_out, uint64_t *const *c1_out, const uint64_t *c0,
+                      const uint64_t *c1, const gq_evk *const *rk);
 /* he_add / he_sub (src/he-add.c:32-76), he_addpt / he_subpt (:79-120: only c0 meets the plaintext,
    c1 is reduced), he_neg (:123-140, in place): out = smod_{q_l}(a op b); outputs may alias inputs */
 int gq_he_add(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
@@ -174,6 +179,12 @@ int gq_he_rot_dev(gq_ctx *ctx, unsigned l, unsigned rot, uint64_t *c0, uint64_t 
                   const gq_evk *rk_rot, void *stream);
 int gq_he_conj_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const gq_evk *ck,
                    void *stream);
+/* `count` rotations rots[k] of ONE ciphertext (the baby steps of he_gemv, src/he-algo.c:62-66): the same
+   bits as `count` he_rot calls, with rns_decompose + ntt of c1 shared (hoisting).  rk[k] = key of
+   rotation rots[k]; outputs must not overlap the inputs. */
+int gq_he_rot_hoisted_dev(gq_ctx *ctx, unsigned l, unsigned count, const unsigned *rots,
+                          uint64_t *const *c0_out, uint64_t *const *c1_out, const uint64_t *c0,
+                          const uint64_t *c1, const gq_evk *const *rk, void *stream);
 int gq_he_add_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
                   const uint64_t *b0, const uint64_t *b1, void *stream);
 int gq_he_sub_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,

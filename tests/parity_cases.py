@@ -170,6 +170,11 @@ def check_he_vs_oracle(lib_path, logn, q, slots, Delta, seed=0, levels=None, rot
             for rot in rots:
                 r4, e4 = ctx.he_rot(c1, rot, {rot: evk}), o.he_rot(oc, d1, rot, (p0, p1))
                 assert g.big_to_ints(r4.c0) == e4["c0"] and g.big_to_ints(r4.c1) == e4["c1"], ("he_rot", l, rot)
+            # hoisted rotations: decompose + NTT of c1 shared, same bits as separate he_rot calls
+            hrots = sorted(set(rots) | {0, 1, 5})
+            for rot, r4 in zip(hrots, ctx.he_rot_hoisted(c1, hrots, {r: evk for r in hrots})):
+                e4 = o.he_rot(oc, d1, rot, (p0, p1))
+                assert g.big_to_ints(r4.c0) == e4["c0"] and g.big_to_ints(r4.c1) == e4["c1"], ("he_rot_hoisted", l, rot)
             r5, e5 = ctx.he_conj(c1, evk), o.he_conj(oc, d1, (p0, p1))
             assert g.big_to_ints(r5.c0) == e5["c0"] and g.big_to_ints(r5.c1) == e5["c1"], ("he_conj", l)
             m = [rng.randrange(1 << 40) - (1 << 39) for _ in range(n)]
