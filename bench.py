@@ -325,7 +325,24 @@ def run_ours(args):
             ck(lib.gq_he_rot_dev(h, L, 3, chk.data_ptr(), chk.data_ptr() + poly, rks[3]._h, None))
             ctx.sync()
             same = bool(torch.equal(chk, hout_r[3]))
-        return {"he_rot_per_s": world * nrot / (ms_rot * 1e-3), "ms_per_rot": ms_rot / nrot, "rotations": NROT,
+        # configs[3] as the reference composes it: he_gemv with slots = 16 (baby-step/giant-step 4 x 4:
+        # 4 hoisted + 4 plain rotations, 16 he_mulpt, 15 he_add, 1 he_rs), device resident
+        import math
+        gdim = int((LOGQ + 1 + math.log2(float(1 << LOGDELTA)) + LOGN) / 59 + 1)       # he-mult.c:168
+        gpts = torch.zeros((NROT, W, n), dtype=torch.int64, device=dev)
+        gpts[:, 0, :].random_(-(1 << LOGDELTA), 1 << LOGDELTA)
+        gpts[:, 1:, :] = (gpts[:, :1, :] >> 63)                                          # sign extension
+        gout = torch.empty((2, W, n), dtype=torch.int64, device=dev)
+        ptsv = VP(*[gpts.data_ptr() + k * poly for k in range(NROT)])
+
+        def gemv_step(i):
+            ck(lib.gq_he_gemv_dev(h, L, 4, 4, gdim, gout.data_ptr(), gout.data_ptr() + poly, src.data_ptr(),
+                                  src.data_ptr() + poly, ptsv, keys, None))
+        ms_g = timed(gemv_step, reps, 2)
+        gemv = {"gemv_per_s": world * reps / (ms_g * 1e-3), "ms_per_gemv": ms_g / reps, "slots": 16, "mulpt_limbs": gdim,
+                "note": "gq_he_gemv_dev: the ciphertext arithmetic of he_gemv (src/he-algo.c:47-90) with pre-encoded "
+                        "diagonals, every intermediate ciphertext in HBM"}
+        return {"he_rot_per_s": world * nrot / (ms_rot * 1e-3), "ms_per_rot": ms_rot / nrot, "rotations": NROT, "gemv": gemv,
                 "keyswitch_limbs": D2, "note": "he_rot at l=L, 16 distinct rotation keys (384 MiB) cycled",
                 "hoisted": {"he_rot_per_s": world * reps * NROT / (ms_h * 1e-3), "ms_per_rot": ms_h / (reps * NROT),
                             "bit_exact_vs_he_rot": same,

@@ -28,6 +28,7 @@
 #include "types.h"
 #include "gpqhe.h"   /* pulls poly.h, params.h */
 
+#include <complex.h>
 #include <errno.h>
 #include <math.h>
 #include <stdio.h>
@@ -525,6 +526,64 @@ void he_subpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt)
   ct_linear(dest, src, &pt->m, NULL, 3, dest->l, __func__);
 }
 void he_neg(he_ct_t *ct) { ct_linear(ct, ct, NULL, NULL, 4, ct->l, __func__); }
+
+/* ---- he_gemv (src/he-algo.c:47-90), device resident ------------------------------------------
+ * The reference walks a baby-step/giant-step loop of he_rot / he_mulpt / he_add on host ciphertexts.
+ * Here only the encoding of the matrix diagonals (he_ecd: floating point, host) stays on the host;
+ * the ciphertext crosses once in and once out and gq_he_gemv runs the same operations in the same
+ * order on the device (baby rotations hoisted and computed once). */
+void he_gemv(he_ct_t *ct_dest, const _Complex double *A, const he_ct_t *ct, const he_evk_t *rk)
+{
+  const unsigned m = hectx.slots, n = polyctx.n, W = G.info.W, l = ct->l;
+  unsigned n1 = sqrt(m);                                                /* he-algo.c:51-54 */
+  if (m != n1 * n1) n1 = sqrt(2 * m);
+  const unsigned n2 = m / n1;
+  const size_t poly = (size_t)W * n;
+  uint64_t *s = stage((4 + (size_t)m) * poly);
+  poly_in(s, &ct->c0, W, __func__);
+  poly_in(s + poly, &ct->c1, W, __func__);
+  /* diagonal k = i*n1+j of A, pre-rotated by -i*n1 slots, encoded at scale Delta (he-algo.c:70-72) */
+  he_pt_t pt;
+  he_alloc_pt(&pt);
+  _Complex double *d = malloc(sizeof(_Complex double) * m);
+  const uint64_t **pts = malloc(sizeof(*pts) * m);
+  const gq_evk **keys = calloc(m, sizeof(*keys));
+  if (!d || !pts || !keys) die(__func__);
+  for (unsigned k = 0; k < m; k++) {
+    const unsigned shift = (k / n1) * n1;
+    for (unsigned t = 0; t < m; t++) {
+      const unsigned u = (t + m - shift % m) % m;                       /* slot after rotating by -shift */
+      d[t] = A[(size_t)u * m + (k + u) % m];
+    }
+    he_ecd(&pt, d);
+    poly_in(s + (4 + (size_t)k) * poly, &pt.m, W, __func__);
+    pts[k] = s + (4 + (size_t)k) * poly;
+  }
+  for (unsigned r = 0; r < m; r++)
+    if (r < n1 || r % n1 == 0) keys[r] = evk_dev(&rk[r]);
+  const unsigned dim = (gcry_mpi_get_nbits(hectx.q[l]) + log2(pt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
+  /* metadata: the reference's sequence of he_mulpt (he-mult.c:162-164), he_add (he-add.c:36-38)
+   * and he_rs (he-rescale.c:36-38) updates, in its loop order */
+  double nu_o = 0, B_o = 0;
+  for (unsigned i = 0; i < n2; i++) {
+    double nu_i = 0, B_i = 0;
+    for (unsigned j = 0; j < n1; j++) {
+      const double nu_t = ct->nu * pt.nu, B_t = ct->B * pt.nu;
+      if (!j) { nu_i = nu_t; B_i = B_t; }
+      else { nu_i = (nu_i >= nu_t) ? nu_i : nu_t; B_i = B_i + B_t; }
+    }
+    if (!i) { nu_o = nu_i; B_o = B_i; }
+    else { nu_o = (nu_o >= nu_i) ? nu_o : nu_i; B_o = B_o + B_i; }
+  }
+  CK(gq_he_gemv(ctx(), l, n1, n2, dim, s + 2 * poly, s + 3 * poly, s, s + poly, pts, keys));
+  ct_dest->l = l - 1;
+  ct_dest->nu = nu_o / hectx.Delta;
+  ct_dest->B = B_o / hectx.Delta + hectx.bnd.Brs;
+  poly_out(&ct_dest->c0, s + 2 * poly, W);
+  poly_out(&ct_dest->c1, s + 3 * poly, W);
+  free(d); free(pts); free(keys);
+  he_free_pt(&pt);
+}
 
 /* diagnostics for tests: coefficients marshalled in / out since load, and whether the direct
  * limb path is active */

@@ -915,6 +915,72 @@ extern "C" int gq_he_rot_hoisted_dev(gq_ctx *c, unsigned l, unsigned count, cons
   return 0;
 }
 
+// he_gemv's ciphertext arithmetic (src/he-algo.c:47-90), device resident: baby-step / giant-step
+// diagonal method with the ENCODED diagonals supplied by the caller (he_ecd is host floating point):
+//   for i < n2: inner = sum_j he_mulpt(he_rot(ct, j), pts[i*n1+j]);  he_rot(inner, i*n1);  outer += inner
+//   he_rs(outer)
+// Same operations in the same order as the reference, each reduced exactly as there, so the result is
+// bit-identical; the n1 baby rotations are computed once (the reference recomputes them for every i)
+// and hoisted.  rk is indexed by rotation amount (entries 0..n1-1 and i*n1 are used).
+extern "C" int gq_he_gemv_dev(gq_ctx *c, unsigned l, unsigned n1, unsigned n2, unsigned dim, uint64_t *c0,
+                              uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
+                              const gq_evk *const *rk, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (l == 0) GQ_FAIL("cannot go below level 0");
+  if (!c0 || !c1 || !a0 || !a1 || !pts || !rk || n1 == 0 || n2 == 0) GQ_FAIL("bad argument");
+  for (unsigned j = 0; j < n1; j++) if (!rk[j]) GQ_FAIL("missing baby-step rotation key");
+  for (unsigned i = 0; i < n2; i++) if (!rk[i * n1]) GQ_FAIL("missing giant-step rotation key");
+  for (unsigned k = 0; k < n1 * n2; k++) if (!pts[k]) GQ_FAIL("missing diagonal");
+  const size_t poly = (size_t)c->W * c->n;
+  if (ensure_slot(c, GQ_SLOT_GEMV, (2 * (size_t)n1 + 6) * poly * 8)) return 1;
+  uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_GEMV];
+  uint64_t *inner = base + 2 * (size_t)n1 * poly, *outer = inner + 2 * poly, *T = outer + 2 * poly;
+  std::vector<unsigned> rots(n1);
+  std::vector<uint64_t *> r0(n1), r1(n1);
+  for (unsigned j = 0; j < n1; j++) { rots[j] = j; r0[j] = base + 2 * (size_t)j * poly; r1[j] = r0[j] + poly; }
+  if (gq_he_rot_hoisted_dev(c, l, n1, rots.data(), r0.data(), r1.data(), a0, a1, rk, stream)) return 1;
+  for (unsigned i = 0; i < n2; i++) {
+    uint64_t *acc = (i == 0) ? outer : inner;        // the first giant step lands in `outer` directly
+    for (unsigned j = 0; j < n1; j++) {
+      uint64_t *dst = (j == 0) ? acc : T;
+      if (gq_he_mulpt_dev(c, l, dim, dst, dst + poly, r0[j], r1[j], pts[i * n1 + j], stream)) return 1;
+      if (j && linear_dev(c, l, acc, acc + poly, acc, acc + poly, T, T + poly, 0, 0, stream)) return 1;
+    }
+    if (gq_he_rot_dev(c, l, i * n1, acc, acc + poly, rk[i * n1], stream)) return 1;
+    if (i && linear_dev(c, l, outer, outer + poly, outer, outer + poly, inner, inner + poly, 0, 0, stream)) return 1;
+  }
+  if (rescale_dev(c, l, outer, outer + poly, true, stream)) return 1;
+  cudaStream_t st = pick(c, stream);
+  GQ_CUDA(cudaMemcpyAsync(c0, outer, poly * 8, cudaMemcpyDeviceToDevice, st));
+  GQ_CUDA(cudaMemcpyAsync(c1, outer + poly, poly * 8, cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
+extern "C" int gq_he_gemv(gq_ctx *c, unsigned l, unsigned n1, unsigned n2, unsigned dim, uint64_t *c0,
+                          uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
+                          const gq_evk *const *rk) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !a0 || !a1 || !pts || !rk || n1 == 0 || n2 == 0) GQ_FAIL("bad argument");
+  const size_t poly = (size_t)c->W * c->n, np = (size_t)n1 * n2;
+  if (ensure_slot(c, GQ_SLOT_PIPE, (4 + np) * poly * 8)) return 1;
+  uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_PIPE];
+  GQ_CUDA(cudaMemcpyAsync(base, a0, poly * 8, cudaMemcpyHostToDevice, c->stream));
+  GQ_CUDA(cudaMemcpyAsync(base + poly, a1, poly * 8, cudaMemcpyHostToDevice, c->stream));
+  std::vector<const uint64_t *> dp(np);
+  for (size_t k = 0; k < np; k++) {
+    if (!pts[k]) GQ_FAIL("missing diagonal");
+    uint64_t *d = base + (4 + k) * poly;
+    GQ_CUDA(cudaMemcpyAsync(d, pts[k], poly * 8, cudaMemcpyHostToDevice, c->stream));
+    dp[k] = d;
+  }
+  if (gq_he_gemv_dev(c, l, n1, n2, dim, base + 2 * poly, base + 3 * poly, base, base + poly, dp.data(), rk, nullptr))
+    return 1;
+  GQ_CUDA(cudaMemcpyAsync(c0, base + 2 * poly, poly * 8, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaMemcpyAsync(c1, base + 3 * poly, poly * 8, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
 // -------------------------------------------------------------- HE primitives (host buffers)
 // stage up to 5 big polys in, run, copy up to 2 out
 struct HostIO {

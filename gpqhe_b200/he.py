@@ -330,6 +330,32 @@ class HeContext:
             arr([o[1].ctypes.data for o in outs]), _ptr(c0), _ptr(c1), arr([rk[r]._h for r in rots])))
         return [HeCt(ct.l, o0, o1, ct.nu, ct.B) for o0, o1 in outs]
 
+    def he_gemv_encoded(self, ct: HeCt, pts, n1: int, n2: int, rk) -> HeCt:
+        """The ciphertext arithmetic of he_gemv(ct_dest, A, ct, rk) (src/he-algo.c:47-90) with the
+        diagonals already encoded: pts[i*n1+j] is the HePt of zrotdiag(A, i*n1+j, -i*n1).
+        Metadata follows the reference's sequence of he_mulpt / he_add / he_rs updates."""
+        pts = list(pts)
+        if len(pts) != n1 * n2:
+            raise GpqheError("he_gemv: need n1*n2 encoded diagonals")
+        dim = self.mulpt_dim(ct.l, pts[0].nu)
+        c0 = np.empty((self.W, self.n), dtype=np.uint64)
+        c1 = np.empty_like(c0)
+        hold = [_c(p.m) for p in pts]
+        nk = n1 * n2
+        keys = (C.c_void_p * nk)(*[(rk[r]._h if (r < n1 or r % n1 == 0) else None) for r in range(nk)])
+        capi.check(self._lib, self._lib.gq_he_gemv(
+            self._h, ct.l, n1, n2, dim, _ptr(c0), _ptr(c1), _ptr(_c(ct.c0)), _ptr(_c(ct.c1)),
+            (C.c_void_p * nk)(*[h.ctypes.data for h in hold]), keys))
+        nu_o = B_o = 0.0
+        for i in range(n2):
+            nu_i = B_i = 0.0
+            for j in range(n1):
+                pt = pts[i * n1 + j]
+                nu_t, B_t = ct.nu * pt.nu, ct.B * pt.nu                     # he-mult.c:162-164
+                nu_i, B_i = (nu_t, B_t) if j == 0 else (max(nu_i, nu_t), B_i + B_t)   # he-add.c:36-38
+            nu_o, B_o = (nu_i, B_i) if i == 0 else (max(nu_o, nu_i), B_o + B_i)
+        return HeCt(ct.l - 1, c0, c1, nu_o / float(self.Delta), B_o / float(self.Delta) + self.Brs)
+
     def he_mul_rs(self, ct1: HeCt, ct2: HeCt, rlk: HeEvk) -> HeCt:
         """he_mul then he_rs on the product, one crossing (gq_he_mul_rs)."""
         return self.he_mul_batch([(ct1, ct2)], rlk, rescale=True, fused_single=True)[0]

@@ -145,6 +145,14 @@ int gq_he_moddown(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1);
 int gq_he_rot_hoisted(gq_ctx *ctx, unsigned l, unsigned count, const unsigned *rots,
                       uint64_t *const *c0_out, uint64_t *const *c1_out, const uint64_t *c0,
                       const uint64_t *c1, const gq_evk *const *rk);
+/* the ciphertext arithmetic of he_gemv (src/he-algo.c:47-90): baby-step/giant-step diagonal method,
+   slots = n1*n2, with the diagonals already encoded by the caller (pts[i*n1+j] = he_ecd of
+   zrotdiag(A, i*n1+j, -i*n1), uint64_t[W][n] each; `dim` = the he_mulpt limb count for their nu,
+   src/he-mult.c:168).  rk[r] = key of rotation r (r < n1 and r = i*n1 are used).  Result at level
+   l-1 (the closing he_rs is included).  One crossing, every intermediate ciphertext stays in HBM. */
+int gq_he_gemv(gq_ctx *ctx, unsigned l, unsigned n1, unsigned n2, unsigned dim, uint64_t *c0, uint64_t *c1,
+               const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
+               const gq_evk *const *rk);
 /* he_add / he_sub (src/he-add.c:32-76), he_addpt / he_subpt (:79-120: only c0 meets the plaintext,
    c1 is reduced), he_neg (:123-140, in place): out = smod_{q_l}(a op b); outputs may alias inputs */
 int gq_he_add(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
@@ -185,6 +193,9 @@ int gq_he_conj_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const gq
 int gq_he_rot_hoisted_dev(gq_ctx *ctx, unsigned l, unsigned count, const unsigned *rots,
                           uint64_t *const *c0_out, uint64_t *const *c1_out, const uint64_t *c0,
                           const uint64_t *c1, const gq_evk *const *rk, void *stream);
+int gq_he_gemv_dev(gq_ctx *ctx, unsigned l, unsigned n1, unsigned n2, unsigned dim, uint64_t *c0,
+                   uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
+                   const gq_evk *const *rk, void *stream);
 int gq_he_add_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
                   const uint64_t *b0, const uint64_t *b1, void *stream);
 int gq_he_sub_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,

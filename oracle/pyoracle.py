@@ -430,6 +430,23 @@ def he_neg(ctx: Ctx, ct: dict) -> dict:
     return {"l": l, "c0": [mpi_smod(-x, q, qh) for x in ct["c0"]], "c1": [mpi_smod(-x, q, qh) for x in ct["c1"]]}
 
 
+def he_gemv_encoded(ctx: Ctx, ct: dict, pts: list, dim: int, n1: int, n2: int, rk) -> dict:
+    """src/he-algo.c:47-90 with the encoded diagonals given: pts[i*n1+j] = coefficients of
+    he_ecd(zrotdiag(A, i*n1+j, -i*n1)); rk[r] = (p0, p1) of rotation r.  The same loop, the same
+    order of he_rot / he_mulpt / he_add / he_rs as the reference."""
+    outer = None
+    for i in range(n2):
+        shift = i * n1
+        inner = None
+        for j in range(n1):
+            ct_rot = he_rot(ctx, ct, j, rk[j])
+            ct_rot = he_mulpt(ctx, ct_rot, pts[shift + j], dim)
+            inner = ct_rot if inner is None else he_add(ctx, inner, ct_rot)
+        inner = he_rot(ctx, inner, shift, rk[shift])
+        outer = inner if outer is None else he_add(ctx, outer, inner)
+    return he_rs(ctx, outer)
+
+
 # --------------------------------------------------------------------------- #
 # packed-word interchange format used at the C-ABI (include/gpqhe_b200.h):
 # word-major two's complement, words[w, i] = bits 64w..64w+63 of coefficient i

@@ -48,6 +48,7 @@ void gpqhe_ref_he_sub(he_ct_t *ct, const he_ct_t *ct1, const he_ct_t *ct2);
 void gpqhe_ref_he_addpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt);
 void gpqhe_ref_he_subpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt);
 void gpqhe_ref_he_neg(he_ct_t *ct);
+void gpqhe_ref_he_gemv(he_ct_t *ct_dest, const _Complex double *A, const he_ct_t *ct, const he_evk_t *rk);
 void gpqhe_dropin_stats(unsigned long long *in, unsigned long long *out, int *fast_mpi);
 
 static unsigned npass, nfail;
@@ -196,6 +197,19 @@ int main(int argc, char **argv)
   report("he_addpt", eq_ct(&g, &r));
   he_subpt(&g, &g, &pt2); gpqhe_ref_he_subpt(&r, &r, &pt2);
   report("he_subpt (in place)", eq_ct(&g, &r));
+
+  /* ---- he_gemv: device-resident loop vs the reference's host loop over the same primitives */
+  if (nrot >= slots) {
+    _Complex double *A = malloc(sizeof(_Complex double) * slots * slots);
+    for (unsigned i = 0; i < slots * slots; i++)
+      A[i] = ((double)(rnd() % 2001) - 1000.0) / 1000.0 + (((double)(rnd() % 2001) - 1000.0) / 1000.0) * I;
+    he_gemv(&g, A, &c1, rk); gpqhe_ref_he_gemv(&r, A, &c1, rk);
+    report("he_gemv", eq_ct(&g, &r));
+    he_copy_ct(&g, &c2); he_copy_ct(&r, &c2);
+    he_gemv(&g, A, &g, rk); gpqhe_ref_he_gemv(&r, A, &r, rk);     /* dest aliases src (he_sum does this) */
+    report("he_gemv (in place)", eq_ct(&g, &r));
+    free(A);
+  }
 
   unsigned long long in = 0, out = 0;
   gpqhe_dropin_stats(&in, &out, NULL);

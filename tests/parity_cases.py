@@ -250,3 +250,28 @@ def check_crt_edges(lib_path, logn=5, q=1 << 438, Delta=1 << 50, logqub=438):
         assert ctx.crt_fixups > before, "edge values must take the exact list path (key switch)"
     finally:
         ctx.close()
+
+
+def check_gemv(lib_path, logn, q, Delta, n1=2, n2=2, logqub=0, seed=3):
+    """Device-resident he_gemv (baby-step/giant-step, hoisted baby rotations) vs the oracle's
+    restatement of the reference loop, distinct rotation keys, at the top level."""
+    rng = random.Random(seed)
+    slots = n1 * n2
+    ctx = g.HeContext(logn, q, slots, Delta, lib_path=lib_path, logqub=logqub)
+    oc = o.Ctx(logn, q, slots, Delta, logqub=logqub or None)
+    try:
+        n, W, l = ctx.n, ctx.W, ctx.L
+        ql = oc.ql[l]
+        a0, a1 = rpoly(rng, ql, n), rpoly(rng, ql, n)
+        need = sorted(set(range(n1)) | {i * n1 for i in range(n2)})
+        keys = {r: (rlimbs(rng, oc.primes, n, oc.dimevk), rlimbs(rng, oc.primes, n, oc.dimevk)) for r in need}
+        dkeys = {r: ctx.genevk(*keys[r]) for r in need}
+        nu = float(Delta)
+        ms = [[rng.randrange(2 * Delta) - Delta for _ in range(n)] for _ in range(slots)]
+        pts = [g.HePt(g.ints_to_big(m, W), nu=nu) for m in ms]
+        got = ctx.he_gemv_encoded(g.HeCt(l, g.ints_to_big(a0, W), g.ints_to_big(a1, W)), pts, n1, n2, dkeys)
+        want = o.he_gemv_encoded(oc, {"l": l, "c0": a0, "c1": a1}, ms, ctx.mulpt_dim(l, nu), n1, n2, keys)
+        assert got.l == want["l"]
+        assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], "he_gemv"
+    finally:
+        ctx.close()

@@ -65,7 +65,7 @@ def _verdicts(out):
     return re.findall(r"\b(OK|FAILED|PASSED)\]", clean) + re.findall(r"(\d+/\d+) subtask", clean)
 
 
-@pytest.mark.parametrize("args", [("7", "120", "4", "40"), ("6", "438", "4", "50"), ("8", "200", "8", "40")])
+@pytest.mark.parametrize("args", [("7", "120", "4", "40", "4"), ("6", "438", "4", "50"), ("8", "200", "8", "40")])
 def test_dropin_diff_emulated(emul_env, args):
     rc, out = _run([os.path.join(BUILD, "dropin_diff"), *args], env=emul_env)
     assert rc == 0 and "PASS" in out, out[-2000:]

@@ -105,3 +105,8 @@ def test_poly_mul_lazy_ntt_two_kernel_path(emul_lib, logn):
 
 def test_crt_edge_values_take_exact_path(emul_lib):
     pc.check_crt_edges(emul_lib)
+
+
+@pytest.mark.parametrize("logn,q,Delta,n1,n2", [(5, 1 << 120, 1 << 40, 2, 2), (5, 1 << 438, 1 << 50, 4, 2)])
+def test_gemv_device_resident(emul_lib, logn, q, Delta, n1, n2):
+    pc.check_gemv(emul_lib, logn, q, Delta, n1, n2, logqub=q.bit_length() - 1)

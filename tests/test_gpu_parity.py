@@ -98,3 +98,8 @@ def test_full_size_n16_he_mul_rs_rot(real_lib):
 def test_crt_edge_values_take_exact_path(real_lib):
     pc.check_crt_edges(real_lib)
     pc.check_crt_edges(real_lib, logn=12, q=1 << 109, Delta=1 << 30, logqub=109)
+
+
+def test_gemv_device_resident(real_lib):
+    """he_gemv with slots = 16 (n1 = n2 = 4, the KAT's shape) at N=2^12."""
+    pc.check_gemv(real_lib, 12, 1 << 109, 1 << 30, 4, 4)
