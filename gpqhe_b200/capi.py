@@ -44,6 +44,11 @@ SIGNATURES = {
     "gq_ctx_launch_count": (C.c_ulonglong, [vp]),
     "gq_ctx_stream": (vp, [vp]),
     "gq_ctx_crt_fixups": (C.c_longlong, [vp]),
+    "gq_ctx_set_lanes": (C.c_int, [vp, C.c_uint]),
+    "gq_ctx_lane_count": (C.c_uint, [vp]),
+    "gq_ctx_lane": (vp, [vp, C.c_uint]),
+    "gq_ctx_lanes_fork": (C.c_int, [vp]),
+    "gq_ctx_lanes_join": (C.c_int, [vp]),
     "gq_host_alloc": (C.c_int, [C.POINTER(vp), C.c_size_t]),
     "gq_host_free": (None, [vp]),
     "gq_ntt": (C.c_int, [vp, C.c_uint, vp]),

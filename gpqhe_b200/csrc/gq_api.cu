@@ -361,18 +361,86 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
 extern "C" void gq_ctx_destroy(gq_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  for (gq_ctx *l : c->lanes) gq_ctx_destroy(l);
+  c->lanes.clear();
   if (c->stream) cudaStreamSynchronize(c->stream);
-  cudaFree(c->d_primes); cudaFree(c->d_tw_fwd); cudaFree(c->d_tw_inv); cudaFree(c->d_tw_inv_last);
-  cudaFree(c->d_pow64); cudaFree(c->d_t1sh); cudaFree(c->d_pow32); cudaFree(c->d_onesh); cudaFree(c->d_Pinv); cudaFree(c->d_Pwords);
+  if (!c->parent) {     // a lane shares the tables of its parent
+    cudaFree(c->d_primes); cudaFree(c->d_tw_fwd); cudaFree(c->d_tw_inv); cudaFree(c->d_tw_inv_last);
+    cudaFree(c->d_pow64); cudaFree(c->d_t1sh); cudaFree(c->d_pow32); cudaFree(c->d_onesh); cudaFree(c->d_Pinv); cudaFree(c->d_Pwords);
+    for (auto &b : c->basis) cudaFree(b.blob);
+    for (auto &m : c->qmod) cudaFree(m.blob);
+  }
   cudaFree(c->d_adhoc); cudaFree(c->d_fix);
-  for (auto &b : c->basis) cudaFree(b.blob);
-  for (auto &m : c->qmod) cudaFree(m.blob);
   for (int s = 0; s < GQ_SLOT_COUNT; s++) cudaFree(c->slot[s]);
   for (auto &e : c->ev_pipe) if (e) cudaEventDestroy(e);
+  for (auto &e : c->ev_batch) if (e) cudaEventDestroy(e);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->s_in) cudaStreamDestroy(c->s_in);
   if (c->s_out) cudaStreamDestroy(c->s_out);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
+}
+
+// ------------------------------------------------------------------------------- lanes
+static int lane_create(gq_ctx *c, gq_ctx **out) {
+  const size_t n = c->n;
+  gq_ctx *l = new gq_ctx(*c);        // tables, level moduli, CRT bases: shared device pointers
+  l->parent = c;
+  l->lanes.clear();
+  l->stream = nullptr; l->s_in = nullptr; l->s_out = nullptr;
+  for (auto &e : l->ev_pipe) e = nullptr;
+  l->ev_batch.clear();
+  l->ev_fork = nullptr; l->ev_join = nullptr;
+  for (int s = 0; s < GQ_SLOT_COUNT; s++) { l->slot[s] = nullptr; l->slot_bytes[s] = 0; }
+  l->d_adhoc = nullptr; l->d_fix = nullptr;
+  l->launches = 0;
+  if (cudaStreamCreateWithFlags(&l->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&l->ev_join, cudaEventDisableTiming) != cudaSuccess ||
+      cudaMalloc((void **)&l->d_adhoc, 2 * GQ_MAX_W * sizeof(uint64_t)) != cudaSuccess ||
+      cudaMalloc((void **)&l->d_fix, (4 + 4 * n) * sizeof(int)) != cudaSuccess ||
+      cudaMemset(l->d_fix, 0, 4 * sizeof(int)) != cudaSuccess) {
+    gq_ctx_destroy(l);
+    GQ_FAIL("cannot allocate a compute lane");
+  }
+  *out = l;
+  return 0;
+}
+extern "C" int gq_ctx_set_lanes(gq_ctx *c, unsigned lanes) {
+  if (!c || c->parent) GQ_FAIL("not a root context");
+  if (lanes < 1 || lanes > 8) GQ_FAIL("lanes must be in [1,8]");
+  GQ_CUDA(cudaSetDevice(c->device));
+  if (!c->ev_fork) {
+    GQ_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    GQ_CUDA(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
+  }
+  while (c->lanes.size() + 1 < lanes) {
+    gq_ctx *l = nullptr;
+    if (lane_create(c, &l)) return 1;
+    c->lanes.push_back(l);
+  }
+  return 0;
+}
+extern "C" unsigned gq_ctx_lane_count(const gq_ctx *c) { return c ? (unsigned)c->lanes.size() + 1 : 0; }
+extern "C" gq_ctx *gq_ctx_lane(gq_ctx *c, unsigned i) {
+  if (!c) return nullptr;
+  if (i == 0) return c;
+  return i <= c->lanes.size() ? c->lanes[i - 1] : nullptr;
+}
+extern "C" int gq_ctx_lanes_fork(gq_ctx *c) {
+  if (!c || c->parent) GQ_FAIL("not a root context");
+  if (c->lanes.empty()) return 0;
+  GQ_CUDA(cudaEventRecord(c->ev_fork, c->stream));
+  for (gq_ctx *l : c->lanes) GQ_CUDA(cudaStreamWaitEvent(l->stream, c->ev_fork, 0));
+  return 0;
+}
+extern "C" int gq_ctx_lanes_join(gq_ctx *c) {
+  if (!c || c->parent) GQ_FAIL("not a root context");
+  for (gq_ctx *l : c->lanes) {
+    GQ_CUDA(cudaEventRecord(l->ev_join, l->stream));
+    GQ_CUDA(cudaStreamWaitEvent(c->stream, l->ev_join, 0));
+  }
+  return 0;
 }
 
 // ------------------------------------------------------------------------------ queries
@@ -408,16 +476,28 @@ extern "C" int gq_ctx_dims(const gq_ctx *c, unsigned l, unsigned *dt, unsigned *
 }
 extern "C" int gq_ctx_sync(gq_ctx *c) {
   if (!c) GQ_FAIL("null context");
+  for (gq_ctx *l : c->lanes) GQ_CUDA(cudaStreamSynchronize(l->stream));
   GQ_CUDA(cudaStreamSynchronize(c->stream));
   return 0;
 }
-extern "C" unsigned long long gq_ctx_launch_count(const gq_ctx *c) { return c ? c->launches : 0; }
+extern "C" unsigned long long gq_ctx_launch_count(const gq_ctx *c) {
+  if (!c) return 0;
+  unsigned long long t = c->launches;
+  for (const gq_ctx *l : c->lanes) t += l->launches;
+  return t;
+}
 extern "C" long long gq_ctx_crt_fixups(gq_ctx *c) {
   if (!c || !c->d_fix) return -1;
   int v[2] = {0, 0};
   if (cudaStreamSynchronize(c->stream) != cudaSuccess) return -1;
   if (cudaMemcpy(v, c->d_fix, sizeof v, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
-  return v[1];
+  long long t = v[1];
+  for (gq_ctx *l : c->lanes) {
+    const long long u = gq_ctx_crt_fixups(l);
+    if (u < 0) return -1;
+    t += u;
+  }
+  return t;
 }
 extern "C" void *gq_ctx_stream(gq_ctx *c) { return c ? (void *)c->stream : nullptr; }
 extern "C" int gq_host_alloc(void **p, size_t bytes) {
@@ -1048,34 +1128,52 @@ extern "C" int gq_he_mul_batch(gq_ctx *c, unsigned l, unsigned count, uint64_t *
     if (!c0[i] || !c1[i] || !a0[i] || !a1[i] || !b0[i] || !b1[i]) GQ_FAIL("null polynomial pointer");
   if (count == 0) return 0;
   GQ_CUDA(cudaSetDevice(c->device));
+  if (c->parent) GQ_FAIL("not a root context");
   if (pipe_init(c)) return 1;
+  // products go round-robin over the compute lanes (3 unless the caller chose with gq_ctx_set_lanes or
+  // GPQHE_B200_LANES); 2*K staging buffers, so buffer b always belongs to lane b % K and a lane never
+  // waits for a buffer that another lane still computes on
+  if (c->lanes.empty()) {
+    const char *e = getenv("GPQHE_B200_LANES");
+    unsigned want = e ? (unsigned)atoi(e) : 3u;
+    if (want < 1 || want > 8) want = 3;
+    if (want > count) want = count;
+    if (want > 1 && gq_ctx_set_lanes(c, want)) return 1;
+  }
+  const unsigned K = (unsigned)c->lanes.size() + 1, NB = 2 * K;
   const size_t poly = (size_t)c->W * c->n;
-  if (ensure_slot(c, GQ_SLOT_PIPE, 12 * poly * 8)) return 1;
+  if (ensure_slot(c, GQ_SLOT_PIPE, (size_t)NB * 6 * poly * 8)) return 1;
+  while (c->ev_batch.size() < 4 * (size_t)NB) {
+    cudaEvent_t e = nullptr;
+    GQ_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    c->ev_batch.push_back(e);
+  }
   uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_PIPE];
-  cudaEvent_t *ev = c->ev_pipe;      // [4*k + {0: in_ready, 1: in_free, 2: out_ready, 3: out_free}]
+  cudaEvent_t *ev = c->ev_batch.data();   // [4*b + {0: in_ready, 1: in_free, 2: out_ready, 3: out_free}]
   int rc = 0;
   for (unsigned i = 0; i < count && !rc; i++) {
-    const int k = (int)(i & 1);
-    uint64_t *in = base + (size_t)k * 6 * poly, *out = in + 4 * poly;
+    const unsigned bf = i % NB;
+    gq_ctx *ln = gq_ctx_lane(c, i % K);
+    uint64_t *in = base + (size_t)bf * 6 * poly, *out = in + 4 * poly;
     const uint64_t *src[4] = {a0[i], a1[i], b0[i], b1[i]};
-    if (i >= 2) GQ_CUDA(cudaStreamWaitEvent(c->s_in, ev[4 * k + 1], 0));
+    if (i >= NB) GQ_CUDA(cudaStreamWaitEvent(c->s_in, ev[4 * bf + 1], 0));
     for (int j = 0; j < 4; j++)
       GQ_CUDA(cudaMemcpyAsync(in + j * poly, src[j], poly * 8, cudaMemcpyHostToDevice, c->s_in));
-    GQ_CUDA(cudaEventRecord(ev[4 * k + 0], c->s_in));
-    GQ_CUDA(cudaStreamWaitEvent(c->stream, ev[4 * k + 0], 0));
-    if (i >= 2) GQ_CUDA(cudaStreamWaitEvent(c->stream, ev[4 * k + 3], 0));
-    rc = gq_he_mul_dev(c, l, out, out + poly, in, in + poly, in + 2 * poly, in + 3 * poly, rlk, nullptr);
-    if (!rc && rescale) rc = rescale_dev(c, l, out, out + poly, true, nullptr);
+    GQ_CUDA(cudaEventRecord(ev[4 * bf + 0], c->s_in));
+    GQ_CUDA(cudaStreamWaitEvent(ln->stream, ev[4 * bf + 0], 0));
+    if (i >= NB) GQ_CUDA(cudaStreamWaitEvent(ln->stream, ev[4 * bf + 3], 0));
+    rc = gq_he_mul_dev(ln, l, out, out + poly, in, in + poly, in + 2 * poly, in + 3 * poly, rlk, nullptr);
+    if (!rc && rescale) rc = rescale_dev(ln, l, out, out + poly, true, nullptr);
     if (rc) break;
-    GQ_CUDA(cudaEventRecord(ev[4 * k + 1], c->stream));
-    GQ_CUDA(cudaEventRecord(ev[4 * k + 2], c->stream));
-    GQ_CUDA(cudaStreamWaitEvent(c->s_out, ev[4 * k + 2], 0));
+    GQ_CUDA(cudaEventRecord(ev[4 * bf + 1], ln->stream));
+    GQ_CUDA(cudaEventRecord(ev[4 * bf + 2], ln->stream));
+    GQ_CUDA(cudaStreamWaitEvent(c->s_out, ev[4 * bf + 2], 0));
     GQ_CUDA(cudaMemcpyAsync(c0[i], out, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
     GQ_CUDA(cudaMemcpyAsync(c1[i], out + poly, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
-    GQ_CUDA(cudaEventRecord(ev[4 * k + 3], c->s_out));
+    GQ_CUDA(cudaEventRecord(ev[4 * bf + 3], c->s_out));
   }
   cudaStreamSynchronize(c->s_in);
-  cudaStreamSynchronize(c->stream);
+  for (unsigned k = 0; k < K; k++) cudaStreamSynchronize(gq_ctx_lane(c, k)->stream);
   GQ_CUDA(cudaStreamSynchronize(c->s_out));
   return rc;
 }

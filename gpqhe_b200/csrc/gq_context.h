@@ -49,6 +49,14 @@ struct gq_ctx {
   cudaStream_t s_in = nullptr, s_out = nullptr;
   cudaEvent_t ev_pipe[8] = {};       // {in_ready, in_free, out_ready, out_free} x 2 buffers
   unsigned long long launches = 0;
+  // compute lanes (gq_ctx_set_lanes): lane 0 is this context; lanes[k-1] (k >= 1) are shadow
+  // contexts that share every device table above (parent != null: not owned) and own a stream,
+  // the scratch slots, d_fix and d_adhoc, so that independent ciphertext operations overlap
+  gq_ctx *parent = nullptr;
+  std::vector<gq_ctx *> lanes;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // staging of the batched host entry points when lanes are in use
+  std::vector<cudaEvent_t> ev_batch;
   bool lazy_ntt = true;          // internal pipelines use gq_ntt_lazy.cu when every prime allows it
 
   GqNttTables ntt_tables() const {

@@ -185,6 +185,21 @@ class HeContext:
     def sync(self):
         capi.check(self._lib, self._lib.gq_ctx_sync(self._h))
 
+    # ---- compute lanes (gq_ctx_set_lanes: independent operations overlap on one GPU) ----
+    def set_lanes(self, lanes: int):
+        capi.check(self._lib, self._lib.gq_ctx_set_lanes(self._h, lanes))
+
+    @property
+    def lanes(self) -> int:
+        return int(self._lib.gq_ctx_lane_count(self._h))
+
+    def lane(self, i: int) -> C.c_void_p:
+        """handle of lane i for the *_dev entry points (lane 0 is the context itself)"""
+        h = self._lib.gq_ctx_lane(self._h, i)
+        if not h:
+            raise GpqheError(f"lane {i} does not exist (lanes={self.lanes})")
+        return C.c_void_p(h)
+
     # ---- limb layer ---------------------------------------------------------------
     def ntt(self, a: np.ndarray, limb: int) -> np.ndarray:
         """ntt(a, rns) (src/ntt.c:37-52); `limb` = index of the rns list node."""

@@ -86,6 +86,23 @@ void *gq_ctx_stream(gq_ctx *ctx); /* the context's cudaStream_t */
  * (values within 2^-56 of the +P/2 edge; diagnostics for the edge-case tests), -1 on error */
 long long gq_ctx_crt_fixups(gq_ctx *ctx);
 
+/* ---- compute lanes (no reference counterpart: the reference is single-threaded and runs one
+ * operation at a time, src/config.h:59 GPQHE_NUM_THREAD is unused) --------------------------
+ * One he_mul at N=2^16 does not fill 148 SMs in every stage (kernel tails, < 1 wave in the CRT
+ * stages), so independent ciphertext operations are run on `lanes` streams of ONE GPU.  A lane is a
+ * context handle that shares every table and key of `ctx` and owns a stream and the scratch, and is
+ * accepted by every *_dev entry point (keys created on `ctx` are valid on its lanes).
+ *   gq_ctx_set_lanes   lanes >= 1 (1..8); lane 0 is `ctx` itself; grows only
+ *   gq_ctx_lane        handle of lane i (NULL if i >= lanes); owned by `ctx`
+ *   gq_ctx_lanes_fork  every lane waits for the work enqueued so far on ctx's stream
+ *   gq_ctx_lanes_join  ctx's stream waits for the work enqueued so far on every lane
+ * gq_he_mul_batch distributes its products over the lanes (3 by default). */
+int gq_ctx_set_lanes(gq_ctx *ctx, unsigned lanes);
+unsigned gq_ctx_lane_count(const gq_ctx *ctx);
+gq_ctx *gq_ctx_lane(gq_ctx *ctx, unsigned i);
+int gq_ctx_lanes_fork(gq_ctx *ctx);
+int gq_ctx_lanes_join(gq_ctx *ctx);
+
 /* pinned host memory for callers that want fast copies */
 int gq_host_alloc(void **p, size_t bytes);
 void gq_host_free(void *p);

@@ -88,7 +88,7 @@ typedef struct gq_emul_event *cudaEvent_t;
 enum cudaMemcpyKind { cudaMemcpyHostToHost = 0, cudaMemcpyHostToDevice = 1,
                       cudaMemcpyDeviceToHost = 2, cudaMemcpyDeviceToDevice = 3,
                       cudaMemcpyDefault = 4 };
-enum { cudaStreamNonBlocking = 1, cudaEventDefault = 0, cudaHostAllocDefault = 0 };
+enum { cudaStreamNonBlocking = 1, cudaEventDefault = 0, cudaEventDisableTiming = 2, cudaHostAllocDefault = 0 };
 
 cudaError_t cudaMalloc(void **p, size_t n);
 cudaError_t cudaFree(void *p);
@@ -109,6 +109,7 @@ cudaError_t cudaSetDevice(int d);
 cudaError_t cudaGetDevice(int *d);
 cudaError_t cudaGetDeviceCount(int *n);
 cudaError_t cudaEventCreate(cudaEvent_t *e);
+static inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t *e, unsigned) { return cudaEventCreate(e); }
 cudaError_t cudaEventDestroy(cudaEvent_t e);
 cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s);
 cudaError_t cudaEventSynchronize(cudaEvent_t e);

@@ -159,8 +159,10 @@ def check_he_vs_oracle(lib_path, logn, q, slots, Delta, seed=0, levels=None, rot
             rf = ctx.he_mul_rs(c1, c2, evk)
             assert rf.l == e2["l"] and g.big_to_ints(rf.c0) == e2["c0"] and g.big_to_ints(rf.c1) == e2["c1"], ("he_mul_rs", l)
             eb = o.he_rs(oc, o.he_mul(oc, d2, d2, (p0, p1)))
-            for resc, want in ((True, [e2, eb, e2]), (False, [e, None, e])):
-                rb = ctx.he_mul_batch([(c1, c2), (c2, c2), (c2, c1)], evk, rescale=resc)
+            # 7 products over 3 compute lanes and 6 staging buffers: lanes and buffers are both reused
+            for resc, want in ((True, [e2, eb, e2] * 2 + [e2]), (False, [e, None, e] * 2 + [e])):
+                rb = ctx.he_mul_batch([(c1, c2), (c2, c2), (c2, c1)] * 2 + [(c1, c2)], evk, rescale=resc)
+                assert ctx.lanes == 3
                 for got_ct, w in zip(rb, want):
                     if w is not None:
                         assert got_ct.l == w["l"] and g.big_to_ints(got_ct.c0) == w["c0"] and \
