@@ -322,6 +322,70 @@ def run_ours(args):
            "kernels": "lazy (internal pipelines); exact_* = the ntt()-semantics kernels"}
     del dn
 
+    # ---- every stage kernel of one he_mul+he_rs, timed alone in the shapes the op uses (gq_stage_* = the
+    # kernels the op launches), against both rooflines: algorithmic bytes / HBM peak and 32x32-multiply
+    # work / measured IMAD.WIDE peak.  Multiplies per unit are the algorithmic counts of DESIGN.md section 4
+    # (a 32x32->64 product = 1, a low-half 32x32 product = 0.5).
+    def stage_table():
+        VP = C.c_void_p
+        b = dpool.data_ptr()
+        xc = torch.empty((4, D1, n), dtype=torch.int64, device=dev)
+        y = torch.empty((3, D1, n), dtype=torch.int64, device=dev)
+        d = torch.empty((3, W, n), dtype=torch.int64, device=dev)
+        x2 = torch.empty((1, D2, n), dtype=torch.int64, device=dev)
+        y2 = torch.empty((2, D2, n), dtype=torch.int64, device=dev)
+        o = torch.empty((2, W, n), dtype=torch.int64, device=dev)
+        in4 = (VP * 4)(*[b + j * poly for j in range(4)])
+        in1 = (VP * 1)(d[2].data_ptr())
+        out3 = (VP * 3)(*[d[j].data_ptr() for j in range(3)])
+        stages = [
+            ("decompose x4 -> D1", "k_decompose32<7>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D1, 4, in4, W, n, xc.data_ptr(), None)),
+             4 * D1 * n, 42.0, 4 * W * n * 8 + 4 * D1 * n * 8),
+            ("forward NTT, 4 x D1 limb-polys", "k_nttl_fwd_strided<4> + k_nttl_fwd_tile<12>", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D1, 4, xc.data_ptr(), 0, None)),
+             4 * D1 * (n // 2) * LOGN, 8.0, 2 * 2 * 4 * D1 * n * 8),
+            ("tensor product", "k_tensor_pm", lambda i: ck(lib.gq_stage_tensor_dev(h, 0, D1, y.data_ptr(), xc.data_ptr(), None)),
+             D1 * n, 4 * 7.0, 7 * D1 * n * 8),
+            ("inverse NTT, 3 x D1", "k_nttl_inv_tile<12> + k_nttl_inv_strided<4>", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D1, 3, y.data_ptr(), 1, None)),
+             3 * D1 * (n // 2) * LOGN, 8.0, 2 * 2 * 3 * D1 * n * 8),
+            ("reconstruct x3 over D1", "k_reconstruct_fast<7>", lambda i: ck(lib.gq_stage_reconstruct_dev(h, D1, L, 3, y.data_ptr(), out3, n, None)),
+             3 * n, D1 * 38.0 + 4 * W, 3 * D1 * n * 8 + 3 * W * n * 8),
+            ("decompose d2 -> D2", "k_decompose32<7>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D2, 1, in1, W, n, x2.data_ptr(), None)),
+             D2 * n, 42.0, W * n * 8 + D2 * n * 8),
+            ("forward NTT, D2", "k_nttl_fwd_*", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D2, 1, x2.data_ptr(), 0, None)),
+             D2 * (n // 2) * LOGN, 8.0, 2 * 2 * D2 * n * 8),
+            ("multiply by rlk", "k_mul_evk_pm", lambda i: ck(lib.gq_stage_mul_evk_dev(h, 0, D2, y2.data_ptr(), x2.data_ptr(), evk._h, None)),
+             D2 * n, 2 * 7.0, 5 * D2 * n * 8),
+            ("inverse NTT, 2 x D2", "k_nttl_inv_*", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D2, 2, y2.data_ptr(), 1, None)),
+             2 * D2 * (n // 2) * LOGN, 8.0, 2 * 2 * 2 * D2 * n * 8),
+            ("key-switch epilogue", "k_ks_epilogue_fast<8>", lambda i: ck(lib.gq_stage_ks_epilogue_dev(h, L, y2.data_ptr(), d[0].data_ptr(), d[1].data_ptr(), o[0].data_ptr(), o[1].data_ptr(), n, None)),
+             2 * n, D2 * 42.0 + ctx.dim * 40.0 + 128 + 64, 2 * D2 * n * 8 + 4 * W * n * 8),
+            ("rescale", "k_rescale_pow2", lambda i: ck(lib.gq_stage_rescale_dev(h, L, o[0].data_ptr(), o[1].data_ptr(), 1, n, None)),
+             2 * n, 0.0, 4 * W * n * 8),
+        ]
+        with torch.cuda.stream(ext):
+            for st in stages:          # one pass in order so that every stage sees real data
+                st[2](0)
+        barrier()
+        rows, total = [], 0.0
+        reps = 20
+        for name, kern, fn, units, mulw, nbytes in stages:
+            t = timed(fn, reps, 3) / reps
+            total += t
+            fi = units * mulw / (t * 1e-3) / mw_peak.value if mw_peak.value else None
+            fh = nbytes / (t * 1e-3) / 1e9 / hbm
+            rows.append({"stage": name, "kernel": kern, "us": t * 1e3, "units": units, "mul32_per_unit": mulw,
+                         "algorithmic_bytes": nbytes, "frac_int_pipe": fi, "frac_hbm": fh,
+                         "bound": "int" if (fi or 0) >= fh else "hbm"})
+        for r in rows:
+            r["share"] = r["us"] / (total * 1e3)
+        return {"rows": rows, "sum_us": total * 1e3,
+                "peaks": {"madwide_Gops": mw_peak.value / 1e9, "hbm_GBps": hbm},
+                "note": "each stage timed alone on one stream (20 launches back to back, L2-warm as inside the op); "
+                        "frac_int_pipe = 32x32-multiply work / measured IMAD.WIDE peak of this GPU (gq_bench_intpipe), "
+                        "frac_hbm = algorithmic bytes / measured HBM copy peak; the NTT rows use 8 multiply-equivalents "
+                        "per butterfly (6 wide + 4 low)"}
+    stages = stage_table()
+
     # ---- configs[3]: rotation sweep, he_rot = Galois permutation + key switch, rot = 0..NROT-1 with
     # one switching key per rotation (the he_gemv workload: slots=16 rotations)
     def rotation_sweep(NROT=16):
@@ -552,7 +616,7 @@ def run_ours(args):
                            "l2": f"inputs rotate over a pool of {POOL} ciphertext pairs ({POOL * 4 * poly / 2**20:.0f} MiB) and the "
                                  f"per-op scratch + key is {ws_mib:.0f} MiB: working set > 126 MB L2"},
                 "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "ntt": ntt,
-                "rot_sweep": rot_sweep, "sharded": sharded, "cpu_baseline": cpu,
+                "stages": stages, "rot_sweep": rot_sweep, "sharded": sharded, "cpu_baseline": cpu,
                 "single_stream": {"ops_per_s": world * args.steps / (ms_single * 1e-3), "ms_per_op": ms_single / args.steps,
                                   "note": "the same products issued back to back on ONE stream (latency of one op)"},
                 "lanes_bit_exact_vs_single_stream": lanes_ok}
