@@ -396,8 +396,14 @@ def run_ours(args):
         def rot_step(i):
             b = drot.data_ptr() + (i % POOL) * 2 * poly
             ck(lib.gq_he_rot_dev(h, L, i % NROT, b, b + poly, rks[i % NROT]._h, None))
+
+        def rot_lane_step(i):            # independent rotations round-robin over the lanes; a buffer stays on its lane
+            k = i % LANES
+            b = drot.data_ptr() + (k + LANES * ((i // LANES) % max(1, POOL // LANES))) * 2 * poly
+            ck(lib.gq_he_rot_dev(lane_h[k], L, i % NROT, b, b + poly, rks[i % NROT]._h, None))
         nrot = max(args.steps, NROT)
-        ms_rot = timed(rot_step, nrot, args.warmup)
+        ms_rot1 = timed(rot_step, nrot, args.warmup)
+        ms_rot = timed(rot_lane_step, nrot, max(args.warmup, LANES), lanes=True)
         # the same 16 rotations of ONE ciphertext with the decomposition + forward NTT of c1 shared
         hout_r = torch.empty((NROT, 2, W, n), dtype=torch.int64, device=dev)
         VP = C.c_void_p * NROT
@@ -433,9 +439,29 @@ def run_ours(args):
         ms_g = timed(gemv_step, reps, 2)
         gemv = {"gemv_per_s": world * reps / (ms_g * 1e-3), "ms_per_gemv": ms_g / reps, "slots": 16, "mulpt_limbs": gdim,
                 "note": "gq_he_gemv_dev: the ciphertext arithmetic of he_gemv (src/he-algo.c:47-90) with pre-encoded "
-                        "diagonals, every intermediate ciphertext in HBM"}
+                        f"diagonals, every intermediate ciphertext in HBM, giant steps over {LANES} lanes"}
+        # configs[4]: the linear-transform half of bootstrapping as the reference composes it (he_coeff2slot,
+        # src/he-bootstrap.c:359-409): he_conj + 4 he_gemv + 2 x (he_add, he_mulpt, he_rs), device resident
+        cdim = int((LOGQ - LOGDELTA + 1 + math.log2(float(1 << LOGDELTA)) + LOGN) / 59 + 1)
+        cpts = gpts.repeat(4, 1, 1)
+        cptsv = (C.c_void_p * (4 * NROT))(*[cpts.data_ptr() + k * poly for k in range(4 * NROT)])
+        cconst = gpts[0].clone()
+        cout = torch.empty((4, W, n), dtype=torch.int64, device=dev)
+
+        def c2s_step(i):
+            ck(lib.gq_he_coeff2slot_dev(h, L, 4, 4, gdim, cdim, cout.data_ptr(), cout.data_ptr() + poly,
+                                        cout.data_ptr() + 2 * poly, cout.data_ptr() + 3 * poly, src.data_ptr(),
+                                        src.data_ptr() + poly, cptsv, cconst.data_ptr(), rks[1]._h, keys, None))
+        ms_c = timed(c2s_step, reps, 2)
+        c2s = {"coeff2slot_per_s": world * reps / (ms_c * 1e-3), "ms_per_coeff2slot": ms_c / reps, "slots": 16,
+               "ops": "1 he_conj, 4 he_gemv (each 4 hoisted + 4 plain rotations, 16 he_mulpt, 15 he_add, 1 he_rs), 2 he_add, "
+                      "2 he_mulpt, 2 he_rs",
+               "note": "configs[4] as far as the reference implements it (he_coeff2slot; he_bootstrap / EvalMod / "
+                       "he_slot2coeff are not in gpqhe.h, SURVEY fact 9); gq_he_coeff2slot_dev, every intermediate in HBM"}
         return {"he_rot_per_s": world * nrot / (ms_rot * 1e-3), "ms_per_rot": ms_rot / nrot, "rotations": NROT, "gemv": gemv,
-                "keyswitch_limbs": D2, "note": "he_rot at l=L, 16 distinct rotation keys (384 MiB) cycled",
+                "coeff2slot": c2s,
+                "keyswitch_limbs": D2, "note": f"he_rot at l=L, 16 distinct rotation keys (384 MiB) cycled, independent rotations over {LANES} lanes",
+                "single_stream": {"he_rot_per_s": world * nrot / (ms_rot1 * 1e-3), "ms_per_rot": ms_rot1 / nrot},
                 "hoisted": {"he_rot_per_s": world * reps * NROT / (ms_h * 1e-3), "ms_per_rot": ms_h / (reps * NROT),
                             "bit_exact_vs_he_rot": same,
                             "note": "16 rotations of one ciphertext per call (gq_he_rot_hoisted_dev): rns_decompose + "

@@ -15,6 +15,9 @@
  *   he_mul, he_mulpt                     src/he-mult.c:88-196
  *   he_rs, he_moddown                    src/he-rescale.c:33-70
  *   he_rot, he_conj                      src/he-automorphism.c:87-115
+ *   he_add, he_sub, he_addpt, he_subpt, he_neg   src/he-add.c:32-142
+ *   he_gemv                              src/he-algo.c:47-90 (device-resident loop)
+ *   he_coeff2slot                        src/he-bootstrap.c:359-409 (device-resident composition)
  *   polyctx_init/exit, hectx_init/exit   src/precomp.c:328-452 (wrappers: the reference
  *                                        builds its tables, we mirror them on the device)
  *   he_free_evk                          src/he-mem.c (wrapper: drops the device copy)
@@ -532,57 +535,138 @@ void he_neg(he_ct_t *ct) { ct_linear(ct, ct, NULL, NULL, 4, ct->l, __func__); }
  * Here only the encoding of the matrix diagonals (he_ecd: floating point, host) stays on the host;
  * the ciphertext crosses once in and once out and gq_he_gemv runs the same operations in the same
  * order on the device (baby rotations hoisted and computed once). */
-void he_gemv(he_ct_t *ct_dest, const _Complex double *A, const he_ct_t *ct, const he_evk_t *rk)
+static void gemv_split(unsigned *n1, unsigned *n2)
 {
-  const unsigned m = hectx.slots, n = polyctx.n, W = G.info.W, l = ct->l;
-  unsigned n1 = sqrt(m);                                                /* he-algo.c:51-54 */
-  if (m != n1 * n1) n1 = sqrt(2 * m);
-  const unsigned n2 = m / n1;
-  const size_t poly = (size_t)W * n;
-  uint64_t *s = stage((4 + (size_t)m) * poly);
-  poly_in(s, &ct->c0, W, __func__);
-  poly_in(s + poly, &ct->c1, W, __func__);
-  /* diagonal k = i*n1+j of A, pre-rotated by -i*n1 slots, encoded at scale Delta (he-algo.c:70-72) */
-  he_pt_t pt;
-  he_alloc_pt(&pt);
+  const unsigned m = hectx.slots;
+  *n1 = sqrt(m);                                                        /* he-algo.c:51-54 */
+  if (m != *n1 * *n1) *n1 = sqrt(2 * m);
+  *n2 = m / *n1;
+}
+
+/* diagonal k = i*n1+j of A, pre-rotated by -i*n1 slots, encoded at scale Delta (he-algo.c:70-72), written
+ * as word-major polys at dst + k*poly; pt keeps the metadata of the last he_ecd */
+static void gemv_diagonals(const _Complex double *A, unsigned n1, uint64_t *dst, const uint64_t **pts,
+                           he_pt_t *pt, const char *who)
+{
+  const unsigned m = hectx.slots, W = G.info.W;
+  const size_t poly = (size_t)W * polyctx.n;
   _Complex double *d = malloc(sizeof(_Complex double) * m);
-  const uint64_t **pts = malloc(sizeof(*pts) * m);
-  const gq_evk **keys = calloc(m, sizeof(*keys));
-  if (!d || !pts || !keys) die(__func__);
+  if (!d) die(who);
   for (unsigned k = 0; k < m; k++) {
     const unsigned shift = (k / n1) * n1;
     for (unsigned t = 0; t < m; t++) {
       const unsigned u = (t + m - shift % m) % m;                       /* slot after rotating by -shift */
       d[t] = A[(size_t)u * m + (k + u) % m];
     }
-    he_ecd(&pt, d);
-    poly_in(s + (4 + (size_t)k) * poly, &pt.m, W, __func__);
-    pts[k] = s + (4 + (size_t)k) * poly;
+    he_ecd(pt, d);
+    poly_in(dst + (size_t)k * poly, &pt->m, W, who);
+    pts[k] = dst + (size_t)k * poly;
   }
-  for (unsigned r = 0; r < m; r++)
-    if (r < n1 || r % n1 == 0) keys[r] = evk_dev(&rk[r]);
-  const unsigned dim = (gcry_mpi_get_nbits(hectx.q[l]) + log2(pt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
-  /* metadata: the reference's sequence of he_mulpt (he-mult.c:162-164), he_add (he-add.c:36-38)
-   * and he_rs (he-rescale.c:36-38) updates, in its loop order */
+  free(d);
+}
+
+/* metadata of he_gemv: the reference's sequence of he_mulpt (he-mult.c:162-164), he_add (he-add.c:36-38)
+ * and he_rs (he-rescale.c:36-38) updates, in its loop order */
+static void gemv_meta(double nu, double B, double ptnu, unsigned n1, unsigned n2, double *nu_out, double *B_out)
+{
   double nu_o = 0, B_o = 0;
   for (unsigned i = 0; i < n2; i++) {
     double nu_i = 0, B_i = 0;
     for (unsigned j = 0; j < n1; j++) {
-      const double nu_t = ct->nu * pt.nu, B_t = ct->B * pt.nu;
+      const double nu_t = nu * ptnu, B_t = B * ptnu;
       if (!j) { nu_i = nu_t; B_i = B_t; }
       else { nu_i = (nu_i >= nu_t) ? nu_i : nu_t; B_i = B_i + B_t; }
     }
     if (!i) { nu_o = nu_i; B_o = B_i; }
     else { nu_o = (nu_o >= nu_i) ? nu_o : nu_i; B_o = B_o + B_i; }
   }
+  *nu_out = nu_o / hectx.Delta;
+  *B_out = B_o / hectx.Delta + hectx.bnd.Brs;
+}
+
+static const gq_evk **gemv_keys(const he_evk_t *rk, unsigned n1, const char *who)
+{
+  const unsigned m = hectx.slots;
+  const gq_evk **keys = calloc(m, sizeof(*keys));
+  if (!keys) die(who);
+  for (unsigned r = 0; r < m; r++)
+    if (r < n1 || r % n1 == 0) keys[r] = evk_dev(&rk[r]);
+  return keys;
+}
+
+void he_gemv(he_ct_t *ct_dest, const _Complex double *A, const he_ct_t *ct, const he_evk_t *rk)
+{
+  const unsigned m = hectx.slots, n = polyctx.n, W = G.info.W, l = ct->l;
+  unsigned n1, n2;
+  gemv_split(&n1, &n2);
+  const size_t poly = (size_t)W * n;
+  uint64_t *s = stage((4 + (size_t)m) * poly);
+  poly_in(s, &ct->c0, W, __func__);
+  poly_in(s + poly, &ct->c1, W, __func__);
+  he_pt_t pt;
+  he_alloc_pt(&pt);
+  const uint64_t **pts = malloc(sizeof(*pts) * m);
+  if (!pts) die(__func__);
+  gemv_diagonals(A, n1, s + 4 * poly, pts, &pt, __func__);
+  const gq_evk **keys = gemv_keys(rk, n1, __func__);
+  const unsigned dim = (gcry_mpi_get_nbits(hectx.q[l]) + log2(pt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
+  double nu_o, B_o;
+  gemv_meta(ct->nu, ct->B, pt.nu, n1, n2, &nu_o, &B_o);
   CK(gq_he_gemv(ctx(), l, n1, n2, dim, s + 2 * poly, s + 3 * poly, s, s + poly, pts, keys));
   ct_dest->l = l - 1;
-  ct_dest->nu = nu_o / hectx.Delta;
-  ct_dest->B = B_o / hectx.Delta + hectx.bnd.Brs;
+  ct_dest->nu = nu_o;
+  ct_dest->B = B_o;
   poly_out(&ct_dest->c0, s + 2 * poly, W);
   poly_out(&ct_dest->c1, s + 3 * poly, W);
-  free(d); free(pts); free(keys);
+  free(pts); free(keys);
   he_free_pt(&pt);
+}
+
+/* ---- he_coeff2slot (src/he-bootstrap.c:359-409), device resident ----------------------------------
+ * he_conj, four he_gemv, he_add, he_mulpt by he_const_pt(1/n) and he_rs for the real and the imaginary
+ * half: one crossing in (the ciphertext + the encoded diagonals of the four matrices of bootstrapctx),
+ * one crossing out; the reference's own composition stays available as gpqhe_ref_he_coeff2slot. */
+extern struct bootstrap_ctx bootstrapctx;
+void he_coeff2slot(he_ct_t *ct_real, he_ct_t *ct_imag, const he_ct_t *ct, const he_evk_t *ck, const he_evk_t *rk)
+{
+  const unsigned m = hectx.slots, n = polyctx.n, W = G.info.W, l = ct->l;
+  unsigned n1, n2;
+  gemv_split(&n1, &n2);
+  const size_t poly = (size_t)W * n;
+  uint64_t *s = stage((7 + 4 * (size_t)m) * poly);
+  poly_in(s, &ct->c0, W, __func__);
+  poly_in(s + poly, &ct->c1, W, __func__);
+  he_pt_t pt, cpt;
+  he_alloc_pt(&pt);
+  he_alloc_pt(&cpt);
+  he_const_pt(&cpt, 1 / polyctx.n);                                     /* he-bootstrap.c:385, integer division as there */
+  poly_in(s + 2 * poly, &cpt.m, W, __func__);
+  const uint64_t **pts = malloc(sizeof(*pts) * 4 * m);
+  if (!pts) die(__func__);
+  const _Complex double *mats[4] = {bootstrapctx.U0_conjT, bootstrapctx.U0_T, bootstrapctx.U1_conjT, bootstrapctx.U1_T};
+  for (unsigned k = 0; k < 4; k++)
+    gemv_diagonals(mats[k], n1, s + (7 + (size_t)k * m) * poly, pts + (size_t)k * m, &pt, __func__);
+  const gq_evk **keys = gemv_keys(rk, n1, __func__);
+  const unsigned dim_gemv = (gcry_mpi_get_nbits(hectx.q[l]) + log2(pt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
+  const unsigned dim_pt = (gcry_mpi_get_nbits(hectx.q[l - 1]) + log2(cpt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
+  double nu_g, B_g;
+  gemv_meta(ct->nu, ct->B, pt.nu, n1, n2, &nu_g, &B_g);                 /* he_conj keeps nu and B */
+  uint64_t *o = s + 3 * poly;
+  CK(gq_he_coeff2slot(ctx(), l, n1, n2, dim_gemv, dim_pt, o, o + poly, o + 2 * poly, o + 3 * poly, s, s + poly,
+                      pts, s + 2 * poly, evk_dev(ck), keys));
+  he_ct_t *outs[2] = {ct_real, ct_imag};
+  for (unsigned k = 0; k < 2; k++) {
+    double nu = nu_g, B = B_g + B_g;                                    /* he_add, he-add.c:36-38 */
+    nu = nu * cpt.nu; B = B * cpt.nu;                                   /* he_mulpt, he-mult.c:162-164 */
+    outs[k]->l = l - 2;                                                 /* he_rs, he-rescale.c:36-38 */
+    outs[k]->nu = nu / hectx.Delta;
+    outs[k]->B = B / hectx.Delta + hectx.bnd.Brs;
+    poly_out(&outs[k]->c0, o + (size_t)(2 * k) * poly, W);
+    poly_out(&outs[k]->c1, o + (size_t)(2 * k + 1) * poly, W);
+  }
+  free(pts); free(keys);
+  he_free_pt(&pt);
+  he_free_pt(&cpt);
 }
 
 /* diagnostics for tests: coefficients marshalled in / out since load, and whether the direct

@@ -1012,22 +1012,34 @@ extern "C" int gq_he_gemv_dev(gq_ctx *c, unsigned l, unsigned n1, unsigned n2, u
   for (unsigned i = 0; i < n2; i++) if (!rk[i * n1]) GQ_FAIL("missing giant-step rotation key");
   for (unsigned k = 0; k < n1 * n2; k++) if (!pts[k]) GQ_FAIL("missing diagonal");
   const size_t poly = (size_t)c->W * c->n;
-  if (ensure_slot(c, GQ_SLOT_GEMV, (2 * (size_t)n1 + 6) * poly * 8)) return 1;
+  // giant steps are independent until they are summed: with compute lanes (gq_ctx_set_lanes) and the
+  // context's own stream, giant step i runs on lane i % K; the sums are taken afterwards in the reference's
+  // order on the context's stream
+  const unsigned K = (c->parent || stream) ? 1u : (unsigned)c->lanes.size() + 1;
+  if (ensure_slot(c, GQ_SLOT_GEMV, (2 * (size_t)n1 + 2 * (size_t)n2 + 2 * (size_t)K) * poly * 8)) return 1;
   uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_GEMV];
-  uint64_t *inner = base + 2 * (size_t)n1 * poly, *outer = inner + 2 * poly, *T = outer + 2 * poly;
+  uint64_t *accs = base + 2 * (size_t)n1 * poly, *Ts = accs + 2 * (size_t)n2 * poly;
   std::vector<unsigned> rots(n1);
   std::vector<uint64_t *> r0(n1), r1(n1);
   for (unsigned j = 0; j < n1; j++) { rots[j] = j; r0[j] = base + 2 * (size_t)j * poly; r1[j] = r0[j] + poly; }
   if (gq_he_rot_hoisted_dev(c, l, n1, rots.data(), r0.data(), r1.data(), a0, a1, rk, stream)) return 1;
+  if (K > 1 && gq_ctx_lanes_fork(c)) return 1;
   for (unsigned i = 0; i < n2; i++) {
-    uint64_t *acc = (i == 0) ? outer : inner;        // the first giant step lands in `outer` directly
+    gq_ctx *ln = (K > 1) ? gq_ctx_lane(c, i % K) : c;
+    void *ls = (K > 1) ? nullptr : stream;
+    uint64_t *acc = accs + 2 * (size_t)i * poly, *T = Ts + 2 * (size_t)(i % K) * poly;
     for (unsigned j = 0; j < n1; j++) {
       uint64_t *dst = (j == 0) ? acc : T;
-      if (gq_he_mulpt_dev(c, l, dim, dst, dst + poly, r0[j], r1[j], pts[i * n1 + j], stream)) return 1;
-      if (j && linear_dev(c, l, acc, acc + poly, acc, acc + poly, T, T + poly, 0, 0, stream)) return 1;
+      if (gq_he_mulpt_dev(ln, l, dim, dst, dst + poly, r0[j], r1[j], pts[i * n1 + j], ls)) return 1;
+      if (j && linear_dev(ln, l, acc, acc + poly, acc, acc + poly, T, T + poly, 0, 0, ls)) return 1;
     }
-    if (gq_he_rot_dev(c, l, i * n1, acc, acc + poly, rk[i * n1], stream)) return 1;
-    if (i && linear_dev(c, l, outer, outer + poly, outer, outer + poly, inner, inner + poly, 0, 0, stream)) return 1;
+    if (gq_he_rot_dev(ln, l, i * n1, acc, acc + poly, rk[i * n1], ls)) return 1;
+  }
+  if (K > 1 && gq_ctx_lanes_join(c)) return 1;
+  uint64_t *outer = accs;
+  for (unsigned i = 1; i < n2; i++) {
+    uint64_t *inner = accs + 2 * (size_t)i * poly;
+    if (linear_dev(c, l, outer, outer + poly, outer, outer + poly, inner, inner + poly, 0, 0, stream)) return 1;
   }
   if (rescale_dev(c, l, outer, outer + poly, true, stream)) return 1;
   cudaStream_t st = pick(c, stream);
@@ -1057,6 +1069,68 @@ extern "C" int gq_he_gemv(gq_ctx *c, unsigned l, unsigned n1, unsigned n2, unsig
     return 1;
   GQ_CUDA(cudaMemcpyAsync(c0, base + 2 * poly, poly * 8, cudaMemcpyDeviceToHost, c->stream));
   GQ_CUDA(cudaMemcpyAsync(c1, base + 3 * poly, poly * 8, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// he_coeff2slot, src/he-bootstrap.c:359-409 (the linear-transform half of bootstrapping as the reference
+// composes it):  ct_conj = he_conj(ct);  for part in {real, imag}:
+//   he_gemv(U_conjT, ct) + he_gemv(U_T, ct_conj) -> he_add -> he_mulpt(const pt) -> he_rs
+// The same operations in the same order, every intermediate ciphertext in HBM.  pts holds the encoded
+// diagonals of U0_conjT, U0_T, U1_conjT, U1_T (4 x n1*n2, each set laid out as gq_he_gemv wants), cpt the
+// encoded constant plaintext; dim_gemv / dim_pt are the he_mulpt limb counts (he-mult.c:168) at levels l and
+// l-1.  Outputs are at level l-2.
+extern "C" int gq_he_coeff2slot_dev(gq_ctx *c, unsigned l, unsigned n1, unsigned n2, unsigned dim_gemv,
+                                    unsigned dim_pt, uint64_t *re0, uint64_t *re1, uint64_t *im0, uint64_t *im1,
+                                    const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
+                                    const uint64_t *cpt, const gq_evk *ck, const gq_evk *const *rk, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (l < 2) GQ_FAIL("needs two levels");
+  if (!re0 || !re1 || !im0 || !im1 || !a0 || !a1 || !pts || !cpt || !ck || !rk) GQ_FAIL("null argument");
+  const size_t poly = (size_t)c->W * c->n, m = (size_t)n1 * n2;
+  if (ensure_slot(c, GQ_SLOT_C2S, 6 * poly * 8)) return 1;
+  uint64_t *cj = (uint64_t *)c->slot[GQ_SLOT_C2S], *t0 = cj + 2 * poly, *t1 = t0 + 2 * poly;
+  cudaStream_t st = pick(c, stream);
+  GQ_CUDA(cudaMemcpyAsync(cj, a0, poly * 8, cudaMemcpyDeviceToDevice, st));
+  GQ_CUDA(cudaMemcpyAsync(cj + poly, a1, poly * 8, cudaMemcpyDeviceToDevice, st));
+  if (gq_he_conj_dev(c, l, cj, cj + poly, ck, stream)) return 1;
+  for (int part = 0; part < 2; part++) {
+    uint64_t *o0 = part ? im0 : re0, *o1 = part ? im1 : re1;
+    if (gq_he_gemv_dev(c, l, n1, n2, dim_gemv, t0, t0 + poly, a0, a1, pts + (2 * part) * m, rk, stream)) return 1;
+    if (gq_he_gemv_dev(c, l, n1, n2, dim_gemv, t1, t1 + poly, cj, cj + poly, pts + (2 * part + 1) * m, rk, stream)) return 1;
+    if (linear_dev(c, l - 1, o0, o1, t0, t0 + poly, t1, t1 + poly, 0, 0, stream)) return 1;
+    if (gq_he_mulpt_dev(c, l - 1, dim_pt, o0, o1, o0, o1, cpt, stream)) return 1;
+    if (rescale_dev(c, l - 1, o0, o1, true, stream)) return 1;
+  }
+  return 0;
+}
+
+extern "C" int gq_he_coeff2slot(gq_ctx *c, unsigned l, unsigned n1, unsigned n2, unsigned dim_gemv,
+                                unsigned dim_pt, uint64_t *re0, uint64_t *re1, uint64_t *im0, uint64_t *im1,
+                                const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
+                                const uint64_t *cpt, const gq_evk *ck, const gq_evk *const *rk) {
+  if (he_check(c, l)) return 1;
+  if (!re0 || !re1 || !im0 || !im1 || !a0 || !a1 || !pts || !cpt || !ck || !rk || n1 == 0 || n2 == 0)
+    GQ_FAIL("bad argument");
+  const size_t poly = (size_t)c->W * c->n, np = 4 * (size_t)n1 * n2;
+  if (ensure_slot(c, GQ_SLOT_PIPE, (7 + np) * poly * 8)) return 1;
+  uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_PIPE];
+  GQ_CUDA(cudaMemcpyAsync(base, a0, poly * 8, cudaMemcpyHostToDevice, c->stream));
+  GQ_CUDA(cudaMemcpyAsync(base + poly, a1, poly * 8, cudaMemcpyHostToDevice, c->stream));
+  GQ_CUDA(cudaMemcpyAsync(base + 2 * poly, cpt, poly * 8, cudaMemcpyHostToDevice, c->stream));
+  std::vector<const uint64_t *> dp(np);
+  for (size_t k = 0; k < np; k++) {
+    if (!pts[k]) GQ_FAIL("missing diagonal");
+    uint64_t *d = base + (7 + k) * poly;
+    GQ_CUDA(cudaMemcpyAsync(d, pts[k], poly * 8, cudaMemcpyHostToDevice, c->stream));
+    dp[k] = d;
+  }
+  uint64_t *o = base + 3 * poly;
+  if (gq_he_coeff2slot_dev(c, l, n1, n2, dim_gemv, dim_pt, o, o + poly, o + 2 * poly, o + 3 * poly, base, base + poly,
+                           dp.data(), base + 2 * poly, ck, rk, nullptr)) return 1;
+  uint64_t *dst[4] = {re0, re1, im0, im1};
+  for (int k = 0; k < 4; k++)
+    GQ_CUDA(cudaMemcpyAsync(dst[k], o + (size_t)k * poly, poly * 8, cudaMemcpyDeviceToHost, c->stream));
   GQ_CUDA(cudaStreamSynchronize(c->stream));
   return 0;
 }

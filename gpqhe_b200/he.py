@@ -371,6 +371,40 @@ class HeContext:
             nu_o, B_o = (nu_i, B_i) if i == 0 else (max(nu_o, nu_i), B_o + B_i)
         return HeCt(ct.l - 1, c0, c1, nu_o / float(self.Delta), B_o / float(self.Delta) + self.Brs)
 
+    def he_coeff2slot_encoded(self, ct: HeCt, pts4, cpt: HePt, n1: int, n2: int, ck: HeEvk, rk):
+        """The ciphertext arithmetic of he_coeff2slot(ct_real, ct_imag, ct, ck, rk) (src/he-bootstrap.c:359-409)
+        with the plaintexts already encoded: pts4 = four lists of n1*n2 HePt (diagonals of U0_conjT, U0_T,
+        U1_conjT, U1_T as he_gemv_encoded wants them), cpt = the constant plaintext.  Returns (real, imag)."""
+        m = n1 * n2
+        flat = [p for part in pts4 for p in part]
+        if len(flat) != 4 * m:
+            raise GpqheError("he_coeff2slot: need 4 x n1*n2 encoded diagonals")
+        l = ct.l
+        dim_gemv = self.mulpt_dim(l, flat[0].nu)
+        outs = [np.empty((self.W, self.n), dtype=np.uint64) for _ in range(4)]
+        hold = [_c(p.m) for p in flat]
+        keys = (C.c_void_p * m)(*[(rk[r]._h if (r < n1 or r % n1 == 0) else None) for r in range(m)])
+        # metadata of the two he_gemv + he_add, before the constant multiply (same for both parts)
+        g = HeCt(l, ct.c0, ct.c1, ct.nu, ct.B)
+        nu_o = B_o = 0.0
+        for i in range(n2):
+            nu_i = B_i = 0.0
+            for j in range(n1):
+                pt = flat[i * n1 + j]
+                nu_t, B_t = g.nu * pt.nu, g.B * pt.nu
+                nu_i, B_i = (nu_t, B_t) if j == 0 else (max(nu_i, nu_t), B_i + B_t)
+            nu_o, B_o = (nu_i, B_i) if i == 0 else (max(nu_o, nu_i), B_o + B_i)
+        nu_g, B_g = nu_o / float(self.Delta), B_o / float(self.Delta) + self.Brs
+        nu_a, B_a = nu_g, 2 * B_g                                              # he-add.c:36-38
+        dim_pt = self.mulpt_dim(l - 1, cpt.nu)
+        capi.check(self._lib, self._lib.gq_he_coeff2slot(
+            self._h, l, n1, n2, dim_gemv, dim_pt, _ptr(outs[0]), _ptr(outs[1]), _ptr(outs[2]), _ptr(outs[3]),
+            _ptr(_c(ct.c0)), _ptr(_c(ct.c1)), (C.c_void_p * (4 * m))(*[h.ctypes.data for h in hold]),
+            _ptr(_c(cpt.m)), ck._h, keys))
+        nu_f = nu_a * cpt.nu / float(self.Delta)                               # he-mult.c:162-164, he-rescale.c:36-38
+        B_f = B_a * cpt.nu / float(self.Delta) + self.Brs
+        return (HeCt(l - 2, outs[0], outs[1], nu_f, B_f), HeCt(l - 2, outs[2], outs[3], nu_f, B_f))
+
     def he_mul_rs(self, ct1: HeCt, ct2: HeCt, rlk: HeEvk) -> HeCt:
         """he_mul then he_rs on the product, one crossing (gq_he_mul_rs)."""
         return self.he_mul_batch([(ct1, ct2)], rlk, rescale=True, fused_single=True)[0]

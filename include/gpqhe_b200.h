@@ -170,6 +170,15 @@ int gq_he_rot_hoisted(gq_ctx *ctx, unsigned l, unsigned count, const unsigned *r
 int gq_he_gemv(gq_ctx *ctx, unsigned l, unsigned n1, unsigned n2, unsigned dim, uint64_t *c0, uint64_t *c1,
                const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
                const gq_evk *const *rk);
+/* he_coeff2slot, src/he-bootstrap.c:359-409: ct_conj = he_conj(ct); for part in {real, imag}:
+   he_gemv(U_conjT, ct) + he_gemv(U_T, ct_conj) -> he_add -> he_mulpt(constant plaintext) -> he_rs, with every
+   intermediate ciphertext on the device.  pts: encoded diagonals of U0_conjT, U0_T, U1_conjT, U1_T (4 sets of
+   n1*n2, each as gq_he_gemv wants them); cpt: the encoded constant plaintext; dim_gemv / dim_pt: he_mulpt limb
+   counts (he-mult.c:168) at levels l and l-1; rk indexed by rotation amount.  Outputs are at level l-2. */
+int gq_he_coeff2slot(gq_ctx *ctx, unsigned l, unsigned n1, unsigned n2, unsigned dim_gemv, unsigned dim_pt,
+                     uint64_t *re0, uint64_t *re1, uint64_t *im0, uint64_t *im1, const uint64_t *a0,
+                     const uint64_t *a1, const uint64_t *const *pts, const uint64_t *cpt, const gq_evk *ck,
+                     const gq_evk *const *rk);
 /* he_add / he_sub (src/he-add.c:32-76), he_addpt / he_subpt (:79-120: only c0 meets the plaintext,
    c1 is reduced), he_neg (:123-140, in place): out = smod_{q_l}(a op b); outputs may alias inputs */
 int gq_he_add(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
@@ -213,6 +222,10 @@ int gq_he_rot_hoisted_dev(gq_ctx *ctx, unsigned l, unsigned count, const unsigne
 int gq_he_gemv_dev(gq_ctx *ctx, unsigned l, unsigned n1, unsigned n2, unsigned dim, uint64_t *c0,
                    uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
                    const gq_evk *const *rk, void *stream);
+int gq_he_coeff2slot_dev(gq_ctx *ctx, unsigned l, unsigned n1, unsigned n2, unsigned dim_gemv, unsigned dim_pt,
+                         uint64_t *re0, uint64_t *re1, uint64_t *im0, uint64_t *im1, const uint64_t *a0,
+                         const uint64_t *a1, const uint64_t *const *pts, const uint64_t *cpt, const gq_evk *ck,
+                         const gq_evk *const *rk, void *stream);
 int gq_he_add_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
                   const uint64_t *b0, const uint64_t *b1, void *stream);
 int gq_he_sub_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,

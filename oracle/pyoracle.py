@@ -447,6 +447,21 @@ def he_gemv_encoded(ctx: Ctx, ct: dict, pts: list, dim: int, n1: int, n2: int, r
     return he_rs(ctx, outer)
 
 
+def he_coeff2slot_encoded(ctx: Ctx, ct: dict, pts4: list, cpt: list, dim_gemv: int, dim_pt: int,
+                          n1: int, n2: int, ck, rk) -> tuple:
+    """src/he-bootstrap.c:359-409 with the plaintexts given: pts4 = encoded diagonals of U0_conjT, U0_T,
+    U1_conjT, U1_T, cpt = coefficients of the constant plaintext.  Returns (ct_real, ct_imag)."""
+    ct_conj = he_conj(ctx, ct, ck)
+    out = []
+    for part in range(2):
+        ct0 = he_gemv_encoded(ctx, ct, pts4[2 * part], dim_gemv, n1, n2, rk)
+        ct1 = he_gemv_encoded(ctx, ct_conj, pts4[2 * part + 1], dim_gemv, n1, n2, rk)
+        r = he_add(ctx, ct0, ct1)
+        r = he_mulpt(ctx, r, cpt, dim_pt)
+        out.append(he_rs(ctx, r))
+    return tuple(out)
+
+
 # --------------------------------------------------------------------------- #
 # packed-word interchange format used at the C-ABI (include/gpqhe_b200.h):
 # word-major two's complement, words[w, i] = bits 64w..64w+63 of coefficient i

@@ -49,6 +49,7 @@ void gpqhe_ref_he_addpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt);
 void gpqhe_ref_he_subpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt);
 void gpqhe_ref_he_neg(he_ct_t *ct);
 void gpqhe_ref_he_gemv(he_ct_t *ct_dest, const _Complex double *A, const he_ct_t *ct, const he_evk_t *rk);
+void gpqhe_ref_he_coeff2slot(he_ct_t *ct_real, he_ct_t *ct_imag, const he_ct_t *ct, const he_evk_t *ck, const he_evk_t *rk);
 void gpqhe_dropin_stats(unsigned long long *in, unsigned long long *out, int *fast_mpi);
 
 static unsigned npass, nfail;
@@ -209,6 +210,16 @@ int main(int argc, char **argv)
     he_gemv(&g, A, &g, rk); gpqhe_ref_he_gemv(&r, A, &r, rk);     /* dest aliases src (he_sum does this) */
     report("he_gemv (in place)", eq_ct(&g, &r));
     free(A);
+    /* ---- he_coeff2slot (src/he-bootstrap.c:359-409): one device-resident call vs the reference's own
+     * composition (he_conj, 4 he_gemv, he_add, he_mulpt, he_rs as separate calls) */
+    he_ct_t gi, ri;
+    he_alloc_ct(&gi); he_alloc_ct(&ri);
+    he_bootstrapctx_init();
+    he_coeff2slot(&g, &gi, &c1, &ck, rk); gpqhe_ref_he_coeff2slot(&r, &ri, &c1, &ck, rk);
+    report("he_coeff2slot (real)", eq_ct(&g, &r));
+    report("he_coeff2slot (imag)", eq_ct(&gi, &ri));
+    he_bootstrapctx_exit();
+    he_free_ct(&gi); he_free_ct(&ri);
   }
 
   unsigned long long in = 0, out = 0;

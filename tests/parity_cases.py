@@ -275,5 +275,47 @@ def check_gemv(lib_path, logn, q, Delta, n1=2, n2=2, logqub=0, seed=3):
         want = o.he_gemv_encoded(oc, {"l": l, "c0": a0, "c1": a1}, ms, ctx.mulpt_dim(l, nu), n1, n2, keys)
         assert got.l == want["l"]
         assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], "he_gemv"
+        # giant steps spread over compute lanes: same bits, twice (scratch of every lane reused)
+        ctx.set_lanes(3)
+        for _ in range(2):
+            got = ctx.he_gemv_encoded(g.HeCt(l, g.ints_to_big(a0, W), g.ints_to_big(a1, W)), pts, n1, n2, dkeys)
+            assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], "he_gemv over lanes"
+    finally:
+        ctx.close()
+
+
+def check_coeff2slot(lib_path, logn, q, Delta, n1=2, n2=2, logqub=0, seed=5, lanes=1):
+    """Device-resident he_coeff2slot (src/he-bootstrap.c:359-409: he_conj, 4 he_gemv, he_add, he_mulpt by
+    the constant plaintext, he_rs) vs the oracle's restatement of the same composition."""
+    rng = random.Random(seed)
+    slots = n1 * n2
+    ctx = g.HeContext(logn, q, slots, Delta, lib_path=lib_path, logqub=logqub)
+    oc = o.Ctx(logn, q, slots, Delta, logqub=logqub or None)
+    try:
+        if lanes > 1:
+            ctx.set_lanes(lanes)
+        n, W, l = ctx.n, ctx.W, ctx.L
+        assert l >= 2
+        ql = oc.ql[l]
+        a0, a1 = rpoly(rng, ql, n), rpoly(rng, ql, n)
+        need = sorted(set(range(n1)) | {i * n1 for i in range(n2)})
+        keys = {r: (rlimbs(rng, oc.primes, n, oc.dimevk), rlimbs(rng, oc.primes, n, oc.dimevk)) for r in need}
+        ckey = (rlimbs(rng, oc.primes, n, oc.dimevk), rlimbs(rng, oc.primes, n, oc.dimevk))
+        dkeys = {r: ctx.genevk(*keys[r]) for r in need}
+        dck = ctx.genevk(*ckey)
+        nu = float(Delta)
+        ms4 = [[[rng.randrange(2 * Delta) - Delta for _ in range(n)] for _ in range(slots)] for _ in range(4)]
+        pts4 = [[g.HePt(g.ints_to_big(m, W), nu=nu) for m in ms] for ms in ms4]
+        # he_const_pt (src/he-encode.c:119-125) touches coefficients 0 and n/2 only
+        cm = [0] * n
+        cm[0], cm[n // 2] = rng.randrange(Delta), -rng.randrange(Delta)
+        cpt = g.HePt(g.ints_to_big(cm, W), nu=nu)
+        re, im = ctx.he_coeff2slot_encoded(g.HeCt(l, g.ints_to_big(a0, W), g.ints_to_big(a1, W)), pts4, cpt,
+                                           n1, n2, dck, dkeys)
+        wre, wim = o.he_coeff2slot_encoded(oc, {"l": l, "c0": a0, "c1": a1}, ms4, cm, ctx.mulpt_dim(l, nu),
+                                           ctx.mulpt_dim(l - 1, nu), n1, n2, ckey, keys)
+        for name, got, want in (("real", re, wre), ("imag", im, wim)):
+            assert got.l == want["l"] == l - 2
+            assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], ("he_coeff2slot", name)
     finally:
         ctx.close()

@@ -110,3 +110,8 @@ def test_crt_edge_values_take_exact_path(emul_lib):
 @pytest.mark.parametrize("logn,q,Delta,n1,n2", [(5, 1 << 120, 1 << 40, 2, 2), (5, 1 << 438, 1 << 50, 4, 2)])
 def test_gemv_device_resident(emul_lib, logn, q, Delta, n1, n2):
     pc.check_gemv(emul_lib, logn, q, Delta, n1, n2, logqub=q.bit_length() - 1)
+
+
+@pytest.mark.parametrize("logn,q,Delta,n1,n2,lanes", [(5, 1 << 120, 1 << 40, 2, 2, 1), (5, 1 << 438, 1 << 50, 2, 2, 3)])
+def test_coeff2slot_device_resident(emul_lib, logn, q, Delta, n1, n2, lanes):
+    pc.check_coeff2slot(emul_lib, logn, q, Delta, n1, n2, logqub=q.bit_length() - 1, lanes=lanes)

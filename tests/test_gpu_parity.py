@@ -103,3 +103,10 @@ def test_crt_edge_values_take_exact_path(real_lib):
 def test_gemv_device_resident(real_lib):
     """he_gemv with slots = 16 (n1 = n2 = 4, the KAT's shape) at N=2^12."""
     pc.check_gemv(real_lib, 12, 1 << 109, 1 << 30, 4, 4)
+
+
+def test_coeff2slot_device_resident(real_lib):
+    """configs[4]: he_coeff2slot (he_conj + 4 he_gemv + he_add + he_mulpt + he_rs) at N=2^12, slots = 16,
+    giant steps spread over 3 compute lanes."""
+    pc.check_coeff2slot(real_lib, 12, 1 << 109, 1 << 30, 4, 4, lanes=3)
+    pc.check_coeff2slot(real_lib, 10, 1 << 120, 1 << 40, 2, 2, logqub=120, lanes=1)
