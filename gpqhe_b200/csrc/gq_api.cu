@@ -1231,8 +1231,12 @@ extern "C" int gq_he_mul_batch(gq_ctx *c, unsigned l, unsigned count, uint64_t *
     uint64_t *in = base + (size_t)bf * 6 * poly, *out = in + 4 * poly;
     const uint64_t *src[4] = {a0[i], a1[i], b0[i], b1[i]};
     if (i >= NB) GQ_CUDA(cudaStreamWaitEvent(c->s_in, ev[4 * bf + 1], 0));
-    for (int j = 0; j < 4; j++)
-      GQ_CUDA(cudaMemcpyAsync(in + j * poly, src[j], poly * 8, cudaMemcpyHostToDevice, c->s_in));
+    for (int j = 0; j < 4;) {          // polys that are adjacent in host memory travel as one copy
+      int e = j + 1;
+      while (e < 4 && src[e] == src[e - 1] + poly) e++;
+      GQ_CUDA(cudaMemcpyAsync(in + j * poly, src[j], (size_t)(e - j) * poly * 8, cudaMemcpyHostToDevice, c->s_in));
+      j = e;
+    }
     GQ_CUDA(cudaEventRecord(ev[4 * bf + 0], c->s_in));
     GQ_CUDA(cudaStreamWaitEvent(ln->stream, ev[4 * bf + 0], 0));
     if (i >= NB) GQ_CUDA(cudaStreamWaitEvent(ln->stream, ev[4 * bf + 3], 0));
@@ -1242,8 +1246,12 @@ extern "C" int gq_he_mul_batch(gq_ctx *c, unsigned l, unsigned count, uint64_t *
     GQ_CUDA(cudaEventRecord(ev[4 * bf + 1], ln->stream));
     GQ_CUDA(cudaEventRecord(ev[4 * bf + 2], ln->stream));
     GQ_CUDA(cudaStreamWaitEvent(c->s_out, ev[4 * bf + 2], 0));
-    GQ_CUDA(cudaMemcpyAsync(c0[i], out, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
-    GQ_CUDA(cudaMemcpyAsync(c1[i], out + poly, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
+    if (c1[i] == c0[i] + poly) {
+      GQ_CUDA(cudaMemcpyAsync(c0[i], out, 2 * poly * 8, cudaMemcpyDeviceToHost, c->s_out));
+    } else {
+      GQ_CUDA(cudaMemcpyAsync(c0[i], out, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
+      GQ_CUDA(cudaMemcpyAsync(c1[i], out + poly, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
+    }
     GQ_CUDA(cudaEventRecord(ev[4 * bf + 3], c->s_out));
   }
   cudaStreamSynchronize(c->s_in);
