@@ -1135,6 +1135,159 @@ extern "C" int gq_he_coeff2slot(gq_ctx *c, unsigned l, unsigned n1, unsigned n2,
   return 0;
 }
 
+// he_exp (src/he-algo.c:363-458), device resident: act = he_rs(he_mulpt(ct, pts[0])); the degree-7 Taylor
+// polynomial of he_exp_taylor (:364-433) in the reference's own evaluation order (ct2, ct4, ct01, ct23, ct0123,
+// ct45, ct67, ct4567 - every he_mul / he_mulpt / he_rs / he_moddown / he_add / he_addpt at the level it has
+// there); then `iter` squarings.  pts (encoded by the caller, host floating point): 0 = he_ecd of a/2^iter in
+// every slot, 1..7 = he_const_pt of 1, 3, 1/6, 5, 1/120, 7, 1/5040.  dim_a / dim_t = he_mulpt limb counts
+// (he-mult.c:168) at levels l and l-1.  Result at level l-4-iter.  The output may alias the input.
+extern "C" int gq_he_exp_dev(gq_ctx *c, unsigned l, unsigned iter, unsigned dim_a, unsigned dim_t, uint64_t *c0,
+                             uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
+                             const gq_evk *rlk, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (l < 4 + iter) GQ_FAIL("he_exp needs 4 + iter levels");
+  if (!c0 || !c1 || !a0 || !a1 || !pts || !rlk) GQ_FAIL("null argument");
+  for (int k = 0; k < 8; k++) if (!pts[k]) GQ_FAIL("missing plaintext");
+  const size_t poly = (size_t)c->W * c->n;
+  if (ensure_slot(c, GQ_SLOT_EXP, 18 * poly * 8)) return 1;
+  uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_EXP];
+  struct Ct { uint64_t *p0, *p1; };
+  auto ct = [&](int k) { Ct x{base + 2 * (size_t)k * poly, base + (2 * (size_t)k + 1) * poly}; return x; };
+  const Ct act = ct(0), ct2 = ct(1), ct4 = ct(2), ct01 = ct(3), ct23 = ct(4), ct0123 = ct(5), ct45 = ct(6),
+           ct67 = ct(7), ct4567 = ct(8);
+  void *s = stream;
+  auto mul = [&](unsigned lv, Ct d, Ct x, Ct y) { return gq_he_mul_dev(c, lv, d.p0, d.p1, x.p0, x.p1, y.p0, y.p1, rlk, s); };
+  auto rs = [&](unsigned lv, Ct x) { return rescale_dev(c, lv, x.p0, x.p1, true, s); };
+  auto md = [&](unsigned lv, Ct x) { return rescale_dev(c, lv, x.p0, x.p1, false, s); };
+  auto add = [&](unsigned lv, Ct d, Ct x, Ct y) { return linear_dev(c, lv, d.p0, d.p1, x.p0, x.p1, y.p0, y.p1, 0, 0, s); };
+  // dest = he_rs(he_mulpt(he_addpt(act, pts[ka]), pts[km]))  (he-algo.c:385-388 and its three siblings)
+  auto lin = [&](unsigned lv, Ct d, int ka, int km) {
+    if (linear_dev(c, lv, d.p0, d.p1, act.p0, act.p1, pts[ka], nullptr, 0, 3, s)) return 1;
+    if (gq_he_mulpt_dev(c, lv, dim_t, d.p0, d.p1, d.p0, d.p1, pts[km], s)) return 1;
+    return rs(lv, d);
+  };
+  if (gq_he_mulpt_dev(c, l, dim_a, act.p0, act.p1, a0, a1, pts[0], s) || rs(l, act)) return 1;   // he-algo.c:448-449
+  const unsigned k = l - 1;
+  if (mul(k, ct2, act, act) || rs(k, ct2)) return 1;                   // ct^2, level k-1
+  if (mul(k - 1, ct4, ct2, ct2) || rs(k - 1, ct4)) return 1;           // ct^4, level k-2
+  if (lin(k, ct01, 1, 1) || md(k - 1, ct01)) return 1;                 // (ct+1)*1, level k-2
+  if (lin(k, ct23, 2, 3) || mul(k - 1, ct23, ct2, ct23) || rs(k - 1, ct23)) return 1;
+  if (add(k - 2, ct0123, ct01, ct23) || md(k - 2, ct0123)) return 1;   // level k-3
+  if (lin(k, ct45, 4, 5) || md(k - 1, ct45)) return 1;
+  if (lin(k, ct67, 6, 7) || mul(k - 1, ct67, ct2, ct67) || rs(k - 1, ct67)) return 1;
+  if (add(k - 2, ct4567, ct45, ct67) || mul(k - 2, ct4567, ct4, ct4567) || rs(k - 2, ct4567)) return 1;
+  const Ct out{c0, c1};
+  if (add(k - 3, out, ct0123, ct4567)) return 1;
+  for (unsigned t = 0; t < iter; t++)                                  // he-algo.c:451-454
+    if (mul(k - 3 - t, out, out, out) || rs(k - 3 - t, out)) return 1;
+  return 0;
+}
+
+// he_rlsin (src/he-bootstrap.c:444-475; the EvalMod step of he_bootstrap, :518-520):
+//   e = he_exp(i*a*ct);  dest = he_rs(he_mulpt(he_sub(e, he_conj(e)), pts[8]))
+// pts[0..7] as gq_he_exp_dev (pts[0] encodes i*a/2^iter), pts[8] = he_ecd of 1/(2*i*a) in every slot; dim_f =
+// he_mulpt limb count at level l-4-iter.  Result at level l-5-iter.  The output may alias the input.
+extern "C" int gq_he_rlsin_dev(gq_ctx *c, unsigned l, unsigned iter, unsigned dim_a, unsigned dim_t, unsigned dim_f,
+                               uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                               const uint64_t *const *pts, const gq_evk *rlk, const gq_evk *ck, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (l < 5 + iter) GQ_FAIL("he_rlsin needs 5 + iter levels");
+  if (!c0 || !c1 || !a0 || !a1 || !pts || !rlk || !ck) GQ_FAIL("null argument");
+  if (!pts[8]) GQ_FAIL("missing plaintext");
+  const size_t poly = (size_t)c->W * c->n;
+  if (ensure_slot(c, GQ_SLOT_RLSIN, 4 * poly * 8)) return 1;
+  uint64_t *e = (uint64_t *)c->slot[GQ_SLOT_RLSIN], *en = e + 2 * poly;
+  const unsigned m = l - 4 - iter;
+  cudaStream_t st = pick(c, stream);
+  if (gq_he_exp_dev(c, l, iter, dim_a, dim_t, e, e + poly, a0, a1, pts, rlk, stream)) return 1;
+  GQ_CUDA(cudaMemcpyAsync(en, e, 2 * poly * 8, cudaMemcpyDeviceToDevice, st));
+  if (gq_he_conj_dev(c, m, en, en + poly, ck, stream)) return 1;
+  if (linear_dev(c, m, c0, c1, e, e + poly, en, en + poly, 1, 1, stream)) return 1;
+  if (gq_he_mulpt_dev(c, m, dim_f, c0, c1, c0, c1, pts[8], stream)) return 1;
+  return rescale_dev(c, m, c0, c1, true, stream);
+}
+
+// he_slot2coeff (src/he-bootstrap.c:414-438): he_gemv(U0, ct0) + he_gemv(U1, ct1); pts = the encoded diagonals
+// of U0 then U1 (2 x n1*n2).  Result at level l-1.
+extern "C" int gq_he_slot2coeff_dev(gq_ctx *c, unsigned l, unsigned n1, unsigned n2, unsigned dim, uint64_t *c0,
+                                    uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *b0,
+                                    const uint64_t *b1, const uint64_t *const *pts, const gq_evk *const *rk,
+                                    void *stream) {
+  if (he_check(c, l)) return 1;
+  if (l < 1) GQ_FAIL("cannot go below level 0");
+  if (!c0 || !c1 || !a0 || !a1 || !b0 || !b1 || !pts || !rk) GQ_FAIL("null argument");
+  const size_t poly = (size_t)c->W * c->n, m = (size_t)n1 * n2;
+  if (ensure_slot(c, GQ_SLOT_C2S, 6 * poly * 8)) return 1;
+  uint64_t *t0 = (uint64_t *)c->slot[GQ_SLOT_C2S] + 2 * poly, *t1 = t0 + 2 * poly;
+  if (gq_he_gemv_dev(c, l, n1, n2, dim, t0, t0 + poly, a0, a1, pts, rk, stream)) return 1;
+  if (gq_he_gemv_dev(c, l, n1, n2, dim, t1, t1 + poly, b0, b1, pts + m, rk, stream)) return 1;
+  return linear_dev(c, l - 1, c0, c1, t0, t0 + poly, t1, t1 + poly, 0, 0, stream);
+}
+
+// host-pointer forms: npts plaintexts and nin input polys up, 2 result polys down, one crossing
+static int staged_call(gq_ctx *c, unsigned nin, const uint64_t *const *in, unsigned npts, const uint64_t *const *pts,
+                       uint64_t *c0, uint64_t *c1, int (*body)(gq_ctx *, uint64_t *const *, const uint64_t *const *, void *),
+                       void *arg) {
+  const size_t poly = (size_t)c->W * c->n;
+  if (ensure_slot(c, GQ_SLOT_PIPE, (2 + (size_t)nin + npts) * poly * 8)) return 1;
+  uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_PIPE];
+  std::vector<uint64_t *> io(2 + nin);
+  std::vector<const uint64_t *> dp(npts);
+  for (unsigned k = 0; k < 2 + nin; k++) io[k] = base + (size_t)k * poly;
+  for (unsigned k = 0; k < nin; k++) {
+    if (!in[k]) GQ_FAIL("null argument");
+    GQ_CUDA(cudaMemcpyAsync(io[2 + k], in[k], poly * 8, cudaMemcpyHostToDevice, c->stream));
+  }
+  for (unsigned k = 0; k < npts; k++) {
+    if (!pts[k]) GQ_FAIL("missing plaintext");
+    uint64_t *d = base + (2 + (size_t)nin + k) * poly;
+    GQ_CUDA(cudaMemcpyAsync(d, pts[k], poly * 8, cudaMemcpyHostToDevice, c->stream));
+    dp[k] = d;
+  }
+  if (body(c, io.data(), dp.data(), arg)) return 1;
+  GQ_CUDA(cudaMemcpyAsync(c0, io[0], poly * 8, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaMemcpyAsync(c1, io[1], poly * 8, cudaMemcpyDeviceToHost, c->stream));
+  GQ_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+struct ExpArgs { unsigned l, iter, dim_a, dim_t, dim_f, n1, n2; const gq_evk *rlk, *ck; const gq_evk *const *rk; };
+extern "C" int gq_he_exp(gq_ctx *c, unsigned l, unsigned iter, unsigned dim_a, unsigned dim_t, uint64_t *c0,
+                         uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
+                         const gq_evk *rlk) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !a0 || !a1 || !pts || !rlk) GQ_FAIL("null argument");
+  ExpArgs a{l, iter, dim_a, dim_t, 0, 0, 0, rlk, nullptr, nullptr};
+  const uint64_t *in[2] = {a0, a1};
+  return staged_call(c, 2, in, 8, pts, c0, c1, [](gq_ctx *c, uint64_t *const *io, const uint64_t *const *dp, void *p) {
+    const ExpArgs &a = *(const ExpArgs *)p;
+    return gq_he_exp_dev(c, a.l, a.iter, a.dim_a, a.dim_t, io[0], io[1], io[2], io[3], dp, a.rlk, nullptr);
+  }, &a);
+}
+extern "C" int gq_he_rlsin(gq_ctx *c, unsigned l, unsigned iter, unsigned dim_a, unsigned dim_t, unsigned dim_f,
+                           uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                           const uint64_t *const *pts, const gq_evk *rlk, const gq_evk *ck) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !a0 || !a1 || !pts || !rlk || !ck) GQ_FAIL("null argument");
+  ExpArgs a{l, iter, dim_a, dim_t, dim_f, 0, 0, rlk, ck, nullptr};
+  const uint64_t *in[2] = {a0, a1};
+  return staged_call(c, 2, in, 9, pts, c0, c1, [](gq_ctx *c, uint64_t *const *io, const uint64_t *const *dp, void *p) {
+    const ExpArgs &a = *(const ExpArgs *)p;
+    return gq_he_rlsin_dev(c, a.l, a.iter, a.dim_a, a.dim_t, a.dim_f, io[0], io[1], io[2], io[3], dp, a.rlk, a.ck, nullptr);
+  }, &a);
+}
+extern "C" int gq_he_slot2coeff(gq_ctx *c, unsigned l, unsigned n1, unsigned n2, unsigned dim, uint64_t *c0,
+                                uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *b0,
+                                const uint64_t *b1, const uint64_t *const *pts, const gq_evk *const *rk) {
+  if (he_check(c, l)) return 1;
+  if (!c0 || !c1 || !a0 || !a1 || !b0 || !b1 || !pts || !rk || n1 == 0 || n2 == 0) GQ_FAIL("bad argument");
+  ExpArgs a{l, 0, dim, 0, 0, n1, n2, nullptr, nullptr, rk};
+  const uint64_t *in[4] = {a0, a1, b0, b1};
+  return staged_call(c, 4, in, 2 * n1 * n2, pts, c0, c1, [](gq_ctx *c, uint64_t *const *io, const uint64_t *const *dp, void *p) {
+    const ExpArgs &a = *(const ExpArgs *)p;
+    return gq_he_slot2coeff_dev(c, a.l, a.n1, a.n2, a.dim_a, io[0], io[1], io[2], io[3], io[4], io[5], dp, a.rk, nullptr);
+  }, &a);
+}
+
 // -------------------------------------------------------------- HE primitives (host buffers)
 // stage up to 5 big polys in, run, copy up to 2 out
 struct HostIO {

@@ -19,7 +19,7 @@ struct GqHostModulus {
   void *blob = nullptr;
 };
 
-enum { GQ_SLOT_LIMB_A = 0, GQ_SLOT_LIMB_B, GQ_SLOT_BIG, GQ_SLOT_IO, GQ_SLOT_PIPE, GQ_SLOT_GEMV, GQ_SLOT_C2S, GQ_SLOT_COUNT };
+enum { GQ_SLOT_LIMB_A = 0, GQ_SLOT_LIMB_B, GQ_SLOT_BIG, GQ_SLOT_IO, GQ_SLOT_PIPE, GQ_SLOT_GEMV, GQ_SLOT_C2S, GQ_SLOT_EXP, GQ_SLOT_RLSIN, GQ_SLOT_COUNT };
 
 struct gq_ctx {
   int device = 0;

@@ -405,6 +405,108 @@ class HeContext:
         B_f = B_a * cpt.nu / float(self.Delta) + self.Brs
         return (HeCt(l - 2, outs[0], outs[1], nu_f, B_f), HeCt(l - 2, outs[2], outs[3], nu_f, B_f))
 
+    # ---- metadata replay: the (nu, B) updates of the reference, one per primitive ---------------------
+    def _m_mul(self, l, a, b):      # he-mult.c:93-95
+        return (a[0] * b[0], a[0] * b[1] + b[0] * a[1] + a[1] * b[1] + self.Bmult[l])
+
+    def _m_rs(self, a):             # he-rescale.c:36-38
+        return (a[0] / float(self.Delta), a[1] / float(self.Delta) + self.Brs)
+
+    @staticmethod
+    def _m_mulpt(a, ptnu):          # he-mult.c:162-164
+        return (a[0] * ptnu, a[1] * ptnu)
+
+    @staticmethod
+    def _m_add(a, b):               # he-add.c:36-38
+        return (max(a[0], b[0]), a[1] + b[1])
+
+    @staticmethod
+    def _m_addpt(a, ptnu):          # he-add.c:85-87
+        return (max(a[0], ptnu), a[1])
+
+    def _exp_meta(self, l, meta, ptnu, iters):
+        """(nu, B) of he_exp (src/he-algo.c:364-458) by replaying its primitives' updates in order."""
+        act = self._m_rs(self._m_mulpt(meta, ptnu))
+        k = l - 1
+        ct2 = self._m_rs(self._m_mul(k, act, act))
+        ct4 = self._m_rs(self._m_mul(k - 1, ct2, ct2))
+        lin = lambda: self._m_rs(self._m_mulpt(self._m_addpt(act, ptnu), ptnu))
+        ct01 = lin()
+        ct23 = self._m_rs(self._m_mul(k - 1, ct2, lin()))
+        ct0123 = self._m_add(ct01, ct23)
+        ct45 = lin()
+        ct67 = self._m_rs(self._m_mul(k - 1, ct2, lin()))
+        ct4567 = self._m_rs(self._m_mul(k - 2, ct4, self._m_add(ct45, ct67)))
+        out = self._m_add(ct0123, ct4567)
+        for t in range(iters):
+            out = self._m_rs(self._m_mul(k - 3 - t, out, out))
+        return out
+
+    def he_exp_encoded(self, ct: HeCt, pts, iters: int, rlk: HeEvk) -> HeCt:
+        """The ciphertext arithmetic of he_exp(ct_exp, a, ct, rlk, iter) (src/he-algo.c:435-458 over
+        he_exp_taylor, :364-433) with the plaintexts already encoded: pts[0] = he_ecd of a/2^iter in every
+        slot, pts[1..7] = he_const_pt of 1, 3, 1/6, 5, 1/120, 7, 1/5040.  One crossing (gq_he_exp)."""
+        pts = list(pts)
+        if len(pts) != 8:
+            raise GpqheError("he_exp: need 8 encoded plaintexts")
+        l = ct.l
+        c0 = np.empty((self.W, self.n), dtype=np.uint64)
+        c1 = np.empty_like(c0)
+        hold = [_c(p.m) for p in pts]
+        capi.check(self._lib, self._lib.gq_he_exp(
+            self._h, l, iters, self.mulpt_dim(l, pts[0].nu), self.mulpt_dim(l - 1, pts[1].nu), _ptr(c0), _ptr(c1),
+            _ptr(_c(ct.c0)), _ptr(_c(ct.c1)), (C.c_void_p * 8)(*[h.ctypes.data for h in hold]), rlk._h))
+        nu, B = self._exp_meta(l, (ct.nu, ct.B), pts[0].nu, iters)
+        return HeCt(l - 4 - iters, c0, c1, nu, B)
+
+    def he_rlsin_encoded(self, ct: HeCt, pts, iters: int, rlk: HeEvk, ck: HeEvk) -> HeCt:
+        """The ciphertext arithmetic of he_rlsin(ct_dest, a, ct, rlk, ck, iter) (src/he-bootstrap.c:444-475):
+        pts[0..7] as he_exp_encoded (pts[0] encodes i*a/2^iter), pts[8] = he_ecd of 1/(2*i*a)."""
+        pts = list(pts)
+        if len(pts) != 9:
+            raise GpqheError("he_rlsin: need 9 encoded plaintexts")
+        l = ct.l
+        c0 = np.empty((self.W, self.n), dtype=np.uint64)
+        c1 = np.empty_like(c0)
+        hold = [_c(p.m) for p in pts]
+        m = l - 4 - iters
+        capi.check(self._lib, self._lib.gq_he_rlsin(
+            self._h, l, iters, self.mulpt_dim(l, pts[0].nu), self.mulpt_dim(l - 1, pts[1].nu),
+            self.mulpt_dim(max(m, 0), pts[8].nu), _ptr(c0), _ptr(c1), _ptr(_c(ct.c0)), _ptr(_c(ct.c1)),
+            (C.c_void_p * 9)(*[h.ctypes.data for h in hold]), rlk._h, ck._h))
+        e = self._exp_meta(l, (ct.nu, ct.B), pts[0].nu, iters)
+        nu, B = self._m_rs(self._m_mulpt(self._m_add(e, e), pts[8].nu))      # he_conj keeps nu and B; he_sub as he_add
+        return HeCt(m - 1, c0, c1, nu, B)
+
+    def he_slot2coeff_encoded(self, ct0: HeCt, ct1: HeCt, pts2, n1: int, n2: int, rk) -> HeCt:
+        """The ciphertext arithmetic of he_slot2coeff(ct, ct0, ct1, rk) (src/he-bootstrap.c:414-438):
+        he_gemv(U0, ct0) + he_gemv(U1, ct1) with pts2 = the encoded diagonals of U0 and of U1."""
+        m = n1 * n2
+        flat = [p for part in pts2 for p in part]
+        if len(flat) != 2 * m or ct0.l != ct1.l:
+            raise GpqheError("he_slot2coeff: need 2 x n1*n2 encoded diagonals and equal levels")
+        l = ct0.l
+        c0 = np.empty((self.W, self.n), dtype=np.uint64)
+        c1 = np.empty_like(c0)
+        hold = [_c(p.m) for p in flat]
+        keys = (C.c_void_p * m)(*[(rk[r]._h if (r < n1 or r % n1 == 0) else None) for r in range(m)])
+        capi.check(self._lib, self._lib.gq_he_slot2coeff(
+            self._h, l, n1, n2, self.mulpt_dim(l, flat[0].nu), _ptr(c0), _ptr(c1), _ptr(_c(ct0.c0)), _ptr(_c(ct0.c1)),
+            _ptr(_c(ct1.c0)), _ptr(_c(ct1.c1)), (C.c_void_p * (2 * m))(*[h.ctypes.data for h in hold]), keys))
+        metas = []
+        for part, src in enumerate((ct0, ct1)):
+            nu_o = B_o = 0.0
+            for i in range(n2):
+                nu_i = B_i = 0.0
+                for j in range(n1):
+                    pt = flat[part * m + i * n1 + j]
+                    nu_t, B_t = src.nu * pt.nu, src.B * pt.nu
+                    nu_i, B_i = (nu_t, B_t) if j == 0 else (max(nu_i, nu_t), B_i + B_t)
+                nu_o, B_o = (nu_i, B_i) if i == 0 else (max(nu_o, nu_i), B_o + B_i)
+            metas.append(self._m_rs((nu_o, B_o)))
+        nu, B = self._m_add(*metas)
+        return HeCt(l - 1, c0, c1, nu, B)
+
     def he_mul_rs(self, ct1: HeCt, ct2: HeCt, rlk: HeEvk) -> HeCt:
         """he_mul then he_rs on the product, one crossing (gq_he_mul_rs)."""
         return self.he_mul_batch([(ct1, ct2)], rlk, rescale=True, fused_single=True)[0]

@@ -179,6 +179,26 @@ int gq_he_coeff2slot(gq_ctx *ctx, unsigned l, unsigned n1, unsigned n2, unsigned
                      uint64_t *re0, uint64_t *re1, uint64_t *im0, uint64_t *im1, const uint64_t *a0,
                      const uint64_t *a1, const uint64_t *const *pts, const uint64_t *cpt, const gq_evk *ck,
                      const gq_evk *const *rk);
+/* he_exp (src/he-algo.c:435-458 over he_exp_taylor, :364-433): exp(a*ct) as the reference evaluates it - he_mulpt
+   by the encoded a/2^iter, he_rs, the degree-7 Taylor polynomial in the reference's evaluation order, `iter`
+   squarings - with every intermediate ciphertext on the device.  pts[0] = he_ecd of a/2^iter in every slot,
+   pts[1..7] = he_const_pt of 1, 3, 1/6, 5, 1/120, 7, 1/5040 (uint64_t[W][n] each, encoded by the caller: host
+   floating point); dim_a / dim_t = he_mulpt limb counts (he-mult.c:168) at levels l and l-1.  Needs
+   l >= 4 + iter; result at level l-4-iter. */
+int gq_he_exp(gq_ctx *ctx, unsigned l, unsigned iter, unsigned dim_a, unsigned dim_t, uint64_t *c0, uint64_t *c1,
+              const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts, const gq_evk *rlk);
+/* he_rlsin (src/he-bootstrap.c:444-475; the EvalMod step of he_bootstrap, :518-520): sin(a*ct)/a =
+   he_rs(he_mulpt(he_sub(e, he_conj(e)), pts[8])) with e = he_exp(i*a*ct).  pts[0..7] as gq_he_exp (pts[0]
+   encodes i*a/2^iter), pts[8] = he_ecd of 1/(2*i*a); dim_f = he_mulpt limb count at level l-4-iter.  Needs
+   l >= 5 + iter; result at level l-5-iter. */
+int gq_he_rlsin(gq_ctx *ctx, unsigned l, unsigned iter, unsigned dim_a, unsigned dim_t, unsigned dim_f,
+                uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
+                const gq_evk *rlk, const gq_evk *ck);
+/* he_slot2coeff (src/he-bootstrap.c:414-438): he_gemv(U0, ct0) + he_gemv(U1, ct1); (a0,a1) = ct0, (b0,b1) = ct1,
+   pts = the encoded diagonals of U0 then of U1 (2 sets of n1*n2 as gq_he_gemv wants them).  Result at level l-1. */
+int gq_he_slot2coeff(gq_ctx *ctx, unsigned l, unsigned n1, unsigned n2, unsigned dim, uint64_t *c0, uint64_t *c1,
+                     const uint64_t *a0, const uint64_t *a1, const uint64_t *b0, const uint64_t *b1,
+                     const uint64_t *const *pts, const gq_evk *const *rk);
 /* he_add / he_sub (src/he-add.c:32-76), he_addpt / he_subpt (:79-120: only c0 meets the plaintext,
    c1 is reduced), he_neg (:123-140, in place): out = smod_{q_l}(a op b); outputs may alias inputs */
 int gq_he_add(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
@@ -226,6 +246,15 @@ int gq_he_coeff2slot_dev(gq_ctx *ctx, unsigned l, unsigned n1, unsigned n2, unsi
                          uint64_t *re0, uint64_t *re1, uint64_t *im0, uint64_t *im1, const uint64_t *a0,
                          const uint64_t *a1, const uint64_t *const *pts, const uint64_t *cpt, const gq_evk *ck,
                          const gq_evk *const *rk, void *stream);
+int gq_he_exp_dev(gq_ctx *ctx, unsigned l, unsigned iter, unsigned dim_a, unsigned dim_t, uint64_t *c0,
+                  uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *const *pts,
+                  const gq_evk *rlk, void *stream);
+int gq_he_rlsin_dev(gq_ctx *ctx, unsigned l, unsigned iter, unsigned dim_a, unsigned dim_t, unsigned dim_f,
+                    uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
+                    const uint64_t *const *pts, const gq_evk *rlk, const gq_evk *ck, void *stream);
+int gq_he_slot2coeff_dev(gq_ctx *ctx, unsigned l, unsigned n1, unsigned n2, unsigned dim, uint64_t *c0,
+                         uint64_t *c1, const uint64_t *a0, const uint64_t *a1, const uint64_t *b0,
+                         const uint64_t *b1, const uint64_t *const *pts, const gq_evk *const *rk, void *stream);
 int gq_he_add_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,
                   const uint64_t *b0, const uint64_t *b1, void *stream);
 int gq_he_sub_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0, const uint64_t *a1,

@@ -462,6 +462,41 @@ def he_coeff2slot_encoded(ctx: Ctx, ct: dict, pts4: list, cpt: list, dim_gemv: i
     return tuple(out)
 
 
+def he_exp_encoded(ctx: Ctx, ct: dict, pts: list, dim_a: int, dim_t: int, iters: int, rlk) -> dict:
+    """src/he-algo.c:435-458 (he_exp) over he_exp_taylor (:364-433) with the plaintexts given: pts[0] =
+    coefficients of he_ecd(a/2^iter), pts[1..7] = he_const_pt of 1, 3, 1/6, 5, 1/120, 7, 1/5040.  The same
+    primitives in the same order as the reference."""
+    act = he_rs(ctx, he_mulpt(ctx, ct, pts[0], dim_a))                       # :448-449
+    ct2 = he_rs(ctx, he_mul(ctx, act, act, rlk))                             # :378-379
+    ct4 = he_rs(ctx, he_mul(ctx, ct2, ct2, rlk))                             # :381-382
+    lin = lambda ka, km: he_rs(ctx, he_mulpt(ctx, he_addpt(ctx, act, pts[ka]), pts[km], dim_t))
+    ct01 = he_moddown(ctx, lin(1, 1))                                        # :384-388
+    ct23 = he_rs(ctx, he_mul(ctx, ct2, lin(2, 3), rlk))                      # :390-396
+    ct0123 = he_moddown(ctx, he_add(ctx, ct01, ct23))                        # :398-399
+    ct45 = he_moddown(ctx, lin(4, 5))                                        # :401-406
+    ct67 = he_rs(ctx, he_mul(ctx, ct2, lin(6, 7), rlk))                      # :408-414
+    ct4567 = he_rs(ctx, he_mul(ctx, ct4, he_add(ctx, ct45, ct67), rlk))      # :416-418
+    out = he_add(ctx, ct0123, ct4567)                                        # :420
+    for _ in range(iters):                                                   # :451-454
+        out = he_rs(ctx, he_mul(ctx, out, out, rlk))
+    return out
+
+
+def he_rlsin_encoded(ctx: Ctx, ct: dict, pts: list, dim_a: int, dim_t: int, dim_f: int, iters: int,
+                     rlk, ck) -> dict:
+    """src/he-bootstrap.c:444-475: pts[0..7] as he_exp_encoded (pts[0] encodes i*a/2^iter), pts[8] =
+    he_ecd(1/(2*i*a))."""
+    e = he_exp_encoded(ctx, ct, pts, dim_a, dim_t, iters, rlk)
+    en = he_conj(ctx, e, ck)
+    return he_rs(ctx, he_mulpt(ctx, he_sub(ctx, e, en), pts[8], dim_f))
+
+
+def he_slot2coeff_encoded(ctx: Ctx, ct0: dict, ct1: dict, pts2: list, dim: int, n1: int, n2: int, rk) -> dict:
+    """src/he-bootstrap.c:414-438: he_gemv(U0, ct0) + he_gemv(U1, ct1)."""
+    return he_add(ctx, he_gemv_encoded(ctx, ct0, pts2[0], dim, n1, n2, rk),
+                  he_gemv_encoded(ctx, ct1, pts2[1], dim, n1, n2, rk))
+
+
 # --------------------------------------------------------------------------- #
 # packed-word interchange format used at the C-ABI (include/gpqhe_b200.h):
 # word-major two's complement, words[w, i] = bits 64w..64w+63 of coefficient i

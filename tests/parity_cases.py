@@ -4,6 +4,7 @@ import os
 import random
 
 import numpy as np
+from pytest import raises as pytest_raises
 
 import gpqhe_b200 as g
 from oracle import pyoracle as o
@@ -317,5 +318,78 @@ def check_coeff2slot(lib_path, logn, q, Delta, n1=2, n2=2, logqub=0, seed=5, lan
         for name, got, want in (("real", re, wre), ("imag", im, wim)):
             assert got.l == want["l"] == l - 2
             assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], ("he_coeff2slot", name)
+    finally:
+        ctx.close()
+
+
+def check_rlsin(lib_path, logn, q, Delta, iters=1, logqub=0, seed=7, lanes=1, start_level=None):
+    """Device-resident he_exp and he_rlsin (src/he-algo.c:364-458, src/he-bootstrap.c:444-475: the EvalMod
+    step of bootstrapping) vs the oracle's restatement of the same compositions, plaintexts given."""
+    rng = random.Random(seed)
+    ctx = g.HeContext(logn, q, 4, Delta, lib_path=lib_path, logqub=logqub)
+    oc = o.Ctx(logn, q, 4, Delta, logqub=logqub or None)
+    try:
+        if lanes > 1:
+            ctx.set_lanes(lanes)
+        n, W = ctx.n, ctx.W
+        l = ctx.L if start_level is None else start_level
+        assert l >= 5 + iters
+        ql = oc.ql[l]
+        a0, a1 = rpoly(rng, ql, n), rpoly(rng, ql, n)
+        rlk = (rlimbs(rng, oc.primes, n, oc.dimevk), rlimbs(rng, oc.primes, n, oc.dimevk))
+        ckey = (rlimbs(rng, oc.primes, n, oc.dimevk), rlimbs(rng, oc.primes, n, oc.dimevk))
+        drlk, dck = ctx.genevk(*rlk), ctx.genevk(*ckey)
+        nu = float(Delta)
+        # pts[0], pts[8]: he_ecd output (dense, |m| around Delta); pts[1..7]: he_const_pt (coefficients 0 and n/2)
+        dense = lambda: [rng.randrange(2 * Delta) - Delta for _ in range(n)]
+        ms = [dense()]
+        for k in range(7):
+            cm = [0] * n
+            cm[0] = rng.randrange(8 * Delta) if k % 2 == 0 else rng.randrange(Delta)
+            ms.append(cm)
+        ms.append(dense())
+        pts = [g.HePt(g.ints_to_big(m, W), nu=nu) for m in ms]
+        ct = g.HeCt(l, g.ints_to_big(a0, W), g.ints_to_big(a1, W), nu, 1.0)
+        dim_a, dim_t = ctx.mulpt_dim(l, nu), ctx.mulpt_dim(l - 1, nu)
+        got = ctx.he_exp_encoded(ct, pts[:8], iters, drlk)
+        want = o.he_exp_encoded(oc, {"l": l, "c0": a0, "c1": a1}, ms[:8], dim_a, dim_t, iters, rlk)
+        assert got.l == want["l"] == l - 4 - iters
+        assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], "he_exp"
+        got = ctx.he_rlsin_encoded(ct, pts, iters, drlk, dck)
+        want = o.he_rlsin_encoded(oc, {"l": l, "c0": a0, "c1": a1}, ms, dim_a, dim_t,
+                                  ctx.mulpt_dim(l - 4 - iters, nu), iters, rlk, ckey)
+        assert got.l == want["l"] == l - 5 - iters
+        assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], "he_rlsin"
+        with pytest_raises(g.GpqheError):
+            ctx.he_rlsin_encoded(g.HeCt(4 + iters, ct.c0, ct.c1, nu, 1.0), pts, iters, drlk, dck)
+    finally:
+        ctx.close()
+
+
+def check_slot2coeff(lib_path, logn, q, Delta, n1=2, n2=2, logqub=0, seed=11, lanes=1):
+    """Device-resident he_slot2coeff (src/he-bootstrap.c:414-438) vs the oracle's composition."""
+    rng = random.Random(seed)
+    slots = n1 * n2
+    ctx = g.HeContext(logn, q, slots, Delta, lib_path=lib_path, logqub=logqub)
+    oc = o.Ctx(logn, q, slots, Delta, logqub=logqub or None)
+    try:
+        if lanes > 1:
+            ctx.set_lanes(lanes)
+        n, W, l = ctx.n, ctx.W, ctx.L
+        ql = oc.ql[l]
+        cts = [(rpoly(rng, ql, n), rpoly(rng, ql, n)) for _ in range(2)]
+        need = sorted(set(range(n1)) | {i * n1 for i in range(n2)})
+        keys = {r: (rlimbs(rng, oc.primes, n, oc.dimevk), rlimbs(rng, oc.primes, n, oc.dimevk)) for r in need}
+        dkeys = {r: ctx.genevk(*keys[r]) for r in need}
+        nu = float(Delta)
+        ms2 = [[[rng.randrange(2 * Delta) - Delta for _ in range(n)] for _ in range(slots)] for _ in range(2)]
+        pts2 = [[g.HePt(g.ints_to_big(m, W), nu=nu) for m in ms] for ms in ms2]
+        hc = [g.HeCt(l, g.ints_to_big(a, W), g.ints_to_big(b, W), nu, 1.0) for a, b in cts]
+        got = ctx.he_slot2coeff_encoded(hc[0], hc[1], pts2, n1, n2, dkeys)
+        want = o.he_slot2coeff_encoded(oc, {"l": l, "c0": cts[0][0], "c1": cts[0][1]},
+                                       {"l": l, "c0": cts[1][0], "c1": cts[1][1]}, ms2, ctx.mulpt_dim(l, nu),
+                                       n1, n2, keys)
+        assert got.l == want["l"] == l - 1
+        assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], "he_slot2coeff"
     finally:
         ctx.close()

@@ -115,3 +115,15 @@ def test_gemv_device_resident(emul_lib, logn, q, Delta, n1, n2):
 @pytest.mark.parametrize("logn,q,Delta,n1,n2,lanes", [(5, 1 << 120, 1 << 40, 2, 2, 1), (5, 1 << 438, 1 << 50, 2, 2, 3)])
 def test_coeff2slot_device_resident(emul_lib, logn, q, Delta, n1, n2, lanes):
     pc.check_coeff2slot(emul_lib, logn, q, Delta, n1, n2, logqub=q.bit_length() - 1, lanes=lanes)
+
+
+@pytest.mark.parametrize("logn,q,Delta,iters,lanes", [(4, 1 << 438, 1 << 50, 1, 1), (4, 1 << 438, 1 << 50, 3, 3),
+                                                     (3, 3 ** 150, 1 << 40, 0, 1)])
+def test_rlsin_device_resident(emul_lib, logn, q, Delta, iters, lanes):
+    """he_exp / he_rlsin (EvalMod of he_bootstrap): pow2 chain down to level 0, and an arbitrary q."""
+    pc.check_rlsin(emul_lib, logn, q, Delta, iters, logqub=q.bit_length() - 1, lanes=lanes)
+
+
+@pytest.mark.parametrize("logn,q,Delta,n1,n2,lanes", [(5, 1 << 120, 1 << 40, 2, 2, 1), (5, 1 << 438, 1 << 50, 2, 2, 3)])
+def test_slot2coeff_device_resident(emul_lib, logn, q, Delta, n1, n2, lanes):
+    pc.check_slot2coeff(emul_lib, logn, q, Delta, n1, n2, logqub=q.bit_length() - 1, lanes=lanes)

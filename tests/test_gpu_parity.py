@@ -110,3 +110,15 @@ def test_coeff2slot_device_resident(real_lib):
     giant steps spread over 3 compute lanes."""
     pc.check_coeff2slot(real_lib, 12, 1 << 109, 1 << 30, 4, 4, lanes=3)
     pc.check_coeff2slot(real_lib, 10, 1 << 120, 1 << 40, 2, 2, logqub=120, lanes=1)
+
+
+def test_rlsin_device_resident(real_lib):
+    """configs[4], EvalMod: he_exp + he_rlsin (7+iter he_mul, 5 he_mulpt, he_conj, ...) at N=2^11 on the KAT modulus
+    chain down to level 0, over compute lanes and on one stream."""
+    pc.check_rlsin(real_lib, 11, 1 << 438, 1 << 50, 3, logqub=438, lanes=3)
+    pc.check_rlsin(real_lib, 10, 1 << 438, 1 << 50, 1, logqub=438, lanes=1)
+
+
+def test_slot2coeff_device_resident(real_lib):
+    """configs[4], SlotToCoeff: two he_gemv + he_add at N=2^12, slots = 16."""
+    pc.check_slot2coeff(real_lib, 12, 1 << 109, 1 << 30, 4, 4, lanes=3)
