@@ -18,6 +18,8 @@
  *   he_add, he_sub, he_addpt, he_subpt, he_neg   src/he-add.c:32-142
  *   he_gemv                              src/he-algo.c:47-90 (device-resident loop)
  *   he_coeff2slot                        src/he-bootstrap.c:359-409 (device-resident composition)
+ *   he_exp                               src/he-algo.c:363-458 (device-resident composition)
+ *   he_rlsin                             src/he-bootstrap.c:444-475 (device-resident composition)
  *   polyctx_init/exit, hectx_init/exit   src/precomp.c:328-452 (wrappers: the reference
  *                                        builds its tables, we mirror them on the device)
  *   he_free_evk                          src/he-mem.c (wrapper: drops the device copy)
@@ -667,6 +669,144 @@ void he_coeff2slot(he_ct_t *ct_real, he_ct_t *ct_imag, const he_ct_t *ct, const 
   free(pts); free(keys);
   he_free_pt(&pt);
   he_free_pt(&cpt);
+}
+
+/* ---- he_exp (src/he-algo.c:363-458) and he_rlsin (src/he-bootstrap.c:444-475), device resident -------------
+ * The reference evaluates exp(a*ct) as he_mulpt by a/2^iter, a degree-7 Taylor polynomial (7 he_mul, 5 he_mulpt,
+ * he_addpt / he_add / he_rs / he_moddown between them) and `iter` squarings, every primitive a separate call on
+ * host ciphertexts.  Here only the encoding of the 8 (he_rlsin: 9) plaintexts stays on the host (he_ecd /
+ * he_const_pt: floating point); the ciphertext crosses once in and once out and gq_he_exp / gq_he_rlsin run the
+ * same primitives in the same order on the device.  Metadata: the reference's own updates, replayed in order. */
+struct meta { double nu, B; };
+static struct meta m_mul(unsigned l, struct meta a, struct meta b)            /* he-mult.c:93-95 */
+{
+  struct meta r = {a.nu * b.nu, (a.nu) * (b.B) + (b.nu) * (a.B) + (a.B) * (b.B) + hectx.bnd.Bmult[l]};
+  return r;
+}
+/* he_mul(&x, &y, &x): the destination aliases ct2, so the B statement reads the nu it has just written (he-mult.c:94-95) */
+static struct meta m_mul_d2(unsigned l, struct meta a, struct meta b)
+{
+  const double nu = a.nu * b.nu;
+  struct meta r = {nu, (a.nu) * (b.B) + (nu) * (a.B) + (a.B) * (b.B) + hectx.bnd.Bmult[l]};
+  return r;
+}
+/* he_mul(&x, &x, &x) */
+static struct meta m_sqr_inplace(unsigned l, struct meta a)
+{
+  const double nu = a.nu * a.nu;
+  struct meta r = {nu, (nu) * (a.B) + (nu) * (a.B) + (a.B) * (a.B) + hectx.bnd.Bmult[l]};
+  return r;
+}
+static struct meta m_rs(struct meta a) { struct meta r = {a.nu / hectx.Delta, a.B / hectx.Delta + hectx.bnd.Brs}; return r; }
+static struct meta m_mulpt(struct meta a, double ptnu) { struct meta r = {a.nu * ptnu, a.B * ptnu}; return r; }
+static struct meta m_add(struct meta a, struct meta b) { struct meta r = {(a.nu >= b.nu) ? a.nu : b.nu, a.B + b.B}; return r; }
+static struct meta m_addpt(struct meta a, double ptnu) { struct meta r = {(a.nu >= ptnu) ? a.nu : ptnu, a.B}; return r; }
+static struct meta m_lin(struct meta act, double ptnu) { return m_rs(m_mulpt(m_addpt(act, ptnu), ptnu)); }
+
+static struct meta exp_meta(unsigned l, struct meta in, double ptnu, unsigned iter)
+{
+  const struct meta act = m_rs(m_mulpt(in, ptnu));
+  const unsigned k = l - 1;
+  const struct meta ct2 = m_rs(m_mul(k, act, act));
+  const struct meta ct4 = m_rs(m_mul(k - 1, ct2, ct2));
+  const struct meta ct01 = m_lin(act, ptnu);
+  const struct meta ct23 = m_rs(m_mul_d2(k - 1, ct2, m_lin(act, ptnu)));
+  const struct meta ct0123 = m_add(ct01, ct23);
+  const struct meta ct45 = m_lin(act, ptnu);
+  const struct meta ct67 = m_rs(m_mul_d2(k - 1, ct2, m_lin(act, ptnu)));
+  const struct meta ct4567 = m_rs(m_mul_d2(k - 2, ct4, m_add(ct45, ct67)));
+  struct meta out = m_add(ct0123, ct4567);
+  for (unsigned t = 0; t < iter; t++) out = m_rs(m_sqr_inplace(k - 3 - t, out));
+  return out;
+}
+
+static unsigned mulpt_dim(unsigned l, double ptnu)                            /* he-mult.c:168 */
+{
+  return (gcry_mpi_get_nbits(hectx.q[l]) + log2(ptnu) + polyctx.logn) / GPQHE_LOGP + 1;
+}
+
+/* the 8 plaintexts of he_exp at dst (pts[0] = he_ecd of a/2^iter in every slot, he-algo.c:443-447; pts[1..7] =
+ * he_const_pt of the Taylor constants, he-algo.c:384-411); returns pt->nu (the same for all of them) */
+static double exp_plaintexts(_Complex double a, unsigned iter, uint64_t *dst, const uint64_t **pts, const char *who)
+{
+  static const double consts[7] = {1.0, 3.0, 1.0 / 6, 5.0, 1.0 / 120, 7.0, 1.0 / 5040};
+  const unsigned m = hectx.slots, W = G.info.W;
+  const size_t poly = (size_t)W * polyctx.n;
+  he_pt_t pt;
+  he_alloc_pt(&pt);
+  _Complex double *coeff = malloc(sizeof(_Complex double) * m);
+  if (!coeff) die(who);
+  a /= (1 << iter);
+  for (unsigned i = 0; i < m; i++) coeff[i] = a;
+  he_ecd(&pt, coeff);
+  poly_in(dst, &pt.m, W, who);
+  pts[0] = dst;
+  he_pt_t cpt;                        /* he_exp_taylor's own plaintext: he_const_pt writes coefficients 0 and n/2 only */
+  he_alloc_pt(&cpt);
+  for (unsigned k = 0; k < 7; k++) {
+    he_const_pt(&cpt, consts[k]);
+    poly_in(dst + (size_t)(k + 1) * poly, &cpt.m, W, who);
+    pts[k + 1] = dst + (size_t)(k + 1) * poly;
+  }
+  const double nu = pt.nu;
+  free(coeff);
+  he_free_pt(&pt);
+  he_free_pt(&cpt);
+  return nu;
+}
+
+void he_exp(he_ct_t *ct_exp, _Complex double a, const he_ct_t *ct, const he_evk_t *rlk, const unsigned int iter)
+{
+  const unsigned n = polyctx.n, W = G.info.W, l = ct->l;
+  const size_t poly = (size_t)W * n;
+  if (l < 4 + iter) { fprintf(stderr, "he_exp: level %u is below the 4+iter levels the evaluation consumes\n", l); errno = EINVAL; abort(); }
+  uint64_t *s = stage(12 * poly);
+  const uint64_t *pts[8];
+  poly_in(s, &ct->c0, W, __func__);
+  poly_in(s + poly, &ct->c1, W, __func__);
+  const double ptnu = exp_plaintexts(a, iter, s + 4 * poly, pts, __func__);
+  const struct meta in = {ct->nu, ct->B}, out = exp_meta(l, in, ptnu, iter);
+  CK(gq_he_exp(ctx(), l, iter, mulpt_dim(l, ptnu), mulpt_dim(l - 1, ptnu), s + 2 * poly, s + 3 * poly, s, s + poly,
+               pts, evk_dev(rlk)));
+  ct_exp->l = l - 4 - iter;
+  ct_exp->nu = out.nu;
+  ct_exp->B = out.B;
+  poly_out(&ct_exp->c0, s + 2 * poly, W);
+  poly_out(&ct_exp->c1, s + 3 * poly, W);
+}
+
+void he_rlsin(he_ct_t *ct_dest, const double a, const he_ct_t *ct, const he_evk_t *rlk, const he_evk_t *ck,
+              const unsigned int iter)
+{
+  const unsigned m = hectx.slots, n = polyctx.n, W = G.info.W, l = ct->l;
+  const size_t poly = (size_t)W * n;
+  if (l < 5 + iter) { fprintf(stderr, "he_rlsin: level %u is below the 5+iter levels the evaluation consumes\n", l); errno = EINVAL; abort(); }
+  uint64_t *s = stage(13 * poly);
+  const uint64_t *pts[9];
+  poly_in(s, &ct->c0, W, __func__);
+  poly_in(s + poly, &ct->c1, W, __func__);
+  const double ptnu = exp_plaintexts(a * I, iter, s + 4 * poly, pts, __func__);   /* he-bootstrap.c:458 */
+  he_pt_t pt;
+  he_alloc_pt(&pt);
+  _Complex double *coeff = malloc(sizeof(_Complex double) * m);
+  if (!coeff) die(__func__);
+  const _Complex double b = 1 / (2 * I * a);                                      /* he-bootstrap.c:465-468 */
+  for (unsigned i = 0; i < m; i++) coeff[i] = b;
+  he_ecd(&pt, coeff);
+  poly_in(s + 12 * poly, &pt.m, W, __func__);
+  pts[8] = s + 12 * poly;
+  const struct meta in = {ct->nu, ct->B}, e = exp_meta(l, in, ptnu, iter);
+  const struct meta out = m_rs(m_mulpt(m_add(e, e), pt.nu));       /* he_conj keeps nu, B; he_sub updates as he_add */
+  const unsigned lf = l - 4 - iter;
+  CK(gq_he_rlsin(ctx(), l, iter, mulpt_dim(l, ptnu), mulpt_dim(l - 1, ptnu), mulpt_dim(lf, pt.nu), s + 2 * poly,
+                 s + 3 * poly, s, s + poly, pts, evk_dev(rlk), evk_dev(ck)));
+  ct_dest->l = lf - 1;
+  ct_dest->nu = out.nu;
+  ct_dest->B = out.B;
+  poly_out(&ct_dest->c0, s + 2 * poly, W);
+  poly_out(&ct_dest->c1, s + 3 * poly, W);
+  free(coeff);
+  he_free_pt(&pt);
 }
 
 /* diagnostics for tests: coefficients marshalled in / out since load, and whether the direct

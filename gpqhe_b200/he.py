@@ -409,6 +409,14 @@ class HeContext:
     def _m_mul(self, l, a, b):      # he-mult.c:93-95
         return (a[0] * b[0], a[0] * b[1] + b[0] * a[1] + a[1] * b[1] + self.Bmult[l])
 
+    def _m_mul_d2(self, l, a, b):   # he_mul(&x, &y, &x): B reads the nu just written (he-mult.c:94-95)
+        nu = a[0] * b[0]
+        return (nu, a[0] * b[1] + nu * a[1] + a[1] * b[1] + self.Bmult[l])
+
+    def _m_sqr_inplace(self, l, a):  # he_mul(&x, &x, &x)
+        nu = a[0] * a[0]
+        return (nu, nu * a[1] + nu * a[1] + a[1] * a[1] + self.Bmult[l])
+
     def _m_rs(self, a):             # he-rescale.c:36-38
         return (a[0] / float(self.Delta), a[1] / float(self.Delta) + self.Brs)
 
@@ -425,21 +433,22 @@ class HeContext:
         return (max(a[0], ptnu), a[1])
 
     def _exp_meta(self, l, meta, ptnu, iters):
-        """(nu, B) of he_exp (src/he-algo.c:364-458) by replaying its primitives' updates in order."""
+        """(nu, B) of he_exp (src/he-algo.c:364-458) by replaying its primitives' updates in order, including
+        the aliased he_mul calls whose B statement reads the nu it has just overwritten."""
         act = self._m_rs(self._m_mulpt(meta, ptnu))
         k = l - 1
         ct2 = self._m_rs(self._m_mul(k, act, act))
         ct4 = self._m_rs(self._m_mul(k - 1, ct2, ct2))
         lin = lambda: self._m_rs(self._m_mulpt(self._m_addpt(act, ptnu), ptnu))
         ct01 = lin()
-        ct23 = self._m_rs(self._m_mul(k - 1, ct2, lin()))
+        ct23 = self._m_rs(self._m_mul_d2(k - 1, ct2, lin()))
         ct0123 = self._m_add(ct01, ct23)
         ct45 = lin()
-        ct67 = self._m_rs(self._m_mul(k - 1, ct2, lin()))
-        ct4567 = self._m_rs(self._m_mul(k - 2, ct4, self._m_add(ct45, ct67)))
+        ct67 = self._m_rs(self._m_mul_d2(k - 1, ct2, lin()))
+        ct4567 = self._m_rs(self._m_mul_d2(k - 2, ct4, self._m_add(ct45, ct67)))
         out = self._m_add(ct0123, ct4567)
         for t in range(iters):
-            out = self._m_rs(self._m_mul(k - 3 - t, out, out))
+            out = self._m_rs(self._m_sqr_inplace(k - 3 - t, out))
         return out
 
     def he_exp_encoded(self, ct: HeCt, pts, iters: int, rlk: HeEvk) -> HeCt:

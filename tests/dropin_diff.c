@@ -50,6 +50,9 @@ void gpqhe_ref_he_subpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt);
 void gpqhe_ref_he_neg(he_ct_t *ct);
 void gpqhe_ref_he_gemv(he_ct_t *ct_dest, const _Complex double *A, const he_ct_t *ct, const he_evk_t *rk);
 void gpqhe_ref_he_coeff2slot(he_ct_t *ct_real, he_ct_t *ct_imag, const he_ct_t *ct, const he_evk_t *ck, const he_evk_t *rk);
+void gpqhe_ref_he_exp(he_ct_t *ct_exp, _Complex double a, const he_ct_t *ct, const he_evk_t *rlk, const unsigned int iter);
+void gpqhe_ref_he_rlsin(he_ct_t *ct_dest, const double a, const he_ct_t *ct, const he_evk_t *rlk, const he_evk_t *ck,
+                        const unsigned int iter);
 void gpqhe_dropin_stats(unsigned long long *in, unsigned long long *out, int *fast_mpi);
 
 static unsigned npass, nfail;
@@ -220,6 +223,20 @@ int main(int argc, char **argv)
     report("he_coeff2slot (imag)", eq_ct(&gi, &ri));
     he_bootstrapctx_exit();
     he_free_ct(&gi); he_free_ct(&ri);
+  }
+
+  /* ---- he_exp (src/he-algo.c:363-458) and he_rlsin (src/he-bootstrap.c:444-475, EvalMod of he_bootstrap): one
+   * device-resident call each vs the reference's own compositions (about 30 primitive calls on host ciphertexts).
+   * Needs 5+iter levels; DROPIN_DIFF_NO_EXP=1 skips it (the CPU side takes minutes at N=2^16). */
+  if (hectx.L >= 6 && !getenv("DROPIN_DIFF_NO_EXP")) {
+    const unsigned iter = hectx.L >= 8 ? 2 : 1;
+    const _Complex double a = 0.37 - 0.21 * I;
+    he_exp(&g, a, &c1, &rlk, iter); gpqhe_ref_he_exp(&r, a, &c1, &rlk, iter);
+    report("he_exp", eq_ct(&g, &r));
+    if (!eq_ct(&g, &r)) printf("  l %u/%u nu %.17g/%.17g B %.17g/%.17g c0 %d c1 %d\n", g.l, r.l, g.nu, r.nu, g.B, r.B, eq_poly(&g.c0, &r.c0), eq_poly(&g.c1, &r.c1));
+    he_copy_ct(&g, &c2); he_copy_ct(&r, &c2);
+    he_rlsin(&g, 1.7, &g, &rlk, &ck, iter); gpqhe_ref_he_rlsin(&r, 1.7, &r, &rlk, &ck, iter);   /* in place, as he_bootstrap calls it */
+    report("he_rlsin (in place)", eq_ct(&g, &r));
   }
 
   unsigned long long in = 0, out = 0;
