@@ -456,10 +456,49 @@ def run_ours(args):
         c2s = {"coeff2slot_per_s": world * reps / (ms_c * 1e-3), "ms_per_coeff2slot": ms_c / reps, "slots": 16,
                "ops": "1 he_conj, 4 he_gemv (each 4 hoisted + 4 plain rotations, 16 he_mulpt, 15 he_add, 1 he_rs), 2 he_add, "
                       "2 he_mulpt, 2 he_rs",
-               "note": "configs[4] as far as the reference implements it (he_coeff2slot; he_bootstrap / EvalMod / "
-                       "he_slot2coeff are not in gpqhe.h, SURVEY fact 9); gq_he_coeff2slot_dev, every intermediate in HBM"}
+               "note": "configs[4], CoeffToSlot (he_coeff2slot, src/he-bootstrap.c:359-409): gq_he_coeff2slot_dev, every "
+                       "intermediate in HBM"}
+        # configs[4], the rest of the chain the reference's he_bootstrap composes (src/he-bootstrap.c:477-545):
+        # EvalMod = he_rlsin on both halves (he_exp: he_mulpt, he_rs, degree-7 Taylor polynomial with 7 he_mul,
+        # then he_conj, he_sub, he_mulpt, he_rs), SlotToCoeff = 2 he_gemv + he_add.  L = 8 leaves iter = 0:
+        # coeff2slot 8 -> 6, rlsin 6 -> 1, slot2coeff 1 -> 0.  Every intermediate ciphertext stays in HBM.
+        dim_at = lambda lv: int((LOGQ - (L - lv) * LOGDELTA + 1 + math.log2(float(1 << LOGDELTA)) + LOGN) / 59 + 1)
+        epts = gpts[:9].clone()
+        epts[1:8, :, 1:] = 0                                                             # he_const_pt: coefficient 0 only
+        eptsv = (C.c_void_p * 9)(*[epts.data_ptr() + k * poly for k in range(9)])
+        sptsv = (C.c_void_p * (2 * NROT))(*[cpts.data_ptr() + k * poly for k in range(2 * NROT)])
+        eout = torch.empty((4, W, n), dtype=torch.int64, device=dev)
+        bout = torch.empty((2, W, n), dtype=torch.int64, device=dev)
+
+        def evalmod_step(i, inp=None):
+            x = cout if inp is None else inp
+            for part in range(2):
+                a = x.data_ptr() + 2 * part * poly
+                o = eout.data_ptr() + 2 * part * poly
+                ck(lib.gq_he_rlsin_dev(h, L - 2, 0, dim_at(L - 2), dim_at(L - 3), dim_at(L - 6), o, o + poly, a, a + poly,
+                                       eptsv, evk._h, rks[1]._h, None))
+        ms_e = timed(evalmod_step, reps, 2)
+
+        def boot_step(i):
+            c2s_step(i)
+            evalmod_step(i)
+            ck(lib.gq_he_slot2coeff_dev(h, L - 7, 4, 4, dim_at(L - 7), bout.data_ptr(), bout.data_ptr() + poly,
+                                        eout.data_ptr(), eout.data_ptr() + poly, eout.data_ptr() + 2 * poly,
+                                        eout.data_ptr() + 3 * poly, sptsv, keys, None))
+        ms_b = timed(boot_step, reps, 2)
+        evalmod = {"rlsin_per_s": world * reps * 2 / (ms_e * 1e-3), "ms_per_rlsin": ms_e / (reps * 2), "iter": 0,
+                   "levels": f"{L - 2} -> {L - 7}",
+                   "ops": "per he_rlsin: 7 he_mul, 6 he_mulpt, 13 he_rs/he_moddown, 4 he_addpt, 3 he_add/he_sub, 1 he_conj",
+                   "note": "gq_he_rlsin_dev (src/he-bootstrap.c:444-475 over he_exp, src/he-algo.c:364-458): EvalMod of "
+                           "he_bootstrap on one half; every intermediate ciphertext in HBM"}
+        bootstrap = {"chains_per_s": world * reps / (ms_b * 1e-3), "ms_per_chain": ms_b / reps, "slots": 16,
+                     "levels": f"{L} -> 0",
+                     "note": "he_coeff2slot -> 2 x he_rlsin (iter = 0) -> he_slot2coeff, the ciphertext arithmetic of "
+                             "he_bootstrap (src/he-bootstrap.c:477-545) as far as L = 8 levels reach, device resident "
+                             "end to end (synthetic encoded plaintexts; the reference's own he_bootstrap is unfinished, "
+                             "SURVEY fact 9)"}
         return {"he_rot_per_s": world * nrot / (ms_rot * 1e-3), "ms_per_rot": ms_rot / nrot, "rotations": NROT, "gemv": gemv,
-                "coeff2slot": c2s,
+                "coeff2slot": c2s, "evalmod": evalmod, "bootstrap_chain": bootstrap,
                 "keyswitch_limbs": D2, "note": f"he_rot at l=L, 16 distinct rotation keys (384 MiB) cycled, independent rotations over {LANES} lanes",
                 "single_stream": {"he_rot_per_s": world * nrot / (ms_rot1 * 1e-3), "ms_per_rot": ms_rot1 / nrot},
                 "hoisted": {"he_rot_per_s": world * reps * NROT / (ms_h * 1e-3), "ms_per_rot": ms_h / (reps * NROT),

@@ -55,6 +55,19 @@ void gpqhe_ref_he_rlsin(he_ct_t *ct_dest, const double a, const he_ct_t *ct, con
                         const unsigned int iter);
 void gpqhe_dropin_stats(unsigned long long *in, unsigned long long *out, int *fast_mpi);
 
+#include <time.h>
+static double now_ms(void)
+{
+  struct timespec t;
+  clock_gettime(CLOCK_MONOTONIC, &t);
+  return t.tv_sec * 1e3 + t.tv_nsec * 1e-6;
+}
+/* wall time of the drop-in symbol (host marshalling + crossings + kernels) next to the reference's definition: pure
+ * CPU for the primitives; for the compositions marked * the reference's host loop, whose primitive calls bind to the
+ * drop-in's GPU symbols (one crossing per primitive) */
+#define TIMED2(label, ours, ref) do { double t0 = now_ms(); ours; double t1 = now_ms(); ref; double t2 = now_ms(); \
+  printf("  time %-28s drop-in %10.3f ms   reference %12.3f ms   x%.1f\n", label, t1 - t0, t2 - t1, (t2 - t1) / (t1 - t0 > 1e-6 ? t1 - t0 : 1e-6)); } while (0)
+
 static unsigned npass, nfail;
 static void report(const char *name, int ok)
 {
@@ -168,9 +181,10 @@ int main(int argc, char **argv)
   }
 
   /* ---- HE primitives, walking down the levels like tests/gpqhe.c does */
-  he_mul(&g, &c1, &c2, &rlk); gpqhe_ref_he_mul(&r, &c1, &c2, &rlk);
+  he_mul(&g, &c1, &c2, &rlk);                                       /* first use uploads the key */
+  TIMED2("he_mul", he_mul(&g, &c1, &c2, &rlk), gpqhe_ref_he_mul(&r, &c1, &c2, &rlk));
   report("he_mul", eq_ct(&g, &r));
-  he_rs(&g); gpqhe_ref_he_rs(&r);
+  TIMED2("he_rs", he_rs(&g), gpqhe_ref_he_rs(&r));
   report("he_rs", eq_ct(&g, &r));
   he_mulpt(&g, &g, &pt2); gpqhe_ref_he_mulpt(&r, &r, &pt2);      /* dest aliases src */
   report("he_mulpt (in place)", eq_ct(&g, &r));
@@ -207,7 +221,7 @@ int main(int argc, char **argv)
     _Complex double *A = malloc(sizeof(_Complex double) * slots * slots);
     for (unsigned i = 0; i < slots * slots; i++)
       A[i] = ((double)(rnd() % 2001) - 1000.0) / 1000.0 + (((double)(rnd() % 2001) - 1000.0) / 1000.0) * I;
-    he_gemv(&g, A, &c1, rk); gpqhe_ref_he_gemv(&r, A, &c1, rk);
+    TIMED2("he_gemv *", he_gemv(&g, A, &c1, rk), gpqhe_ref_he_gemv(&r, A, &c1, rk));
     report("he_gemv", eq_ct(&g, &r));
     he_copy_ct(&g, &c2); he_copy_ct(&r, &c2);
     he_gemv(&g, A, &g, rk); gpqhe_ref_he_gemv(&r, A, &r, rk);     /* dest aliases src (he_sum does this) */
@@ -218,7 +232,7 @@ int main(int argc, char **argv)
     he_ct_t gi, ri;
     he_alloc_ct(&gi); he_alloc_ct(&ri);
     he_bootstrapctx_init();
-    he_coeff2slot(&g, &gi, &c1, &ck, rk); gpqhe_ref_he_coeff2slot(&r, &ri, &c1, &ck, rk);
+    TIMED2("he_coeff2slot *", he_coeff2slot(&g, &gi, &c1, &ck, rk), gpqhe_ref_he_coeff2slot(&r, &ri, &c1, &ck, rk));
     report("he_coeff2slot (real)", eq_ct(&g, &r));
     report("he_coeff2slot (imag)", eq_ct(&gi, &ri));
     he_bootstrapctx_exit();
@@ -231,11 +245,11 @@ int main(int argc, char **argv)
   if (hectx.L >= 6 && !getenv("DROPIN_DIFF_NO_EXP")) {
     const unsigned iter = hectx.L >= 8 ? 2 : 1;
     const _Complex double a = 0.37 - 0.21 * I;
-    he_exp(&g, a, &c1, &rlk, iter); gpqhe_ref_he_exp(&r, a, &c1, &rlk, iter);
+    TIMED2("he_exp *", he_exp(&g, a, &c1, &rlk, iter), gpqhe_ref_he_exp(&r, a, &c1, &rlk, iter));
     report("he_exp", eq_ct(&g, &r));
     if (!eq_ct(&g, &r)) printf("  l %u/%u nu %.17g/%.17g B %.17g/%.17g c0 %d c1 %d\n", g.l, r.l, g.nu, r.nu, g.B, r.B, eq_poly(&g.c0, &r.c0), eq_poly(&g.c1, &r.c1));
     he_copy_ct(&g, &c2); he_copy_ct(&r, &c2);
-    he_rlsin(&g, 1.7, &g, &rlk, &ck, iter); gpqhe_ref_he_rlsin(&r, 1.7, &r, &rlk, &ck, iter);   /* in place, as he_bootstrap calls it */
+    TIMED2("he_rlsin *", he_rlsin(&g, 1.7, &g, &rlk, &ck, iter), gpqhe_ref_he_rlsin(&r, 1.7, &r, &rlk, &ck, iter));   /* in place, as he_bootstrap calls it */
     report("he_rlsin (in place)", eq_ct(&g, &r));
   }
 
