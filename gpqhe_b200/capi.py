@@ -63,6 +63,7 @@ SIGNATURES = {
     "gq_poly_conj": (C.c_int, [vp, vp, vp, C.c_uint]),
     "gq_evk_create": (C.c_int, [vp, C.POINTER(vp), vp, vp]),
     "gq_evk_create_dev": (C.c_int, [vp, C.POINTER(vp), vp, vp]),
+    "gq_evk_export": (C.c_int, [vp, vp, vp]),
     "gq_evk_destroy": (None, [vp]),
     "gq_he_mul": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp]),
     "gq_he_add": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp]),

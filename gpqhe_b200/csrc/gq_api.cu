@@ -776,6 +776,16 @@ extern "C" int gq_evk_create_dev(gq_ctx *c, gq_evk **evk, const uint64_t *p0, co
   *evk = e;
   return 0;
 }
+// wire format support: the device copy of a key back to the host, he_evk_t layout
+extern "C" int gq_evk_export(const gq_evk *e, uint64_t *p0, uint64_t *p1) {
+  if (!e || !e->ctx || !p0 || !p1) GQ_FAIL("null argument");
+  const gq_ctx *c = e->ctx;
+  const size_t bytes = (size_t)c->dimevk * c->n * 8;
+  GQ_CUDA(cudaSetDevice(c->device));
+  GQ_CUDA(cudaMemcpy(p0, e->p0, bytes, cudaMemcpyDeviceToHost));
+  GQ_CUDA(cudaMemcpy(p1, e->p1, bytes, cudaMemcpyDeviceToHost));
+  return 0;
+}
 extern "C" void gq_evk_destroy(gq_evk *e) {
   if (!e) return;
   if (e->owned) { cudaFree(e->p0); cudaFree(e->p1); }

@@ -135,6 +135,10 @@ int gq_poly_conj(gq_ctx *ctx, uint64_t *r, const uint64_t *a, unsigned W);
 /* upload a key laid out as he_evk_t (src/gpqhe.h:78-82): p0, p1 = uint64_t[dimevk][n] */
 int gq_evk_create(gq_ctx *ctx, gq_evk **evk, const uint64_t *p0, const uint64_t *p1);
 int gq_evk_create_dev(gq_ctx *ctx, gq_evk **evk, const uint64_t *p0_dev, const uint64_t *p1_dev);
+/* the device copy of a key back into two host buffers of dimevk*n words each, he_evk_t layout (limb-major, ntt()
+   output order): what gpqhe_b200/wire.py serialises (the reference has no key wire format,
+   src/precomp.c:455-463 computes kemctx sizes nobody uses) */
+int gq_evk_export(const gq_evk *evk, uint64_t *p0, uint64_t *p1);
 void gq_evk_destroy(gq_evk *evk);
 
 /* ---- HE primitives, host pointers; every big poly is uint64_t[W][n], W = gq_info.W - */
