@@ -551,7 +551,7 @@ static int ntt_internal(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npo
     const GqPrime &P = c->primes[d];
     if (P.bits < 33 || P.bits > 60) { lazy = false; break; }
     const uint64_t top = 1ull << (P.bits - 1), cc = P.p - top;
-    if (cc >= (top >> 4)) lazy = false;
+    if (cc >= (top >> 5)) lazy = false;      // gq_ntt_lazy.cu: 32c < 2^sh
   }
   if (!lazy) return gq_ntt_batch_dev(c, limb0, nlimbs, npolys, data, (inverse ? 1 : 0) | (only << 1), (void *)st);
   if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");

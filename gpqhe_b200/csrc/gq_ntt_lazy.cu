@@ -12,12 +12,18 @@
 // which removes two of the three compare/select pairs of every butterfly (ncu of the exact
 // kernels: ALU pipe 59 %, math-pipe throttle the top stall - instruction count is the bound).
 //
-// Ranges (p < 2^64/15 is checked on the host, else the exact kernels are used):
+// Ranges (p = 2^sh + c with 32c < 2^sh and p < 2^60 is checked on the host, else the exact kernels are
+// used; so 30p < 2^64):
 //   forward CT butterfly: t = y*w - hi(y*wsh)*p in [0,2p) for ANY y < 2^64;
-//     x' = x + t, y' = x - t + 2p: bounds grow by 2p per stage, no reduction inside a round;
-//     one conditional subtraction of 8p per value per radix-8 round keeps round inputs < 8p
-//     (8p + 3*2p = 14p < 2^64); the last round ends with an exact reduction to [0,p).
-//   inverse GS butterfly: s = x + y (- 2p if >= 2p), d = x - y + 2p, y' = lazy d*w in [0,2p).
+//     x' = x + t, y' = x - t + 2p: every value grows by 2p per stage and nothing is reduced on the way:
+//     canonical input, logn stages -> (1 + 2 logn) p, at most 25p up to n = 2^12.  The two-kernel
+//     transforms (n >= 2^13) take ONE conditional subtraction of 16p per value when the last radix-8
+//     round loads its inputs (< 29p -> < 16p, + 6p = 22p at the end); the last round ends with an exact
+//     reduction to [0,p) (full_reduce: v < 27p).
+//   inverse GS butterfly: s = x + y, d = x - y + B*p (B*p = bound of y), y' = lazy d*w in [0,2p):
+//     differences come back below 2p, sums double their bound per stage (2p, 4p, 8p, 16p < 2^64), so a
+//     radix-8 round with inputs < 2p ends with bounds {16,8,4,4,2,2,2,2} p and only positions 0..3 are
+//     reduced (7 conditional subtractions per round instead of one per butterfly = 12).
 #include "gq_kernels.h"
 
 namespace {
@@ -43,16 +49,33 @@ GQ_DEV void bf_inv(uint64_t &x, uint64_t &y, uint64_t w, uint64_t wsh, uint64_t 
   x = s;
   y = mul_lazy(d, w, wsh, p);
 }
-// v < 15p  ->  v mod p.  p = 2^sh + c with 16c < 2^sh, so k = v >> sh is floor(v/p) or one more.
+// v < 27p  ->  v mod p.  p = 2^sh + c with 32c < 2^sh, so k = v >> sh (<= 27) is floor(v/p) or one more:
+// v - k*p = (v mod 2^sh) - k*c > -p.
 GQ_DEV uint64_t full_reduce(uint64_t v, uint64_t p, int sh) {
   const uint64_t k = v >> sh;
   const uint64_t r = v - k * p;
   return ((int64_t)r < 0) ? r + p : r;
 }
 
-struct PC { uint64_t p, p2, p8; int sh; };
+struct PC { uint64_t p, p2, p4, p8, p16; int sh; };
 GQ_DEV PC load_pc(const GqPrime &P) {
-  PC c; c.p = P.p; c.p2 = 2 * P.p; c.p8 = 8 * P.p; c.sh = (int)P.bits - 1; return c;
+  PC c; c.p = P.p; c.p2 = 2 * P.p; c.p4 = 4 * P.p; c.p8 = 8 * P.p; c.p16 = 16 * P.p; c.sh = (int)P.bits - 1; return c;
+}
+
+// lazy GS butterfly on values with the SAME known bound b*p (b = 2, 4, 8; compile-time after unrolling):
+// sum < 2b*p unreduced, difference + b*p multiplied lazily back into [0,2p)
+GQ_DEV uint64_t pmul(const PC &c, int b) { return b == 2 ? c.p2 : b == 4 ? c.p4 : c.p8; }
+GQ_DEV void bf_inv_lz(uint64_t &x, uint64_t &y, int b, uint64_t w, uint64_t wsh, const PC &c) {
+  const uint64_t d = x - y + pmul(c, b);
+  x = x + y;
+  y = mul_lazy(d, w, wsh, c.p);
+}
+// v < b*p -> v < 2p
+GQ_DEV uint64_t norm2p(uint64_t v, int b, const PC &c) {
+  if (b >= 16) v = csub(v, c.p8);
+  if (b >= 8) v = csub(v, c.p4);
+  if (b >= 4) v = csub(v, c.p2);
+  return v;
 }
 
 template <int NB>
@@ -81,9 +104,42 @@ GQ_DEV void fwd_round(uint64_t *v, int lo, int kq, const ulonglong2 *__restrict_
   }
 }
 
+// radix-8 inverse round, inputs < 2p, outputs < 2p, sums left unreduced inside the round
+GQ_DEV void inv_round8_lz(uint64_t *v, int lo, int kq, const ulonglong2 *__restrict__ tw, const PC &c) {
+  {
+    const int kb = kq >> (lo + 1);
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+      const ulonglong2 w = __ldg(&tw[kb + g]);
+      bf_inv_lz(v[2 * g], v[2 * g + 1], 2, w.x, w.y, c);            // bounds -> {4,2,4,2,4,2,4,2}
+    }
+  }
+  {
+    const int kb = kq >> (lo + 2);
+#pragma unroll
+    for (int g = 0; g < 2; g++) {
+      const ulonglong2 w = __ldg(&tw[kb + g]);
+      bf_inv_lz(v[4 * g + 0], v[4 * g + 2], 4, w.x, w.y, c);        // -> {8,4,2,2,8,4,2,2}
+      bf_inv_lz(v[4 * g + 1], v[4 * g + 3], 2, w.x, w.y, c);
+    }
+  }
+  {
+    const ulonglong2 w = __ldg(&tw[kq >> (lo + 3)]);
+    bf_inv_lz(v[0], v[4], 8, w.x, w.y, c);                          // -> {16,8,4,4,2,2,2,2}
+    bf_inv_lz(v[1], v[5], 4, w.x, w.y, c);
+    bf_inv_lz(v[2], v[6], 2, w.x, w.y, c);
+    bf_inv_lz(v[3], v[7], 2, w.x, w.y, c);
+  }
+  v[0] = norm2p(v[0], 16, c);
+  v[1] = norm2p(v[1], 8, c);
+  v[2] = norm2p(v[2], 4, c);
+  v[3] = norm2p(v[3], 4, c);
+}
+
 template <int NB, bool LAST>
 GQ_DEV void inv_round(uint64_t *v, int lo, int kq, const ulonglong2 *__restrict__ tw, const PC &c,
                       ulonglong2 wlast, uint64_t ninv, uint64_t ninv_sh) {
+  if (NB == 3 && !LAST) { inv_round8_lz(v, lo, kq, tw, c); return; }
   if (NB >= 3) {
     const int kb = kq >> (lo + 1);
 #pragma unroll
@@ -124,7 +180,7 @@ struct TileCfg {
 };
 
 // ---- forward tile kernel: 2^LOGT contiguous elements, the last LOGT stages ----------
-// PRE: inputs may be as large as 11p (they come from the strided kernel): reduce below 8p first.
+// PRE: inputs come from the strided kernel (up to 11p); see the range notes at the top.
 template <int LOGT, bool PRE>
 __global__ void __launch_bounds__(TileCfg<LOGT>::NT, (TileCfg<LOGT>::NT >= 512 ? 2 : 1))
 k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
@@ -140,10 +196,6 @@ k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
   uint64_t v[8];
 #pragma unroll
   for (int e = 0; e < 8; e++) v[e] = a[e * C::NT + t];
-  if (PRE) {
-#pragma unroll
-    for (int e = 0; e < 8; e++) v[e] = csub(v[e], c.p8);
-  }
   fwd_round<C::NB0>(v, LOGT - 3, jbase + t, tw, c);
   if (C::NFULL > 0) {
 #pragma unroll
@@ -154,7 +206,11 @@ k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
       const int lo = LOGT - C::NB0 - 3 * (r + 1);
       const int base = idx8(t, lo);
 #pragma unroll
-      for (int e = 0; e < 8; e++) v[e] = csub(sm[swz(base | (e << lo))], c.p8);
+      for (int e = 0; e < 8; e++) v[e] = sm[swz(base | (e << lo))];
+      if (PRE && r == C::NFULL - 1) {       // two-kernel transform: < 29p here, the only reduction on the way
+#pragma unroll
+        for (int e = 0; e < 8; e++) v[e] = csub(v[e], c.p16);
+      }
       fwd_round<3>(v, lo, jbase + base, tw, c);
       if (r == C::NFULL - 1) {
 #pragma unroll
@@ -264,6 +320,13 @@ k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
   uint64_t v[R];
 #pragma unroll
   for (int r = 0; r < R; r++) v[r] = a[(size_t)r * cols];
+  // inputs < 2p (the tile kernel's outputs).  Lazy stages: both legs of a butterfly carry the same bound
+  // bnd[r]*p (it depends only on the index bits already processed); sums double it, differences return to
+  // 2p; a pair at 16p is brought back to 8p first so that no sum reaches 32p.  All indices and bounds are
+  // compile-time constants after unrolling.
+  int bnd[R];
+#pragma unroll
+  for (int r = 0; r < R; r++) bnd[r] = 2;
 #pragma unroll
   for (int s = SA - 1; s >= 1; s--) {
     const int mb = SA - 1 - s;
@@ -272,16 +335,20 @@ k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
       const ulonglong2 w = __ldg(&tw[(1 << s) + g]);
 #pragma unroll
       for (int i = 0; i < (1 << mb); i++) {
-        const int r = (g << (mb + 1)) | i;
-        bf_inv(v[r], v[r | (1 << mb)], w.x, w.y, c.p, c.p2);
+        const int r = (g << (mb + 1)) | i, q = r | (1 << mb);
+        if (bnd[r] >= 16) { v[r] = csub(v[r], c.p8); v[q] = csub(v[q], c.p8); bnd[r] = 8; }
+        bf_inv_lz(v[r], v[q], bnd[r], w.x, w.y, c);
+        bnd[r] *= 2; bnd[q] = 2;
       }
     }
   }
 #pragma unroll
   for (int r = 0; r < R / 2; r++) {
-    const uint64_t s = v[r] + v[r + R / 2], dd = v[r] - v[r + R / 2] + c.p2;
+    const int q = r + R / 2;
+    if (bnd[r] >= 16) { v[r] = csub(v[r], c.p8); v[q] = csub(v[q], c.p8); bnd[r] = 8; }
+    const uint64_t s = v[r] + v[q], dd = v[r] - v[q] + pmul(c, bnd[r]);
     v[r] = csub(mul_lazy(s, pr.ninv, pr.ninv_sh, c.p), c.p);
-    v[r + R / 2] = csub(mul_lazy(dd, wlast.x, wlast.y, c.p), c.p);
+    v[q] = csub(mul_lazy(dd, wlast.x, wlast.y, c.p), c.p);
   }
 #pragma unroll
   for (int r = 0; r < R; r++) a[(size_t)r * cols] = v[r];

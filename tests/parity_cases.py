@@ -393,3 +393,45 @@ def check_slot2coeff(lib_path, logn, q, Delta, n1=2, n2=2, logqub=0, seed=11, la
         assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], "he_slot2coeff"
     finally:
         ctx.close()
+
+
+def check_lazy_ntt_vs_exact(lib_path, logn, q, device="cpu", limbs=None, seed=1):
+    """The lazy transforms of the internal pipelines (gq_ntt_lazy.cu through gq_stage_ntt_dev: canonical in,
+    canonical out, sums left unreduced on the way) against the exact ntt() / invntt() kernels, which are pinned
+    to the reference, on vectors that maximise the growth of the unreduced values: all p-1, alternating
+    0 / p-1, impulses, random."""
+    import contextlib
+    import ctypes as C
+    import torch
+    ctx = g.HeContext(logn, q, lib_path=lib_path, logqub=q.bit_length() - 1)
+    try:
+        n = ctx.n
+        rng = np.random.default_rng(seed)
+        cm = contextlib.nullcontext()
+        if torch.device(device).type == "cuda":
+            cm = torch.cuda.stream(torch.cuda.ExternalStream(ctx._lib.gq_ctx_stream(ctx._h), device=device))
+        for d in (limbs or (0, ctx.dimub - 1)):
+            p = ctx.primes[d]
+            vecs = [np.full(n, p - 1, dtype=np.uint64), np.zeros(n, dtype=np.uint64),
+                    rng.integers(0, p, size=n, dtype=np.uint64)]
+            alt = np.zeros(n, dtype=np.uint64); alt[::2] = p - 1
+            blk = np.zeros(n, dtype=np.uint64); blk[: n // 2] = p - 1
+            imp = np.zeros(n, dtype=np.uint64); imp[n - 1] = p - 1
+            vecs += [alt, blk, imp]
+            for inverse in (0, 1):
+                want = [(ctx.invntt(v, d) if inverse else ctx.ntt(v, d)) % np.uint64(p) for v in vecs]
+                buf = torch.from_numpy(np.stack(vecs).view(np.int64)).to(device)        # [npolys][1 limb][n]
+                with cm:
+                    capi_check(ctx, ctx._lib.gq_stage_ntt_dev(ctx._h, d, 1, len(vecs), C.c_void_p(buf.data_ptr()),
+                                                              inverse, None))
+                    ctx.sync()
+                got = buf.cpu().numpy().view(np.uint64)
+                for k in range(len(vecs)):
+                    eq(got[k], want[k], f"lazy {'inverse' if inverse else 'forward'} NTT logn={logn} limb={d} vector {k}")
+    finally:
+        ctx.close()
+
+
+def capi_check(ctx, rc):
+    from gpqhe_b200 import capi
+    capi.check(ctx._lib, rc)

@@ -127,3 +127,9 @@ def test_rlsin_device_resident(emul_lib, logn, q, Delta, iters, lanes):
 @pytest.mark.parametrize("logn,q,Delta,n1,n2,lanes", [(5, 1 << 120, 1 << 40, 2, 2, 1), (5, 1 << 438, 1 << 50, 2, 2, 3)])
 def test_slot2coeff_device_resident(emul_lib, logn, q, Delta, n1, n2, lanes):
     pc.check_slot2coeff(emul_lib, logn, q, Delta, n1, n2, logqub=q.bit_length() - 1, lanes=lanes)
+
+
+@pytest.mark.parametrize("logn,logq", [(9, 100), (12, 100), (13, 120), (14, 120), (16, 61), (17, 61)])
+def test_lazy_ntt_vs_exact(emul_lib, logn, logq):
+    """single-tile (n <= 2^12) and two-kernel (n >= 2^13) lazy transforms on growth-maximising vectors"""
+    pc.check_lazy_ntt_vs_exact(emul_lib, logn, 1 << logq)

@@ -122,3 +122,9 @@ def test_rlsin_device_resident(real_lib):
 def test_slot2coeff_device_resident(real_lib):
     """configs[4], SlotToCoeff: two he_gemv + he_add at N=2^12, slots = 16."""
     pc.check_slot2coeff(real_lib, 12, 1 << 109, 1 << 30, 4, 4, lanes=3)
+
+
+@pytest.mark.parametrize("logn,logq", [(10, 100), (12, 100), (13, 120), (15, 120), (16, 438), (17, 61)])
+def test_lazy_ntt_vs_exact(real_lib, logn, logq):
+    pc.check_lazy_ntt_vs_exact(real_lib, logn, 1 << logq, device="cuda:0",
+                               limbs=(0, 5, 23) if logq == 438 else None)
