@@ -28,7 +28,11 @@
 
 namespace {
 
-GQ_DEV int swz(int i) { return i ^ ((i >> 4) & 7); }
+// shared-memory index swizzle (8-byte elements, 16 per 128-byte wavefront): the low 3 bits take bits 4-6 and
+// bit 3 takes bit 7, so that the warp access patterns of all three radix-8 rounds (element strides 1, 8
+// and 64) touch every 8-byte bank exactly twice; without the bit-3 term the stride-8 round was 4-way
+// (ncu: 0.54 M conflicts on 2.1 M wavefronts)
+GQ_DEV int swz(int i) { return i ^ ((i >> 4) & 7) ^ (((i >> 7) & 1) << 3); }
 GQ_DEV int idx8(int t, int lo) { return ((t >> lo) << (lo + 3)) | (t & ((1 << lo) - 1)); }
 
 GQ_DEV uint64_t csub(uint64_t x, uint64_t m) { return (x >= m) ? x - m : x; }
@@ -57,6 +61,12 @@ GQ_DEV uint64_t full_reduce(uint64_t v, uint64_t p, int sh) {
   return ((int64_t)r < 0) ? r + p : r;
 }
 
+// resident CTAs the strided kernels are compiled for: 3 x 256 threads (80 registers, no spills) up to 16
+// points per thread; the 32-point form (n = 2^17) needs its 200+ registers
+#ifndef GQ_STRIDED_CTAS
+#define GQ_STRIDED_CTAS 3
+#endif
+#define GQ_STRIDED_MIN_CTAS (SA <= 4 ? GQ_STRIDED_CTAS : 1)
 struct PC { uint64_t p, p2, p4, p8, p16; int sh; };
 GQ_DEV PC load_pc(const GqPrime &P) {
   PC c; c.p = P.p; c.p2 = 2 * P.p; c.p4 = 4 * P.p; c.p8 = 8 * P.p; c.p16 = 16 * P.p; c.sh = (int)P.bits - 1; return c;
@@ -271,17 +281,24 @@ k_nttl_inv_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
 }
 
 // ---- strided register kernels ------------------------------------------------------
+// The 2^SA - 1 twiddles of these stages are the same for every thread of the grid row: they are staged in
+// shared memory once per CTA (broadcast reads at the point of use) instead of being held in 4 registers
+// each from the top of the kernel - ncu had these kernels at 112-128 registers, 2 CTAs per SM, 22 % of
+// the warp slots and 36-40 % issue utilisation.
 template <int SA>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, GQ_STRIDED_MIN_CTAS)
 k_nttl_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
   constexpr int R = 1 << SA;
+  __shared__ ulonglong2 stw[R];
   const int cols = tb.n >> SA;
   const int col = blockIdx.x * blockDim.x + threadIdx.x;
-  if (col >= cols) return;
   const int m = blockIdx.y;
   const int d = limb0 + m % nlimbs;
+  if (threadIdx.x < R) stw[threadIdx.x] = tb.tw_fwd[(size_t)d * tb.n + threadIdx.x];
+  __syncthreads();
+  if (col >= cols) return;
   const PC c = load_pc(tb.primes[d]);
-  const ulonglong2 *tw = tb.tw_fwd + (size_t)d * tb.n;
+  const ulonglong2 *tw = stw;
   uint64_t *a = data + (size_t)m * tb.n + col;
   uint64_t v[R];
 #pragma unroll
@@ -291,7 +308,7 @@ k_nttl_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
     const int mb = SA - 1 - s;
 #pragma unroll
     for (int g = 0; g < (1 << s); g++) {
-      const ulonglong2 w = __ldg(&tw[(1 << s) + g]);
+      const ulonglong2 w = tw[(1 << s) + g];
 #pragma unroll
       for (int i = 0; i < (1 << mb); i++) {
         const int r = (g << (mb + 1)) | i;
@@ -304,17 +321,20 @@ k_nttl_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
 }
 
 template <int SA>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, GQ_STRIDED_MIN_CTAS)
 k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
   constexpr int R = 1 << SA;
+  __shared__ ulonglong2 stw[R];
   const int cols = tb.n >> SA;
   const int col = blockIdx.x * blockDim.x + threadIdx.x;
-  if (col >= cols) return;
   const int m = blockIdx.y;
   const int d = limb0 + m % nlimbs;
+  if (threadIdx.x < R) stw[threadIdx.x] = tb.tw_inv[(size_t)d * tb.n + threadIdx.x];
+  __syncthreads();
+  if (col >= cols) return;
   const GqPrime pr = tb.primes[d];
   const PC c = load_pc(pr);
-  const ulonglong2 *tw = tb.tw_inv + (size_t)d * tb.n;
+  const ulonglong2 *tw = stw;
   const ulonglong2 wlast = tb.tw_inv_last[d];
   uint64_t *a = data + (size_t)m * tb.n + col;
   uint64_t v[R];
@@ -332,7 +352,7 @@ k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
     const int mb = SA - 1 - s;
 #pragma unroll
     for (int g = 0; g < (1 << s); g++) {
-      const ulonglong2 w = __ldg(&tw[(1 << s) + g]);
+      const ulonglong2 w = tw[(1 << s) + g];
 #pragma unroll
       for (int i = 0; i < (1 << mb); i++) {
         const int r = (g << (mb + 1)) | i, q = r | (1 << mb);
