@@ -138,6 +138,10 @@ def test_dropin_diff_gpu(args):
     if args[0] == "16":
         env["DROPIN_DIFF_NO_EXP"] = "1"      # the CPU side of he_exp / he_rlsin takes minutes at N=2^16; N=2^14 covers it
     rc, out = _run([os.path.join(BUILD, "dropin_diff"), *args], env=env, timeout=1800)
+    keep = os.path.join(ROOT, "gpurun_out")          # the drop-in vs reference wall times it prints are worth keeping
+    if os.path.isdir(keep):
+        with open(os.path.join(keep, "dropin_diff_n%s_q%s.log" % (args[0], args[1])), "w") as f:
+            f.write(out)
     assert rc == 0 and "PASS" in out, out[-3000:]
 
 
