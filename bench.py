@@ -339,8 +339,8 @@ def run_ours(args):
         in1 = (VP * 1)(d[2].data_ptr())
         out3 = (VP * 3)(*[d[j].data_ptr() for j in range(3)])
         stages = [
-            ("decompose x4 -> D1", "k_decompose32<7>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D1, 4, in4, W, n, xc.data_ptr(), None)),
-             4 * D1 * n, 42.0, 4 * W * n * 8 + 4 * D1 * n * 8),
+            ("decompose x4 -> D1", "k_decompose28<7, pm>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D1, 4, in4, W, n, xc.data_ptr(), None)),
+             4 * D1 * n, 34.0, 4 * W * n * 8 + 4 * D1 * n * 8),     # 15 digits x 2 multiply-adds + 4 in the fold
             ("forward NTT, 4 x D1 limb-polys", "k_nttl_fwd_strided<4> + k_nttl_fwd_tile<12>", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D1, 4, xc.data_ptr(), 0, None)),
              4 * D1 * (n // 2) * LOGN, 8.0, 2 * 2 * 4 * D1 * n * 8),
             ("tensor product", "k_tensor_pm", lambda i: ck(lib.gq_stage_tensor_dev(h, 0, D1, y.data_ptr(), xc.data_ptr(), None)),
@@ -349,8 +349,8 @@ def run_ours(args):
              3 * D1 * (n // 2) * LOGN, 8.0, 2 * 2 * 3 * D1 * n * 8),
             ("reconstruct x3 over D1", "k_reconstruct_fast<7>", lambda i: ck(lib.gq_stage_reconstruct_dev(h, D1, L, 3, y.data_ptr(), out3, n, None)),
              3 * n, D1 * 38.0 + 4 * W, 3 * D1 * n * 8 + 3 * W * n * 8),
-            ("decompose d2 -> D2", "k_decompose32<7>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D2, 1, in1, W, n, x2.data_ptr(), None)),
-             D2 * n, 42.0, W * n * 8 + D2 * n * 8),
+            ("decompose d2 -> D2", "k_decompose28<7, pm>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D2, 1, in1, W, n, x2.data_ptr(), None)),
+             D2 * n, 34.0, W * n * 8 + D2 * n * 8),
             ("forward NTT, D2", "k_nttl_fwd_*", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D2, 1, x2.data_ptr(), 0, None)),
              D2 * (n // 2) * LOGN, 8.0, 2 * 2 * D2 * n * 8),
             ("multiply by rlk", "k_mul_evk_pm", lambda i: ck(lib.gq_stage_mul_evk_dev(h, 0, D2, y2.data_ptr(), x2.data_ptr(), evk._h, None)),

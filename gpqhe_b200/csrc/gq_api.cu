@@ -278,7 +278,15 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
       for (unsigned j = 0; j < GQ_DEC32; j++) { p32[(size_t)d * GQ_DEC32 + j] = v; v = mulm(v, b32, pd); }
       osh[d] = (uint64_t)((((gq_u128)1) << 64) / pd);
     }
+    std::vector<uint64_t> p28((size_t)K * GQ_DEC28);
+    for (unsigned d = 0; d < K; d++) {
+      const uint64_t pd = c->primes[d].p;
+      uint64_t v = 1 % pd;
+      const uint64_t b28 = (1ull << 28) % pd;
+      for (unsigned j = 0; j < GQ_DEC28; j++) { p28[(size_t)d * GQ_DEC28 + j] = v; v = mulm(v, b28, pd); }
+    }
     if (upload(&c->d_pow64, pw.data(), pw.size()) || upload(&c->d_t1sh, t1.data(), t1.size()) ||
+        upload(&c->d_pow28, p28.data(), p28.size()) ||
         upload(&c->d_pow32, p32.data(), p32.size()) || upload(&c->d_onesh, osh.data(), osh.size())) {
       gq_ctx_destroy(c); return 1;
     }
@@ -366,7 +374,7 @@ extern "C" void gq_ctx_destroy(gq_ctx *c) {
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (!c->parent) {     // a lane shares the tables of its parent
     cudaFree(c->d_primes); cudaFree(c->d_tw_fwd); cudaFree(c->d_tw_inv); cudaFree(c->d_tw_inv_last);
-    cudaFree(c->d_pow64); cudaFree(c->d_t1sh); cudaFree(c->d_pow32); cudaFree(c->d_onesh); cudaFree(c->d_Pinv); cudaFree(c->d_Pwords);
+    cudaFree(c->d_pow64); cudaFree(c->d_t1sh); cudaFree(c->d_pow32); cudaFree(c->d_pow28); cudaFree(c->d_onesh); cudaFree(c->d_Pinv); cudaFree(c->d_Pwords);
     for (auto &b : c->basis) cudaFree(b.blob);
     for (auto &m : c->qmod) cudaFree(m.blob);
   }
@@ -627,9 +635,12 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
   if (ncoef == 0) ncoef = c->n;
   if (limb0 + nlimbs > c->dimub) GQ_FAIL("limb range exceeds dimub");
   if (W == 0 || W > GQ_MAX_W) GQ_FAIL("word count out of range");
-  bool digits = c->fast_crt && W <= 8;      // A1 of k_decompose32 stays below 2^64 for <= 15 digits
-  for (unsigned d = limb0; digits && d < limb0 + nlimbs; d++)
-    digits = c->primes[d].bits >= 33 && c->primes[d].bits <= 60;
+  bool dig = c->fast_crt && W <= 8;         // A1 of k_decompose32 stays below 2^64 for <= 15 digits
+  for (unsigned d = limb0; dig && d < limb0 + nlimbs; d++)
+    dig = c->primes[d].bits >= 33 && c->primes[d].bits <= 60;
+  // 0 = word form, 1 = 32-bit digits, 2 = 28-bit digits (at most 16 of them: carry-free column sums),
+  // 3 = 28-bit digits with the pseudo-Mersenne fold
+  const int digits = !dig ? 0 : (W <= 7 && !getenv("GPQHE_B200_DEC32")) ? (pm_ok(c, limb0, nlimbs) ? 3 : 2) : 1;
   if (gq_launch_decompose(c->dec_tables(), (int)ncoef, (int)limb0, (int)nlimbs, in, (int)W, out,
                           (int)npolys, st, digits) < 0)
     GQ_FAIL("no decompose kernel for this width");

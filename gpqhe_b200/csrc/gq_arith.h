@@ -19,6 +19,18 @@ GQ_HD uint64_t gq_mulhi(uint64_t a, uint64_t b) {
 #endif
 }
 
+// a*b + c with 32-bit factors: one IMAD.WIDE.U32.  Written as PTX because the C form
+// (uint64_t)a * (uint64_t)b + c leaves an add of the (zero) high cross term behind every multiply in the SASS.
+GQ_HD uint64_t gq_mad_wide(uint32_t a, uint32_t b, uint64_t c) {
+#if defined(__CUDA_ARCH__)
+  uint64_t r;
+  asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(a), "r"(b), "l"(c));
+  return r;
+#else
+  return (uint64_t)a * (uint64_t)b + c;
+#endif
+}
+
 // Per-prime constants (device image of one struct rns_ctx node, src/poly.h:28-41).
 struct GqPrime {
   uint64_t p;          // the prime

@@ -36,7 +36,7 @@ struct gq_ctx {
   // device tables
   GqPrime *d_primes = nullptr;
   ulonglong2 *d_tw_fwd = nullptr, *d_tw_inv = nullptr, *d_tw_inv_last = nullptr;
-  uint64_t *d_pow64 = nullptr, *d_t1sh = nullptr, *d_pow32 = nullptr, *d_onesh = nullptr;
+  uint64_t *d_pow64 = nullptr, *d_t1sh = nullptr, *d_pow32 = nullptr, *d_onesh = nullptr, *d_pow28 = nullptr;
   uint64_t *d_Pinv = nullptr;        // P^-1 mod 2^(64*GQ_MAX_W)
   uint64_t *d_Pwords = nullptr;      // P and floor(P/2), GQ_MAX_W words each (general path)
   int *d_fix = nullptr;              // {count, pad x3, list[4n]} of the fast CRT kernels
@@ -67,7 +67,7 @@ struct gq_ctx {
   }
   GqDecTables dec_tables() const {
     GqDecTables t; t.primes = d_primes; t.pow64 = d_pow64; t.t1_sh = d_t1sh;
-    t.pow32 = d_pow32; t.one_sh = d_onesh; return t;
+    t.pow32 = d_pow32; t.one_sh = d_onesh; t.pow28 = d_pow28; return t;
   }
 };
 

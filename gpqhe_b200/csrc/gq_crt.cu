@@ -549,6 +549,86 @@ k_decompose32(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t
   }
 }
 
+// K4, 28-bit digit form (coefficients of at most 7 words = 16 digits, primes of 33..60 bits).  With
+//   U_j = 2^(28j) mod p = u0_j + 2^32 u1_j   (u1_j < 2^28),
+//   sum_j x_j U_j = A0 + 2^32 A1,  A0 = sum x_j u0_j < 16 * 2^28 * 2^32 = 2^64,  A1 = sum x_j u1_j < 2^60:
+// both column sums fit 64 bits, so every term is ONE 32x32+64 multiply-add with no carry handling (the 32-bit
+// digit form needs a 70-bit A0: three add-with-carry per term; SASS 188 -> about 105 instructions per residue).
+// The 93-bit total is folded as in k_decompose32.
+// PM: every prime is 2^s + c with 33 <= s <= 59, c < 2^min(s-31,28) (the shape of every GPQHE prime,
+// src/precomp.c:358-376: 2^59 + 1 + k*2N).  Then 2^s == -c and the 93-bit total V = Vh*2^s + Vl folds with two
+// small products instead of two 64-bit Shoup multiplications:  t = c*Vh < 2^62 = th*2^s + tl,
+//   V == Vl - tl + c*th  (mod p),   r = Vl + p - tl + c*th  in (0, 2p + 2^31).
+template <int W, bool PM>
+__global__ void __launch_bounds__(256)
+k_decompose28(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *__restrict__ out) {
+  constexpr int J = (64 * W + 27) / 28;
+  static_assert(J <= GQ_DEC28, "at most 16 digits");
+  __shared__ uint64_t sU[GQ_MAX_PRIMES * J];
+  __shared__ uint64_t sC[GQ_MAX_PRIMES * 6];      // p, T1, T1sh, one_sh, TW, pad
+  for (int j = threadIdx.x; j < nlimbs * J; j += blockDim.x)
+    sU[j] = dt.pow28[(size_t)(limb0 + j / J) * GQ_DEC28 + j % J];
+  for (int d = threadIdx.x; d < nlimbs; d += blockDim.x) {
+    sC[6 * d + 0] = dt.primes[limb0 + d].p;
+    sC[6 * d + 1] = dt.pow64[(size_t)(limb0 + d) * GQ_DEC_W + 1];
+    sC[6 * d + 2] = dt.t1_sh[limb0 + d];
+    sC[6 * d + 3] = dt.one_sh[limb0 + d];
+    sC[6 * d + 4] = dt.pow64[(size_t)(limb0 + d) * GQ_DEC_W + W];
+    sC[6 * d + 5] = dt.primes[limb0 + d].bits - 1;
+  }
+  __syncthreads();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int b = blockIdx.y;
+  const uint64_t *src = (b == 0) ? in.p[0] : (b == 1) ? in.p[1] : (b == 2) ? in.p[2] : in.p[3];
+  uint64_t *dst = out + (size_t)b * nlimbs * n;
+  uint64_t xw[W];
+#pragma unroll
+  for (int w = 0; w < W; w++) xw[w] = src[(size_t)w * n + i];
+  const bool neg = (xw[W - 1] >> 63) != 0;
+  uint32_t x[J];
+#pragma unroll
+  for (int j = 0; j < J; j++) {
+    const int o = 28 * j, w = o >> 6, sft = o & 63;
+    uint64_t v = xw[w] >> sft;
+    if (sft > 36 && w + 1 < W) v |= xw[w + 1] << (64 - sft);
+    x[j] = (uint32_t)v & 0x0fffffffu;
+  }
+  for (int d = 0; d < nlimbs; d++) {
+    const uint64_t *U = &sU[d * J];
+    const uint64_t p = sC[6 * d], T1 = sC[6 * d + 1], T1sh = sC[6 * d + 2], osh = sC[6 * d + 3];
+    uint64_t A0 = x[0], A1 = 0;
+#pragma unroll
+    for (int j = 1; j < J; j++) {
+      const uint64_t u = U[j];
+      A0 = gq_mad_wide(x[j], (uint32_t)u, A0);
+      A1 = gq_mad_wide(x[j], (uint32_t)(u >> 32), A1);
+    }
+    const uint64_t vlo = A0 + (A1 << 32);
+    const uint64_t vhi = (A1 >> 32) + (vlo < A0 ? 1u : 0u);
+    uint64_t r;
+    if (PM) {
+      const int sh = (int)sC[6 * d + 5];                       // 33..59
+      const uint64_t mask = (((uint64_t)1) << sh) - 1;
+      const uint32_t cc = (uint32_t)(p - (mask + 1));
+      const uint64_t Vh = (vlo >> sh) | (vhi << (64 - sh));     // < 2^(93-sh) <= 2^60
+      const uint64_t t = Vh * cc;                               // < 2^62
+      const uint64_t u = gq_mad_wide((uint32_t)(t >> sh), cc, (vlo & mask) + p - (t & mask));
+      r = u;
+    } else {
+      // vhi*2^64 + vlo  ==  vhi*T1 + vlo*1 (mod p), each lazy product in [0,2p)
+      r = (vhi * T1 - gq_mulhi(vhi, T1sh) * p) + (vlo - gq_mulhi(vlo, osh) * p);
+    }
+    r = (r >= 2 * p) ? r - 2 * p : r;
+    r = (r >= p) ? r - p : r;
+    if (neg) {
+      const uint64_t TW = sC[6 * d + 4];
+      r = (r >= TW) ? r - TW : r - TW + p;
+    }
+    dst[(size_t)d * n + i] = r;
+  }
+}
+
 template <int W>
 __global__ void __launch_bounds__(256)
 k_decompose(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *__restrict__ out) {
@@ -683,14 +763,18 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
 
 template <int W>
 static void dec_launch(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
-                       uint64_t *out, int npolys, cudaStream_t st, bool digits) {
+                       uint64_t *out, int npolys, cudaStream_t st, int digits) {
   dim3 grid((n + 255) / 256, npolys), block(256);
+  if constexpr (W <= 7) {
+    if (digits == 3) { GQ_LAUNCH((k_decompose28<W, true>), grid, block, st, dt, n, limb0, nlimbs, in, out); return; }
+    if (digits == 2) { GQ_LAUNCH((k_decompose28<W, false>), grid, block, st, dt, n, limb0, nlimbs, in, out); return; }
+  }
   if (digits) GQ_LAUNCH(k_decompose32<W>, grid, block, st, dt, n, limb0, nlimbs, in, out);
   else GQ_LAUNCH(k_decompose<W>, grid, block, st, dt, n, limb0, nlimbs, in, out);
 }
 
 int gq_launch_decompose(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
-                        int W, uint64_t *out, int npolys, cudaStream_t st, bool digits) {
+                        int W, uint64_t *out, int npolys, cudaStream_t st, int digits) {
   switch (W) {
 #define GQ_CASE(V) case V: dec_launch<V>(dt, n, limb0, nlimbs, in, out, npolys, st, digits); return 1;
     GQ_CASE(1) GQ_CASE(2) GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8)

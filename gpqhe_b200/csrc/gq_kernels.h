@@ -31,7 +31,7 @@ void gq_launch_mul_pt(const GqPrime *primes, int n, int D, uint64_t *y, const ui
 // fix = device scratch {int count (16-byte slot), int list[4n]}: enables the fast low-word kernels
 // digits: 32-bit digit kernel (every prime of the range needs >= 33 and <= 60 bits)
 int gq_launch_decompose(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
-                        int W, uint64_t *out, int npolys, cudaStream_t st, bool digits = false);
+                        int W, uint64_t *out, int npolys, cudaStream_t st, int digits = false);
 int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
                           cudaStream_t st, int *fix = nullptr);

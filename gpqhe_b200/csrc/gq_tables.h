@@ -22,10 +22,13 @@ struct GqNttTables {
 // companion of pow64[d][1].
 // pow32[d*GQ_DEC32 + j] = 2^(32j) mod p_d for j = 0..2*GQ_MAX_W-1 (digit form of the same table);
 // one_sh[d] = floor(2^64 / p_d), the Shoup companion of the constant 1.
+// pow28[d*GQ_DEC28 + j] = 2^(28j) mod p_d for j = 0..15 (k_decompose28: coefficients of at most 7 words).
 #define GQ_DEC32 (2 * GQ_MAX_W)
+#define GQ_DEC28 16
 struct GqDecTables {
   const GqPrime *primes;
   const uint64_t *pow32;
+  const uint64_t *pow28;
   const uint64_t *one_sh;
   const uint64_t *pow64;
   const uint64_t *t1_sh;
