@@ -425,39 +425,42 @@ k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
 
 // key-switch epilogue: T low WP words by crt_low over the D2 basis, r = T mod P exactly over the
 // first `dim` limbs (full width WP, cheap), then the same exact quotient as ks_one.
-template <int WP>
+// WQ <= WP: the result is only needed modulo q = 2^k, k < 64*WQ, so T, T - r and the quotient are carried in
+// WQ words (WQ = the context's words per coefficient; 7 against WP = 8 at logq = 438); only r = T mod P needs
+// the full width of P.
+template <int WP, int WQ>
 __global__ void __launch_bounds__(128)
 k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
                    const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
                    unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout, int *fix_count, int *fix_list) {
-  __shared__ CrtSharedLow<WP> S;
+  __shared__ CrtSharedLow<WQ> S;
   __shared__ CrtShared<WP> SP;
-  __shared__ uint64_t sPinv[WP];
-  crt_low_stage<WP>(S, B, primes);
+  __shared__ uint64_t sPinv[WQ];
+  crt_low_stage<WQ>(S, B, primes);
   crt_stage<WP>(SP, BP, primes);
-  for (int j = threadIdx.x; j < WP; j += blockDim.x) sPinv[j] = Pinv[j];
+  for (int j = threadIdx.x; j < WQ; j += blockDim.x) sPinv[j] = Pinv[j];
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int b = blockIdx.y;
   const uint64_t *ch = chat + (size_t)b * B.D * n;
-  uint64_t x[WP];
-  if (!crt_low<WP>(x, S, B.D, B.F - 64, ch, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
+  uint64_t x[WQ];
+  if (!crt_low<WQ>(x, S, B.D, B.F - 64, ch, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
   bool round_up;
   {
     uint64_t r[WP + 1];
     crt_mod_P<WP>(r, SP, BP, ch, n, i);            // r = T mod P in [0,P)
     round_up = !mw_geq<WP>(SP.Ph, r);              // r > floor(P/2)
-    mw_sub<WP>(x, x, r);                           // low words of T - r
+    mw_sub<WQ>(x, x, r);                           // low words of T - r
   }
-  uint64_t Q[WP];                                  // (T - r) * P^-1 mod 2^(64*WP): the exact quotient
+  uint64_t Q[WQ];                                  // (T - r) * P^-1 mod 2^(64*WQ): the exact quotient mod 2^(64*WQ)
 #pragma unroll
-  for (int w = 0; w < WP; w++) Q[w] = 0;
+  for (int w = 0; w < WQ; w++) Q[w] = 0;
 #pragma unroll
-  for (int a = 0; a < WP; a++) {
+  for (int a = 0; a < WQ; a++) {
     uint64_t carry = 0;
 #pragma unroll
-    for (int c = 0; c + a < WP; c++) {
+    for (int c = 0; c + a < WQ; c++) {
       gq_u128 t = (gq_u128)x[a] * sPinv[c] + Q[a + c] + carry;
       Q[a + c] = (uint64_t)t;
       carry = (uint64_t)(t >> 64);
@@ -467,7 +470,7 @@ k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pin
     const uint64_t *ap = add.p[b];
     uint64_t carry = round_up ? 1u : 0u, top = 0;
 #pragma unroll
-    for (int w = 0; w < WP; w++) {
+    for (int w = 0; w < WQ; w++) {
       uint64_t ad = 0;
       if (ap) { if (w < Wadd) { ad = ap[(size_t)w * n + i]; top = ad; } else ad = (top >> 63) ? ~(uint64_t)0 : 0; }
       gq_u128 t = (gq_u128)Q[w] + ad + carry;
@@ -475,8 +478,8 @@ k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pin
       carry = (uint64_t)(t >> 64);
     }
   }
-  mw_smod_pow2<WP>(Q, k);
-  store_words<WP>(out.p[b], n, i, Wout, Q);
+  mw_smod_pow2<WQ>(Q, k);
+  store_words<WQ>(out.p[b], n, i, Wout, Q);
 }
 
 // ---- K4 ---------------------------------------------------------------------------
@@ -743,8 +746,13 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
     fc = fix; fl = fix + 4;
     dim3 block(128);
     switch (BP.WT) {
-#define GQ_KF(V) case V: GQ_LAUNCH(k_ks_epilogue_fast<V>, grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl); break;
-      GQ_KF(8) GQ_KF(16) GQ_KF(24) GQ_KF(32)
+#define GQ_KF(V) case V: GQ_LAUNCH((k_ks_epilogue_fast<V, V>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl); break;
+      case 8:     // the shipped parameter sets (logq = 438: 7 words per coefficient, P of 8 words) and their neighbours
+        if (Wout == 7 && Wadd <= 7 && k < 64u * 7) GQ_LAUNCH((k_ks_epilogue_fast<8, 7>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl);
+        else if (Wout == 6 && Wadd <= 6 && k < 64u * 6) GQ_LAUNCH((k_ks_epilogue_fast<8, 6>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl);
+        else GQ_LAUNCH((k_ks_epilogue_fast<8, 8>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl);
+        break;
+      GQ_KF(16) GQ_KF(24) GQ_KF(32)
 #undef GQ_KF
       default: return -1;
     }
