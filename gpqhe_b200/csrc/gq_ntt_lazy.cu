@@ -197,6 +197,8 @@ k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
   typedef TileCfg<LOGT> C;
   __shared__ uint64_t sm[C::T];
   const int t = threadIdx.x;
+  const int st = swz(t);      // swz is XOR-linear: swz(x | y) = swz(x) ^ swz(y) for disjoint bits, and the second
+                              // term is a compile-time constant in every access below
   const int m = blockIdx.y;
   const int d = limb0 + m % nlimbs;
   const PC c = load_pc(tb.primes[d]);
@@ -209,14 +211,14 @@ k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
   fwd_round<C::NB0>(v, LOGT - 3, jbase + t, tw, c);
   if (C::NFULL > 0) {
 #pragma unroll
-    for (int e = 0; e < 8; e++) sm[swz(e * C::NT + t)] = v[e];
+    for (int e = 0; e < 8; e++) sm[st ^ swz(e * C::NT)] = v[e];
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < C::NFULL; r++) {
       const int lo = LOGT - C::NB0 - 3 * (r + 1);
-      const int base = idx8(t, lo);
+      const int base = idx8(t, lo), sb = swz(base);
 #pragma unroll
-      for (int e = 0; e < 8; e++) v[e] = sm[swz(base | (e << lo))];
+      for (int e = 0; e < 8; e++) v[e] = sm[sb ^ swz(e << lo)];
       if (PRE && r == C::NFULL - 1) {       // two-kernel transform: < 29p here, the only reduction on the way
 #pragma unroll
         for (int e = 0; e < 8; e++) v[e] = csub(v[e], c.p16);
@@ -227,11 +229,11 @@ k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
         for (int e = 0; e < 8; e++) v[e] = full_reduce(v[e], c.p, c.sh);
       }
 #pragma unroll
-      for (int e = 0; e < 8; e++) sm[swz(base | (e << lo))] = v[e];
+      for (int e = 0; e < 8; e++) sm[sb ^ swz(e << lo)] = v[e];
       __syncthreads();
     }
 #pragma unroll
-    for (int e = 0; e < 8; e++) a[e * C::NT + t] = sm[swz(e * C::NT + t)];
+    for (int e = 0; e < 8; e++) a[e * C::NT + t] = sm[st ^ swz(e * C::NT)];
   } else {
 #pragma unroll
     for (int e = 0; e < 8; e++) a[e * C::NT + t] = full_reduce(v[e], c.p, c.sh);
@@ -245,6 +247,7 @@ k_nttl_inv_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
   typedef TileCfg<LOGT> C;
   __shared__ uint64_t sm[C::T];
   const int t = threadIdx.x;
+  const int st = swz(t);
   const int m = blockIdx.y;
   const int d = limb0 + m % nlimbs;
   const GqPrime pr = tb.primes[d];
@@ -256,21 +259,21 @@ k_nttl_inv_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
   uint64_t v[8];
   if (C::NFULL > 0) {
 #pragma unroll
-    for (int e = 0; e < 8; e++) sm[swz(e * C::NT + t)] = a[e * C::NT + t];
+    for (int e = 0; e < 8; e++) sm[st ^ swz(e * C::NT)] = a[e * C::NT + t];
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < C::NFULL; r++) {
       const int lo = 3 * r;
-      const int base = idx8(t, lo);
+      const int base = idx8(t, lo), sb = swz(base);
 #pragma unroll
-      for (int e = 0; e < 8; e++) v[e] = sm[swz(base | (e << lo))];
+      for (int e = 0; e < 8; e++) v[e] = sm[sb ^ swz(e << lo)];
       inv_round<3, false>(v, lo, jbase + base, tw, c, wlast, pr.ninv, pr.ninv_sh);
 #pragma unroll
-      for (int e = 0; e < 8; e++) sm[swz(base | (e << lo))] = v[e];
+      for (int e = 0; e < 8; e++) sm[sb ^ swz(e << lo)] = v[e];
       __syncthreads();
     }
 #pragma unroll
-    for (int e = 0; e < 8; e++) v[e] = sm[swz(e * C::NT + t)];
+    for (int e = 0; e < 8; e++) v[e] = sm[st ^ swz(e * C::NT)];
   } else {
 #pragma unroll
     for (int e = 0; e < 8; e++) v[e] = a[e * C::NT + t];
