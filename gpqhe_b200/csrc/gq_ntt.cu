@@ -124,21 +124,21 @@ k_ntt_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimb
     return;
   }
 #pragma unroll
-  for (int e = 0; e < 8; e++) sm[swz(e * C::NT + t)] = v[e];
+  for (int e = 0; e < 8; e++) sm[swz(t) ^ swz(e * C::NT)] = v[e];
   __syncthreads();
 #pragma unroll
   for (int r = 0; r < C::NFULL; r++) {
     const int lo = LOGT - C::NB0 - 3 * (r + 1);
     const int base = idx8(t, lo);
 #pragma unroll
-    for (int e = 0; e < 8; e++) v[e] = sm[swz(base | (e << lo))];
+    for (int e = 0; e < 8; e++) v[e] = sm[swz(base) ^ swz(e << lo)];
     fwd_round<3>(v, lo, jbase + base, tw, p);
 #pragma unroll
-    for (int e = 0; e < 8; e++) sm[swz(base | (e << lo))] = v[e];
+    for (int e = 0; e < 8; e++) sm[swz(base) ^ swz(e << lo)] = v[e];
     __syncthreads();
   }
 #pragma unroll
-  for (int e = 0; e < 8; e++) a[e * C::NT + t] = sm[swz(e * C::NT + t)];
+  for (int e = 0; e < 8; e++) a[e * C::NT + t] = sm[swz(t) ^ swz(e * C::NT)];
 }
 
 // ---- inverse tile kernel -----------------------------------------------------------
@@ -161,21 +161,21 @@ k_ntt_inv_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimb
 
   if (C::NFULL > 0) {
 #pragma unroll
-    for (int e = 0; e < 8; e++) sm[swz(e * C::NT + t)] = a[e * C::NT + t];
+    for (int e = 0; e < 8; e++) sm[swz(t) ^ swz(e * C::NT)] = a[e * C::NT + t];
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < C::NFULL; r++) {
       const int lo = 3 * r;
       const int base = idx8(t, lo);
 #pragma unroll
-      for (int e = 0; e < 8; e++) v[e] = sm[swz(base | (e << lo))];
+      for (int e = 0; e < 8; e++) v[e] = sm[swz(base) ^ swz(e << lo)];
       inv_round<3, (WHOLE && C::NB0 == 0)>(v, lo, jbase + base, tw, p, wlast, pr.ninv, pr.ninv_sh);
 #pragma unroll
-      for (int e = 0; e < 8; e++) sm[swz(base | (e << lo))] = v[e];
+      for (int e = 0; e < 8; e++) sm[swz(base) ^ swz(e << lo)] = v[e];
       __syncthreads();
     }
 #pragma unroll
-    for (int e = 0; e < 8; e++) v[e] = sm[swz(e * C::NT + t)];
+    for (int e = 0; e < 8; e++) v[e] = sm[swz(t) ^ swz(e * C::NT)];
   } else {
 #pragma unroll
     for (int e = 0; e < 8; e++) v[e] = a[e * C::NT + t];
