@@ -321,6 +321,17 @@ def run_ours(args):
            "batch_limb_polys": nlp, "fwd_GBps_algorithmic": ntt_bytes / (ms_f * 1e-3) / 1e9,
            "kernels": "lazy (internal pipelines); exact_* = the ntt()-semantics kernels"}
     del dn
+    # measurement only (gq_ntt32.cu, not on the product path): the same two-kernel forward transform over 30-bit
+    # primes on 32-bit words, the building block of the internal 31-bit-class RNS basis planned in DESIGN.md
+    # section 4; 720 limb-polys = 184 MB against the 192 MB of the 64-bit batch
+    n32_rate, n32_bad = C.c_double(0), C.c_int(-1)
+    with torch.cuda.stream(ext):
+        ck(lib.gq_bench_ntt32(h, LOGN, 30, 24, 5, C.byref(n32_rate), C.byref(n32_bad)))
+    ntt["ntt32_probe"] = {"fwd_limb_ntt_per_s": world * n32_rate.value, "batch_limb_polys": 720, "prime_bits": 30,
+                          "mismatches_vs_host": n32_bad.value,
+                          "limbs_needed_vs_64bit": "30 (tensor basis) / 48 (key-switch basis) against 16 / 24",
+                          "note": "not used by any product path yet; limb-NTT for limb-NTT it has to be compared with "
+                                  "fwd_limb_ntt_per_s x 16/30"}
 
     # ---- every stage kernel of one he_mul+he_rs, timed alone in the shapes the op uses (gq_stage_* = the
     # kernels the op launches), against both rooflines: algorithmic bytes / HBM peak and 32x32-multiply

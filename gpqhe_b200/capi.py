@@ -88,6 +88,7 @@ SIGNATURES = {
     "gq_he_rlsin_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, vp, vp]),
     "gq_he_slot2coeff": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, vp, vp]),
     "gq_he_slot2coeff_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "gq_bench_ntt32": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
     "gq_bench_intpipe": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "gq_he_mul_rs": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp]),
     "gq_he_mul_batch": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, vp, C.c_int]),

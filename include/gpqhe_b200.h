@@ -273,6 +273,12 @@ int gq_he_neg_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, void *str
    NTT / CRT kernels): lazy Shoup butterflies per second with operands in registers, and raw
    32x32+64 multiply-adds per second.  Runs two short kernels on the context's stream and waits. */
 int gq_bench_intpipe(gq_ctx *ctx, double *butterflies_per_s, double *madwide_per_s);
+/* measurement only (no reference counterpart, not on any product path): forward negacyclic NTT over 30-bit
+   primes on 32-bit words with the same two-kernel structure as the 64-bit transforms, nlimbs x npolys limb-polys
+   per launch, logn in 13..16.  Reports limb-NTTs per second and the number of mismatches of one transform against
+   a plain host implementation (the planned 31-bit-class internal RNS basis). */
+int gq_bench_ntt32(gq_ctx *ctx, unsigned logn, unsigned nlimbs, unsigned npolys, unsigned reps,
+                   double *limb_ntt_per_s, int *mismatches);
 
 /* ---- stage-level entry points (DEVICE pointers, enqueue only) ------------------------
  * One call = one stage of the pipelines above on a limb range [limb0, limb0+nlimbs) (NTT domain,

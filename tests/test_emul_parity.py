@@ -133,3 +133,18 @@ def test_slot2coeff_device_resident(emul_lib, logn, q, Delta, n1, n2, lanes):
 def test_lazy_ntt_vs_exact(emul_lib, logn, logq):
     """single-tile (n <= 2^12) and two-kernel (n >= 2^13) lazy transforms on growth-maximising vectors"""
     pc.check_lazy_ntt_vs_exact(emul_lib, logn, 1 << logq)
+
+
+@pytest.mark.parametrize("logn,nlimbs,npolys", [(13, 2, 1), (14, 3, 2), (16, 2, 1)])
+def test_ntt32_probe_matches_host(emul_lib, logn, nlimbs, npolys):
+    """gq_ntt32.cu (measurement-only 32-bit transform): device output == plain host transform == direct
+    evaluation at psi^(2 brv(j) + 1)"""
+    import ctypes as C
+    ctx = g.HeContext(8, 1 << 120, lib_path=emul_lib, logqub=120)
+    try:
+        rate, bad = C.c_double(0), C.c_int(-1)
+        assert ctx._lib.gq_bench_ntt32(ctx._h, logn, nlimbs, npolys, 1, C.byref(rate), C.byref(bad)) == 0
+        assert bad.value == 0 and rate.value > 0
+        assert ctx._lib.gq_bench_ntt32(ctx._h, 12, 1, 1, 1, C.byref(rate), C.byref(bad)) != 0   # outside 13..16
+    finally:
+        ctx.close()

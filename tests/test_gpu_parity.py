@@ -128,3 +128,16 @@ def test_slot2coeff_device_resident(real_lib):
 def test_lazy_ntt_vs_exact(real_lib, logn, logq):
     pc.check_lazy_ntt_vs_exact(real_lib, logn, 1 << logq, device="cuda:0",
                                limbs=(0, 5, 23) if logq == 438 else None)
+
+
+@pytest.mark.parametrize("logn", [13, 16])
+def test_ntt32_probe_matches_host(real_lib, logn):
+    import ctypes as C
+    import gpqhe_b200 as g
+    ctx = g.HeContext(8, 1 << 120, lib_path=real_lib, logqub=120)
+    try:
+        rate, bad = C.c_double(0), C.c_int(-1)
+        assert ctx._lib.gq_bench_ntt32(ctx._h, logn, 30, 2, 2, C.byref(rate), C.byref(bad)) == 0
+        assert bad.value == 0 and rate.value > 0
+    finally:
+        ctx.close()
