@@ -108,6 +108,10 @@ GQ_DEV void smod_general(uint64_t *acc, const GqModulus &q) {
   for (int w = 0; w < WT; w++) acc[w] = u[w];
 }
 
+// the four batch pointers are kernel parameters: selecting with a chain keeps them in the constant bank (an
+// index computed from blockIdx.y copies the struct to local memory: 64-byte stack frame in the ptxas log)
+GQ_DEV uint64_t *ptr4(const GqPtrs4 &P, int b) { return b == 0 ? P.p[0] : b == 1 ? P.p[1] : b == 2 ? P.p[2] : P.p[3]; }
+
 template <int WT>
 GQ_DEV void store_words(uint64_t *__restrict__ out, int n, int i, int Wout, const uint64_t *acc) {
   const uint64_t fill = (acc[WT - 1] >> 63) ? ~(uint64_t)0 : 0;
@@ -420,7 +424,7 @@ k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
   uint64_t acc[W];
   if (!crt_low<W>(acc, S, B.D, B.F - 64, rhat + (size_t)b * B.D * n, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
   mw_smod_pow2<W>(acc, k);
-  store_words<W>(out.p[b], n, i, Wout, acc);
+  store_words<W>(ptr4(out, b), n, i, Wout, acc);
 }
 
 // key-switch epilogue: T low WP words by crt_low over the D2 basis, r = T mod P exactly over the
@@ -467,7 +471,7 @@ k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pin
     }
   }
   {
-    const uint64_t *ap = add.p[b];
+    const uint64_t *ap = ptr4(add, b);
     uint64_t carry = round_up ? 1u : 0u, top = 0;
 #pragma unroll
     for (int w = 0; w < WQ; w++) {
@@ -479,7 +483,7 @@ k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pin
     }
   }
   mw_smod_pow2<WQ>(Q, k);
-  store_words<WQ>(out.p[b], n, i, Wout, Q);
+  store_words<WQ>(ptr4(out, b), n, i, Wout, Q);
 }
 
 // ---- K4 ---------------------------------------------------------------------------
