@@ -656,7 +656,8 @@ def run_ours(args):
         ck(lib.gq_he_mul_batch(h, L, cnt, outs[0], outs[1], ins[0], ins[1], ins[2], ins[3], evk._h, 1))
     # the host-buffer leg hides more of the copy / compute interplay with more lanes than the device-resident one
     # needs (B200, K = 20: 2 965 ops/s over 3 lanes, 3 060 over 6; `value` is flat to -2 % beyond 3): it gets its own count
-    E2E_LANES = max(LANES, args.e2e_lanes)
+    # (one process per node only: with 2 ranks the host side is the limit and six lanes cost 6 %)
+    E2E_LANES = max(LANES, args.e2e_lanes) if world == 1 else LANES
     ctx.set_lanes(E2E_LANES)
     wcnt = max(args.warmup, 2 * E2E_LANES)
     batch_call(*batch_args(0, wcnt), wcnt)
