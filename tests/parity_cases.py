@@ -435,3 +435,153 @@ def check_lazy_ntt_vs_exact(lib_path, logn, q, device="cpu", limbs=None, seed=1)
 def capi_check(ctx, rc):
     from gpqhe_b200 import capi
     capi.check(ctx._lib, rc)
+
+
+# ---------------------------------------------------------------------------------------------------
+# Compositions at the sizes the configs are quoted on (N = 2^14 .. 2^16), where the Python big-integer
+# oracle would take hours: the device-resident composite entry points (he_gemv, hoisted rotations,
+# he_coeff2slot, he_exp / he_rlsin, he_slot2coeff) against the SAME compositions of oracle/pyoracle.py
+# evaluated over the library's own primitives through the C ABI, one call per primitive.  The primitives
+# are pinned to the oracle / the live reference at these sizes elsewhere (test_full_size_n16_he_mul_rs_rot,
+# dropin_diff); the composition functions are the oracle's own code, so this closes the chain.
+class _GpuPrims:
+    """oracle.pyoracle's primitive names over gpqhe_b200.HeContext calls; ciphertexts are dicts holding
+    word-major numpy arrays instead of lists of ints (the compositions never look inside)."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+        self.keys = {}            # id(host key tuple) -> HeEvk
+
+    def _ct(self, d):
+        return g.HeCt(d["l"], d["c0"], d["c1"], d.get("nu", 1.0), d.get("B", 1.0))
+
+    @staticmethod
+    def _d(c):
+        return {"l": c.l, "c0": c.c0, "c1": c.c1, "nu": c.nu, "B": c.B}
+
+    def he_mul(self, _, a, b, rlk):
+        return self._d(self.ctx.he_mul(self._ct(a), self._ct(b), rlk))
+
+    def he_mulpt(self, _, a, m, dim):
+        assert self.ctx.mulpt_dim(a["l"], m.nu) == dim
+        return self._d(self.ctx.he_mulpt(self._ct(a), m))
+
+    def he_rs(self, _, a):
+        return self._d(self.ctx.he_rs(self._ct(a)))
+
+    def he_moddown(self, _, a):
+        return self._d(self.ctx.he_moddown(self._ct(a)))
+
+    def he_rot(self, _, a, rot, rk_rot):
+        return self._d(self.ctx.he_rot(self._ct(a), rot, {rot: rk_rot}))
+
+    def he_conj(self, _, a, ck):
+        return self._d(self.ctx.he_conj(self._ct(a), ck))
+
+    def he_add(self, _, a, b):
+        return self._d(self.ctx.he_add(self._ct(a), self._ct(b)))
+
+    def he_sub(self, _, a, b):
+        return self._d(self.ctx.he_sub(self._ct(a), self._ct(b)))
+
+    def he_addpt(self, _, a, m, sign=1):
+        return self._d(self.ctx.he_addpt(self._ct(a), m) if sign > 0 else self.ctx.he_subpt(self._ct(a), m))
+
+
+class _patched_oracle:
+    """run the oracle's composition functions with its primitives swapped for `prims`"""
+    NAMES = ("he_mul", "he_mulpt", "he_rs", "he_moddown", "he_rot", "he_conj", "he_add", "he_sub", "he_addpt")
+
+    def __init__(self, prims):
+        self.prims, self.saved = prims, {}
+
+    def __enter__(self):
+        for k in self.NAMES:
+            self.saved[k] = getattr(o, k)
+            setattr(o, k, getattr(self.prims, k))
+
+    def __exit__(self, *a):
+        for k, v in self.saved.items():
+            setattr(o, k, v)
+
+
+def _rand_big(nr, n, W, bits):
+    """uniform on the centred range of 2^bits, word-major two's complement"""
+    w = nr.integers(0, 1 << 63, size=(W, n), dtype=np.uint64) * np.uint64(2) + nr.integers(0, 2, size=(W, n), dtype=np.uint64)
+    sw, sb = (bits - 1) // 64, (bits - 1) % 64
+    top = (w[sw].astype(np.int64) << np.int64(63 - sb)) >> np.int64(63 - sb)
+    w[sw] = top.astype(np.uint64)
+    for k in range(sw + 1, W):
+        w[k] = (top >> np.int64(63)).astype(np.uint64)
+    return w
+
+
+def check_compositions_full_size(lib_path, logn=16, q=1 << 438, Delta=1 << 50, n1=4, n2=4, lanes=3, logqub=0,
+                                 iters=1, seed=2016):
+    nr = np.random.default_rng(seed)
+    slots = n1 * n2
+    ctx = g.HeContext(logn, q, slots, Delta, lib_path=lib_path, logqub=logqub)
+    try:
+        if lanes > 1:
+            ctx.set_lanes(lanes)
+        n, W, L = ctx.n, ctx.W, ctx.L
+        ld = Delta.bit_length() - 1
+        key = lambda: ctx.genevk(np.stack([nr.integers(0, ctx.primes[d], size=n, dtype=np.uint64) for d in range(ctx.dimevk)]),
+                                 np.stack([nr.integers(0, ctx.primes[d], size=n, dtype=np.uint64) for d in range(ctx.dimevk)]))
+        need = sorted(set(range(n1)) | {i * n1 for i in range(n2)})
+        rk = {r: key() for r in need}
+        rlk, ck = key(), key()
+        nu = float(Delta)
+        pt = lambda: g.HePt(_rand_big(nr, n, W, ld + 1), nu=nu)
+        ct = lambda l: {"l": l, "c0": _rand_big(nr, n, W, ctx.ql[l].bit_length() - 1),
+                        "c1": _rand_big(nr, n, W, ctx.ql[l].bit_length() - 1), "nu": nu, "B": 1.0}
+        prims = _GpuPrims(ctx)
+        same = lambda got, want, what: (eq(got.c0, want["c0"], what + " c0"), eq(got.c1, want["c1"], what + " c1"))
+        hc = lambda d: g.HeCt(d["l"], d["c0"], d["c1"], d["nu"], d["B"])
+
+        # hoisted rotations == he_rot, rotation by rotation
+        a = ct(L)
+        outs = ctx.he_rot_hoisted(hc(a), need, rk)
+        for r, got in zip(need, outs):
+            want = ctx.he_rot(hc(a), r, rk)
+            eq(got.c0, want.c0, f"hoisted rotation {r} c0"); eq(got.c1, want.c1, f"hoisted rotation {r} c1")
+
+        # he_gemv (configs[3])
+        pts = [pt() for _ in range(slots)]
+        with _patched_oracle(prims):
+            want = o.he_gemv_encoded(None, a, pts, ctx.mulpt_dim(L, nu), n1, n2, rk)
+        same(ctx.he_gemv_encoded(hc(a), pts, n1, n2, rk), want, "he_gemv")
+
+        # he_coeff2slot (configs[4], CoeffToSlot)
+        pts4 = [[pt() for _ in range(slots)] for _ in range(4)]
+        cm = np.zeros((W, n), dtype=np.uint64)
+        cm[0, 0], cm[0, n // 2] = 12345, (1 << ld) - 77
+        cpt = g.HePt(cm, nu=nu)
+        with _patched_oracle(prims):
+            wre, wim = o.he_coeff2slot_encoded(None, a, pts4, cpt, ctx.mulpt_dim(L, nu), ctx.mulpt_dim(L - 1, nu),
+                                               n1, n2, ck, rk)
+        re, im = ctx.he_coeff2slot_encoded(hc(a), pts4, cpt, n1, n2, ck, rk)
+        same(re, wre, "he_coeff2slot real"); same(im, wim, "he_coeff2slot imag")
+
+        # he_exp / he_rlsin (configs[4], EvalMod), as deep as the levels allow
+        it = min(iters, L - 5) if L >= 5 else -1
+        if it >= 0:
+            epts = [pt()]
+            for k in range(7):
+                z = np.zeros((W, n), dtype=np.uint64)
+                z[0, 0] = int(nr.integers(1, 1 << (ld + 2)))
+                epts.append(g.HePt(z, nu=nu))
+            epts.append(pt())
+            with _patched_oracle(prims):
+                want = o.he_rlsin_encoded(None, a, epts, ctx.mulpt_dim(L, nu), ctx.mulpt_dim(L - 1, nu),
+                                          ctx.mulpt_dim(L - 4 - it, nu), it, rlk, ck)
+            same(ctx.he_rlsin_encoded(hc(a), epts, it, rlk, ck), want, "he_rlsin")
+
+        # he_slot2coeff (configs[4], SlotToCoeff) at a lower level
+        ls = max(1, L - 3)
+        b0, b1 = ct(ls), ct(ls)
+        with _patched_oracle(prims):
+            want = o.he_slot2coeff_encoded(None, b0, b1, pts4[:2], ctx.mulpt_dim(ls, nu), n1, n2, rk)
+        same(ctx.he_slot2coeff_encoded(hc(b0), hc(b1), pts4[:2], n1, n2, rk), want, "he_slot2coeff")
+    finally:
+        ctx.close()

@@ -148,3 +148,9 @@ def test_ntt32_probe_matches_host(emul_lib, logn, nlimbs, npolys):
         assert ctx._lib.gq_bench_ntt32(ctx._h, 12, 1, 1, 1, C.byref(rate), C.byref(bad)) != 0   # outside 13..16
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("logn,q,Delta,n1,n2,lanes", [(5, 1 << 438, 1 << 50, 2, 2, 1), (4, 1 << 438, 1 << 50, 2, 1, 3)])
+def test_compositions_vs_primitives(emul_lib, logn, q, Delta, n1, n2, lanes):
+    """the full-size composition check of the GPU tier, validated here at a toy ring"""
+    pc.check_compositions_full_size(emul_lib, logn, q, Delta, n1, n2, lanes=lanes, logqub=438, iters=1)

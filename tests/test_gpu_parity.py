@@ -141,3 +141,11 @@ def test_ntt32_probe_matches_host(real_lib, logn):
         assert bad.value == 0 and rate.value > 0
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("logn", [16, 14])
+def test_compositions_at_config_size(real_lib, logn):
+    """configs[3] / configs[4] at the sizes they are quoted on (N=2^16; N=2^14 = the KAT ring), slots = 16:
+    he_gemv, hoisted rotations, he_coeff2slot, he_rlsin (iter = 1), he_slot2coeff as ONE device-resident call
+    each against the oracle's compositions run primitive by primitive through the C ABI."""
+    pc.check_compositions_full_size(real_lib, logn, 1 << 438, 1 << 50, 4, 4, lanes=3, iters=1)
