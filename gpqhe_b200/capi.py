@@ -100,7 +100,9 @@ SIGNATURES = {
     "gq_ntt_batch_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.c_int, vp]),
     "gq_poly_rns_mul_batch_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp]),
     "gq_he_mul_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "gq_he_mul_rs_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp, vp]),
     "gq_he_mulpt_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp]),
+    "gq_he_mulpt_rs_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp]),
     "gq_he_rs_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp]),
     "gq_he_moddown_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp]),
     "gq_he_rot_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp]),

@@ -649,15 +649,16 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
   return 0;
 }
 
+// rs_j > 0: he_rs fused behind the CRT (power-of-two q and Delta; the caller checks with rs_fusable)
 static int reconstruct_dev(gq_ctx *c, unsigned D, const uint64_t *rhat, const GqModulus &q,
                            const GqPtrs4 &out, unsigned Wout, unsigned npolys, cudaStream_t st,
-                           unsigned ncoef = 0) {
+                           unsigned ncoef = 0, unsigned rs_j = 0) {
   if (ncoef == 0) ncoef = c->n;
   if (D == 0 || D > c->dimub) GQ_FAIL("basis size out of range");
   if (c->basis[D - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
   if (npolys > 4) GQ_FAIL("at most 4 polynomials per reconstruct launch");
   const int r = gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)ncoef, rhat, q, out, (int)Wout,
-                                      (int)npolys, st, c->fast_crt ? c->d_fix : nullptr);
+                                      (int)npolys, st, c->fast_crt ? c->d_fix : nullptr, rs_j);
   if (r < 0) GQ_FAIL("no reconstruct kernel for this width");
   c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);
@@ -807,7 +808,7 @@ extern "C" void gq_evk_destroy(gq_evk *e) {
 // K6 on a coefficient slice: chat[2][D2][ncoef] -> c0, c1 (W words each), + add0/add1 (may be null)
 static int ks_epilogue_dev(gq_ctx *c, unsigned l, unsigned D2, const uint64_t *B, const uint64_t *add0,
                            const uint64_t *add1, uint64_t *c0, uint64_t *c1, unsigned ncoef,
-                           cudaStream_t st) {
+                           cudaStream_t st, unsigned rs_j = 0) {
   if (ncoef == 0) ncoef = c->n;
   const unsigned n = ncoef, W = c->W;
   if (D2 == 0 || D2 > c->dimub || c->basis[D2 - 1].dev.WT == 0) GQ_FAIL("key-switch basis not supported");
@@ -816,8 +817,9 @@ static int ks_epilogue_dev(gq_ctx *c, unsigned l, unsigned D2, const uint64_t *B
   if (qm.dev.is_pow2) {
     r = gq_launch_ks_epilogue(c->basis[D2 - 1].dev, c->basis[c->dim - 1].dev, c->d_Pinv, c->d_primes,
                               (int)n, B, qm.dev.k, ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st,
-                              c->fast_crt ? c->d_fix : nullptr);
+                              c->fast_crt ? c->d_fix : nullptr, rs_j);
   } else {
+    if (rs_j) GQ_FAIL("fused rescale needs power-of-two moduli");
     r = gq_launch_ks_epilogue_general(c->basis[D2 - 1].dev, c->d_Pwords, (int)c->P.w.size(),
                                       c->d_Pwords + GQ_MAX_W, c->d_primes, (int)n, B, qm.dev,
                                       ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st);
@@ -832,7 +834,7 @@ static int ks_epilogue_dev(gq_ctx *c, unsigned l, unsigned D2, const uint64_t *B
 //   out_k = smod_ql( rdiv(d * evk.p_k, P) + add_k ),  k = 0,1 ; add_k may be null.
 static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk *evk,
                          const uint64_t *add0, const uint64_t *add1, uint64_t *c0, uint64_t *c1,
-                         cudaStream_t st) {
+                         cudaStream_t st, unsigned rs_j = 0) {
   const unsigned D2 = dim_ks(c, l), n = c->n, W = c->W;
   if (D2 > c->dimevk) GQ_FAIL("key-switch basis exceeds dimevk");
   if (!ntt_ok(c, 0, D2)) GQ_FAIL("modulus below 32 bits");
@@ -845,7 +847,7 @@ static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk 
   gq_launch_mul_evk(c->d_primes, (int)n, (int)D2, B, A, evk->p0, evk->p1, st, pm_ok(c, 0, D2));
   c->launches++;
   if (ntt_internal(c, 0, D2, 2, B, true, st)) return 1;
-  return ks_epilogue_dev(c, l, D2, B, add0, add1, c0, c1, 0, st);
+  return ks_epilogue_dev(c, l, D2, B, add0, add1, c0, c1, 0, st, rs_j);
 }
 
 static int he_check(const gq_ctx *c, unsigned l) {
@@ -855,12 +857,26 @@ static int he_check(const gq_ctx *c, unsigned l) {
   return 0;
 }
 
-extern "C" int gq_he_mul_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
-                             const uint64_t *a1, const uint64_t *b0, const uint64_t *b1,
-                             const gq_evk *rlk, void *stream) {
+// he_rs can ride on the CRT kernel that produces the ciphertext when q_l, q_(l-1) and Delta are powers of two
+// (every shipped parameter set): log2(Delta) then, 0 otherwise (the caller launches the rescale kernel)
+static unsigned rs_fusable(const gq_ctx *c, unsigned l) {
+  if (l == 0 || !c->fast_crt) return 0;
+  if ((c->Delta & (c->Delta - 1)) != 0) return 0;
+  const GqModulus &a = c->qmod[l].dev, &b = c->qmod[l - 1].dev;
+  if (!a.is_pow2 || !b.is_pow2 || a.k != b.k + c->logDelta) return 0;
+  return c->logDelta;
+}
+static int rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, bool divide, void *stream, unsigned ncoef);
+
+// he_mul (src/he-mult.c:88-156), optionally with he_rs (src/he-rescale.c:33-54) on the product
+static int he_mul_impl(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                       const uint64_t *a1, const uint64_t *b0, const uint64_t *b1,
+                       const gq_evk *rlk, void *stream, bool rescale) {
   if (he_check(c, l)) return 1;
+  if (rescale && l == 0) GQ_FAIL("cannot go below level 0");
   if (!c0 || !c1 || !a0 || !a1 || !b0 || !b1 || !rlk) GQ_FAIL("null argument");
   cudaStream_t st = pick(c, stream);
+  const unsigned rs_j = rescale ? rs_fusable(c, l) : 0;
   const unsigned D1 = dim_tensor(c, l), n = c->n, W = c->W;
   if (D1 > c->dimub) GQ_FAIL("tensor basis exceeds dimub");
   if (!ntt_ok(c, 0, D1)) GQ_FAIL("modulus below 32 bits");
@@ -878,14 +894,28 @@ extern "C" int gq_he_mul_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, 
   if (ntt_internal(c, 0, D1, 3, B, true, st)) return 1;
   // hot loop B (he-mult.c:139-141): d0, d1, d2 mod q_l
   if (reconstruct_dev(c, D1, B, c->qmod[l].dev, ptrs(d0, d1, d2), W, 3, st)) return 1;
-  // he_relin (he-mult.c:143)
-  return keyswitch_dev(c, l, d2, rlk, d0, d1, c0, c1, st);
+  // he_relin (he-mult.c:143); he_rs in the same epilogue kernel when it can be fused
+  if (keyswitch_dev(c, l, d2, rlk, d0, d1, c0, c1, st, rs_j)) return 1;
+  if (rescale && !rs_j) return rescale_dev(c, l, c0, c1, true, stream, 0);
+  return 0;
+}
+extern "C" int gq_he_mul_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                             const uint64_t *a1, const uint64_t *b0, const uint64_t *b1,
+                             const gq_evk *rlk, void *stream) {
+  return he_mul_impl(c, l, c0, c1, a0, a1, b0, b1, rlk, stream, false);
+}
+extern "C" int gq_he_mul_rs_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                                const uint64_t *a1, const uint64_t *b0, const uint64_t *b1,
+                                const gq_evk *rlk, void *stream) {
+  return he_mul_impl(c, l, c0, c1, a0, a1, b0, b1, rlk, stream, true);
 }
 
-extern "C" int gq_he_mulpt_dev(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
-                               const uint64_t *a0, const uint64_t *a1, const uint64_t *m, void *stream) {
+static int he_mulpt_impl(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
+                         const uint64_t *a0, const uint64_t *a1, const uint64_t *m, void *stream, bool rescale) {
   if (he_check(c, l)) return 1;
+  if (rescale && l == 0) GQ_FAIL("cannot go below level 0");
   if (!c0 || !c1 || !a0 || !a1 || !m) GQ_FAIL("null argument");
+  const unsigned rs_j = rescale ? rs_fusable(c, l) : 0;
   if (dim == 0 || dim > c->dimub) GQ_FAIL("dim out of range");
   if (!ntt_ok(c, 0, dim)) GQ_FAIL("modulus below 32 bits");
   cudaStream_t st = pick(c, stream);
@@ -898,11 +928,21 @@ extern "C" int gq_he_mulpt_dev(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0
   gq_launch_mul_pt(c->d_primes, (int)n, (int)dim, B, A, st, pm_ok(c, 0, dim));
   c->launches++;
   if (ntt_internal(c, 0, dim, 2, B, true, st)) return 1;
-  return reconstruct_dev(c, dim, B, c->qmod[l].dev, ptrs(c0, c1), W, 2, st);
+  if (reconstruct_dev(c, dim, B, c->qmod[l].dev, ptrs(c0, c1), W, 2, st, 0, rs_j)) return 1;
+  if (rescale && !rs_j) return rescale_dev(c, l, c0, c1, true, stream, 0);
+  return 0;
+}
+extern "C" int gq_he_mulpt_dev(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
+                               const uint64_t *a0, const uint64_t *a1, const uint64_t *m, void *stream) {
+  return he_mulpt_impl(c, l, dim, c0, c1, a0, a1, m, stream, false);
+}
+extern "C" int gq_he_mulpt_rs_dev(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
+                                  const uint64_t *a0, const uint64_t *a1, const uint64_t *m, void *stream) {
+  return he_mulpt_impl(c, l, dim, c0, c1, a0, a1, m, stream, true);
 }
 
 static int rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, bool divide, void *stream,
-                       unsigned ncoef = 0) {
+                       unsigned ncoef) {
   if (c && ncoef == 0) ncoef = c->n;
   if (he_check(c, l)) return 1;
   if (l == 0) GQ_FAIL("cannot go below level 0");
@@ -919,10 +959,10 @@ static int rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, bool d
   return 0;
 }
 extern "C" int gq_he_rs_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, void *s) {
-  return rescale_dev(c, l, c0, c1, true, s);
+  return rescale_dev(c, l, c0, c1, true, s, 0);
 }
 extern "C" int gq_he_moddown_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, void *s) {
-  return rescale_dev(c, l, c0, c1, false, s);
+  return rescale_dev(c, l, c0, c1, false, s, 0);
 }
 
 // he_add / he_sub / he_addpt / he_subpt / he_neg (src/he-add.c:32-142): coefficient-local, one launch
@@ -1062,7 +1102,7 @@ extern "C" int gq_he_gemv_dev(gq_ctx *c, unsigned l, unsigned n1, unsigned n2, u
     uint64_t *inner = accs + 2 * (size_t)i * poly;
     if (linear_dev(c, l, outer, outer + poly, outer, outer + poly, inner, inner + poly, 0, 0, stream)) return 1;
   }
-  if (rescale_dev(c, l, outer, outer + poly, true, stream)) return 1;
+  if (rescale_dev(c, l, outer, outer + poly, true, stream, 0)) return 1;
   cudaStream_t st = pick(c, stream);
   GQ_CUDA(cudaMemcpyAsync(c0, outer, poly * 8, cudaMemcpyDeviceToDevice, st));
   GQ_CUDA(cudaMemcpyAsync(c1, outer + poly, poly * 8, cudaMemcpyDeviceToDevice, st));
@@ -1120,8 +1160,7 @@ extern "C" int gq_he_coeff2slot_dev(gq_ctx *c, unsigned l, unsigned n1, unsigned
     if (gq_he_gemv_dev(c, l, n1, n2, dim_gemv, t0, t0 + poly, a0, a1, pts + (2 * part) * m, rk, stream)) return 1;
     if (gq_he_gemv_dev(c, l, n1, n2, dim_gemv, t1, t1 + poly, cj, cj + poly, pts + (2 * part + 1) * m, rk, stream)) return 1;
     if (linear_dev(c, l - 1, o0, o1, t0, t0 + poly, t1, t1 + poly, 0, 0, stream)) return 1;
-    if (gq_he_mulpt_dev(c, l - 1, dim_pt, o0, o1, o0, o1, cpt, stream)) return 1;
-    if (rescale_dev(c, l - 1, o0, o1, true, stream)) return 1;
+    if (he_mulpt_impl(c, l - 1, dim_pt, o0, o1, o0, o1, cpt, stream, true)) return 1;
   }
   return 0;
 }
@@ -1177,30 +1216,29 @@ extern "C" int gq_he_exp_dev(gq_ctx *c, unsigned l, unsigned iter, unsigned dim_
   const Ct act = ct(0), ct2 = ct(1), ct4 = ct(2), ct01 = ct(3), ct23 = ct(4), ct0123 = ct(5), ct45 = ct(6),
            ct67 = ct(7), ct4567 = ct(8);
   void *s = stream;
-  auto mul = [&](unsigned lv, Ct d, Ct x, Ct y) { return gq_he_mul_dev(c, lv, d.p0, d.p1, x.p0, x.p1, y.p0, y.p1, rlk, s); };
-  auto rs = [&](unsigned lv, Ct x) { return rescale_dev(c, lv, x.p0, x.p1, true, s); };
-  auto md = [&](unsigned lv, Ct x) { return rescale_dev(c, lv, x.p0, x.p1, false, s); };
+  // every he_mul of he_exp_taylor is followed by he_rs on its result: one fused epilogue
+  auto mulrs = [&](unsigned lv, Ct d, Ct x, Ct y) { return he_mul_impl(c, lv, d.p0, d.p1, x.p0, x.p1, y.p0, y.p1, rlk, s, true); };
+  auto md = [&](unsigned lv, Ct x) { return rescale_dev(c, lv, x.p0, x.p1, false, s, 0); };
   auto add = [&](unsigned lv, Ct d, Ct x, Ct y) { return linear_dev(c, lv, d.p0, d.p1, x.p0, x.p1, y.p0, y.p1, 0, 0, s); };
   // dest = he_rs(he_mulpt(he_addpt(act, pts[ka]), pts[km]))  (he-algo.c:385-388 and its three siblings)
   auto lin = [&](unsigned lv, Ct d, int ka, int km) {
     if (linear_dev(c, lv, d.p0, d.p1, act.p0, act.p1, pts[ka], nullptr, 0, 3, s)) return 1;
-    if (gq_he_mulpt_dev(c, lv, dim_t, d.p0, d.p1, d.p0, d.p1, pts[km], s)) return 1;
-    return rs(lv, d);
+    return he_mulpt_impl(c, lv, dim_t, d.p0, d.p1, d.p0, d.p1, pts[km], s, true);
   };
-  if (gq_he_mulpt_dev(c, l, dim_a, act.p0, act.p1, a0, a1, pts[0], s) || rs(l, act)) return 1;   // he-algo.c:448-449
+  if (he_mulpt_impl(c, l, dim_a, act.p0, act.p1, a0, a1, pts[0], s, true)) return 1;   // he-algo.c:448-449
   const unsigned k = l - 1;
-  if (mul(k, ct2, act, act) || rs(k, ct2)) return 1;                   // ct^2, level k-1
-  if (mul(k - 1, ct4, ct2, ct2) || rs(k - 1, ct4)) return 1;           // ct^4, level k-2
+  if (mulrs(k, ct2, act, act)) return 1;                               // ct^2, level k-1
+  if (mulrs(k - 1, ct4, ct2, ct2)) return 1;                           // ct^4, level k-2
   if (lin(k, ct01, 1, 1) || md(k - 1, ct01)) return 1;                 // (ct+1)*1, level k-2
-  if (lin(k, ct23, 2, 3) || mul(k - 1, ct23, ct2, ct23) || rs(k - 1, ct23)) return 1;
+  if (lin(k, ct23, 2, 3) || mulrs(k - 1, ct23, ct2, ct23)) return 1;
   if (add(k - 2, ct0123, ct01, ct23) || md(k - 2, ct0123)) return 1;   // level k-3
   if (lin(k, ct45, 4, 5) || md(k - 1, ct45)) return 1;
-  if (lin(k, ct67, 6, 7) || mul(k - 1, ct67, ct2, ct67) || rs(k - 1, ct67)) return 1;
-  if (add(k - 2, ct4567, ct45, ct67) || mul(k - 2, ct4567, ct4, ct4567) || rs(k - 2, ct4567)) return 1;
+  if (lin(k, ct67, 6, 7) || mulrs(k - 1, ct67, ct2, ct67)) return 1;
+  if (add(k - 2, ct4567, ct45, ct67) || mulrs(k - 2, ct4567, ct4, ct4567)) return 1;
   const Ct out{c0, c1};
   if (add(k - 3, out, ct0123, ct4567)) return 1;
   for (unsigned t = 0; t < iter; t++)                                  // he-algo.c:451-454
-    if (mul(k - 3 - t, out, out, out) || rs(k - 3 - t, out)) return 1;
+    if (mulrs(k - 3 - t, out, out, out)) return 1;
   return 0;
 }
 
@@ -1224,8 +1262,7 @@ extern "C" int gq_he_rlsin_dev(gq_ctx *c, unsigned l, unsigned iter, unsigned di
   GQ_CUDA(cudaMemcpyAsync(en, e, 2 * poly * 8, cudaMemcpyDeviceToDevice, st));
   if (gq_he_conj_dev(c, m, en, en + poly, ck, stream)) return 1;
   if (linear_dev(c, m, c0, c1, e, e + poly, en, en + poly, 1, 1, stream)) return 1;
-  if (gq_he_mulpt_dev(c, m, dim_f, c0, c1, c0, c1, pts[8], stream)) return 1;
-  return rescale_dev(c, m, c0, c1, true, stream);
+  return he_mulpt_impl(c, m, dim_f, c0, c1, c0, c1, pts[8], stream, true);
 }
 
 // he_slot2coeff (src/he-bootstrap.c:414-438): he_gemv(U0, ct0) + he_gemv(U1, ct1); pts = the encoded diagonals
@@ -1349,8 +1386,7 @@ extern "C" int gq_he_mul_rs(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, c
   if (!c0 || !c1 || !a0 || !a1 || !b0 || !b1) GQ_FAIL("null argument");
   HostIO io; const uint64_t *src[4] = {a0, a1, b0, b1};
   if (io_begin(c, &io, src, 4)) return 1;
-  if (gq_he_mul_dev(c, l, io.in(5), io.in(6), io.in(0), io.in(1), io.in(2), io.in(3), rlk, nullptr)) return 1;
-  if (rescale_dev(c, l, io.in(5), io.in(6), true, nullptr)) return 1;
+  if (he_mul_impl(c, l, io.in(5), io.in(6), io.in(0), io.in(1), io.in(2), io.in(3), rlk, nullptr, true)) return 1;
   return io_end(&io, c0, c1, 5, 6);
 }
 
@@ -1414,8 +1450,7 @@ extern "C" int gq_he_mul_batch(gq_ctx *c, unsigned l, unsigned count, uint64_t *
     GQ_CUDA(cudaEventRecord(ev[4 * bf + 0], c->s_in));
     GQ_CUDA(cudaStreamWaitEvent(ln->stream, ev[4 * bf + 0], 0));
     if (i >= NB) GQ_CUDA(cudaStreamWaitEvent(ln->stream, ev[4 * bf + 3], 0));
-    rc = gq_he_mul_dev(ln, l, out, out + poly, in, in + poly, in + 2 * poly, in + 3 * poly, rlk, nullptr);
-    if (!rc && rescale) rc = rescale_dev(ln, l, out, out + poly, true, nullptr);
+    rc = he_mul_impl(ln, l, out, out + poly, in, in + poly, in + 2 * poly, in + 3 * poly, rlk, nullptr, rescale != 0);
     if (rc) break;
     GQ_CUDA(cudaEventRecord(ev[4 * bf + 1], ln->stream));
     GQ_CUDA(cudaEventRecord(ev[4 * bf + 2], ln->stream));

@@ -123,15 +123,20 @@ GQ_DEV void store_words(uint64_t *__restrict__ out, int n, int i, int Wout, cons
 
 // ---- K5 ---------------------------------------------------------------------------
 // batch: poly b reads rhat + b*D*n, writes out.p[b]
+// rs_j > 0 (POW2 only): he_rs fused behind the CRT - rounded division by 2^rs_j, then smod 2^(k - rs_j).  The
+// reference reduces smod 2^k first (src/poly.c:117) and divides afterwards (src/he-rescale.c:45-50); with
+// x = T + m*2^k, floor(x / 2^j) = floor(T / 2^j) + m*2^(k-j) and x mod 2^j = T mod 2^j, so dividing the unreduced
+// value and reducing once modulo 2^(k-j) gives the same residue, tie rule included.
 template <int WT, bool POW2>
 GQ_DEV void reconstruct_one(const CrtShared<WT> &S, const GqCrtBasis &B, int n,
                             const uint64_t *__restrict__ rhat, const GqModulus &q, const GqPtrs4 &out,
-                            int Wout, int b, int i) {
+                            int Wout, int b, int i, unsigned rs_j) {
   uint64_t acc[WT + 1];
   crt_mod_P<WT>(acc, S, B, rhat + (size_t)b * B.D * n, n, i);
   crt_centre<WT>(acc, S);
   if (POW2) {
-    if (q.k < 64u * WT) mw_smod_pow2<WT>(acc, q.k);
+    if (rs_j) mw_rdiv_pow2<WT>(acc, rs_j);
+    if (q.k - rs_j < 64u * WT) mw_smod_pow2<WT>(acc, q.k - rs_j);
   } else {
     smod_general<WT>(acc, q);
   }
@@ -145,7 +150,7 @@ template <int WT, bool POW2>
 __global__ void __launch_bounds__(128)
 k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
               const uint64_t *__restrict__ rhat, GqModulus q, GqPtrs4 out, int Wout,
-              int *fix_count, const int *__restrict__ fix_list) {
+              int *fix_count, const int *__restrict__ fix_list, unsigned rs_j) {
   __shared__ CrtShared<WT> S;
   if (fix_list) {
     const int cnt = *fix_count;
@@ -153,7 +158,7 @@ k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
     crt_stage<WT>(S, B, primes);
     __syncthreads();
     for (int e = threadIdx.x; e < cnt; e += blockDim.x)
-      reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, fix_list[e] / n, fix_list[e] % n);
+      reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, fix_list[e] / n, fix_list[e] % n, rs_j);
     __syncthreads();
     if (threadIdx.x == 0) *fix_count = 0;
     return;
@@ -162,7 +167,7 @@ k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, blockIdx.y, i);
+  reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, blockIdx.y, i, rs_j);
 }
 
 // ---- K6 (power-of-two q_l fast path) ------------------------------------------------
@@ -171,7 +176,8 @@ k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
 template <int WT, int WP>
 GQ_DEV void ks_one(const CrtShared<WT> &S, const CrtShared<WP> &SP, const uint64_t *sPinv,
                    const GqCrtBasis &B, const GqCrtBasis &BP, int n, const uint64_t *__restrict__ chat,
-                   unsigned k, const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int b, int i) {
+                   unsigned k, const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int b, int i,
+                   unsigned rs_j) {
   const uint64_t *ch = chat + (size_t)b * B.D * n;
   uint64_t T[WT + 1];
   crt_mod_P<WT>(T, S, B, ch, n, i);
@@ -226,7 +232,8 @@ GQ_DEV void ks_one(const CrtShared<WT> &S, const CrtShared<WP> &SP, const uint64
       carry = (uint64_t)(t >> 64);
     }
   }
-  mw_smod_pow2<WP>(Q, k);
+  if (rs_j) mw_rdiv_pow2<WP>(Q, rs_j);          // he_rs fused (see reconstruct_one)
+  mw_smod_pow2<WP>(Q, k - rs_j);
   store_words<WP>(out.p[b], n, i, Wout, Q);
 }
 
@@ -235,7 +242,7 @@ __global__ void __launch_bounds__(128)
 k_ks_epilogue(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
               const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
               unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout,
-              int *fix_count, const int *__restrict__ fix_list) {
+              int *fix_count, const int *__restrict__ fix_list, unsigned rs_j) {
   __shared__ CrtShared<WT> S;
   __shared__ CrtShared<WP> SP;
   __shared__ uint64_t sPinv[WP];
@@ -247,14 +254,14 @@ k_ks_epilogue(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
   if (fix_list) {   // one block: the coefficients the fast kernel left undecided
     const int cnt = *fix_count;
     for (int e = threadIdx.x; e < cnt; e += blockDim.x)
-      ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, fix_list[e] / n, fix_list[e] % n);
+      ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, fix_list[e] / n, fix_list[e] % n, rs_j);
     __syncthreads();
     if (threadIdx.x == 0) *fix_count = 0;
     return;
   }
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, blockIdx.y, i);
+  ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, blockIdx.y, i, rs_j);
 }
 
 // ---- K6, general modulus: exact long division by P (slow path) -----------------------
@@ -414,7 +421,7 @@ template <int W>
 __global__ void __launch_bounds__(256)
 k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
                    const uint64_t *__restrict__ rhat, unsigned k, GqPtrs4 out, int Wout,
-                   int *fix_count, int *fix_list) {
+                   int *fix_count, int *fix_list, unsigned rs_j) {
   __shared__ CrtSharedLow<W> S;
   crt_low_stage<W>(S, B, primes);
   __syncthreads();
@@ -423,7 +430,8 @@ k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
   const int b = blockIdx.y;
   uint64_t acc[W];
   if (!crt_low<W>(acc, S, B.D, B.F - 64, rhat + (size_t)b * B.D * n, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
-  mw_smod_pow2<W>(acc, k);
+  if (rs_j) mw_rdiv_pow2<W>(acc, rs_j);         // he_rs fused (see reconstruct_one)
+  mw_smod_pow2<W>(acc, k - rs_j);
   store_words<W>(ptr4(out, b), n, i, Wout, acc);
 }
 
@@ -436,7 +444,8 @@ template <int WP, int WQ>
 __global__ void __launch_bounds__(128)
 k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
                    const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
-                   unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout, int *fix_count, int *fix_list) {
+                   unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout, int *fix_count, int *fix_list,
+                   unsigned rs_j) {
   __shared__ CrtSharedLow<WQ> S;
   __shared__ CrtShared<WP> SP;
   __shared__ uint64_t sPinv[WQ];
@@ -482,7 +491,8 @@ k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pin
       carry = (uint64_t)(t >> 64);
     }
   }
-  mw_smod_pow2<WQ>(Q, k);
+  if (rs_j) mw_rdiv_pow2<WQ>(Q, rs_j);          // he_rs fused into the epilogue: the quotient is in registers
+  mw_smod_pow2<WQ>(Q, k - rs_j);
   store_words<WQ>(ptr4(out, b), n, i, Wout, Q);
 }
 
@@ -689,7 +699,8 @@ k_decompose(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *
 // by the exact kernel in list mode (power-of-two q only).  Returns kernels launched.
 int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix) {
+                          cudaStream_t st, int *fix, unsigned rs_j) {
+  if (rs_j && (!q.is_pow2 || rs_j > q.k)) return -1;
   dim3 grid((n + 127) / 128, npolys), block(128);
   int *fc = nullptr, *fl = nullptr;
   int launches = 1;
@@ -697,7 +708,7 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
     fc = fix; fl = fix + 4;
     const int W = (int)((q.k + 63) / 64);
     dim3 g2((n + 255) / 256, npolys), b2(256);
-#define GQ_RF(V) GQ_LAUNCH(k_reconstruct_fast<V>, g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl)
+#define GQ_RF(V) GQ_LAUNCH(k_reconstruct_fast<V>, g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j)
     if (W <= 1) GQ_RF(1); else if (W <= 2) GQ_RF(2); else if (W <= 3) GQ_RF(3); else if (W <= 4) GQ_RF(4);
     else if (W <= 5) GQ_RF(5); else if (W <= 6) GQ_RF(6); else if (W <= 7) GQ_RF(7); else if (W <= 8) GQ_RF(8);
     else if (W <= 12) GQ_RF(12); else if (W <= 16) GQ_RF(16); else if (W <= 24) GQ_RF(24); else GQ_RF(32);
@@ -707,16 +718,16 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
   }
   if (q.is_pow2) {
     GQ_WT_SWITCH(B.WT,
-      GQ_LAUNCH((k_reconstruct<8, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
-      GQ_LAUNCH((k_reconstruct<16, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
-      GQ_LAUNCH((k_reconstruct<24, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
-      GQ_LAUNCH((k_reconstruct<32, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl))
+      GQ_LAUNCH((k_reconstruct<8, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
+      GQ_LAUNCH((k_reconstruct<16, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
+      GQ_LAUNCH((k_reconstruct<24, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
+      GQ_LAUNCH((k_reconstruct<32, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j))
   } else {
     GQ_WT_SWITCH(B.WT,
-      GQ_LAUNCH((k_reconstruct<8, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
-      GQ_LAUNCH((k_reconstruct<16, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
-      GQ_LAUNCH((k_reconstruct<24, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl),
-      GQ_LAUNCH((k_reconstruct<32, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl))
+      GQ_LAUNCH((k_reconstruct<8, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
+      GQ_LAUNCH((k_reconstruct<16, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
+      GQ_LAUNCH((k_reconstruct<24, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
+      GQ_LAUNCH((k_reconstruct<32, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j))
   }
   return launches;
 }
@@ -725,10 +736,10 @@ template <int WT>
 static int ks_dispatch_wp(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, dim3 grid,
-                          cudaStream_t st, int *fc, int *fl) {
+                          cudaStream_t st, int *fc, int *fl, unsigned rs_j) {
   dim3 block(128);
   if (BP.WT > WT) return -1;
-#define GQ_KS(WPV) GQ_LAUNCH((k_ks_epilogue<WT, (WT >= WPV ? WPV : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl)
+#define GQ_KS(WPV) GQ_LAUNCH((k_ks_epilogue<WT, (WT >= WPV ? WPV : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j)
   switch (BP.WT) {
     case 8: GQ_KS(8); return 1;
     case 16: if (WT >= 16) { GQ_KS(16); return 1; } return -1;
@@ -742,7 +753,8 @@ static int ks_dispatch_wp(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
 int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix) {
+                          cudaStream_t st, int *fix, unsigned rs_j) {
+  if (rs_j > k) return -1;
   dim3 grid((n + 127) / 128, npolys);
   int *fc = nullptr, *fl = nullptr;
   int launches = 1;
@@ -750,11 +762,11 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
     fc = fix; fl = fix + 4;
     dim3 block(128);
     switch (BP.WT) {
-#define GQ_KF(V) case V: GQ_LAUNCH((k_ks_epilogue_fast<V, V>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl); break;
+#define GQ_KF(V) case V: GQ_LAUNCH((k_ks_epilogue_fast<V, V>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j); break;
       case 8:     // the shipped parameter sets (logq = 438: 7 words per coefficient, P of 8 words) and their neighbours
-        if (Wout == 7 && Wadd <= 7 && k < 64u * 7) GQ_LAUNCH((k_ks_epilogue_fast<8, 7>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl);
-        else if (Wout == 6 && Wadd <= 6 && k < 64u * 6) GQ_LAUNCH((k_ks_epilogue_fast<8, 6>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl);
-        else GQ_LAUNCH((k_ks_epilogue_fast<8, 8>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl);
+        if (Wout == 7 && Wadd <= 7 && k < 64u * 7) GQ_LAUNCH((k_ks_epilogue_fast<8, 7>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j);
+        else if (Wout == 6 && Wadd <= 6 && k < 64u * 6) GQ_LAUNCH((k_ks_epilogue_fast<8, 6>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j);
+        else GQ_LAUNCH((k_ks_epilogue_fast<8, 8>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j);
         break;
       GQ_KF(16) GQ_KF(24) GQ_KF(32)
 #undef GQ_KF
@@ -765,10 +777,10 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
   }
   int r = -1;
   switch (B.WT) {
-    case 8: r = ks_dispatch_wp<8>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl); break;
-    case 16: r = ks_dispatch_wp<16>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl); break;
-    case 24: r = ks_dispatch_wp<24>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl); break;
-    case 32: r = ks_dispatch_wp<32>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl); break;
+    case 8: r = ks_dispatch_wp<8>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j); break;
+    case 16: r = ks_dispatch_wp<16>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j); break;
+    case 24: r = ks_dispatch_wp<24>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j); break;
+    case 32: r = ks_dispatch_wp<32>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j); break;
   }
   return r < 0 ? r : launches;
 }

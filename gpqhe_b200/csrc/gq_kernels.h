@@ -29,16 +29,17 @@ void gq_launch_mul_pt(const GqPrime *primes, int n, int D, uint64_t *y, const ui
 
 // K4/K5/K6 (gq_crt.cu); return the number of kernels launched, <0 when no instantiation fits.
 // fix = device scratch {int count (16-byte slot), int list[4n]}: enables the fast low-word kernels
+// rs_j > 0 (power-of-two q and Delta only): he_rs fused behind the CRT, the output is rdiv(., 2^rs_j) smod 2^(k-rs_j)
 // digits: 32-bit digit kernel (every prime of the range needs >= 33 and <= 60 bits)
 int gq_launch_decompose(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
                         int W, uint64_t *out, int npolys, cudaStream_t st, int digits = false);
 int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix = nullptr);
+                          cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0);
 int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix = nullptr);
+                          cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0);
 // general-modulus key-switch epilogue (exact long division, slow path)
 int gq_launch_ks_epilogue_general(const GqCrtBasis &B, const uint64_t *P, int nP,
                                   const uint64_t *Ph, const GqPrime *primes, int n,

@@ -229,8 +229,18 @@ int gq_poly_rns_mul_batch_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsi
 int gq_he_mul_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
                   const uint64_t *a1, const uint64_t *b0, const uint64_t *b1, const gq_evk *rlk,
                   void *stream);
+/* he_mul immediately followed by he_rs on the product (src/he-mult.c:88-156, src/he-rescale.c:33-54): when q_l and
+   Delta are powers of two the rounded division rides in the key-switch epilogue kernel (the quotient is still in
+   registers), otherwise it is the separate rescale kernel; same bits either way.  Result at level l-1. */
+int gq_he_mul_rs_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const uint64_t *a0,
+                     const uint64_t *a1, const uint64_t *b0, const uint64_t *b1, const gq_evk *rlk,
+                     void *stream);
 int gq_he_mulpt_dev(gq_ctx *ctx, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
                     const uint64_t *a0, const uint64_t *a1, const uint64_t *m, void *stream);
+/* he_mulpt followed by he_rs (the pair he_exp_taylor and he_coeff2slot make, src/he-algo.c:385-388,
+   src/he-bootstrap.c:386-388), the division fused behind the CRT as in gq_he_mul_rs_dev */
+int gq_he_mulpt_rs_dev(gq_ctx *ctx, unsigned l, unsigned dim, uint64_t *c0, uint64_t *c1,
+                       const uint64_t *a0, const uint64_t *a1, const uint64_t *m, void *stream);
 int gq_he_rs_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, void *stream);
 int gq_he_moddown_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, void *stream);
 int gq_he_rot_dev(gq_ctx *ctx, unsigned l, unsigned rot, uint64_t *c0, uint64_t *c1,

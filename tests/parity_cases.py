@@ -585,3 +585,42 @@ def check_compositions_full_size(lib_path, logn=16, q=1 << 438, Delta=1 << 50, n
         same(ctx.he_slot2coeff_encoded(hc(b0), hc(b1), pts4[:2], n1, n2, rk), want, "he_slot2coeff")
     finally:
         ctx.close()
+
+
+def check_fused_rescale_ties(lib_path, logn=5, q=1 << 438, Delta=1 << 50, logqub=438, seed=9):
+    """he_rs fused into the key-switch epilogue (gq_he_mul_rs / gq_he_mul_batch): mpi_rdiv's tie rule
+    (src/types.c:115-128: remainder == Delta/2 rounds toward -inf) on products whose remainder modulo Delta is
+    exactly Delta/2, Delta/2 +- 1, 0 and Delta - 1, positive and negative.  Multiplying by the trivial ciphertext
+    (1, 0) makes he_mul return its other operand unchanged (d2 = 0), so the values entering the division are chosen."""
+    rng = random.Random(seed)
+    ctx = g.HeContext(logn, q, 4, Delta, lib_path=lib_path, logqub=logqub)
+    oc = o.Ctx(logn, q, 4, Delta, logqub=logqub or None)
+    try:
+        n, W = ctx.n, ctx.W
+        rlk = (rlimbs(rng, oc.primes, n, oc.dimevk), rlimbs(rng, oc.primes, n, oc.dimevk))
+        drlk = ctx.genevk(*rlk)
+        for l in sorted({oc.L, max(1, oc.L // 2), 1}, reverse=True):
+            ql, half = oc.ql[l], Delta // 2
+            rems = [half, half + 1, half - 1, 0, Delta - 1, 1]
+            vals = []
+            for i in range(n):
+                hi = rng.randrange(ql // Delta) - ql // (2 * Delta)
+                v = hi * Delta + rems[i % len(rems)]
+                vals.append(o.mpi_smod(v % ql, ql, ql // 2))
+            a0, a1 = vals, [-v if -v >= -(ql // 2) and -v < ql - ql // 2 else v for v in reversed(vals)]
+            a1 = [o.mpi_smod(x % ql, ql, ql // 2) for x in a1]
+            one, zero = [1] + [0] * (n - 1), [0] * n
+            cta = g.HeCt(l, g.ints_to_big(a0, W), g.ints_to_big(a1, W))
+            ctb = g.HeCt(l, g.ints_to_big(one, W), g.ints_to_big(zero, W))
+            want = o.he_rs(oc, o.he_mul(oc, {"l": l, "c0": a0, "c1": a1}, {"l": l, "c0": one, "c1": zero}, rlk))
+            assert want["c0"] == o.he_rs(oc, {"l": l, "c0": a0, "c1": a1})["c0"]      # the construction holds
+            got = ctx.he_mul_rs(cta, ctb, drlk)
+            assert got.l == l - 1
+            assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], ("fused he_mul+he_rs ties", l)
+            got2 = ctx.he_mul_batch([(cta, ctb), (ctb, cta)], drlk, rescale=True)
+            for r in got2:
+                assert g.big_to_ints(r.c0) == want["c0"] and g.big_to_ints(r.c1) == want["c1"], ("batch ties", l)
+            sep = ctx.he_rs(ctx.he_mul(cta, ctb, drlk))                                 # two kernels, same bits
+            eq(sep.c0, got.c0, "fused == separate c0"); eq(sep.c1, got.c1, "fused == separate c1")
+    finally:
+        ctx.close()

@@ -154,3 +154,8 @@ def test_ntt32_probe_matches_host(emul_lib, logn, nlimbs, npolys):
 def test_compositions_vs_primitives(emul_lib, logn, q, Delta, n1, n2, lanes):
     """the full-size composition check of the GPU tier, validated here at a toy ring"""
     pc.check_compositions_full_size(emul_lib, logn, q, Delta, n1, n2, lanes=lanes, logqub=438, iters=1)
+
+
+def test_fused_rescale_tie_rule(emul_lib):
+    pc.check_fused_rescale_ties(emul_lib)
+    pc.check_fused_rescale_ties(emul_lib, logn=4, q=1 << 120, Delta=1 << 40, logqub=120)

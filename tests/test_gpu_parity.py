@@ -149,3 +149,8 @@ def test_compositions_at_config_size(real_lib, logn):
     he_gemv, hoisted rotations, he_coeff2slot, he_rlsin (iter = 1), he_slot2coeff as ONE device-resident call
     each against the oracle's compositions run primitive by primitive through the C ABI."""
     pc.check_compositions_full_size(real_lib, logn, 1 << 438, 1 << 50, 4, 4, lanes=3, iters=1)
+
+
+def test_fused_rescale_tie_rule(real_lib):
+    pc.check_fused_rescale_ties(real_lib)
+    pc.check_fused_rescale_ties(real_lib, logn=13, q=1 << 120, Delta=1 << 40, logqub=120)
