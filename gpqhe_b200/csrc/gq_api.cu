@@ -143,6 +143,7 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
     uint64_t inv = powm(phat.mod_u64(pd), pd - 2, pd);   // precomp.c:289
     hinv[d] = inv;
     hinvsh[d] = (uint64_t)(((gq_u128)inv << 64) / pd);
+    hb.inv.push_back(inv);
   }
   // fixed point for the fast CRT kernels: F = 64 + bits(p) - 1 when every prime has the same length
   int F = 64 + (int)c->primes[0].bits - 1;
@@ -174,6 +175,36 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
     B.recip = (uint64_t)(num / t1);
   } else {
     B.sh = -1; B.recip = 0;
+  }
+  return 0;
+}
+
+// Final-scale tables of the lazy inverse NTT with the CRT pre-multiplication folded in, one pair per prefix basis
+// (K x K Shoup pairs, a few KB), and for the key switch the factors that turn the pre-scaled residues of a basis D
+// into those of the special-modulus basis {p_0..p_(dim-1)}.  Built once per context (lanes share them).
+static int build_prescale(gq_ctx *c) {
+  const unsigned K = c->dimub;
+  if (getenv("GPQHE_B200_NO_PRESCALE")) return 0;
+  for (unsigned D = 1; D <= K; D++) {
+    GqHostBasis &hb = c->basis[D - 1];
+    if (hb.dev.WT == 0 || hb.dev.F == 0 || hb.inv.size() != D) continue;
+    std::vector<ulonglong2> fs(K, make_ulonglong2(0, 0)), fw(K, make_ulonglong2(0, 0));
+    for (unsigned d = 0; d < D; d++) {
+      const GqPrime &P = c->primes[d];
+      const uint64_t sv = mulm(P.ninv, hb.inv[d], P.p), wv = mulm(c->h_inv1[d], sv, P.p);
+      fs[d] = make_ulonglong2(sv, (uint64_t)(((gq_u128)sv << 64) / P.p));
+      fw[d] = make_ulonglong2(wv, (uint64_t)(((gq_u128)wv << 64) / P.p));
+    }
+    if (upload(&hb.fin_s, fs.data(), fs.size()) || upload(&hb.fin_w, fw.data(), fw.size())) return 1;
+    if (c->has_he && D >= c->dim && c->basis[c->dim - 1].inv.size() == c->dim) {
+      std::vector<ulonglong2> rt(c->dim);
+      for (unsigned d = 0; d < c->dim; d++) {
+        const GqPrime &P = c->primes[d];
+        const uint64_t r = mulm(c->basis[c->dim - 1].inv[d], powm(hb.inv[d], P.p - 2, P.p), P.p);
+        rt[d] = make_ulonglong2(r, (uint64_t)(((gq_u128)r << 64) / P.p));
+      }
+      if (upload(&hb.ratio, rt.data(), rt.size())) return 1;
+    }
   }
   return 0;
 }
@@ -256,9 +287,14 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
       }
       uint64_t wl = mulm(iv[1].x, P.ninv, P.p);
       last[d] = make_ulonglong2(wl, (uint64_t)(((gq_u128)wl << 64) / P.p));
+      c->h_inv1.push_back(iv[1].x);
     }
+    std::vector<ulonglong2> fs(K);
+    for (unsigned d = 0; d < K; d++) fs[d] = make_ulonglong2(c->primes[d].ninv, c->primes[d].ninv_sh);
     if (upload(&c->d_tw_fwd, fwd.data(), fwd.size()) || upload(&c->d_tw_inv, inv.data(), inv.size()) ||
-        upload(&c->d_tw_inv_last, last.data(), last.size())) { gq_ctx_destroy(c); return 1; }
+        upload(&c->d_tw_inv_last, last.data(), last.size()) || upload(&c->d_fin_s, fs.data(), fs.size())) {
+      gq_ctx_destroy(c); return 1;
+    }
   }
   if (upload(&c->d_primes, c->primes.data(), K)) { gq_ctx_destroy(c); return 1; }
   {   // decompose table: 2^(64w) mod p
@@ -362,6 +398,7 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
   } else {
     c->W = (c->q.bits() + 63) / 64;
   }
+  if (build_prescale(c)) { gq_ctx_destroy(c); return 1; }
   *out = c;
   return 0;
 }
@@ -373,7 +410,8 @@ extern "C" void gq_ctx_destroy(gq_ctx *c) {
   c->lanes.clear();
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (!c->parent) {     // a lane shares the tables of its parent
-    cudaFree(c->d_primes); cudaFree(c->d_tw_fwd); cudaFree(c->d_tw_inv); cudaFree(c->d_tw_inv_last);
+    cudaFree(c->d_primes); cudaFree(c->d_tw_fwd); cudaFree(c->d_tw_inv); cudaFree(c->d_tw_inv_last); cudaFree(c->d_fin_s);
+    for (auto &b : c->basis) { cudaFree(b.fin_s); cudaFree(b.fin_w); cudaFree(b.ratio); }
     cudaFree(c->d_pow64); cudaFree(c->d_t1sh); cudaFree(c->d_pow32); cudaFree(c->d_pow28); cudaFree(c->d_onesh); cudaFree(c->d_Pinv); cudaFree(c->d_Pwords);
     for (auto &b : c->basis) cudaFree(b.blob);
     for (auto &m : c->qmod) cudaFree(m.blob);
@@ -552,18 +590,49 @@ static bool pm_ok(const gq_ctx *c, unsigned limb0, unsigned nlimbs) {
 
 // NTT of the internal pipelines: canonical in / canonical out is all they need, so the lazy
 // kernels are used whenever every prime of the range has the shape they assume.
-static int ntt_internal(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys, uint64_t *data,
-                        bool inverse, cudaStream_t st, int only = 0) {
-  bool lazy = c->lazy_ntt;
+static bool lazy_ok(const gq_ctx *c, unsigned limb0, unsigned nlimbs) {
+  bool lazy = c->lazy_ntt && limb0 + nlimbs <= c->dimub;
   for (unsigned d = limb0; lazy && d < limb0 + nlimbs; d++) {
     const GqPrime &P = c->primes[d];
     if (P.bits < 33 || P.bits > 60) { lazy = false; break; }
     const uint64_t top = 1ull << (P.bits - 1), cc = P.p - top;
     if (cc >= (top >> 5)) lazy = false;      // gq_ntt_lazy.cu: 32c < 2^sh
   }
-  if (!lazy) return gq_ntt_batch_dev(c, limb0, nlimbs, npolys, data, (inverse ? 1 : 0) | (only << 1), (void *)st);
+  return lazy;
+}
+// scaleD > 0 (lazy kernels only; the caller checked crt_pre_ok): the inverse transform ends with the CRT
+// pre-multiplication of the basis {p_0..p_(scaleD-1)} folded into N^-1
+static int ntt_internal(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys, uint64_t *data,
+                        bool inverse, cudaStream_t st, int only = 0, unsigned scaleD = 0) {
+  const bool lazy = lazy_ok(c, limb0, nlimbs);
+  if (!lazy) {
+    if (scaleD) GQ_FAIL("internal: pre-scaled inverse NTT needs the lazy kernels");
+    return gq_ntt_batch_dev(c, limb0, nlimbs, npolys, data, (inverse ? 1 : 0) | (only << 1), (void *)st);
+  }
   if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
-  int r = gq_launch_ntt_lazy(c->ntt_tables(), data, (int)limb0, (int)nlimbs, (int)npolys, inverse, st, only);
+  int r = gq_launch_ntt_lazy(c->ntt_tables(inverse ? scaleD : 0), data, (int)limb0, (int)nlimbs, (int)npolys, inverse, st, only);
+  if (r < 0) GQ_FAIL("unsupported ring degree");
+  c->launches += (unsigned)r;
+  GQ_CHECK_LAUNCH(c);
+  return 0;
+}
+
+// The residues entering the CRT over {p_0..p_(D-1)} may arrive pre-multiplied by (P/p_d)^-1 (folded into the final
+// scaling of the lazy inverse NTT) when the fast CRT kernels will consume them: power-of-two modulus, fixed-point
+// constants available, tables built.
+static bool crt_pre_ok(const gq_ctx *c, unsigned D, const GqModulus &q) {
+  if (D == 0 || D > c->dimub || !c->fast_crt || !lazy_ok(c, 0, D)) return false;
+  const GqHostBasis &hb = c->basis[D - 1];
+  return hb.fin_s && hb.dev.F && hb.dev.WT && q.is_pow2 && q.k >= 1 && q.k <= 64u * GQ_MAX_W;
+}
+
+// pointwise stage + inverse NTT in one pass when the lazy kernels and the pseudo-Mersenne products apply to the
+// whole range (gq_launch_ntt_lazy_fused); false = the caller runs the separate pointwise kernel and ntt_internal
+static bool fused_inv_ok(const gq_ctx *c, unsigned limb0, unsigned nlimbs);
+static int ntt_inv_fused(gq_ctx *c, int mode, unsigned limb0, unsigned nlimbs, const uint64_t *x, uint64_t *y,
+                         const uint64_t *e0, const uint64_t *e1, uint64_t g, cudaStream_t st, unsigned scaleD) {
+  if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
+  int r = gq_launch_ntt_lazy_fused(c->ntt_tables(scaleD), mode, x, y, e0, e1, (unsigned)g, (int)limb0, (int)nlimbs, st);
   if (r < 0) GQ_FAIL("unsupported ring degree");
   c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);
@@ -620,6 +689,11 @@ extern "C" int gq_poly_rns_mul(gq_ctx *c, unsigned limb, uint64_t *r, const uint
   return binary_host(c, limb, r, a, b, true);
 }
 
+static bool pm_ok(const gq_ctx *c, unsigned limb0, unsigned nlimbs);
+static bool fused_inv_ok(const gq_ctx *c, unsigned limb0, unsigned nlimbs) {
+  return !getenv("GPQHE_B200_NO_FUSED_INV") && lazy_ok(c, limb0, nlimbs) && pm_ok(c, limb0, nlimbs);
+}
+
 // ------------------------------------------------------------------- MPI <-> RNS (device)
 static GqPtrs4 ptrs(const uint64_t *a, const uint64_t *b = nullptr, const uint64_t *c2 = nullptr,
                     const uint64_t *d = nullptr) {
@@ -652,13 +726,13 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
 // rs_j > 0: he_rs fused behind the CRT (power-of-two q and Delta; the caller checks with rs_fusable)
 static int reconstruct_dev(gq_ctx *c, unsigned D, const uint64_t *rhat, const GqModulus &q,
                            const GqPtrs4 &out, unsigned Wout, unsigned npolys, cudaStream_t st,
-                           unsigned ncoef = 0, unsigned rs_j = 0) {
+                           unsigned ncoef = 0, unsigned rs_j = 0, bool pre = false) {
   if (ncoef == 0) ncoef = c->n;
   if (D == 0 || D > c->dimub) GQ_FAIL("basis size out of range");
   if (c->basis[D - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
   if (npolys > 4) GQ_FAIL("at most 4 polynomials per reconstruct launch");
   const int r = gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)ncoef, rhat, q, out, (int)Wout,
-                                      (int)npolys, st, c->fast_crt ? c->d_fix : nullptr, rs_j);
+                                      (int)npolys, st, c->fast_crt ? c->d_fix : nullptr, rs_j, pre);
   if (r < 0) GQ_FAIL("no reconstruct kernel for this width");
   c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);
@@ -727,12 +801,17 @@ extern "C" int gq_poly_mul(gq_ctx *c, uint64_t *r, unsigned Wr, const uint64_t *
   cudaStream_t st = c->stream;
   GQ_CUDA(cudaMemcpyAsync(da, a, ib, cudaMemcpyHostToDevice, st));
   GQ_CUDA(cudaMemcpyAsync(db, b, ib, cudaMemcpyHostToDevice, st));
+  const bool pre = crt_pre_ok(c, dim, m);
   if (decompose_dev(c, 0, dim, ptrs(da, db), W, 2, A, st)) return 1;
   if (ntt_internal(c, 0, dim, 2, A, false, st)) return 1;
-  gq_launch_binary(c->d_primes, (int)n, 0, (int)dim, 1, true, B, A, A + (size_t)dim * n, st);   // poly_mul: Barrett as is
-  c->launches++;
-  if (ntt_internal(c, 0, dim, 1, B, true, st)) return 1;
-  if (reconstruct_dev(c, dim, B, m, ptrs(dr), Wr, 1, st)) return 1;
+  if (fused_inv_ok(c, 0, dim)) {
+    if (ntt_inv_fused(c, GQ_NTTF_MUL, 0, dim, A, B, nullptr, nullptr, 1, st, pre ? dim : 0)) return 1;
+  } else {
+    gq_launch_binary(c->d_primes, (int)n, 0, (int)dim, 1, true, B, A, A + (size_t)dim * n, st);   // poly_mul: Barrett as is
+    c->launches++;
+    if (ntt_internal(c, 0, dim, 1, B, true, st, 0, pre ? dim : 0)) return 1;
+  }
+  if (reconstruct_dev(c, dim, B, m, ptrs(dr), Wr, 1, st, 0, 0, pre)) return 1;
   GQ_CUDA(cudaMemcpyAsync(r, dr, ob, cudaMemcpyDeviceToHost, st));
   GQ_CUDA(cudaStreamSynchronize(st));
   return 0;
@@ -808,7 +887,7 @@ extern "C" void gq_evk_destroy(gq_evk *e) {
 // K6 on a coefficient slice: chat[2][D2][ncoef] -> c0, c1 (W words each), + add0/add1 (may be null)
 static int ks_epilogue_dev(gq_ctx *c, unsigned l, unsigned D2, const uint64_t *B, const uint64_t *add0,
                            const uint64_t *add1, uint64_t *c0, uint64_t *c1, unsigned ncoef,
-                           cudaStream_t st, unsigned rs_j = 0) {
+                           cudaStream_t st, unsigned rs_j = 0, bool pre = false) {
   if (ncoef == 0) ncoef = c->n;
   const unsigned n = ncoef, W = c->W;
   if (D2 == 0 || D2 > c->dimub || c->basis[D2 - 1].dev.WT == 0) GQ_FAIL("key-switch basis not supported");
@@ -817,9 +896,9 @@ static int ks_epilogue_dev(gq_ctx *c, unsigned l, unsigned D2, const uint64_t *B
   if (qm.dev.is_pow2) {
     r = gq_launch_ks_epilogue(c->basis[D2 - 1].dev, c->basis[c->dim - 1].dev, c->d_Pinv, c->d_primes,
                               (int)n, B, qm.dev.k, ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st,
-                              c->fast_crt ? c->d_fix : nullptr, rs_j);
+                              c->fast_crt ? c->d_fix : nullptr, rs_j, pre ? c->basis[D2 - 1].ratio : nullptr);
   } else {
-    if (rs_j) GQ_FAIL("fused rescale needs power-of-two moduli");
+    if (rs_j || pre) GQ_FAIL("fused rescale / pre-scaled residues need power-of-two moduli");
     r = gq_launch_ks_epilogue_general(c->basis[D2 - 1].dev, c->d_Pwords, (int)c->P.w.size(),
                                       c->d_Pwords + GQ_MAX_W, c->d_primes, (int)n, B, qm.dev,
                                       ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st);
@@ -842,12 +921,17 @@ static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk 
   if (ensure_slot(c, GQ_SLOT_LIMB_A, (size_t)4 * c->dimub * n * 8) ||
       ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8)) return 1;
   uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
+  const bool pre = crt_pre_ok(c, D2, c->qmod[l].dev) && c->basis[D2 - 1].ratio && D2 >= c->dim;
   if (decompose_dev(c, 0, D2, ptrs(d), W, 1, A, st)) return 1;
   if (ntt_internal(c, 0, D2, 1, A, false, st)) return 1;
-  gq_launch_mul_evk(c->d_primes, (int)n, (int)D2, B, A, evk->p0, evk->p1, st, pm_ok(c, 0, D2));
-  c->launches++;
-  if (ntt_internal(c, 0, D2, 2, B, true, st)) return 1;
-  return ks_epilogue_dev(c, l, D2, B, add0, add1, c0, c1, 0, st, rs_j);
+  if (fused_inv_ok(c, 0, D2)) {
+    if (ntt_inv_fused(c, GQ_NTTF_EVK, 0, D2, A, B, evk->p0, evk->p1, 1, st, pre ? D2 : 0)) return 1;
+  } else {
+    gq_launch_mul_evk(c->d_primes, (int)n, (int)D2, B, A, evk->p0, evk->p1, st, pm_ok(c, 0, D2));
+    c->launches++;
+    if (ntt_internal(c, 0, D2, 2, B, true, st, 0, pre ? D2 : 0)) return 1;
+  }
+  return ks_epilogue_dev(c, l, D2, B, add0, add1, c0, c1, 0, st, rs_j, pre);
 }
 
 static int he_check(const gq_ctx *c, unsigned l) {
@@ -887,13 +971,18 @@ static int he_mul_impl(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, const 
   uint64_t *big = (uint64_t *)c->slot[GQ_SLOT_BIG];
   uint64_t *d0 = big, *d1 = big + (size_t)W * n, *d2 = big + 2 * (size_t)W * n;
   // hot loop A (he-mult.c:116-138): decompose, forward NTT, tensor, inverse NTT
+  const bool pre = crt_pre_ok(c, D1, c->qmod[l].dev);
   if (decompose_dev(c, 0, D1, ptrs(a0, a1, b0, b1), W, 4, A, st)) return 1;
   if (ntt_internal(c, 0, D1, 4, A, false, st)) return 1;
-  gq_launch_tensor(c->d_primes, (int)n, (int)D1, B, A, st, pm_ok(c, 0, D1));
-  c->launches++;
-  if (ntt_internal(c, 0, D1, 3, B, true, st)) return 1;
+  if (fused_inv_ok(c, 0, D1)) {      // tensor product formed while the inverse transform loads its tiles
+    if (ntt_inv_fused(c, GQ_NTTF_TENSOR, 0, D1, A, B, nullptr, nullptr, 1, st, pre ? D1 : 0)) return 1;
+  } else {
+    gq_launch_tensor(c->d_primes, (int)n, (int)D1, B, A, st, pm_ok(c, 0, D1));
+    c->launches++;
+    if (ntt_internal(c, 0, D1, 3, B, true, st, 0, pre ? D1 : 0)) return 1;
+  }
   // hot loop B (he-mult.c:139-141): d0, d1, d2 mod q_l
-  if (reconstruct_dev(c, D1, B, c->qmod[l].dev, ptrs(d0, d1, d2), W, 3, st)) return 1;
+  if (reconstruct_dev(c, D1, B, c->qmod[l].dev, ptrs(d0, d1, d2), W, 3, st, 0, 0, pre)) return 1;
   // he_relin (he-mult.c:143); he_rs in the same epilogue kernel when it can be fused
   if (keyswitch_dev(c, l, d2, rlk, d0, d1, c0, c1, st, rs_j)) return 1;
   if (rescale && !rs_j) return rescale_dev(c, l, c0, c1, true, stream, 0);
@@ -923,12 +1012,17 @@ static int he_mulpt_impl(gq_ctx *c, unsigned l, unsigned dim, uint64_t *c0, uint
   if (ensure_slot(c, GQ_SLOT_LIMB_A, (size_t)4 * c->dimub * n * 8) ||
       ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8)) return 1;
   uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
+  const bool pre = crt_pre_ok(c, dim, c->qmod[l].dev);
   if (decompose_dev(c, 0, dim, ptrs(a0, a1, m), W, 3, A, st)) return 1;
   if (ntt_internal(c, 0, dim, 3, A, false, st)) return 1;
-  gq_launch_mul_pt(c->d_primes, (int)n, (int)dim, B, A, st, pm_ok(c, 0, dim));
-  c->launches++;
-  if (ntt_internal(c, 0, dim, 2, B, true, st)) return 1;
-  if (reconstruct_dev(c, dim, B, c->qmod[l].dev, ptrs(c0, c1), W, 2, st, 0, rs_j)) return 1;
+  if (fused_inv_ok(c, 0, dim)) {
+    if (ntt_inv_fused(c, GQ_NTTF_PT, 0, dim, A, B, nullptr, nullptr, 1, st, pre ? dim : 0)) return 1;
+  } else {
+    gq_launch_mul_pt(c->d_primes, (int)n, (int)dim, B, A, st, pm_ok(c, 0, dim));
+    c->launches++;
+    if (ntt_internal(c, 0, dim, 2, B, true, st, 0, pre ? dim : 0)) return 1;
+  }
+  if (reconstruct_dev(c, dim, B, c->qmod[l].dev, ptrs(c0, c1), W, 2, st, 0, rs_j, pre)) return 1;
   if (rescale && !rs_j) return rescale_dev(c, l, c0, c1, true, stream, 0);
   return 0;
 }
@@ -1044,14 +1138,21 @@ extern "C" int gq_he_rot_hoisted_dev(gq_ctx *c, unsigned l, unsigned count, cons
   uint64_t *d0 = (uint64_t *)c->slot[GQ_SLOT_BIG] + 3 * (size_t)W * n;
   if (decompose_dev(c, 0, D2, ptrs(c1), W, 1, A, st)) return 1;
   if (ntt_internal(c, 0, D2, 1, A, false, st)) return 1;
+  const bool pre = crt_pre_ok(c, D2, c->qmod[l].dev) && c->basis[D2 - 1].ratio && D2 >= c->dim;
+  const bool fused = fused_inv_ok(c, 0, D2);
   for (unsigned k = 0; k < count; k++) {
     const uint64_t g = galois_rot(c, rots[k]);
-    gq_launch_mul_evk_perm(c->d_primes, (int)n, (int)c->logn, (int)D2, B, A, rk[k]->p0, rk[k]->p1, g, st,
-                           pm_ok(c, 0, D2));
     gq_launch_automorph((int)n, (int)W, ptrs(d0), ptrs(c0), 1, g, st);
-    c->launches += 2;
-    if (ntt_internal(c, 0, D2, 2, B, true, st)) return 1;
-    if (ks_epilogue_dev(c, l, D2, B, d0, nullptr, c0_out[k], c1_out[k], 0, st)) return 1;
+    c->launches++;
+    if (fused) {
+      if (ntt_inv_fused(c, GQ_NTTF_EVKPERM, 0, D2, A, B, rk[k]->p0, rk[k]->p1, g, st, pre ? D2 : 0)) return 1;
+    } else {
+      gq_launch_mul_evk_perm(c->d_primes, (int)n, (int)c->logn, (int)D2, B, A, rk[k]->p0, rk[k]->p1, g, st,
+                             pm_ok(c, 0, D2));
+      c->launches++;
+      if (ntt_internal(c, 0, D2, 2, B, true, st, 0, pre ? D2 : 0)) return 1;
+    }
+    if (ks_epilogue_dev(c, l, D2, B, d0, nullptr, c0_out[k], c1_out[k], 0, st, 0, pre)) return 1;
   }
   return 0;
 }

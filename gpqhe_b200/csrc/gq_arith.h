@@ -140,3 +140,15 @@ GQ_HD uint64_t gq_reduce_pm(GqWide z, uint64_t p, uint32_t c, int s) {
   r = ((int64_t)r < 0) ? r + p : r;
   return (r >= p) ? r - p : r;
 }
+
+// per-prime constants of the pseudo-Mersenne products (p = 2^s + c) and the products of two variables the
+// internal pointwise stages use (gq_pointwise.cu, and the loaders of the fused inverse NTT in gq_ntt_lazy.cu)
+struct GqPM { uint64_t p; uint32_t c; int s; };
+GQ_HD GqPM gq_load_pm(const GqPrime &P) {
+  GqPM m; m.p = P.p; m.s = (int)P.bits - 1; m.c = (uint32_t)(P.p - (((uint64_t)1) << m.s)); return m;
+}
+GQ_HD uint64_t gq_mulm_pm(uint64_t a, uint64_t b, const GqPM &m) { return gq_reduce_pm(gq_mul_wide(a, b), m.p, m.c, m.s); }
+// a*b + c2*d mod p (the cross term of the tensor product, one reduction for both products)
+GQ_HD uint64_t gq_mul2add_pm(uint64_t a, uint64_t b, uint64_t c2, uint64_t d, const GqPM &m) {
+  return gq_reduce_pm(gq_add_wide(gq_mul_wide(a, b), gq_mul_wide(c2, d)), m.p, m.c, m.s);
+}

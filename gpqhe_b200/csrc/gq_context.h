@@ -11,6 +11,12 @@ struct GqHostBasis {
   GqCrtBasis dev;   // device pointers
   BigU P;
   void *blob = nullptr;
+  std::vector<uint64_t> inv;          // host copy of (P/p_d)^-1 mod p_d
+  // final-scale tables of the lazy inverse NTT with (P/p_d)^-1 folded in (built on first use, gq_api.cu)
+  ulonglong2 *fin_s = nullptr, *fin_w = nullptr;
+  // key switch over this basis: (P_dim/p_d)^-1 * ((P/p_d)^-1)^-1 mod p_d for d < dim, Shoup pairs; turns the
+  // prescaled residues of this basis into those of the special-modulus basis (r = T mod P_dim)
+  ulonglong2 *ratio = nullptr;
 };
 
 struct GqHostModulus {
@@ -36,6 +42,8 @@ struct gq_ctx {
   // device tables
   GqPrime *d_primes = nullptr;
   ulonglong2 *d_tw_fwd = nullptr, *d_tw_inv = nullptr, *d_tw_inv_last = nullptr;
+  ulonglong2 *d_fin_s = nullptr;     // {N^-1, Shoup companion} per prime: the plain final scale of the lazy inverse NTT
+  std::vector<uint64_t> h_inv1;      // zetas_inv[1] per prime (plain residue), for the folded final-scale tables
   uint64_t *d_pow64 = nullptr, *d_t1sh = nullptr, *d_pow32 = nullptr, *d_onesh = nullptr, *d_pow28 = nullptr;
   uint64_t *d_Pinv = nullptr;        // P^-1 mod 2^(64*GQ_MAX_W)
   uint64_t *d_Pwords = nullptr;      // P and floor(P/2), GQ_MAX_W words each (general path)
@@ -59,10 +67,14 @@ struct gq_ctx {
   std::vector<cudaEvent_t> ev_batch;
   bool lazy_ntt = true;          // internal pipelines use gq_ntt_lazy.cu when every prime allows it
 
-  GqNttTables ntt_tables() const {
+  // D > 0: inverse transforms end with the CRT pre-multiplication of the basis {p_0..p_(D-1)} folded into N^-1
+  // (the tables must have been built: gq_api.cu crt_prescale)
+  GqNttTables ntt_tables(unsigned D = 0) const {
     GqNttTables t;
     t.logn = (int)logn; t.n = (int)n; t.primes = d_primes;
     t.tw_fwd = d_tw_fwd; t.tw_inv = d_tw_inv; t.tw_inv_last = d_tw_inv_last;
+    t.fin_s = D ? basis[D - 1].fin_s : d_fin_s;
+    t.fin_w = D ? basis[D - 1].fin_w : d_tw_inv_last;
     return t;
   }
   GqDecTables dec_tables() const {

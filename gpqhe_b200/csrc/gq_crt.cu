@@ -36,24 +36,29 @@ struct CrtShared {
   uint64_t p[MaxD<WT>::v];
 };
 
+// inv_over != null: Shoup pairs that replace (P/p_d)^-1 - the residues then arrive pre-multiplied for ANOTHER
+// basis and the pair converts between the two (GqHostBasis::ratio)
 template <int WT>
-GQ_DEV void crt_stage(CrtShared<WT> &S, const GqCrtBasis &B, const GqPrime *primes) {
+GQ_DEV void crt_stage(CrtShared<WT> &S, const GqCrtBasis &B, const GqPrime *primes,
+                      const ulonglong2 *inv_over = nullptr) {
   for (int j = threadIdx.x; j < B.D * WT; j += blockDim.x) S.phat[j] = B.phat[j];
   for (int j = threadIdx.x; j <= WT; j += blockDim.x) {
     S.P[j] = (j < WT) ? B.P[j] : 0;
     S.Ph[j] = (j < WT) ? B.Ph[j] : 0;
   }
   for (int j = threadIdx.x; j < B.D; j += blockDim.x) {
-    S.inv[j] = B.inv[j];
-    S.inv_sh[j] = B.inv_sh[j];
+    S.inv[j] = inv_over ? inv_over[j].x : B.inv[j];
+    S.inv_sh[j] = inv_over ? inv_over[j].y : B.inv_sh[j];
     S.p[j] = primes[j].p;
   }
 }
 
 // acc[0..WT) <- (sum_d rhat[d][i] * C_d) mod P, in [0,P)
+// pre: the residues are already y_d = a_d * (P/p_d)^-1 mod p_d (the inverse NTT folded that constant into its
+// final N^-1 scaling, GqNttTables::fin_s), so the first multiplication of rns_reconstruct is skipped
 template <int WT>
 GQ_DEV void crt_mod_P(uint64_t *acc, const CrtShared<WT> &S, const GqCrtBasis &B,
-                      const uint64_t *__restrict__ rhat, int n, int i) {
+                      const uint64_t *__restrict__ rhat, int n, int i, bool pre = false) {
 #pragma unroll
   for (int w = 0; w <= WT; w++) acc[w] = 0;
   uint64_t a0 = rhat[i], a1 = (B.D > 1) ? rhat[(size_t)n + i] : 0;
@@ -61,7 +66,7 @@ GQ_DEV void crt_mod_P(uint64_t *acc, const CrtShared<WT> &S, const GqCrtBasis &B
     const uint64_t a = a0;
     a0 = a1;
     a1 = (d + 2 < B.D) ? rhat[(size_t)(d + 2) * n + i] : 0;
-    uint64_t y = gq_mul_shoup(a, S.inv[d], S.inv_sh[d], S.p[d]);
+    uint64_t y = pre ? a : gq_mul_shoup(a, S.inv[d], S.inv_sh[d], S.p[d]);
     mw_mac<WT>(acc, y, &S.phat[d * WT]);
   }
   if (B.sh >= 0) {
@@ -130,9 +135,9 @@ GQ_DEV void store_words(uint64_t *__restrict__ out, int n, int i, int Wout, cons
 template <int WT, bool POW2>
 GQ_DEV void reconstruct_one(const CrtShared<WT> &S, const GqCrtBasis &B, int n,
                             const uint64_t *__restrict__ rhat, const GqModulus &q, const GqPtrs4 &out,
-                            int Wout, int b, int i, unsigned rs_j) {
+                            int Wout, int b, int i, unsigned rs_j, bool pre) {
   uint64_t acc[WT + 1];
-  crt_mod_P<WT>(acc, S, B, rhat + (size_t)b * B.D * n, n, i);
+  crt_mod_P<WT>(acc, S, B, rhat + (size_t)b * B.D * n, n, i, pre);
   crt_centre<WT>(acc, S);
   if (POW2) {
     if (rs_j) mw_rdiv_pow2<WT>(acc, rs_j);
@@ -150,7 +155,7 @@ template <int WT, bool POW2>
 __global__ void __launch_bounds__(128)
 k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
               const uint64_t *__restrict__ rhat, GqModulus q, GqPtrs4 out, int Wout,
-              int *fix_count, const int *__restrict__ fix_list, unsigned rs_j) {
+              int *fix_count, const int *__restrict__ fix_list, unsigned rs_j, bool pre) {
   __shared__ CrtShared<WT> S;
   if (fix_list) {
     const int cnt = *fix_count;
@@ -158,7 +163,7 @@ k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
     crt_stage<WT>(S, B, primes);
     __syncthreads();
     for (int e = threadIdx.x; e < cnt; e += blockDim.x)
-      reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, fix_list[e] / n, fix_list[e] % n, rs_j);
+      reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, fix_list[e] / n, fix_list[e] % n, rs_j, pre);
     __syncthreads();
     if (threadIdx.x == 0) *fix_count = 0;
     return;
@@ -167,7 +172,7 @@ k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, blockIdx.y, i, rs_j);
+  reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, blockIdx.y, i, rs_j, pre);
 }
 
 // ---- K6 (power-of-two q_l fast path) ------------------------------------------------
@@ -177,10 +182,10 @@ template <int WT, int WP>
 GQ_DEV void ks_one(const CrtShared<WT> &S, const CrtShared<WP> &SP, const uint64_t *sPinv,
                    const GqCrtBasis &B, const GqCrtBasis &BP, int n, const uint64_t *__restrict__ chat,
                    unsigned k, const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int b, int i,
-                   unsigned rs_j) {
+                   unsigned rs_j, bool pre) {
   const uint64_t *ch = chat + (size_t)b * B.D * n;
   uint64_t T[WT + 1];
-  crt_mod_P<WT>(T, S, B, ch, n, i);
+  crt_mod_P<WT>(T, S, B, ch, n, i, pre);
   crt_centre<WT>(T, S);
   uint64_t r[WP + 1];
   crt_mod_P<WP>(r, SP, BP, ch, n, i);            // r = T mod P in [0,P)
@@ -242,26 +247,27 @@ __global__ void __launch_bounds__(128)
 k_ks_epilogue(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
               const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
               unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout,
-              int *fix_count, const int *__restrict__ fix_list, unsigned rs_j) {
+              int *fix_count, const int *__restrict__ fix_list, unsigned rs_j, const ulonglong2 *ratio) {
   __shared__ CrtShared<WT> S;
   __shared__ CrtShared<WP> SP;
   __shared__ uint64_t sPinv[WP];
   if (fix_list && *fix_count == 0) return;
+  const bool pre = ratio != nullptr;
   crt_stage<WT>(S, B, primes);
-  crt_stage<WP>(SP, BP, primes);
+  crt_stage<WP>(SP, BP, primes, ratio);
   for (int j = threadIdx.x; j < WP; j += blockDim.x) sPinv[j] = Pinv[j];
   __syncthreads();
   if (fix_list) {   // one block: the coefficients the fast kernel left undecided
     const int cnt = *fix_count;
     for (int e = threadIdx.x; e < cnt; e += blockDim.x)
-      ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, fix_list[e] / n, fix_list[e] % n, rs_j);
+      ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, fix_list[e] / n, fix_list[e] % n, rs_j, pre);
     __syncthreads();
     if (threadIdx.x == 0) *fix_count = 0;
     return;
   }
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, blockIdx.y, i, rs_j);
+  ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, blockIdx.y, i, rs_j, pre);
 }
 
 // ---- K6, general modulus: exact long division by P (slow path) -----------------------
@@ -364,7 +370,7 @@ GQ_DEV void crt_low_stage(CrtSharedLow<W> &S, const GqCrtBasis &B, const GqPrime
 }
 
 // acc[0..W) = low words of the centred CRT value; false if M could not be decided
-template <int W>
+template <int W, bool PRE>
 GQ_DEV bool crt_low(uint64_t *acc, const CrtSharedLow<W> &S, int D, int fs,
                     const uint64_t *__restrict__ rhat, int n, int i) {
 #pragma unroll
@@ -376,7 +382,7 @@ GQ_DEV bool crt_low(uint64_t *acc, const CrtSharedLow<W> &S, int D, int fs,
     const uint64_t a = a0;
     a0 = a1;
     a1 = (d + 2 < D) ? rhat[(size_t)(d + 2) * n + i] : 0;
-    const uint64_t y = gq_mul_shoup(a, S.inv[d], S.inv_sh[d], S.p[d]);
+    const uint64_t y = PRE ? a : gq_mul_shoup(a, S.inv[d], S.inv_sh[d], S.p[d]);
     mw_mac_low<W>(acc, y, &S.phat[d * W]);
     // est += y * floor(2^F / p_d)   (one 64x64 product, 192-bit accumulator)
     const uint64_t h0 = gq_mulhi(y, S.u0[d]), l0 = y * S.u0[d];
@@ -417,7 +423,7 @@ GQ_DEV void fix_push(int *fix_count, int *fix_list, int entry) {
 #endif
 }
 
-template <int W>
+template <int W, bool PRE>
 __global__ void __launch_bounds__(256)
 k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
                    const uint64_t *__restrict__ rhat, unsigned k, GqPtrs4 out, int Wout,
@@ -429,7 +435,7 @@ k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
   if (i >= n) return;
   const int b = blockIdx.y;
   uint64_t acc[W];
-  if (!crt_low<W>(acc, S, B.D, B.F - 64, rhat + (size_t)b * B.D * n, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
+  if (!crt_low<W, PRE>(acc, S, B.D, B.F - 64, rhat + (size_t)b * B.D * n, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
   if (rs_j) mw_rdiv_pow2<W>(acc, rs_j);         // he_rs fused (see reconstruct_one)
   mw_smod_pow2<W>(acc, k - rs_j);
   store_words<W>(ptr4(out, b), n, i, Wout, acc);
@@ -440,17 +446,17 @@ k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
 // WQ <= WP: the result is only needed modulo q = 2^k, k < 64*WQ, so T, T - r and the quotient are carried in
 // WQ words (WQ = the context's words per coefficient; 7 against WP = 8 at logq = 438); only r = T mod P needs
 // the full width of P.
-template <int WP, int WQ>
+template <int WP, int WQ, bool PRE>
 __global__ void __launch_bounds__(128)
 k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
                    const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
                    unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout, int *fix_count, int *fix_list,
-                   unsigned rs_j) {
+                   unsigned rs_j, const ulonglong2 *ratio) {
   __shared__ CrtSharedLow<WQ> S;
   __shared__ CrtShared<WP> SP;
   __shared__ uint64_t sPinv[WQ];
   crt_low_stage<WQ>(S, B, primes);
-  crt_stage<WP>(SP, BP, primes);
+  crt_stage<WP>(SP, BP, primes, PRE ? ratio : nullptr);
   for (int j = threadIdx.x; j < WQ; j += blockDim.x) sPinv[j] = Pinv[j];
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -458,7 +464,7 @@ k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pin
   const int b = blockIdx.y;
   const uint64_t *ch = chat + (size_t)b * B.D * n;
   uint64_t x[WQ];
-  if (!crt_low<WQ>(x, S, B.D, B.F - 64, ch, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
+  if (!crt_low<WQ, PRE>(x, S, B.D, B.F - 64, ch, n, i)) { fix_push(fix_count, fix_list, b * n + i); return; }
   bool round_up;
   {
     uint64_t r[WP + 1];
@@ -699,7 +705,7 @@ k_decompose(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *
 // by the exact kernel in list mode (power-of-two q only).  Returns kernels launched.
 int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix, unsigned rs_j) {
+                          cudaStream_t st, int *fix, unsigned rs_j, bool pre) {
   if (rs_j && (!q.is_pow2 || rs_j > q.k)) return -1;
   dim3 grid((n + 127) / 128, npolys), block(128);
   int *fc = nullptr, *fl = nullptr;
@@ -708,26 +714,29 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
     fc = fix; fl = fix + 4;
     const int W = (int)((q.k + 63) / 64);
     dim3 g2((n + 255) / 256, npolys), b2(256);
-#define GQ_RF(V) GQ_LAUNCH(k_reconstruct_fast<V>, g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j)
+#define GQ_RF(V) do { if (pre) GQ_LAUNCH((k_reconstruct_fast<V, true>), g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j); \
+                      else GQ_LAUNCH((k_reconstruct_fast<V, false>), g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j); } while (0)
     if (W <= 1) GQ_RF(1); else if (W <= 2) GQ_RF(2); else if (W <= 3) GQ_RF(3); else if (W <= 4) GQ_RF(4);
     else if (W <= 5) GQ_RF(5); else if (W <= 6) GQ_RF(6); else if (W <= 7) GQ_RF(7); else if (W <= 8) GQ_RF(8);
     else if (W <= 12) GQ_RF(12); else if (W <= 16) GQ_RF(16); else if (W <= 24) GQ_RF(24); else GQ_RF(32);
 #undef GQ_RF
     grid = dim3(1, 1);
     launches = 2;
+  } else if (pre) {
+    return -1;        // pre-scaled residues are only produced for the fast path
   }
   if (q.is_pow2) {
     GQ_WT_SWITCH(B.WT,
-      GQ_LAUNCH((k_reconstruct<8, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
-      GQ_LAUNCH((k_reconstruct<16, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
-      GQ_LAUNCH((k_reconstruct<24, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
-      GQ_LAUNCH((k_reconstruct<32, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j))
+      GQ_LAUNCH((k_reconstruct<8, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
+      GQ_LAUNCH((k_reconstruct<16, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
+      GQ_LAUNCH((k_reconstruct<24, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
+      GQ_LAUNCH((k_reconstruct<32, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre))
   } else {
     GQ_WT_SWITCH(B.WT,
-      GQ_LAUNCH((k_reconstruct<8, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
-      GQ_LAUNCH((k_reconstruct<16, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
-      GQ_LAUNCH((k_reconstruct<24, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j),
-      GQ_LAUNCH((k_reconstruct<32, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j))
+      GQ_LAUNCH((k_reconstruct<8, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
+      GQ_LAUNCH((k_reconstruct<16, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
+      GQ_LAUNCH((k_reconstruct<24, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
+      GQ_LAUNCH((k_reconstruct<32, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre))
   }
   return launches;
 }
@@ -736,10 +745,10 @@ template <int WT>
 static int ks_dispatch_wp(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, dim3 grid,
-                          cudaStream_t st, int *fc, int *fl, unsigned rs_j) {
+                          cudaStream_t st, int *fc, int *fl, unsigned rs_j, const ulonglong2 *ratio) {
   dim3 block(128);
   if (BP.WT > WT) return -1;
-#define GQ_KS(WPV) GQ_LAUNCH((k_ks_epilogue<WT, (WT >= WPV ? WPV : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j)
+#define GQ_KS(WPV) GQ_LAUNCH((k_ks_epilogue<WT, (WT >= WPV ? WPV : 8)>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j, ratio)
   switch (BP.WT) {
     case 8: GQ_KS(8); return 1;
     case 16: if (WT >= 16) { GQ_KS(16); return 1; } return -1;
@@ -753,7 +762,7 @@ static int ks_dispatch_wp(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
 int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix, unsigned rs_j) {
+                          cudaStream_t st, int *fix, unsigned rs_j, const ulonglong2 *ratio) {
   if (rs_j > k) return -1;
   dim3 grid((n + 127) / 128, npolys);
   int *fc = nullptr, *fl = nullptr;
@@ -762,25 +771,30 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
     fc = fix; fl = fix + 4;
     dim3 block(128);
     switch (BP.WT) {
-#define GQ_KF(V) case V: GQ_LAUNCH((k_ks_epilogue_fast<V, V>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j); break;
+#define GQ_KFL(WPV, WQV) do { if (ratio) GQ_LAUNCH((k_ks_epilogue_fast<WPV, WQV, true>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j, ratio); \
+                              else GQ_LAUNCH((k_ks_epilogue_fast<WPV, WQV, false>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j, ratio); } while (0)
+#define GQ_KF(V) case V: GQ_KFL(V, V); break;
       case 8:     // the shipped parameter sets (logq = 438: 7 words per coefficient, P of 8 words) and their neighbours
-        if (Wout == 7 && Wadd <= 7 && k < 64u * 7) GQ_LAUNCH((k_ks_epilogue_fast<8, 7>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j);
-        else if (Wout == 6 && Wadd <= 6 && k < 64u * 6) GQ_LAUNCH((k_ks_epilogue_fast<8, 6>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j);
-        else GQ_LAUNCH((k_ks_epilogue_fast<8, 8>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j);
+        if (Wout == 7 && Wadd <= 7 && k < 64u * 7) GQ_KFL(8, 7);
+        else if (Wout == 6 && Wadd <= 6 && k < 64u * 6) GQ_KFL(8, 6);
+        else GQ_KFL(8, 8);
         break;
       GQ_KF(16) GQ_KF(24) GQ_KF(32)
 #undef GQ_KF
+#undef GQ_KFL
       default: return -1;
     }
     grid = dim3(1, 1);
     launches = 2;
+  } else if (ratio) {
+    return -1;        // pre-scaled residues are only produced for the fast path
   }
   int r = -1;
   switch (B.WT) {
-    case 8: r = ks_dispatch_wp<8>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j); break;
-    case 16: r = ks_dispatch_wp<16>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j); break;
-    case 24: r = ks_dispatch_wp<24>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j); break;
-    case 32: r = ks_dispatch_wp<32>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j); break;
+    case 8: r = ks_dispatch_wp<8>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j, ratio); break;
+    case 16: r = ks_dispatch_wp<16>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j, ratio); break;
+    case 24: r = ks_dispatch_wp<24>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j, ratio); break;
+    case 32: r = ks_dispatch_wp<32>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j, ratio); break;
   }
   return r < 0 ? r : launches;
 }

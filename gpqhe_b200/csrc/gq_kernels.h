@@ -13,6 +13,13 @@ int gq_launch_ntt(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, 
 int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
                        bool inverse, cudaStream_t st, int only = 0);
 
+// pointwise stage fused into the load of the lazy inverse transform (gq_ntt_lazy.cu): x -> y = invntt(product)
+//   TENSOR x[4][D][n] -> y[3][D][n];  EVK / EVKPERM x[D][n], e0, e1 -> y[2][D][n];  PT x[3][D][n] -> y[2][D][n];
+//   MUL x[2][D][n] -> y[D][n]
+enum { GQ_NTTF_TENSOR = 1, GQ_NTTF_EVK = 2, GQ_NTTF_EVKPERM = 3, GQ_NTTF_PT = 4, GQ_NTTF_MUL = 5 };
+int gq_launch_ntt_lazy_fused(const GqNttTables &tb, int mode, const uint64_t *x, uint64_t *y, const uint64_t *e0,
+                             const uint64_t *e1, unsigned g, int limb0, int nlimbs, cudaStream_t st);
+
 // K3 (gq_pointwise.cu)
 void gq_launch_binary(const GqPrime *primes, int n, int limb0, int nlimbs, int npolys, bool mul,
                       uint64_t *r, const uint64_t *a, const uint64_t *b, cudaStream_t st);
@@ -29,17 +36,19 @@ void gq_launch_mul_pt(const GqPrime *primes, int n, int D, uint64_t *y, const ui
 
 // K4/K5/K6 (gq_crt.cu); return the number of kernels launched, <0 when no instantiation fits.
 // fix = device scratch {int count (16-byte slot), int list[4n]}: enables the fast low-word kernels
+// pre / ratio: the residues come pre-multiplied by (P/p_d)^-1 from the lazy inverse NTT (GqNttTables::fin_s); for the
+// key switch `ratio` converts them to the special-modulus basis (GqHostBasis::ratio).  Fast path only.
 // rs_j > 0 (power-of-two q and Delta only): he_rs fused behind the CRT, the output is rdiv(., 2^rs_j) smod 2^(k-rs_j)
 // digits: 32-bit digit kernel (every prime of the range needs >= 33 and <= 60 bits)
 int gq_launch_decompose(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
                         int W, uint64_t *out, int npolys, cudaStream_t st, int digits = false);
 int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0);
+                          cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0, bool pre = false);
 int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0);
+                          cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0, const ulonglong2 *ratio = nullptr);
 // general-modulus key-switch epilogue (exact long division, slow path)
 int gq_launch_ks_epilogue_general(const GqCrtBasis &B, const uint64_t *P, int nP,
                                   const uint64_t *Ph, const GqPrime *primes, int n,

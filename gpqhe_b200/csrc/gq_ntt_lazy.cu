@@ -148,7 +148,8 @@ GQ_DEV void inv_round8_lz(uint64_t *v, int lo, int kq, const ulonglong2 *__restr
 
 template <int NB, bool LAST>
 GQ_DEV void inv_round(uint64_t *v, int lo, int kq, const ulonglong2 *__restrict__ tw, const PC &c,
-                      ulonglong2 wlast, uint64_t ninv, uint64_t ninv_sh) {
+                      ulonglong2 wlast, ulonglong2 fs) {
+  const uint64_t ninv = fs.x, ninv_sh = fs.y;
   if (NB == 3 && !LAST) { inv_round8_lz(v, lo, kq, tw, c); return; }
   if (NB >= 3) {
     const int kb = kq >> (lo + 1);
@@ -241,25 +242,70 @@ k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
 }
 
 // ---- inverse tile kernel: the first LOGT stages; WHOLE: also the final one ------------
-template <int LOGT, bool WHOLE>
+// MODE selects what the kernel transforms (the pointwise stage of every pipeline sits exactly between a forward
+// transform that ends on these tiles and this kernel, so it is done while the tile is loaded; K3 as separate
+// launches is gone from he_mul / he_rot / he_mulpt / poly_mul):
+//   GQ_INV_PLAIN   y[m] in place (x == y)
+//   GQ_INV_TENSOR  x[4][D][n] = NTT(a0, a1, b0, b1) -> y[3][D][n] = a0*b0, a0*b1 + a1*b0, a1*b1  (he-mult.c:125-136)
+//   GQ_INV_EVK     x[D][n], key halves e0, e1 [D][n] -> y[2][D][n] = x*e0, x*e1                   (he-mult.c:61-64)
+//   GQ_INV_EVKPERM the same with x read through the slot permutation of the Galois map g (hoisted rotations)
+//   GQ_INV_PT      x[3][D][n] = NTT(c0, c1, m) -> y[2][D][n] = c0*m, c1*m                          (he-mult.c:186-189)
+//   GQ_INV_MUL     x[2][D][n] = NTT(a, b) -> y[1][D][n] = a*b                                       (poly.c:96-101)
+// Products are the pseudo-Mersenne ones of gq_arith.h (canonical, the residue poly_rns_mul stores); the host
+// selects these modes only when every prime of the range has that shape (pm_ok), else the separate kernels run.
+enum { GQ_INV_PLAIN = 0, GQ_INV_TENSOR, GQ_INV_EVK, GQ_INV_EVKPERM, GQ_INV_PT, GQ_INV_MUL };
+
+struct InvSrc {
+  const uint64_t *x;        // inputs (limb-major batches as above)
+  const uint64_t *e0, *e1;  // key halves, already offset to the first limb of the range
+  unsigned g;               // Galois element (GQ_INV_EVKPERM)
+};
+
+template <int MODE>
+GQ_DEV uint64_t inv_load(const InvSrc &S, const GqPM &pm, int n, int logn, int nlimbs, int b, int dd, int j) {
+  const size_t lp = (size_t)dd * n + j, stride = (size_t)nlimbs * n;
+  if (MODE == GQ_INV_TENSOR) {
+    if (b == 0) return gq_mulm_pm(S.x[lp], S.x[2 * stride + lp], pm);
+    if (b == 2) return gq_mulm_pm(S.x[stride + lp], S.x[3 * stride + lp], pm);
+    return gq_mul2add_pm(S.x[lp], S.x[3 * stride + lp], S.x[stride + lp], S.x[2 * stride + lp], pm);
+  }
+  if (MODE == GQ_INV_EVK) return gq_mulm_pm(S.x[lp], (b ? S.e1 : S.e0)[lp], pm);
+  if (MODE == GQ_INV_EVKPERM) {
+    // slot j of ntt()'s output holds the value at psi^(2*brv(j)+1); sigma_g moves it to the slot of exponent e*g
+    const unsigned e = ((2u * (__brev((unsigned)j) >> (32 - logn)) + 1u) * S.g) & (2u * (unsigned)n - 1u);
+    const unsigned src = __brev((e - 1u) >> 1) >> (32 - logn);
+    return gq_mulm_pm(S.x[(size_t)dd * n + src], (b ? S.e1 : S.e0)[lp], pm);
+  }
+  if (MODE == GQ_INV_PT) return gq_mulm_pm(S.x[(size_t)b * stride + lp], S.x[2 * stride + lp], pm);
+  if (MODE == GQ_INV_MUL) return gq_mulm_pm(S.x[lp], S.x[stride + lp], pm);
+  return S.x[(size_t)b * stride + lp];
+}
+
+template <int LOGT, bool WHOLE, int MODE>
 __global__ void __launch_bounds__(TileCfg<LOGT>::NT, (TileCfg<LOGT>::NT >= 512 ? 2 : 1))
-k_nttl_inv_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+k_nttl_inv_tile(GqNttTables tb, InvSrc src, uint64_t *__restrict__ y, int limb0, int nlimbs) {
   typedef TileCfg<LOGT> C;
   __shared__ uint64_t sm[C::T];
   const int t = threadIdx.x;
   const int st = swz(t);
   const int m = blockIdx.y;
-  const int d = limb0 + m % nlimbs;
+  const int dd = m % nlimbs, b = m / nlimbs;
+  const int d = limb0 + dd;
   const GqPrime pr = tb.primes[d];
   const PC c = load_pc(pr);
   const ulonglong2 *tw = tb.tw_inv + (size_t)d * tb.n;
-  const ulonglong2 wlast = tb.tw_inv_last[d];
-  uint64_t *a = data + (size_t)m * tb.n + (size_t)blockIdx.x * C::T;
-  const int jbase = tb.n + blockIdx.x * C::T;
+  const int tile0 = blockIdx.x * C::T;
+  uint64_t *a = y + (size_t)m * tb.n + tile0;
+  const int jbase = tb.n + tile0;
   uint64_t v[8];
+  {
+    const GqPM pm = gq_load_pm(pr);
+#pragma unroll
+    for (int e = 0; e < 8; e++) v[e] = inv_load<MODE>(src, pm, tb.n, tb.logn, nlimbs, b, dd, tile0 + e * C::NT + t);
+  }
   if (C::NFULL > 0) {
 #pragma unroll
-    for (int e = 0; e < 8; e++) sm[st ^ swz(e * C::NT)] = a[e * C::NT + t];
+    for (int e = 0; e < 8; e++) sm[st ^ swz(e * C::NT)] = v[e];
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < C::NFULL; r++) {
@@ -267,18 +313,15 @@ k_nttl_inv_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
       const int base = idx8(t, lo), sb = swz(base);
 #pragma unroll
       for (int e = 0; e < 8; e++) v[e] = sm[sb ^ swz(e << lo)];
-      inv_round<3, false>(v, lo, jbase + base, tw, c, wlast, pr.ninv, pr.ninv_sh);
+      inv_round<3, false>(v, lo, jbase + base, tw, c, make_ulonglong2(0, 0), make_ulonglong2(0, 0));
 #pragma unroll
       for (int e = 0; e < 8; e++) sm[sb ^ swz(e << lo)] = v[e];
       __syncthreads();
     }
 #pragma unroll
     for (int e = 0; e < 8; e++) v[e] = sm[st ^ swz(e * C::NT)];
-  } else {
-#pragma unroll
-    for (int e = 0; e < 8; e++) v[e] = a[e * C::NT + t];
   }
-  inv_round<C::NB0, WHOLE>(v, LOGT - 3, jbase + t, tw, c, wlast, pr.ninv, pr.ninv_sh);
+  inv_round<C::NB0, WHOLE>(v, LOGT - 3, jbase + t, tw, c, tb.fin_w[d], tb.fin_s[d]);
 #pragma unroll
   for (int e = 0; e < 8; e++) a[e * C::NT + t] = v[e];
 }
@@ -338,7 +381,7 @@ k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
   const GqPrime pr = tb.primes[d];
   const PC c = load_pc(pr);
   const ulonglong2 *tw = stw;
-  const ulonglong2 wlast = tb.tw_inv_last[d];
+  const ulonglong2 wlast = tb.fin_w[d], fs = tb.fin_s[d];
   uint64_t *a = data + (size_t)m * tb.n + col;
   uint64_t v[R];
 #pragma unroll
@@ -370,7 +413,7 @@ k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
     const int q = r + R / 2;
     if (bnd[r] >= 16) { v[r] = csub(v[r], c.p8); v[q] = csub(v[q], c.p8); bnd[r] = 8; }
     const uint64_t s = v[r] + v[q], dd = v[r] - v[q] + pmul(c, bnd[r]);
-    v[r] = csub(mul_lazy(s, pr.ninv, pr.ninv_sh, c.p), c.p);
+    v[r] = csub(mul_lazy(s, fs.x, fs.y, c.p), c.p);
     v[q] = csub(mul_lazy(dd, wlast.x, wlast.y, c.p), c.p);
   }
 #pragma unroll
@@ -378,6 +421,33 @@ k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
 }
 
 }  // namespace
+
+template <int MODE>
+static int launch_inv(const GqNttTables &tb, const InvSrc &src, uint64_t *y, int limb0, int nlimbs, int npolys,
+                      cudaStream_t st, int only) {
+  const int logn = tb.logn;
+  const int lt = logn > 12 ? 12 : logn, sa = logn - lt;
+  const dim3 gt(tb.n >> lt, nlimbs * npolys), gs(((tb.n >> (sa ? sa : 1)) + 255) / 256, nlimbs * npolys);
+  if (sa) {
+    if (only != 2) GQ_LAUNCH((k_nttl_inv_tile<12, false, MODE>), gt, dim3(TileCfg<12>::NT), st, tb, src, y, limb0, nlimbs);
+    if (only != 1) {
+      switch (sa) {
+        case 1: GQ_LAUNCH(k_nttl_inv_strided<1>, gs, dim3(256), st, tb, y, limb0, nlimbs); break;
+        case 2: GQ_LAUNCH(k_nttl_inv_strided<2>, gs, dim3(256), st, tb, y, limb0, nlimbs); break;
+        case 3: GQ_LAUNCH(k_nttl_inv_strided<3>, gs, dim3(256), st, tb, y, limb0, nlimbs); break;
+        case 4: GQ_LAUNCH(k_nttl_inv_strided<4>, gs, dim3(256), st, tb, y, limb0, nlimbs); break;
+        case 5: GQ_LAUNCH(k_nttl_inv_strided<5>, gs, dim3(256), st, tb, y, limb0, nlimbs); break;
+      }
+    }
+    return only ? 1 : 2;
+  }
+  switch (lt) {
+#define GQ_CASE(L) case L: GQ_LAUNCH((k_nttl_inv_tile<L, true, MODE>), gt, dim3(TileCfg<L>::NT), st, tb, src, y, limb0, nlimbs); break;
+    GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8) GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12)
+#undef GQ_CASE
+  }
+  return 1;
+}
 
 // Same contract as gq_launch_ntt, canonical in / canonical out only.
 int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
@@ -387,42 +457,47 @@ int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nli
   const int logn = tb.logn;
   if (logn < 3 || logn > 17) return -1;
   if (only && logn <= 12) return -1;
+  if (inverse) {
+    InvSrc src; src.x = data; src.e0 = src.e1 = nullptr; src.g = 1;
+    return launch_inv<GQ_INV_PLAIN>(tb, src, data, limb0, nlimbs, npolys, st, only);
+  }
   const int lt = logn > 12 ? 12 : logn, sa = logn - lt;
   const dim3 gt(tb.n >> lt, nlimbs * npolys), gs(((tb.n >> (sa ? sa : 1)) + 255) / 256, nlimbs * npolys);
-  int launches = 0;
-#define GQ_STRIDED(K) \
-  switch (sa) { \
-    case 1: GQ_LAUNCH(K<1>, gs, dim3(256), st, tb, data, limb0, nlimbs); break; \
-    case 2: GQ_LAUNCH(K<2>, gs, dim3(256), st, tb, data, limb0, nlimbs); break; \
-    case 3: GQ_LAUNCH(K<3>, gs, dim3(256), st, tb, data, limb0, nlimbs); break; \
-    case 4: GQ_LAUNCH(K<4>, gs, dim3(256), st, tb, data, limb0, nlimbs); break; \
-    case 5: GQ_LAUNCH(K<5>, gs, dim3(256), st, tb, data, limb0, nlimbs); break; \
-  }
-  if (!inverse) {
-    if (sa) {
-      if (only != 1) { GQ_STRIDED(k_nttl_fwd_strided) }
-      if (only != 2) GQ_LAUNCH((k_nttl_fwd_tile<12, true>), gt, dim3(TileCfg<12>::NT), st, tb, data, limb0, nlimbs);
-      return only ? 1 : 2;
+  if (sa) {
+    if (only != 1) {
+      switch (sa) {
+        case 1: GQ_LAUNCH(k_nttl_fwd_strided<1>, gs, dim3(256), st, tb, data, limb0, nlimbs); break;
+        case 2: GQ_LAUNCH(k_nttl_fwd_strided<2>, gs, dim3(256), st, tb, data, limb0, nlimbs); break;
+        case 3: GQ_LAUNCH(k_nttl_fwd_strided<3>, gs, dim3(256), st, tb, data, limb0, nlimbs); break;
+        case 4: GQ_LAUNCH(k_nttl_fwd_strided<4>, gs, dim3(256), st, tb, data, limb0, nlimbs); break;
+        case 5: GQ_LAUNCH(k_nttl_fwd_strided<5>, gs, dim3(256), st, tb, data, limb0, nlimbs); break;
+      }
     }
-    switch (lt) {
+    if (only != 2) GQ_LAUNCH((k_nttl_fwd_tile<12, true>), gt, dim3(TileCfg<12>::NT), st, tb, data, limb0, nlimbs);
+    return only ? 1 : 2;
+  }
+  switch (lt) {
 #define GQ_CASE(L) case L: GQ_LAUNCH((k_nttl_fwd_tile<L, false>), gt, dim3(TileCfg<L>::NT), st, tb, data, limb0, nlimbs); break;
-      GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8) GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12)
+    GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8) GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12)
 #undef GQ_CASE
-    }
-    launches = 1;
-  } else {
-    if (sa) {
-      if (only != 2) GQ_LAUNCH((k_nttl_inv_tile<12, false>), gt, dim3(TileCfg<12>::NT), st, tb, data, limb0, nlimbs);
-      if (only != 1) { GQ_STRIDED(k_nttl_inv_strided) }
-      return only ? 1 : 2;
-    }
-    switch (lt) {
-#define GQ_CASE(L) case L: GQ_LAUNCH((k_nttl_inv_tile<L, true>), gt, dim3(TileCfg<L>::NT), st, tb, data, limb0, nlimbs); break;
-      GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8) GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12)
-#undef GQ_CASE
-    }
-    launches = 1;
   }
-#undef GQ_STRIDED
-  return launches;
+  return 1;
+}
+
+// The pointwise stage + inverse transform of the internal pipelines in one pass: y[nout][nlimbs][n] from x (and
+// the key halves e0, e1 at the same limb range; g = Galois element for the permuted form).  mode = GQ_NTTF_*.
+// Every prime of the range must be pseudo-Mersenne (the caller checks pm_ok).  Returns kernels launched.
+int gq_launch_ntt_lazy_fused(const GqNttTables &tb, int mode, const uint64_t *x, uint64_t *y, const uint64_t *e0,
+                             const uint64_t *e1, unsigned g, int limb0, int nlimbs, cudaStream_t st) {
+  const int logn = tb.logn;
+  if (logn < 3 || logn > 17) return -1;
+  InvSrc src; src.x = x; src.e0 = e0; src.e1 = e1; src.g = g;
+  switch (mode) {
+    case GQ_NTTF_TENSOR: return launch_inv<GQ_INV_TENSOR>(tb, src, y, limb0, nlimbs, 3, st, 0);
+    case GQ_NTTF_EVK: return launch_inv<GQ_INV_EVK>(tb, src, y, limb0, nlimbs, 2, st, 0);
+    case GQ_NTTF_EVKPERM: return launch_inv<GQ_INV_EVKPERM>(tb, src, y, limb0, nlimbs, 2, st, 0);
+    case GQ_NTTF_PT: return launch_inv<GQ_INV_PT>(tb, src, y, limb0, nlimbs, 2, st, 0);
+    case GQ_NTTF_MUL: return launch_inv<GQ_INV_MUL>(tb, src, y, limb0, nlimbs, 1, st, 0);
+  }
+  return -1;
 }

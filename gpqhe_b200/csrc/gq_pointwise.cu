@@ -109,14 +109,10 @@ k_mul_pt(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict_
 }
 
 // ---- the same three internal kernels for primes 2^s + c, c < 2^28 (gq_reduce_pm) -------------
-struct PM { uint64_t p; uint32_t c; int s; };
-GQ_DEV PM load_pm(const GqPrime &P) {
-  PM m; m.p = P.p; m.s = (int)P.bits - 1; m.c = (uint32_t)(P.p - (((uint64_t)1) << m.s)); return m;
-}
-GQ_DEV uint64_t mulm_pm(uint64_t a, uint64_t b, const PM &m) { return gq_reduce_pm(gq_mul_wide(a, b), m.p, m.c, m.s); }
-GQ_DEV uint64_t mul2add_pm(uint64_t a, uint64_t b, uint64_t c2, uint64_t d, const PM &m) {
-  return gq_reduce_pm(gq_add_wide(gq_mul_wide(a, b), gq_mul_wide(c2, d)), m.p, m.c, m.s);
-}
+typedef GqPM PM;
+GQ_DEV PM load_pm(const GqPrime &P) { return gq_load_pm(P); }
+GQ_DEV uint64_t mulm_pm(uint64_t a, uint64_t b, const PM &m) { return gq_mulm_pm(a, b, m); }
+GQ_DEV uint64_t mul2add_pm(uint64_t a, uint64_t b, uint64_t c2, uint64_t d, const PM &m) { return gq_mul2add_pm(a, b, c2, d, m); }
 
 __global__ void __launch_bounds__(256)
 k_tensor_pm(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict__ y,

@@ -16,6 +16,12 @@ struct GqNttTables {
   const ulonglong2 *tw_fwd;     // [nprimes][n]  {w, floor(w*2^64/p)}, index as zetas[k]
   const ulonglong2 *tw_inv;     // [nprimes][n]  same for zetas_inv[k]
   const ulonglong2 *tw_inv_last;// [nprimes]     zetas_inv[1]*N^-1 mod p, folded final stage
+  // final scaling of the LAZY inverse transforms (gq_ntt_lazy.cu), Shoup pairs per prime: fin_s = s, fin_w =
+  // zetas_inv[1]*s with s = N^-1 (the plain invntt()), or s = N^-1 * (P/p_d)^-1 mod p_d when the output feeds
+  // the CRT over the basis {p_0..p_(D-1)} directly: rns_reconstruct's first multiplication (src/rns.c:68-69)
+  // then costs nothing (gq_ctx::ntt_tables(D))
+  const ulonglong2 *fin_s;      // [nprimes]
+  const ulonglong2 *fin_w;      // [nprimes]
 };
 
 // MPI -> RNS view (K4): pow64[d*GQ_DEC_W + w] = 2^(64w) mod p_d; t1_sh[d] is the Shoup

@@ -624,3 +624,49 @@ def check_fused_rescale_ties(lib_path, logn=5, q=1 << 438, Delta=1 << 50, logqub
             eq(sep.c0, got.c0, "fused == separate c0"); eq(sep.c1, got.c1, "fused == separate c1")
     finally:
         ctx.close()
+
+
+def check_fused_vs_separate(lib_path, logn, q=1 << 438, Delta=1 << 50, logqub=438, seed=77, level=None):
+    """The pointwise stage folded into the load of the inverse NTT (gq_ntt_lazy.cu, GQ_INV_*) and the CRT
+    pre-multiplication folded into its final scaling, against the separate-kernel pipeline of the same library
+    (GPQHE_B200_NO_FUSED_INV / GPQHE_B200_NO_PRESCALE, which the oracle pins at small sizes and the GPU tier at
+    full size): he_mul, he_mul+he_rs, he_mulpt, he_rot, he_conj, hoisted rotations, poly_mul - identical bits."""
+    nr = np.random.default_rng(seed)
+    res = []
+    for separate in (False, True):
+        if separate:
+            os.environ["GPQHE_B200_NO_FUSED_INV"] = "1"
+            os.environ["GPQHE_B200_NO_PRESCALE"] = "1"
+        try:
+            ctx = g.HeContext(logn, q, 4, Delta, lib_path=lib_path, logqub=logqub)
+            try:
+                n, W = ctx.n, ctx.W
+                l = ctx.L if level is None else level
+                rr = np.random.default_rng(seed)          # the same inputs for both passes
+                key = lambda: ctx.genevk(
+                    np.stack([rr.integers(0, ctx.primes[d], size=n, dtype=np.uint64) for d in range(ctx.dimevk)]),
+                    np.stack([rr.integers(0, ctx.primes[d], size=n, dtype=np.uint64) for d in range(ctx.dimevk)]))
+                k1, k2 = key(), key()
+                bits = ctx.ql[l].bit_length() - 1
+                a = g.HeCt(l, _rand_big(rr, n, W, bits), _rand_big(rr, n, W, bits), float(Delta), 1.0)
+                b = g.HeCt(l, _rand_big(rr, n, W, bits), _rand_big(rr, n, W, bits), float(Delta), 1.0)
+                pt = g.HePt(_rand_big(rr, n, W, Delta.bit_length()), nu=float(Delta))
+                out = []
+                m = ctx.he_mul(a, b, k1); out += [m.c0, m.c1]
+                m = ctx.he_mul_rs(a, b, k1); out += [m.c0, m.c1]
+                m = ctx.he_mulpt(a, pt); out += [m.c0, m.c1]
+                m = ctx.he_rot(a, 3, {3: k2}); out += [m.c0, m.c1]
+                m = ctx.he_conj(b, k2); out += [m.c0, m.c1]
+                for m in ctx.he_rot_hoisted(a, [0, 1, 5], {0: k1, 1: k2, 5: k1}):
+                    out += [m.c0, m.c1]
+                out.append(ctx.poly_mul(a.c0, b.c1, ctx.dim, ctx.ql[l]))
+                res.append(out)
+            finally:
+                ctx.close()
+        finally:
+            os.environ.pop("GPQHE_B200_NO_FUSED_INV", None)
+            os.environ.pop("GPQHE_B200_NO_PRESCALE", None)
+    assert len(res[0]) == len(res[1])
+    for k, (x, y) in enumerate(zip(res[0], res[1])):
+        eq(x, y, f"fused vs separate pipeline, output {k}")
+    del nr

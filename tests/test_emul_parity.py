@@ -159,3 +159,9 @@ def test_compositions_vs_primitives(emul_lib, logn, q, Delta, n1, n2, lanes):
 def test_fused_rescale_tie_rule(emul_lib):
     pc.check_fused_rescale_ties(emul_lib)
     pc.check_fused_rescale_ties(emul_lib, logn=4, q=1 << 120, Delta=1 << 40, logqub=120)
+
+
+@pytest.mark.parametrize("logn,level", [(13, 2), (9, None)])
+def test_fused_inverse_equals_separate_kernels(emul_lib, logn, level):
+    """two-kernel transforms (n = 2^13) and one-tile transforms: every loader mode of the fused inverse NTT"""
+    pc.check_fused_vs_separate(emul_lib, logn, level=level)

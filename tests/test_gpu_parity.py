@@ -154,3 +154,8 @@ def test_compositions_at_config_size(real_lib, logn):
 def test_fused_rescale_tie_rule(real_lib):
     pc.check_fused_rescale_ties(real_lib)
     pc.check_fused_rescale_ties(real_lib, logn=13, q=1 << 120, Delta=1 << 40, logqub=120)
+
+
+@pytest.mark.parametrize("logn", [16, 14, 12])
+def test_fused_inverse_equals_separate_kernels(real_lib, logn):
+    pc.check_fused_vs_separate(real_lib, logn)
