@@ -85,6 +85,62 @@ def synth_evk(rng, primes, n, dimevk):
 
 
 # ------------------------------------------------------------------ reference CPU path
+def cpu_reference_extras(budget_s=40.0, logn=LOGN):
+    """the other CPU figures that stand beside ours - he_rot, one-limb ntt / invntt (the "NTT limbs/s" of
+    BASELINE.json's metric) on the unmodified reference as shipped (-Og), and he_mul+he_rs / ntt on the same sources
+    built -O3 (oracle/_ref/libgpqhe_O3.so, a courtesy build).  One thread: the reference has no threading."""
+    import ctypes as C
+    import random
+
+    import numpy as np
+    from oracle import refbind as rb
+    out = {}
+    q, Delta = 1 << LOGQ, 1 << LOGDELTA
+    t_start = time.perf_counter()
+    for variant, tag in (("libgpqhe.so", "Og"), ("libgpqhe_O3.so", "O3")):
+        if not rb.available(variant) or time.perf_counter() - t_start > budget_s:
+            continue
+        R = rb.Ref(variant)
+        R.hectx_init(logn, q, SLOTS, Delta)
+        n, l = R.n, R.hectx.L
+        rng, nrng = random.Random(2), np.random.default_rng(2)
+        primes = R.primes()
+        a = nrng.integers(0, primes[0], size=n, dtype=np.uint64)
+        nd = R.node(0)
+        ts = []
+        for _ in range(5):
+            b = a.copy(); t0 = time.perf_counter(); R.lib.ntt(rb.ptr(b), nd); ts.append(time.perf_counter() - t0)
+        ti = []
+        for _ in range(5):
+            b = a.copy(); t0 = time.perf_counter(); R.lib.invntt(rb.ptr(b), nd); ti.append(time.perf_counter() - t0)
+        out[f"ntt_limb_per_s_{tag}"] = 1.0 / statistics.median(ts)
+        out[f"invntt_limb_per_s_{tag}"] = 1.0 / statistics.median(ti)
+        ql = R.to_int(R.hectx.q[l])
+        mk = lambda: [rng.randrange(ql) - ql // 2 for _ in range(n)]
+        evk = R.new_evk(synth_evk(nrng, primes, n, R.hectx.dimevk).reshape(-1),
+                        synth_evk(nrng, primes, n, R.hectx.dimevk).reshape(-1))
+        if tag == "Og":
+            ca = R.new_ct(l, mk(), mk())
+            t0 = time.perf_counter(); R.lib.he_rot(C.byref(ca), 0, C.byref(evk)); out["he_rot_per_s_Og"] = 1.0 / (time.perf_counter() - t0)
+        else:
+            ca, cb = R.new_ct(l, mk(), mk()), R.new_ct(l, mk(), mk())
+            cr = R.new_ct(l, [0] * n, [0] * n)
+            t0 = time.perf_counter()
+            R.lib.he_mul(C.byref(cr), C.byref(ca), C.byref(cb), C.byref(evk)); R.lib.he_rs(C.byref(cr))
+            out["he_mul_rs_per_s_O3"] = 1.0 / (time.perf_counter() - t0)
+    out["note"] = ("unmodified reference, 1 thread; Og = gcc -Og as shipped (Makefile:21), O3 = the same sources at -O3 "
+                   "(courtesy); ntt/invntt: one limb-poly at N=2^%d (src/ntt.c:37,54), median of 5; he_rot: one call" % logn)
+    return out
+
+
+def ref_config(note):
+    import math
+    bits = LOGQ + 1
+    return {"workload": WORKLOAD, "logn": LOGN, "logq": LOGQ, "logDelta": LOGDELTA, "level": LOGQ // LOGDELTA,
+            "tensor_limbs": (2 * bits + LOGN) // 59 + 1, "keyswitch_limbs": 24, "words_per_coeff": (bits + 63) // 64,
+            "note": note}
+
+
 def cpu_reference(nmeas, budget_s=150.0, logn=LOGN):
     """Time he_mul + he_rs of the reference's own CPU implementation on this box.
     kind "reference": the unmodified library in oracle/_ref (gcc -Og as shipped, 1 thread:
@@ -145,8 +201,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "ops/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "logn": LOGN, "logq": LOGQ, "logDelta": LOGDELTA,
-                       "note": f"CPU reference arm: {nm} op(s) measured (each ~{sec:.1f} s), median"},
+            "config": ref_config(f"CPU reference arm: {nm} op(s) measured (each ~{sec:.1f} s), median"),
             "cpu_baseline": {"value": val, "unit": "ops/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": "ops/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -179,6 +234,9 @@ def run_ours(args):
 
     ctx = g.HeContext(LOGN, 1 << LOGQ, SLOTS, 1 << LOGDELTA, device=local)
     lib, h = ctx._lib, ctx._h
+    # measurement-only kernels (integer-pipe peaks, 32-bit NTT probe, tensor-core contraction probe): a separate library
+    probe = C.CDLL(os.path.join(ROOT, "profiles", "probe", "libgqprobe.so"))
+    probe.gqp_last_error.restype = C.c_char_p
     n, W, L = ctx.n, ctx.W, ctx.L
     D1, D2 = ctx.dims(L)
     rng = np.random.default_rng(1234 + rank)
@@ -202,8 +260,7 @@ def run_ours(args):
     def step(i):
         b = dpool.data_ptr() + (i % POOL) * 4 * poly
         o0, o1 = dout.data_ptr(), dout.data_ptr() + poly
-        ck(lib.gq_he_mul_dev(h, L, o0, o1, b, b + poly, b + 2 * poly, b + 3 * poly, evk._h, None))
-        ck(lib.gq_he_rs_dev(h, L, o0, o1, None))
+        ck(lib.gq_he_mul_rs_dev(h, L, o0, o1, b, b + poly, b + 2 * poly, b + 3 * poly, evk._h, None))
 
     # throughput mode: independent products round-robin over LANES compute lanes of this GPU (each lane =
     # stream + scratch, tables and key shared); the timed region forks from / joins into the context's stream
@@ -216,8 +273,7 @@ def run_ours(args):
         k = i % LANES
         b = dpool.data_ptr() + (i % POOL) * 4 * poly
         o0, o1 = douts[k].data_ptr(), douts[k].data_ptr() + poly
-        ck(lib.gq_he_mul_dev(lane_h[k], L, o0, o1, b, b + poly, b + 2 * poly, b + 3 * poly, evk._h, None))
-        ck(lib.gq_he_rs_dev(lane_h[k], L, o0, o1, None))
+        ck(lib.gq_he_mul_rs_dev(lane_h[k], L, o0, o1, b, b + poly, b + 2 * poly, b + 3 * poly, evk._h, None))
 
     def barrier():
         ctx.sync()
@@ -249,22 +305,34 @@ def run_ours(args):
             ms = float(t.item())
         return ms
 
+    def timed_regions(fn, steps, warm, lanes=False, min_total_s=0.5, max_regions=400):
+        """the `steps`-sized timed region repeated until at least min_total_s of device time has been measured (at least
+        3 regions): one region of 20 products is a few milliseconds.  Returns the per-region times in ms."""
+        first = timed(fn, steps, warm, lanes)
+        want = int(min(max_regions, max(3, min_total_s * 1e3 / max(first, 1e-3) + 1)))
+        if world > 1:
+            t = torch.tensor([want], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            want = int(t.item())
+        return [first] + [timed(fn, steps, 0, lanes) for _ in range(want - 1)]
+
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     l0 = ctx.launch_count
-    ms = timed(lane_step, args.steps, max(args.warmup, LANES), lanes=True)
-    launches = (ctx.launch_count - l0) * args.steps // (args.steps + max(args.warmup, LANES))
+    regions = timed_regions(lane_step, args.steps, max(args.warmup, LANES), lanes=True)
+    ms = statistics.median(regions)
+    launches = (ctx.launch_count - l0) * args.steps // (args.steps * len(regions) + max(args.warmup, LANES))
     # every lane's last product equals the single-stream result of the same inputs
     lanes_ok = True
     for k in range(LANES):
-        i_last = max(i for i in range(max(args.warmup, LANES) + args.steps) if i % LANES == k)
+        i_last = max(i for i in range(args.steps) if i % LANES == k)        # the last region started at step index 0
         got = douts[k].clone()
         with torch.cuda.stream(ext):
             step(i_last)
         barrier()
         lanes_ok = lanes_ok and bool(torch.equal(got, dout if k == 0 else douts[0]))
-    ms_single = timed(step, args.steps, args.warmup)
+    ms_single = statistics.median(timed_regions(step, args.steps, args.warmup, min_total_s=0.2))
     clocks = sampler.stop() if rank == 0 else None
     ms_per_step = ms / args.steps
     value = world * args.steps / (ms * 1e-3)
@@ -306,15 +374,23 @@ def run_ours(args):
     # integer-pipe roofline: what the tile kernel achieves in butterflies/s against the measured
     # register-resident butterfly rate of this GPU (gq_peak.cu)
     bf_peak, mw_peak = C.c_double(0), C.c_double(0)
-    ck(lib.gq_bench_intpipe(h, C.byref(bf_peak), C.byref(mw_peak)))
+    p0c = ctx.prime_consts(0)
+    w0 = int(p0c[0]) // 3
+    if probe.gqp_bench_intpipe(local, C.c_uint64(int(p0c[0])), C.c_uint64(w0), C.c_uint64((w0 << 64) // int(p0c[0])),
+                               C.byref(bf_peak), C.byref(mw_peak)) != 0:
+        raise RuntimeError(probe.gqp_last_error().decode())
     tile_bf = nlp * (n // 2) * 12 / (ms_tile * 1e-3)
-    roofline["int_pipe"] = {"bound": "integer multiply pipe (fmaheavy)", "unit": "Gbutterfly/s",
-                            "achieved": tile_bf / 1e9, "peak": bf_peak.value / 1e9,
-                            "frac": tile_bf / bf_peak.value if bf_peak.value else None,
-                            "madwide_peak_Gops": mw_peak.value / 1e9,
-                            "peak_source": "measured in this run: k_peak_butterfly (lazy Shoup butterfly, operands in "
-                                           "registers, 4 chains per thread, no memory)",
-                            "algorithmic_butterflies_per_launch": nlp * (n // 2) * 12}
+    MUL_PER_BF = 8.0          # 6 IMAD.WIDE + 4 low-half IMAD per lazy Shoup butterfly, a low-half product counted 0.5
+    roofline["int_pipe"] = {"bound": "integer multiply pipe (fmaheavy)", "unit": "G 32x32-multiply-equivalents/s",
+                            "achieved": tile_bf * MUL_PER_BF / 1e9, "peak": mw_peak.value / 1e9,
+                            "frac": tile_bf * MUL_PER_BF / mw_peak.value if mw_peak.value else None,
+                            "mul32_per_butterfly": MUL_PER_BF,
+                            "peak_source": "measured in this run: k_peak_madwide (dependent-free IMAD.WIDE.U32, profiles/probe)",
+                            "algorithmic_butterflies_per_launch": nlp * (n // 2) * 12,
+                            "butterfly_ceiling": {"achieved_Gbf": tile_bf / 1e9, "peak_Gbf": bf_peak.value / 1e9,
+                                                  "frac": tile_bf / bf_peak.value if bf_peak.value else None,
+                                                  "note": "secondary: against k_peak_butterfly, this kernel's own butterfly "
+                                                          "instruction sequence run from registers (memory / barrier overhead only)"}}
     ntt = {"fwd_limb_ntt_per_s": world * nlp / (ms_f * 1e-3), "inv_limb_ntt_per_s": world * nlp / (ms_i * 1e-3),
            "fwd_ms_per_batch": ms_f, "inv_ms_per_batch": ms_i, "tile_kernel_ms_per_batch": ms_tile,
            "exact_fwd_limb_ntt_per_s": world * nlp / (ms_fx * 1e-3),
@@ -325,13 +401,31 @@ def run_ours(args):
     # primes on 32-bit words, the building block of the internal 31-bit-class RNS basis planned in DESIGN.md
     # section 4; 720 limb-polys = 184 MB against the 192 MB of the 64-bit batch
     n32_rate, n32_bad = C.c_double(0), C.c_int(-1)
-    with torch.cuda.stream(ext):
-        ck(lib.gq_bench_ntt32(h, LOGN, 30, 24, 5, C.byref(n32_rate), C.byref(n32_bad)))
+    ctx.sync()
+    if probe.gqp_bench_ntt32(local, LOGN, 30, 24, 5, C.byref(n32_rate), C.byref(n32_bad)) != 0:
+        raise RuntimeError(probe.gqp_last_error().decode())
     ntt["ntt32_probe"] = {"fwd_limb_ntt_per_s": world * n32_rate.value, "batch_limb_polys": 720, "prime_bits": 30,
                           "mismatches_vs_host": n32_bad.value,
                           "limbs_needed_vs_64bit": "30 (tensor basis) / 48 (key-switch basis) against 16 / 24",
                           "note": "not used by any product path yet; limb-NTT for limb-NTT it has to be compared with "
                                   "fwd_limb_ntt_per_s x 16/30"}
+    # measurement only (profiles/probe/gqp_imma.cu): rns_decompose as a u8 tensor-core contraction (mma.sync m16n8k32,
+    # exact int32 accumulation) in the shape of he_mul's first decomposition, next to the integer-pipe kernel's time
+    imma = None
+    try:
+        raw, rate, msl, bad = C.c_double(0), C.c_double(0), C.c_double(0), C.c_int(-1)
+        pr16 = (C.c_uint64 * 16)(*ctx.primes[:16])
+        if probe.gqp_bench_imma_raw(local, C.byref(raw)) == 0 and \
+           probe.gqp_bench_imma_decompose(local, LOGN, 16, pr16, 10, C.byref(rate), C.byref(msl), C.byref(bad)) == 0:
+            imma = {"raw_u8_Tmac_per_s": raw.value / 1e12, "decompose_4x16_us": msl.value * 1e3,
+                    "residues_per_s": rate.value, "mismatches_vs_host": bad.value,
+                    "note": "prototype: A fragments straight from the word-major coefficients, B (2^(8j) mod p, byte split) "
+                            "from shared memory, thread-local recombination of the 8 byte columns + pseudo-Mersenne fold; "
+                            "compare with the 'decompose x4 -> D1' row of `stages`"}
+        else:
+            imma = {"error": probe.gqp_last_error().decode()}
+    except Exception as ex:
+        imma = {"error": repr(ex)}
 
     # ---- every stage kernel of one he_mul+he_rs, timed alone in the shapes the op uses (gq_stage_* = the
     # kernels the op launches), against both rooflines: algorithmic bytes / HBM peak and 32x32-multiply
@@ -354,24 +448,20 @@ def run_ours(args):
              4 * D1 * n, 34.0, 4 * W * n * 8 + 4 * D1 * n * 8),     # 15 digits x 2 multiply-adds + 4 in the fold
             ("forward NTT, 4 x D1 limb-polys", "k_nttl_fwd_strided<4> + k_nttl_fwd_tile<12>", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D1, 4, xc.data_ptr(), 0, None)),
              4 * D1 * (n // 2) * LOGN, 8.0, 2 * 2 * 4 * D1 * n * 8),
-            ("tensor product", "k_tensor_pm", lambda i: ck(lib.gq_stage_tensor_dev(h, 0, D1, y.data_ptr(), xc.data_ptr(), None)),
-             D1 * n, 4 * 7.0, 7 * D1 * n * 8),
-            ("inverse NTT, 3 x D1", "k_nttl_inv_tile<12> + k_nttl_inv_strided<4>", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D1, 3, y.data_ptr(), 1, None)),
-             3 * D1 * (n // 2) * LOGN, 8.0, 2 * 2 * 3 * D1 * n * 8),
+            ("tensor product + inverse NTT, 3 x D1", "k_nttl_inv_tile<12, TENSOR> + k_nttl_inv_strided<4>",
+             lambda i: ck(lib.gq_stage_tensor_inv_dev(h, 0, D1, y.data_ptr(), xc.data_ptr(), None)),
+             3 * D1 * (n // 2) * LOGN, 8.0 + 4 * 7.0 * 2 / (3 * LOGN), (4 + 3 + 2 * 3) * D1 * n * 8),
             ("reconstruct x3 over D1", "k_reconstruct_fast<7>", lambda i: ck(lib.gq_stage_reconstruct_dev(h, D1, L, 3, y.data_ptr(), out3, n, None)),
              3 * n, D1 * 38.0 + 4 * W, 3 * D1 * n * 8 + 3 * W * n * 8),
             ("decompose d2 -> D2", "k_decompose28<7, pm>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D2, 1, in1, W, n, x2.data_ptr(), None)),
              D2 * n, 34.0, W * n * 8 + D2 * n * 8),
             ("forward NTT, D2", "k_nttl_fwd_*", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D2, 1, x2.data_ptr(), 0, None)),
              D2 * (n // 2) * LOGN, 8.0, 2 * 2 * D2 * n * 8),
-            ("multiply by rlk", "k_mul_evk_pm", lambda i: ck(lib.gq_stage_mul_evk_dev(h, 0, D2, y2.data_ptr(), x2.data_ptr(), evk._h, None)),
-             D2 * n, 2 * 7.0, 5 * D2 * n * 8),
-            ("inverse NTT, 2 x D2", "k_nttl_inv_*", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D2, 2, y2.data_ptr(), 1, None)),
-             2 * D2 * (n // 2) * LOGN, 8.0, 2 * 2 * 2 * D2 * n * 8),
-            ("key-switch epilogue", "k_ks_epilogue_fast<8>", lambda i: ck(lib.gq_stage_ks_epilogue_dev(h, L, y2.data_ptr(), d[0].data_ptr(), d[1].data_ptr(), o[0].data_ptr(), o[1].data_ptr(), n, None)),
+            ("multiply by rlk + inverse NTT, 2 x D2", "k_nttl_inv_tile<12, EVK> + k_nttl_inv_strided<4>",
+             lambda i: ck(lib.gq_stage_mul_evk_inv_dev(h, 0, D2, y2.data_ptr(), x2.data_ptr(), evk._h, None)),
+             2 * D2 * (n // 2) * LOGN, 8.0 + 2 * 7.0 * 2 / (2 * LOGN), (3 + 2 + 2 * 2) * D2 * n * 8),
+            ("key-switch epilogue + rescale", "k_ks_epilogue_fast<8, 7> (he_rs fused)", lambda i: ck(lib.gq_stage_ks_epilogue_rs_dev(h, L, y2.data_ptr(), d[0].data_ptr(), d[1].data_ptr(), o[0].data_ptr(), o[1].data_ptr(), n, None)),
              2 * n, D2 * 42.0 + ctx.dim * 40.0 + 128 + 64, 2 * D2 * n * 8 + 4 * W * n * 8),
-            ("rescale", "k_rescale_pow2", lambda i: ck(lib.gq_stage_rescale_dev(h, L, o[0].data_ptr(), o[1].data_ptr(), 1, n, None)),
-             2 * n, 0.0, 4 * W * n * 8),
         ]
         with torch.cuda.stream(ext):
             for st in stages:          # one pass in order so that every stage sees real data
@@ -391,7 +481,9 @@ def run_ours(args):
             r["share"] = r["us"] / (total * 1e3)
         return {"rows": rows, "sum_us": total * 1e3,
                 "peaks": {"madwide_Gops": mw_peak.value / 1e9, "hbm_GBps": hbm},
-                "note": "each stage timed alone on one stream (20 launches back to back, L2-warm as inside the op); "
+                "note": "the op's own launches (the stage-level entry points call the kernels gq_he_mul_rs_dev launches; inside the op "
+                        "the CRT stages additionally skip their first multiplication because the inverse NTT folds (P/p_d)^-1 into "
+                        "its final scaling); each stage timed alone on one stream (20 launches back to back, L2-warm as inside the op); "
                         "frac_int_pipe = 32x32-multiply work / measured IMAD.WIDE peak of this GPU (gq_bench_intpipe), "
                         "frac_hbm = algorithmic bytes / measured HBM copy peak; the NTT rows use 8 multiply-equivalents "
                         "per butterfly (6 wide + 4 low)"}
@@ -520,6 +612,13 @@ def run_ours(args):
 
     # ---- limb-sharded single-stream pipeline: all ranks cooperate on ONE he_mul+he_rs;
     # ciphertexts stay coefficient-sharded, four all-to-alls per op (gpqhe_b200/sharded.py)
+    def all_ok(flag):
+        if world == 1:
+            return bool(flag)
+        t = torch.tensor([1 if flag else 0], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return bool(t.item())
+
     sharded = None
     if not args.no_sharded:
         from gpqhe_b200.sharded import MulPlan, ShardedHe
@@ -535,6 +634,12 @@ def run_ours(args):
             def sstep(i):
                 c0, c1 = sh.he_mul(L, sl[0], sl[1], sl[2], sl[3], evk_s)
                 sh.he_rs(L, c0, c1)
+            # the same op on ONE GPU (every rank holds the full inputs): what the sharded results must equal, bit for bit
+            single = torch.empty((2, W, n), dtype=torch.int64, device=dev)
+            ck(lib.gq_he_mul_rs_dev(h, L, single[0].data_ptr(), single[1].data_ptr(), full[0].data_ptr(), full[1].data_ptr(),
+                                    full[2].data_ptr(), full[3].data_ptr(), evk_s._h, None))
+            ctx.sync()
+            want_sl = [sh.shard(single[0]), sh.shard(single[1])]
         ex0, by0 = sh.exchanges, sh.exchanged_bytes
         ms_eager = timed(sstep, args.steps, args.warmup)
         a2a_per_op = (sh.exchanges - ex0) // (args.steps + args.warmup)
@@ -552,7 +657,13 @@ def run_ours(args):
             ms_s, graphed = timed(lambda i: plan.run(), args.steps, args.warmup), True
         except Exception as ex:   # keep the eager number and say why
             print(f"bench.py: graph-planned sharded op failed: {ex!r}", file=sys.stderr)
+        nccl_exact = None
+        if plan is not None:
+            with torch.cuda.stream(ext):
+                ctx.sync()
+                nccl_exact = bool(torch.equal(plan.out[0], want_sl[0]) and torch.equal(plan.out[1], want_sl[1]))
         sharded = {"ops_per_s": args.steps / (ms_s * 1e-3), "ms_per_op": ms_s / args.steps, "ranks": world,
+                   "bit_exact_vs_single_gpu": None if nccl_exact is None else all_ok(nccl_exact),
                    "scaling": "strong", "all_to_all_per_op": a2a_per_op, "bytes_sent_per_rank_per_op": bytes_per_op,
                    "cuda_graphs_between_exchanges": graphed, "eager_ms_per_op": ms_eager / args.steps,
                    "note": "one ciphertext stream sharded by RNS limb (NTT domain) and by coefficient (CRT domain); "
@@ -560,12 +671,6 @@ def run_ours(args):
 
         # peer-to-peer variant: the re-layouts are scatter kernels writing into the peers' slabs over
         # NVLink (gq_p2p.cu), epoch flags instead of NCCL, the whole op one CUDA graph per rank
-        def all_ok(flag):
-            if world == 1:
-                return bool(flag)
-            t = torch.tensor([1 if flag else 0], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MIN)
-            return bool(t.item())
         if not args.no_p2p and plan is not None:
             from gpqhe_b200.sharded import P2PPlan
             pp, ok, match = None, True, False
@@ -574,16 +679,16 @@ def run_ours(args):
                     pp = P2PPlan.build(sh, L, evk_s, rescale=True)
                     for k in range(4):
                         pp.inp[k].copy_(sl[k])
-                    pp.run()
+                    pp.run(check=False)
                     ctx.sync()
-                    want0, want1 = plan.out[0], plan.out[1]
+                    want0, want1 = want_sl[0], want_sl[1]
                     match = bool(torch.equal(pp.out[0], want0) and torch.equal(pp.out[1], want1)) and not pp.failed()
             except Exception as ex:
                 print(f"bench.py: p2p plan failed: {ex!r}", file=sys.stderr)
                 ok = False
             if all_ok(ok):
-                ms_pe = timed(lambda i: pp.run(), args.steps, args.warmup)
-                p2p = {"bit_exact_vs_nccl_plan": all_ok(match), "eager_ms_per_op": ms_pe / args.steps}
+                ms_pe = timed(lambda i: pp.run(check=False), args.steps, args.warmup)
+                p2p = {"bit_exact_vs_single_gpu": all_ok(match), "eager_ms_per_op": ms_pe / args.steps}
                 okc = True
                 try:
                     with torch.cuda.stream(ext):
@@ -592,15 +697,19 @@ def run_ours(args):
                     print(f"bench.py: p2p graph capture failed: {ex!r}", file=sys.stderr)
                     okc = False
                 if all_ok(okc):
-                    ms_pg = timed(lambda i: pp.run(), args.steps, args.warmup)
+                    ms_pg = statistics.median(timed(lambda i: pp.run(check=False), args.steps, args.warmup if r == 0 else 0)
+                                              for r in range(5))
                     with torch.cuda.stream(ext):
                         ctx.sync()
-                        same = bool(torch.equal(pp.out[0], plan.out[0]) and torch.equal(pp.out[1], plan.out[1]))
+                        same = bool(torch.equal(pp.out[0], want_sl[0]) and torch.equal(pp.out[1], want_sl[1]))
                     p2p.update({"ms_per_op": ms_pg / args.steps, "ops_per_s": args.steps / (ms_pg * 1e-3),
                                 "one_graph_per_op": True, "bit_exact_after_replays": all_ok(same and not pp.failed())})
                 else:
                     pp.graph = None
                 sharded["p2p"] = p2p
+                if world > 1:
+                    dist.barrier()
+                pp.close()
             else:
                 sharded["p2p"] = {"error": "plan construction failed on some rank (see stderr)"}
 
@@ -686,6 +795,28 @@ def run_ours(args):
         sec, nm, kind, cores, sample = cpu_reference(1, budget_s=30.0)
         cpu = {"value": 1.0 / sec, "unit": "ops/s", "cores": cores, "kind": kind, "sample": sample,
                "host_cores_on_box": os.cpu_count()}
+        try:
+            if kind == "reference":
+                cpu["more"] = cpu_reference_extras()
+        except Exception as ex:
+            cpu["more"] = {"error": repr(ex)}
+    # the drop-in itself: he_mul + he_rs through the REFERENCE'S OWN SYMBOLS of dropin/_build/libgpqhe.so with gcry_mpi
+    # ciphertexts (what a GPQHE caller links), timed by dropin/_build/dropin_bench in its own process
+    dropin = None
+    if rank == 0 and world == 1 and not args.no_dropin:
+        exe = os.path.join(ROOT, "dropin", "_build", "dropin_bench")
+        if os.path.exists(exe):
+            ctx.sync()
+            try:
+                out = subprocess.run([exe, str(LOGN), str(LOGQ), str(SLOTS), str(LOGDELTA), str(max(8, args.steps))],
+                                     stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+                dropin = json.loads(out.stdout.strip().splitlines()[-1]) if out.returncode == 0 else \
+                    {"error": (out.stderr or out.stdout)[-400:]}
+            except Exception as ex:
+                dropin = {"error": repr(ex)}
+        else:
+            dropin = {"error": "dropin/_build/dropin_bench is not built"}
+    e2e["dropin"] = dropin
 
     if rank == 0:
         ws_mib = (4 + 3) * ctx.dimub * n * 8 / 2**20 + 2 * ctx.dimevk * n * 8 / 2**20
@@ -696,11 +827,20 @@ def run_ours(args):
                            "tensor_limbs": D1, "keyswitch_limbs": D2, "words_per_coeff": W,
                            "parallelism": f"{world} GPU(s), each running independent he_mul+he_rs products round-robin over {LANES} "
                                           "compute lanes (streams) of its own context; no data-path collective",
-                           "lanes_per_gpu": LANES,
+                           "lanes_per_gpu": LANES, "timed_regions": len(regions),
+                           "timed_region_ms": {"median": ms, "min": min(regions), "max": max(regions),
+                                               "total_s": sum(regions) * 1e-3},
+                           "sharded_ranks": (sharded or {}).get("ranks"),
+                           "sharded_nccl_ms_per_op": (sharded or {}).get("ms_per_op"),
+                           "sharded_p2p_ms_per_op": ((sharded or {}).get("p2p") or {}).get("ms_per_op"),
+                           "sharded_bytes_sent_per_rank_per_op": (sharded or {}).get("bytes_sent_per_rank_per_op"),
+                           "sharded_bit_exact_vs_single_gpu": (None if not sharded else bool(
+                               sharded.get("bit_exact_vs_single_gpu") and
+                               ((sharded.get("p2p") or {}).get("bit_exact_after_replays", (sharded.get("p2p") or {}).get("bit_exact_vs_single_gpu", True))))),
                            "l2": f"inputs rotate over a pool of {POOL} ciphertext pairs ({POOL * 4 * poly / 2**20:.0f} MiB) and the "
                                  f"per-op scratch + key is {ws_mib:.0f} MiB: working set > 126 MB L2"},
                 "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "ntt": ntt,
-                "stages": stages, "rot_sweep": rot_sweep, "sharded": sharded, "cpu_baseline": cpu,
+                "stages": stages, "imma_probe": imma, "rot_sweep": rot_sweep, "sharded": sharded, "cpu_baseline": cpu,
                 "single_stream": {"ops_per_s": world * args.steps / (ms_single * 1e-3), "ms_per_op": ms_single / args.steps,
                                   "note": "the same products issued back to back on ONE stream (latency of one op)"},
                 "lanes_bit_exact_vs_single_stream": lanes_ok}
@@ -720,6 +860,7 @@ def main():
     ap.add_argument("--lanes", type=int, default=3, help="compute lanes per GPU for the throughput figure")
     ap.add_argument("--e2e-lanes", type=int, default=6, help="compute lanes per GPU for the host-buffer (e2e) leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-dropin", action="store_true", help="skip the drop-in (reference symbols, gcry_mpi) leg")
     ap.add_argument("--no-rot", action="store_true", help="skip the rotation sweep leg")
     ap.add_argument("--no-p2p", action="store_true", help="skip the peer-to-peer variant of the sharded leg")
     ap.add_argument("--no-sharded", action="store_true", help="skip the limb-sharded single-stream leg")

@@ -88,8 +88,6 @@ SIGNATURES = {
     "gq_he_rlsin_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, vp, vp]),
     "gq_he_slot2coeff": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, vp, vp]),
     "gq_he_slot2coeff_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
-    "gq_bench_ntt32": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(C.c_double), C.POINTER(C.c_int)]),
-    "gq_bench_intpipe": (C.c_int, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "gq_he_mul_rs": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp]),
     "gq_he_mul_batch": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp, vp, vp, vp, C.c_int]),
     "gq_he_mulpt": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp, vp]),
@@ -110,9 +108,12 @@ SIGNATURES = {
     "gq_stage_decompose_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, C.POINTER(vp), C.c_uint, C.c_uint, vp, vp]),
     "gq_stage_ntt_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.c_int, vp]),
     "gq_stage_tensor_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp]),
+    "gq_stage_tensor_inv_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp]),
     "gq_stage_mul_evk_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp]),
+    "gq_stage_mul_evk_inv_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp]),
     "gq_stage_reconstruct_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.POINTER(vp), C.c_uint, vp]),
     "gq_stage_ks_epilogue_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, vp]),
+    "gq_stage_ks_epilogue_rs_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, vp]),
     "gq_stage_rescale_dev": (C.c_int, [vp, C.c_uint, vp, vp, C.c_int, C.c_uint, vp]),
     "gq_p2p_alloc": (C.c_int, [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]),
     "gq_p2p_open": (C.c_int, [vp, C.c_char_p, C.POINTER(vp)]),
@@ -121,7 +122,7 @@ SIGNATURES = {
     "gq_p2p_scatter_c2l_dev": (C.c_int, [vp, vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(vp), C.POINTER(C.c_int), vp]),
     "gq_p2p_scatter_l2c_dev": (C.c_int, [vp, vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(vp), C.POINTER(C.c_int), vp]),
     "gq_p2p_bump_dev": (C.c_int, [vp, vp, vp]),
-    "gq_p2p_signal_dev": (C.c_int, [vp, C.POINTER(vp), C.c_uint, C.c_uint, C.c_uint, vp, vp]),
+    "gq_p2p_signal_dev": (C.c_int, [vp, C.POINTER(vp), C.c_uint, C.c_uint, C.c_uint, vp, vp, vp]),
     "gq_p2p_wait_dev": (C.c_int, [vp, vp, C.c_uint, C.c_uint, vp, vp, vp]),
 }
 

@@ -238,7 +238,17 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
   c->logqub = logqub;
   c->dimub = (1 + logn + 4 * logqub) / logp + 1;       // precomp.c:357
   if (c->dimub > GQ_MAX_PRIMES) { delete c; GQ_FAIL("dimub exceeds GQ_MAX_PRIMES"); }
-  GQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  // from here on every failure goes through gq_ctx_destroy(c): nothing allocated so far may leak
+#define GQ_CUDA_CTX(call)                                                                \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) {                                                             \
+      gq_set_error(std::string(__func__) + ": " #call " -> " + cudaGetErrorString(e_));  \
+      gq_ctx_destroy(c);                                                                 \
+      return 1;                                                                          \
+    }                                                                                    \
+  } while (0)
+  GQ_CUDA_CTX(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   c->lazy_ntt = getenv("GPQHE_B200_EXACT_NTT") == nullptr;   // A/B switch for tests and profiling
 
   const unsigned n = c->n, K = c->dimub;
@@ -336,9 +346,10 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
       if (build_basis(c, D, P)) { gq_ctx_destroy(c); return 1; }
     }
   }
-  GQ_CUDA(cudaMalloc((void **)&c->d_adhoc, 2 * GQ_MAX_W * sizeof(uint64_t)));
-  GQ_CUDA(cudaMalloc((void **)&c->d_fix, (4 + 4 * (size_t)n) * sizeof(int)));
-  GQ_CUDA(cudaMemset(c->d_fix, 0, 4 * sizeof(int)));
+  GQ_CUDA_CTX(cudaMalloc((void **)&c->d_adhoc, 2 * GQ_MAX_W * sizeof(uint64_t)));
+  GQ_CUDA_CTX(cudaMalloc((void **)&c->d_fix, (4 + 4 * (size_t)n) * sizeof(int)));
+  GQ_CUDA_CTX(cudaMemset(c->d_fix, 0, 4 * sizeof(int)));
+#undef GQ_CUDA_CTX
   c->fast_crt = getenv("GPQHE_B200_EXACT_CRT") == nullptr;    // A/B switch for tests and profiling
 
   // hectx_init / qtable_init (precomp.c:386-452)
@@ -1521,9 +1532,8 @@ extern "C" int gq_he_mul_batch(gq_ctx *c, unsigned l, unsigned count, uint64_t *
   if (c->lanes.empty()) {
     const char *e = getenv("GPQHE_B200_LANES");
     unsigned want = e ? (unsigned)atoi(e) : 3u;
-    if (want < 1 || want > 8) want = 3;
-    if (want > count) want = count;
-    if (want > 1 && gq_ctx_set_lanes(c, want)) return 1;
+    if (want < 1 || want > 8) want = 3;          // not clamped to `count`: a first call with few products must not
+    if (want > 1 && gq_ctx_set_lanes(c, want)) return 1;   // freeze the lane count of every later batch
   }
   const unsigned K = (unsigned)c->lanes.size() + 1, NB = 2 * K;
   const size_t poly = (size_t)c->W * c->n;
@@ -1536,37 +1546,53 @@ extern "C" int gq_he_mul_batch(gq_ctx *c, unsigned l, unsigned count, uint64_t *
   uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_PIPE];
   cudaEvent_t *ev = c->ev_batch.data();   // [4*b + {0: in_ready, 1: in_free, 2: out_ready, 3: out_free}]
   int rc = 0;
+  // every exit drains the copy streams and the lanes first: copies and kernels in flight reference the caller's
+  // host buffers and the shared staging slot, and the next call starts without waits
+  auto drain = [&]() {
+    cudaStreamSynchronize(c->s_in);
+    for (unsigned k = 0; k < K; k++) cudaStreamSynchronize(gq_ctx_lane(c, k)->stream);
+    return cudaStreamSynchronize(c->s_out);
+  };
+#define GQ_CUDA_B(call)                                                                  \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) {                                                             \
+      gq_set_error(std::string(__func__) + ": " #call " -> " + cudaGetErrorString(e_));  \
+      drain();                                                                           \
+      return 1;                                                                          \
+    }                                                                                    \
+  } while (0)
   for (unsigned i = 0; i < count && !rc; i++) {
     const unsigned bf = i % NB;
     gq_ctx *ln = gq_ctx_lane(c, i % K);
     uint64_t *in = base + (size_t)bf * 6 * poly, *out = in + 4 * poly;
     const uint64_t *src[4] = {a0[i], a1[i], b0[i], b1[i]};
-    if (i >= NB) GQ_CUDA(cudaStreamWaitEvent(c->s_in, ev[4 * bf + 1], 0));
+    if (i >= NB) GQ_CUDA_B(cudaStreamWaitEvent(c->s_in, ev[4 * bf + 1], 0));
     for (int j = 0; j < 4;) {          // polys that are adjacent in host memory travel as one copy
       int e = j + 1;
       while (e < 4 && src[e] == src[e - 1] + poly) e++;
-      GQ_CUDA(cudaMemcpyAsync(in + j * poly, src[j], (size_t)(e - j) * poly * 8, cudaMemcpyHostToDevice, c->s_in));
+      GQ_CUDA_B(cudaMemcpyAsync(in + j * poly, src[j], (size_t)(e - j) * poly * 8, cudaMemcpyHostToDevice, c->s_in));
       j = e;
     }
-    GQ_CUDA(cudaEventRecord(ev[4 * bf + 0], c->s_in));
-    GQ_CUDA(cudaStreamWaitEvent(ln->stream, ev[4 * bf + 0], 0));
-    if (i >= NB) GQ_CUDA(cudaStreamWaitEvent(ln->stream, ev[4 * bf + 3], 0));
+    GQ_CUDA_B(cudaEventRecord(ev[4 * bf + 0], c->s_in));
+    GQ_CUDA_B(cudaStreamWaitEvent(ln->stream, ev[4 * bf + 0], 0));
+    if (i >= NB) GQ_CUDA_B(cudaStreamWaitEvent(ln->stream, ev[4 * bf + 3], 0));
     rc = he_mul_impl(ln, l, out, out + poly, in, in + poly, in + 2 * poly, in + 3 * poly, rlk, nullptr, rescale != 0);
     if (rc) break;
-    GQ_CUDA(cudaEventRecord(ev[4 * bf + 1], ln->stream));
-    GQ_CUDA(cudaEventRecord(ev[4 * bf + 2], ln->stream));
-    GQ_CUDA(cudaStreamWaitEvent(c->s_out, ev[4 * bf + 2], 0));
+    GQ_CUDA_B(cudaEventRecord(ev[4 * bf + 1], ln->stream));
+    GQ_CUDA_B(cudaEventRecord(ev[4 * bf + 2], ln->stream));
+    GQ_CUDA_B(cudaStreamWaitEvent(c->s_out, ev[4 * bf + 2], 0));
     if (c1[i] == c0[i] + poly) {
-      GQ_CUDA(cudaMemcpyAsync(c0[i], out, 2 * poly * 8, cudaMemcpyDeviceToHost, c->s_out));
+      GQ_CUDA_B(cudaMemcpyAsync(c0[i], out, 2 * poly * 8, cudaMemcpyDeviceToHost, c->s_out));
     } else {
-      GQ_CUDA(cudaMemcpyAsync(c0[i], out, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
-      GQ_CUDA(cudaMemcpyAsync(c1[i], out + poly, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
+      GQ_CUDA_B(cudaMemcpyAsync(c0[i], out, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
+      GQ_CUDA_B(cudaMemcpyAsync(c1[i], out + poly, poly * 8, cudaMemcpyDeviceToHost, c->s_out));
     }
-    GQ_CUDA(cudaEventRecord(ev[4 * bf + 3], c->s_out));
+    GQ_CUDA_B(cudaEventRecord(ev[4 * bf + 3], c->s_out));
   }
-  cudaStreamSynchronize(c->s_in);
-  for (unsigned k = 0; k < K; k++) cudaStreamSynchronize(gq_ctx_lane(c, k)->stream);
-  GQ_CUDA(cudaStreamSynchronize(c->s_out));
+  const cudaError_t de = drain();
+#undef GQ_CUDA_B
+  if (!rc && de != cudaSuccess) { gq_set_error(std::string(__func__) + ": " + cudaGetErrorString(de)); return 1; }
   return rc;
 }
 
@@ -1696,6 +1722,31 @@ extern "C" int gq_stage_mul_evk_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, 
   return 0;
 }
 
+// tensor product + inverse NTT of a limb range in one pass (the pointwise stage rides on the load of the inverse
+// transform's tiles): x[4][nlimbs][n] (forward-transformed) -> y[3][nlimbs][n] (coefficient domain, canonical)
+extern "C" int gq_stage_tensor_inv_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, uint64_t *y,
+                                       const uint64_t *x, void *stream) {
+  if (!c || !y || !x) GQ_FAIL("bad argument");
+  if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
+  cudaStream_t st = pick(c, stream);
+  if (fused_inv_ok(c, limb0, nlimbs))
+    return ntt_inv_fused(c, GQ_NTTF_TENSOR, limb0, nlimbs, x, y, nullptr, nullptr, 1, st, 0);
+  if (gq_stage_tensor_dev(c, limb0, nlimbs, y, x, stream)) return 1;
+  return ntt_internal(c, limb0, nlimbs, 3, y, true, st);
+}
+// x * evk.p0, x * evk.p1 + inverse NTT of a limb range in one pass: x[nlimbs][n] -> y[2][nlimbs][n]
+extern "C" int gq_stage_mul_evk_inv_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, uint64_t *y,
+                                        const uint64_t *x, const gq_evk *evk, void *stream) {
+  if (!c || !y || !x || !evk) GQ_FAIL("bad argument");
+  if (limb0 + nlimbs > c->dimevk || !ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid");
+  cudaStream_t st = pick(c, stream);
+  const size_t off = (size_t)limb0 * c->n;
+  if (fused_inv_ok(c, limb0, nlimbs))
+    return ntt_inv_fused(c, GQ_NTTF_EVK, limb0, nlimbs, x, y, evk->p0 + off, evk->p1 + off, 1, st, 0);
+  if (gq_stage_mul_evk_dev(c, limb0, nlimbs, y, x, evk, stream)) return 1;
+  return ntt_internal(c, limb0, nlimbs, 2, y, true, st);
+}
+
 extern "C" int gq_stage_reconstruct_dev(gq_ctx *c, unsigned D, unsigned l, unsigned npolys,
                                         const uint64_t *rhat, uint64_t *const *out, unsigned ncoef,
                                         void *stream) {
@@ -1713,6 +1764,20 @@ extern "C" int gq_stage_ks_epilogue_dev(gq_ctx *c, unsigned l, const uint64_t *c
   if (!chat || !c0 || !c1) GQ_FAIL("null argument");
   if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
   return ks_epilogue_dev(c, l, dim_ks(c, l), chat, add0, add1, c0, c1, ncoef, pick(c, stream));
+}
+
+// key-switch epilogue followed by he_rs on the slice, one kernel when the moduli are powers of two
+extern "C" int gq_stage_ks_epilogue_rs_dev(gq_ctx *c, unsigned l, const uint64_t *chat,
+                                           const uint64_t *add0, const uint64_t *add1, uint64_t *c0,
+                                           uint64_t *c1, unsigned ncoef, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (l == 0) GQ_FAIL("cannot go below level 0");
+  if (!chat || !c0 || !c1) GQ_FAIL("null argument");
+  if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
+  const unsigned rs_j = rs_fusable(c, l);
+  if (ks_epilogue_dev(c, l, dim_ks(c, l), chat, add0, add1, c0, c1, ncoef, pick(c, stream), rs_j)) return 1;
+  if (!rs_j) return rescale_dev(c, l, c0, c1, true, stream, ncoef);
+  return 0;
 }
 
 extern "C" int gq_stage_rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, int divide,

@@ -12,6 +12,7 @@
 // can only reach exchange k of op t+1 after every peer has consumed exchange k of op t.
 // One process per GPU drives one GPU; the kernels that wait run on a different GPU than the
 // kernels they wait for.
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -71,10 +72,16 @@ k_scatter_l2c(GqPeers pr, const uint64_t *__restrict__ src, int P, int Dl, int D
 // the epoch lives in device memory so that the same (graph-captured) launch works for every op
 __global__ void k_bump(unsigned long long *epoch) { if (threadIdx.x == 0) *epoch += 1; }
 
-__global__ void k_signal(GqPeers flags, int slot, int G, int me, const unsigned long long *epoch_p) {
+// A rank whose error flag is set (a wait of this or an earlier op timed out: its slab may be half written) does
+// not publish the epoch but a POISON value: it passes every peer's `flag >= epoch` test at once, and k_wait turns it
+// into the peer's own error flag.  One late rank therefore fails the op on every rank, visibly, instead of letting
+// the others consume a half-written slab.  The flag is sticky: every later op of the plan fails fast.
+#define GQ_P2P_POISON (~0ull)
+
+__global__ void k_signal(GqPeers flags, int slot, int G, int me, const unsigned long long *epoch_p, const int *err) {
   const int s = threadIdx.x;
   if (s >= G) return;
-  const unsigned long long epoch = *epoch_p;
+  const unsigned long long epoch = (err && *err) ? GQ_P2P_POISON : *epoch_p;
 #ifndef GQ_EMULATE
   __threadfence_system();
 #endif
@@ -82,10 +89,14 @@ __global__ void k_signal(GqPeers flags, int slot, int G, int me, const unsigned 
   *f = epoch;
 }
 
-// err[0] is set when a peer never showed up (bounded spin: a lost peer must not hang the GPU)
-__global__ void k_wait(const uint64_t *flags, int slot, int G, const unsigned long long *epoch_p, int *err) {
+// err[0] is set when a peer never showed up within `spin_limit` polls of 200 ns (bounded spin: a lost peer must not
+// hang the GPU) or published the poison value.  An acquire fence follows the spin so that the slab reads of the
+// consuming kernels are ordered after the flag read on every path, not only across the kernel boundary.
+__global__ void k_wait(const uint64_t *flags, int slot, int G, const unsigned long long *epoch_p, int *err,
+                       unsigned long long spin_limit) {
   const int s = threadIdx.x;
   if (s >= G) return;
+  if (*err) return;                                       // sticky: fail fast, never wait again
   const unsigned long long epoch = *epoch_p;
   const volatile unsigned long long *f = (const volatile unsigned long long *)(flags + (size_t)slot * GQ_P2P_MAX_RANKS + s);
   unsigned long long spins = 0;
@@ -94,9 +105,13 @@ __global__ void k_wait(const uint64_t *flags, int slot, int G, const unsigned lo
     if (++spins > 4) { *err = 1; return; }
 #else
     __nanosleep(200);
-    if (++spins > 20000000ull) { *err = 1; return; }   // a few seconds
+    if (++spins > spin_limit) { *err = 1; return; }
 #endif
   }
+  if (*f == GQ_P2P_POISON) *err = 2;
+#ifndef GQ_EMULATE
+  __threadfence_system();
+#endif
 }
 
 }  // namespace
@@ -201,10 +216,10 @@ extern "C" int gq_p2p_bump_dev(gq_ctx *c, unsigned long long *epoch_dev, void *s
 }
 
 extern "C" int gq_p2p_signal_dev(gq_ctx *c, const uint64_t *const *flags, unsigned slot, unsigned G, unsigned me,
-                                 const unsigned long long *epoch, void *stream) {
+                                 const unsigned long long *epoch, const int *err_dev, void *stream) {
   GqPeers pr;
   if (!c || !flags || me >= G || fill_peers(&pr, flags, nullptr, G)) P2P_FAIL("bad argument");
-  GQ_LAUNCH(k_signal, dim3(1), dim3(32), pick(c, stream), pr, (int)slot, (int)G, (int)me, epoch);
+  GQ_LAUNCH(k_signal, dim3(1), dim3(32), pick(c, stream), pr, (int)slot, (int)G, (int)me, epoch, err_dev);
   c->launches++;
   P2P_CUDA(cudaGetLastError());
   return 0;
@@ -213,7 +228,14 @@ extern "C" int gq_p2p_signal_dev(gq_ctx *c, const uint64_t *const *flags, unsign
 extern "C" int gq_p2p_wait_dev(gq_ctx *c, const uint64_t *flags_local, unsigned slot, unsigned G,
                                const unsigned long long *epoch, int *err_dev, void *stream) {
   if (!c || !flags_local || !err_dev || G == 0 || G > GQ_P2P_MAX_RANKS) P2P_FAIL("bad argument");
-  GQ_LAUNCH(k_wait, dim3(1), dim3(32), pick(c, stream), flags_local, (int)slot, (int)G, epoch, err_dev);
+  // GPQHE_B200_P2P_TIMEOUT_MS: how long a rank waits for a peer (default 4000 ms; first use of a plan includes the
+  // peers' allocations and graph uploads).  Read when the launch is enqueued / captured.
+  unsigned long long limit = 20000000ull;
+  if (const char *e = getenv("GPQHE_B200_P2P_TIMEOUT_MS")) {
+    const long long ms = atoll(e);
+    if (ms > 0) limit = (unsigned long long)ms * 5000ull;      // 200 ns per poll
+  }
+  GQ_LAUNCH(k_wait, dim3(1), dim3(32), pick(c, stream), flags_local, (int)slot, (int)G, epoch, err_dev, limit);
   c->launches++;
   P2P_CUDA(cudaGetLastError());
   return 0;

@@ -21,6 +21,14 @@
   kernel<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__)
 #endif
 
+// dynamic shared memory of a kernel launched with a byte count
+#ifdef GQ_EMULATE
+#define GQ_DYN_SMEM(type, name) type *name = reinterpret_cast<type *>(::gq_emul::dyn_smem())
+#else
+#define GQ_DYN_SMEM(type, name) extern __shared__ __align__(16) unsigned char name##_raw_[]; \
+  type *name = reinterpret_cast<type *>(name##_raw_)
+#endif
+
 #define GQ_HD __host__ __device__ __forceinline__
 #define GQ_DEV __device__ __forceinline__
 

@@ -134,8 +134,7 @@ class ShardedHe:
         x = self._coef_to_limb(self._decompose([a0, a1, b0, b1], D1), D1)          # [4, D1l, n]
         self._ck(lib.gq_stage_ntt_dev(h, lo1, D1l, 4, x.data_ptr(), 0, None))
         y = self._empty(3, D1l, self.n)
-        self._ck(lib.gq_stage_tensor_dev(h, lo1, D1l, y.data_ptr(), x.data_ptr(), None))
-        self._ck(lib.gq_stage_ntt_dev(h, lo1, D1l, 3, y.data_ptr(), 1, None))
+        self._ck(lib.gq_stage_tensor_inv_dev(h, lo1, D1l, y.data_ptr(), x.data_ptr(), None))   # tensor + inverse NTT
         # hot loop B (he-mult.c:139-141)
         rh = self._limb_to_coef(y, D1)                                            # [3, D1, n_loc]
         d = self._empty(3, self.W, self.n_loc)
@@ -153,8 +152,7 @@ class ShardedHe:
         x = self._coef_to_limb(self._decompose([dpoly], D2), D2)                  # [1, D2l, n]
         self._ck(lib.gq_stage_ntt_dev(h, lo2, D2l, 1, x.data_ptr(), 0, None))
         y = self._empty(2, D2l, self.n)
-        self._ck(lib.gq_stage_mul_evk_dev(h, lo2, D2l, y.data_ptr(), x.data_ptr(), evk._h, None))
-        self._ck(lib.gq_stage_ntt_dev(h, lo2, D2l, 2, y.data_ptr(), 1, None))
+        self._ck(lib.gq_stage_mul_evk_inv_dev(h, lo2, D2l, y.data_ptr(), x.data_ptr(), evk._h, None))   # x evk + inverse NTT
         ch = self._limb_to_coef(y, D2)                                            # [2, D2, n_loc]
         c0, c1 = self._empty(self.W, self.n_loc), self._empty(self.W, self.n_loc)
         self._ck(lib.gq_stage_ks_epilogue_dev(h, l, ch.data_ptr(), add0.data_ptr() if add0 is not None else None,
@@ -263,8 +261,7 @@ class MulPlan:
         sh, lib, h = self.sh, self.sh._lib, self.sh._h
         self._unpack_c2l(0, self.xl)
         sh._ck(lib.gq_stage_ntt_dev(h, self.lo1, self.D1l, 4, self.xl.data_ptr(), 0, None))
-        sh._ck(lib.gq_stage_tensor_dev(h, self.lo1, self.D1l, self.yl.data_ptr(), self.xl.data_ptr(), None))
-        sh._ck(lib.gq_stage_ntt_dev(h, self.lo1, self.D1l, 3, self.yl.data_ptr(), 1, None))
+        sh._ck(lib.gq_stage_tensor_inv_dev(h, self.lo1, self.D1l, self.yl.data_ptr(), self.xl.data_ptr(), None))
         self._pack_l2c(1, self.yl)
 
     def _seg2(self):
@@ -280,17 +277,15 @@ class MulPlan:
         sh, lib, h = self.sh, self.sh._lib, self.sh._h
         self._unpack_c2l(2, self.x2l)
         sh._ck(lib.gq_stage_ntt_dev(h, self.lo2, self.D2l, 1, self.x2l.data_ptr(), 0, None))
-        sh._ck(lib.gq_stage_mul_evk_dev(h, self.lo2, self.D2l, self.y2l.data_ptr(), self.x2l.data_ptr(), self.rlk._h, None))
-        sh._ck(lib.gq_stage_ntt_dev(h, self.lo2, self.D2l, 2, self.y2l.data_ptr(), 1, None))
+        sh._ck(lib.gq_stage_mul_evk_inv_dev(h, self.lo2, self.D2l, self.y2l.data_ptr(), self.x2l.data_ptr(), self.rlk._h, None))
         self._pack_l2c(3, self.y2l)
 
     def _seg4(self):
         sh, lib, h = self.sh, self.sh._lib, self.sh._h
         self._unpack_l2c(3, self.ch, self.off2)
-        sh._ck(lib.gq_stage_ks_epilogue_dev(h, self.l, self.ch.data_ptr(), self.d[0].data_ptr(), self.d[1].data_ptr(),
-                                            self.out[0].data_ptr(), self.out[1].data_ptr(), sh.n_loc, None))
-        if self.rescale:
-            sh._ck(lib.gq_stage_rescale_dev(h, self.l, self.out[0].data_ptr(), self.out[1].data_ptr(), 1, sh.n_loc, None))
+        ks = lib.gq_stage_ks_epilogue_rs_dev if self.rescale else lib.gq_stage_ks_epilogue_dev     # he_rs rides in the epilogue
+        sh._ck(ks(h, self.l, self.ch.data_ptr(), self.d[0].data_ptr(), self.d[1].data_ptr(),
+                  self.out[0].data_ptr(), self.out[1].data_ptr(), sh.n_loc, None))
 
     def _capture(self):
         """record each segment once; must be called with the context's stream current"""
@@ -343,6 +338,7 @@ class P2PPlan:
         lay = self.layout(ctx, G, l)
         self.lay = lay
         self.slab = slabs[rank]
+        self._slabs, self._owned, self._mapped = list(slabs), None, False
         E = lambda *shape: torch.empty(shape, dtype=torch.int64, device=self.device)
         self.inp, self.out = E(4, self.W, self.nl), E(2, self.W, self.nl)
         self.xc, self.yl = E(4, self.D1, self.nl), E(3, max(self.D1l, 1), self.n)
@@ -388,12 +384,12 @@ class P2PPlan:
     def _c2l(self, src, P, D, dst, off, slot):
         lib, h = self._lib, self._h
         self._ck(lib.gq_p2p_scatter_c2l_dev(h, src.data_ptr(), P, D, self.nl, self.G, self.rank, dst, off, None))
-        self._ck(lib.gq_p2p_signal_dev(h, self.p_flags, slot, self.G, self.rank, self.epoch.data_ptr(), None))
+        self._ck(lib.gq_p2p_signal_dev(h, self.p_flags, slot, self.G, self.rank, self.epoch.data_ptr(), self.err.data_ptr(), None))
 
     def _l2c(self, src, P, Dl, D, dst, off, slot):
         lib, h = self._lib, self._h
         self._ck(lib.gq_p2p_scatter_l2c_dev(h, src.data_ptr(), P, Dl, D, self.nl, self.G, self.rank, dst, off, None))
-        self._ck(lib.gq_p2p_signal_dev(h, self.p_flags, slot, self.G, self.rank, self.epoch.data_ptr(), None))
+        self._ck(lib.gq_p2p_signal_dev(h, self.p_flags, slot, self.G, self.rank, self.epoch.data_ptr(), self.err.data_ptr(), None))
 
     def _wait(self, slot):
         self._ck(self._lib.gq_p2p_wait_dev(self._h, self._loc("flags"), slot, self.G, self.epoch.data_ptr(),
@@ -412,8 +408,7 @@ class P2PPlan:
             if self.D1l:
                 xl = self._loc("xl1")
                 self._ck(lib.gq_stage_ntt_dev(h, self.lo1, self.D1l, 4, xl, 0, None))
-                self._ck(lib.gq_stage_tensor_dev(h, self.lo1, self.D1l, self.yl.data_ptr(), xl, None))
-                self._ck(lib.gq_stage_ntt_dev(h, self.lo1, self.D1l, 3, self.yl.data_ptr(), 1, None))
+                self._ck(lib.gq_stage_tensor_inv_dev(h, self.lo1, self.D1l, self.yl.data_ptr(), xl, None))
             self._l2c(self.yl, 3, self.D1l, self.D1, self.p_rh, self.c_off1, 1)
         elif k == 2:
             self._wait(1)
@@ -427,25 +422,39 @@ class P2PPlan:
             if self.D2l:
                 xl = self._loc("xl2")
                 self._ck(lib.gq_stage_ntt_dev(h, self.lo2, self.D2l, 1, xl, 0, None))
-                self._ck(lib.gq_stage_mul_evk_dev(h, self.lo2, self.D2l, self.y2l.data_ptr(), xl, self.rlk._h, None))
-                self._ck(lib.gq_stage_ntt_dev(h, self.lo2, self.D2l, 2, self.y2l.data_ptr(), 1, None))
+                self._ck(lib.gq_stage_mul_evk_inv_dev(h, self.lo2, self.D2l, self.y2l.data_ptr(), xl, self.rlk._h, None))
             self._l2c(self.y2l, 2, self.D2l, self.D2, self.p_ch, self.c_off2, 3)
         else:
             self._wait(3)
-            self._ck(lib.gq_stage_ks_epilogue_dev(h, self.l, self._loc("ch"), self.d[0].data_ptr(),
-                                                  self.d[1].data_ptr(), self.out[0].data_ptr(),
-                                                  self.out[1].data_ptr(), nl, None))
-            if self.rescale:
-                self._ck(lib.gq_stage_rescale_dev(h, self.l, self.out[0].data_ptr(), self.out[1].data_ptr(), 1, nl, None))
+            ks = lib.gq_stage_ks_epilogue_rs_dev if self.rescale else lib.gq_stage_ks_epilogue_dev
+            self._ck(ks(h, self.l, self._loc("ch"), self.d[0].data_ptr(), self.d[1].data_ptr(),
+                        self.out[0].data_ptr(), self.out[1].data_ptr(), nl, None))
 
-    def run(self):
-        """one he_mul (+ he_rs): self.inp -> self.out (real multi-rank use; every rank calls it)"""
+    def run(self, check=True):
+        """one he_mul (+ he_rs): self.inp -> self.out (real multi-rank use; every rank calls it).
+        check=True waits for the op and raises if this rank, or any peer (poison epoch), timed out on an exchange:
+        the outputs are never handed out unchecked.  A caller that pipelines ops passes check=False and must call
+        failed() before it uses any output."""
         if self.graph is not None:
             self.graph.replay()
         else:
             for k in range(5):
                 self.seg(k)
+        if check and self.failed():
+            raise GpqheError("P2PPlan: a peer did not reach an exchange in time (GPQHE_B200_P2P_TIMEOUT_MS); "
+                             "the plan is poisoned on every rank and must be rebuilt")
         return self.out[0], self.out[1]
+
+    def close(self):
+        """unmap the peers' slabs and free this rank's (every rank must have finished using the plan)"""
+        lib, h = self.ctx._lib, self.ctx._h
+        owned = getattr(self, "_owned", None)
+        for s, p in enumerate(getattr(self, "_slabs", [])):
+            if p and p != owned and getattr(self, "_mapped", False):
+                lib.gq_p2p_close(h, C.c_void_p(p))
+        if owned:
+            lib.gq_p2p_free(h, C.c_void_p(owned))
+        self._owned, self._slabs, self.graph = None, [], None
 
     def capture(self):
         """record the whole op as one CUDA graph (call with the context's stream current, after a
@@ -481,7 +490,7 @@ class P2PPlan:
                 capi.check(ctx._lib, ctx._lib.gq_p2p_open(ctx._h, handles[s], C.byref(p)))
                 slabs.append(p.value)
         plan = cls(ctx, G, r, l, rlk, slabs, rescale, sh.device)
-        plan._owned = mine.value
+        plan._owned, plan._mapped = mine.value, True
         if G > 1:
             dist.barrier(group=sh.group)     # every slab is zeroed and mapped before anyone signals
         return plan
@@ -495,7 +504,10 @@ class P2PPlan:
             p, hd = C.c_void_p(), C.create_string_buffer(64)
             capi.check(ctx._lib, ctx._lib.gq_p2p_alloc(ctx._h, 8 * lay["words"], C.byref(p), hd))
             slabs.append(p.value)
-        return [cls(ctx, G, r, l, rlk, slabs, rescale, device) for r in range(G)]
+        plans = [cls(ctx, G, r, l, rlk, slabs, rescale, device) for r in range(G)]
+        for r, pl in enumerate(plans):
+            pl._owned = slabs[r]          # one address space: every virtual rank frees its own slab in close()
+        return plans
 
     @staticmethod
     def run_lockstep(plans):

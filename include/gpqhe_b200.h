@@ -26,6 +26,10 @@
  * (SURVEY 8b); the dropin shim turns a non-zero return into the same abort().
  * One context is bound to one device; calls on one context must be serialised
  * by the caller (the reference is single-threaded, process-global state).
+ * The scratch buffers of a context (and of each lane) are shared by all its calls: a non-NULL
+ * `stream` argument must be ordered after all work enqueued earlier on that context - pass the
+ * same stream every time, or make the new stream wait for the old one; independent operations
+ * that should overlap belong on different LANES (gq_ctx_set_lanes), which own their scratch.
  */
 #ifndef GPQHE_B200_H
 #define GPQHE_B200_H
@@ -279,17 +283,6 @@ int gq_he_subpt_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, const u
                     const uint64_t *a1, const uint64_t *m, void *stream);
 int gq_he_neg_dev(gq_ctx *ctx, unsigned l, uint64_t *c0, uint64_t *c1, void *stream);
 
-/* measured integer-pipe ceilings of this GPU (no reference counterpart; roofline denominators of the
-   NTT / CRT kernels): lazy Shoup butterflies per second with operands in registers, and raw
-   32x32+64 multiply-adds per second.  Runs two short kernels on the context's stream and waits. */
-int gq_bench_intpipe(gq_ctx *ctx, double *butterflies_per_s, double *madwide_per_s);
-/* measurement only (no reference counterpart, not on any product path): forward negacyclic NTT over 30-bit
-   primes on 32-bit words with the same two-kernel structure as the 64-bit transforms, nlimbs x npolys limb-polys
-   per launch, logn in 13..16.  Reports limb-NTTs per second and the number of mismatches of one transform against
-   a plain host implementation (the planned 31-bit-class internal RNS basis). */
-int gq_bench_ntt32(gq_ctx *ctx, unsigned logn, unsigned nlimbs, unsigned npolys, unsigned reps,
-                   double *limb_ntt_per_s, int *mismatches);
-
 /* ---- stage-level entry points (DEVICE pointers, enqueue only) ------------------------
  * One call = one stage of the pipelines above on a limb range [limb0, limb0+nlimbs) (NTT domain,
  * limb-polys of the full ring degree n) or on a slice of `ncoef` coefficients (big-integer domain:
@@ -311,6 +304,16 @@ int gq_stage_tensor_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, uint64_t *
                         const uint64_t *x_dev, void *stream);
 int gq_stage_mul_evk_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, uint64_t *y_dev,
                          const uint64_t *x_dev, const gq_evk *evk, void *stream);
+/* tensor / mul_evk followed by the inverse NTT of the same limb range, the pointwise products formed while the
+   inverse transform loads its tiles (one pass instead of two kernels + a round trip): y is in the coefficient
+   domain.  ks_epilogue_rs: ks_epilogue followed by he_rs on the slice (one kernel for power-of-two moduli). */
+int gq_stage_tensor_inv_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, uint64_t *y_dev,
+                            const uint64_t *x_dev, void *stream);
+int gq_stage_mul_evk_inv_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, uint64_t *y_dev,
+                             const uint64_t *x_dev, const gq_evk *evk, void *stream);
+int gq_stage_ks_epilogue_rs_dev(gq_ctx *ctx, unsigned l, const uint64_t *chat_dev, const uint64_t *add0_dev,
+                                const uint64_t *add1_dev, uint64_t *c0_dev, uint64_t *c1_dev, unsigned ncoef,
+                                void *stream);
 int gq_stage_reconstruct_dev(gq_ctx *ctx, unsigned D, unsigned l, unsigned npolys, const uint64_t *rhat_dev,
                              uint64_t *const *out_dev, unsigned ncoef, void *stream);
 int gq_stage_ks_epilogue_dev(gq_ctx *ctx, unsigned l, const uint64_t *chat_dev, const uint64_t *add0_dev,
@@ -325,7 +328,9 @@ int gq_stage_rescale_dev(gq_ctx *ctx, unsigned l, uint64_t *c0_dev, uint64_t *c1
  * coefficient; dst[s] is rank s's destination buffer as mapped in THIS process, off[G+1] the limb
  * ownership.  signal/wait: per-exchange epoch flags in the peers' slabs (slot < 8); the epoch is
  * read from device memory (bump increments it) so the launches can be replayed from a CUDA graph.
- * err_dev is set non-zero when a peer does not show up within a few seconds. */
+ * err_dev is set non-zero when a peer does not show up within GPQHE_B200_P2P_TIMEOUT_MS (default 4000) and is STICKY:
+ * a rank whose flag is set signals a poison epoch, so the failure reaches every rank's err_dev within the same op
+ * and every later wait returns at once.  A caller must read err_dev before it trusts an output. */
 int gq_p2p_alloc(gq_ctx *ctx, size_t bytes, void **ptr_dev, unsigned char handle[64]);
 int gq_p2p_open(gq_ctx *ctx, const unsigned char handle[64], void **peer_ptr_dev);
 int gq_p2p_close(gq_ctx *ctx, void *peer_ptr_dev);
@@ -337,7 +342,7 @@ int gq_p2p_scatter_l2c_dev(gq_ctx *ctx, const uint64_t *src_dev, unsigned P, uns
                            void *stream);
 int gq_p2p_bump_dev(gq_ctx *ctx, unsigned long long *epoch_dev, void *stream);
 int gq_p2p_signal_dev(gq_ctx *ctx, const uint64_t *const *flags, unsigned slot, unsigned G, unsigned me,
-                      const unsigned long long *epoch_dev, void *stream);
+                      const unsigned long long *epoch_dev, const int *err_dev, void *stream);
 int gq_p2p_wait_dev(gq_ctx *ctx, const uint64_t *flags_local_dev, unsigned slot, unsigned G,
                     const unsigned long long *epoch_dev, int *err_dev, void *stream);
 

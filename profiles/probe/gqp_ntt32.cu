@@ -1,4 +1,4 @@
-// gq_ntt32.cu - measurement only: the forward negacyclic NTT over 30-bit primes on 32-bit words.
+// gqp_ntt32.cu - MEASUREMENT ONLY (profiles/probe/libgqprobe.so, loaded by bench.py; not part of the product library): the forward negacyclic NTT over 30-bit primes on 32-bit words.
 //
 // Not on any product path.  DESIGN.md section 4 ("what ncu says is left") plans a 31-bit-class internal RNS
 // basis for the polynomial products: only exact integers cross the stage boundaries of he_mul / he_relin, so
@@ -11,12 +11,9 @@
 // Primes: the largest p < 2^30 with p == 1 (mod 2n) (4p < 2^32: Harvey butterflies with values in [0,4p)).
 // Twiddles: psi^brv(k) in the reference's order (src/precomp.c:255-263), plain form + Shoup companion
 // floor(w * 2^32 / p).  Butterfly: x <- x mod 2p; t = w*y - hi32(w'*y)*p in [0,2p); (x, y) <- (x + t, x - t + 2p).
-#include <string>
 #include <vector>
 
-#include "../../include/gpqhe_b200.h"
-#include "gq_arith.h"
-#include "gq_context.h"
+#include "gqp_common.h"
 
 namespace {
 
@@ -155,7 +152,7 @@ k_ntt32_fwd_strided(Tab32 tb, uint32_t *__restrict__ data, int nlimbs) {
   do {                                                                                  \
     cudaError_t e_ = (call);                                                            \
     if (e_ != cudaSuccess) {                                                            \
-      gq_set_error(std::string(__func__) + ": " #call " -> " + cudaGetErrorString(e_)); \
+      gqp_set_error(std::string(__func__) + ": " #call " -> " + cudaGetErrorString(e_)); \
       return 1;                                                                         \
     }                                                                                   \
   } while (0)
@@ -190,18 +187,19 @@ static unsigned brv(unsigned x, int bits) {
 // limb-NTTs per second of the forward transform on 30-bit primes, nlimbs x npolys limb-polys per launch;
 // *mismatches = differences of one device transform against the host implementation below plus failed
 // evaluation checks (the output at index j must be a(psi^(2*brv(j)+1)))
-extern "C" int gq_bench_ntt32(gq_ctx *c, unsigned logn, unsigned nlimbs, unsigned npolys, unsigned reps,
-                              double *limb_ntt_per_s, int *mismatches) {
-  if (!c || !limb_ntt_per_s || !mismatches || nlimbs == 0 || npolys == 0 || reps == 0) {
-    gq_set_error("gq_bench_ntt32: bad argument"); return 1;
+extern "C" GQP_EXPORT int gqp_bench_ntt32(int device, unsigned logn, unsigned nlimbs, unsigned npolys, unsigned reps,
+                                          double *limb_ntt_per_s, int *mismatches) {
+  cudaStream_t stream = 0;
+  if (!limb_ntt_per_s || !mismatches || nlimbs == 0 || npolys == 0 || reps == 0) {
+    gqp_set_error("gqp_bench_ntt32: bad argument"); return 1;
   }
-  if (logn < 13 || logn > 16) { gq_set_error("gq_bench_ntt32: logn must be 13..16 (two-kernel transform)"); return 1; }
-  N32_CUDA(cudaSetDevice(c->device));
+  if (logn < 13 || logn > 16) { gqp_set_error("gqp_bench_ntt32: logn must be 13..16 (two-kernel transform)"); return 1; }
+  N32_CUDA(cudaSetDevice(device));
   const unsigned n = 1u << logn, two_n = 2 * n;
   std::vector<uint32_t> primes;
   for (uint32_t cand = ((1u << 30) - 1) / two_n * two_n + 1; primes.size() < nlimbs && cand > two_n; cand -= two_n)
     if (cand < (1u << 30) && is_prime32(cand)) primes.push_back(cand);
-  if (primes.size() < nlimbs) { gq_set_error("gq_bench_ntt32: not enough 30-bit primes for this ring"); return 1; }
+  if (primes.size() < nlimbs) { gqp_set_error("gqp_bench_ntt32: not enough 30-bit primes for this ring"); return 1; }
   std::vector<Tw32> tw((size_t)nlimbs * n);
   std::vector<uint32_t> psis(nlimbs);
   for (unsigned d = 0; d < nlimbs; d++) {
@@ -211,7 +209,7 @@ extern "C" int gq_bench_ntt32(gq_ctx *c, unsigned logn, unsigned nlimbs, unsigne
       const uint32_t y = powm32(x, (p - 1) / two_n, p);
       if (powm32(y, n, p) == p - 1) psi = y;           // order exactly 2n
     }
-    if (!psi) { gq_set_error("gq_bench_ntt32: no primitive root found"); return 1; }
+    if (!psi) { gqp_set_error("gqp_bench_ntt32: no primitive root found"); return 1; }
     psis[d] = psi;
     std::vector<uint32_t> pw(n);
     uint64_t v = 1;
@@ -241,16 +239,15 @@ extern "C" int gq_bench_ntt32(gq_ctx *c, unsigned logn, unsigned nlimbs, unsigne
   const dim3 gt(n >> 12, M), gs(((n >> sa) + 255) / 256, M);
   auto run = [&]() {
     switch (sa) {
-      case 1: GQ_LAUNCH(k_ntt32_fwd_strided<1>, gs, dim3(256), c->stream, tb, d_data, (int)nlimbs); break;
-      case 2: GQ_LAUNCH(k_ntt32_fwd_strided<2>, gs, dim3(256), c->stream, tb, d_data, (int)nlimbs); break;
-      case 3: GQ_LAUNCH(k_ntt32_fwd_strided<3>, gs, dim3(256), c->stream, tb, d_data, (int)nlimbs); break;
-      default: GQ_LAUNCH(k_ntt32_fwd_strided<4>, gs, dim3(256), c->stream, tb, d_data, (int)nlimbs); break;
+      case 1: GQ_LAUNCH(k_ntt32_fwd_strided<1>, gs, dim3(256), stream, tb, d_data, (int)nlimbs); break;
+      case 2: GQ_LAUNCH(k_ntt32_fwd_strided<2>, gs, dim3(256), stream, tb, d_data, (int)nlimbs); break;
+      case 3: GQ_LAUNCH(k_ntt32_fwd_strided<3>, gs, dim3(256), stream, tb, d_data, (int)nlimbs); break;
+      default: GQ_LAUNCH(k_ntt32_fwd_strided<4>, gs, dim3(256), stream, tb, d_data, (int)nlimbs); break;
     }
-    GQ_LAUNCH(k_ntt32_fwd_tile, gt, dim3(512), c->stream, tb, d_data, (int)nlimbs);
-    c->launches += 2;
+    GQ_LAUNCH(k_ntt32_fwd_tile, gt, dim3(512), stream, tb, d_data, (int)nlimbs);
   };
   run();
-  N32_CUDA(cudaStreamSynchronize(c->stream));
+  N32_CUDA(cudaStreamSynchronize(stream));
   // check limb-poly 0 of the last limb against a plain host transform and against direct evaluation
   int bad = 0;
   {
@@ -280,9 +277,9 @@ extern "C" int gq_bench_ntt32(gq_ctx *c, unsigned logn, unsigned nlimbs, unsigne
   cudaEvent_t e0, e1;
   N32_CUDA(cudaEventCreate(&e0));
   N32_CUDA(cudaEventCreate(&e1));
-  N32_CUDA(cudaEventRecord(e0, c->stream));
+  N32_CUDA(cudaEventRecord(e0, stream));
   for (unsigned r = 0; r < reps; r++) run();      // transforms of transforms: values stay below p, timing is data independent
-  N32_CUDA(cudaEventRecord(e1, c->stream));
+  N32_CUDA(cudaEventRecord(e1, stream));
   N32_CUDA(cudaEventSynchronize(e1));
   float ms = 0.f;
   N32_CUDA(cudaEventElapsedTime(&ms, e0, e1));

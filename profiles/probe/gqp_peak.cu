@@ -1,4 +1,5 @@
-// gq_peak.cu - measured integer-pipe ceilings for the roofline of the NTT / CRT kernels (SURVEY 8d:
+// gqp_peak.cu - MEASUREMENT ONLY (profiles/probe/libgqprobe.so, loaded by bench.py; not part of the product library).
+// Measured integer-pipe ceilings for the roofline of the NTT / CRT kernels (SURVEY 8d:
 // "measure the IMAD peak on the box with a dependent-free IMAD microbenchmark").
 //   k_peak_butterfly : the lazy Harvey butterfly of gq_ntt_lazy.cu (one Shoup multiplication by a
 //                      fixed twiddle + add / sub), operands in registers, 4 independent chains per
@@ -6,11 +7,7 @@
 //   k_peak_madwide   : dependent-free 32x32+64 multiply-adds (IMAD.WIDE.U32), the raw multiplier rate.
 // Both report operations per second over the whole GPU; bench.py divides what the NTT kernels achieve
 // by the first one.
-#include <string>
-
-#include "../../include/gpqhe_b200.h"
-#include "gq_arith.h"
-#include "gq_context.h"
+#include "gqp_common.h"
 
 namespace {
 
@@ -63,18 +60,19 @@ k_peak_madwide(uint64_t *sink, uint32_t m, int iters) {
   do {                                                                                  \
     cudaError_t e_ = (call);                                                            \
     if (e_ != cudaSuccess) {                                                            \
-      gq_set_error(std::string(__func__) + ": " #call " -> " + cudaGetErrorString(e_)); \
+      gqp_set_error(std::string(__func__) + ": " #call " -> " + cudaGetErrorString(e_)); \
       return 1;                                                                         \
     }                                                                                   \
   } while (0)
 
-extern "C" int gq_bench_intpipe(gq_ctx *c, double *butterflies_per_s, double *madwide_per_s) {
-  if (!c || !butterflies_per_s || !madwide_per_s) { gq_set_error("gq_bench_intpipe: null argument"); return 1; }
-  if (c->primes.empty()) { gq_set_error("gq_bench_intpipe: context has no primes"); return 1; }
-  PK_CUDA(cudaSetDevice(c->device));
+// p: a prime below 2^60, w: any residue, wsh = floor(w * 2^64 / p)
+extern "C" GQP_EXPORT int gqp_bench_intpipe(int device, uint64_t p, uint64_t w, uint64_t wsh, double *butterflies_per_s,
+                                            double *madwide_per_s) {
+  if (!butterflies_per_s || !madwide_per_s || p < 3) { gqp_set_error("gqp_bench_intpipe: bad argument"); return 1; }
+  PK_CUDA(cudaSetDevice(device));
   uint64_t *sink = nullptr;
   PK_CUDA(cudaMalloc(&sink, 8));
-  const uint64_t p = c->primes[0].p, w = c->primes[0].ninv, wsh = c->primes[0].ninv_sh;
+  cudaStream_t stream = 0;
   const int blocks = GQ_NUM_SMS * 8, threads = 256;
   cudaEvent_t e0, e1;
   PK_CUDA(cudaEventCreate(&e0));
@@ -85,22 +83,21 @@ extern "C" int gq_bench_intpipe(gq_ctx *c, double *butterflies_per_s, double *ma
   iters = 2;
 #endif
   for (int rep = 0; rep < 2; rep++) {   // first pass warms up
-    PK_CUDA(cudaEventRecord(e0, c->stream));
-    GQ_LAUNCH(k_peak_butterfly, dim3(blocks), dim3(threads), c->stream, sink, p, w, wsh, iters);
-    PK_CUDA(cudaEventRecord(e1, c->stream));
+    PK_CUDA(cudaEventRecord(e0, stream));
+    GQ_LAUNCH(k_peak_butterfly, dim3(blocks), dim3(threads), stream, sink, p, w, wsh, iters);
+    PK_CUDA(cudaEventRecord(e1, stream));
     PK_CUDA(cudaEventSynchronize(e1));
     PK_CUDA(cudaEventElapsedTime(&ms, e0, e1));
   }
   *butterflies_per_s = (double)blocks * threads * 4.0 * iters / ((ms > 0.f ? ms : 1e-3) * 1e-3);
   for (int rep = 0; rep < 2; rep++) {
-    PK_CUDA(cudaEventRecord(e0, c->stream));
-    GQ_LAUNCH(k_peak_madwide, dim3(blocks), dim3(threads), c->stream, sink, 0x9E3779B1u, iters * 4);
-    PK_CUDA(cudaEventRecord(e1, c->stream));
+    PK_CUDA(cudaEventRecord(e0, stream));
+    GQ_LAUNCH(k_peak_madwide, dim3(blocks), dim3(threads), stream, sink, 0x9E3779B1u, iters * 4);
+    PK_CUDA(cudaEventRecord(e1, stream));
     PK_CUDA(cudaEventSynchronize(e1));
     PK_CUDA(cudaEventElapsedTime(&ms, e0, e1));
   }
   *madwide_per_s = (double)blocks * threads * 8.0 * iters * 4 / ((ms > 0.f ? ms : 1e-3) * 1e-3);
-  c->launches += 4;
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   cudaFree(sink);

@@ -1,0 +1,43 @@
+#!/usr/bin/env python
+"""One he_mul+he_rs at N=2^16 for ncu: 3 warm-up ops, then ONE op between cudaProfilerStart/Stop
+(ncu --profile-from-start off ... python profiles/tools/one_op.py [--rot] [--gemv])."""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+import gpqhe_b200 as g  # noqa: E402
+
+ctx = g.HeContext(bench.LOGN, 1 << bench.LOGQ, bench.SLOTS, 1 << bench.LOGDELTA, device=0)
+lib, h = ctx._lib, ctx._h
+n, W, L = ctx.n, ctx.W, ctx.L
+rng = np.random.default_rng(1)
+evk = ctx.genevk(bench.synth_evk(rng, ctx.primes, n, ctx.dimevk), bench.synth_evk(rng, ctx.primes, n, ctx.dimevk))
+dev = torch.device("cuda", 0)
+inp = torch.from_numpy(np.stack([bench.synth_ct(rng, n, W, bench.LOGQ) for _ in range(4)]).view(np.int64)).to(dev)
+out = torch.empty((2, W, n), dtype=torch.int64, device=dev)
+poly = W * n * 8
+
+
+def op():
+    b = inp.data_ptr()
+    if "--rot" in sys.argv:
+        rc = lib.gq_he_rot_dev(h, L, 1, b, b + poly, evk._h, None)
+    else:
+        rc = lib.gq_he_mul_rs_dev(h, L, out.data_ptr(), out.data_ptr() + poly, b, b + poly, b + 2 * poly, b + 3 * poly, evk._h, None)
+    assert rc == 0, lib.gq_last_error()
+
+
+for _ in range(3):
+    op()
+ctx.sync()
+torch.cuda.profiler.start()
+op()
+ctx.sync()
+torch.cuda.profiler.stop()
+print("one_op done, launches so far:", ctx.launch_count)
+ctx.close()

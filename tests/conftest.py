@@ -20,7 +20,7 @@ def pytest_configure(config):
 def emul_lib():
     """Library sources compiled against the fibre-based CUDA stand-in (tests/emul):
     test infrastructure for the CPU tier, never loaded by the package itself."""
-    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "tests", "emul"), "-j8"])
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "tests", "emul"), "-j8", "all"])
     return EMUL_LIB
 
 

@@ -51,6 +51,24 @@ uint64_t exchange(uint64_t v, unsigned src) {
   return r;
 }
 
+static std::vector<uint32_t> g_wide;
+static std::vector<char> g_dyn;
+void *dyn_smem() { return g_dyn.data(); }
+void launch_dyn(dim3 grid, dim3 block, size_t bytes, const std::function<void()> &body) {
+  if (g_dyn.size() < bytes + 16) g_dyn.resize(bytes + 16);
+  launch(grid, block, body);
+}
+void warp_gather(const uint32_t *mine, int nwords, uint32_t *all) {
+  const unsigned tid = linear_tid(), nt = blockDim.x * blockDim.y * blockDim.z;
+  if (g_wide.size() < (size_t)nt * 8) g_wide.resize((size_t)nt * 8 + 256);
+  for (int k = 0; k < nwords; k++) g_wide[(size_t)tid * 8 + k] = mine[k];
+  yield_barrier();
+  const unsigned w0 = tid & ~31u;
+  for (unsigned l = 0; l < 32; l++)
+    for (int k = 0; k < nwords; k++) all[l * nwords + k] = (w0 + l < nt) ? g_wide[(size_t)(w0 + l) * 8 + k] : 0;
+  yield_barrier();
+}
+
 void launch(dim3 grid, dim3 block, const std::function<void()> &body) {
   g_launches++;
   const unsigned nt = block.x * block.y * block.z;

@@ -36,6 +36,12 @@ static const int warpSize = 32;
 
 namespace gq_emul {
 void launch(dim3 grid, dim3 block, const std::function<void()> &body);
+// launch with `bytes` of dynamic shared memory, reachable through dyn_smem() (GQ_DYN_SMEM in gq_platform.h)
+void launch_dyn(dim3 grid, dim3 block, size_t bytes, const std::function<void()> &body);
+void *dyn_smem();
+// warp-wide all-gather of `nwords` 32-bit words per lane: all[lane][0..nwords) for the 32 lanes of the caller's
+// warp (every lane of the warp must call it); building block of the tensor-core emulation below
+void warp_gather(const uint32_t *mine, int nwords, uint32_t *all);
 void yield_barrier();                 // __syncthreads
 uint64_t exchange(uint64_t v, unsigned src_lane_in_block);   // shuffle helper
 unsigned linear_tid();
@@ -78,6 +84,26 @@ template <typename T> static inline T __shfl_sync(unsigned, T v, int srclane) {
   unsigned tid = gq_emul::linear_tid();
   raw = gq_emul::exchange(raw, (tid & ~31u) | ((unsigned)srclane & 31u));
   T r; std::memcpy(&r, &raw, sizeof(T)); return r;
+}
+
+// mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 (PTX ISA fragment layouts): g = lane / 4, t = lane % 4
+//   A: a0..a3 = rows (g, g+8, g, g+8) x k-bytes (4t.., 4t.., 16+4t.., 16+4t..);  B: b0, b1 = k-bytes (4t.., 16+4t..) x col g
+//   C: c0, c1 = row g, cols 2t, 2t+1;  c2, c3 = row g+8
+static inline void gq_emul_mma_u8(int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  uint32_t mine[6] = {a[0], a[1], a[2], a[3], b0, b1}, all[32][6];
+  gq_emul::warp_gather(mine, 6, &all[0][0]);
+  const unsigned lane = gq_emul::linear_tid() & 31u, g = lane >> 2, t = lane & 3u;
+  for (int e = 0; e < 4; e++) {
+    const unsigned row = g + ((e & 2) ? 8 : 0), col = 2 * t + (e & 1);
+    long long acc = c[e];
+    for (unsigned k = 0; k < 32; k++) {
+      const unsigned tk = (k & 15) >> 2, byte = k & 3;
+      const uint32_t ar = all[(row & 7) * 4 + tk][(row >= 8 ? 1 : 0) + (k >= 16 ? 2 : 0)];
+      const uint32_t br = all[col * 4 + tk][k >= 16 ? 5 : 4];
+      acc += (long long)((ar >> (8 * byte)) & 0xff) * (long long)((br >> (8 * byte)) & 0xff);
+    }
+    c[e] = (int)acc;
+  }
 }
 
 // ---------------------------------------------------------------- fake runtime

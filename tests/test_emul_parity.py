@@ -135,19 +135,39 @@ def test_lazy_ntt_vs_exact(emul_lib, logn, logq):
     pc.check_lazy_ntt_vs_exact(emul_lib, logn, 1 << logq)
 
 
+def _probe(path):
+    import ctypes as C
+    lib = C.CDLL(path)
+    lib.gqp_last_error.restype = C.c_char_p
+    return lib
+
+
 @pytest.mark.parametrize("logn,nlimbs,npolys", [(13, 2, 1), (14, 3, 2), (16, 2, 1)])
 def test_ntt32_probe_matches_host(emul_lib, logn, nlimbs, npolys):
-    """gq_ntt32.cu (measurement-only 32-bit transform): device output == plain host transform == direct
-    evaluation at psi^(2 brv(j) + 1)"""
+    """profiles/probe/gqp_ntt32.cu (measurement-only 32-bit transform): device output == plain host transform ==
+    direct evaluation at psi^(2 brv(j) + 1)"""
     import ctypes as C
-    ctx = g.HeContext(8, 1 << 120, lib_path=emul_lib, logqub=120)
-    try:
-        rate, bad = C.c_double(0), C.c_int(-1)
-        assert ctx._lib.gq_bench_ntt32(ctx._h, logn, nlimbs, npolys, 1, C.byref(rate), C.byref(bad)) == 0
-        assert bad.value == 0 and rate.value > 0
-        assert ctx._lib.gq_bench_ntt32(ctx._h, 12, 1, 1, 1, C.byref(rate), C.byref(bad)) != 0   # outside 13..16
-    finally:
-        ctx.close()
+    import os
+    lib = _probe(os.path.join(os.path.dirname(emul_lib), "libgqprobe_emul.so"))
+    rate, bad = C.c_double(0), C.c_int(-1)
+    assert lib.gqp_bench_ntt32(0, logn, nlimbs, npolys, 1, C.byref(rate), C.byref(bad)) == 0
+    assert bad.value == 0 and rate.value > 0
+    assert lib.gqp_bench_ntt32(0, 12, 1, 1, 1, C.byref(rate), C.byref(bad)) != 0   # outside 13..16
+
+
+@pytest.mark.parametrize("logn,D", [(6, 8), (7, 4)])
+def test_imma_decompose_probe_matches_host(emul_lib, logn, D):
+    """profiles/probe/gqp_imma.cu (measurement only): rns_decompose as a u8 tensor-core contraction with thread-local
+    byte-column recombination, under the emulated mma.sync fragment layouts, against plain modular reduction"""
+    import ctypes as C
+    import os
+    from oracle import pyoracle as o
+    lib = _probe(os.path.join(os.path.dirname(emul_lib), "libgqprobe_emul.so"))
+    oc = o.Ctx(logn, 1 << 438, 4, 1 << 50, logqub=438)
+    pr = (C.c_uint64 * D)(*oc.primes[:D])
+    rate, ms, bad = C.c_double(0), C.c_double(0), C.c_int(-1)
+    assert lib.gqp_bench_imma_decompose(0, logn, D, pr, 1, C.byref(rate), C.byref(ms), C.byref(bad)) == 0, lib.gqp_last_error()
+    assert bad.value == 0
 
 
 @pytest.mark.parametrize("logn,q,Delta,n1,n2,lanes", [(5, 1 << 438, 1 << 50, 2, 2, 1), (4, 1 << 438, 1 << 50, 2, 1, 3)])

@@ -130,17 +130,36 @@ def test_lazy_ntt_vs_exact(real_lib, logn, logq):
                                limbs=(0, 5, 23) if logq == 438 else None)
 
 
-@pytest.mark.parametrize("logn", [13, 16])
-def test_ntt32_probe_matches_host(real_lib, logn):
+def _probe():
     import ctypes as C
-    import gpqhe_b200 as g
-    ctx = g.HeContext(8, 1 << 120, lib_path=real_lib, logqub=120)
-    try:
-        rate, bad = C.c_double(0), C.c_int(-1)
-        assert ctx._lib.gq_bench_ntt32(ctx._h, logn, 30, 2, 2, C.byref(rate), C.byref(bad)) == 0
-        assert bad.value == 0 and rate.value > 0
-    finally:
-        ctx.close()
+    import os
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "probe", "libgqprobe.so")
+    if not os.path.exists(path):
+        pytest.skip("profiles/probe/libgqprobe.so not built")
+    lib = C.CDLL(path)
+    lib.gqp_last_error.restype = C.c_char_p
+    return lib
+
+
+@pytest.mark.parametrize("logn", [13, 16])
+def test_ntt32_probe_matches_host(logn):
+    import ctypes as C
+    lib = _probe()
+    rate, bad = C.c_double(0), C.c_int(-1)
+    assert lib.gqp_bench_ntt32(0, logn, 30, 2, 2, C.byref(rate), C.byref(bad)) == 0, lib.gqp_last_error()
+    assert bad.value == 0 and rate.value > 0
+
+
+def test_imma_decompose_probe_matches_host():
+    """measurement-only tensor-core decomposition prototype at the op's shape: every residue it is checked on equals
+    the plain modular reduction"""
+    import ctypes as C
+    lib = _probe()
+    oc = o.Ctx(16, 1 << 438, 16, 1 << 50)
+    pr = (C.c_uint64 * 16)(*oc.primes[:16])
+    rate, ms, bad = C.c_double(0), C.c_double(0), C.c_int(-1)
+    assert lib.gqp_bench_imma_decompose(0, 16, 16, pr, 3, C.byref(rate), C.byref(ms), C.byref(bad)) == 0, lib.gqp_last_error()
+    assert bad.value == 0 and rate.value > 0
 
 
 @pytest.mark.parametrize("logn", [16, 14])

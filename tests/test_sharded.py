@@ -144,6 +144,8 @@ def _loopback_case(lib_path, logn, q, Delta, logqub, G, device):
         ctx.sync()
         assert not any(pl.failed() for pl in plans), "a flag wait timed out"
         got = [g.big_to_ints(torch.cat([pl.out[k] for pl in plans], dim=1).cpu().numpy().view(np.uint64)) for k in range(2)]
+        for pl in plans:
+            pl.close()
     e = o.he_rs(oc, o.he_mul(oc, {"l": l, "c0": polys[0], "c1": polys[1]}, {"l": l, "c0": polys[2], "c1": polys[3]}, (p0, p1)))
     ctx.close()
     assert got == [e["c0"], e["c1"]]
@@ -154,6 +156,41 @@ def test_p2p_plan_loopback_emulated(emul_lib, G, logn, logq, logDelta):
     if (1 << logn) % G:
         pytest.skip("ring degree not divisible")
     _loopback_case(emul_lib, logn, 1 << logq, 1 << logDelta, logq, G, "cpu")
+
+
+def test_p2p_timeout_is_sticky_and_poisons_peers(emul_lib):
+    """A rank whose wait timed out (error flag set) must not let its peers consume its half-written slab: it signals
+    a poison epoch, the peers' waits turn it into their own error flag, and run(check=True) raises on every rank."""
+    import gpqhe_b200 as g
+    from gpqhe_b200.sharded import P2PPlan
+    ctx = g.HeContext(6, 1 << 120, 4, 1 << 40, lib_path=emul_lib, logqub=120)
+    try:
+        n = ctx.n
+        nr = np.random.default_rng(3)
+        key = lambda: np.concatenate([nr.integers(0, ctx.primes[d], size=n, dtype=np.uint64) for d in range(ctx.dimevk)])
+        evk = ctx.genevk(key(), key())
+        plans = P2PPlan.loopback(ctx, 2, ctx.L, evk, rescale=True, device="cpu")
+        for pl in plans:
+            pl.inp.zero_()
+        P2PPlan.run_lockstep(plans)
+        assert not any(pl.failed() for pl in plans)
+        # rank 1 skips its producer step of the next op: rank 0's wait times out (bounded spin) ...
+        plans[0].seg(0)
+        plans[0].seg(1)
+        assert plans[0].failed() and not plans[1].failed()
+        # ... and from then on rank 0 signals poison: rank 1 fails too instead of reading rank 0's stale slab
+        plans[1].seg(0)
+        plans[1].seg(1)
+        plans[0].seg(2)                  # signals slot 2 with the poison value
+        plans[1].seg(2)
+        plans[1].seg(3)                  # waits on slot 2
+        assert plans[1].failed()
+        with pytest.raises(g.GpqheError):
+            plans[1].run()
+        for pl in plans:
+            pl.close()
+    finally:
+        ctx.close()
 
 
 @pytest.mark.gpu
