@@ -112,6 +112,7 @@ SIGNATURES = {
     "gq_stage_mul_evk_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp]),
     "gq_stage_mul_evk_inv_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, vp]),
     "gq_stage_reconstruct_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.POINTER(vp), C.c_uint, vp]),
+    "gq_stage_reconstruct_noalloc_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.POINTER(vp), C.c_uint, vp]),
     "gq_stage_ks_epilogue_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, vp]),
     "gq_stage_ks_epilogue_rs_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, vp]),
     "gq_stage_rescale_dev": (C.c_int, [vp, C.c_uint, vp, vp, C.c_int, C.c_uint, vp]),

@@ -316,6 +316,16 @@ int gq_stage_ks_epilogue_rs_dev(gq_ctx *ctx, unsigned l, const uint64_t *chat_de
                                 void *stream);
 int gq_stage_reconstruct_dev(gq_ctx *ctx, unsigned D, unsigned l, unsigned npolys, const uint64_t *rhat_dev,
                              uint64_t *const *out_dev, unsigned ncoef, void *stream);
+/* gq_stage_reconstruct_dev for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  It has NO COUNTERPART IN THE REFERENCE.
+ * Same kernels, same arguments, bit-identical results; the fix-list scratch of the fast CRT kernels comes
+ * from a file-scope __device__ array of the library (gq_noalloc.cu: 1 MiB + 16 B per GPU, held until the process
+ * exits) instead of the context's cudaMalloc'd buffer, and the call invokes no cudaMalloc / cudaFree / allocating
+ * routine.  Limit: npolys * ncoef <= 262 144 (4 polynomials of 65 536 coefficients); larger calls fail with an
+ * error.  The array is shared by every call and context on a device and keeps the last call's contents (its header is
+ * cleared on `stream` at the start of each call): calls that overlap on the GPU race - order them on one stream. */
+int gq_stage_reconstruct_noalloc_dev(gq_ctx *ctx, unsigned D, unsigned l, unsigned npolys, const uint64_t *rhat_dev,
+                                     uint64_t *const *out_dev, unsigned ncoef, void *stream);
 int gq_stage_ks_epilogue_dev(gq_ctx *ctx, unsigned l, const uint64_t *chat_dev, const uint64_t *add0_dev,
                              const uint64_t *add1_dev, uint64_t *c0_dev, uint64_t *c1_dev, unsigned ncoef,
                              void *stream);

@@ -141,6 +141,10 @@ cudaError_t cudaEventRecord(cudaEvent_t e, cudaStream_t s);
 cudaError_t cudaEventSynchronize(cudaEvent_t e);
 cudaError_t cudaEventElapsedTime(float *ms, cudaEvent_t a, cudaEvent_t b);
 cudaError_t cudaStreamWaitEvent(cudaStream_t s, cudaEvent_t e, unsigned flags);
+// a __device__ variable is a plain host object here: its "device address" is its address
+template <typename T> static inline cudaError_t cudaGetSymbolAddress(void **p, T &symbol) {
+  *p = (void *)&symbol; return cudaSuccess;
+}
 template <typename T> static inline cudaError_t cudaMalloc(T **p, size_t n) {
   return cudaMalloc((void **)p, n);
 }
