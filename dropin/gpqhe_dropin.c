@@ -22,7 +22,10 @@
  *   he_rlsin                             src/he-bootstrap.c:444-475 (device-resident composition)
  *   polyctx_init/exit, hectx_init/exit   src/precomp.c:328-452 (wrappers: the reference
  *                                        builds its tables, we mirror them on the device)
- *   he_free_evk                          src/he-mem.c (wrapper: drops the device copy)
+ *   he_free_evk, he_genrlk/ck/rk         src/he-mem.c, src/he-kem.c (wrappers: drop the device copy of the key)
+ *   he_enc_pk/sk, he_dec, he_copy_ct,    src/he-encrypt.c, src/he-mem.c (wrappers: ciphertexts live in device
+ *   poly_mpi_free                        shadows between calls; these are the points where the host MPIs are
+ *                                        written, read, copied or freed)
  *
  * Signatures, metadata updates (l, nu, B), aliasing rules and the stderr+abort() error
  * convention are the reference's.  Big integers cross the boundary as word-major
@@ -61,6 +64,16 @@ struct evk_slot {
   const uint64_t *p0, *p1;  /* host addresses the key was uploaded from */
   uint64_t print;           /* sampled content fingerprint */
   gq_evk *dev;
+  unsigned long long used;  /* last use (LRU eviction) */
+};
+
+/* device shadow of one he_ct_t, keyed by ct->c0.coeffs (see "device-resident ciphertexts" below) */
+struct shadow {
+  const void *key;
+  uint64_t *dev;            /* c0 at dev, c1 at dev + W*n; NULL until first needed */
+  unsigned char dev_ok;     /* the device copy is current */
+  unsigned char host_ok;    /* the gcry_mpi objects are current */
+  unsigned char tomb;       /* deleted slot of the open-addressing table */
 };
 
 static struct {
@@ -74,6 +87,16 @@ static struct {
   unsigned nevk, capevk;
   int fast_mpi;             /* direct limb access verified against the public API */
   unsigned long long marshal_in, marshal_out;
+  unsigned long long evk_clock;
+  struct shadow *sh;        /* open-addressing table, power-of-two capacity */
+  size_t shcap, shused;
+  uint64_t **pool;          /* free 2-poly device buffers */
+  unsigned npool, cappool;
+  uint64_t *dscratch;       /* device scratch for plaintexts / encoded diagonals */
+  size_t dscratch_words;
+  uint64_t *ring;           /* pinned staging ring of the asynchronous uploads / downloads */
+  unsigned ring_pos;
+  unsigned long long ct_uploads, ct_downloads, shadow_allocs;
 } G;
 
 static void die(const char *where)
@@ -89,6 +112,7 @@ static void die(const char *where)
  * against the public API on this very library; otherwise the gcry_mpi_print/scan path runs. */
 struct mpi_view { int alloced; int nlimbs; int sign; unsigned int flags; unsigned long *d; };
 
+static void words_to_mpi(MPI a, const uint64_t *in, size_t stride, unsigned W);
 static void mpi_layout_selftest(void)
 {
   static const unsigned char be[24] = {0x01, 0x23, 0x45, 0x67, 0x89, 0xab, 0xcd, 0xef, 0xfe, 0xdc, 0xba, 0x98,
@@ -106,6 +130,29 @@ static void mpi_layout_selftest(void)
   ok = ok && v->nlimbs == 0;
   gcry_mpi_release(a);
   G.fast_mpi = ok;
+  if (!ok) return;
+  /* the WRITE path too: store values through the limb view and read them back with the public API */
+  static const uint64_t vals[3][3] = {{0x1122334455667788ull, 0x99aabbccddeeff00ull, 0x0fedcba987654321ull},
+                                      {5, 0, 0}, {0, 0, 0}};
+  for (int t = 0; t < 6 && G.fast_mpi; t++) {
+    const int neg = t & 1;
+    uint64_t w[4] = {vals[t / 2][0], vals[t / 2][1], vals[t / 2][2], 0};
+    if (neg) { uint64_t c = 1; for (int i = 0; i < 4; i++) { uint64_t x = ~w[i] + c; c = (c && x == 0); w[i] = x; } }
+    MPI b = gcry_mpi_new(320);
+    gcry_mpi_set_ui(b, 1);
+    gcry_mpi_lshift(b, b, 300);            /* make libgcrypt allocate the limbs */
+    words_to_mpi(b, w, 1, 4);
+    unsigned char buf[64];
+    size_t len = 0;
+    int good = gcry_mpi_print(GCRYMPI_FMT_USG, buf, sizeof buf, &len, b) == 0;
+    uint64_t back[4] = {0, 0, 0, 0};
+    for (size_t k = 0; good && k < len; k++) back[k / 8] |= (uint64_t)buf[len - 1 - k] << (8 * (k % 8));
+    const int zero = !vals[t / 2][0] && !vals[t / 2][1] && !vals[t / 2][2];
+    good = good && back[0] == vals[t / 2][0] && back[1] == vals[t / 2][1] && back[2] == vals[t / 2][2] &&
+           (gcry_mpi_is_neg(b) != 0) == (neg && !zero);
+    gcry_mpi_release(b);
+    if (!good) G.fast_mpi = 0;
+  }
 }
 
 /* a -> W little-endian words, two's complement, written with stride n (word-major poly) */
@@ -279,8 +326,10 @@ static void poly_out(poly_mpi_t *r, const uint64_t *src, unsigned W)
 }
 
 /* ------------------------------------------------------------------- context mirror */
+static void shadows_drop_all(void);
 static void ctx_drop(void)
 {
+  shadows_drop_all();
   for (unsigned k = 0; k < G.nevk; k++) gq_evk_destroy(G.evk[k].dev);
   G.nevk = 0;
   if (G.ctx) { gq_ctx_destroy(G.ctx); G.ctx = NULL; }
@@ -411,14 +460,21 @@ void poly_rot(poly_mpi_t *r, const poly_mpi_t *a, size_t rot) { automorph(r, a, 
 void poly_conj(poly_mpi_t *r, const poly_mpi_t *a) { automorph(r, a, 1, 0, __func__); }
 
 /* ---------------------------------------------------------------- evaluation keys */
-/* he_genswk writes keys with the CPU ntt() into plain malloc buffers (src/he-kem.c:103-110);
- * the device copy is made on first use and found again by address + sampled fingerprint, so a
- * buffer that was freed and reused for another key is re-uploaded. */
+/* he_genswk writes keys with ntt() into plain malloc buffers (src/he-kem.c:103-110).  The device copy is made on
+ * first use and found again by the address of the buffers.  Everything inside this library that writes a key
+ * (he_genrlk / he_genck / he_genrk, wrapped below) or frees one (he_free_evk) drops the copy; a caller that rewrites a
+ * key buffer by hand says so with gpqhe_dropin_invalidate_evk().  A 64-word sampled fingerprint stays as a cheap
+ * second line (hashing 2 x 12 MiB per he_mul would cost ten times the kernels).  The cache is bounded
+ * (GPQHE_DROPIN_EVK_CACHE_MB, default 16384): the least recently used copies are dropped first. */
+void gpqhe_ref_he_genrlk(he_evk_t *rlk, const poly_mpi_t *sk);
+void gpqhe_ref_he_genck(he_evk_t *ck, const poly_mpi_t *sk);
+void gpqhe_ref_he_genrk(he_evk_t *rk, const poly_mpi_t *sk);
+
 static uint64_t evk_print(const he_evk_t *k)
 {
   const size_t words = (size_t)hectx.dimevk * polyctx.n;
   uint64_t h = 0x9E3779B97F4A7C15ull, x = 0x243F6A8885A308D3ull;
-  for (unsigned s = 0; s < 2048; s++) {
+  for (unsigned s = 0; s < 64; s++) {
     x = x * 6364136223846793005ull + 1442695040888963407ull;
     size_t i = (size_t)((x >> 20) % words);
     h = (h ^ k->p0.coeffs[i]) * 0x100000001B3ull;
@@ -428,98 +484,378 @@ static uint64_t evk_print(const he_evk_t *k)
   return h;
 }
 
+static size_t evk_cache_cap(void)
+{
+  static size_t cap;
+  if (!cap) {
+    const char *e = getenv("GPQHE_DROPIN_EVK_CACHE_MB");
+    long long mb = e ? atoll(e) : 16384;
+    if (mb < 64) mb = 64;
+    cap = (size_t)mb << 20;
+  }
+  return cap;
+}
+
+static void evk_drop(unsigned i)
+{
+  gq_ctx_sync(G.ctx);                     /* a kernel in flight may still read the key */
+  gq_evk_destroy(G.evk[i].dev);
+  G.evk[i] = G.evk[--G.nevk];
+}
+
 static const gq_evk *evk_dev(const he_evk_t *k)
 {
   const uint64_t pr = evk_print(k);
+  G.evk_clock++;
   for (unsigned i = 0; i < G.nevk; i++) {
     struct evk_slot *s = &G.evk[i];
     if (s->p0 == k->p0.coeffs && s->p1 == k->p1.coeffs) {
+      s->used = G.evk_clock;
       if (s->print == pr) return s->dev;
+      gq_ctx_sync(G.ctx);
       gq_evk_destroy(s->dev);
       CK(gq_evk_create(ctx(), &s->dev, k->p0.coeffs, k->p1.coeffs));
       s->print = pr;
       return s->dev;
     }
   }
+  const size_t bytes = 2 * (size_t)hectx.dimevk * polyctx.n * 8;
+  while (G.nevk && (size_t)(G.nevk + 1) * bytes > evk_cache_cap()) {     /* least recently used first */
+    unsigned lru = 0;
+    for (unsigned i = 1; i < G.nevk; i++) if (G.evk[i].used < G.evk[lru].used) lru = i;
+    /* one call may hold up to `slots` keys + rlk + ck at once (he_gemv, he_coeff2slot, he_rlsin): copies looked up
+     * that recently are never dropped, the cap gives way instead */
+    if (G.evk_clock - G.evk[lru].used < (unsigned long long)hectx.slots + 4) break;
+    evk_drop(lru);
+  }
   if (G.nevk == G.capevk) {
     G.capevk = G.capevk ? 2 * G.capevk : 16;
     G.evk = realloc(G.evk, G.capevk * sizeof *G.evk);
   }
   struct evk_slot *s = &G.evk[G.nevk++];
-  s->p0 = k->p0.coeffs; s->p1 = k->p1.coeffs; s->print = pr; s->dev = NULL;
+  s->p0 = k->p0.coeffs; s->p1 = k->p1.coeffs; s->print = pr; s->dev = NULL; s->used = G.evk_clock;
   CK(gq_evk_create(ctx(), &s->dev, k->p0.coeffs, k->p1.coeffs));
   return s->dev;
 }
 
-void he_free_evk(he_evk_t *evk)
+void gpqhe_dropin_invalidate_evk(const he_evk_t *evk)
 {
   for (unsigned i = 0; i < G.nevk; i++)
-    if (G.evk[i].p0 == evk->p0.coeffs && G.evk[i].p1 == evk->p1.coeffs) {
-      gq_evk_destroy(G.evk[i].dev);
-      G.evk[i] = G.evk[--G.nevk];
-      break;
-    }
+    if (G.evk[i].p0 == evk->p0.coeffs && G.evk[i].p1 == evk->p1.coeffs) { evk_drop(i); break; }
+}
+
+void he_free_evk(he_evk_t *evk)
+{
+  gpqhe_dropin_invalidate_evk(evk);
   gpqhe_ref_he_free_evk(evk);
+}
+/* key generation stays the reference's (RNG order, stdout prints); its rns_decompose / ntt calls bind to the GPU */
+void he_genrlk(he_evk_t *rlk, const poly_mpi_t *sk) { gpqhe_dropin_invalidate_evk(rlk); gpqhe_ref_he_genrlk(rlk, sk); }
+void he_genck(he_evk_t *ck, const poly_mpi_t *sk) { gpqhe_dropin_invalidate_evk(ck); gpqhe_ref_he_genck(ck, sk); }
+void he_genrk(he_evk_t *rk, const poly_mpi_t *sk)
+{
+  for (unsigned r = 0; r < hectx.slots; r++) gpqhe_dropin_invalidate_evk(&rk[r]);
+  gpqhe_ref_he_genrk(rk, sk);
+}
+
+/* ------------------------------------------------- device-resident ciphertexts --------
+ * he_ct_t is a public host struct holding 2N gcry_mpi objects (src/gpqhe.h:84-91); converting them costs ten times
+ * the kernels of an he_mul.  Every he_* entry point below therefore works on a device SHADOW of the ciphertext: a
+ * table keyed by ct->c0.coeffs (the address of the MPI array, stable from he_alloc_ct to he_free_ct) holds the two
+ * polynomials as word-major device buffers plus two bits, `dev_ok` (the shadow is current) and `host_ok` (the MPIs
+ * are current).  An operation uploads an operand only if its shadow is not current, runs on the device, and marks
+ * its result device-only; nothing comes back until somebody READS the MPIs.  Inside libgpqhe.so the readers are
+ * he_dec (src/he-encrypt.c:113-123) and he_copy_ct from a host-current source; the writers are he_enc_pk /
+ * he_enc_sk (:37-98).  All are wrapped here (same -D rename as the hot symbols), as is poly_mpi_free, which ends a
+ * shadow's life.  he_show_ct_params prints metadata only (src/he-info.c:95-104), and l / nu / B always live on the
+ * host.  A caller that reads or writes ct->c0.coeffs[i] directly - none of the reference's tests or algorithms does -
+ * calls gpqhe_dropin_sync_ct() before reading, gpqhe_dropin_touch_ct() after writing, or sets GPQHE_DROPIN_EAGER=1,
+ * which writes every result back at once (the behaviour of round 1). */
+void gpqhe_ref_he_enc_pk(struct he_ct *ct, const struct he_pt *pt, const struct he_pk *pk);
+void gpqhe_ref_he_enc_sk(struct he_ct *ct, const struct he_pt *pt, const poly_mpi_t *sk);
+void gpqhe_ref_he_dec(struct he_pt *pt, const struct he_ct *ct, const poly_mpi_t *sk);
+void gpqhe_ref_he_copy_ct(struct he_ct *dest, const struct he_ct *src);
+void gpqhe_ref_poly_mpi_free(poly_mpi_t *a);
+
+static size_t ct_poly(void) { return (size_t)G.info.W * polyctx.n; }
+
+static size_t sh_hash(const void *key, size_t cap)
+{
+  return (size_t)((((uintptr_t)key >> 4) * 0x9E3779B97F4A7C15ull) >> 20) & (cap - 1);
+}
+
+static struct shadow *sh_find(const void *key)
+{
+  if (!G.shcap || !key) return NULL;
+  for (size_t i = sh_hash(key, G.shcap);; i = (i + 1) & (G.shcap - 1)) {
+    struct shadow *s = &G.sh[i];
+    if (s->key == key) return s;
+    if (!s->key && !s->tomb) return NULL;
+  }
+}
+
+static void sh_grow(void)
+{
+  const size_t ocap = G.shcap, ncap = ocap ? 2 * ocap : 64;
+  struct shadow *old = G.sh;
+  G.sh = calloc(ncap, sizeof *G.sh);
+  if (!G.sh) die("shadow table");
+  G.shcap = ncap; G.shused = 0;
+  for (size_t i = 0; i < ocap; i++)
+    if (old[i].key) {
+      size_t j = sh_hash(old[i].key, ncap);
+      while (G.sh[j].key) j = (j + 1) & (ncap - 1);
+      G.sh[j] = old[i];
+      G.shused++;
+    }
+  free(old);
+}
+
+/* entry of a ciphertext, created (host-current, no device buffer) on first sight.  The returned pointer is valid
+ * until the next sh_get(); the device buffers themselves never move. */
+static struct shadow *sh_get(const he_ct_t *ct)
+{
+  const void *key = ct->c0.coeffs;
+  struct shadow *s = sh_find(key);
+  if (s) return s;
+  if (2 * (G.shused + 1) > G.shcap) sh_grow();
+  size_t i = sh_hash(key, G.shcap);
+  while (G.sh[i].key) i = (i + 1) & (G.shcap - 1);
+  s = &G.sh[i];
+  if (!s->tomb) G.shused++;
+  s->key = key; s->tomb = 0; s->dev = NULL; s->dev_ok = 0; s->host_ok = 1;
+  return s;
+}
+
+static uint64_t *pool_take(void)
+{
+  if (G.npool) return G.pool[--G.npool];
+  void *p = NULL;
+  CK(gq_dev_alloc(ctx(), 2 * ct_poly() * 8, &p));
+  G.shadow_allocs++;
+  return p;
+}
+static void pool_give(uint64_t *p)
+{
+  if (!p) return;
+  if (G.npool == G.cappool) {
+    G.cappool = G.cappool ? 2 * G.cappool : 32;
+    G.pool = realloc(G.pool, G.cappool * sizeof *G.pool);
+  }
+  G.pool[G.npool++] = p;       /* stream order makes reuse safe: the next writer is enqueued after the last reader */
+}
+
+static void sh_release(const void *key)
+{
+  struct shadow *s = sh_find(key);
+  if (!s) return;
+  pool_give(s->dev);
+  s->key = NULL; s->dev = NULL; s->tomb = 1;
+}
+
+static void shadows_drop_all(void)
+{
+  if (G.ctx) gq_ctx_sync(G.ctx);
+  for (size_t i = 0; i < G.shcap; i++)
+    if (G.sh[i].key && G.sh[i].dev && G.ctx) gq_dev_free(G.ctx, G.sh[i].dev);
+  free(G.sh); G.sh = NULL; G.shcap = G.shused = 0;
+  for (unsigned i = 0; i < G.npool; i++) if (G.ctx) gq_dev_free(G.ctx, G.pool[i]);
+  G.npool = 0;
+  if (G.dscratch && G.ctx) gq_dev_free(G.ctx, G.dscratch);
+  G.dscratch = NULL; G.dscratch_words = 0;
+  if (G.ring) gq_host_free(G.ring);
+  G.ring = NULL; G.ring_pos = 0;
+}
+
+/* pinned staging ring: a slot handed to an asynchronous copy is not reused before the stream has been synchronised */
+#define RING_SLOTS 16
+static uint64_t *ring_slot(void)
+{
+  const size_t poly = ct_poly();
+  if (!G.ring) {       /* its own pinned buffer: stage() is rewritten synchronously by poly_mul, rns_decompose ... */
+    void *p = NULL;
+    if (gq_host_alloc(&p, (size_t)RING_SLOTS * poly * 8 + 64)) die("staging ring");
+    G.ring = p;
+  }
+  if (G.ring_pos == RING_SLOTS) { CK(gq_ctx_sync(ctx())); G.ring_pos = 0; }
+  return G.ring + (size_t)(G.ring_pos++) * poly;
+}
+static void ring_sync(void) { CK(gq_ctx_sync(ctx())); G.ring_pos = 0; }
+
+/* upload one MPI polynomial into dst (device) */
+static void poly_up(uint64_t *dst, const poly_mpi_t *a, const char *who)
+{
+  uint64_t *s = ring_slot();
+  poly_in(s, a, G.info.W, who);
+  CK(gq_dev_upload(ctx(), dst, s, ct_poly() * 8, NULL));
+}
+
+/* device buffer holding a ciphertext's current value (c0 at p, c1 at p + poly); uploads it first if the MPIs are
+ * the only current copy.  The pointer stays valid whatever happens to the table afterwards. */
+static uint64_t *ct_dev_in(const he_ct_t *ct, const char *who)
+{
+  struct shadow *s = sh_get(ct);
+  if (!s->dev) s->dev = pool_take();
+  if (!s->dev_ok) {
+    poly_up(s->dev, &ct->c0, who);
+    poly_up(s->dev + ct_poly(), &ct->c1, who);
+    s->dev_ok = 1;
+    G.ct_uploads++;
+  }
+  return s->dev;
+}
+/* device buffer that will receive a ciphertext's new value; ct_written() once the operation has been enqueued */
+static uint64_t *ct_dev_out(he_ct_t *ct)
+{
+  struct shadow *s = sh_get(ct);
+  if (!s->dev) s->dev = pool_take();
+  return s->dev;
+}
+static void ct_flush(const he_ct_t *ct)
+{
+  struct shadow *s = sh_find(ct->c0.coeffs);
+  if (!s || s->host_ok || !s->dev_ok) return;
+  const size_t poly = ct_poly();
+  const uint64_t *d = s->dev;
+  ring_sync();
+  uint64_t *a = ring_slot(), *b = ring_slot();
+  CK(gq_dev_download(ctx(), a, d, poly * 8, NULL));
+  CK(gq_dev_download(ctx(), b, d + poly, poly * 8, NULL));
+  ring_sync();
+  poly_out((poly_mpi_t *)&ct->c0, a, G.info.W);
+  poly_out((poly_mpi_t *)&ct->c1, b, G.info.W);
+  s->host_ok = 1;
+  G.ct_downloads++;
+}
+static int eager(void)
+{
+  static int e = -1;
+  if (e < 0) e = getenv("GPQHE_DROPIN_EAGER") != NULL;
+  return e;
+}
+static void ct_written(he_ct_t *ct)
+{
+  struct shadow *s = sh_get(ct);
+  s->dev_ok = 1; s->host_ok = 0;
+  if (eager()) ct_flush(ct);
+}
+
+/* public hooks for callers that touch ct->c0.coeffs / c1.coeffs directly; gpqhe_dropin_wait() only waits for the
+ * device to finish what has been enqueued (timing), nothing is downloaded */
+void gpqhe_dropin_wait(void) { if (G.ctx) CK(gq_ctx_sync(G.ctx)); }
+void gpqhe_dropin_sync_ct(const he_ct_t *ct) { ct_flush(ct); }
+void gpqhe_dropin_touch_ct(const he_ct_t *ct)
+{
+  struct shadow *s = sh_find(ct->c0.coeffs);
+  if (s) { s->dev_ok = 0; s->host_ok = 1; }
+}
+
+/* growable device scratch for plaintexts / encoded diagonals (words) */
+static uint64_t *dscratch(size_t words)
+{
+  if (G.dscratch_words < words) {
+    if (G.dscratch) gq_dev_free(ctx(), G.dscratch);
+    void *p = NULL;
+    CK(gq_dev_alloc(ctx(), words * 8 + 64, &p));
+    G.dscratch = p; G.dscratch_words = words;
+  }
+  return G.dscratch;
+}
+
+/* ---- wrapped readers / writers of the host MPIs ---------------------------------------------------- */
+void he_enc_pk(struct he_ct *ct, const struct he_pt *pt, const struct he_pk *pk)
+{
+  gpqhe_ref_he_enc_pk(ct, pt, pk);
+  gpqhe_dropin_touch_ct(ct);
+}
+void he_enc_sk(struct he_ct *ct, const struct he_pt *pt, const poly_mpi_t *sk)
+{
+  gpqhe_ref_he_enc_sk(ct, pt, sk);
+  gpqhe_dropin_touch_ct(ct);
+}
+void he_dec(struct he_pt *pt, const struct he_ct *ct, const poly_mpi_t *sk)
+{
+  ct_flush(ct);
+  gpqhe_ref_he_dec(pt, ct, sk);
+}
+void he_copy_ct(struct he_ct *dest, const struct he_ct *src)
+{
+  if (dest == src || dest->c0.coeffs == src->c0.coeffs) return;
+  struct shadow *s = sh_find(src->c0.coeffs);
+  const int dev_ok = s && s->dev_ok, host_ok = !s || s->host_ok;
+  const uint64_t *sd = s ? s->dev : NULL;
+  if (!host_ok) {                            /* the current value lives on the device only: copy it there */
+    uint64_t *d = ct_dev_out(dest);
+    CK(gq_dev_copy(ctx(), d, sd, 2 * ct_poly() * 8, NULL));
+    dest->l = src->l; dest->nu = src->nu; dest->B = src->B;        /* he-mem.c:90-92 */
+    ct_written(dest);
+    return;
+  }
+  gpqhe_ref_he_copy_ct(dest, src);
+  gpqhe_dropin_touch_ct(dest);
+  if (dev_ok) {                              /* both copies current: keep the device one too (no marshalling later) */
+    uint64_t *d = ct_dev_out(dest);
+    CK(gq_dev_copy(ctx(), d, sd, 2 * ct_poly() * 8, NULL));
+    struct shadow *t = sh_get(dest);
+    t->dev_ok = 1; t->host_ok = 1;
+  }
+}
+void poly_mpi_free(poly_mpi_t *a)
+{
+  sh_release(a->coeffs);
+  gpqhe_ref_poly_mpi_free(a);
 }
 
 /* ------------------------------------------------------------------ HE primitives */
 void he_mul(he_ct_t *ct, const he_ct_t *ct1, const he_ct_t *ct2, const he_evk_t *rlk)
 {
   assert(ct1->l == ct2->l);
-  /* metadata first and in the reference's statement order (he-mult.c:92-95): with ct aliasing
-   * ct1/ct2 the later statements read the values the earlier ones wrote */
+  const size_t poly = ct_poly();
+  const uint64_t *a = ct_dev_in(ct1, __func__), *b = (ct2 == ct1) ? a : ct_dev_in(ct2, __func__);
+  /* metadata in the reference's statement order (he-mult.c:92-95): with ct aliasing ct1/ct2 the later statements
+   * read the values the earlier ones wrote */
   ct->l = ct1->l;
   ct->nu = ct1->nu * ct2->nu;
   ct->B = (ct1->nu) * (ct2->B) + (ct2->nu) * (ct1->B) + (ct1->B) * (ct2->B) + hectx.bnd.Bmult[ct->l];
-  const unsigned l = ct->l, n = polyctx.n, W = G.info.W;
-  const size_t poly = (size_t)W * n;
-  uint64_t *s = stage(6 * poly);
-  poly_in(s, &ct1->c0, W, __func__);
-  poly_in(s + poly, &ct1->c1, W, __func__);
-  if (ct2 == ct1) {
-    CK(gq_he_mul(ctx(), l, s + 4 * poly, s + 5 * poly, s, s + poly, s, s + poly, evk_dev(rlk)));
-  } else {
-    poly_in(s + 2 * poly, &ct2->c0, W, __func__);
-    poly_in(s + 3 * poly, &ct2->c1, W, __func__);
-    CK(gq_he_mul(ctx(), l, s + 4 * poly, s + 5 * poly, s, s + poly, s + 2 * poly, s + 3 * poly, evk_dev(rlk)));
-  }
-  poly_out(&ct->c0, s + 4 * poly, W);
-  poly_out(&ct->c1, s + 5 * poly, W);
+  uint64_t *o = ct_dev_out(ct);
+  CK(gq_he_mul_dev(ctx(), ct->l, o, o + poly, a, a + poly, b, b + poly, evk_dev(rlk), NULL));
+  ct_written(ct);
+}
+
+static const uint64_t *pt_dev(const he_pt_t *pt, unsigned slot, const char *who)
+{
+  uint64_t *d = dscratch((size_t)4 * ct_poly()) + (size_t)slot * ct_poly();
+  poly_up(d, &pt->m, who);
+  return d;
 }
 
 void he_mulpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt)
 {
+  const size_t poly = ct_poly();
+  const uint64_t *a = ct_dev_in(src, __func__);
   dest->l = src->l;                                                     /* he-mult.c:162-164 */
   dest->nu = src->nu * pt->nu;
   dest->B = src->B * pt->nu;
-  const unsigned l = dest->l, n = polyctx.n, W = G.info.W;
+  const unsigned l = dest->l;
   /* limb count in double arithmetic, truncated, exactly as he-mult.c:168 */
   const unsigned dim = (gcry_mpi_get_nbits(hectx.q[l]) + log2(pt->nu) + polyctx.logn) / GPQHE_LOGP + 1;
-  const size_t poly = (size_t)W * n;
-  uint64_t *s = stage(5 * poly);
-  poly_in(s, &src->c0, W, __func__);
-  poly_in(s + poly, &src->c1, W, __func__);
-  poly_in(s + 2 * poly, &pt->m, W, __func__);
-  CK(gq_he_mulpt(ctx(), l, dim, s + 3 * poly, s + 4 * poly, s, s + poly, s + 2 * poly));
-  poly_out(&dest->c0, s + 3 * poly, W);
-  poly_out(&dest->c1, s + 4 * poly, W);
+  const uint64_t *m = pt_dev(pt, 0, __func__);
+  uint64_t *o = ct_dev_out(dest);
+  CK(gq_he_mulpt_dev(ctx(), l, dim, o, o + poly, a, a + poly, m, NULL));
+  ct_written(dest);
 }
 
 static void ct_inplace(he_ct_t *ct, int op, unsigned rot, const he_evk_t *k, const char *who)
 {
-  const unsigned n = polyctx.n, W = G.info.W;
-  const size_t poly = (size_t)W * n;
-  uint64_t *s = stage(2 * poly);
-  poly_in(s, &ct->c0, W, who);
-  poly_in(s + poly, &ct->c1, W, who);
+  const size_t poly = ct_poly();
+  uint64_t *s = ct_dev_in(ct, who);
   switch (op) {
-    case 0: CK(gq_he_rs(ctx(), ct->l, s, s + poly)); break;
-    case 1: CK(gq_he_moddown(ctx(), ct->l, s, s + poly)); break;
-    case 2: CK(gq_he_rot(ctx(), ct->l, rot, s, s + poly, evk_dev(k))); break;
-    case 3: CK(gq_he_conj(ctx(), ct->l, s, s + poly, evk_dev(k))); break;
+    case 0: CK(gq_he_rs_dev(ctx(), ct->l, s, s + poly, NULL)); break;
+    case 1: CK(gq_he_moddown_dev(ctx(), ct->l, s, s + poly, NULL)); break;
+    case 2: CK(gq_he_rot_dev(ctx(), ct->l, rot, s, s + poly, evk_dev(k), NULL)); break;
+    case 3: CK(gq_he_conj_dev(ctx(), ct->l, s, s + poly, evk_dev(k), NULL)); break;
   }
-  poly_out(&ct->c0, s, W);
-  poly_out(&ct->c1, s + poly, W);
+  ct_written(ct);
 }
 
 void he_rs(struct he_ct *ct)
@@ -538,57 +874,57 @@ void he_rot(he_ct_t *ct, const int rot, const he_evk_t *rk) { ct_inplace(ct, 2, 
 void he_conj(he_ct_t *ct, const he_evk_t *ck) { ct_inplace(ct, 3, 0, ck, __func__); }
 
 /* ---- coefficient-local ops: src/he-add.c:32-146 ------------------------------- */
-static void ct_linear(he_ct_t *ct, const he_ct_t *a, const poly_mpi_t *b0, const poly_mpi_t *b1, int op,
-                      unsigned l, const char *who)
+/* op: 0 add, 1 sub (b = second ciphertext); 2 addpt, 3 subpt (pt); 4 neg */
+static void ct_linear(he_ct_t *ct, const he_ct_t *a, const he_ct_t *b, const he_pt_t *pt, int op, unsigned l,
+                      const char *who)
 {
-  const unsigned n = polyctx.n, W = G.info.W;
-  const size_t poly = (size_t)W * n;
-  uint64_t *s = stage(6 * poly);
-  poly_in(s, &a->c0, W, who);
-  poly_in(s + poly, &a->c1, W, who);
-  if (b0) poly_in(s + 2 * poly, b0, W, who);
-  if (b1) poly_in(s + 3 * poly, b1, W, who);
-  uint64_t *o0 = s + 4 * poly, *o1 = s + 5 * poly;
+  const size_t poly = ct_poly();
+  const uint64_t *pa = ct_dev_in(a, who), *pb = NULL;
+  if (b) pb = (b == a) ? pa : ct_dev_in(b, who);
+  if (pt) pb = pt_dev(pt, 0, who);
+  uint64_t *o = ct_dev_out(ct);
   switch (op) {
-    case 0: CK(gq_he_add(ctx(), l, o0, o1, s, s + poly, s + 2 * poly, s + 3 * poly)); break;
-    case 1: CK(gq_he_sub(ctx(), l, o0, o1, s, s + poly, s + 2 * poly, s + 3 * poly)); break;
-    case 2: CK(gq_he_addpt(ctx(), l, o0, o1, s, s + poly, s + 2 * poly)); break;
-    case 3: CK(gq_he_subpt(ctx(), l, o0, o1, s, s + poly, s + 2 * poly)); break;
-    case 4: memcpy(o0, s, 2 * poly * sizeof(uint64_t)); CK(gq_he_neg(ctx(), l, o0, o1)); break;
+    case 0: CK(gq_he_add_dev(ctx(), l, o, o + poly, pa, pa + poly, pb, pb + poly, NULL)); break;
+    case 1: CK(gq_he_sub_dev(ctx(), l, o, o + poly, pa, pa + poly, pb, pb + poly, NULL)); break;
+    case 2: CK(gq_he_addpt_dev(ctx(), l, o, o + poly, pa, pa + poly, pb, NULL)); break;
+    case 3: CK(gq_he_subpt_dev(ctx(), l, o, o + poly, pa, pa + poly, pb, NULL)); break;
+    case 4:
+      if (o != pa) CK(gq_dev_copy(ctx(), o, pa, 2 * poly * 8, NULL));
+      CK(gq_he_neg_dev(ctx(), l, o, o + poly, NULL));
+      break;
   }
-  poly_out(&ct->c0, o0, W);
-  poly_out(&ct->c1, o1, W);
+  ct_written(ct);
 }
 
 void he_add(he_ct_t *ct, const he_ct_t *ct1, const he_ct_t *ct2)
 {
   assert(ct1->l == ct2->l);
-  ct->l = ct1->l;                                                       /* he-add.c:36-38, in order */
-  ct->nu = (ct1->nu >= ct2->nu) ? ct1->nu : ct2->nu;
-  ct->B = ct1->B + ct2->B;
-  ct_linear(ct, ct1, &ct2->c0, &ct2->c1, 0, ct->l, __func__);
+  const unsigned l = ct1->l;
+  const double nu = (ct1->nu >= ct2->nu) ? ct1->nu : ct2->nu, B = ct1->B + ct2->B;    /* he-add.c:36-38 */
+  ct_linear(ct, ct1, ct2, NULL, 0, l, __func__);
+  ct->l = l; ct->nu = nu; ct->B = B;
 }
 void he_sub(he_ct_t *ct, const he_ct_t *ct1, const he_ct_t *ct2)
 {
   assert(ct1->l == ct2->l);
-  ct->l = ct1->l;                                                       /* he-add.c:61-63 */
-  ct->nu = (ct1->nu >= ct2->nu) ? ct1->nu : ct2->nu;
-  ct->B = ct1->B + ct2->B;
-  ct_linear(ct, ct1, &ct2->c0, &ct2->c1, 1, ct->l, __func__);
+  const unsigned l = ct1->l;
+  const double nu = (ct1->nu >= ct2->nu) ? ct1->nu : ct2->nu, B = ct1->B + ct2->B;    /* he-add.c:61-63 */
+  ct_linear(ct, ct1, ct2, NULL, 1, l, __func__);
+  ct->l = l; ct->nu = nu; ct->B = B;
 }
 void he_addpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt)
 {
-  dest->l = src->l;                                                     /* he-add.c:85-87 */
-  dest->nu = (src->nu >= pt->nu) ? src->nu : pt->nu;
-  dest->B = src->B;
-  ct_linear(dest, src, &pt->m, NULL, 2, dest->l, __func__);
+  const unsigned l = src->l;
+  const double nu = (src->nu >= pt->nu) ? src->nu : pt->nu, B = src->B;                /* he-add.c:85-87 */
+  ct_linear(dest, src, NULL, pt, 2, l, __func__);
+  dest->l = l; dest->nu = nu; dest->B = B;
 }
 void he_subpt(he_ct_t *dest, const he_ct_t *src, const he_pt_t *pt)
 {
-  dest->l = src->l;                                                     /* he-add.c:109-111 */
-  dest->nu = (src->nu >= pt->nu) ? src->nu : pt->nu;
-  dest->B = src->B;
-  ct_linear(dest, src, &pt->m, NULL, 3, dest->l, __func__);
+  const unsigned l = src->l;
+  const double nu = (src->nu >= pt->nu) ? src->nu : pt->nu, B = src->B;                /* he-add.c:109-111 */
+  ct_linear(dest, src, NULL, pt, 3, l, __func__);
+  dest->l = l; dest->nu = nu; dest->B = B;
 }
 void he_neg(he_ct_t *ct) { ct_linear(ct, ct, NULL, NULL, 4, ct->l, __func__); }
 
@@ -605,13 +941,13 @@ static void gemv_split(unsigned *n1, unsigned *n2)
   *n2 = m / *n1;
 }
 
-/* diagonal k = i*n1+j of A, pre-rotated by -i*n1 slots, encoded at scale Delta (he-algo.c:70-72), written
- * as word-major polys at dst + k*poly; pt keeps the metadata of the last he_ecd */
+/* diagonal k = i*n1+j of A, pre-rotated by -i*n1 slots, encoded at scale Delta (he-algo.c:70-72), uploaded
+ * as word-major polys to the DEVICE buffer dst + k*poly; pt keeps the metadata of the last he_ecd */
 static void gemv_diagonals(const _Complex double *A, unsigned n1, uint64_t *dst, const uint64_t **pts,
                            he_pt_t *pt, const char *who)
 {
-  const unsigned m = hectx.slots, W = G.info.W;
-  const size_t poly = (size_t)W * polyctx.n;
+  const unsigned m = hectx.slots;
+  const size_t poly = ct_poly();
   _Complex double *d = malloc(sizeof(_Complex double) * m);
   if (!d) die(who);
   for (unsigned k = 0; k < m; k++) {
@@ -621,7 +957,7 @@ static void gemv_diagonals(const _Complex double *A, unsigned n1, uint64_t *dst,
       d[t] = A[(size_t)u * m + (k + u) % m];
     }
     he_ecd(pt, d);
-    poly_in(dst + (size_t)k * poly, &pt->m, W, who);
+    poly_up(dst + (size_t)k * poly, &pt->m, who);
     pts[k] = dst + (size_t)k * poly;
   }
   free(d);
@@ -658,28 +994,27 @@ static const gq_evk **gemv_keys(const he_evk_t *rk, unsigned n1, const char *who
 
 void he_gemv(he_ct_t *ct_dest, const _Complex double *A, const he_ct_t *ct, const he_evk_t *rk)
 {
-  const unsigned m = hectx.slots, n = polyctx.n, W = G.info.W, l = ct->l;
+  const unsigned m = hectx.slots, l = ct->l;
   unsigned n1, n2;
   gemv_split(&n1, &n2);
-  const size_t poly = (size_t)W * n;
-  uint64_t *s = stage((4 + (size_t)m) * poly);
-  poly_in(s, &ct->c0, W, __func__);
-  poly_in(s + poly, &ct->c1, W, __func__);
+  const size_t poly = ct_poly();
+  const uint64_t *a = ct_dev_in(ct, __func__);
+  uint64_t *dp = dscratch((4 + (size_t)m) * poly) + 4 * poly;      /* slots 0..3 belong to pt_dev() */
   he_pt_t pt;
   he_alloc_pt(&pt);
   const uint64_t **pts = malloc(sizeof(*pts) * m);
   if (!pts) die(__func__);
-  gemv_diagonals(A, n1, s + 4 * poly, pts, &pt, __func__);
+  gemv_diagonals(A, n1, dp, pts, &pt, __func__);
   const gq_evk **keys = gemv_keys(rk, n1, __func__);
   const unsigned dim = (gcry_mpi_get_nbits(hectx.q[l]) + log2(pt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
   double nu_o, B_o;
   gemv_meta(ct->nu, ct->B, pt.nu, n1, n2, &nu_o, &B_o);
-  CK(gq_he_gemv(ctx(), l, n1, n2, dim, s + 2 * poly, s + 3 * poly, s, s + poly, pts, keys));
+  uint64_t *o = ct_dev_out(ct_dest);
+  CK(gq_he_gemv_dev(ctx(), l, n1, n2, dim, o, o + poly, a, a + poly, pts, keys, NULL));
   ct_dest->l = l - 1;
   ct_dest->nu = nu_o;
   ct_dest->B = B_o;
-  poly_out(&ct_dest->c0, s + 2 * poly, W);
-  poly_out(&ct_dest->c1, s + 3 * poly, W);
+  ct_written(ct_dest);
   free(pts); free(keys);
   he_free_pt(&pt);
 }
@@ -691,31 +1026,39 @@ void he_gemv(he_ct_t *ct_dest, const _Complex double *A, const he_ct_t *ct, cons
 extern struct bootstrap_ctx bootstrapctx;
 void he_coeff2slot(he_ct_t *ct_real, he_ct_t *ct_imag, const he_ct_t *ct, const he_evk_t *ck, const he_evk_t *rk)
 {
-  const unsigned m = hectx.slots, n = polyctx.n, W = G.info.W, l = ct->l;
+  const unsigned m = hectx.slots, l = ct->l;
   unsigned n1, n2;
   gemv_split(&n1, &n2);
-  const size_t poly = (size_t)W * n;
-  uint64_t *s = stage((7 + 4 * (size_t)m) * poly);
-  poly_in(s, &ct->c0, W, __func__);
-  poly_in(s + poly, &ct->c1, W, __func__);
+  const size_t poly = ct_poly();
+  if (ct_real == ct_imag) { fprintf(stderr, "he_coeff2slot: the two outputs must be distinct ciphertexts\n"); errno = EINVAL; abort(); }
+  const uint64_t *a = ct_dev_in(ct, __func__);
+  uint64_t *dbase = dscratch((5 + 4 * (size_t)m) * poly);
+  uint64_t *dcpt = dbase + 4 * poly, *dp = dbase + 5 * poly;
   he_pt_t pt, cpt;
   he_alloc_pt(&pt);
   he_alloc_pt(&cpt);
   he_const_pt(&cpt, 1 / polyctx.n);                                     /* he-bootstrap.c:385, integer division as there */
-  poly_in(s + 2 * poly, &cpt.m, W, __func__);
+  poly_up(dcpt, &cpt.m, __func__);
   const uint64_t **pts = malloc(sizeof(*pts) * 4 * m);
   if (!pts) die(__func__);
   const _Complex double *mats[4] = {bootstrapctx.U0_conjT, bootstrapctx.U0_T, bootstrapctx.U1_conjT, bootstrapctx.U1_T};
   for (unsigned k = 0; k < 4; k++)
-    gemv_diagonals(mats[k], n1, s + (7 + (size_t)k * m) * poly, pts + (size_t)k * m, &pt, __func__);
+    gemv_diagonals(mats[k], n1, dp + (size_t)k * m * poly, pts + (size_t)k * m, &pt, __func__);
   const gq_evk **keys = gemv_keys(rk, n1, __func__);
   const unsigned dim_gemv = (gcry_mpi_get_nbits(hectx.q[l]) + log2(pt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
   const unsigned dim_pt = (gcry_mpi_get_nbits(hectx.q[l - 1]) + log2(cpt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
   double nu_g, B_g;
   gemv_meta(ct->nu, ct->B, pt.nu, n1, n2, &nu_g, &B_g);                 /* he_conj keeps nu and B */
-  uint64_t *o = s + 3 * poly;
-  CK(gq_he_coeff2slot(ctx(), l, n1, n2, dim_gemv, dim_pt, o, o + poly, o + 2 * poly, o + 3 * poly, s, s + poly,
-                      pts, s + 2 * poly, evk_dev(ck), keys));
+  /* an output may alias the input (the device call reads `a` up to its last he_gemv): such an output is computed
+   * into a spare buffer and copied */
+  uint64_t *o_re = ct_dev_out(ct_real), *o_im = ct_dev_out(ct_imag);
+  uint64_t *tmp = (o_re == a || o_im == a) ? pool_take() : NULL;
+  uint64_t *w_re = (o_re == a) ? tmp : o_re, *w_im = (o_im == a) ? tmp : o_im;
+  CK(gq_he_coeff2slot_dev(ctx(), l, n1, n2, dim_gemv, dim_pt, w_re, w_re + poly, w_im, w_im + poly, a, a + poly,
+                          pts, dcpt, evk_dev(ck), keys, NULL));
+  if (w_re != o_re) CK(gq_dev_copy(ctx(), o_re, w_re, 2 * poly * 8, NULL));
+  if (w_im != o_im) CK(gq_dev_copy(ctx(), o_im, w_im, 2 * poly * 8, NULL));
+  pool_give(tmp);
   he_ct_t *outs[2] = {ct_real, ct_imag};
   for (unsigned k = 0; k < 2; k++) {
     double nu = nu_g, B = B_g + B_g;                                    /* he_add, he-add.c:36-38 */
@@ -723,8 +1066,7 @@ void he_coeff2slot(he_ct_t *ct_real, he_ct_t *ct_imag, const he_ct_t *ct, const 
     outs[k]->l = l - 2;                                                 /* he_rs, he-rescale.c:36-38 */
     outs[k]->nu = nu / hectx.Delta;
     outs[k]->B = B / hectx.Delta + hectx.bnd.Brs;
-    poly_out(&outs[k]->c0, o + (size_t)(2 * k) * poly, W);
-    poly_out(&outs[k]->c1, o + (size_t)(2 * k + 1) * poly, W);
+    ct_written(outs[k]);
   }
   free(pts); free(keys);
   he_free_pt(&pt);
@@ -785,13 +1127,13 @@ static unsigned mulpt_dim(unsigned l, double ptnu)                            /*
   return (gcry_mpi_get_nbits(hectx.q[l]) + log2(ptnu) + polyctx.logn) / GPQHE_LOGP + 1;
 }
 
-/* the 8 plaintexts of he_exp at dst (pts[0] = he_ecd of a/2^iter in every slot, he-algo.c:443-447; pts[1..7] =
+/* the 8 plaintexts of he_exp uploaded to the DEVICE buffer dst (pts[0] = he_ecd of a/2^iter in every slot, he-algo.c:443-447; pts[1..7] =
  * he_const_pt of the Taylor constants, he-algo.c:384-411); returns pt->nu (the same for all of them) */
 static double exp_plaintexts(_Complex double a, unsigned iter, uint64_t *dst, const uint64_t **pts, const char *who)
 {
   static const double consts[7] = {1.0, 3.0, 1.0 / 6, 5.0, 1.0 / 120, 7.0, 1.0 / 5040};
-  const unsigned m = hectx.slots, W = G.info.W;
-  const size_t poly = (size_t)W * polyctx.n;
+  const unsigned m = hectx.slots;
+  const size_t poly = ct_poly();
   he_pt_t pt;
   he_alloc_pt(&pt);
   _Complex double *coeff = malloc(sizeof(_Complex double) * m);
@@ -799,13 +1141,13 @@ static double exp_plaintexts(_Complex double a, unsigned iter, uint64_t *dst, co
   a /= (1 << iter);
   for (unsigned i = 0; i < m; i++) coeff[i] = a;
   he_ecd(&pt, coeff);
-  poly_in(dst, &pt.m, W, who);
+  poly_up(dst, &pt.m, who);
   pts[0] = dst;
   he_pt_t cpt;                        /* he_exp_taylor's own plaintext: he_const_pt writes coefficients 0 and n/2 only */
   he_alloc_pt(&cpt);
   for (unsigned k = 0; k < 7; k++) {
     he_const_pt(&cpt, consts[k]);
-    poly_in(dst + (size_t)(k + 1) * poly, &cpt.m, W, who);
+    poly_up(dst + (size_t)(k + 1) * poly, &cpt.m, who);
     pts[k + 1] = dst + (size_t)(k + 1) * poly;
   }
   const double nu = pt.nu;
@@ -817,35 +1159,33 @@ static double exp_plaintexts(_Complex double a, unsigned iter, uint64_t *dst, co
 
 void he_exp(he_ct_t *ct_exp, _Complex double a, const he_ct_t *ct, const he_evk_t *rlk, const unsigned int iter)
 {
-  const unsigned n = polyctx.n, W = G.info.W, l = ct->l;
-  const size_t poly = (size_t)W * n;
+  const unsigned l = ct->l;
+  const size_t poly = ct_poly();
   if (l < 4 + iter) { fprintf(stderr, "he_exp: level %u is below the 4+iter levels the evaluation consumes\n", l); errno = EINVAL; abort(); }
-  uint64_t *s = stage(12 * poly);
   const uint64_t *pts[8];
-  poly_in(s, &ct->c0, W, __func__);
-  poly_in(s + poly, &ct->c1, W, __func__);
-  const double ptnu = exp_plaintexts(a, iter, s + 4 * poly, pts, __func__);
+  const uint64_t *x = ct_dev_in(ct, __func__);
+  uint64_t *dp = dscratch((4 + 9) * poly) + 4 * poly;
+  const double ptnu = exp_plaintexts(a, iter, dp, pts, __func__);
   const struct meta in = {ct->nu, ct->B}, out = exp_meta(l, in, ptnu, iter);
-  CK(gq_he_exp(ctx(), l, iter, mulpt_dim(l, ptnu), mulpt_dim(l - 1, ptnu), s + 2 * poly, s + 3 * poly, s, s + poly,
-               pts, evk_dev(rlk)));
+  uint64_t *o = ct_dev_out(ct_exp);
+  CK(gq_he_exp_dev(ctx(), l, iter, mulpt_dim(l, ptnu), mulpt_dim(l - 1, ptnu), o, o + poly, x, x + poly,
+                   pts, evk_dev(rlk), NULL));
   ct_exp->l = l - 4 - iter;
   ct_exp->nu = out.nu;
   ct_exp->B = out.B;
-  poly_out(&ct_exp->c0, s + 2 * poly, W);
-  poly_out(&ct_exp->c1, s + 3 * poly, W);
+  ct_written(ct_exp);
 }
 
 void he_rlsin(he_ct_t *ct_dest, const double a, const he_ct_t *ct, const he_evk_t *rlk, const he_evk_t *ck,
               const unsigned int iter)
 {
-  const unsigned m = hectx.slots, n = polyctx.n, W = G.info.W, l = ct->l;
-  const size_t poly = (size_t)W * n;
+  const unsigned m = hectx.slots, l = ct->l;
+  const size_t poly = ct_poly();
   if (l < 5 + iter) { fprintf(stderr, "he_rlsin: level %u is below the 5+iter levels the evaluation consumes\n", l); errno = EINVAL; abort(); }
-  uint64_t *s = stage(13 * poly);
   const uint64_t *pts[9];
-  poly_in(s, &ct->c0, W, __func__);
-  poly_in(s + poly, &ct->c1, W, __func__);
-  const double ptnu = exp_plaintexts(a * I, iter, s + 4 * poly, pts, __func__);   /* he-bootstrap.c:458 */
+  const uint64_t *x = ct_dev_in(ct, __func__);
+  uint64_t *dp = dscratch((4 + 9) * poly) + 4 * poly;
+  const double ptnu = exp_plaintexts(a * I, iter, dp, pts, __func__);   /* he-bootstrap.c:458 */
   he_pt_t pt;
   he_alloc_pt(&pt);
   _Complex double *coeff = malloc(sizeof(_Complex double) * m);
@@ -853,27 +1193,33 @@ void he_rlsin(he_ct_t *ct_dest, const double a, const he_ct_t *ct, const he_evk_
   const _Complex double b = 1 / (2 * I * a);                                      /* he-bootstrap.c:465-468 */
   for (unsigned i = 0; i < m; i++) coeff[i] = b;
   he_ecd(&pt, coeff);
-  poly_in(s + 12 * poly, &pt.m, W, __func__);
-  pts[8] = s + 12 * poly;
+  poly_up(dp + 8 * poly, &pt.m, __func__);
+  pts[8] = dp + 8 * poly;
   const struct meta in = {ct->nu, ct->B}, e = exp_meta(l, in, ptnu, iter);
   const struct meta out = m_rs(m_mulpt(m_add(e, e), pt.nu));       /* he_conj keeps nu, B; he_sub updates as he_add */
   const unsigned lf = l - 4 - iter;
-  CK(gq_he_rlsin(ctx(), l, iter, mulpt_dim(l, ptnu), mulpt_dim(l - 1, ptnu), mulpt_dim(lf, pt.nu), s + 2 * poly,
-                 s + 3 * poly, s, s + poly, pts, evk_dev(rlk), evk_dev(ck)));
+  uint64_t *o = ct_dev_out(ct_dest);
+  CK(gq_he_rlsin_dev(ctx(), l, iter, mulpt_dim(l, ptnu), mulpt_dim(l - 1, ptnu), mulpt_dim(lf, pt.nu), o, o + poly,
+                     x, x + poly, pts, evk_dev(rlk), evk_dev(ck), NULL));
   ct_dest->l = lf - 1;
   ct_dest->nu = out.nu;
   ct_dest->B = out.B;
-  poly_out(&ct_dest->c0, s + 2 * poly, W);
-  poly_out(&ct_dest->c1, s + 3 * poly, W);
+  ct_written(ct_dest);
   free(coeff);
   he_free_pt(&pt);
 }
 
-/* diagnostics for tests: coefficients marshalled in / out since load, and whether the direct
- * limb path is active */
+/* diagnostics for tests: coefficients marshalled in / out since load, whether the direct limb path is active, and
+ * how many whole ciphertexts crossed (uploads / downloads, device buffers allocated for shadows) */
 void gpqhe_dropin_stats(unsigned long long *in, unsigned long long *out, int *fast_mpi)
 {
   if (in) *in = G.marshal_in;
   if (out) *out = G.marshal_out;
   if (fast_mpi) *fast_mpi = G.fast_mpi;
+}
+void gpqhe_dropin_ct_stats(unsigned long long *uploads, unsigned long long *downloads, unsigned long long *allocs)
+{
+  if (uploads) *uploads = G.ct_uploads;
+  if (downloads) *downloads = G.ct_downloads;
+  if (allocs) *allocs = G.shadow_allocs;
 }

@@ -565,6 +565,35 @@ extern "C" int gq_host_alloc(void **p, size_t bytes) {
 extern "C" void gq_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 static cudaStream_t pick(gq_ctx *c, void *s) { return s ? (cudaStream_t)s : c->stream; }
+
+// ---- device memory for hosts that do not link the CUDA runtime (dropin/: plain C) -------------------
+extern "C" int gq_dev_alloc(gq_ctx *c, size_t bytes, void **p) {
+  if (!c || !p || bytes == 0) GQ_FAIL("bad argument");
+  GQ_CUDA(cudaSetDevice(c->device));
+  GQ_CUDA(cudaMalloc(p, bytes));
+  return 0;
+}
+extern "C" void gq_dev_free(gq_ctx *c, void *p) {
+  if (!c || !p) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  cudaFree(p);
+}
+extern "C" int gq_dev_upload(gq_ctx *c, void *dst_dev, const void *src_host, size_t bytes, void *stream) {
+  if (!c || !dst_dev || !src_host) GQ_FAIL("null argument");
+  GQ_CUDA(cudaMemcpyAsync(dst_dev, src_host, bytes, cudaMemcpyHostToDevice, pick(c, stream)));
+  return 0;
+}
+extern "C" int gq_dev_download(gq_ctx *c, void *dst_host, const void *src_dev, size_t bytes, void *stream) {
+  if (!c || !dst_host || !src_dev) GQ_FAIL("null argument");
+  GQ_CUDA(cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, pick(c, stream)));
+  return 0;
+}
+extern "C" int gq_dev_copy(gq_ctx *c, void *dst_dev, const void *src_dev, size_t bytes, void *stream) {
+  if (!c || !dst_dev || !src_dev) GQ_FAIL("null argument");
+  GQ_CUDA(cudaMemcpyAsync(dst_dev, src_dev, bytes, cudaMemcpyDeviceToDevice, pick(c, stream)));
+  return 0;
+}
 static bool ntt_ok(const gq_ctx *c, unsigned limb0, unsigned nlimbs) {
   if (limb0 + nlimbs > c->dimub || nlimbs == 0) return false;
   for (unsigned d = limb0; d < limb0 + nlimbs; d++)

@@ -107,6 +107,16 @@ gq_ctx *gq_ctx_lane(gq_ctx *ctx, unsigned i);
 int gq_ctx_lanes_fork(gq_ctx *ctx);
 int gq_ctx_lanes_join(gq_ctx *ctx);
 
+/* ---- device memory and copies for hosts that do not link the CUDA runtime (dropin/ is plain C): the device-resident
+ * shadow of a he_ct_t lives in such buffers (no reference counterpart: struct he_ct keeps N gcry_mpi objects,
+ * src/gpqhe.h:84-91).  upload / download / copy only ENQUEUE on the stream (NULL = the context's); the host buffer of
+ * an upload must stay untouched, and that of a download unread, until the stream has been synchronised. */
+int gq_dev_alloc(gq_ctx *ctx, size_t bytes, void **ptr_dev);
+void gq_dev_free(gq_ctx *ctx, void *ptr_dev);
+int gq_dev_upload(gq_ctx *ctx, void *dst_dev, const void *src_host, size_t bytes, void *stream);
+int gq_dev_download(gq_ctx *ctx, void *dst_host, const void *src_dev, size_t bytes, void *stream);
+int gq_dev_copy(gq_ctx *ctx, void *dst_dev, const void *src_dev, size_t bytes, void *stream);
+
 /* pinned host memory for callers that want fast copies */
 int gq_host_alloc(void **p, size_t bytes);
 void gq_host_free(void *p);

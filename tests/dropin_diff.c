@@ -54,6 +54,14 @@ void gpqhe_ref_he_exp(he_ct_t *ct_exp, _Complex double a, const he_ct_t *ct, con
 void gpqhe_ref_he_rlsin(he_ct_t *ct_dest, const double a, const he_ct_t *ct, const he_evk_t *rlk, const he_evk_t *ck,
                         const unsigned int iter);
 void gpqhe_dropin_stats(unsigned long long *in, unsigned long long *out, int *fast_mpi);
+void gpqhe_dropin_ct_stats(unsigned long long *uploads, unsigned long long *downloads, unsigned long long *allocs);
+/* ciphertexts live in device shadows between drop-in calls (dropin/gpqhe_dropin.c): this program reads and writes
+ * the MPIs directly (eq_poly, the pure-CPU gpqhe_ref_* bodies), so it uses the two hooks a caller that pokes
+ * ct->c0.coeffs is told to use */
+void gpqhe_dropin_sync_ct(const he_ct_t *ct);
+void gpqhe_dropin_touch_ct(const he_ct_t *ct);
+void gpqhe_dropin_wait(void);
+#define REFW(ct, call) do { call; gpqhe_dropin_touch_ct(ct); } while (0)   /* a pure-CPU reference body wrote *ct */
 
 #include <time.h>
 static double now_ms(void)
@@ -62,10 +70,11 @@ static double now_ms(void)
   clock_gettime(CLOCK_MONOTONIC, &t);
   return t.tv_sec * 1e3 + t.tv_nsec * 1e-6;
 }
-/* wall time of the drop-in symbol (host marshalling + crossings + kernels) next to the reference's definition: pure
+/* wall time of the drop-in symbol INCLUDING the write-back of its result into the MPIs (gpqhe_dropin_sync_ct: what an
+ * isolated call whose result is read at once costs; chained calls skip it, see "chained" below) next to the reference's definition: pure
  * CPU for the primitives; for the compositions marked * the reference's host loop, whose primitive calls bind to the
  * drop-in's GPU symbols (one crossing per primitive) */
-#define TIMED2(label, ours, ref) do { double t0 = now_ms(); ours; double t1 = now_ms(); ref; double t2 = now_ms(); \
+#define TIMED2(label, ours, ref) do { double t0 = now_ms(); ours; gpqhe_dropin_sync_ct(&g); double t1 = now_ms(); ref; double t2 = now_ms(); \
   printf("  time %-28s drop-in %10.3f ms   reference %12.3f ms   x%.1f\n", label, t1 - t0, t2 - t1, (t2 - t1) / (t1 - t0 > 1e-6 ? t1 - t0 : 1e-6)); } while (0)
 
 static unsigned npass, nfail;
@@ -84,6 +93,8 @@ static int eq_poly(const poly_mpi_t *a, const poly_mpi_t *b)
 }
 static int eq_ct(const he_ct_t *a, const he_ct_t *b)
 {
+  gpqhe_dropin_sync_ct(a);
+  gpqhe_dropin_sync_ct(b);
   return a->l == b->l && a->nu == b->nu && a->B == b->B && eq_poly(&a->c0, &b->c0) && eq_poly(&a->c1, &b->c1);
 }
 static uint64_t rng_state = 0x9E3779B97F4A7C15ull;
@@ -182,38 +193,38 @@ int main(int argc, char **argv)
 
   /* ---- HE primitives, walking down the levels like tests/gpqhe.c does */
   he_mul(&g, &c1, &c2, &rlk);                                       /* first use uploads the key */
-  TIMED2("he_mul", he_mul(&g, &c1, &c2, &rlk), gpqhe_ref_he_mul(&r, &c1, &c2, &rlk));
+  TIMED2("he_mul", he_mul(&g, &c1, &c2, &rlk), REFW(&r, gpqhe_ref_he_mul(&r, &c1, &c2, &rlk)));
   report("he_mul", eq_ct(&g, &r));
-  TIMED2("he_rs", he_rs(&g), gpqhe_ref_he_rs(&r));
+  TIMED2("he_rs", he_rs(&g), REFW(&r, gpqhe_ref_he_rs(&r)));
   report("he_rs", eq_ct(&g, &r));
-  he_mulpt(&g, &g, &pt2); gpqhe_ref_he_mulpt(&r, &r, &pt2);      /* dest aliases src */
+  he_mulpt(&g, &g, &pt2); REFW(&r, gpqhe_ref_he_mulpt(&r, &r, &pt2));      /* dest aliases src */
   report("he_mulpt (in place)", eq_ct(&g, &r));
-  he_moddown(&g); gpqhe_ref_he_moddown(&r);
+  he_moddown(&g); REFW(&r, gpqhe_ref_he_moddown(&r));
   report("he_moddown", eq_ct(&g, &r));
-  he_mul(&g, &g, &g, &rlk); gpqhe_ref_he_mul(&r, &r, &r, &rlk);   /* he_mul(&x,&x,&x) at a lower level */
+  he_mul(&g, &g, &g, &rlk); REFW(&r, gpqhe_ref_he_mul(&r, &r, &r, &rlk));   /* he_mul(&x,&x,&x) at a lower level */
   report("he_mul (x,x,x) lower level", eq_ct(&g, &r));
   for (unsigned rot = 0; rot < nrot && rot < slots; rot++) {
     he_copy_ct(&g, &c1); he_copy_ct(&r, &c1);
-    he_rot(&g, (int)rot, rk); gpqhe_ref_he_rot(&r, (int)rot, rk);
+    he_rot(&g, (int)rot, rk); REFW(&r, gpqhe_ref_he_rot(&r, (int)rot, rk));
     char nm[40]; snprintf(nm, sizeof nm, "he_rot %u", rot);
     report(nm, eq_ct(&g, &r));
   }
   he_copy_ct(&g, &c2); he_copy_ct(&r, &c2);
-  he_conj(&g, &ck); gpqhe_ref_he_conj(&r, &ck);
+  he_conj(&g, &ck); REFW(&r, gpqhe_ref_he_conj(&r, &ck));
   report("he_conj", eq_ct(&g, &r));
 
   /* ---- coefficient-local ops (src/he-add.c), aliased forms included */
-  he_add(&g, &c1, &c2); gpqhe_ref_he_add(&r, &c1, &c2);
+  he_add(&g, &c1, &c2); REFW(&r, gpqhe_ref_he_add(&r, &c1, &c2));
   report("he_add", eq_ct(&g, &r));
-  he_sub(&g, &g, &c1); gpqhe_ref_he_sub(&r, &r, &c1);            /* dest aliases ct1 */
+  he_sub(&g, &g, &c1); REFW(&r, gpqhe_ref_he_sub(&r, &r, &c1));            /* dest aliases ct1 */
   report("he_sub (in place)", eq_ct(&g, &r));
-  he_add(&g, &g, &g); gpqhe_ref_he_add(&r, &r, &r);              /* x + x: wraps past q/2 */
+  he_add(&g, &g, &g); REFW(&r, gpqhe_ref_he_add(&r, &r, &r));              /* x + x: wraps past q/2 */
   report("he_add (x,x,x)", eq_ct(&g, &r));
-  he_neg(&g); gpqhe_ref_he_neg(&r);
+  he_neg(&g); REFW(&r, gpqhe_ref_he_neg(&r));
   report("he_neg", eq_ct(&g, &r));
-  he_addpt(&g, &c2, &pt2); gpqhe_ref_he_addpt(&r, &c2, &pt2);
+  he_addpt(&g, &c2, &pt2); REFW(&r, gpqhe_ref_he_addpt(&r, &c2, &pt2));
   report("he_addpt", eq_ct(&g, &r));
-  he_subpt(&g, &g, &pt2); gpqhe_ref_he_subpt(&r, &r, &pt2);
+  he_subpt(&g, &g, &pt2); REFW(&r, gpqhe_ref_he_subpt(&r, &r, &pt2));
   report("he_subpt (in place)", eq_ct(&g, &r));
 
   /* ---- he_gemv: device-resident loop vs the reference's host loop over the same primitives */
@@ -251,6 +262,33 @@ int main(int argc, char **argv)
     he_copy_ct(&g, &c2); he_copy_ct(&r, &c2);
     TIMED2("he_rlsin *", he_rlsin(&g, 1.7, &g, &rlk, &ck, iter), gpqhe_ref_he_rlsin(&r, 1.7, &r, &rlk, &ck, iter));   /* in place, as he_bootstrap calls it */
     report("he_rlsin (in place)", eq_ct(&g, &r));
+  }
+
+  /* ---- chained use: 9 primitives on one ciphertext with no host access in between - the
+   * ciphertext crosses once in and once out, everything else runs on its device shadow */
+  if (hectx.L >= 2 && !getenv("DROPIN_DIFF_NO_CHAIN")) {
+    he_copy_ct(&g, &c1); he_copy_ct(&r, &c1);
+    gpqhe_dropin_sync_ct(&g);
+    unsigned long long up0 = 0, dn0 = 0, up1 = 0, dn1 = 0;
+    gpqhe_dropin_ct_stats(&up0, &dn0, NULL);
+    const double t0 = now_ms();
+    he_mul(&g, &g, &g, &rlk); he_rs(&g); he_add(&g, &g, &g); he_rot(&g, 1, rk); he_neg(&g);
+    he_mul(&g, &g, &g, &rlk); he_rs(&g); he_conj(&g, &ck); he_sub(&g, &g, &g);
+    gpqhe_dropin_wait();
+    const double t1 = now_ms();
+    gpqhe_dropin_sync_ct(&g);
+    const double t2 = now_ms();
+    gpqhe_dropin_ct_stats(&up1, &dn1, NULL);
+    REFW(&r, gpqhe_ref_he_mul(&r, &r, &r, &rlk)); REFW(&r, gpqhe_ref_he_rs(&r)); REFW(&r, gpqhe_ref_he_add(&r, &r, &r));
+    REFW(&r, gpqhe_ref_he_rot(&r, 1, rk)); REFW(&r, gpqhe_ref_he_neg(&r));
+    REFW(&r, gpqhe_ref_he_mul(&r, &r, &r, &rlk)); REFW(&r, gpqhe_ref_he_rs(&r)); REFW(&r, gpqhe_ref_he_conj(&r, &ck));
+    REFW(&r, gpqhe_ref_he_sub(&r, &r, &r));
+    const double t3 = now_ms();
+    printf("  time chained x9                   drop-in %10.3f ms (%.3f ms per primitive; + %.3f ms write-back)   reference %12.3f ms   x%.1f\n",
+           t1 - t0, (t1 - t0) / 9, t2 - t1, t3 - t2, (t3 - t2) / (t2 - t0 > 1e-6 ? t2 - t0 : 1e-6));
+    printf("  chained: ciphertext uploads %llu, downloads %llu\n", up1 - up0, dn1 - dn0);
+    const int lazy = getenv("GPQHE_DROPIN_EAGER") == NULL;     /* eager mode writes every result back by design */
+    report("chained x9 (device-resident)", eq_ct(&g, &r) && (!lazy || (up1 - up0 <= 1 && dn1 - dn0 == 1)));
   }
 
   unsigned long long in = 0, out = 0;

@@ -128,6 +128,27 @@ def test_reference_coeff2slot_program_same_output_emulated(emul_env):
     assert _diffs(ours) and _diffs(ours) == _diffs(ref), (ours[-1500:], ref[-1500:])
 
 
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "test-gpqhe")), reason="reference build absent")
+@pytest.mark.parametrize("op", ["inv", "sqrt", "sigmoid", "nrm2", "sum", "idx", "log", "add", "enc"])
+def test_reference_algo_program_same_output_emulated(emul_env, op):
+    """The compositions of src/he-algo.c that are NOT hand-ported (he_inv :131, he_sqrt :166, he_sigmoid, he_log,
+    he_cmp, he_sum, he_idx, he_nrm2) run as the reference wrote them, primitive by primitive, on the device shadows
+    of their ciphertexts (he_copy_ct / he_free_ct / he_dec wrapped): same printed numbers as the reference."""
+    args = [op, "pk", "--logn=6"]
+    _, ours = _run([os.path.join(BUILD, "test-gpqhe"), *args], env=emul_env)
+    _, ref = _run([os.path.join(ROOT, "oracle", "_ref", "test-gpqhe"), *args])
+    assert _verdicts(ours) and _verdicts(ours) == _verdicts(ref), (ours[-1500:], ref[-1500:])
+    assert _diffs(ours) == _diffs(ref), (ours[-1500:], ref[-1500:])
+
+
+def test_dropin_eager_mode_emulated(emul_env):
+    """GPQHE_DROPIN_EAGER=1 writes every result back into the MPIs at once (for callers that read ct->c0.coeffs
+    directly without the sync hook): same results"""
+    env = dict(emul_env, GPQHE_DROPIN_EAGER="1")
+    rc, out = _run([os.path.join(BUILD, "dropin_diff"), "6", "120", "4", "40", "4"], env=env)
+    assert rc == 0 and "PASS" in out, out[-2000:]
+
+
 def test_reference_polymul_program_emulated(emul_env):
     """tests/polymul.c (N=2^7, the polynomial tests/polymul.gp computes): same printout."""
     _, ours = _run([os.path.join(BUILD, "test-polymul")], env=emul_env)
@@ -197,7 +218,7 @@ def test_dropin_diff_gpu(args):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("op", ["mul", "rot", "conj", "gemv", "exp", "rlsin"])
+@pytest.mark.parametrize("op", ["mul", "rot", "conj", "gemv", "exp", "rlsin", "inv", "sqrt", "sigmoid", "nrm2"])
 def test_reference_kat_program_gpu(op):
     """configs[0]: ./test-gpqhe <op> pk at the default params.h ring (N=2^14, logq=438, Delta=2^50,
     -DSUPERCOP stream), the reference's unmodified test program on the GPU library."""
@@ -206,7 +227,7 @@ def test_reference_kat_program_gpu(op):
     clean = re.sub(r"\x1b\[[0-9;]*m", "", out)
     assert "PASSED" in clean and "FAILED" not in clean, clean[-3000:]
     ref_bin = os.path.join(ROOT, "oracle", "_ref", "test-gpqhe")
-    if op in ("mul", "gemv") and os.path.exists(ref_bin) and _have_gcrypt():
+    if op in ("mul", "gemv", "inv") and os.path.exists(ref_bin) and _have_gcrypt():
         _, ref = _run([ref_bin, op, "pk"], timeout=1800)
         assert _diffs(out) and _diffs(out) == _diffs(ref), "decoded results differ from the reference run"
 
