@@ -807,11 +807,19 @@ def run_ours(args):
         exe = os.path.join(ROOT, "dropin", "_build", "dropin_bench")
         if os.path.exists(exe):
             ctx.sync()
-            try:
+            def run_tool(extra_env):
                 out = subprocess.run([exe, str(LOGN), str(LOGQ), str(SLOTS), str(LOGDELTA), str(max(8, args.steps))],
-                                     stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
-                dropin = json.loads(out.stdout.strip().splitlines()[-1]) if out.returncode == 0 else \
-                    {"error": (out.stderr or out.stdout)[-400:]}
+                                     stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900,
+                                     env=dict(os.environ, **extra_env))
+                if out.returncode != 0:
+                    return {"error": (out.stderr or out.stdout)[-400:]}
+                return json.loads(out.stdout.strip().splitlines()[-1])
+            try:
+                dropin = run_tool({})
+                if "chained" in dropin:
+                    dropin["value"], dropin["unit"] = dropin["chained"]["ops_per_s"], "ops/s"
+                    slow = run_tool({"GPQHE_DROPIN_SLOW_MPI": "1"})      # gcry_mpi_print / scan instead of the limb view
+                    dropin["slow_mpi"] = {k: slow.get(k) for k in ("mpi_path", "isolated", "chained", "error") if k in slow}
             except Exception as ex:
                 dropin = {"error": repr(ex)}
         else:
