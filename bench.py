@@ -370,7 +370,7 @@ def run_ours(args):
                 "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({pk_src})",
                 "algorithmic_bytes_per_launch": ntt_bytes, "kernel_ms_per_launch": ms_tile,
                 "note": "this kernel is bound by the integer-multiply pipe, not HBM: ncu shows sm__pipe_fmaheavy_cycles_active "
-                        "61 % / alu 48 % / dram 12 % (profiles/r01_call5_full.md); the HBM fraction is reported as the contract asks"}
+                        "61 % / alu 46 % / dram 13 % (profiles/r02_call2_full.md; SASS mix in profiles/r02_sass_fwd_tile.md); the HBM fraction is reported as the contract asks"}
     # integer-pipe roofline: what the tile kernel achieves in butterflies/s against the measured
     # register-resident butterfly rate of this GPU (gq_peak.cu)
     bf_peak, mw_peak = C.c_double(0), C.c_double(0)
@@ -535,6 +535,10 @@ def run_ours(args):
         gpts[:, 1:, :] = (gpts[:, :1, :] >> 63)                                          # sign extension
         gout = torch.empty((2, W, n), dtype=torch.int64, device=dev)
         ptsv = VP(*[gpts.data_ptr() + k * poly for k in range(NROT)])
+
+        # the synthetic diagonals are below 2^LOGDELTA in magnitude: with the bound he_gemv accumulates each giant step
+        # in the NTT domain (one inverse NTT + CRT per giant step instead of one per he_mulpt)
+        ck(lib.gq_ctx_set_plaintext_bits(h, LOGDELTA + 1))
 
         def gemv_step(i):
             ck(lib.gq_he_gemv_dev(h, L, 4, 4, gdim, gout.data_ptr(), gout.data_ptr() + poly, src.data_ptr(),

@@ -327,8 +327,10 @@ static void poly_out(poly_mpi_t *r, const uint64_t *src, unsigned W)
 
 /* ------------------------------------------------------------------- context mirror */
 static void shadows_drop_all(void);
+static void diag_drop_all(void);
 static void ctx_drop(void)
 {
+  diag_drop_all();
   shadows_drop_all();
   for (unsigned k = 0; k < G.nevk; k++) gq_evk_destroy(G.evk[k].dev);
   G.nevk = 0;
@@ -941,13 +943,79 @@ static void gemv_split(unsigned *n1, unsigned *n2)
   *n2 = m / *n1;
 }
 
-/* diagonal k = i*n1+j of A, pre-rotated by -i*n1 slots, encoded at scale Delta (he-algo.c:70-72), uploaded
- * as word-major polys to the DEVICE buffer dst + k*poly; pt keeps the metadata of the last he_ecd */
-static void gemv_diagonals(const _Complex double *A, unsigned n1, uint64_t *dst, const uint64_t **pts,
-                           he_pt_t *pt, const char *who)
+/* The encoded diagonals of a matrix, device resident and cached.  The reference re-encodes every diagonal on every
+ * he_gemv call (he_ecd at src/he-algo.c:70-72: an inverse canonical embedding plus N double_to_mpi per diagonal,
+ * 1-2 ms each at N = 2^14 - for he_coeff2slot's 4 x slots diagonals that is 10 times the device work).  he_ecd is a
+ * pure function of the matrix (and of the context), so the encodings are kept on the device keyed by the EXACT
+ * contents of A (a copy is compared, no hashing risk) and reused as long as the context lives; the matrices of
+ * bootstrapctx never change after he_bootstrapctx_init.  Diagonal k = i*n1+j of A is pre-rotated by -i*n1 slots and
+ * encoded at scale Delta (he-algo.c:70-72), stored as word-major polys at dev + k*poly.  `bits` bounds the encoded
+ * coefficients (|m| < 2^bits), measured while marshalling: it lets the device accumulate a giant step in the NTT
+ * domain (gq_ctx_set_plaintext_bits).  Bounded by GPQHE_DROPIN_DIAG_CACHE_MB (default 4096), least recently used out. */
+struct diag_entry {
+  _Complex double *A;       /* private copy of the matrix, m*m entries */
+  unsigned m, n1;
+  uint64_t *dev;            /* m polys */
+  double nu;                /* pt.nu of he_ecd (the same for every diagonal: he-encode.c) */
+  unsigned bits;
+  unsigned long long used;
+};
+static struct diag_entry *G_diag;
+static unsigned G_ndiag, G_capdiag;
+static unsigned long long G_diag_clock, G_diag_hits, G_diag_misses;
+
+static void diag_drop(unsigned i)
+{
+  gq_dev_free(ctx(), G_diag[i].dev);        /* waits for the stream first */
+  free(G_diag[i].A);
+  G_diag[i] = G_diag[--G_ndiag];
+}
+static void diag_drop_all(void)
+{
+  while (G_ndiag) { if (G.ctx) gq_dev_free(G.ctx, G_diag[G_ndiag - 1].dev); free(G_diag[G_ndiag - 1].A); G_ndiag--; }
+}
+
+static const struct diag_entry *diag_get(const _Complex double *A, unsigned n1, const char *who)
 {
   const unsigned m = hectx.slots;
-  const size_t poly = ct_poly();
+  const size_t poly = ct_poly(), abytes = sizeof(_Complex double) * m * m;
+  G_diag_clock++;
+  for (unsigned i = 0; i < G_ndiag; i++)
+    if (G_diag[i].m == m && G_diag[i].n1 == n1 && !memcmp(G_diag[i].A, A, abytes)) {
+      G_diag[i].used = G_diag_clock;
+      G_diag_hits++;
+      return &G_diag[i];
+    }
+  G_diag_misses++;
+  static size_t cap;
+  if (!cap) {
+    const char *e = getenv("GPQHE_DROPIN_DIAG_CACHE_MB");
+    long long mb = e ? atoll(e) : 4096;
+    cap = (size_t)(mb < 0 ? 0 : mb) << 20;
+  }
+  size_t held = 0;
+  for (unsigned i = 0; i < G_ndiag; i++) held += (size_t)G_diag[i].m * poly * 8;
+  while (G_ndiag && held + (size_t)m * poly * 8 > cap) {
+    unsigned lru = 0;
+    for (unsigned i = 1; i < G_ndiag; i++) if (G_diag[i].used < G_diag[lru].used) lru = i;
+    if (G_diag_clock - G_diag[lru].used < 8) break;      /* one call holds up to 4 matrices (he_coeff2slot) */
+    held -= (size_t)G_diag[lru].m * poly * 8;
+    diag_drop(lru);
+  }
+  if (G_ndiag == G_capdiag) {
+    G_capdiag = G_capdiag ? 2 * G_capdiag : 8;
+    G_diag = realloc(G_diag, G_capdiag * sizeof *G_diag);
+  }
+  struct diag_entry *e = &G_diag[G_ndiag++];
+  e->m = m; e->n1 = n1; e->used = G_diag_clock; e->bits = 1;
+  e->A = malloc(abytes);
+  if (!e->A) die(who);
+  memcpy(e->A, A, abytes);
+  void *dv = NULL;
+  CK(gq_dev_alloc(ctx(), (size_t)m * poly * 8, &dv));
+  e->dev = dv;
+  he_pt_t pt;
+  he_alloc_pt(&pt);
   _Complex double *d = malloc(sizeof(_Complex double) * m);
   if (!d) die(who);
   for (unsigned k = 0; k < m; k++) {
@@ -956,11 +1024,22 @@ static void gemv_diagonals(const _Complex double *A, unsigned n1, uint64_t *dst,
       const unsigned u = (t + m - shift % m) % m;                       /* slot after rotating by -shift */
       d[t] = A[(size_t)u * m + (k + u) % m];
     }
-    he_ecd(pt, d);
-    poly_up(dst + (size_t)k * poly, &pt->m, who);
-    pts[k] = dst + (size_t)k * poly;
+    he_ecd(&pt, d);
+    for (unsigned i = 0; i < polyctx.n; i++) {
+      const unsigned nb = gcry_mpi_get_nbits(pt.m.coeffs[i]) + 1;       /* |m_i| < 2^nbits */
+      if (nb > e->bits) e->bits = nb;
+    }
+    poly_up(e->dev + (size_t)k * poly, &pt.m, who);
   }
+  e->nu = pt.nu;
   free(d);
+  he_free_pt(&pt);
+  return e;
+}
+void gpqhe_dropin_diag_stats(unsigned long long *hits, unsigned long long *misses)
+{
+  if (hits) *hits = G_diag_hits;
+  if (misses) *misses = G_diag_misses;
 }
 
 /* metadata of he_gemv: the reference's sequence of he_mulpt (he-mult.c:162-164), he_add (he-add.c:36-38)
@@ -999,24 +1078,22 @@ void he_gemv(he_ct_t *ct_dest, const _Complex double *A, const he_ct_t *ct, cons
   gemv_split(&n1, &n2);
   const size_t poly = ct_poly();
   const uint64_t *a = ct_dev_in(ct, __func__);
-  uint64_t *dp = dscratch((4 + (size_t)m) * poly) + 4 * poly;      /* slots 0..3 belong to pt_dev() */
-  he_pt_t pt;
-  he_alloc_pt(&pt);
+  const struct diag_entry *dg = diag_get(A, n1, __func__);
   const uint64_t **pts = malloc(sizeof(*pts) * m);
   if (!pts) die(__func__);
-  gemv_diagonals(A, n1, dp, pts, &pt, __func__);
+  for (unsigned k = 0; k < m; k++) pts[k] = dg->dev + (size_t)k * poly;
   const gq_evk **keys = gemv_keys(rk, n1, __func__);
-  const unsigned dim = (gcry_mpi_get_nbits(hectx.q[l]) + log2(pt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
+  const unsigned dim = (gcry_mpi_get_nbits(hectx.q[l]) + log2(dg->nu) + polyctx.logn) / GPQHE_LOGP + 1;
   double nu_o, B_o;
-  gemv_meta(ct->nu, ct->B, pt.nu, n1, n2, &nu_o, &B_o);
+  gemv_meta(ct->nu, ct->B, dg->nu, n1, n2, &nu_o, &B_o);
   uint64_t *o = ct_dev_out(ct_dest);
+  CK(gq_ctx_set_plaintext_bits(ctx(), dg->bits));
   CK(gq_he_gemv_dev(ctx(), l, n1, n2, dim, o, o + poly, a, a + poly, pts, keys, NULL));
   ct_dest->l = l - 1;
   ct_dest->nu = nu_o;
   ct_dest->B = B_o;
   ct_written(ct_dest);
   free(pts); free(keys);
-  he_free_pt(&pt);
 }
 
 /* ---- he_coeff2slot (src/he-bootstrap.c:359-409), device resident ----------------------------------
@@ -1032,23 +1109,28 @@ void he_coeff2slot(he_ct_t *ct_real, he_ct_t *ct_imag, const he_ct_t *ct, const 
   const size_t poly = ct_poly();
   if (ct_real == ct_imag) { fprintf(stderr, "he_coeff2slot: the two outputs must be distinct ciphertexts\n"); errno = EINVAL; abort(); }
   const uint64_t *a = ct_dev_in(ct, __func__);
-  uint64_t *dbase = dscratch((5 + 4 * (size_t)m) * poly);
-  uint64_t *dcpt = dbase + 4 * poly, *dp = dbase + 5 * poly;
-  he_pt_t pt, cpt;
-  he_alloc_pt(&pt);
+  he_pt_t cpt;
   he_alloc_pt(&cpt);
   he_const_pt(&cpt, 1 / polyctx.n);                                     /* he-bootstrap.c:385, integer division as there */
-  poly_up(dcpt, &cpt.m, __func__);
+  const uint64_t *dcpt = pt_dev(&cpt, 1, __func__);
   const uint64_t **pts = malloc(sizeof(*pts) * 4 * m);
   if (!pts) die(__func__);
   const _Complex double *mats[4] = {bootstrapctx.U0_conjT, bootstrapctx.U0_T, bootstrapctx.U1_conjT, bootstrapctx.U1_T};
-  for (unsigned k = 0; k < 4; k++)
-    gemv_diagonals(mats[k], n1, dp + (size_t)k * m * poly, pts + (size_t)k * m, &pt, __func__);
+  double ptnu = 0;
+  unsigned ptbits = 1;
+  for (unsigned k = 0; k < 4; k++) {
+    const struct diag_entry *dg = diag_get(mats[k], n1, __func__);
+    uint64_t *dv = dg->dev;                  /* the entry may move when the next matrix is inserted; its buffer does not */
+    ptnu = dg->nu;
+    if (dg->bits > ptbits) ptbits = dg->bits;
+    for (unsigned t = 0; t < m; t++) pts[(size_t)k * m + t] = dv + (size_t)t * poly;
+  }
   const gq_evk **keys = gemv_keys(rk, n1, __func__);
-  const unsigned dim_gemv = (gcry_mpi_get_nbits(hectx.q[l]) + log2(pt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
+  CK(gq_ctx_set_plaintext_bits(ctx(), ptbits));
+  const unsigned dim_gemv = (gcry_mpi_get_nbits(hectx.q[l]) + log2(ptnu) + polyctx.logn) / GPQHE_LOGP + 1;
   const unsigned dim_pt = (gcry_mpi_get_nbits(hectx.q[l - 1]) + log2(cpt.nu) + polyctx.logn) / GPQHE_LOGP + 1;
   double nu_g, B_g;
-  gemv_meta(ct->nu, ct->B, pt.nu, n1, n2, &nu_g, &B_g);                 /* he_conj keeps nu and B */
+  gemv_meta(ct->nu, ct->B, ptnu, n1, n2, &nu_g, &B_g);                  /* he_conj keeps nu and B */
   /* an output may alias the input (the device call reads `a` up to its last he_gemv): such an output is computed
    * into a spare buffer and copied */
   uint64_t *o_re = ct_dev_out(ct_real), *o_im = ct_dev_out(ct_imag);
@@ -1069,7 +1151,6 @@ void he_coeff2slot(he_ct_t *ct_real, he_ct_t *ct_imag, const he_ct_t *ct, const 
     ct_written(outs[k]);
   }
   free(pts); free(keys);
-  he_free_pt(&pt);
   he_free_pt(&cpt);
 }
 

@@ -98,6 +98,7 @@ SIGNATURES = {
     "gq_ntt_batch_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.c_int, vp]),
     "gq_poly_rns_mul_batch_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp]),
     "gq_he_mul_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "gq_ctx_set_plaintext_bits": (C.c_int, [vp, C.c_uint]),
     "gq_dev_alloc": (C.c_int, [vp, C.c_size_t, C.POINTER(vp)]),
     "gq_dev_free": (None, [vp, vp]),
     "gq_dev_upload": (C.c_int, [vp, vp, vp, C.c_size_t, vp]),

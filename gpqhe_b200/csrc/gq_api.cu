@@ -5,6 +5,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -529,6 +530,14 @@ extern "C" int gq_ctx_dims(const gq_ctx *c, unsigned l, unsigned *dt, unsigned *
   if (!c || !c->has_he || l > c->L) GQ_FAIL("bad argument");
   if (dt) *dt = dim_tensor(c, l);
   if (dk) *dk = dim_ks(c, l);
+  return 0;
+}
+// Bound on the plaintext coefficients handed to gq_he_gemv / gq_he_coeff2slot / gq_he_slot2coeff from now on:
+// |m| < 2^bits for every coefficient of every encoded diagonal; 0 = unknown (the per-term path of he_gemv runs).
+extern "C" int gq_ctx_set_plaintext_bits(gq_ctx *c, unsigned bits) {
+  if (!c) GQ_FAIL("null context");
+  if (bits > 64u * GQ_MAX_W) GQ_FAIL("bound out of range");
+  c->pt_bits = bits;
   return 0;
 }
 extern "C" int gq_ctx_sync(gq_ctx *c) {
@@ -1214,26 +1223,72 @@ extern "C" int gq_he_gemv_dev(gq_ctx *c, unsigned l, unsigned n1, unsigned n2, u
   for (unsigned i = 0; i < n2; i++) if (!rk[i * n1]) GQ_FAIL("missing giant-step rotation key");
   for (unsigned k = 0; k < n1 * n2; k++) if (!pts[k]) GQ_FAIL("missing diagonal");
   const size_t poly = (size_t)c->W * c->n;
+  const size_t n = c->n;
   // giant steps are independent until they are summed: with compute lanes (gq_ctx_set_lanes) and the
   // context's own stream, giant step i runs on lane i % K; the sums are taken afterwards in the reference's
   // order on the context's stream
   const unsigned K = (c->parent || stream) ? 1u : (unsigned)c->lanes.size() + 1;
-  if (ensure_slot(c, GQ_SLOT_GEMV, (2 * (size_t)n1 + 2 * (size_t)n2 + 2 * (size_t)K) * poly * 8)) return 1;
+  // NTT-domain accumulation.  The reference computes inner_i = smod(sum_j smod(he_mulpt(rot_j(ct), pt_ij))) with one
+  // decompose / NTT / inverse NTT / CRT per term (src/he-algo.c:65-79, src/he-mult.c:159-196).  Each he_mulpt is
+  // smod_q(X_j), X_j the exact integer product, as long as |X_j| < P_dim / 2; smod_q of a sum of representatives is
+  // smod_q of the exact sum, so inner_i = smod_q(sum_j X_j), and that sum is what ONE inverse NTT + CRT of
+  // sum_j NTT(c_j) * NTT(m_ij) returns provided |sum_j X_j| < P_dimX / 2.  Both bounds follow from |c| <= q_l / 2 and
+  // the caller's plaintext bound |m| < 2^pt_bits (gq_ctx_set_plaintext_bits; the drop-in measures it while it
+  // marshals the diagonals): |X_j| <= n * 2^(bits(q_l) - 2) * 2^pt_bits.  Without a bound, or when a bound fails (the
+  // reference's own he_mulpt would wrap modulo P_dim: reproduced only by the per-term path), the per-term path runs.
+  unsigned dimX = 0;
+  if (c->pt_bits && !getenv("GPQHE_B200_GEMV_PER_TERM") && dim >= 1 && dim <= c->dimub) {
+    unsigned lg = 0;
+    while ((1u << lg) < n1) lg++;
+    const unsigned term = c->logn + c->ql[l].bits() - 1 + c->pt_bits;      // |X_j| < 2^term (one spare bit)
+    const bool ref_exact = c->basis[dim - 1].dev.WT && term + 3 <= c->basis[dim - 1].dev.bitsP;
+    for (unsigned D = dim; ref_exact && D <= c->dimub && !dimX; D++)
+      if (c->basis[D - 1].dev.WT && term + lg + 3 <= c->basis[D - 1].dev.bitsP) dimX = D;
+    if (dimX && (!fused_inv_ok(c, 0, dimX) || (2 * (size_t)n1 + (size_t)n1 * n2) * dimX * n * 8 > ((size_t)6 << 30))) dimX = 0;
+  }
+  const size_t hat_words = dimX ? (2 * (size_t)n1 + (size_t)n1 * n2) * dimX * n : 0;
+  if (ensure_slot(c, GQ_SLOT_GEMV, ((2 * (size_t)n1 + 2 * (size_t)n2 + 2 * (size_t)K) * poly + hat_words) * 8)) return 1;
   uint64_t *base = (uint64_t *)c->slot[GQ_SLOT_GEMV];
   uint64_t *accs = base + 2 * (size_t)n1 * poly, *Ts = accs + 2 * (size_t)n2 * poly;
+  uint64_t *Xhat = Ts + 2 * (size_t)K * poly, *Mhat = Xhat + 2 * (size_t)n1 * dimX * n;
   std::vector<unsigned> rots(n1);
   std::vector<uint64_t *> r0(n1), r1(n1);
   for (unsigned j = 0; j < n1; j++) { rots[j] = j; r0[j] = base + 2 * (size_t)j * poly; r1[j] = r0[j] + poly; }
   if (gq_he_rot_hoisted_dev(c, l, n1, rots.data(), r0.data(), r1.data(), a0, a1, rk, stream)) return 1;
+  if (dimX) {
+    // NTT(decompose(.)) of the 2*n1 rotated polynomials and of the n1*n2 encoded diagonals, over dimX limbs, once
+    cudaStream_t st0 = pick(c, stream);
+    std::vector<const uint64_t *> src;
+    for (unsigned j = 0; j < n1; j++) { src.push_back(r0[j]); src.push_back(r1[j]); }
+    for (unsigned k = 0; k < n1 * n2; k++) src.push_back(pts[k]);
+    for (size_t g0 = 0; g0 < src.size(); g0 += 4) {
+      const unsigned cnt = (unsigned)std::min<size_t>(4, src.size() - g0);
+      if (decompose_dev(c, 0, dimX, ptrs(src[g0], cnt > 1 ? src[g0 + 1] : nullptr, cnt > 2 ? src[g0 + 2] : nullptr,
+                                        cnt > 3 ? src[g0 + 3] : nullptr),
+                        c->W, cnt, Xhat + g0 * dimX * n, st0)) return 1;
+    }
+    if (ntt_internal(c, 0, dimX, (unsigned)src.size(), Xhat, false, st0)) return 1;
+  }
   if (K > 1 && gq_ctx_lanes_fork(c)) return 1;
   for (unsigned i = 0; i < n2; i++) {
     gq_ctx *ln = (K > 1) ? gq_ctx_lane(c, i % K) : c;
     void *ls = (K > 1) ? nullptr : stream;
     uint64_t *acc = accs + 2 * (size_t)i * poly, *T = Ts + 2 * (size_t)(i % K) * poly;
-    for (unsigned j = 0; j < n1; j++) {
-      uint64_t *dst = (j == 0) ? acc : T;
-      if (gq_he_mulpt_dev(ln, l, dim, dst, dst + poly, r0[j], r1[j], pts[i * n1 + j], ls)) return 1;
-      if (j && linear_dev(ln, l, acc, acc + poly, acc, acc + poly, T, T + poly, 0, 0, ls)) return 1;
+    if (dimX) {
+      // one giant step: sum_j NTT(rot_j) * NTT(pt_ij) formed in the load of ONE inverse transform, one CRT
+      cudaStream_t lst = pick(ln, ls);
+      if (ensure_slot(ln, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8)) return 1;
+      uint64_t *Y = (uint64_t *)ln->slot[GQ_SLOT_LIMB_B];
+      const bool pre = crt_pre_ok(c, dimX, c->qmod[l].dev);
+      if (ntt_inv_fused(ln, GQ_NTTF_GEMV, 0, dimX, Xhat, Y, Mhat + (size_t)i * n1 * dimX * n, nullptr, n1, lst,
+                        pre ? dimX : 0)) return 1;
+      if (reconstruct_dev(ln, dimX, Y, c->qmod[l].dev, ptrs(acc, acc + poly), c->W, 2, lst, 0, 0, pre)) return 1;
+    } else {
+      for (unsigned j = 0; j < n1; j++) {
+        uint64_t *dst = (j == 0) ? acc : T;
+        if (gq_he_mulpt_dev(ln, l, dim, dst, dst + poly, r0[j], r1[j], pts[i * n1 + j], ls)) return 1;
+        if (j && linear_dev(ln, l, acc, acc + poly, acc, acc + poly, T, T + poly, 0, 0, ls)) return 1;
+      }
     }
     if (gq_he_rot_dev(ln, l, i * n1, acc, acc + poly, rk[i * n1], ls)) return 1;
   }

@@ -65,6 +65,7 @@ struct gq_ctx {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   // staging of the batched host entry points when lanes are in use
   std::vector<cudaEvent_t> ev_batch;
+  unsigned pt_bits = 0;          // gq_ctx_set_plaintext_bits: |m| < 2^pt_bits for the plaintexts of he_gemv (0 = unknown)
   bool lazy_ntt = true;          // internal pipelines use gq_ntt_lazy.cu when every prime allows it
 
   // D > 0: inverse transforms end with the CRT pre-multiplication of the basis {p_0..p_(D-1)} folded into N^-1

@@ -15,8 +15,8 @@ int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nli
 
 // pointwise stage fused into the load of the lazy inverse transform (gq_ntt_lazy.cu): x -> y = invntt(product)
 //   TENSOR x[4][D][n] -> y[3][D][n];  EVK / EVKPERM x[D][n], e0, e1 -> y[2][D][n];  PT x[3][D][n] -> y[2][D][n];
-//   MUL x[2][D][n] -> y[D][n]
-enum { GQ_NTTF_TENSOR = 1, GQ_NTTF_EVK = 2, GQ_NTTF_EVKPERM = 3, GQ_NTTF_PT = 4, GQ_NTTF_MUL = 5 };
+//   MUL x[2][D][n] -> y[D][n];  GEMV x[T][2][D][n], e0[T][D][n], g = T -> y[2][D][n] = sum_t x[t][k] * e0[t]
+enum { GQ_NTTF_TENSOR = 1, GQ_NTTF_EVK = 2, GQ_NTTF_EVKPERM = 3, GQ_NTTF_PT = 4, GQ_NTTF_MUL = 5, GQ_NTTF_GEMV = 6 };
 int gq_launch_ntt_lazy_fused(const GqNttTables &tb, int mode, const uint64_t *x, uint64_t *y, const uint64_t *e0,
                              const uint64_t *e1, unsigned g, int limb0, int nlimbs, cudaStream_t st);
 

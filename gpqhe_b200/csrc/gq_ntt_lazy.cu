@@ -251,9 +251,12 @@ k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlim
 //   GQ_INV_EVKPERM the same with x read through the slot permutation of the Galois map g (hoisted rotations)
 //   GQ_INV_PT      x[3][D][n] = NTT(c0, c1, m) -> y[2][D][n] = c0*m, c1*m                          (he-mult.c:186-189)
 //   GQ_INV_MUL     x[2][D][n] = NTT(a, b) -> y[1][D][n] = a*b                                       (poly.c:96-101)
+//   GQ_INV_GEMV    x[T][2][D][n] = NTT(c0, c1) of T rotated ciphertexts, e0[T][D][n] = NTT of T plaintexts ->
+//                  y[2][D][n] = sum_t c0_t*m_t, sum_t c1_t*m_t: one giant step of he_gemv (he-algo.c:65-79)
+//                  accumulated in the NTT domain, one inverse transform for T he_mulpt calls (T = S.g)
 // Products are the pseudo-Mersenne ones of gq_arith.h (canonical, the residue poly_rns_mul stores); the host
 // selects these modes only when every prime of the range has that shape (pm_ok), else the separate kernels run.
-enum { GQ_INV_PLAIN = 0, GQ_INV_TENSOR, GQ_INV_EVK, GQ_INV_EVKPERM, GQ_INV_PT, GQ_INV_MUL };
+enum { GQ_INV_PLAIN = 0, GQ_INV_TENSOR, GQ_INV_EVK, GQ_INV_EVKPERM, GQ_INV_PT, GQ_INV_MUL, GQ_INV_GEMV };
 
 struct InvSrc {
   const uint64_t *x;        // inputs (limb-major batches as above)
@@ -278,6 +281,17 @@ GQ_DEV uint64_t inv_load(const InvSrc &S, const GqPM &pm, int n, int logn, int n
   }
   if (MODE == GQ_INV_PT) return gq_mulm_pm(S.x[(size_t)b * stride + lp], S.x[2 * stride + lp], pm);
   if (MODE == GQ_INV_MUL) return gq_mulm_pm(S.x[lp], S.x[stride + lp], pm);
+  if (MODE == GQ_INV_GEMV) {
+    // products below p^2 < 2^118 (1 + 2^-30): four of them stay below the 2^(2s+3) gq_reduce_pm accepts, so the
+    // 128-bit sum is folded every four terms and the canonical partial result rides along into the next group
+    GqWide acc; acc.lo = 0; acc.hi = 0;
+    const int T = (int)S.g;
+    for (int t = 0; t < T; t++) {
+      acc = gq_add_wide(acc, gq_mul_wide(S.x[(size_t)(2 * t + b) * stride + lp], S.e0[(size_t)t * stride + lp]));
+      if ((t & 3) == 3 || t == T - 1) { acc.lo = gq_reduce_pm(acc, pm.p, pm.c, pm.s); acc.hi = 0; }
+    }
+    return acc.lo;
+  }
   return S.x[(size_t)b * stride + lp];
 }
 
@@ -498,6 +512,7 @@ int gq_launch_ntt_lazy_fused(const GqNttTables &tb, int mode, const uint64_t *x,
     case GQ_NTTF_EVKPERM: return launch_inv<GQ_INV_EVKPERM>(tb, src, y, limb0, nlimbs, 2, st, 0);
     case GQ_NTTF_PT: return launch_inv<GQ_INV_PT>(tb, src, y, limb0, nlimbs, 2, st, 0);
     case GQ_NTTF_MUL: return launch_inv<GQ_INV_MUL>(tb, src, y, limb0, nlimbs, 1, st, 0);
+    case GQ_NTTF_GEMV: return g ? launch_inv<GQ_INV_GEMV>(tb, src, y, limb0, nlimbs, 2, st, 0) : -1;
   }
   return -1;
 }

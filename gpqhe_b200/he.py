@@ -345,6 +345,25 @@ class HeContext:
             arr([o[1].ctypes.data for o in outs]), _ptr(c0), _ptr(c1), arr([rk[r]._h for r in rots])))
         return [HeCt(ct.l, o0, o1, ct.nu, ct.B) for o0, o1 in outs]
 
+    def set_plaintext_bits(self, bits: int):
+        """gq_ctx_set_plaintext_bits: |m| < 2^bits for the plaintexts of the next he_gemv-type calls (0 = unknown)."""
+        capi.check(self._lib, self._lib.gq_ctx_set_plaintext_bits(self._h, int(bits)))
+
+    @staticmethod
+    def plaintext_bits(pts) -> int:
+        """smallest b with |m| < 2^b over every coefficient of the word-major plaintexts"""
+        best = 1
+        for p in pts:
+            m = np.asarray(p.m, dtype=np.uint64)
+            neg = (m[-1] >> np.uint64(63)).astype(bool)
+            mag = np.where(neg[None, :], ~m, m)          # |m| - 1 for negatives: same bit length bound
+            for w in range(m.shape[0] - 1, -1, -1):
+                top = int(mag[w].max())
+                if top:
+                    best = max(best, 64 * w + top.bit_length() + 1)
+                    break
+        return best
+
     def he_gemv_encoded(self, ct: HeCt, pts, n1: int, n2: int, rk) -> HeCt:
         """The ciphertext arithmetic of he_gemv(ct_dest, A, ct, rk) (src/he-algo.c:47-90) with the
         diagonals already encoded: pts[i*n1+j] is the HePt of zrotdiag(A, i*n1+j, -i*n1).

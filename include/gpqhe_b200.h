@@ -83,6 +83,12 @@ int gq_ctx_prime_consts(const gq_ctx *ctx, unsigned limb, uint64_t out[4]);
 /* limb counts at level l: he-mult.c:99 (tensor) and he-mult.c:51 (key switch) */
 int gq_ctx_dims(const gq_ctx *ctx, unsigned l, unsigned *dim_tensor, unsigned *dim_ks);
 int gq_ctx_sync(gq_ctx *ctx);
+/* Bound on the encoded plaintexts handed to gq_he_gemv / gq_he_coeff2slot / gq_he_slot2coeff (host and _dev forms)
+ * from now on: |m| < 2^bits for every coefficient (he_ecd output is about Delta * |value|, src/he-encode.c:53-66).
+ * With a bound he_gemv accumulates the n1 products of a giant step in the NTT domain and does ONE inverse NTT + CRT
+ * instead of n1 (src/he-algo.c:65-79 does one per he_mulpt) - the same bits, proof in gq_api.cu.  bits = 0 (the
+ * default): unknown, every he_mulpt is evaluated on its own. */
+int gq_ctx_set_plaintext_bits(gq_ctx *ctx, unsigned bits);
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 unsigned long long gq_ctx_launch_count(const gq_ctx *ctx);
 void *gq_ctx_stream(gq_ctx *ctx); /* the context's cudaStream_t */

@@ -74,7 +74,7 @@ static double now_ms(void)
  * isolated call whose result is read at once costs; chained calls skip it, see "chained" below) next to the reference's definition: pure
  * CPU for the primitives; for the compositions marked * the reference's host loop, whose primitive calls bind to the
  * drop-in's GPU symbols (one crossing per primitive) */
-#define TIMED2(label, ours, ref) do { double t0 = now_ms(); ours; gpqhe_dropin_sync_ct(&g); double t1 = now_ms(); ref; double t2 = now_ms(); \
+#define TIMED2(label, ours, ref) do { double t0 = now_ms(); ours; gpqhe_dropin_sync_ct(&g); double t1 = now_ms(); ref; gpqhe_dropin_sync_ct(&r); double t2 = now_ms(); \
   printf("  time %-28s drop-in %10.3f ms   reference %12.3f ms   x%.1f\n", label, t1 - t0, t2 - t1, (t2 - t1) / (t1 - t0 > 1e-6 ? t1 - t0 : 1e-6)); } while (0)
 
 static unsigned npass, nfail;

@@ -276,6 +276,21 @@ def check_gemv(lib_path, logn, q, Delta, n1=2, n2=2, logqub=0, seed=3):
         want = o.he_gemv_encoded(oc, {"l": l, "c0": a0, "c1": a1}, ms, ctx.mulpt_dim(l, nu), n1, n2, keys)
         assert got.l == want["l"]
         assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], "he_gemv"
+        # with a plaintext bound the n1 products of a giant step are accumulated in the NTT domain (one inverse NTT
+        # + CRT per giant step): same bits, fewer launches; a bound too large for any basis falls back
+        before = ctx.launch_count
+        got = ctx.he_gemv_encoded(g.HeCt(l, g.ints_to_big(a0, W), g.ints_to_big(a1, W)), pts, n1, n2, dkeys)
+        per_term = ctx.launch_count - before
+        ctx.set_plaintext_bits(ctx.plaintext_bits(pts))
+        before = ctx.launch_count
+        got = ctx.he_gemv_encoded(g.HeCt(l, g.ints_to_big(a0, W), g.ints_to_big(a1, W)), pts, n1, n2, dkeys)
+        accumulated = ctx.launch_count - before
+        assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], "he_gemv, NTT-domain accumulation"
+        assert accumulated < per_term, (accumulated, per_term)
+        ctx.set_plaintext_bits(64 * W)
+        got = ctx.he_gemv_encoded(g.HeCt(l, g.ints_to_big(a0, W), g.ints_to_big(a1, W)), pts, n1, n2, dkeys)
+        assert g.big_to_ints(got.c0) == want["c0"] and g.big_to_ints(got.c1) == want["c1"], "he_gemv, bound too large"
+        ctx.set_plaintext_bits(ctx.plaintext_bits(pts))
         # giant steps spread over compute lanes: same bits, twice (scratch of every lane reused)
         ctx.set_lanes(3)
         for _ in range(2):
@@ -546,8 +561,10 @@ def check_compositions_full_size(lib_path, logn=16, q=1 << 438, Delta=1 << 50, n
             want = ctx.he_rot(hc(a), r, rk)
             eq(got.c0, want.c0, f"hoisted rotation {r} c0"); eq(got.c1, want.c1, f"hoisted rotation {r} c1")
 
-        # he_gemv (configs[3])
+        # he_gemv (configs[3]); the plaintext bound switches the device call to NTT-domain accumulation, the
+        # composition below still runs one he_mulpt per term
         pts = [pt() for _ in range(slots)]
+        ctx.set_plaintext_bits(ctx.plaintext_bits(pts) + 1)
         with _patched_oracle(prims):
             want = o.he_gemv_encoded(None, a, pts, ctx.mulpt_dim(L, nu), n1, n2, rk)
         same(ctx.he_gemv_encoded(hc(a), pts, n1, n2, rk), want, "he_gemv")
