@@ -398,8 +398,75 @@ static gq_ctx *ctx(void)
 
 static unsigned limb_of(const struct rns_ctx *rns) { return rns->dim - 1; }   /* src/precomp.c:371 */
 
+/* ---- batched evaluation-key generation -----------------------------------------------------------
+ * he_genswk (src/he-kem.c:103-110) ends with, for every limb d < dimevk and both key halves,
+ *     rns_decompose(&swk->p[d*n], poly.coeffs, rns_d);  ntt(&swk->p[d*n], rns_d);
+ * i.e. 4*dimevk single-limb host<->device crossings per key, each marshalling the same N big integers again.  While
+ * one of the key generators runs (he_genrlk / he_genck / he_genrk are wrapped below and open this scope; the
+ * samplers and everything else stay the reference's, RNG order untouched), the FIRST rns_decompose of a polynomial
+ * marshals it once, computes NTT(decompose(.)) for ALL dimevk limbs in two batched crossings and keeps the result;
+ * every rns_decompose of that polynomial then copies its limb - already transformed - and the ntt() call that
+ * follows on the same buffer is a no-op.  A cached polynomial dies with poly_mpi_free (he_genswk frees both at its
+ * end), so a recycled address can never hit.  Outside the scope nothing changes.  ntt() keeps the reference's exact
+ * bit pattern (gq_ntt_batch), so the keys are byte-identical (tests/keydump.c). */
+#define KG_POLYS 2
+static struct {
+  int active;
+  const MPI *a[KG_POLYS];        /* cached polynomials (address of the MPI array) */
+  uint64_t *hat[KG_POLYS];       /* NTT(decompose(a)) over dimevk limbs, host */
+  const uint64_t *pending[4];    /* buffers whose ntt() call is still to come */
+  unsigned npending;
+  unsigned long long batched, skipped;
+} KG;
+
+static void kg_forget(const void *coeffs)
+{
+  for (int k = 0; k < KG_POLYS; k++) if (KG.a[k] == (const MPI *)coeffs) KG.a[k] = NULL;
+}
+static void kg_close(const char *who)
+{
+  if (KG.npending) { fprintf(stderr, "%s: rns_decompose without its ntt() inside key generation\n", who); abort(); }
+  KG.active = 0;
+  for (int k = 0; k < KG_POLYS; k++) KG.a[k] = NULL;
+}
+static int kg_decompose(uint64_t ahat[], const MPI a[], const struct rns_ctx *rns)
+{
+  const unsigned n = polyctx.n, D = hectx.dimevk, d = limb_of(rns);
+  if (!KG.active || d >= D) return 0;
+  int k = -1;
+  for (int i = 0; i < KG_POLYS; i++) if (KG.a[i] == a) k = i;
+  if (k < 0) {
+    for (int i = 0; i < KG_POLYS; i++) if (!KG.a[i]) { k = i; break; }
+    if (k < 0) k = 0;
+    const unsigned W = poly_words(a, n);
+    if (W > DROPIN_MAX_W) return 0;
+    uint64_t *s = stage((size_t)W * n);
+    struct in_args x = {s, &(poly_mpi_t){(MPI *)a}, W, "rns_decompose"};
+    par_for(n, poly_in_range, &x);
+    if (!KG.hat[k]) {
+      void *p = NULL;
+      if (gq_host_alloc(&p, (size_t)polyctx.dimub * n * 8)) die("keygen batch");
+      KG.hat[k] = p;
+    }
+    CK(gq_rns_decompose(ctx(), 0, D, KG.hat[k], s, W));
+    CK(gq_ntt_batch(ctx(), 0, D, 1, KG.hat[k], 0));
+    KG.a[k] = a;
+    KG.batched++;
+  }
+  memcpy(ahat, KG.hat[k] + (size_t)d * n, (size_t)n * 8);
+  if (KG.npending == 4) { fprintf(stderr, "rns_decompose: too many transforms pending inside key generation\n"); abort(); }
+  KG.pending[KG.npending++] = ahat;
+  return 1;
+}
+static int kg_ntt(const uint64_t a[])
+{
+  for (unsigned i = 0; i < KG.npending; i++)
+    if (KG.pending[i] == a) { KG.pending[i] = KG.pending[--KG.npending]; KG.skipped++; return 1; }
+  return 0;
+}
+
 /* ------------------------------------------------------------------------ limb layer */
-void ntt(uint64_t a[], const struct rns_ctx *rns) { CK(gq_ntt(ctx(), limb_of(rns), a)); }
+void ntt(uint64_t a[], const struct rns_ctx *rns) { if (KG.active && kg_ntt(a)) return; CK(gq_ntt(ctx(), limb_of(rns), a)); }
 void invntt(uint64_t a[], const struct rns_ctx *rns) { CK(gq_invntt(ctx(), limb_of(rns), a)); }
 void poly_rns_add(uint64_t r[], const uint64_t a[], const uint64_t b[], const struct rns_ctx *rns)
 {
@@ -413,6 +480,7 @@ void poly_rns_mul(uint64_t r[], const uint64_t a[], const uint64_t b[], const st
 /* -------------------------------------------------------------------- MPI <-> RNS */
 void rns_decompose(uint64_t ahat[], const MPI a[], const struct rns_ctx *rns)
 {
+  if (KG.active && kg_decompose(ahat, a, rns)) return;
   const unsigned n = polyctx.n, W = poly_words(a, n);
   if (W > DROPIN_MAX_W) { fprintf(stderr, "rns_decompose: coefficient wider than %u words\n", DROPIN_MAX_W); abort(); }
   uint64_t *s = stage((size_t)W * n);
@@ -552,12 +620,32 @@ void he_free_evk(he_evk_t *evk)
   gpqhe_ref_he_free_evk(evk);
 }
 /* key generation stays the reference's (RNG order, stdout prints); its rns_decompose / ntt calls bind to the GPU */
-void he_genrlk(he_evk_t *rlk, const poly_mpi_t *sk) { gpqhe_dropin_invalidate_evk(rlk); gpqhe_ref_he_genrlk(rlk, sk); }
-void he_genck(he_evk_t *ck, const poly_mpi_t *sk) { gpqhe_dropin_invalidate_evk(ck); gpqhe_ref_he_genck(ck, sk); }
+static int kg_enabled(void) { return getenv("GPQHE_DROPIN_NO_KEYGEN_BATCH") == NULL; }
+void he_genrlk(he_evk_t *rlk, const poly_mpi_t *sk)
+{
+  gpqhe_dropin_invalidate_evk(rlk);
+  KG.active = kg_enabled();
+  gpqhe_ref_he_genrlk(rlk, sk);
+  kg_close(__func__);
+}
+void he_genck(he_evk_t *ck, const poly_mpi_t *sk)
+{
+  gpqhe_dropin_invalidate_evk(ck);
+  KG.active = kg_enabled();
+  gpqhe_ref_he_genck(ck, sk);
+  kg_close(__func__);
+}
 void he_genrk(he_evk_t *rk, const poly_mpi_t *sk)
 {
   for (unsigned r = 0; r < hectx.slots; r++) gpqhe_dropin_invalidate_evk(&rk[r]);
+  KG.active = kg_enabled();
   gpqhe_ref_he_genrk(rk, sk);
+  kg_close(__func__);
+}
+void gpqhe_dropin_keygen_stats(unsigned long long *batched, unsigned long long *skipped)
+{
+  if (batched) *batched = KG.batched;
+  if (skipped) *skipped = KG.skipped;
 }
 
 /* ------------------------------------------------- device-resident ciphertexts --------
@@ -804,6 +892,7 @@ void he_copy_ct(struct he_ct *dest, const struct he_ct *src)
 }
 void poly_mpi_free(poly_mpi_t *a)
 {
+  kg_forget(a->coeffs);
   sh_release(a->coeffs);
   gpqhe_ref_poly_mpi_free(a);
 }

@@ -161,6 +161,29 @@ def test_reference_polymul_program_emulated(emul_env):
     assert strip(ours) == strip(ref)
 
 
+def _keys(out):
+    return [l for l in out.splitlines() if l.startswith("key ")]
+
+
+def _check_keydump(args, env):
+    """tests/keydump.c against the drop-in and against the unmodified reference (same -DSUPERCOP stream): sk, pk and
+    every evaluation-key buffer (rlk, ck, rk[0..slots)) must be byte-identical (src/he-kem.c:74-169)"""
+    ours_bin, ref_bin = os.path.join(BUILD, "keydump"), os.path.join(ROOT, "oracle", "_ref", "keydump")
+    if not (os.path.exists(ours_bin) and os.path.exists(ref_bin)):
+        pytest.skip("keydump builds absent")
+    rc, ours = _run([ours_bin, *args], env=env, timeout=1800)
+    assert rc == 0, ours[-1500:]
+    rc, ref = _run([ref_bin, *args], timeout=1800)
+    assert rc == 0, ref[-1500:]
+    assert len(_keys(ours)) == 4 + int(args[2]) and _keys(ours) == _keys(ref), (ours[-1500:], ref[-1500:])
+    return ours, ref
+
+
+@pytest.mark.parametrize("args", [("7", "120", "4", "40"), ("6", "438", "8", "50")])
+def test_keygen_byte_identical_emulated(emul_env, args):
+    _check_keydump(args, emul_env)
+
+
 def _crt_printout(binary, env=None):
     """tests/crt.c (-DTEST_CRT: 9-bit primes) prints the prime table, P, phat, phat_invmp and the residues of
     rns_decompose, then crashes in BOTH builds: it passes `a.coeffs` (MPI *) where rns_reconstruct takes an MPI
@@ -193,6 +216,21 @@ def test_reference_crt_program_emulated(emul_env):
 
 
 # ------------------------------------------------------------------------------- GPU tier
+@pytest.mark.gpu
+def test_keygen_byte_identical_gpu():
+    """he_keypair / he_genrlk / he_genck / he_genrk at the KAT ring (N=2^14, logq=438): the drop-in's keys (decompose,
+    NTT and poly_mul on the GPU, samplers on the host) equal the reference's byte for byte"""
+    _build_dropin()
+    if not _have_gcrypt():
+        pytest.skip("libgcrypt.so.20 is not installed on this machine")
+    ours, ref = _check_keydump(("14", "438", "4", "50"), None)
+    keep = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(keep):
+        with open(os.path.join(keep, "keydump_n14.log"), "w") as f:
+            f.write("drop-in:   " + [l for l in ours.splitlines() if l.startswith("time")][-1] + "\n")
+            f.write("reference: " + [l for l in ref.splitlines() if l.startswith("time")][-1] + "\n")
+
+
 @pytest.mark.gpu
 def test_reference_crt_program_gpu():
     _build_dropin()
