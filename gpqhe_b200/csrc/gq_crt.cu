@@ -21,6 +21,7 @@
 //    2^(64*WP) it is a multiplication by P^-1 mod 2^(64*WP).
 #include "gq_bigint.h"
 #include "gq_kernels.h"
+#include "gq_p2p.h"
 
 namespace {
 
@@ -427,9 +428,10 @@ template <int W, bool PRE>
 __global__ void __launch_bounds__(256)
 k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
                    const uint64_t *__restrict__ rhat, unsigned k, GqPtrs4 out, int Wout,
-                   int *fix_count, int *fix_list, unsigned rs_j) {
+                   int *fix_count, int *fix_list, unsigned rs_j, GqWaitIn wt) {
   __shared__ CrtSharedLow<W> S;
   crt_low_stage<W>(S, B, primes);
+  gq_peer_wait(wt);                   // sharded pipeline: rhat is a receive slab (gq_p2p.h); no-op otherwise
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -451,13 +453,14 @@ __global__ void __launch_bounds__(128)
 k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
                    const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
                    unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout, int *fix_count, int *fix_list,
-                   unsigned rs_j, const ulonglong2 *ratio) {
+                   unsigned rs_j, const ulonglong2 *ratio, GqWaitIn wt) {
   __shared__ CrtSharedLow<WQ> S;
   __shared__ CrtShared<WP> SP;
   __shared__ uint64_t sPinv[WQ];
   crt_low_stage<WQ>(S, B, primes);
   crt_stage<WP>(SP, BP, primes, PRE ? ratio : nullptr);
   for (int j = threadIdx.x; j < WQ; j += blockDim.x) sPinv[j] = Pinv[j];
+  gq_peer_wait(wt);                   // sharded pipeline: chat is a receive slab (gq_p2p.h); no-op otherwise
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -582,9 +585,11 @@ k_decompose32(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t
 // src/precomp.c:358-376: 2^59 + 1 + k*2N).  Then 2^s == -c and the 93-bit total V = Vh*2^s + Vl folds with two
 // small products instead of two 64-bit Shoup multiplications:  t = c*Vh < 2^62 = th*2^s + tl,
 //   V == Vl - tl + c*th  (mod p),   r = Vl + p - tl + c*th  in (0, 2p + 2^31).
-template <int W, bool PM>
+// PEER: the residues are not written to `out` but straight into the receive slabs of the ranks that own their limbs
+// (sharded pipeline, gq_p2p.h); the last block to finish publishes the exchange's epoch.
+template <int W, bool PM, bool PEER>
 __global__ void __launch_bounds__(256)
-k_decompose28(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *__restrict__ out) {
+k_decompose28(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *__restrict__ out, GqPeerOut po) {
   constexpr int J = (64 * W + 27) / 28;
   static_assert(J <= GQ_DEC28, "at most 16 digits");
   __shared__ uint64_t sU[GQ_MAX_PRIMES * J];
@@ -601,13 +606,14 @@ k_decompose28(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t
   }
   __syncthreads();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+  const bool live = i < n;
+  if (!PEER && !live) return;
   const int b = blockIdx.y;
   const uint64_t *src = (b == 0) ? in.p[0] : (b == 1) ? in.p[1] : (b == 2) ? in.p[2] : in.p[3];
   uint64_t *dst = out + (size_t)b * nlimbs * n;
   uint64_t xw[W];
 #pragma unroll
-  for (int w = 0; w < W; w++) xw[w] = src[(size_t)w * n + i];
+  for (int w = 0; w < W; w++) xw[w] = live ? src[(size_t)w * n + i] : 0;
   const bool neg = (xw[W - 1] >> 63) != 0;
   uint32_t x[J];
 #pragma unroll
@@ -648,8 +654,10 @@ k_decompose28(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t
       const uint64_t TW = sC[6 * d + 4];
       r = (r >= TW) ? r - TW : r - TW + p;
     }
-    dst[(size_t)d * n + i] = r;
+    if (PEER) { if (live) *gq_peer_c2l(po, b, limb0 + d, i) = r; }
+    else dst[(size_t)d * n + i] = r;
   }
+  if (PEER) gq_peer_signal(po);
 }
 
 template <int W>
@@ -705,8 +713,10 @@ k_decompose(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *
 // by the exact kernel in list mode (power-of-two q only).  Returns kernels launched.
 int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix, unsigned rs_j, bool pre) {
+                          cudaStream_t st, int *fix, unsigned rs_j, bool pre, const GqWaitIn *wt) {
   if (rs_j && (!q.is_pow2 || rs_j > q.k)) return -1;
+  GqWaitIn w0 = GqWaitIn();
+  if (wt) w0 = *wt;
   dim3 grid((n + 127) / 128, npolys), block(128);
   int *fc = nullptr, *fl = nullptr;
   int launches = 1;
@@ -714,8 +724,8 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
     fc = fix; fl = fix + 4;
     const int W = (int)((q.k + 63) / 64);
     dim3 g2((n + 255) / 256, npolys), b2(256);
-#define GQ_RF(V) do { if (pre) GQ_LAUNCH((k_reconstruct_fast<V, true>), g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j); \
-                      else GQ_LAUNCH((k_reconstruct_fast<V, false>), g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j); } while (0)
+#define GQ_RF(V) do { if (pre) GQ_LAUNCH((k_reconstruct_fast<V, true>), g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j, w0); \
+                      else GQ_LAUNCH((k_reconstruct_fast<V, false>), g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j, w0); } while (0)
     if (W <= 1) GQ_RF(1); else if (W <= 2) GQ_RF(2); else if (W <= 3) GQ_RF(3); else if (W <= 4) GQ_RF(4);
     else if (W <= 5) GQ_RF(5); else if (W <= 6) GQ_RF(6); else if (W <= 7) GQ_RF(7); else if (W <= 8) GQ_RF(8);
     else if (W <= 12) GQ_RF(12); else if (W <= 16) GQ_RF(16); else if (W <= 24) GQ_RF(24); else GQ_RF(32);
@@ -724,6 +734,8 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
     launches = 2;
   } else if (pre) {
     return -1;        // pre-scaled residues are only produced for the fast path
+  } else if (wt) {
+    return -2;        // the flag wait lives in the fast kernel only
   }
   if (q.is_pow2) {
     GQ_WT_SWITCH(B.WT,
@@ -762,8 +774,10 @@ static int ks_dispatch_wp(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
 int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix, unsigned rs_j, const ulonglong2 *ratio) {
+                          cudaStream_t st, int *fix, unsigned rs_j, const ulonglong2 *ratio, const GqWaitIn *wt) {
   if (rs_j > k) return -1;
+  GqWaitIn w0 = GqWaitIn();
+  if (wt) w0 = *wt;
   dim3 grid((n + 127) / 128, npolys);
   int *fc = nullptr, *fl = nullptr;
   int launches = 1;
@@ -771,8 +785,8 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
     fc = fix; fl = fix + 4;
     dim3 block(128);
     switch (BP.WT) {
-#define GQ_KFL(WPV, WQV) do { if (ratio) GQ_LAUNCH((k_ks_epilogue_fast<WPV, WQV, true>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j, ratio); \
-                              else GQ_LAUNCH((k_ks_epilogue_fast<WPV, WQV, false>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j, ratio); } while (0)
+#define GQ_KFL(WPV, WQV) do { if (ratio) GQ_LAUNCH((k_ks_epilogue_fast<WPV, WQV, true>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j, ratio, w0); \
+                              else GQ_LAUNCH((k_ks_epilogue_fast<WPV, WQV, false>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j, ratio, w0); } while (0)
 #define GQ_KF(V) case V: GQ_KFL(V, V); break;
       case 8:     // the shipped parameter sets (logq = 438: 7 words per coefficient, P of 8 words) and their neighbours
         if (Wout == 7 && Wadd <= 7 && k < 64u * 7) GQ_KFL(8, 7);
@@ -788,6 +802,8 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
     launches = 2;
   } else if (ratio) {
     return -1;        // pre-scaled residues are only produced for the fast path
+  } else if (wt) {
+    return -2;        // the flag wait lives in the fast kernel only
   }
   int r = -1;
   switch (B.WT) {
@@ -800,21 +816,30 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
 }
 
 template <int W>
-static void dec_launch(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
-                       uint64_t *out, int npolys, cudaStream_t st, int digits) {
+static int dec_launch(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
+                      uint64_t *out, int npolys, cudaStream_t st, int digits, const GqPeerOut *po) {
   dim3 grid((n + 255) / 256, npolys), block(256);
+  const GqPeerOut none = GqPeerOut();
   if constexpr (W <= 7) {
-    if (digits == 3) { GQ_LAUNCH((k_decompose28<W, true>), grid, block, st, dt, n, limb0, nlimbs, in, out); return; }
-    if (digits == 2) { GQ_LAUNCH((k_decompose28<W, false>), grid, block, st, dt, n, limb0, nlimbs, in, out); return; }
+    if (po) {      // peer output exists for the 28-bit digit kernels only (every shipped parameter set)
+      if (digits == 3) { GQ_LAUNCH((k_decompose28<W, true, true>), grid, block, st, dt, n, limb0, nlimbs, in, out, *po); return 1; }
+      if (digits == 2) { GQ_LAUNCH((k_decompose28<W, false, true>), grid, block, st, dt, n, limb0, nlimbs, in, out, *po); return 1; }
+      return -2;
+    }
+    if (digits == 3) { GQ_LAUNCH((k_decompose28<W, true, false>), grid, block, st, dt, n, limb0, nlimbs, in, out, none); return 1; }
+    if (digits == 2) { GQ_LAUNCH((k_decompose28<W, false, false>), grid, block, st, dt, n, limb0, nlimbs, in, out, none); return 1; }
   }
+  if (po) return -2;
   if (digits) GQ_LAUNCH(k_decompose32<W>, grid, block, st, dt, n, limb0, nlimbs, in, out);
   else GQ_LAUNCH(k_decompose<W>, grid, block, st, dt, n, limb0, nlimbs, in, out);
+  return 1;
 }
 
+// po != null: peer output (sharded pipeline); returns -2 when no peer-output kernel covers these parameters
 int gq_launch_decompose(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
-                        int W, uint64_t *out, int npolys, cudaStream_t st, int digits) {
+                        int W, uint64_t *out, int npolys, cudaStream_t st, int digits, const GqPeerOut *po) {
   switch (W) {
-#define GQ_CASE(V) case V: dec_launch<V>(dt, n, limb0, nlimbs, in, out, npolys, st, digits); return 1;
+#define GQ_CASE(V) case V: return dec_launch<V>(dt, n, limb0, nlimbs, in, out, npolys, st, digits, po);
     GQ_CASE(1) GQ_CASE(2) GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8)
     GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12) GQ_CASE(13) GQ_CASE(14) GQ_CASE(15) GQ_CASE(16)
     GQ_CASE(17) GQ_CASE(18) GQ_CASE(19) GQ_CASE(20) GQ_CASE(21) GQ_CASE(22) GQ_CASE(23) GQ_CASE(24)

@@ -3,6 +3,8 @@
 #include "gq_tables.h"
 
 struct GqPtrs4 { uint64_t *p[4]; };
+struct GqPeerOut;   // gq_p2p.h: peer output / flag wait of the sharded pipeline, inside the producing / consuming kernel
+struct GqWaitIn;
 
 // K1/K2 (gq_ntt.cu): data[npolys][nlimbs][n] in place; returns kernels launched or <0
 int gq_launch_ntt(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
@@ -10,15 +12,18 @@ int gq_launch_ntt(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, 
 
 // K1/K2 lazy variants for the internal pipelines (gq_ntt_lazy.cu): canonical in, canonical out;
 // valid only for primes p = 2^b + c, b <= 59, 16c < 2^b (checked by the caller)
+// wt != null (forward, n > 2^12): the strided kernel waits for the peers' flags first (sharded pipeline); -2 = no such form
 int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
-                       bool inverse, cudaStream_t st, int only = 0);
+                       bool inverse, cudaStream_t st, int only = 0, const GqWaitIn *wt = nullptr);
 
 // pointwise stage fused into the load of the lazy inverse transform (gq_ntt_lazy.cu): x -> y = invntt(product)
 //   TENSOR x[4][D][n] -> y[3][D][n];  EVK / EVKPERM x[D][n], e0, e1 -> y[2][D][n];  PT x[3][D][n] -> y[2][D][n];
 //   MUL x[2][D][n] -> y[D][n];  GEMV x[T][2][D][n], e0[T][D][n], g = T -> y[2][D][n] = sum_t x[t][k] * e0[t]
 enum { GQ_NTTF_TENSOR = 1, GQ_NTTF_EVK = 2, GQ_NTTF_EVKPERM = 3, GQ_NTTF_PT = 4, GQ_NTTF_MUL = 5, GQ_NTTF_GEMV = 6 };
+// po != null (TENSOR / EVK, n > 2^12): the last pass stores into the peers' slabs and signals; -2 = no such form
 int gq_launch_ntt_lazy_fused(const GqNttTables &tb, int mode, const uint64_t *x, uint64_t *y, const uint64_t *e0,
-                             const uint64_t *e1, unsigned g, int limb0, int nlimbs, cudaStream_t st);
+                             const uint64_t *e1, unsigned g, int limb0, int nlimbs, cudaStream_t st,
+                             const GqPeerOut *po = nullptr);
 
 // K3 (gq_pointwise.cu)
 void gq_launch_binary(const GqPrime *primes, int n, int limb0, int nlimbs, int npolys, bool mul,
@@ -41,14 +46,17 @@ void gq_launch_mul_pt(const GqPrime *primes, int n, int D, uint64_t *y, const ui
 // rs_j > 0 (power-of-two q and Delta only): he_rs fused behind the CRT, the output is rdiv(., 2^rs_j) smod 2^(k-rs_j)
 // digits: 32-bit digit kernel (every prime of the range needs >= 33 and <= 60 bits)
 int gq_launch_decompose(const GqDecTables &dt, int n, int limb0, int nlimbs, const GqPtrs4 &in,
-                        int W, uint64_t *out, int npolys, cudaStream_t st, int digits = false);
+                        int W, uint64_t *out, int npolys, cudaStream_t st, int digits = false,
+                        const GqPeerOut *po = nullptr);
 int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0, bool pre = false);
+                          cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0, bool pre = false,
+                          const GqWaitIn *wt = nullptr);
 int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0, const ulonglong2 *ratio = nullptr);
+                          cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0, const ulonglong2 *ratio = nullptr,
+                          const GqWaitIn *wt = nullptr);
 // general-modulus key-switch epilogue (exact long division, slow path)
 int gq_launch_ks_epilogue_general(const GqCrtBasis &B, const uint64_t *P, int nP,
                                   const uint64_t *Ph, const GqPrime *primes, int n,

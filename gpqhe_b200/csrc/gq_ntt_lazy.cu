@@ -25,6 +25,7 @@
 //     radix-8 round with inputs < 2p ends with bounds {16,8,4,4,2,2,2,2} p and only positions 0..3 are
 //     reduced (7 conditional subtractions per round instead of one per butterfly = 12).
 #include "gq_kernels.h"
+#include "gq_p2p.h"
 
 namespace {
 
@@ -345,9 +346,10 @@ k_nttl_inv_tile(GqNttTables tb, InvSrc src, uint64_t *__restrict__ y, int limb0,
 // shared memory once per CTA (broadcast reads at the point of use) instead of being held in 4 registers
 // each from the top of the kernel - ncu had these kernels at 112-128 registers, 2 CTAs per SM, 22 % of
 // the warp slots and 36-40 % issue utilisation.
+// wt.flags != null: `data` is a receive slab of the sharded pipeline - wait for every peer's epoch first (gq_p2p.h)
 template <int SA>
 __global__ void __launch_bounds__(256, GQ_STRIDED_MIN_CTAS)
-k_nttl_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+k_nttl_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs, GqWaitIn wt) {
   constexpr int R = 1 << SA;
   __shared__ ulonglong2 stw[R];
   const int cols = tb.n >> SA;
@@ -355,6 +357,7 @@ k_nttl_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
   const int m = blockIdx.y;
   const int d = limb0 + m % nlimbs;
   if (threadIdx.x < R) stw[threadIdx.x] = tb.tw_fwd[(size_t)d * tb.n + threadIdx.x];
+  gq_peer_wait(wt);
   __syncthreads();
   if (col >= cols) return;
   const PC c = load_pc(tb.primes[d]);
@@ -380,9 +383,11 @@ k_nttl_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
   for (int r = 0; r < R; r++) a[(size_t)r * cols] = v[r];
 }
 
-template <int SA>
+// PEER: the finished coefficients are not written back to `data` but into the receive slabs of the ranks that own
+// them (sharded pipeline, gq_p2p.h); the last block to finish publishes the exchange's epoch.
+template <int SA, bool PEER>
 __global__ void __launch_bounds__(256, GQ_STRIDED_MIN_CTAS)
-k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs, GqPeerOut po) {
   constexpr int R = 1 << SA;
   __shared__ ulonglong2 stw[R];
   const int cols = tb.n >> SA;
@@ -391,12 +396,13 @@ k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
   const int d = limb0 + m % nlimbs;
   if (threadIdx.x < R) stw[threadIdx.x] = tb.tw_inv[(size_t)d * tb.n + threadIdx.x];
   __syncthreads();
-  if (col >= cols) return;
+  const bool live = col < cols;
+  if (!PEER && !live) return;
   const GqPrime pr = tb.primes[d];
   const PC c = load_pc(pr);
   const ulonglong2 *tw = stw;
   const ulonglong2 wlast = tb.fin_w[d], fs = tb.fin_s[d];
-  uint64_t *a = data + (size_t)m * tb.n + col;
+  uint64_t *a = data + (size_t)m * tb.n + (live ? col : 0);
   uint64_t v[R];
 #pragma unroll
   for (int r = 0; r < R; r++) v[r] = a[(size_t)r * cols];
@@ -430,31 +436,44 @@ k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
     v[r] = csub(mul_lazy(s, fs.x, fs.y, c.p), c.p);
     v[q] = csub(mul_lazy(dd, wlast.x, wlast.y, c.p), c.p);
   }
+  if (PEER) {
+    if (live) {
 #pragma unroll
-  for (int r = 0; r < R; r++) a[(size_t)r * cols] = v[r];
+      for (int r = 0; r < R; r++) *gq_peer_l2c(po, m / nlimbs, m % nlimbs, col + r * cols, limb0) = v[r];
+    }
+    gq_peer_signal(po);
+  } else {
+#pragma unroll
+    for (int r = 0; r < R; r++) a[(size_t)r * cols] = v[r];
+  }
 }
 
 }  // namespace
 
 template <int MODE>
 static int launch_inv(const GqNttTables &tb, const InvSrc &src, uint64_t *y, int limb0, int nlimbs, int npolys,
-                      cudaStream_t st, int only) {
+                      cudaStream_t st, int only, const GqPeerOut *po = nullptr) {
   const int logn = tb.logn;
   const int lt = logn > 12 ? 12 : logn, sa = logn - lt;
   const dim3 gt(tb.n >> lt, nlimbs * npolys), gs(((tb.n >> (sa ? sa : 1)) + 255) / 256, nlimbs * npolys);
   if (sa) {
     if (only != 2) GQ_LAUNCH((k_nttl_inv_tile<12, false, MODE>), gt, dim3(TileCfg<12>::NT), st, tb, src, y, limb0, nlimbs);
     if (only != 1) {
+      const GqPeerOut none = GqPeerOut();
+#define GQ_INVS(SAV) do { if (po) GQ_LAUNCH((k_nttl_inv_strided<SAV, true>), gs, dim3(256), st, tb, y, limb0, nlimbs, *po); \
+                          else GQ_LAUNCH((k_nttl_inv_strided<SAV, false>), gs, dim3(256), st, tb, y, limb0, nlimbs, none); } while (0)
       switch (sa) {
-        case 1: GQ_LAUNCH(k_nttl_inv_strided<1>, gs, dim3(256), st, tb, y, limb0, nlimbs); break;
-        case 2: GQ_LAUNCH(k_nttl_inv_strided<2>, gs, dim3(256), st, tb, y, limb0, nlimbs); break;
-        case 3: GQ_LAUNCH(k_nttl_inv_strided<3>, gs, dim3(256), st, tb, y, limb0, nlimbs); break;
-        case 4: GQ_LAUNCH(k_nttl_inv_strided<4>, gs, dim3(256), st, tb, y, limb0, nlimbs); break;
-        case 5: GQ_LAUNCH(k_nttl_inv_strided<5>, gs, dim3(256), st, tb, y, limb0, nlimbs); break;
+        case 1: GQ_INVS(1); break;
+        case 2: GQ_INVS(2); break;
+        case 3: GQ_INVS(3); break;
+        case 4: GQ_INVS(4); break;
+        case 5: GQ_INVS(5); break;
       }
+#undef GQ_INVS
     }
     return only ? 1 : 2;
   }
+  if (po) return -2;          // one-kernel transforms (n <= 2^12) have no peer-output form
   switch (lt) {
 #define GQ_CASE(L) case L: GQ_LAUNCH((k_nttl_inv_tile<L, true, MODE>), gt, dim3(TileCfg<L>::NT), st, tb, src, y, limb0, nlimbs); break;
     GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8) GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12)
@@ -465,31 +484,35 @@ static int launch_inv(const GqNttTables &tb, const InvSrc &src, uint64_t *y, int
 
 // Same contract as gq_launch_ntt, canonical in / canonical out only.
 int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nlimbs, int npolys,
-                       bool inverse, cudaStream_t st, int only) {
+                       bool inverse, cudaStream_t st, int only, const GqWaitIn *wt) {
   // only: 0 = whole transform; 1 = tile kernel only, 2 = strided kernel only (profiling: the
   // output is then not a transform)
   const int logn = tb.logn;
   if (logn < 3 || logn > 17) return -1;
   if (only && logn <= 12) return -1;
   if (inverse) {
+    if (wt) return -2;
     InvSrc src; src.x = data; src.e0 = src.e1 = nullptr; src.g = 1;
     return launch_inv<GQ_INV_PLAIN>(tb, src, data, limb0, nlimbs, npolys, st, only);
   }
+  GqWaitIn w0 = GqWaitIn();
+  if (wt) w0 = *wt;
   const int lt = logn > 12 ? 12 : logn, sa = logn - lt;
   const dim3 gt(tb.n >> lt, nlimbs * npolys), gs(((tb.n >> (sa ? sa : 1)) + 255) / 256, nlimbs * npolys);
   if (sa) {
     if (only != 1) {
       switch (sa) {
-        case 1: GQ_LAUNCH(k_nttl_fwd_strided<1>, gs, dim3(256), st, tb, data, limb0, nlimbs); break;
-        case 2: GQ_LAUNCH(k_nttl_fwd_strided<2>, gs, dim3(256), st, tb, data, limb0, nlimbs); break;
-        case 3: GQ_LAUNCH(k_nttl_fwd_strided<3>, gs, dim3(256), st, tb, data, limb0, nlimbs); break;
-        case 4: GQ_LAUNCH(k_nttl_fwd_strided<4>, gs, dim3(256), st, tb, data, limb0, nlimbs); break;
-        case 5: GQ_LAUNCH(k_nttl_fwd_strided<5>, gs, dim3(256), st, tb, data, limb0, nlimbs); break;
+        case 1: GQ_LAUNCH(k_nttl_fwd_strided<1>, gs, dim3(256), st, tb, data, limb0, nlimbs, w0); break;
+        case 2: GQ_LAUNCH(k_nttl_fwd_strided<2>, gs, dim3(256), st, tb, data, limb0, nlimbs, w0); break;
+        case 3: GQ_LAUNCH(k_nttl_fwd_strided<3>, gs, dim3(256), st, tb, data, limb0, nlimbs, w0); break;
+        case 4: GQ_LAUNCH(k_nttl_fwd_strided<4>, gs, dim3(256), st, tb, data, limb0, nlimbs, w0); break;
+        case 5: GQ_LAUNCH(k_nttl_fwd_strided<5>, gs, dim3(256), st, tb, data, limb0, nlimbs, w0); break;
       }
     }
     if (only != 2) GQ_LAUNCH((k_nttl_fwd_tile<12, true>), gt, dim3(TileCfg<12>::NT), st, tb, data, limb0, nlimbs);
     return only ? 1 : 2;
   }
+  if (wt) return -2;          // one-kernel transforms (n <= 2^12) have no flag-wait form
   switch (lt) {
 #define GQ_CASE(L) case L: GQ_LAUNCH((k_nttl_fwd_tile<L, false>), gt, dim3(TileCfg<L>::NT), st, tb, data, limb0, nlimbs); break;
     GQ_CASE(3) GQ_CASE(4) GQ_CASE(5) GQ_CASE(6) GQ_CASE(7) GQ_CASE(8) GQ_CASE(9) GQ_CASE(10) GQ_CASE(11) GQ_CASE(12)
@@ -502,13 +525,14 @@ int gq_launch_ntt_lazy(const GqNttTables &tb, uint64_t *data, int limb0, int nli
 // the key halves e0, e1 at the same limb range; g = Galois element for the permuted form).  mode = GQ_NTTF_*.
 // Every prime of the range must be pseudo-Mersenne (the caller checks pm_ok).  Returns kernels launched.
 int gq_launch_ntt_lazy_fused(const GqNttTables &tb, int mode, const uint64_t *x, uint64_t *y, const uint64_t *e0,
-                             const uint64_t *e1, unsigned g, int limb0, int nlimbs, cudaStream_t st) {
+                             const uint64_t *e1, unsigned g, int limb0, int nlimbs, cudaStream_t st,
+                             const GqPeerOut *po) {
   const int logn = tb.logn;
   if (logn < 3 || logn > 17) return -1;
   InvSrc src; src.x = x; src.e0 = e0; src.e1 = e1; src.g = g;
   switch (mode) {
-    case GQ_NTTF_TENSOR: return launch_inv<GQ_INV_TENSOR>(tb, src, y, limb0, nlimbs, 3, st, 0);
-    case GQ_NTTF_EVK: return launch_inv<GQ_INV_EVK>(tb, src, y, limb0, nlimbs, 2, st, 0);
+    case GQ_NTTF_TENSOR: return launch_inv<GQ_INV_TENSOR>(tb, src, y, limb0, nlimbs, 3, st, 0, po);
+    case GQ_NTTF_EVK: return launch_inv<GQ_INV_EVK>(tb, src, y, limb0, nlimbs, 2, st, 0, po);
     case GQ_NTTF_EVKPERM: return launch_inv<GQ_INV_EVKPERM>(tb, src, y, limb0, nlimbs, 2, st, 0);
     case GQ_NTTF_PT: return launch_inv<GQ_INV_PT>(tb, src, y, limb0, nlimbs, 2, st, 0);
     case GQ_NTTF_MUL: return launch_inv<GQ_INV_MUL>(tb, src, y, limb0, nlimbs, 1, st, 0);
