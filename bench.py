@@ -677,22 +677,33 @@ def run_ours(args):
         # NVLink (gq_p2p.cu), epoch flags instead of NCCL, the whole op one CUDA graph per rank
         if not args.no_p2p and plan is not None:
             from gpqhe_b200.sharded import P2PPlan
-            pp, ok, match = None, True, False
-            try:
-                with torch.cuda.stream(ext):
-                    pp = P2PPlan.build(sh, L, evk_s, rescale=True)
-                    for k in range(4):
-                        pp.inp[k].copy_(sl[k])
-                    pp.run(check=False)
-                    ctx.sync()
-                    want0, want1 = want_sl[0], want_sl[1]
-                    match = bool(torch.equal(pp.out[0], want0) and torch.equal(pp.out[1], want1)) and not pp.failed()
-            except Exception as ex:
-                print(f"bench.py: p2p plan failed: {ex!r}", file=sys.stderr)
-                ok = False
-            if all_ok(ok):
+
+            def p2p_leg(unfused):
+                """one P2P plan: build, check against the single-GPU result, time eagerly and as one CUDA graph.
+                unfused=True keeps the round-1 exchange (scatter + signal + wait launches) for comparison."""
+                pp, ok, match = None, True, False
+                if unfused:
+                    os.environ["GPQHE_B200_P2P_UNFUSED"] = "1"
+                try:
+                    with torch.cuda.stream(ext):
+                        pp = P2PPlan.build(sh, L, evk_s, rescale=True)
+                        for k in range(4):
+                            pp.inp[k].copy_(sl[k])
+                        pp.run(check=False)
+                        ctx.sync()
+                        match = bool(torch.equal(pp.out[0], want_sl[0]) and torch.equal(pp.out[1], want_sl[1])) and not pp.failed()
+                except Exception as ex:
+                    print(f"bench.py: p2p plan failed: {ex!r}", file=sys.stderr)
+                    ok = False
+                finally:
+                    os.environ.pop("GPQHE_B200_P2P_UNFUSED", None)
+                if not all_ok(ok):
+                    return {"error": "plan construction failed on some rank (see stderr)"}
+                l0 = ctx.launch_count
                 ms_pe = timed(lambda i: pp.run(check=False), args.steps, args.warmup)
-                p2p = {"bit_exact_vs_single_gpu": all_ok(match), "eager_ms_per_op": ms_pe / args.steps}
+                res = {"fused_exchange": bool(pp.fused), "bit_exact_vs_single_gpu": all_ok(match),
+                       "eager_ms_per_op": ms_pe / args.steps,
+                       "launches_per_op": (ctx.launch_count - l0) // (args.steps + args.warmup)}
                 okc = True
                 try:
                     with torch.cuda.stream(ext):
@@ -702,20 +713,21 @@ def run_ours(args):
                     okc = False
                 if all_ok(okc):
                     ms_pg = statistics.median(timed(lambda i: pp.run(check=False), args.steps, args.warmup if r == 0 else 0)
-                                              for r in range(5))
+                                              for r in range(9))
                     with torch.cuda.stream(ext):
                         ctx.sync()
                         same = bool(torch.equal(pp.out[0], want_sl[0]) and torch.equal(pp.out[1], want_sl[1]))
-                    p2p.update({"ms_per_op": ms_pg / args.steps, "ops_per_s": args.steps / (ms_pg * 1e-3),
+                    res.update({"ms_per_op": ms_pg / args.steps, "ops_per_s": args.steps / (ms_pg * 1e-3),
                                 "one_graph_per_op": True, "bit_exact_after_replays": all_ok(same and not pp.failed())})
                 else:
                     pp.graph = None
-                sharded["p2p"] = p2p
                 if world > 1:
                     dist.barrier()
                 pp.close()
-            else:
-                sharded["p2p"] = {"error": "plan construction failed on some rank (see stderr)"}
+                return res
+            sharded["p2p"] = p2p_leg(False)
+            if sharded["p2p"].get("fused_exchange"):
+                sharded["p2p"]["unfused"] = p2p_leg(True)
 
     # ---- end to end through the host C ABI: pinned host buffers, copies inside the timed region ----
     hout = torch.empty((2, W, n), dtype=torch.int64).pin_memory()
@@ -845,6 +857,8 @@ def run_ours(args):
                            "sharded_ranks": (sharded or {}).get("ranks"),
                            "sharded_nccl_ms_per_op": (sharded or {}).get("ms_per_op"),
                            "sharded_p2p_ms_per_op": ((sharded or {}).get("p2p") or {}).get("ms_per_op"),
+                           "sharded_p2p_fused_exchange": ((sharded or {}).get("p2p") or {}).get("fused_exchange"),
+                           "sharded_p2p_unfused_ms_per_op": (((sharded or {}).get("p2p") or {}).get("unfused") or {}).get("ms_per_op"),
                            "sharded_bytes_sent_per_rank_per_op": (sharded or {}).get("bytes_sent_per_rank_per_op"),
                            "sharded_bit_exact_vs_single_gpu": (None if not sharded else bool(
                                sharded.get("bit_exact_vs_single_gpu") and

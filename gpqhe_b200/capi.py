@@ -25,6 +25,13 @@ class GqInfo(C.Structure):
                [("device", C.c_int)]
 
 
+class GqP2pXchg(C.Structure):
+    """gq_p2p_xchg: one exchange of the sharded pipeline, producer (`send`) or consumer (`wait`) side"""
+    _fields_ = [("G", C.c_uint), ("me", C.c_uint), ("slot", C.c_uint), ("D", C.c_uint),
+                ("dst", C.c_void_p), ("off", C.c_void_p), ("flags", C.c_void_p), ("flags_local", C.c_void_p),
+                ("epoch_dev", C.c_void_p), ("err_dev", C.c_void_p), ("ticket_dev", C.c_void_p)]
+
+
 class GpqheError(RuntimeError):
     pass
 
@@ -129,6 +136,13 @@ SIGNATURES = {
     "gq_p2p_scatter_c2l_dev": (C.c_int, [vp, vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(vp), C.POINTER(C.c_int), vp]),
     "gq_p2p_scatter_l2c_dev": (C.c_int, [vp, vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(vp), C.POINTER(C.c_int), vp]),
     "gq_p2p_bump_dev": (C.c_int, [vp, vp, vp]),
+    "gq_p2p_fused_ok": (C.c_int, [vp, C.c_uint]),
+    "gq_p2p_decompose_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.POINTER(vp), C.c_uint, C.c_uint, C.POINTER(GqP2pXchg), vp]),
+    "gq_p2p_ntt_fwd_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.POINTER(GqP2pXchg), vp]),
+    "gq_p2p_tensor_inv_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, C.POINTER(GqP2pXchg), vp]),
+    "gq_p2p_mul_evk_inv_dev": (C.c_int, [vp, C.c_uint, C.c_uint, vp, vp, vp, C.POINTER(GqP2pXchg), vp]),
+    "gq_p2p_reconstruct_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.POINTER(vp), C.c_uint, C.POINTER(GqP2pXchg), vp]),
+    "gq_p2p_ks_epilogue_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, C.c_int, C.POINTER(GqP2pXchg), vp]),
     "gq_p2p_signal_dev": (C.c_int, [vp, C.POINTER(vp), C.c_uint, C.c_uint, C.c_uint, vp, vp, vp]),
     "gq_p2p_wait_dev": (C.c_int, [vp, vp, C.c_uint, C.c_uint, vp, vp, vp]),
 }

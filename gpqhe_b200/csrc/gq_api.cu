@@ -11,6 +11,7 @@
 
 #include "../../include/gpqhe_b200.h"
 #include "gq_context.h"
+#include "gq_p2p.h"
 
 // ------------------------------------------------------------------------------ errors
 static thread_local std::string g_err;
@@ -652,15 +653,16 @@ static bool lazy_ok(const gq_ctx *c, unsigned limb0, unsigned nlimbs) {
 // scaleD > 0 (lazy kernels only; the caller checked crt_pre_ok): the inverse transform ends with the CRT
 // pre-multiplication of the basis {p_0..p_(scaleD-1)} folded into N^-1
 static int ntt_internal(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys, uint64_t *data,
-                        bool inverse, cudaStream_t st, int only = 0, unsigned scaleD = 0) {
+                        bool inverse, cudaStream_t st, int only = 0, unsigned scaleD = 0,
+                        const GqWaitIn *wt = nullptr) {
   const bool lazy = lazy_ok(c, limb0, nlimbs);
   if (!lazy) {
-    if (scaleD) GQ_FAIL("internal: pre-scaled inverse NTT needs the lazy kernels");
+    if (scaleD || wt) GQ_FAIL("internal: pre-scaled / flag-waiting NTT needs the lazy kernels");
     return gq_ntt_batch_dev(c, limb0, nlimbs, npolys, data, (inverse ? 1 : 0) | (only << 1), (void *)st);
   }
   if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
-  int r = gq_launch_ntt_lazy(c->ntt_tables(inverse ? scaleD : 0), data, (int)limb0, (int)nlimbs, (int)npolys, inverse, st, only);
-  if (r < 0) GQ_FAIL("unsupported ring degree");
+  int r = gq_launch_ntt_lazy(c->ntt_tables(inverse ? scaleD : 0), data, (int)limb0, (int)nlimbs, (int)npolys, inverse, st, only, wt);
+  if (r < 0) GQ_FAIL(r == -2 ? "no flag-waiting transform for this ring degree" : "unsupported ring degree");
   c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);
   return 0;
@@ -679,10 +681,11 @@ static bool crt_pre_ok(const gq_ctx *c, unsigned D, const GqModulus &q) {
 // whole range (gq_launch_ntt_lazy_fused); false = the caller runs the separate pointwise kernel and ntt_internal
 static bool fused_inv_ok(const gq_ctx *c, unsigned limb0, unsigned nlimbs);
 static int ntt_inv_fused(gq_ctx *c, int mode, unsigned limb0, unsigned nlimbs, const uint64_t *x, uint64_t *y,
-                         const uint64_t *e0, const uint64_t *e1, uint64_t g, cudaStream_t st, unsigned scaleD) {
+                         const uint64_t *e0, const uint64_t *e1, uint64_t g, cudaStream_t st, unsigned scaleD,
+                         const GqPeerOut *po = nullptr) {
   if (!ntt_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or modulus below 32 bits");
-  int r = gq_launch_ntt_lazy_fused(c->ntt_tables(scaleD), mode, x, y, e0, e1, (unsigned)g, (int)limb0, (int)nlimbs, st);
-  if (r < 0) GQ_FAIL("unsupported ring degree");
+  int r = gq_launch_ntt_lazy_fused(c->ntt_tables(scaleD), mode, x, y, e0, e1, (unsigned)g, (int)limb0, (int)nlimbs, st, po);
+  if (r < 0) GQ_FAIL(r == -2 ? "no peer-output transform for this ring degree" : "unsupported ring degree");
   c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);
   return 0;
@@ -754,7 +757,8 @@ static GqPtrs4 ptrs(const uint64_t *a, const uint64_t *b = nullptr, const uint64
 // ncoef: coefficients per polynomial in this call (0 = the whole ring); the coefficient-local
 // stages work on any slice because one thread owns one coefficient
 static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtrs4 &in, unsigned W,
-                         unsigned npolys, uint64_t *out, cudaStream_t st, unsigned ncoef = 0) {
+                         unsigned npolys, uint64_t *out, cudaStream_t st, unsigned ncoef = 0,
+                         const GqPeerOut *po = nullptr) {
   if (ncoef == 0) ncoef = c->n;
   if (limb0 + nlimbs > c->dimub) GQ_FAIL("limb range exceeds dimub");
   if (W == 0 || W > GQ_MAX_W) GQ_FAIL("word count out of range");
@@ -765,8 +769,8 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
   // 3 = 28-bit digits with the pseudo-Mersenne fold
   const int digits = !dig ? 0 : (W <= 7 && !getenv("GPQHE_B200_DEC32")) ? (pm_ok(c, limb0, nlimbs) ? 3 : 2) : 1;
   if (gq_launch_decompose(c->dec_tables(), (int)ncoef, (int)limb0, (int)nlimbs, in, (int)W, out,
-                          (int)npolys, st, digits) < 0)
-    GQ_FAIL("no decompose kernel for this width");
+                          (int)npolys, st, digits, po) < 0)
+    GQ_FAIL(po ? "no peer-output decompose kernel for these parameters" : "no decompose kernel for this width");
   c->launches++;
   GQ_CHECK_LAUNCH(c);
   return 0;
@@ -775,14 +779,14 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
 // rs_j > 0: he_rs fused behind the CRT (power-of-two q and Delta; the caller checks with rs_fusable)
 static int reconstruct_dev(gq_ctx *c, unsigned D, const uint64_t *rhat, const GqModulus &q,
                            const GqPtrs4 &out, unsigned Wout, unsigned npolys, cudaStream_t st,
-                           unsigned ncoef = 0, unsigned rs_j = 0, bool pre = false) {
+                           unsigned ncoef = 0, unsigned rs_j = 0, bool pre = false, const GqWaitIn *wt = nullptr) {
   if (ncoef == 0) ncoef = c->n;
   if (D == 0 || D > c->dimub) GQ_FAIL("basis size out of range");
   if (c->basis[D - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
   if (npolys > 4) GQ_FAIL("at most 4 polynomials per reconstruct launch");
   const int r = gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)ncoef, rhat, q, out, (int)Wout,
-                                      (int)npolys, st, c->fast_crt ? c->d_fix : nullptr, rs_j, pre);
-  if (r < 0) GQ_FAIL("no reconstruct kernel for this width");
+                                      (int)npolys, st, c->fast_crt ? c->d_fix : nullptr, rs_j, pre, wt);
+  if (r < 0) GQ_FAIL(r == -2 ? "no flag-waiting reconstruct kernel for these parameters" : "no reconstruct kernel for this width");
   c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);
   return 0;
@@ -936,7 +940,7 @@ extern "C" void gq_evk_destroy(gq_evk *e) {
 // K6 on a coefficient slice: chat[2][D2][ncoef] -> c0, c1 (W words each), + add0/add1 (may be null)
 static int ks_epilogue_dev(gq_ctx *c, unsigned l, unsigned D2, const uint64_t *B, const uint64_t *add0,
                            const uint64_t *add1, uint64_t *c0, uint64_t *c1, unsigned ncoef,
-                           cudaStream_t st, unsigned rs_j = 0, bool pre = false) {
+                           cudaStream_t st, unsigned rs_j = 0, bool pre = false, const GqWaitIn *wt = nullptr) {
   if (ncoef == 0) ncoef = c->n;
   const unsigned n = ncoef, W = c->W;
   if (D2 == 0 || D2 > c->dimub || c->basis[D2 - 1].dev.WT == 0) GQ_FAIL("key-switch basis not supported");
@@ -945,9 +949,9 @@ static int ks_epilogue_dev(gq_ctx *c, unsigned l, unsigned D2, const uint64_t *B
   if (qm.dev.is_pow2) {
     r = gq_launch_ks_epilogue(c->basis[D2 - 1].dev, c->basis[c->dim - 1].dev, c->d_Pinv, c->d_primes,
                               (int)n, B, qm.dev.k, ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st,
-                              c->fast_crt ? c->d_fix : nullptr, rs_j, pre ? c->basis[D2 - 1].ratio : nullptr);
+                              c->fast_crt ? c->d_fix : nullptr, rs_j, pre ? c->basis[D2 - 1].ratio : nullptr, wt);
   } else {
-    if (rs_j || pre) GQ_FAIL("fused rescale / pre-scaled residues need power-of-two moduli");
+    if (rs_j || pre || wt) GQ_FAIL("fused rescale / pre-scaled residues / flag wait need power-of-two moduli");
     r = gq_launch_ks_epilogue_general(c->basis[D2 - 1].dev, c->d_Pwords, (int)c->P.w.size(),
                                       c->d_Pwords + GQ_MAX_W, c->d_primes, (int)n, B, qm.dev,
                                       ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st);
@@ -1869,4 +1873,111 @@ extern "C" int gq_stage_rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_
   if (!c) GQ_FAIL("null context");
   if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
   return rescale_dev(c, l, c0, c1, divide != 0, stream, ncoef);
+}
+
+// ---------------------------------------------- fused compute + exchange of the limb-sharded pipeline
+// The same stages as gq_stage_*_dev with the exchange folded into the kernels (gq_p2p.h): `send` makes the producing
+// kernel store its results straight into the peers' receive slabs over NVLink and publish the epoch from its last
+// block; `wait` makes the consuming kernel poll this rank's flags before it reads its slab.  One launch where the
+// unfused plan has scatter + signal (producer) or wait + kernel (consumer).
+static int to_peer_out(const gq_ctx *c, const gq_p2p_xchg *x, unsigned nloc, GqPeerOut *po) {
+  if (!x || !x->dst || !x->off || !x->flags || !x->epoch_dev || !x->err_dev || !x->ticket_dev) GQ_FAIL("incomplete send descriptor");
+  if (x->G == 0 || x->G > GQ_P2P_MAX_RANKS || x->me >= x->G || x->slot >= 8) GQ_FAIL("bad rank / slot in send descriptor");
+  if (nloc == 0 || nloc * x->G != c->n) GQ_FAIL("coefficient slice does not match the rank count");
+  for (unsigned s = 0; s < GQ_P2P_MAX_RANKS; s++) {
+    po->dst.base[s] = s < x->G ? (uint64_t *)x->dst[s] : nullptr;
+    po->flags[s] = s < x->G ? (uint64_t *)x->flags[s] : nullptr;
+  }
+  for (unsigned s = 0; s <= GQ_P2P_MAX_RANKS; s++) po->dst.off[s] = x->off[s <= x->G ? s : x->G];
+  po->G = (int)x->G; po->me = (int)x->me; po->nloc = (int)nloc; po->n = (int)c->n; po->D = (int)x->D;
+  po->slot = (int)x->slot; po->epoch = x->epoch_dev; po->err = x->err_dev; po->ticket = x->ticket_dev;
+  return 0;
+}
+static int to_wait(const gq_p2p_xchg *x, GqWaitIn *w) {
+  if (!x || !x->flags_local || !x->epoch_dev || !x->err_dev) GQ_FAIL("incomplete wait descriptor");
+  if (x->G == 0 || x->G > GQ_P2P_MAX_RANKS || x->slot >= 8) GQ_FAIL("bad rank count / slot in wait descriptor");
+  w->flags = x->flags_local; w->slot = (int)x->slot; w->G = (int)x->G; w->epoch = x->epoch_dev; w->err = x->err_dev;
+  w->spin_limit = 20000000ull;          // 4 s of 200 ns polls; GPQHE_B200_P2P_TIMEOUT_MS overrides
+  if (const char *e = getenv("GPQHE_B200_P2P_TIMEOUT_MS")) {
+    const long long ms = atoll(e);
+    if (ms > 0) w->spin_limit = (unsigned long long)ms * 5000ull;
+  }
+  return 0;
+}
+
+// 1 when every stage of he_mul at level l has its fused form for this context (two-kernel transforms, 28-bit digit
+// decomposition, fast CRT kernels, pseudo-Mersenne pointwise loaders), else 0: the caller then uses the unfused plan
+extern "C" int gq_p2p_fused_ok(gq_ctx *c, unsigned l) {
+  if (!c || !c->has_he || l > c->L) return 0;
+  const unsigned D1 = dim_tensor(c, l), D2 = dim_ks(c, l);
+  if (c->logn <= 12 || c->W > 7 || !c->fast_crt || getenv("GPQHE_B200_DEC32")) return 0;
+  if (D1 > c->dimub || D2 > c->dimub || D2 > c->dimevk) return 0;
+  if (!fused_inv_ok(c, 0, D1) || !fused_inv_ok(c, 0, D2)) return 0;
+  for (unsigned d = 0; d < D2; d++) if (c->primes[d].bits < 33 || c->primes[d].bits > 60) return 0;
+  const GqModulus &q = c->qmod[l].dev;
+  if (!q.is_pow2 || q.k < 1 || !c->basis[D1 - 1].dev.F || !c->basis[D2 - 1].dev.F) return 0;
+  if (c->basis[c->dim - 1].dev.WT > c->basis[D2 - 1].dev.WT) return 0;
+  return 1;
+}
+
+extern "C" int gq_p2p_decompose_dev(gq_ctx *c, unsigned nlimbs, unsigned npolys, const uint64_t *const *in, unsigned W,
+                                    unsigned ncoef, const gq_p2p_xchg *send, void *stream) {
+  if (!c || !in || npolys == 0 || npolys > 4 || nlimbs == 0) GQ_FAIL("bad argument");
+  GqPeerOut po;
+  if (to_peer_out(c, send, ncoef, &po)) return 1;
+  GqPtrs4 p = ptrs(in[0], npolys > 1 ? in[1] : nullptr, npolys > 2 ? in[2] : nullptr, npolys > 3 ? in[3] : nullptr);
+  return decompose_dev(c, 0, nlimbs, p, W, npolys, nullptr, pick(c, stream), ncoef, &po);
+}
+
+extern "C" int gq_p2p_ntt_fwd_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned npolys, uint64_t *data,
+                                  const gq_p2p_xchg *wait, void *stream) {
+  if (!c || !data || npolys == 0) GQ_FAIL("bad argument");
+  GqWaitIn w;
+  if (to_wait(wait, &w)) return 1;
+  return ntt_internal(c, limb0, nlimbs, npolys, data, false, pick(c, stream), 0, 0, &w);
+}
+
+extern "C" int gq_p2p_tensor_inv_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, uint64_t *y_scratch, const uint64_t *x,
+                                     const gq_p2p_xchg *send, void *stream) {
+  if (!c || !y_scratch || !x) GQ_FAIL("bad argument");
+  if (!fused_inv_ok(c, limb0, nlimbs)) GQ_FAIL("no fused tensor + inverse NTT for these primes");
+  GqPeerOut po;
+  if (to_peer_out(c, send, c->n / (send ? send->G : 1), &po)) return 1;
+  return ntt_inv_fused(c, GQ_NTTF_TENSOR, limb0, nlimbs, x, y_scratch, nullptr, nullptr, 1, pick(c, stream), 0, &po);
+}
+
+extern "C" int gq_p2p_mul_evk_inv_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, uint64_t *y_scratch, const uint64_t *x,
+                                      const gq_evk *evk, const gq_p2p_xchg *send, void *stream) {
+  if (!c || !y_scratch || !x || !evk) GQ_FAIL("bad argument");
+  if (limb0 + nlimbs > c->dimevk || !fused_inv_ok(c, limb0, nlimbs)) GQ_FAIL("limb range invalid or no fused form for these primes");
+  GqPeerOut po;
+  if (to_peer_out(c, send, c->n / (send ? send->G : 1), &po)) return 1;
+  const size_t off = (size_t)limb0 * c->n;
+  return ntt_inv_fused(c, GQ_NTTF_EVK, limb0, nlimbs, x, y_scratch, evk->p0 + off, evk->p1 + off, 1, pick(c, stream), 0, &po);
+}
+
+extern "C" int gq_p2p_reconstruct_dev(gq_ctx *c, unsigned D, unsigned l, unsigned npolys, const uint64_t *rhat,
+                                      uint64_t *const *out, unsigned ncoef, const gq_p2p_xchg *wait, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (!rhat || !out || npolys == 0 || npolys > 4) GQ_FAIL("bad argument");
+  if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
+  GqWaitIn w;
+  if (to_wait(wait, &w)) return 1;
+  GqPtrs4 p = ptrs(out[0], npolys > 1 ? out[1] : nullptr, npolys > 2 ? out[2] : nullptr, npolys > 3 ? out[3] : nullptr);
+  return reconstruct_dev(c, D, rhat, c->qmod[l].dev, p, c->W, npolys, pick(c, stream), ncoef, 0, false, &w);
+}
+
+extern "C" int gq_p2p_ks_epilogue_dev(gq_ctx *c, unsigned l, const uint64_t *chat, const uint64_t *add0,
+                                      const uint64_t *add1, uint64_t *c0, uint64_t *c1, unsigned ncoef, int rescale,
+                                      const gq_p2p_xchg *wait, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (rescale && l == 0) GQ_FAIL("cannot go below level 0");
+  if (!chat || !c0 || !c1) GQ_FAIL("null argument");
+  if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
+  GqWaitIn w;
+  if (to_wait(wait, &w)) return 1;
+  const unsigned rs_j = rescale ? rs_fusable(c, l) : 0;
+  if (ks_epilogue_dev(c, l, dim_ks(c, l), chat, add0, add1, c0, c1, ncoef, pick(c, stream), rs_j, false, &w)) return 1;
+  if (rescale && !rs_j) return rescale_dev(c, l, c0, c1, true, stream, ncoef);
+  return 0;
 }

@@ -24,6 +24,7 @@ to the single-GPU result (tests/test_sharded.py).
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
@@ -352,6 +353,24 @@ class P2PPlan:
         self.c_off1 = (C.c_int * (G + 1))(*self.off1)
         self.c_off2 = (C.c_int * (G + 1))(*self.off2)
         self.graph = None
+        # fused compute + exchange (gq_p2p.h): the producing kernels store into the peers' slabs and signal from their
+        # last block, the consuming kernels poll their flags in their prologue - no scatter / signal / wait launches.
+        # Needs the two-kernel transforms (n > 2^12) and the fast CRT / decompose kernels; GPQHE_B200_P2P_UNFUSED=1
+        # keeps the round-1 plan for A/B measurements.
+        self.fused = bool(self._lib.gq_p2p_fused_ok(self._h, l)) and not os.environ.get("GPQHE_B200_P2P_UNFUSED")
+        self.ticket = torch.zeros(8, dtype=torch.int32, device=self.device)
+        vp = lambda arr: C.cast(arr, C.c_void_p)
+
+        def xchg(slot, D, dst, off):
+            x = capi.GqP2pXchg()
+            x.G, x.me, x.slot, x.D = G, rank, slot, D
+            x.dst, x.off, x.flags = vp(dst), vp(off), vp(self.p_flags)
+            x.flags_local = self._loc("flags")
+            x.epoch_dev, x.err_dev = self.epoch.data_ptr(), self.err.data_ptr()
+            x.ticket_dev = self.ticket.data_ptr() + 4 * slot
+            return x
+        self.x = [xchg(0, self.D1, self.p_xl1, self.c_off1), xchg(1, self.D1, self.p_rh, self.c_off1),
+                  xchg(2, self.D2, self.p_xl2, self.c_off2), xchg(3, self.D2, self.p_ch, self.c_off2)]
 
     def _offsets(self, D):
         base, extra = divmod(D, self.G)
@@ -397,6 +416,8 @@ class P2PPlan:
 
     # -- the five segments (producer side ends with scatter + signal, consumer side starts with wait)
     def seg(self, k):
+        if self.fused:
+            return self._seg_fused(k)
         lib, h, W, nl = self._lib, self._h, self.W, self.nl
         if k == 0:
             self._ck(lib.gq_p2p_bump_dev(h, self.epoch.data_ptr(), None))
@@ -429,6 +450,40 @@ class P2PPlan:
             ks = lib.gq_stage_ks_epilogue_rs_dev if self.rescale else lib.gq_stage_ks_epilogue_dev
             self._ck(ks(h, self.l, self._loc("ch"), self.d[0].data_ptr(), self.d[1].data_ptr(),
                         self.out[0].data_ptr(), self.out[1].data_ptr(), nl, None))
+
+    def _seg_fused(self, k):
+        """the same five segments with the exchanges inside the kernels: 16 launches per op instead of 28"""
+        lib, h, W, nl, x = self._lib, self._h, self.W, self.nl, self.x
+        ref = C.byref
+        if k == 0:
+            self._ck(lib.gq_p2p_bump_dev(h, self.epoch.data_ptr(), None))
+            arr = (C.c_void_p * 4)(*[self.inp[j].data_ptr() for j in range(4)])
+            self._ck(lib.gq_p2p_decompose_dev(h, self.D1, 4, arr, W, nl, ref(x[0]), None))
+        elif k == 1:
+            if self.D1l:
+                xl = self._loc("xl1")
+                self._ck(lib.gq_p2p_ntt_fwd_dev(h, self.lo1, self.D1l, 4, xl, ref(x[0]), None))
+                self._ck(lib.gq_p2p_tensor_inv_dev(h, self.lo1, self.D1l, self.yl.data_ptr(), xl, ref(x[1]), None))
+            else:                      # a rank that owns no limb of this basis still takes part in the exchange
+                self._wait(0)
+                self._ck(lib.gq_p2p_signal_dev(h, self.p_flags, 1, self.G, self.rank, self.epoch.data_ptr(), self.err.data_ptr(), None))
+        elif k == 2:
+            outs = (C.c_void_p * 3)(*[self.d[j].data_ptr() for j in range(3)])
+            self._ck(lib.gq_p2p_reconstruct_dev(h, self.D1, self.l, 3, self._loc("rh"), outs, nl, ref(x[1]), None))
+            arr = (C.c_void_p * 1)(self.d[2].data_ptr())
+            self._ck(lib.gq_p2p_decompose_dev(h, self.D2, 1, arr, W, nl, ref(x[2]), None))
+        elif k == 3:
+            if self.D2l:
+                xl = self._loc("xl2")
+                self._ck(lib.gq_p2p_ntt_fwd_dev(h, self.lo2, self.D2l, 1, xl, ref(x[2]), None))
+                self._ck(lib.gq_p2p_mul_evk_inv_dev(h, self.lo2, self.D2l, self.y2l.data_ptr(), xl, self.rlk._h, ref(x[3]), None))
+            else:
+                self._wait(2)
+                self._ck(lib.gq_p2p_signal_dev(h, self.p_flags, 3, self.G, self.rank, self.epoch.data_ptr(), self.err.data_ptr(), None))
+        else:
+            self._ck(lib.gq_p2p_ks_epilogue_dev(h, self.l, self._loc("ch"), self.d[0].data_ptr(), self.d[1].data_ptr(),
+                                                self.out[0].data_ptr(), self.out[1].data_ptr(), nl,
+                                                1 if self.rescale else 0, ref(x[3]), None))
 
     def run(self, check=True):
         """one he_mul (+ he_rs): self.inp -> self.out (real multi-rank use; every rank calls it).

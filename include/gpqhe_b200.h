@@ -372,6 +372,44 @@ int gq_p2p_signal_dev(gq_ctx *ctx, const uint64_t *const *flags, unsigned slot, 
 int gq_p2p_wait_dev(gq_ctx *ctx, const uint64_t *flags_local_dev, unsigned slot, unsigned G,
                     const unsigned long long *epoch_dev, int *err_dev, void *stream);
 
+/* ---- fused compute + exchange (round 2): the stages above with the exchange INSIDE the producing / consuming kernel
+ * (gq_p2p.h).  `send`: the kernel stores its results straight into the peers' receive slabs (dst[s] = rank s's
+ * buffer of this exchange as mapped here, off[G+1] = limb ownership, D = limbs of the exchange) and its last block
+ * publishes *epoch_dev in flag[slot][me] of every rank (flags[s]) - or a poison value when *err_dev is set;
+ * ticket_dev is a zeroed device word the kernel uses to find its last block.  `wait`: every block of the kernel polls
+ * flag[slot][0..G) of this rank (flags_local) for *epoch_dev before it reads its slab; a timeout
+ * (GPQHE_B200_P2P_TIMEOUT_MS) or a poisoned flag sets *err_dev (sticky).  No reference counterpart: the reference has
+ * no multi-device path at all.  gq_p2p_fused_ok: 1 when he_mul at level l can run entirely on these entry points.
+ *   decompose    in[npolys] (W words x ncoef, my coefficient slice) -> residues of all nlimbs limbs at their owners
+ *   ntt_fwd      forward NTT of a receive slab (waits first)
+ *   tensor_inv / mul_evk_inv   pointwise stage + inverse NTT of my limbs; y_scratch[3|2][nlimbs][n] is scratch between
+ *                              the two passes, the finished coefficients go to their owners
+ *   reconstruct / ks_epilogue  CRT stages on a receive slab (wait first); ks_epilogue folds he_rs in when `rescale` */
+typedef struct gq_p2p_xchg {
+  unsigned G, me, slot, D;
+  const uint64_t *const *dst;
+  const int *off;
+  const uint64_t *const *flags;
+  const uint64_t *flags_local;
+  const unsigned long long *epoch_dev;
+  int *err_dev;
+  unsigned *ticket_dev;
+} gq_p2p_xchg;
+int gq_p2p_fused_ok(gq_ctx *ctx, unsigned l);
+int gq_p2p_decompose_dev(gq_ctx *ctx, unsigned nlimbs, unsigned npolys, const uint64_t *const *in_dev, unsigned W,
+                         unsigned ncoef, const gq_p2p_xchg *send, void *stream);
+int gq_p2p_ntt_fwd_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsigned npolys, uint64_t *data_dev,
+                       const gq_p2p_xchg *wait, void *stream);
+int gq_p2p_tensor_inv_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, uint64_t *y_scratch_dev, const uint64_t *x_dev,
+                          const gq_p2p_xchg *send, void *stream);
+int gq_p2p_mul_evk_inv_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, uint64_t *y_scratch_dev, const uint64_t *x_dev,
+                           const gq_evk *evk, const gq_p2p_xchg *send, void *stream);
+int gq_p2p_reconstruct_dev(gq_ctx *ctx, unsigned D, unsigned l, unsigned npolys, const uint64_t *rhat_dev,
+                           uint64_t *const *out_dev, unsigned ncoef, const gq_p2p_xchg *wait, void *stream);
+int gq_p2p_ks_epilogue_dev(gq_ctx *ctx, unsigned l, const uint64_t *chat_dev, const uint64_t *add0_dev,
+                           const uint64_t *add1_dev, uint64_t *c0_dev, uint64_t *c1_dev, unsigned ncoef, int rescale,
+                           const gq_p2p_xchg *wait, void *stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

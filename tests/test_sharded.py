@@ -113,8 +113,9 @@ def test_sharded_stage_entry_points_gpu(real_lib):
     assert got == want and single == want
 
 
-def _loopback_case(lib_path, logn, q, Delta, logqub, G, device):
-    """G virtual ranks in ONE process through the peer-to-peer plan (scatter kernels + flags)."""
+def _loopback_case(lib_path, logn, q, Delta, logqub, G, device, expect_fused=None):
+    """G virtual ranks in ONE process through the peer-to-peer plan (scatter kernels + flags, or - for n > 2^12 -
+    the exchanges fused into the producing / consuming kernels)."""
     import gpqhe_b200 as g
     from gpqhe_b200.sharded import P2PPlan
     from oracle import pyoracle as o
@@ -123,18 +124,28 @@ def _loopback_case(lib_path, logn, q, Delta, logqub, G, device):
     rng = random.Random(7)
     n, W, l = ctx.n, ctx.W, ctx.L
     ql = oc.ql[l]
-    polys = [[rng.randrange(ql) - ql // 2 for _ in range(n)] for _ in range(4)]
+    if n > 4096:          # Python big integers are too slow up here: numpy words, checked against the single-GPU call
+        polys = None
+    else:
+        polys = [[rng.randrange(ql) - ql // 2 for _ in range(n)] for _ in range(4)]
     nr = np.random.default_rng(11)
     p0 = np.concatenate([nr.integers(0, oc.primes[d], size=n, dtype=np.uint64) for d in range(oc.dimevk)])
     p1 = np.concatenate([nr.integers(0, oc.primes[d], size=n, dtype=np.uint64) for d in range(oc.dimevk)])
     evk = ctx.genevk(p0, p1)
-    big = [torch.from_numpy(g.ints_to_big(p, W).view(np.int64)).to(device) for p in polys]
+    if polys is None:
+        import parity_cases as pc
+        words = [pc._rand_big(nr, n, W, ql.bit_length() - 1) for _ in range(4)]
+        big = [torch.from_numpy(w.view(np.int64)).to(device) for w in words]
+    else:
+        big = [torch.from_numpy(g.ints_to_big(p, W).view(np.int64)).to(device) for p in polys]
     import contextlib
     cm = contextlib.nullcontext()
     if torch.device(device).type == "cuda":
         cm = torch.cuda.stream(torch.cuda.ExternalStream(ctx._lib.gq_ctx_stream(ctx._h), device=device))
     with cm:
         plans = P2PPlan.loopback(ctx, G, l, evk, rescale=True, device=device)
+        if expect_fused is not None:
+            assert all(pl.fused == expect_fused for pl in plans)
         nl = n // G
         for r, pl in enumerate(plans):
             for k in range(4):
@@ -146,6 +157,11 @@ def _loopback_case(lib_path, logn, q, Delta, logqub, G, device):
         got = [g.big_to_ints(torch.cat([pl.out[k] for pl in plans], dim=1).cpu().numpy().view(np.uint64)) for k in range(2)]
         for pl in plans:
             pl.close()
+    if polys is None:
+        want = ctx.he_mul_rs(g.HeCt(l, words[0], words[1]), g.HeCt(l, words[2], words[3]), evk)
+        ctx.close()
+        assert got == [g.big_to_ints(want.c0), g.big_to_ints(want.c1)]
+        return
     e = o.he_rs(oc, o.he_mul(oc, {"l": l, "c0": polys[0], "c1": polys[1]}, {"l": l, "c0": polys[2], "c1": polys[3]}, (p0, p1)))
     ctx.close()
     assert got == [e["c0"], e["c1"]]
@@ -156,6 +172,15 @@ def test_p2p_plan_loopback_emulated(emul_lib, G, logn, logq, logDelta):
     if (1 << logn) % G:
         pytest.skip("ring degree not divisible")
     _loopback_case(emul_lib, logn, 1 << logq, 1 << logDelta, logq, G, "cpu")
+
+
+@pytest.mark.parametrize("G", [2, 4])
+def test_p2p_plan_fused_exchange_emulated(emul_lib, G, monkeypatch):
+    """n = 2^13: the exchanges run inside the producing / consuming kernels (gq_p2p.h); same bits as one GPU, and
+    the same bits with the fusion switched off"""
+    _loopback_case(emul_lib, 13, 1 << 120, 1 << 40, 120, G, "cpu", expect_fused=True)
+    monkeypatch.setenv("GPQHE_B200_P2P_UNFUSED", "1")
+    _loopback_case(emul_lib, 13, 1 << 120, 1 << 40, 120, G, "cpu", expect_fused=False)
 
 
 def test_p2p_timeout_is_sticky_and_poisons_peers(emul_lib):
@@ -197,3 +222,12 @@ def test_p2p_timeout_is_sticky_and_poisons_peers(emul_lib):
 @pytest.mark.parametrize("G", [1, 4, 8])
 def test_p2p_plan_loopback_gpu(real_lib, G):
     _loopback_case(real_lib, 12, 1 << 109, 1 << 30, 0, G, torch.device("cuda", 0))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("G,logn", [(2, 16), (8, 16), (4, 14)])
+def test_p2p_plan_fused_exchange_loopback_gpu(real_lib, G, logn):
+    """the fused exchange at the headline ring (and a ragged limb split) on one real GPU, virtual ranks in lockstep"""
+    if (1 << logn) % G:
+        pytest.skip("ring degree not divisible")
+    _loopback_case(real_lib, logn, 1 << 438, 1 << 50, 0, G, torch.device("cuda", 0), expect_fused=True)
