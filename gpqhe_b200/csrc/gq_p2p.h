@@ -60,9 +60,8 @@ GQ_DEV uint64_t *gq_peer_l2c(const GqPeerOut &po, int b, int dl, int j, int my_l
 // arrive publishes the epoch - or the poison value when this rank's error flag is set - to every peer.
 GQ_DEV void gq_peer_signal(const GqPeerOut &po) {
   __shared__ int s_last;
-#ifndef GQ_EMULATE
-  __threadfence_system();             // my stores to the peers are visible system-wide before my block's ticket
-#endif
+  // the grid-barrier pattern of cooperative groups: the block barrier orders every thread's stores before thread 0,
+  // whose system-scope fence is cumulative over them; one fence per block instead of one per thread
   __syncthreads();
   if (threadIdx.x == 0 && threadIdx.y == 0 && threadIdx.z == 0) {
     const unsigned nb = gridDim.x * gridDim.y * gridDim.z;
@@ -109,9 +108,9 @@ GQ_DEV void gq_peer_wait(const GqWaitIn &w) {
     }
     if (!ok) *w.err = 1;
     else if (*f == GQ_P2P_POISON) *w.err = 2;
-  }
 #ifndef GQ_EMULATE
-  __threadfence_system();             // acquire: slab reads below are ordered after the flag read
+    __threadfence_system();           // acquire: the slab reads behind the barrier are ordered after the flag read
 #endif
+  }
   __syncthreads();
 }
