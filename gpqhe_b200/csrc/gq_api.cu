@@ -127,8 +127,8 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
   hb.P = P;
   const unsigned bitsP = P.bits();
   const unsigned WT = round_wt((bitsP + 1 + 63) / 64);
-  if (WT > GQ_MAX_W || D > WT + WT / 8 + 2) {
-    // wider than the register-resident CRT kernels support (2048 bits): the context is still
+  if (WT > GQ_MAX_WT || D > WT + WT / 8 + 2) {
+    // wider than the register-resident CRT kernels support (3072 bits): the context is still
     // usable for the limb layer and for narrower bases; CRT over this basis fails loudly.
     hb.dev.D = (int)D; hb.dev.WT = 0;
     return 0;
@@ -782,7 +782,7 @@ static int reconstruct_dev(gq_ctx *c, unsigned D, const uint64_t *rhat, const Gq
                            unsigned ncoef = 0, unsigned rs_j = 0, bool pre = false, const GqWaitIn *wt = nullptr) {
   if (ncoef == 0) ncoef = c->n;
   if (D == 0 || D > c->dimub) GQ_FAIL("basis size out of range");
-  if (c->basis[D - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
+  if (c->basis[D - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 3072 bits is not supported by the CRT kernels");
   if (npolys > 4) GQ_FAIL("at most 4 polynomials per reconstruct launch");
   const int r = gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)ncoef, rhat, q, out, (int)Wout,
                                       (int)npolys, st, c->fast_crt ? c->d_fix : nullptr, rs_j, pre, wt);
@@ -970,7 +970,7 @@ static int keyswitch_dev(gq_ctx *c, unsigned l, const uint64_t *d, const gq_evk 
   const unsigned D2 = dim_ks(c, l), n = c->n, W = c->W;
   if (D2 > c->dimevk) GQ_FAIL("key-switch basis exceeds dimevk");
   if (!ntt_ok(c, 0, D2)) GQ_FAIL("modulus below 32 bits");
-  if (c->basis[D2 - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
+  if (c->basis[D2 - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 3072 bits is not supported by the CRT kernels");
   if (ensure_slot(c, GQ_SLOT_LIMB_A, (size_t)4 * c->dimub * n * 8) ||
       ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8)) return 1;
   uint64_t *A = (uint64_t *)c->slot[GQ_SLOT_LIMB_A], *B = (uint64_t *)c->slot[GQ_SLOT_LIMB_B];
@@ -1183,7 +1183,7 @@ extern "C" int gq_he_rot_hoisted_dev(gq_ctx *c, unsigned l, unsigned count, cons
   const unsigned D2 = dim_ks(c, l), n = c->n, W = c->W;
   if (D2 > c->dimevk) GQ_FAIL("key-switch basis exceeds dimevk");
   if (!ntt_ok(c, 0, D2)) GQ_FAIL("modulus below 32 bits");
-  if (c->basis[D2 - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
+  if (c->basis[D2 - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 3072 bits is not supported by the CRT kernels");
   if (ensure_slot(c, GQ_SLOT_LIMB_A, (size_t)4 * c->dimub * n * 8) ||
       ensure_slot(c, GQ_SLOT_LIMB_B, (size_t)3 * c->dimub * n * 8) ||
       ensure_slot(c, GQ_SLOT_BIG, (size_t)5 * W * n * 8)) return 1;

@@ -705,9 +705,11 @@ k_decompose(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *
 }  // namespace
 
 // ---- launchers --------------------------------------------------------------------
-#define GQ_WT_SWITCH(WTV, STMT8, STMT16, STMT24, STMT32) \
-  switch (WTV) { case 8: STMT8; break; case 16: STMT16; break; case 24: STMT24; break; \
-                 case 32: STMT32; break; default: return -1; }
+// exact (full-width) kernels exist for CRT bases of up to GQ_MAX_WT = 48 words (3 072 bits: the 47-limb key-switch
+// basis of the reference's logn = 15, logq = 881 ring needs 2 774); M(WT) is expanded once per width
+#define GQ_WT_CASES(WTV, M) \
+  switch (WTV) { case 8: M(8); break; case 16: M(16); break; case 24: M(24); break; case 32: M(32); break; \
+                 case 40: M(40); break; case 48: M(48); break; default: return -1; }
 
 // fix: {count, list} scratch of the context; non-null selects the fast low-word kernel followed
 // by the exact kernel in list mode (power-of-two q only).  Returns kernels launched.
@@ -737,19 +739,15 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
   } else if (wt) {
     return -2;        // the flag wait lives in the fast kernel only
   }
+#define GQ_REC_T(V) GQ_LAUNCH((k_reconstruct<V, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre)
+#define GQ_REC_F(V) GQ_LAUNCH((k_reconstruct<V, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre)
   if (q.is_pow2) {
-    GQ_WT_SWITCH(B.WT,
-      GQ_LAUNCH((k_reconstruct<8, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
-      GQ_LAUNCH((k_reconstruct<16, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
-      GQ_LAUNCH((k_reconstruct<24, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
-      GQ_LAUNCH((k_reconstruct<32, true>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre))
+    GQ_WT_CASES(B.WT, GQ_REC_T)
   } else {
-    GQ_WT_SWITCH(B.WT,
-      GQ_LAUNCH((k_reconstruct<8, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
-      GQ_LAUNCH((k_reconstruct<16, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
-      GQ_LAUNCH((k_reconstruct<24, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre),
-      GQ_LAUNCH((k_reconstruct<32, false>), grid, block, st, B, primes, n, rhat, q, out, Wout, fc, fl, rs_j, pre))
+    GQ_WT_CASES(B.WT, GQ_REC_F)
   }
+#undef GQ_REC_T
+#undef GQ_REC_F
   return launches;
 }
 
@@ -811,6 +809,8 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
     case 16: r = ks_dispatch_wp<16>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j, ratio); break;
     case 24: r = ks_dispatch_wp<24>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j, ratio); break;
     case 32: r = ks_dispatch_wp<32>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j, ratio); break;
+    case 40: r = ks_dispatch_wp<40>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j, ratio); break;
+    case 48: r = ks_dispatch_wp<48>(B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, grid, st, fc, fl, rs_j, ratio); break;
   }
   return r < 0 ? r : launches;
 }
@@ -854,10 +854,8 @@ int gq_launch_ks_epilogue_general(const GqCrtBasis &B, const uint64_t *P, int nP
                                   const GqModulus &q, const GqPtrs4 &add, int Wadd,
                                   const GqPtrs4 &out, int Wout, int npolys, cudaStream_t st) {
   dim3 grid((n + 127) / 128, npolys), block(128);
-  GQ_WT_SWITCH(B.WT,
-    GQ_LAUNCH(k_ks_epilogue_general<8>, grid, block, st, B, P, nP, Ph, primes, n, chat, q, add, Wadd, out, Wout),
-    GQ_LAUNCH(k_ks_epilogue_general<16>, grid, block, st, B, P, nP, Ph, primes, n, chat, q, add, Wadd, out, Wout),
-    GQ_LAUNCH(k_ks_epilogue_general<24>, grid, block, st, B, P, nP, Ph, primes, n, chat, q, add, Wadd, out, Wout),
-    GQ_LAUNCH(k_ks_epilogue_general<32>, grid, block, st, B, P, nP, Ph, primes, n, chat, q, add, Wadd, out, Wout))
+#define GQ_KSG(V) GQ_LAUNCH(k_ks_epilogue_general<V>, grid, block, st, B, P, nP, Ph, primes, n, chat, q, add, Wadd, out, Wout)
+  GQ_WT_CASES(B.WT, GQ_KSG)
+#undef GQ_KSG
   return 1;
 }

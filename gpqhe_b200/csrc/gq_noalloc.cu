@@ -67,7 +67,7 @@ extern "C" int gq_stage_reconstruct_noalloc_dev(gq_ctx *c, unsigned D, unsigned 
   if ((unsigned long long)npolys * ncoef > GQ_NOALLOC_MAX_ENTRIES)
     NA_FAIL("npolys * ncoef exceeds the static scratch (GQ_NOALLOC_MAX_ENTRIES = 262144 coefficients per call)");
   if (D == 0 || D > c->dimub) NA_FAIL("basis size out of range");
-  if (c->basis[D - 1].dev.WT == 0) NA_FAIL("RNS basis wider than 2048 bits is not supported by the CRT kernels");
+  if (c->basis[D - 1].dev.WT == 0) NA_FAIL("RNS basis wider than 3072 bits is not supported by the CRT kernels");
   cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
   int *fix = nullptr;
   if (c->fast_crt) {

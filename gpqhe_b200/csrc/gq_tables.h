@@ -5,7 +5,9 @@
 #include "gq_arith.h"
 
 #define GQ_MAX_PRIMES 64   // polyctx.dimub is 30 for the largest shipped ring
-#define GQ_MAX_W 32        // widest multiword integer kept in registers (2048 bits)
+#define GQ_MAX_W 32        // widest coefficient / modulus (words per big-poly coefficient, q, P): 2048 bits
+#define GQ_MAX_WT 48       // widest CRT basis product the exact kernels hold (3072 bits; only the low W words are
+                           // touched by the fast kernels, the full width by the rare exact fix-list kernels)
 #define GQ_DEC_W 33        // powers 2^(64w) mod p tabulated for w = 0..32
 
 // NTT view: everything kernels K1/K2/K3 need.

@@ -129,7 +129,7 @@ def test_reference_coeff2slot_program_same_output_emulated(emul_env):
 
 
 @pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "test-gpqhe")), reason="reference build absent")
-@pytest.mark.parametrize("op", ["inv", "sqrt", "sigmoid", "nrm2", "sum", "idx", "log", "add", "enc"])
+@pytest.mark.parametrize("op", ["inv", "sqrt", "sigmoid", "nrm2", "sum", "idx", "log", "cmp", "add", "enc"])
 def test_reference_algo_program_same_output_emulated(emul_env, op):
     """The compositions of src/he-algo.c that are NOT hand-ported (he_inv :131, he_sqrt :166, he_sigmoid, he_log,
     he_cmp, he_sum, he_idx, he_nrm2) run as the reference wrote them, primitive by primitive, on the device shadows
