@@ -127,6 +127,23 @@ GQ_DEV void store_words(uint64_t *__restrict__ out, int n, int i, int Wout, cons
   for (int w = WT; w < Wout; w++) out[(size_t)w * n + i] = fill;
 }
 
+// List mode of the exact kernels runs on GQ_FIX_BLOCKS blocks (an input crafted to sit on the +P/2 edge could put up to
+// 4n coefficients on the list: one block would serialise them on one SM).  fix[0] = pending count, fix[1] = lifetime
+// total, fix[2] = ticket: the last block to finish empties the list for the next call.
+#define GQ_FIX_BLOCKS 148
+GQ_DEV void fix_list_done(int *fix_count) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#ifdef GQ_EMULATE
+    const int t = fix_count[2]++;
+#else
+    __threadfence();
+    const int t = atomicAdd(fix_count + 2, 1);
+#endif
+    if (t == (int)gridDim.x - 1) { fix_count[0] = 0; fix_count[2] = 0; }
+  }
+}
+
 // ---- K5 ---------------------------------------------------------------------------
 // batch: poly b reads rhat + b*D*n, writes out.p[b]
 // rs_j > 0 (POW2 only): he_rs fused behind the CRT - rounded division by 2^rs_j, then smod 2^(k - rs_j).  The
@@ -163,10 +180,9 @@ k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
     if (cnt == 0) return;
     crt_stage<WT>(S, B, primes);
     __syncthreads();
-    for (int e = threadIdx.x; e < cnt; e += blockDim.x)
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < cnt; e += gridDim.x * blockDim.x)
       reconstruct_one<WT, POW2>(S, B, n, rhat, q, out, Wout, fix_list[e] / n, fix_list[e] % n, rs_j, pre);
-    __syncthreads();
-    if (threadIdx.x == 0) *fix_count = 0;
+    fix_list_done(fix_count);
     return;
   }
   crt_stage<WT>(S, B, primes);
@@ -260,10 +276,9 @@ k_ks_epilogue(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
   __syncthreads();
   if (fix_list) {   // one block: the coefficients the fast kernel left undecided
     const int cnt = *fix_count;
-    for (int e = threadIdx.x; e < cnt; e += blockDim.x)
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < cnt; e += gridDim.x * blockDim.x)
       ks_one<WT, WP>(S, SP, sPinv, B, BP, n, chat, k, add, Wadd, out, Wout, fix_list[e] / n, fix_list[e] % n, rs_j, pre);
-    __syncthreads();
-    if (threadIdx.x == 0) *fix_count = 0;
+    fix_list_done(fix_count);
     return;
   }
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -732,7 +747,7 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
     else if (W <= 5) GQ_RF(5); else if (W <= 6) GQ_RF(6); else if (W <= 7) GQ_RF(7); else if (W <= 8) GQ_RF(8);
     else if (W <= 12) GQ_RF(12); else if (W <= 16) GQ_RF(16); else if (W <= 24) GQ_RF(24); else GQ_RF(32);
 #undef GQ_RF
-    grid = dim3(1, 1);
+    grid = dim3(GQ_FIX_BLOCKS, 1);
     launches = 2;
   } else if (pre) {
     return -1;        // pre-scaled residues are only produced for the fast path
@@ -796,7 +811,7 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
 #undef GQ_KFL
       default: return -1;
     }
-    grid = dim3(1, 1);
+    grid = dim3(GQ_FIX_BLOCKS, 1);
     launches = 2;
   } else if (ratio) {
     return -1;        // pre-scaled residues are only produced for the fast path
