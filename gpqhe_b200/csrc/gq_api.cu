@@ -147,6 +147,7 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
     hinvsh[d] = (uint64_t)(((gq_u128)inv << 64) / pd);
     hb.inv.push_back(inv);
   }
+  hb.phat.assign(hphat, hphat + (size_t)D * WT);
   // fixed point for the fast CRT kernels: F = 64 + bits(p) - 1 when every prime has the same length
   int F = 64 + (int)c->primes[0].bits - 1;
   for (unsigned d = 0; d < D; d++) if (c->primes[d].bits != c->primes[0].bits) F = 0;
@@ -161,6 +162,7 @@ static int build_basis(gq_ctx *c, unsigned D, const BigU &P) {
     uint64_t cy = 1;
     for (size_t i = 0; i < hv.size(); i++) { uint64_t t = half.word(i) + cy; cy = (cy && t == 0); hv[i] = t; }
     BigU(hv.data(), hv.size()).mul(BigU(pw.data(), 3)).div(P).store(hhc, 2);
+    for (unsigned d = 0; d < D; d++) hb.u.push_back(hu[2 * d]);
   }
   uint64_t *dv = nullptr;
   if (upload(&dv, buf.data(), buf.size())) return 1;
@@ -425,6 +427,7 @@ extern "C" void gq_ctx_destroy(gq_ctx *c) {
   if (!c->parent) {     // a lane shares the tables of its parent
     cudaFree(c->d_primes); cudaFree(c->d_tw_fwd); cudaFree(c->d_tw_inv); cudaFree(c->d_tw_inv_last); cudaFree(c->d_fin_s);
     for (auto &b : c->basis) { cudaFree(b.fin_s); cudaFree(b.fin_w); cudaFree(b.ratio); }
+    for (auto &kv : c->tc_tabs) cudaFree(kv.second);
     cudaFree(c->d_pow64); cudaFree(c->d_t1sh); cudaFree(c->d_pow32); cudaFree(c->d_pow28); cudaFree(c->d_onesh); cudaFree(c->d_Pinv); cudaFree(c->d_Pwords);
     for (auto &b : c->basis) cudaFree(b.blob);
     for (auto &m : c->qmod) cudaFree(m.blob);
@@ -776,6 +779,29 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
   return 0;
 }
 
+// B-fragment table of the tensor-core CRT for (basis D, W result words), built once and kept by the root context
+static const uint32_t *tc_table(gq_ctx *c, unsigned D, unsigned W) {
+  const bool off = getenv("GPQHE_B200_NO_TC_CRT") != nullptr;      // A/B switch for tests and profiling
+  gq_ctx *root = c->parent ? c->parent : c;
+  if (off || W == 0 || W > 7 || D == 0 || D > root->dimub) return nullptr;
+  const GqHostBasis &hb = root->basis[D - 1];
+  if (!hb.dev.WT || hb.dev.F < 96 || hb.dev.F > 126 || hb.u.size() != D || hb.phat.size() != (size_t)D * hb.dev.WT) return nullptr;
+  const unsigned key = D * 16 + W;
+  auto it = root->tc_tabs.find(key);
+  if (it != root->tc_tabs.end()) return it->second;
+  std::vector<uint64_t> low((size_t)D * W, 0);
+  for (unsigned d = 0; d < D; d++)
+    for (unsigned w = 0; w < W && w < (unsigned)hb.dev.WT; w++) low[(size_t)d * W + w] = hb.phat[(size_t)d * hb.dev.WT + w];
+  std::vector<uint32_t> tab(gq_crt_tc_table_words((int)D, (int)W));
+  gq_crt_tc_table(tab.data(), (int)D, (int)W, low.data(), hb.u.data());
+  uint32_t *dv = nullptr;
+  if (cudaMalloc((void **)&dv, tab.size() * 4) != cudaSuccess) return nullptr;
+  // synchronous copy: every stream that will read the table is ordered after this host call
+  if (cudaMemcpy(dv, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(dv); return nullptr; }
+  root->tc_tabs[key] = dv;
+  return dv;
+}
+
 // rs_j > 0: he_rs fused behind the CRT (power-of-two q and Delta; the caller checks with rs_fusable)
 static int reconstruct_dev(gq_ctx *c, unsigned D, const uint64_t *rhat, const GqModulus &q,
                            const GqPtrs4 &out, unsigned Wout, unsigned npolys, cudaStream_t st,
@@ -784,8 +810,9 @@ static int reconstruct_dev(gq_ctx *c, unsigned D, const uint64_t *rhat, const Gq
   if (D == 0 || D > c->dimub) GQ_FAIL("basis size out of range");
   if (c->basis[D - 1].dev.WT == 0) GQ_FAIL("RNS basis wider than 3072 bits is not supported by the CRT kernels");
   if (npolys > 4) GQ_FAIL("at most 4 polynomials per reconstruct launch");
+  const uint32_t *tct = (pre && c->fast_crt && q.is_pow2 && q.k >= 1) ? tc_table(c, D, (q.k + 63) / 64) : nullptr;
   const int r = gq_launch_reconstruct(c->basis[D - 1].dev, c->d_primes, (int)ncoef, rhat, q, out, (int)Wout,
-                                      (int)npolys, st, c->fast_crt ? c->d_fix : nullptr, rs_j, pre, wt);
+                                      (int)npolys, st, c->fast_crt ? c->d_fix : nullptr, rs_j, pre, wt, tct);
   if (r < 0) GQ_FAIL(r == -2 ? "no flag-waiting reconstruct kernel for these parameters" : "no reconstruct kernel for this width");
   c->launches += (unsigned)r;
   GQ_CHECK_LAUNCH(c);

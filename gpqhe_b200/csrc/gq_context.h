@@ -1,6 +1,7 @@
 // gq_context.h - host-side context: the flattened, device-resident image of the
 // reference's process-global `polyctx` / `hectx` (src/precomp.c:38-47).
 #pragma once
+#include <map>
 #include <string>
 #include <vector>
 
@@ -12,6 +13,8 @@ struct GqHostBasis {
   BigU P;
   void *blob = nullptr;
   std::vector<uint64_t> inv;          // host copy of (P/p_d)^-1 mod p_d
+  std::vector<uint64_t> phat;         // host copy of P/p_d, [D][WT] words
+  std::vector<uint64_t> u;            // host copy of floor(2^F / p_d), [D]
   // final-scale tables of the lazy inverse NTT with (P/p_d)^-1 folded in (built on first use, gq_api.cu)
   ulonglong2 *fin_s = nullptr, *fin_w = nullptr;
   // key switch over this basis: (P_dim/p_d)^-1 * ((P/p_d)^-1)^-1 mod p_d for d < dim, Shoup pairs; turns the
@@ -65,6 +68,9 @@ struct gq_ctx {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   // staging of the batched host entry points when lanes are in use
   std::vector<cudaEvent_t> ev_batch;
+  // B-fragment tables of the tensor-core CRT (gq_crt_tc.cu), built on first use per (basis D, result words W);
+  // kept by the ROOT context (lanes look them up there)
+  std::map<unsigned, uint32_t *> tc_tabs;
   unsigned pt_bits = 0;          // gq_ctx_set_plaintext_bits: |m| < 2^pt_bits for the plaintexts of he_gemv (0 = unknown)
   bool lazy_ntt = true;          // internal pipelines use gq_ntt_lazy.cu when every prime allows it
 

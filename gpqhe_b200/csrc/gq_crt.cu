@@ -730,7 +730,8 @@ k_decompose(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *
 // by the exact kernel in list mode (power-of-two q only).  Returns kernels launched.
 int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, const uint64_t *rhat,
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix, unsigned rs_j, bool pre, const GqWaitIn *wt) {
+                          cudaStream_t st, int *fix, unsigned rs_j, bool pre, const GqWaitIn *wt,
+                          const uint32_t *tc_tab) {
   if (rs_j && (!q.is_pow2 || rs_j > q.k)) return -1;
   GqWaitIn w0 = GqWaitIn();
   if (wt) w0 = *wt;
@@ -743,6 +744,9 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
     dim3 g2((n + 255) / 256, npolys), b2(256);
 #define GQ_RF(V) do { if (pre) GQ_LAUNCH((k_reconstruct_fast<V, true>), g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j, w0); \
                       else GQ_LAUNCH((k_reconstruct_fast<V, false>), g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j, w0); } while (0)
+    // tensor-core form (gq_crt_tc.cu) when its table was built for this (basis, W): pre-scaled residues, W <= 7
+    if (tc_tab && pre && gq_launch_reconstruct_tc(B, tc_tab, n, rhat, q.k, out, Wout, npolys, st, fix, rs_j, wt) == 1) {
+    } else
     if (W <= 1) GQ_RF(1); else if (W <= 2) GQ_RF(2); else if (W <= 3) GQ_RF(3); else if (W <= 4) GQ_RF(4);
     else if (W <= 5) GQ_RF(5); else if (W <= 6) GQ_RF(6); else if (W <= 7) GQ_RF(7); else if (W <= 8) GQ_RF(8);
     else if (W <= 12) GQ_RF(12); else if (W <= 16) GQ_RF(16); else if (W <= 24) GQ_RF(24); else GQ_RF(32);

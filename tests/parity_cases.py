@@ -655,10 +655,12 @@ def check_fused_vs_separate(lib_path, logn, q=1 << 438, Delta=1 << 50, logqub=43
     full size): he_mul, he_mul+he_rs, he_mulpt, he_rot, he_conj, hoisted rotations, poly_mul - identical bits."""
     nr = np.random.default_rng(seed)
     res = []
-    for separate in (False, True):
-        if separate:
+    for separate in (False, True, "no_tc"):
+        if separate is True:
             os.environ["GPQHE_B200_NO_FUSED_INV"] = "1"
             os.environ["GPQHE_B200_NO_PRESCALE"] = "1"
+        elif separate == "no_tc":            # the integer-pipe CRT instead of the tensor-core contraction (gq_crt_tc.cu)
+            os.environ["GPQHE_B200_NO_TC_CRT"] = "1"
         try:
             ctx = g.HeContext(logn, q, 4, Delta, lib_path=lib_path, logqub=logqub)
             try:
@@ -688,7 +690,9 @@ def check_fused_vs_separate(lib_path, logn, q=1 << 438, Delta=1 << 50, logqub=43
         finally:
             os.environ.pop("GPQHE_B200_NO_FUSED_INV", None)
             os.environ.pop("GPQHE_B200_NO_PRESCALE", None)
-    assert len(res[0]) == len(res[1])
-    for k, (x, y) in enumerate(zip(res[0], res[1])):
+            os.environ.pop("GPQHE_B200_NO_TC_CRT", None)
+    assert len(res[0]) == len(res[1]) == len(res[2])
+    for k, (x, y, z) in enumerate(zip(res[0], res[1], res[2])):
         eq(x, y, f"fused vs separate pipeline, output {k}")
+        eq(x, z, f"tensor-core vs integer-pipe CRT, output {k}")
     del nr
