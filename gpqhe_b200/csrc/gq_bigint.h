@@ -122,9 +122,21 @@ GQ_HD void mw_smod_pow2(uint64_t *r, unsigned k) {
     for (int w = 0; w < W; w++) r[w] = ~(uint64_t)0;
     return;
   }
+  const unsigned sw = (k - 1) >> 6, sb = (k - 1) & 63;
+  // the usual case (k is the same for every thread of a launch: a uniform branch): the sign bit lies in the top
+  // word, only that word changes
+  if (sw == (unsigned)(W - 1)) {
+    r[W - 1] = (uint64_t)(((int64_t)(r[W - 1] << (63 - sb))) >> (63 - sb));
+    return;
+  }
+  if (W >= 2 && sw == (unsigned)(W - 2)) {
+    const uint64_t x = (uint64_t)(((int64_t)(r[W >= 2 ? W - 2 : 0] << (63 - sb))) >> (63 - sb));
+    r[W >= 2 ? W - 2 : 0] = x;
+    r[W - 1] = (uint64_t)((int64_t)x >> 63);
+    return;
+  }
   // Word selection is done with masks, never `if (w == sw) x = r[w]`: the compiler turns
   // such chains into a dynamic index, which forces the whole array into local memory.
-  const unsigned sw = (k - 1) >> 6, sb = (k - 1) & 63;
   uint64_t sel = 0;
 #pragma unroll
   for (int w = 0; w < W; w++) sel |= r[w] & (0 - (uint64_t)((unsigned)w == sw));
@@ -143,6 +155,20 @@ GQ_HD void mw_smod_pow2(uint64_t *r, unsigned k) {
 // == mpi_rdiv(r, 2^j) (an exact tie rounds toward -inf).  In place, signed.
 template <int W>
 GQ_HD void mw_rdiv_pow2(uint64_t *r, unsigned j) {
+  if (j < 64) {     // the usual case (Delta below 2^64; j is uniform over the launch): word-local funnel shifts
+    const uint64_t half = (r[0] >> (j - 1)) & 1u;
+    const uint64_t lower = (j > 1) ? (r[0] & ((((uint64_t)1) << (j - 1)) - 1)) : 0;
+    const uint64_t sign = 0 - (r[W - 1] >> 63);
+    uint64_t carry = (half && lower) ? 1u : 0u;        // remainder > 2^(j-1): an exact tie rounds toward -inf
+#pragma unroll
+    for (int w = 0; w < W; w++) {
+      const uint64_t hi = (w + 1 < W) ? r[w + 1] : sign;
+      const uint64_t x = ((r[w] >> j) | (hi << (64 - j))) + carry;
+      carry = (x < carry) ? 1u : 0u;
+      r[w] = x;
+    }
+    return;
+  }
   const unsigned jw = j >> 6, jb = j & 63;
   // remainder > 2^(j-1)  <=>  bit j-1 set and some lower bit set
   const unsigned hb = j - 1, hw = hb >> 6, hbb = hb & 63;
