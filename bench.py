@@ -443,25 +443,55 @@ def run_ours(args):
         in4 = (VP * 4)(*[b + j * poly for j in range(4)])
         in1 = (VP * 1)(d[2].data_ptr())
         out3 = (VP * 3)(*[d[j].data_ptr() for j in range(3)])
+        # the forms the op itself uses: inverse NTT ending in the CRT pre-multiplication, CRT stages on the tensor cores
+        pre1 = bool(lib.gq_stage_prescale_ok(h, D1, L, 0))
+        pre2 = bool(lib.gq_stage_prescale_ok(h, D2, L, 1))
+        imma_peak = (imma or {}).get("raw_u8_Tmac_per_s")
+
+        def tensor_inv(i):
+            if pre1:
+                ck(lib.gq_stage_tensor_inv_pre_dev(h, 0, D1, D1, y.data_ptr(), xc.data_ptr(), None))
+            else:
+                ck(lib.gq_stage_tensor_inv_dev(h, 0, D1, y.data_ptr(), xc.data_ptr(), None))
+
+        def reconstruct(i):
+            f = lib.gq_stage_reconstruct_pre_dev if pre1 else lib.gq_stage_reconstruct_dev
+            ck(f(h, D1, L, 3, y.data_ptr(), out3, n, None))
+
+        def evk_inv(i):
+            if pre2:
+                ck(lib.gq_stage_mul_evk_inv_pre_dev(h, 0, D2, D2, y2.data_ptr(), x2.data_ptr(), evk._h, None))
+            else:
+                ck(lib.gq_stage_mul_evk_inv_dev(h, 0, D2, y2.data_ptr(), x2.data_ptr(), evk._h, None))
+
+        def ks_epilogue(i):
+            if pre2:
+                ck(lib.gq_stage_ks_epilogue_pre_dev(h, L, y2.data_ptr(), d[0].data_ptr(), d[1].data_ptr(), o[0].data_ptr(), o[1].data_ptr(), n, 1, None))
+            else:
+                ck(lib.gq_stage_ks_epilogue_rs_dev(h, L, y2.data_ptr(), d[0].data_ptr(), d[1].data_ptr(), o[0].data_ptr(), o[1].data_ptr(), n, None))
+        # u8 multiply-accumulates per coefficient of the tensor-core CRT: 32 K-bytes per chunk of 4 limbs x 80 columns
+        tc_mac1 = 32 * ((D1 + 3) // 4) * 80
+        tc_mac2 = 32 * ((D2 + 3) // 4 + (ctx.dim + 3) // 4) * 80
         stages = [
             ("decompose x4 -> D1", "k_decompose28<7, pm>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D1, 4, in4, W, n, xc.data_ptr(), None)),
              4 * D1 * n, 34.0, 4 * W * n * 8 + 4 * D1 * n * 8),     # 15 digits x 2 multiply-adds + 4 in the fold
             ("forward NTT, 4 x D1 limb-polys", "k_nttl_fwd_strided<4> + k_nttl_fwd_tile<12>", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D1, 4, xc.data_ptr(), 0, None)),
              4 * D1 * (n // 2) * LOGN, 8.0, 2 * 2 * 4 * D1 * n * 8),
             ("tensor product + inverse NTT, 3 x D1", "k_nttl_inv_tile<12, TENSOR> + k_nttl_inv_strided<4>",
-             lambda i: ck(lib.gq_stage_tensor_inv_dev(h, 0, D1, y.data_ptr(), xc.data_ptr(), None)),
+             tensor_inv,
              3 * D1 * (n // 2) * LOGN, 8.0 + 4 * 7.0 * 2 / (3 * LOGN), (4 + 3 + 2 * 3) * D1 * n * 8),
-            ("reconstruct x3 over D1", "k_reconstruct_fast<7>", lambda i: ck(lib.gq_stage_reconstruct_dev(h, D1, L, 3, y.data_ptr(), out3, n, None)),
-             3 * n, D1 * 38.0 + 4 * W, 3 * D1 * n * 8 + 3 * W * n * 8),
+            ("reconstruct x3 over D1", "k_crt_tc<K5> (u8 mma.sync contraction)" if pre1 else "k_reconstruct_fast<7>", reconstruct,
+             3 * n, (tc_mac1 if pre1 else D1 * 38.0 + 4 * W), 3 * D1 * n * 8 + 3 * W * n * 8),
             ("decompose d2 -> D2", "k_decompose28<7, pm>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D2, 1, in1, W, n, x2.data_ptr(), None)),
              D2 * n, 34.0, W * n * 8 + D2 * n * 8),
             ("forward NTT, D2", "k_nttl_fwd_*", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D2, 1, x2.data_ptr(), 0, None)),
              D2 * (n // 2) * LOGN, 8.0, 2 * 2 * D2 * n * 8),
             ("multiply by rlk + inverse NTT, 2 x D2", "k_nttl_inv_tile<12, EVK> + k_nttl_inv_strided<4>",
-             lambda i: ck(lib.gq_stage_mul_evk_inv_dev(h, 0, D2, y2.data_ptr(), x2.data_ptr(), evk._h, None)),
+             evk_inv,
              2 * D2 * (n // 2) * LOGN, 8.0 + 2 * 7.0 * 2 / (2 * LOGN), (3 + 2 + 2 * 2) * D2 * n * 8),
-            ("key-switch epilogue + rescale", "k_ks_epilogue_fast<8, 7> (he_rs fused)", lambda i: ck(lib.gq_stage_ks_epilogue_rs_dev(h, L, y2.data_ptr(), d[0].data_ptr(), d[1].data_ptr(), o[0].data_ptr(), o[1].data_ptr(), n, None)),
-             2 * n, D2 * 42.0 + ctx.dim * 40.0 + 128 + 64, 2 * D2 * n * 8 + 4 * W * n * 8),
+            ("key-switch epilogue + rescale", "k_crt_tc<K6> (u8 mma.sync contraction, he_rs fused)" if pre2 else "k_ks_epilogue_fast<8, 7> (he_rs fused)",
+             ks_epilogue,
+             2 * n, (tc_mac2 if pre2 else D2 * 42.0 + ctx.dim * 40.0 + 128 + 64), 2 * D2 * n * 8 + 4 * W * n * 8),
         ]
         with torch.cuda.stream(ext):
             for st in stages:          # one pass in order so that every stage sees real data
@@ -472,8 +502,14 @@ def run_ours(args):
         for name, kern, fn, units, mulw, nbytes in stages:
             t = timed(fn, reps, 3) / reps
             total += t
-            fi = units * mulw / (t * 1e-3) / mw_peak.value if mw_peak.value else None
             fh = nbytes / (t * 1e-3) / 1e9 / hbm
+            if "k_crt_tc" in kern:       # tensor-core rows: the work is u8 MACs against the measured mma.sync u8 peak
+                ft = units * mulw / (t * 1e-3) / (imma_peak * 1e12) if imma_peak else None
+                rows.append({"stage": name, "kernel": kern, "us": t * 1e3, "units": units, "u8_mac_per_unit": mulw,
+                             "algorithmic_bytes": nbytes, "frac_tensor_u8": ft, "frac_hbm": fh,
+                             "bound": "latency (carry epilogue); nearest roof: " + ("hbm" if fh >= (ft or 0) else "tensor")})
+                continue
+            fi = units * mulw / (t * 1e-3) / mw_peak.value if mw_peak.value else None
             rows.append({"stage": name, "kernel": kern, "us": t * 1e3, "units": units, "mul32_per_unit": mulw,
                          "algorithmic_bytes": nbytes, "frac_int_pipe": fi, "frac_hbm": fh,
                          "bound": "int" if (fi or 0) >= fh else "hbm"})
@@ -481,9 +517,9 @@ def run_ours(args):
             r["share"] = r["us"] / (total * 1e3)
         return {"rows": rows, "sum_us": total * 1e3,
                 "peaks": {"madwide_Gops": mw_peak.value / 1e9, "hbm_GBps": hbm},
-                "note": "the op's own launches (the stage-level entry points call the kernels gq_he_mul_rs_dev launches; inside the op "
-                        "the CRT stages additionally skip their first multiplication because the inverse NTT folds (P/p_d)^-1 into "
-                        "its final scaling); each stage timed alone on one stream (20 launches back to back, L2-warm as inside the op); "
+                "note": "the op's own launches (the stage-level entry points call the kernels gq_he_mul_rs_dev launches, in the "
+                        "pre-scaled forms when gq_stage_prescale_ok: the inverse NTT folds (P/p_d)^-1 into its final scaling and the "
+                        "CRT stages run as u8 tensor-core contractions, gq_crt_tc.cu); each stage timed alone on one stream (20 launches back to back, L2-warm as inside the op); "
                         "frac_int_pipe = 32x32-multiply work / measured IMAD.WIDE peak of this GPU (gq_bench_intpipe), "
                         "frac_hbm = algorithmic bytes / measured HBM copy peak; the NTT rows use 8 multiply-equivalents "
                         "per butterfly (6 wide + 4 low)"}

@@ -29,7 +29,8 @@ class GqP2pXchg(C.Structure):
     """gq_p2p_xchg: one exchange of the sharded pipeline, producer (`send`) or consumer (`wait`) side"""
     _fields_ = [("G", C.c_uint), ("me", C.c_uint), ("slot", C.c_uint), ("D", C.c_uint),
                 ("dst", C.c_void_p), ("off", C.c_void_p), ("flags", C.c_void_p), ("flags_local", C.c_void_p),
-                ("epoch_dev", C.c_void_p), ("err_dev", C.c_void_p), ("ticket_dev", C.c_void_p)]
+                ("epoch_dev", C.c_void_p), ("err_dev", C.c_void_p), ("ticket_dev", C.c_void_p),
+                ("pre", C.c_uint)]
 
 
 class GpqheError(RuntimeError):
@@ -129,6 +130,11 @@ SIGNATURES = {
     "gq_stage_ks_epilogue_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, vp]),
     "gq_stage_ks_epilogue_rs_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, vp]),
     "gq_stage_rescale_dev": (C.c_int, [vp, C.c_uint, vp, vp, C.c_int, C.c_uint, vp]),
+    "gq_stage_prescale_ok": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_int]),
+    "gq_stage_tensor_inv_pre_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp]),
+    "gq_stage_mul_evk_inv_pre_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp]),
+    "gq_stage_reconstruct_pre_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, C.POINTER(vp), C.c_uint, vp]),
+    "gq_stage_ks_epilogue_pre_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, C.c_int, vp]),
     "gq_p2p_alloc": (C.c_int, [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]),
     "gq_p2p_open": (C.c_int, [vp, C.c_char_p, C.POINTER(vp)]),
     "gq_p2p_close": (C.c_int, [vp, vp]),

@@ -406,6 +406,7 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
       std::vector<uint64_t> pp(2 * GQ_MAX_W);
       c->P.store(pp.data(), GQ_MAX_W);
       c->P.shr(1).store(pp.data() + GQ_MAX_W, GQ_MAX_W);
+      c->h_Pinv = pinv;
       if (upload(&c->d_Pinv, pinv.data(), pinv.size()) || upload(&c->d_Pwords, pp.data(), pp.size())) {
         gq_ctx_destroy(c); return 1;
       }
@@ -779,27 +780,89 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
   return 0;
 }
 
-// B-fragment table of the tensor-core CRT for (basis D, W result words), built once and kept by the root context
-static const uint32_t *tc_table(gq_ctx *c, unsigned D, unsigned W) {
-  const bool off = getenv("GPQHE_B200_NO_TC_CRT") != nullptr;      // A/B switch for tests and profiling
-  gq_ctx *root = c->parent ? c->parent : c;
-  if (off || W == 0 || W > 7 || D == 0 || D > root->dimub) return nullptr;
-  const GqHostBasis &hb = root->basis[D - 1];
-  if (!hb.dev.WT || hb.dev.F < 96 || hb.dev.F > 126 || hb.u.size() != D || hb.phat.size() != (size_t)D * hb.dev.WT) return nullptr;
-  const unsigned key = D * 16 + W;
-  auto it = root->tc_tabs.find(key);
-  if (it != root->tc_tabs.end()) return it->second;
-  std::vector<uint64_t> low((size_t)D * W, 0);
-  for (unsigned d = 0; d < D; d++)
-    for (unsigned w = 0; w < W && w < (unsigned)hb.dev.WT; w++) low[(size_t)d * W + w] = hb.phat[(size_t)d * hb.dev.WT + w];
-  std::vector<uint32_t> tab(gq_crt_tc_table_words((int)D, (int)W));
-  gq_crt_tc_table(tab.data(), (int)D, (int)W, low.data(), hb.u.data());
+// r = a * b mod 2^512 (8 words each)
+static void mul_lo8(uint64_t *r, const uint64_t *a, const uint64_t *b) {
+  uint64_t t[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int i = 0; i < 8; i++) {
+    uint64_t cy = 0;
+    for (int j = 0; i + j < 8; j++) {
+      gq_u128 x = (gq_u128)a[i] * b[j] + t[i + j] + cy;
+      t[i + j] = (uint64_t)x; cy = (uint64_t)(x >> 64);
+    }
+  }
+  for (int i = 0; i < 8; i++) r[i] = t[i];
+}
+
+static const uint32_t *tc_upload(gq_ctx *root, unsigned key, int slots, const std::vector<uint64_t> &K,
+                                 const std::vector<uint64_t> &u, const uint64_t *cw) {
+  std::vector<uint32_t> tab(gq_crt_tc_table_words(slots));
+  gq_crt_tc_table(tab.data(), slots, K.data(), u.data(), cw);
   uint32_t *dv = nullptr;
   if (cudaMalloc((void **)&dv, tab.size() * 4) != cudaSuccess) return nullptr;
   // synchronous copy: every stream that will read the table is ordered after this host call
   if (cudaMemcpy(dv, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(dv); return nullptr; }
   root->tc_tabs[key] = dv;
   return dv;
+}
+
+static bool tc_basis_ok(const GqHostBasis &hb, unsigned D) {
+  return hb.dev.WT && hb.dev.F >= 96 && hb.dev.F <= 126 && hb.u.size() == D && hb.phat.size() == (size_t)D * hb.dev.WT;
+}
+
+// B-fragment table of the tensor-core CRT over the basis D (results of at most 8 words), built once and kept by the
+// root context
+static const uint32_t *tc_table(gq_ctx *c, unsigned D, unsigned W) {
+  const bool off = getenv("GPQHE_B200_NO_TC_CRT") != nullptr;      // A/B switch for tests and profiling
+  gq_ctx *root = c->parent ? c->parent : c;
+  if (off || W == 0 || W > 8 || D == 0 || D > root->dimub) return nullptr;
+  const GqHostBasis &hb = root->basis[D - 1];
+  if (!tc_basis_ok(hb, D)) return nullptr;
+  auto it = root->tc_tabs.find(D);
+  if (it != root->tc_tabs.end()) return it->second;
+  const int slots = 4 * (int)((D + 3) / 4);
+  std::vector<uint64_t> K((size_t)slots * 8, 0), u(slots, 0);
+  for (unsigned d = 0; d < D; d++) {
+    for (unsigned w = 0; w < 8 && w < (unsigned)hb.dev.WT; w++) K[(size_t)d * 8 + w] = hb.phat[(size_t)d * hb.dev.WT + w];
+    u[d] = hb.u[d];
+  }
+  uint64_t cw[8];
+  hb.P.store(cw, 8);
+  return tc_upload(root, D, slots, K, u, cw);
+}
+
+// ... of the key-switch epilogue over the basis D2 (y part) and the special basis {p_0..p_(dim-1)} (z part):
+// every constant carries the factor P^-1 mod 2^512 of the exact quotient (gq_crt_tc.cu)
+static const uint32_t *tc_table_ks(gq_ctx *c, unsigned D2, unsigned k) {
+  const bool off = getenv("GPQHE_B200_NO_TC_CRT") != nullptr;
+  gq_ctx *root = c->parent ? c->parent : c;
+  if (off || k == 0 || k > 512 || D2 == 0 || D2 > root->dimub || !root->has_he || root->dim == 0 || root->dim > D2) return nullptr;
+  const GqHostBasis &hb = root->basis[D2 - 1], &hp = root->basis[root->dim - 1];
+  if (!tc_basis_ok(hb, D2) || !tc_basis_ok(hp, root->dim) || root->h_Pinv.size() < 8) return nullptr;
+  const unsigned key = 0x10000u + D2;
+  auto it = root->tc_tabs.find(key);
+  if (it != root->tc_tabs.end()) return it->second;
+  const unsigned dim = root->dim;
+  const int ys = 4 * (int)((D2 + 3) / 4), zs = 4 * (int)((dim + 3) / 4);
+  std::vector<uint64_t> K((size_t)(ys + zs) * 8, 0), u(ys + zs, 0);
+  const uint64_t *pinv = root->h_Pinv.data();
+  uint64_t lo[8];
+  for (unsigned d = 0; d < D2; d++) {              // (PQ / p_d) * P^-1
+    for (unsigned w = 0; w < 8; w++) lo[w] = w < (unsigned)hb.dev.WT ? hb.phat[(size_t)d * hb.dev.WT + w] : 0;
+    mul_lo8(&K[(size_t)d * 8], lo, pinv);
+    u[d] = hb.u[d];
+  }
+  for (unsigned i = 0; i < dim; i++) {             // -(P / p_i) * P^-1
+    for (unsigned w = 0; w < 8; w++) lo[w] = w < (unsigned)hp.dev.WT ? hp.phat[(size_t)i * hp.dev.WT + w] : 0;
+    uint64_t *Kz = &K[(size_t)(ys + i) * 8];
+    mul_lo8(Kz, lo, pinv);
+    uint64_t cy = 1;
+    for (unsigned w = 0; w < 8; w++) { const uint64_t x = ~Kz[w] + cy; cy = (cy && x == 0) ? 1 : 0; Kz[w] = x; }
+    u[ys + i] = hp.u[i];
+  }
+  uint64_t cw[8];
+  hb.P.store(lo, 8);
+  mul_lo8(cw, lo, pinv);                           // PQ * P^-1 = Q
+  return tc_upload(root, key, ys + zs, K, u, cw);
 }
 
 // rs_j > 0: he_rs fused behind the CRT (power-of-two q and Delta; the caller checks with rs_fusable)
@@ -976,7 +1039,8 @@ static int ks_epilogue_dev(gq_ctx *c, unsigned l, unsigned D2, const uint64_t *B
   if (qm.dev.is_pow2) {
     r = gq_launch_ks_epilogue(c->basis[D2 - 1].dev, c->basis[c->dim - 1].dev, c->d_Pinv, c->d_primes,
                               (int)n, B, qm.dev.k, ptrs(add0, add1), (int)W, ptrs(c0, c1), (int)W, 2, st,
-                              c->fast_crt ? c->d_fix : nullptr, rs_j, pre ? c->basis[D2 - 1].ratio : nullptr, wt);
+                              c->fast_crt ? c->d_fix : nullptr, rs_j, pre ? c->basis[D2 - 1].ratio : nullptr, wt,
+                              (pre && c->fast_crt) ? tc_table_ks(c, D2, qm.dev.k) : nullptr);
   } else {
     if (rs_j || pre || wt) GQ_FAIL("fused rescale / pre-scaled residues / flag wait need power-of-two moduli");
     r = gq_launch_ks_epilogue_general(c->basis[D2 - 1].dev, c->d_Pwords, (int)c->P.w.size(),
@@ -1895,6 +1959,55 @@ extern "C" int gq_stage_ks_epilogue_rs_dev(gq_ctx *c, unsigned l, const uint64_t
   return 0;
 }
 
+// ---- the same stages on PRE-SCALED residues: the inverse transforms end with the CRT pre-multiplication of the basis
+// {p_0..p_(D-1)} folded into N^-1 (y_d = a_d (P/p_d)^-1 mod p_d), the CRT stages take such residues and run on the
+// tensor cores where gq_crt_tc.cu applies.  gq_stage_prescale_ok says whether the forms exist for (D, l).
+extern "C" int gq_stage_prescale_ok(gq_ctx *c, unsigned D, unsigned l, int keyswitch) {
+  if (!c || !c->has_he || l > c->L || D == 0 || D > c->dimub) return 0;
+  if (!crt_pre_ok(c, D, c->qmod[l].dev) || !fused_inv_ok(c, 0, D)) return 0;
+  if (keyswitch && (!c->basis[D - 1].ratio || D < c->dim || D != dim_ks(c, l))) return 0;
+  return 1;
+}
+extern "C" int gq_stage_tensor_inv_pre_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned D, uint64_t *y,
+                                           const uint64_t *x, void *stream) {
+  if (!c || !y || !x) GQ_FAIL("bad argument");
+  if (limb0 + nlimbs > D || !fused_inv_ok(c, limb0, nlimbs) || D > c->dimub || !c->basis[D - 1].fin_s)
+    GQ_FAIL("no pre-scaled inverse transform for this limb range / basis (gq_stage_prescale_ok)");
+  return ntt_inv_fused(c, GQ_NTTF_TENSOR, limb0, nlimbs, x, y, nullptr, nullptr, 1, pick(c, stream), D);
+}
+extern "C" int gq_stage_mul_evk_inv_pre_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, unsigned D, uint64_t *y,
+                                            const uint64_t *x, const gq_evk *evk, void *stream) {
+  if (!c || !y || !x || !evk) GQ_FAIL("bad argument");
+  if (limb0 + nlimbs > D || limb0 + nlimbs > c->dimevk || !fused_inv_ok(c, limb0, nlimbs) || D > c->dimub ||
+      !c->basis[D - 1].fin_s)
+    GQ_FAIL("no pre-scaled inverse transform for this limb range / basis (gq_stage_prescale_ok)");
+  const size_t off = (size_t)limb0 * c->n;
+  return ntt_inv_fused(c, GQ_NTTF_EVK, limb0, nlimbs, x, y, evk->p0 + off, evk->p1 + off, 1, pick(c, stream), D);
+}
+extern "C" int gq_stage_reconstruct_pre_dev(gq_ctx *c, unsigned D, unsigned l, unsigned npolys,
+                                            const uint64_t *rhat, uint64_t *const *out, unsigned ncoef,
+                                            void *stream) {
+  if (he_check(c, l)) return 1;
+  if (!rhat || !out || npolys == 0 || npolys > 4) GQ_FAIL("bad argument");
+  if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
+  if (!gq_stage_prescale_ok(c, D, l, 0)) GQ_FAIL("pre-scaled residues are not supported for this basis / level");
+  GqPtrs4 p = ptrs(out[0], npolys > 1 ? out[1] : nullptr, npolys > 2 ? out[2] : nullptr, npolys > 3 ? out[3] : nullptr);
+  return reconstruct_dev(c, D, rhat, c->qmod[l].dev, p, c->W, npolys, pick(c, stream), ncoef, 0, true);
+}
+extern "C" int gq_stage_ks_epilogue_pre_dev(gq_ctx *c, unsigned l, const uint64_t *chat, const uint64_t *add0,
+                                            const uint64_t *add1, uint64_t *c0, uint64_t *c1, unsigned ncoef,
+                                            int rescale, void *stream) {
+  if (he_check(c, l)) return 1;
+  if (rescale && l == 0) GQ_FAIL("cannot go below level 0");
+  if (!chat || !c0 || !c1) GQ_FAIL("null argument");
+  if (ncoef == 0 || ncoef > c->n) GQ_FAIL("coefficient count out of range");
+  if (!gq_stage_prescale_ok(c, dim_ks(c, l), l, 1)) GQ_FAIL("pre-scaled residues are not supported for this level");
+  const unsigned rs_j = rescale ? rs_fusable(c, l) : 0;
+  if (ks_epilogue_dev(c, l, dim_ks(c, l), chat, add0, add1, c0, c1, ncoef, pick(c, stream), rs_j, true)) return 1;
+  if (rescale && !rs_j) return rescale_dev(c, l, c0, c1, true, stream, ncoef);
+  return 0;
+}
+
 extern "C" int gq_stage_rescale_dev(gq_ctx *c, unsigned l, uint64_t *c0, uint64_t *c1, int divide,
                                     unsigned ncoef, void *stream) {
   if (!c) GQ_FAIL("null context");
@@ -1970,7 +2083,9 @@ extern "C" int gq_p2p_tensor_inv_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs,
   if (!fused_inv_ok(c, limb0, nlimbs)) GQ_FAIL("no fused tensor + inverse NTT for these primes");
   GqPeerOut po;
   if (to_peer_out(c, send, c->n / (send ? send->G : 1), &po)) return 1;
-  return ntt_inv_fused(c, GQ_NTTF_TENSOR, limb0, nlimbs, x, y_scratch, nullptr, nullptr, 1, pick(c, stream), 0, &po);
+  if (send && send->pre && (send->D > c->dimub || !c->basis[send->D - 1].fin_s)) GQ_FAIL("no pre-scale tables for this basis");
+  return ntt_inv_fused(c, GQ_NTTF_TENSOR, limb0, nlimbs, x, y_scratch, nullptr, nullptr, 1, pick(c, stream),
+                       (send && send->pre) ? send->D : 0, &po);
 }
 
 extern "C" int gq_p2p_mul_evk_inv_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, uint64_t *y_scratch, const uint64_t *x,
@@ -1980,7 +2095,9 @@ extern "C" int gq_p2p_mul_evk_inv_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs
   GqPeerOut po;
   if (to_peer_out(c, send, c->n / (send ? send->G : 1), &po)) return 1;
   const size_t off = (size_t)limb0 * c->n;
-  return ntt_inv_fused(c, GQ_NTTF_EVK, limb0, nlimbs, x, y_scratch, evk->p0 + off, evk->p1 + off, 1, pick(c, stream), 0, &po);
+  if (send && send->pre && (send->D > c->dimub || !c->basis[send->D - 1].fin_s)) GQ_FAIL("no pre-scale tables for this basis");
+  return ntt_inv_fused(c, GQ_NTTF_EVK, limb0, nlimbs, x, y_scratch, evk->p0 + off, evk->p1 + off, 1, pick(c, stream),
+                       (send && send->pre) ? send->D : 0, &po);
 }
 
 extern "C" int gq_p2p_reconstruct_dev(gq_ctx *c, unsigned D, unsigned l, unsigned npolys, const uint64_t *rhat,
@@ -1991,7 +2108,9 @@ extern "C" int gq_p2p_reconstruct_dev(gq_ctx *c, unsigned D, unsigned l, unsigne
   GqWaitIn w;
   if (to_wait(wait, &w)) return 1;
   GqPtrs4 p = ptrs(out[0], npolys > 1 ? out[1] : nullptr, npolys > 2 ? out[2] : nullptr, npolys > 3 ? out[3] : nullptr);
-  return reconstruct_dev(c, D, rhat, c->qmod[l].dev, p, c->W, npolys, pick(c, stream), ncoef, 0, false, &w);
+  const bool pre = wait && wait->pre;
+  if (pre && !gq_stage_prescale_ok(c, D, l, 0)) GQ_FAIL("pre-scaled residues are not supported for this basis / level");
+  return reconstruct_dev(c, D, rhat, c->qmod[l].dev, p, c->W, npolys, pick(c, stream), ncoef, 0, pre, &w);
 }
 
 extern "C" int gq_p2p_ks_epilogue_dev(gq_ctx *c, unsigned l, const uint64_t *chat, const uint64_t *add0,
@@ -2004,7 +2123,9 @@ extern "C" int gq_p2p_ks_epilogue_dev(gq_ctx *c, unsigned l, const uint64_t *cha
   GqWaitIn w;
   if (to_wait(wait, &w)) return 1;
   const unsigned rs_j = rescale ? rs_fusable(c, l) : 0;
-  if (ks_epilogue_dev(c, l, dim_ks(c, l), chat, add0, add1, c0, c1, ncoef, pick(c, stream), rs_j, false, &w)) return 1;
+  const bool pre = wait && wait->pre;
+  if (pre && !gq_stage_prescale_ok(c, dim_ks(c, l), l, 1)) GQ_FAIL("pre-scaled residues are not supported for this level");
+  if (ks_epilogue_dev(c, l, dim_ks(c, l), chat, add0, add1, c0, c1, ncoef, pick(c, stream), rs_j, pre, &w)) return 1;
   if (rescale && !rs_j) return rescale_dev(c, l, c0, c1, true, stream, ncoef);
   return 0;
 }

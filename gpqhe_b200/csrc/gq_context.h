@@ -68,9 +68,10 @@ struct gq_ctx {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   // staging of the batched host entry points when lanes are in use
   std::vector<cudaEvent_t> ev_batch;
-  // B-fragment tables of the tensor-core CRT (gq_crt_tc.cu), built on first use per (basis D, result words W);
-  // kept by the ROOT context (lanes look them up there)
+  // B-fragment tables of the tensor-core CRT (gq_crt_tc.cu), built on first use per basis D (key D: reconstruct,
+  // key 0x10000 + D: key-switch epilogue over the basis D); kept by the ROOT context (lanes look them up there)
   std::map<unsigned, uint32_t *> tc_tabs;
+  std::vector<uint64_t> h_Pinv;      // host copy of d_Pinv
   unsigned pt_bits = 0;          // gq_ctx_set_plaintext_bits: |m| < 2^pt_bits for the plaintexts of he_gemv (0 = unknown)
   bool lazy_ntt = true;          // internal pipelines use gq_ntt_lazy.cu when every prime allows it
 

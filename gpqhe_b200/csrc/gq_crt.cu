@@ -744,7 +744,7 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
     dim3 g2((n + 255) / 256, npolys), b2(256);
 #define GQ_RF(V) do { if (pre) GQ_LAUNCH((k_reconstruct_fast<V, true>), g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j, w0); \
                       else GQ_LAUNCH((k_reconstruct_fast<V, false>), g2, b2, st, B, primes, n, rhat, q.k, out, Wout, fc, fl, rs_j, w0); } while (0)
-    // tensor-core form (gq_crt_tc.cu) when its table was built for this (basis, W): pre-scaled residues, W <= 7
+    // tensor-core form (gq_crt_tc.cu) when its table was built for this basis: pre-scaled residues, k <= 512
     if (tc_tab && pre && gq_launch_reconstruct_tc(B, tc_tab, n, rhat, q.k, out, Wout, npolys, st, fix, rs_j, wt) == 1) {
     } else
     if (W <= 1) GQ_RF(1); else if (W <= 2) GQ_RF(2); else if (W <= 3) GQ_RF(3); else if (W <= 4) GQ_RF(4);
@@ -791,7 +791,8 @@ static int ks_dispatch_wp(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
 int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
-                          cudaStream_t st, int *fix, unsigned rs_j, const ulonglong2 *ratio, const GqWaitIn *wt) {
+                          cudaStream_t st, int *fix, unsigned rs_j, const ulonglong2 *ratio, const GqWaitIn *wt,
+                          const uint32_t *tc_tab) {
   if (rs_j > k) return -1;
   GqWaitIn w0 = GqWaitIn();
   if (wt) w0 = *wt;
@@ -801,6 +802,10 @@ int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint6
   if (fix && B.F && k >= 1 && BP.WT <= B.WT) {
     fc = fix; fl = fix + 4;
     dim3 block(128);
+    // tensor-core form (gq_crt_tc.cu) when its table was built for this pair of bases: pre-scaled residues, k <= 512
+    if (tc_tab && ratio &&
+        gq_launch_ks_epilogue_tc(B, BP, tc_tab, primes, ratio, n, chat, k, add, Wadd, out, Wout, npolys, st, fix, rs_j, wt) == 1) {
+    } else
     switch (BP.WT) {
 #define GQ_KFL(WPV, WQV) do { if (ratio) GQ_LAUNCH((k_ks_epilogue_fast<WPV, WQV, true>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j, ratio, w0); \
                               else GQ_LAUNCH((k_ks_epilogue_fast<WPV, WQV, false>), grid, block, st, B, BP, Pinv, primes, n, chat, k, add, Wadd, out, Wout, fc, fl, rs_j, ratio, w0); } while (0)

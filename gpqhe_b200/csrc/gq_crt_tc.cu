@@ -1,26 +1,36 @@
-// gq_crt_tc.cu - K5 (poly_rns2mpi, src/poly.c:109-120 over rns_reconstruct, src/rns.c:60-75) as a dense integer
-// contraction on the tensor cores.
+// gq_crt_tc.cu - K5 (poly_rns2mpi, src/poly.c:109-120 over rns_reconstruct, src/rns.c:60-75) and K6 (the key-switch
+// epilogue of he_mul / he_rot / he_conj: round(T / P) + ct, src/he-mult.c:57-64, src/he-kem.c:24-45) as dense integer
+// contractions on the tensor cores.
 //
-// The fast CRT of gq_crt.cu computes, per coefficient, T = sum_d y_d * (P/p_d) - M * P modulo 2^(64W) with
-// M = floor(sum_d y_d * floor(2^F/p_d) / 2^F + ...) from a fixed-point estimate: D x W 64-bit multiply-accumulates with
-// carry chains, about 2 100 integer instructions per coefficient, latency-bound (ncu: 54 % issue, 46 % warps active).
-// Both sums are contractions of the residue BYTES with constant byte tables:
-//     C[i][j] = sum_{d, a} byte_a(y_d[i]) * byte_{j-a}(K_d),     K_d = (P/p_d) mod 2^(64W)   (j < 8W)
-//                                                                 K_d = floor(2^F/p_d)         (16 more columns)
-// i.e. (coefficients x 8D) * (8D x (8W + 16)) in u8 with exact int32 accumulation (at most 8D products of 255^2:
-// below 2^24), which mma.sync.m16n8k32 does at 568 T MAC/s on this part (profiles/probe/gqp_imma.cu).  What is left
-// per coefficient is the carry propagation of 8W + 16 byte columns - about 200 instructions - and the tail of the
-// integer kernel (subtract M * P, optional fused he_rs, smod 2^k, store).  Same integers, same fix-list rule, same
-// stores as k_reconstruct_fast: bit-identical (tests: every he_mul / he_mulpt / poly_mul parity case runs through it).
+// The integer kernels of gq_crt.cu compute, per coefficient, T = sum_d y_d * (P/p_d) - M * P modulo 2^(64W) with the
+// overflow count M from a fixed-point estimate: D x W 64-bit multiply-accumulates with carry chains (about 2 000
+// instructions per coefficient; the key-switch epilogue, which adds T mod P over the special limbs and a W x W
+// product with P^-1, about 6 000), latency-bound.  Every one of those sums is LINEAR in the bytes of the residues:
+//     C[i][j] = sum_{d, a} byte_a(y_d[i]) * byte_{j-a}(K_d)
+// is a (coefficients x 8D) * (8D x 64) product in u8 with exact int32 accumulation (at most 8D products of 255^2),
+// which mma.sync.m16n8k32 does at 568 T MAC/s on this part (profiles/probe/gqp_imma.cu), with
+//     K_d = (P/p_d) mod 2^512                                   for K5,
+//     K_d = (PQ/p_d) * P^-1 mod 2^512                           for K6 (the exact quotient (T - r) / P is
+//     K'_i = -(P/p_i) * P^-1 mod 2^512 on z_i                   (T - r) * P^-1 modulo a power of two, and both
+//                                                               T = sum y_d (PQ/p_d) - M PQ and r = T mod P =
+//                                                               sum z_i (P/p_i) - M' P are sums of this kind),
+// and 16 more columns per sum for the fixed-point estimates floor(2^F/p_d) of M and M'.  z_i = y_i * ratio_i mod p_i
+// (one Shoup product per special limb) are the residues pre-scaled for the basis of P (GqHostBasis::ratio).  What is
+// left per coefficient is the carry propagation of the byte columns, -M * C (C = P for K5, PQ * P^-1 = Q for K6; M
+// is at most D + 1, so this is a small multiple), + M' + [r > P/2] (decided from the fraction of the M' estimate), the
+// ciphertext addend, the fused he_rs, smod 2^k and the store.  The same integers, the same fix-list rule (estimates
+// too close to a decision boundary go to the exact kernel in list mode), the same stores as the integer kernels:
+// bit-identical (tests: every he_mul / he_rot / poly_mul parity case runs through it, and against the integer kernels
+// with GPQHE_B200_NO_TC_CRT).
 //
 // Fragment layouts (PTX ISA, mma.m16n8k32 .u8; g = lane / 4, t = lane % 4): A: a0..a3 = rows (g, g+8, g, g+8) x
 // k-bytes (4t.., 4t.., 16+4t.., 16+4t..); B: b0, b1 = k-bytes (4t.., 16+4t..) x column g; C: c0, c1 = row g, columns
 // 2t, 2t+1; c2, c3 = row g+8.  The K and N orders are ours (the table is a constant):
 //   * k-slots (4t..4t+3, 16+4t..16+4t+3) of chunk c carry the 8 bytes of the residue of LIMB 4c + t: an A fragment is
 //     one 64-bit load per row, 8 consecutive coefficients per quad column (one 64-byte segment);
-//   * column 2t + e of n-tile v < W is output byte 2W*t + 2v + e: quad lane t ends up with 2W CONSECUTIVE byte columns
-//     (its slice of T is one 128-bit partial sum, W <= 7); n-tiles W, W+1 carry estimate bytes 4t + 2(v-W) + e.
-// The four partial sums of a row meet through 24 64-bit shuffles; lanes t = 0, 1 finish rows g, g+8.
+//   * column 2t + e of n-tile v < 8 is output byte 16t + 2v + e: quad lane t ends up with 16 CONSECUTIVE byte columns =
+//     words 2t, 2t+1 of an 8-word result (W <= 8: k <= 512); n-tiles 8, 9 carry estimate bytes 4t + 2(v-8) + e.
+// Carries between the four lanes of a quad are small signed numbers (below 2^31) and ripple through three shuffles.
 #include "gq_bigint.h"
 #include "gq_kernels.h"
 #include "gq_p2p.h"
@@ -42,25 +52,6 @@ GQ_DEV uint64_t shfl64(uint64_t v, int src) {
   return ((uint64_t)hi << 32) | lo;
 }
 
-// T[0..W) += (hi:lo) << off (mod 2^(64W)); off is a compile-time constant after unrolling
-template <int W>
-GQ_DEV void add_shifted(uint64_t *T, uint64_t lo, uint64_t hi, int off) {
-  const int w0 = off >> 6, sb = off & 63;
-  const uint64_t p0 = lo << sb;
-  const uint64_t p1 = sb ? ((lo >> (64 - sb)) | (hi << sb)) : hi;
-  const uint64_t p2 = sb ? (hi >> (64 - sb)) : 0;
-  uint64_t carry = 0;
-#pragma unroll
-  for (int w = 0; w < W; w++) {
-    const uint64_t add = (w == w0) ? p0 : (w == w0 + 1) ? p1 : (w == w0 + 2) ? p2 : 0;
-    if (w >= w0) {
-      const uint64_t s = T[w] + add, c1 = s < add, s2 = s + carry, c2 = s2 < carry;
-      T[w] = s2;
-      carry = c1 | c2;
-    }
-  }
-}
-
 GQ_DEV void fix_push_tc(int *fix_count, int *fix_list, int entry) {
 #ifdef GQ_EMULATE
   fix_list[(*fix_count)++] = entry;
@@ -73,115 +64,258 @@ GQ_DEV void fix_push_tc(int *fix_count, int *fix_list, int entry) {
 
 GQ_DEV uint64_t *ptr4(const GqPtrs4 &P, int b) { return b == 0 ? P.p[0] : b == 1 ? P.p[1] : b == 2 ? P.p[2] : P.p[3]; }
 
-// tab: B fragments [chunk][n-tile][lane][2], built by gq_crt_tc_table; the residues rhat are PRE-SCALED
-// (y_d = a_d (P/p_d)^-1 mod p_d, folded into the inverse NTT: GqNttTables::fin_s)
-template <int W>
-__global__ void __launch_bounds__(128)
-k_reconstruct_tc(GqCrtBasis B, const uint32_t *__restrict__ tab, int nchunks, int n, const uint64_t *__restrict__ rhat,
-                 unsigned k, GqPtrs4 out, int Wout, int *fix_count, int *fix_list, unsigned rs_j, GqWaitIn wt) {
-  constexpr int NT = W + 2;
-  GQ_DYN_SMEM(uint32_t, sB);
-  __shared__ uint64_t sP[W];
-  __shared__ uint64_t sHc[2];
-  for (int j = threadIdx.x; j < nchunks * NT * 64; j += blockDim.x) sB[j] = tab[j];
-  for (int j = threadIdx.x; j < W; j += blockDim.x) sP[j] = (j < B.WT) ? B.P[j] : 0;
-  if (threadIdx.x < 2) sHc[threadIdx.x] = B.hc[threadIdx.x];
-  gq_peer_wait(wt);
+// three-word accumulator (v2 in two's complement): v += b, v -= b
+GQ_DEV void add3(uint64_t &v0, uint64_t &v1, uint64_t &v2, uint64_t b0, uint64_t b1, uint64_t b2) {
+#if defined(__CUDA_ARCH__)
+  asm("add.cc.u64 %0, %0, %3;\n\taddc.cc.u64 %1, %1, %4;\n\taddc.u64 %2, %2, %5;"
+      : "+l"(v0), "+l"(v1), "+l"(v2) : "l"(b0), "l"(b1), "l"(b2));
+#else
+  const uint64_t s0 = v0 + b0, c0 = s0 < b0;
+  const uint64_t s1 = v1 + b1, c1 = s1 < b1, s1b = s1 + c0, c1b = s1b < c0;
+  v0 = s0; v1 = s1b; v2 = v2 + b2 + c1 + c1b;
+#endif
+}
+GQ_DEV void sub3(uint64_t &v0, uint64_t &v1, uint64_t &v2, uint64_t b0, uint64_t b1, uint64_t b2) {
+#if defined(__CUDA_ARCH__)
+  asm("sub.cc.u64 %0, %0, %3;\n\tsubc.cc.u64 %1, %1, %4;\n\tsubc.u64 %2, %2, %5;"
+      : "+l"(v0), "+l"(v1), "+l"(v2) : "l"(b0), "l"(b1), "l"(b2));
+#else
+  const uint64_t d0 = v0 - b0, w0 = v0 < b0;
+  const uint64_t d1 = v1 - b1, w1 = v1 < b1, d1b = d1 - w0, w1b = d1 < w0;
+  v0 = d0; v1 = d1b; v2 = v2 - b2 - (w1 | w1b);
+#endif
+}
+
+// four byte columns (each below 2^24) -> c0 + c1 2^8 + c2 2^16 + c3 2^24 (below 2^49): three 32 x 32 + 64 multiply-adds
+GQ_DEV uint64_t pack4(int c0, int c1, int c2, int c3) {
+  uint64_t r = (uint64_t)(uint32_t)c1 * 0x100u + (uint32_t)c0;
+  r = (uint64_t)(uint32_t)c2 * 0x10000u + r;
+  return (uint64_t)(uint32_t)c3 * 0x1000000u + r;
+}
+// P0 + P1 2^32 + P2 2^64 + P3 2^96 (each P below 2^49) as three words
+GQ_DEV void sum4(uint64_t P0, uint64_t P1, uint64_t P2, uint64_t P3, uint64_t &w0, uint64_t &w1, uint64_t &w2) {
+#if defined(__CUDA_ARCH__)
+  uint32_t s1, s2, s3, s4;
+  asm("add.cc.u32 %0, %4, %5;\n\taddc.cc.u32 %1, %6, %7;\n\taddc.cc.u32 %2, %8, %9;\n\taddc.u32 %3, %10, 0;"
+      : "=r"(s1), "=r"(s2), "=r"(s3), "=r"(s4)
+      : "r"((uint32_t)(P0 >> 32)), "r"((uint32_t)P1), "r"((uint32_t)(P1 >> 32)), "r"((uint32_t)P2),
+        "r"((uint32_t)(P2 >> 32)), "r"((uint32_t)P3), "r"((uint32_t)(P3 >> 32)));
+  w0 = ((uint64_t)s1 << 32) | (uint32_t)P0;
+  w1 = ((uint64_t)s3 << 32) | s2;
+  w2 = s4;
+#else
+  const uint64_t a = P1 << 32;
+  w0 = P0 + a;
+  const uint64_t c0 = w0 < a;
+  const uint64_t bsum = (P1 >> 32) + P2 + c0;              // below 2^50: no overflow
+  const uint64_t d = P3 << 32;
+  w1 = bsum + d;
+  w2 = (P3 >> 32) + (w1 < d ? 1u : 0u);
+#endif
+}
+// m * (C1 : C0) for a 32-bit m: five 32-bit limbs through four chained 32 x 32 + 32 multiply-adds
+GQ_DEV void mul_small(uint32_t m, uint64_t C0, uint64_t C1, uint64_t &b0, uint64_t &b1, uint64_t &b2) {
+  const uint64_t t0 = (uint64_t)m * (uint32_t)C0;
+  const uint64_t t1 = (uint64_t)m * (uint32_t)(C0 >> 32) + (t0 >> 32);
+  const uint64_t t2 = (uint64_t)m * (uint32_t)C1 + (t1 >> 32);
+  const uint64_t t3 = (uint64_t)m * (uint32_t)(C1 >> 32) + (t2 >> 32);
+  b0 = (t1 << 32) | (uint32_t)t0;
+  b1 = (t3 << 32) | (uint32_t)t2;
+  b2 = t3 >> 32;
+}
+
+struct TcArgs {
+  const unsigned long long *frag;   // B fragments [chunk][10 n-tiles][32 lanes], 64 bits per lane
+  const uint64_t *cw;               // [8] multiplier of the overflow count (P for K5, Q = PQ * P^-1 for K6), low 512 bits
+  const uint64_t *hc;               // [2] centring constant of the estimate of M (GqCrtBasis::hc)
+  const GqPrime *primes;            // K6: the special limbs
+  const ulonglong2 *ratio;          // K6: y_i -> z_i (GqHostBasis::ratio)
+  int D, ych, DP, zch;              // limbs / chunks of the y part; limbs / chunks of the z part (K6)
+  int fs, fsP;                      // fractional bits of the estimates beyond 64 (GqCrtBasis::F - 64)
+};
+
+// one chunk (four limbs, one per quad lane) of a 16-coefficient step: ten MMAs, and for a special limb of K6 ten more
+// on the residue re-scaled for the basis of P
+template <bool KS>
+GQ_DEV void tc_chunk(const TcArgs &a, const unsigned long long *sfrag, int c, int lane, int t, uint64_t v0, uint64_t v1,
+                     int (&acc)[8][4], int (&eM)[2][4], int (&eP)[2][4]) {
+  constexpr int NT = 10;
+  if (c >= a.ych) return;
+  const uint32_t A[4] = {(uint32_t)v0, (uint32_t)v1, (uint32_t)(v0 >> 32), (uint32_t)(v1 >> 32)};
+  const unsigned long long *tb = sfrag + (size_t)c * NT * 32 + lane;
+#pragma unroll
+  for (int v = 0; v < NT; v++) {
+    const unsigned long long bb = tb[v * 32];         // 8 bytes per lane, consecutive lanes: conflict-free
+    if (v < 8) mma_u8(acc[v], A, (uint32_t)bb, (uint32_t)(bb >> 32));
+    else mma_u8(eM[v - 8], A, (uint32_t)bb, (uint32_t)(bb >> 32));
+  }
+  if (KS && c < a.zch) {
+    const int d = 4 * c + t;
+    uint64_t z0 = 0, z1 = 0;
+    if (d < a.DP) {
+      const ulonglong2 rt = a.ratio[d];
+      const uint64_t p = a.primes[d].p;
+      z0 = v0 * rt.x - gq_mulhi(v0, rt.y) * p;
+      if (z0 >= p) z0 -= p;
+      z1 = v1 * rt.x - gq_mulhi(v1, rt.y) * p;
+      if (z1 >= p) z1 -= p;
+    }
+    const uint32_t Az[4] = {(uint32_t)z0, (uint32_t)z1, (uint32_t)(z0 >> 32), (uint32_t)(z1 >> 32)};
+    const unsigned long long *tz = sfrag + (size_t)(a.ych + c) * NT * 32 + lane;
+#pragma unroll
+    for (int v = 0; v < NT; v++) {
+      const unsigned long long bb = tz[v * 32];
+      if (v < 8) mma_u8(acc[v], Az, (uint32_t)bb, (uint32_t)(bb >> 32));
+      else mma_u8(eP[v - 8], Az, (uint32_t)bb, (uint32_t)(bb >> 32));
+    }
+  }
+}
+
+// KS = false: K5, out = smod(round-shift(T)); KS = true: K6, out = smod(round-shift(round(T / P) + add)).
+// The residues rhat are PRE-SCALED for the basis (y_d = a_d (P/p_d)^-1 mod p_d, canonical; GqNttTables::fin_s).
+// Quad lane t owns words 2t, 2t+1 of an 8-word integer (only the first Wout are stored).
+// RCH: chunks whose residues are held in registers and fetched one step ahead (later chunks, if any, are loaded in
+// place).  Persistent blocks: the fragment table is staged in shared memory once, each warp walks 16-coefficient steps.
+template <bool KS, int RCH>
+__global__ void __launch_bounds__(128, 4)
+k_crt_tc(TcArgs a, int n, const uint64_t *__restrict__ rhat, unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout,
+         int *fix_count, int *fix_list, unsigned rs_j, GqWaitIn wt) {
+  constexpr int NT = 10;
+  GQ_DYN_SMEM(unsigned long long, sfrag);
+  {                                                   // 2 560 bytes per chunk: 160 16-byte pieces, loads batched by 5
+    const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(a.frag);
+    ulonglong2 *dst2 = reinterpret_cast<ulonglong2 *>(sfrag);
+    const int pieces = (a.ych + a.zch) * NT * 16;
+    for (int j0 = threadIdx.x; j0 < pieces; j0 += 5 * 128) {
+      ulonglong2 tmp[5];
+#pragma unroll
+      for (int u = 0; u < 5; u++) if (j0 + u * 128 < pieces) tmp[u] = src[j0 + u * 128];
+#pragma unroll
+      for (int u = 0; u < 5; u++) if (j0 + u * 128 < pieces) dst2[j0 + u * 128] = tmp[u];
+    }
+  }
+  gq_peer_wait(wt);                                   // (ends with the block barrier that also publishes sfrag)
   __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
-  const int b = blockIdx.y, D = B.D, fs = B.F - 64;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3, qb = lane & ~3;
+  const int b = blockIdx.y, D = a.D;
   const uint64_t *rh = rhat + (size_t)b * D * n;
   uint64_t *dst = ptr4(out, b);
-  for (int i0 = (blockIdx.x * 4 + warp) * 16; i0 < n; i0 += gridDim.x * 64) {
-    int acc[NT][4];
+  const uint64_t *ap = KS ? ptr4(add, b) : nullptr;
+  const uint64_t C0 = a.cw[2 * t], C1 = a.cw[2 * t + 1];
+  const uint64_t hc0 = a.hc[0], hc1 = a.hc[1];
+  const unsigned kk = k - rs_j;                       // the result is reduced smod 2^kk
+  const unsigned sw = (kk - 1) >> 6, sb = (kk - 1) & 63;
+  const uint64_t keep = (sb == 63) ? ~(uint64_t)0 : ((((uint64_t)1) << (sb + 1)) - 1);
+  const uint64_t R = rs_j ? (((uint64_t)1) << (rs_j - 1)) - 1 : 0;      // he_rs: floor((x + 2^(j-1) - 1) / 2^j) rounds
+                                                                         // to nearest, ties down (mw_rdiv_pow2)
+  const unsigned ia = 2 * t, ib = 2 * t + 1;
+  const int stride = gridDim.x * 64;
+  uint64_t Rs[RCH][2];
+  {
+    const int i0 = (blockIdx.x * 4 + warp) * 16;
 #pragma unroll
-    for (int v = 0; v < NT; v++)
+    for (int u = 0; u < RCH; u++) {
+      const int d = 4 * u + t;
+      Rs[u][0] = (d < D && i0 + g < n) ? rh[(size_t)d * n + i0 + g] : 0;
+      Rs[u][1] = (d < D && i0 + g + 8 < n) ? rh[(size_t)d * n + i0 + g + 8] : 0;
+    }
+  }
+  for (int i0 = (blockIdx.x * 4 + warp) * 16; i0 < n; i0 += stride) {
+    int acc[8][4], eM[2][4], eP[2][4];
+#pragma unroll
+    for (int v = 0; v < 8; v++)
 #pragma unroll
       for (int e = 0; e < 4; e++) acc[v][e] = 0;
+#pragma unroll
+    for (int v = 0; v < 2; v++)
+#pragma unroll
+      for (int e = 0; e < 4; e++) eM[v][e] = eP[v][e] = 0;
     const bool r0 = i0 + g < n, r1 = i0 + g + 8 < n;
-    for (int c = 0; c < nchunks; c++) {
+    uint64_t ad[2][2] = {{0, 0}, {0, 0}};
+    if (KS && ap) {                                   // the ciphertext addend: my two words of rows g, g+8
+      if (r0 && (int)ia < Wadd) ad[0][0] = ap[(size_t)ia * n + i0 + g];
+      if (r0 && (int)ib < Wadd) ad[0][1] = ap[(size_t)ib * n + i0 + g];
+      if (r1 && (int)ia < Wadd) ad[1][0] = ap[(size_t)ia * n + i0 + g + 8];
+      if (r1 && (int)ib < Wadd) ad[1][1] = ap[(size_t)ib * n + i0 + g + 8];
+    }
+#pragma unroll
+    for (int u = 0; u < RCH; u++) tc_chunk<KS>(a, sfrag, u, lane, t, Rs[u][0], Rs[u][1], acc, eM, eP);
+    for (int c = RCH; c < a.ych; c++) {               // bases wider than the register window
       const int d = 4 * c + t;
       const uint64_t v0 = (d < D && r0) ? rh[(size_t)d * n + i0 + g] : 0;
       const uint64_t v1 = (d < D && r1) ? rh[(size_t)d * n + i0 + g + 8] : 0;
-      const uint32_t A[4] = {(uint32_t)v0, (uint32_t)v1, (uint32_t)(v0 >> 32), (uint32_t)(v1 >> 32)};
+      tc_chunk<KS>(a, sfrag, c, lane, t, v0, v1, acc, eM, eP);
+    }
+    {                                                 // the next step's residues travel while this step's carries resolve
+      const int j0 = i0 + stride;
 #pragma unroll
-      for (int v = 0; v < NT; v++) {
-        const uint64_t bb = *reinterpret_cast<const uint64_t *>(&sB[((c * NT + v) * 32 + lane) * 2]);
-        mma_u8(acc[v], A, (uint32_t)bb, (uint32_t)(bb >> 32));
+      for (int u = 0; u < RCH; u++) {
+        const int d = 4 * u + t;
+        Rs[u][0] = (d < D && j0 + g < n) ? rh[(size_t)d * n + j0 + g] : 0;
+        Rs[u][1] = (d < D && j0 + g + 8 < n) ? rh[(size_t)d * n + j0 + g + 8] : 0;
       }
     }
-    // my 2W byte columns of T and my 4 estimate bytes -> 128-bit / 64-bit partial sums, for both of my rows
-    uint64_t Sl[2], Sh[2], E[2];
 #pragma unroll
     for (int row = 0; row < 2; row++) {
-      uint64_t lo = 0, hi = 0;
+      const int i = i0 + g + 8 * row, e0 = 2 * row, e1 = 2 * row + 1;
+      uint64_t v0, v1, v2;
+      sum4(pack4(acc[0][e0], acc[0][e1], acc[1][e0], acc[1][e1]), pack4(acc[2][e0], acc[2][e1], acc[3][e0], acc[3][e1]),
+           pack4(acc[4][e0], acc[4][e1], acc[5][e0], acc[5][e1]), pack4(acc[6][e0], acc[6][e1], acc[7][e0], acc[7][e1]),
+           v0, v1, v2);
+      // fixed-point estimate of the overflow count: every lane gathers the four 4-byte slices
+      const uint64_t Em = pack4(eM[0][e0], eM[0][e1], eM[1][e0], eM[1][e1]);
+      uint64_t s0, s1, s2;
+      sum4(shfl64(Em, qb), shfl64(Em, qb + 1), shfl64(Em, qb + 2), shfl64(Em, qb + 3), s0, s1, s2);
+      add3(s0, s1, s2, hc0, hc1, 0);
+      const uint64_t frac = (s0 >> a.fs) | (s1 << (64 - a.fs));
+      bool undecided = frac >= ~(uint64_t)0 - 1023;                  // the same rule as crt_low (gq_crt.cu)
+      const uint32_t M = (uint32_t)((s1 >> a.fs) | (s2 << (64 - a.fs)));   // at most D + 1
+      uint64_t b0, b1, b2;
+      mul_small(M, C0, C1, b0, b1, b2);
+      sub3(v0, v1, v2, b0, b1, b2);
+      uint64_t lane0 = R;
+      if (KS) {
+        const uint64_t Ep = pack4(eP[0][e0], eP[0][e1], eP[1][e0], eP[1][e1]);
+        uint64_t p0, p1, p2;
+        sum4(shfl64(Ep, qb), shfl64(Ep, qb + 1), shfl64(Ep, qb + 2), shfl64(Ep, qb + 3), p0, p1, p2);
+        const uint64_t fracP = (p0 >> a.fsP) | (p1 << (64 - a.fsP));        // (r / P) 2^64, from below, error < 1024
+        const uint32_t MP = (uint32_t)((p1 >> a.fsP) | (p2 << (64 - a.fsP)));
+        const uint64_t half = ((uint64_t)1) << 63;
+        // r = sum z_i (P/p_i) - M' P needs floor() decided; [r > P/2] needs the fraction clear of 1/2 (P is odd:
+        // r / P is never 1/2, and the estimate is a lower bound, so fracP >= 1/2 decides "above")
+        undecided = undecided || fracP >= ~(uint64_t)0 - 1023 || (fracP < half && fracP >= half - 1024);
+        lane0 += (uint64_t)MP + (fracP >= half ? 1u : 0u);           // -r contributes +M' (P * P^-1 = 1); round up
+        add3(v0, v1, v2, ad[row][0], ad[row][1], 0);
+      }
+      add3(v0, v1, v2, t == 0 ? lane0 : 0, 0, 0);
+      // ripple the small signed carries across the quad: lane r takes lane r-1's third word
 #pragma unroll
-      for (int m = 0; m < 2 * W; m++) {
-        const uint64_t cv = (uint32_t)acc[m >> 1][2 * row + (m & 1)];      // < 2^24
-        const int sh = 8 * m;
-        if (sh < 64) {
-          const uint64_t add = cv << sh;
-          lo += add;
-          hi += (lo < add ? 1u : 0u) + ((sh > 40) ? (cv >> (64 - sh)) : 0);
-        } else {
-          hi += cv << (sh - 64);
+      for (int r = 1; r < 4; r++) {
+        const int cin = __shfl_sync(0xffffffffu, (int)(uint32_t)v2, qb + r - 1);
+        if (t == r) {
+          const uint64_t ext = (uint64_t)((int64_t)cin >> 63);
+          add3(v0, v1, v2, (uint64_t)(int64_t)cin, ext, ext);
         }
       }
-      Sl[row] = lo; Sh[row] = hi;
-      uint64_t e = 0;
-#pragma unroll
-      for (int m = 0; m < 4; m++) e += (uint64_t)(uint32_t)acc[W + (m >> 1)][2 * row + (m & 1)] << (8 * m);   // < 2^49
-      E[row] = e;
-    }
-    // quad lanes 0 and 1 collect the four partial sums of rows g and g+8
-    const int qb = lane & ~3, mine = t & 1;
-    uint64_t T[W];
-#pragma unroll
-    for (int w = 0; w < W; w++) T[w] = 0;
-    uint64_t e0 = sHc[0], e1 = sHc[1], e2 = 0;
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-      const uint64_t l0 = shfl64(Sl[0], qb + q), l1 = shfl64(Sl[1], qb + q);
-      const uint64_t h0 = shfl64(Sh[0], qb + q), h1 = shfl64(Sh[1], qb + q);
-      const uint64_t x0 = shfl64(E[0], qb + q), x1 = shfl64(E[1], qb + q);
-      add_shifted<W>(T, mine ? l1 : l0, mine ? h1 : h0, 16 * W * q);
-      // estimate += E_q << 32q  (192-bit accumulator e2:e1:e0)
-      const uint64_t x = mine ? x1 : x0;
-      const int off = 32 * q;
-      const uint64_t a0 = (off < 64) ? (x << off) : 0;
-      const uint64_t a1 = (off == 0) ? 0 : (off < 64) ? (x >> (64 - off)) : (x << (off - 64));
-      const uint64_t a2 = (off > 64) ? (x >> (128 - off)) : 0;
-      const uint64_t s0 = e0 + a0, c0 = s0 < a0;
-      e0 = s0;
-      const uint64_t s1 = e1 + a1, c1 = s1 < a1, s1b = s1 + c0, c1b = s1b < c0;
-      e1 = s1b;
-      e2 += a2 + c1 + c1b;
-    }
-    const int i = i0 + g + 8 * mine;
-    if (t < 2 && i < n) {
-      // est = M * 2^F + fraction, F = 64 + fs (the same decision rule as crt_low, gq_crt.cu)
-      const uint64_t frac = (e0 >> fs) | (e1 << (64 - fs));
-      if (frac >= ~(uint64_t)0 - 1023) {
-        fix_push_tc(fix_count, fix_list, b * n + i);
-      } else {
-        const uint64_t M = (e1 >> fs) | (e2 << (64 - fs));
-        uint64_t carry = 0, borrow = 0;
-#pragma unroll
-        for (int w = 0; w < W; w++) {          // T -= M * P (low words)
-          const gq_u128 pr = (gq_u128)M * sP[w] + carry;
-          const uint64_t lo = (uint64_t)pr;
-          carry = (uint64_t)(pr >> 64);
-          const uint64_t a = T[w], dd = a - lo, b1 = a < lo, d2 = dd - borrow, b2 = dd < borrow;
-          T[w] = d2;
-          borrow = b1 | b2;
+      if (rs_j) {                // floor shift by j < 64: my upper word needs the next lane's lower word
+        const uint64_t nxt = shfl64(v0, qb + ((t + 1) & 3));
+        const uint64_t top = (t == 3) ? (uint64_t)((int64_t)v1 >> 63) : nxt;
+        v0 = (v0 >> rs_j) | (v1 << (64 - rs_j));
+        v1 = (v1 >> rs_j) | (top << (64 - rs_j));
+      }
+      // smod 2^kk: sign-extend from bit kk-1 (word sw, owned by quad lane sw / 2)
+      const uint64_t sword = (sw & 1) ? v1 : v0;
+      const uint32_t sbit = __shfl_sync(0xffffffffu, (uint32_t)((sword >> sb) & 1u), qb + (int)(sw >> 1));
+      const uint64_t fill = 0 - (uint64_t)sbit;
+      const uint64_t o0 = (ia < sw) ? v0 : (ia == sw) ? ((v0 & keep) | (fill & ~keep)) : fill;
+      const uint64_t o1 = (ib < sw) ? v1 : (ib == sw) ? ((v1 & keep) | (fill & ~keep)) : fill;
+      if (i < n) {
+        if (undecided) {
+          if (t == 0) fix_push_tc(fix_count, fix_list, b * n + i);
+        } else {
+          if ((int)ia < Wout) dst[(size_t)ia * n + i] = o0;
+          if ((int)ib < Wout) dst[(size_t)ib * n + i] = o1;
         }
-        if (rs_j) mw_rdiv_pow2<W>(T, rs_j);    // he_rs fused (see reconstruct_one, gq_crt.cu)
-        mw_smod_pow2<W>(T, k - rs_j);
-        const uint64_t fill = (T[W - 1] >> 63) ? ~(uint64_t)0 : 0;
-#pragma unroll
-        for (int w = 0; w < W; w++)
-          if (w < Wout) dst[(size_t)w * n + i] = T[w];
-        for (int w = W; w < Wout; w++) dst[(size_t)w * n + i] = fill;
       }
     }
   }
@@ -189,71 +323,103 @@ k_reconstruct_tc(GqCrtBasis B, const uint32_t *__restrict__ tab, int nchunks, in
 
 }  // namespace
 
-// Words of the B-fragment table for a basis of D limbs and W result words.
-size_t gq_crt_tc_table_words(int D, int W) { return (size_t)((D + 3) / 4) * (W + 2) * 64; }
+// Words (32-bit) of the table for `slots` limb slots (a multiple of 4): fragments, then the 8 words of the multiplier.
+size_t gq_crt_tc_table_words(int slots) { return (size_t)(slots / 4) * 10 * 64 + 16; }
 
-// Host side: the B fragments.  phat_low[d*W + w]: low W words of P/p_d; u[d] = floor(2^F / p_d) (one word).
-void gq_crt_tc_table(uint32_t *tab, int D, int W, const uint64_t *phat_low, const uint64_t *u) {
-  const int NT = W + 2, nchunks = (D + 3) / 4;
+// Host side: the B fragments.  K[s*8 + w]: the 8 words of the constant of slot s (zero for padding slots);
+// u[s] = the estimate constant floor(2^F / p) of slot s (one word); cw[8]: the multiplier of the overflow count.
+void gq_crt_tc_table(uint32_t *tab, int slots, const uint64_t *K, const uint64_t *u, const uint64_t *cw) {
+  const int NT = 10, nchunks = slots / 4;
   for (int c = 0; c < nchunks; c++)
     for (int v = 0; v < NT; v++)
       for (int lane = 0; lane < 32; lane++) {
         const int g = lane >> 2, t = lane & 3;        // B fragment: column g of the n-tile, k-bytes 4t.. and 16+4t..
-        // column g belongs to quad lane tc = g / 2 of the C fragment, e = g % 2
-        const int tc = g >> 1, e = g & 1;
-        const int d = 4 * c + t;
+        const int tc = g >> 1, e = g & 1;             // column g belongs to quad lane tc of the C fragment
+        const int s = 4 * c + t;
         uint32_t reg[2] = {0, 0};
         for (int half = 0; half < 2; half++)
           for (int kb = 0; kb < 4; kb++) {
-            const int a = 4 * half + kb;              // byte a of the residue of limb d
+            const int a = 4 * half + kb;              // byte a of the residue in slot s
             int val = 0;
-            if (d < D) {
-              if (v < W) {
-                const int j = 2 * W * tc + 2 * v + e; // output byte position
-                const int src = j - a;                // byte of K_d = phat_d mod 2^(64W)
-                if (src >= 0 && src < 8 * W) val = (int)((phat_low[(size_t)d * W + src / 8] >> (8 * (src % 8))) & 0xff);
-              } else {
-                const int j = 4 * tc + 2 * (v - W) + e;
-                const int src = j - a;                // byte of u_d (64 bits)
-                if (src >= 0 && src < 8) val = (int)((u[d] >> (8 * src)) & 0xff);
-              }
+            if (v < 8) {
+              const int j = 16 * tc + 2 * v + e;      // output byte position (8 words)
+              const int src = j - a;                  // byte of K_s
+              if (src >= 0 && src < 64) val = (int)((K[(size_t)s * 8 + src / 8] >> (8 * (src % 8))) & 0xff);
+            } else {
+              const int j = 4 * tc + 2 * (v - 8) + e;
+              const int src = j - a;                  // byte of u_s (64 bits)
+              if (src >= 0 && src < 8) val = (int)((u[s] >> (8 * src)) & 0xff);
             }
             reg[half] |= (uint32_t)val << (8 * kb);
           }
         tab[(((size_t)c * NT + v) * 32 + lane) * 2 + 0] = reg[0];
         tab[(((size_t)c * NT + v) * 32 + lane) * 2 + 1] = reg[1];
       }
+  uint32_t *tail = tab + (size_t)nchunks * NT * 64;
+  for (int w = 0; w < 8; w++) { tail[2 * w] = (uint32_t)cw[w]; tail[2 * w + 1] = (uint32_t)(cw[w] >> 32); }
 }
 
-// Returns 1 (one launch; the caller follows with the exact list-mode kernel), -1 when no instantiation fits.
+// persistent grid: four blocks of four warps per SM (up to 128 registers per thread; five blocks at 96 registers
+// measured slower, 19.7 / 26.8 us against 18.1 / 24.5 us), shared between the polynomials
+static dim3 tc_grid(int n, int npolys) {
+  int gx = (n + 63) / 64, cap = (GQ_NUM_SMS * 4) / npolys;       // never a second, nearly empty wave
+  if (gx > cap) gx = cap;
+  if (gx < 1) gx = 1;
+  return dim3(gx, npolys);
+}
+
+#ifdef GQ_EMULATE
+#define GQ_TC_LAUNCH(KSV, RV, ...) gq_emul::launch_dyn(grid, block, smem, [&]() { k_crt_tc<KSV, RV>(__VA_ARGS__); })
+#else
+#define GQ_TC_LAUNCH(KSV, RV, ...) k_crt_tc<KSV, RV><<<grid, block, smem, st>>>(__VA_ARGS__)
+#endif
+
+// K5.  Returns 1 (one launch; the caller follows with the exact list-mode kernel), -1 when this form does not apply.
 int gq_launch_reconstruct_tc(const GqCrtBasis &B, const uint32_t *tab, int n, const uint64_t *rhat, unsigned k,
                              const GqPtrs4 &out, int Wout, int npolys, cudaStream_t st, int *fix, unsigned rs_j,
                              const GqWaitIn *wt) {
-  if (!tab || !fix || k < 1 || rs_j > k || B.F < 64 + 32 || B.F > 64 + 62) return -1;
-  const int W = (int)((k + 63) / 64), nchunks = (B.D + 3) / 4;
-  if (W > 7 || W > Wout) return -1;
+  if (!tab || !fix || k < 1 || rs_j >= k || rs_j >= 64 || B.F < 64 + 32 || B.F > 64 + 62) return -1;
+  if (k > 512 || Wout > 8 || Wout < (int)((k + 63) / 64)) return -1;
+  TcArgs a = TcArgs();
+  a.D = B.D; a.ych = (B.D + 3) / 4;
+  a.frag = (const unsigned long long *)tab;
+  a.cw = (const uint64_t *)(tab + (size_t)a.ych * 10 * 64);
+  a.hc = B.hc; a.fs = B.F - 64; a.fsP = a.fs;
   GqWaitIn w0 = GqWaitIn();
   if (wt) w0 = *wt;
-  int gx = (n + 255) / 256;           // 256 coefficients per block: the 9-14 KB table is staged once per block
-  if (gx < 1) gx = 1;
-  const dim3 grid(gx, npolys), block(128);
-  const size_t smem = gq_crt_tc_table_words(B.D, W) * 4;
-  int *fc = fix, *fl = fix + 4;
-#ifdef GQ_EMULATE
-#define GQ_TC(V) gq_emul::launch_dyn(grid, block, smem, [&]() { k_reconstruct_tc<V>(B, tab, nchunks, n, rhat, k, out, Wout, fc, fl, rs_j, w0); })
-#else
-#define GQ_TC(V) k_reconstruct_tc<V><<<grid, block, smem, st>>>(B, tab, nchunks, n, rhat, k, out, Wout, fc, fl, rs_j, w0)
-#endif
-  switch (W) {
-    case 1: GQ_TC(1); break;
-    case 2: GQ_TC(2); break;
-    case 3: GQ_TC(3); break;
-    case 4: GQ_TC(4); break;
-    case 5: GQ_TC(5); break;
-    case 6: GQ_TC(6); break;
-    case 7: GQ_TC(7); break;
-    default: return -1;
-  }
-#undef GQ_TC
+  const dim3 grid = tc_grid(n, npolys), block(128);
+  const size_t smem = (size_t)a.ych * 10 * 32 * 8;
+  if (smem > 48 * 1024) return -1;
+  GqPtrs4 none = GqPtrs4();
+  if (a.ych <= 2) GQ_TC_LAUNCH(false, 2, a, n, rhat, k, none, 0, out, Wout, fix, fix + 4, rs_j, w0);
+  else if (a.ych <= 4) GQ_TC_LAUNCH(false, 4, a, n, rhat, k, none, 0, out, Wout, fix, fix + 4, rs_j, w0);
+  else GQ_TC_LAUNCH(false, 6, a, n, rhat, k, none, 0, out, Wout, fix, fix + 4, rs_j, w0);
+  return 1;
+}
+
+// K6.  tab: the table of gq_crt_tc_table over 4*ceil(D2/4) + 4*ceil(dim/4) slots (y part, then z part).
+int gq_launch_ks_epilogue_tc(const GqCrtBasis &B, const GqCrtBasis &BP, const uint32_t *tab, const GqPrime *primes,
+                             const ulonglong2 *ratio, int n, const uint64_t *chat, unsigned k, const GqPtrs4 &add,
+                             int Wadd, const GqPtrs4 &out, int Wout, int npolys, cudaStream_t st, int *fix,
+                             unsigned rs_j, const GqWaitIn *wt) {
+  if (!tab || !fix || !ratio || k < 1 || rs_j >= k || rs_j >= 64) return -1;
+  if (B.F < 64 + 32 || B.F > 64 + 62 || BP.F < 64 + 32 || BP.F > 64 + 62 || BP.D > B.D) return -1;
+  if (k > 512 || Wout > 8 || Wout < (int)((k + 63) / 64)) return -1;
+  bool has_add = false;
+  for (int b = 0; b < npolys && b < 4; b++) has_add = has_add || add.p[b];
+  if (has_add && (Wadd > 8 || 64u * (unsigned)Wadd < k)) return -1;     // the addend's sign words would matter
+  TcArgs a = TcArgs();
+  a.D = B.D; a.ych = (B.D + 3) / 4; a.DP = BP.D; a.zch = (BP.D + 3) / 4;
+  a.frag = (const unsigned long long *)tab;
+  a.cw = (const uint64_t *)(tab + (size_t)(a.ych + a.zch) * 10 * 64);
+  a.hc = B.hc; a.fs = B.F - 64; a.fsP = BP.F - 64;
+  a.primes = primes; a.ratio = ratio;
+  GqWaitIn w0 = GqWaitIn();
+  if (wt) w0 = *wt;
+  const dim3 grid = tc_grid(n, npolys), block(128);
+  const size_t smem = (size_t)(a.ych + a.zch) * 10 * 32 * 8;
+  if (smem > 48 * 1024) return -1;
+  if (a.ych <= 4) GQ_TC_LAUNCH(true, 4, a, n, chat, k, add, Wadd, out, Wout, fix, fix + 4, rs_j, w0);
+  else GQ_TC_LAUNCH(true, 6, a, n, chat, k, add, Wadd, out, Wout, fix, fix + 4, rs_j, w0);
   return 1;
 }

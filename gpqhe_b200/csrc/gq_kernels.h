@@ -52,17 +52,22 @@ int gq_launch_reconstruct(const GqCrtBasis &B, const GqPrime *primes, int n, con
                           const GqModulus &q, const GqPtrs4 &out, int Wout, int npolys,
                           cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0, bool pre = false,
                           const GqWaitIn *wt = nullptr, const uint32_t *tc_tab = nullptr);
-// K5 on the tensor cores (gq_crt_tc.cu): u8 mma.sync contraction of the residue bytes with a constant byte table
-size_t gq_crt_tc_table_words(int D, int W);
-void gq_crt_tc_table(uint32_t *tab, int D, int W, const uint64_t *phat_low, const uint64_t *u);
+// K5 / K6 on the tensor cores (gq_crt_tc.cu): u8 mma.sync contraction of the residue bytes with a constant byte
+// table over `slots` limb slots (K: 8 words per slot, u: one estimate word per slot, cw: 8 words)
+size_t gq_crt_tc_table_words(int slots);
+void gq_crt_tc_table(uint32_t *tab, int slots, const uint64_t *K, const uint64_t *u, const uint64_t *cw);
 int gq_launch_reconstruct_tc(const GqCrtBasis &B, const uint32_t *tab, int n, const uint64_t *rhat, unsigned k,
                              const GqPtrs4 &out, int Wout, int npolys, cudaStream_t st, int *fix, unsigned rs_j,
                              const GqWaitIn *wt);
+int gq_launch_ks_epilogue_tc(const GqCrtBasis &B, const GqCrtBasis &BP, const uint32_t *tab, const GqPrime *primes,
+                             const ulonglong2 *ratio, int n, const uint64_t *chat, unsigned k, const GqPtrs4 &add,
+                             int Wadd, const GqPtrs4 &out, int Wout, int npolys, cudaStream_t st, int *fix,
+                             unsigned rs_j, const GqWaitIn *wt);
 int gq_launch_ks_epilogue(const GqCrtBasis &B, const GqCrtBasis &BP, const uint64_t *Pinv,
                           const GqPrime *primes, int n, const uint64_t *chat, unsigned k,
                           const GqPtrs4 &add, int Wadd, const GqPtrs4 &out, int Wout, int npolys,
                           cudaStream_t st, int *fix = nullptr, unsigned rs_j = 0, const ulonglong2 *ratio = nullptr,
-                          const GqWaitIn *wt = nullptr);
+                          const GqWaitIn *wt = nullptr, const uint32_t *tc_tab = nullptr);
 // general-modulus key-switch epilogue (exact long division, slow path)
 int gq_launch_ks_epilogue_general(const GqCrtBasis &B, const uint64_t *P, int nP,
                                   const uint64_t *Ph, const GqPrime *primes, int n,

@@ -39,6 +39,7 @@ class ShardedHe:
 
     def __init__(self, ctx: HeContext, group=None, device: torch.device | str | None = None):
         self.ctx, self.group = ctx, group
+        self._pre_cache = {}
         self.G = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.n, self.W = ctx.n, ctx.W
@@ -124,6 +125,43 @@ class ShardedHe:
                                                   out.data_ptr(), None))
         return out
 
+
+    # -- stage calls: the pre-scaled forms (inverse NTT ending in the CRT pre-multiplication, CRT stages on the tensor
+    #    cores) when the library has them for the basis, else the plain ones.  GPQHE_B200_SHARDED_PLAIN=1 forces plain.
+    def _pre(self, D, l, ks):
+        key = (D, l, ks)
+        if key not in self._pre_cache:
+            ok = not os.environ.get("GPQHE_B200_SHARDED_PLAIN") and \
+                bool(self._lib.gq_stage_prescale_ok(self._h, D, l, 1 if ks else 0))
+            self._pre_cache[key] = ok
+        return self._pre_cache[key]
+
+    def _tensor_inv(self, lo, Dl, D, l, y, x):
+        if self._pre(D, l, False):
+            self._ck(self._lib.gq_stage_tensor_inv_pre_dev(self._h, lo, Dl, D, y.data_ptr(), x.data_ptr(), None))
+        else:
+            self._ck(self._lib.gq_stage_tensor_inv_dev(self._h, lo, Dl, y.data_ptr(), x.data_ptr(), None))
+
+    def _mul_evk_inv(self, lo, Dl, D, l, y, x, evk):
+        if self._pre(D, l, True):
+            self._ck(self._lib.gq_stage_mul_evk_inv_pre_dev(self._h, lo, Dl, D, y.data_ptr(), x.data_ptr(), evk._h, None))
+        else:
+            self._ck(self._lib.gq_stage_mul_evk_inv_dev(self._h, lo, Dl, y.data_ptr(), x.data_ptr(), evk._h, None))
+
+    def _reconstruct(self, D, l, rh_ptr, outs, npolys=3):
+        f = self._lib.gq_stage_reconstruct_pre_dev if self._pre(D, l, False) else self._lib.gq_stage_reconstruct_dev
+        self._ck(f(self._h, D, l, npolys, rh_ptr, outs, self.n_loc, None))
+
+    def _ks_epilogue(self, D2, l, ch_ptr, add0, add1, c0, c1, rescale):
+        a0 = add0.data_ptr() if add0 is not None else None
+        a1 = add1.data_ptr() if add1 is not None else None
+        if self._pre(D2, l, True):
+            self._ck(self._lib.gq_stage_ks_epilogue_pre_dev(self._h, l, ch_ptr, a0, a1, c0.data_ptr(), c1.data_ptr(),
+                                                            self.n_loc, 1 if rescale else 0, None))
+        else:
+            f = self._lib.gq_stage_ks_epilogue_rs_dev if rescale else self._lib.gq_stage_ks_epilogue_dev
+            self._ck(f(self._h, l, ch_ptr, a0, a1, c0.data_ptr(), c1.data_ptr(), self.n_loc, None))
+
     # ------------------------------------------------------------------ operations
     def he_mul(self, l: int, a0, a1, b0, b1, rlk: HeEvk):
         """he_mul + relinearise on coefficient slices; returns (c0, c1) slices at level l."""
@@ -135,12 +173,12 @@ class ShardedHe:
         x = self._coef_to_limb(self._decompose([a0, a1, b0, b1], D1), D1)          # [4, D1l, n]
         self._ck(lib.gq_stage_ntt_dev(h, lo1, D1l, 4, x.data_ptr(), 0, None))
         y = self._empty(3, D1l, self.n)
-        self._ck(lib.gq_stage_tensor_inv_dev(h, lo1, D1l, y.data_ptr(), x.data_ptr(), None))   # tensor + inverse NTT
+        self._tensor_inv(lo1, D1l, D1, l, y, x)                                   # tensor + inverse NTT
         # hot loop B (he-mult.c:139-141)
         rh = self._limb_to_coef(y, D1)                                            # [3, D1, n_loc]
         d = self._empty(3, self.W, self.n_loc)
         outs = (C.c_void_p * 3)(*[d[k].data_ptr() for k in range(3)])
-        self._ck(lib.gq_stage_reconstruct_dev(h, D1, l, 3, rh.data_ptr(), outs, self.n_loc, None))
+        self._reconstruct(D1, l, rh.data_ptr(), outs)
         # he_relin (he-mult.c:40-85): key switch of d2 = d[2]
         c0, c1 = self.keyswitch(l, d[2], rlk, d[0], d[1], lo2, D2l, D2)
         return c0, c1
@@ -153,12 +191,10 @@ class ShardedHe:
         x = self._coef_to_limb(self._decompose([dpoly], D2), D2)                  # [1, D2l, n]
         self._ck(lib.gq_stage_ntt_dev(h, lo2, D2l, 1, x.data_ptr(), 0, None))
         y = self._empty(2, D2l, self.n)
-        self._ck(lib.gq_stage_mul_evk_inv_dev(h, lo2, D2l, y.data_ptr(), x.data_ptr(), evk._h, None))   # x evk + inverse NTT
+        self._mul_evk_inv(lo2, D2l, D2, l, y, x, evk)                             # x evk + inverse NTT
         ch = self._limb_to_coef(y, D2)                                            # [2, D2, n_loc]
         c0, c1 = self._empty(self.W, self.n_loc), self._empty(self.W, self.n_loc)
-        self._ck(lib.gq_stage_ks_epilogue_dev(h, l, ch.data_ptr(), add0.data_ptr() if add0 is not None else None,
-                                              add1.data_ptr() if add1 is not None else None,
-                                              c0.data_ptr(), c1.data_ptr(), self.n_loc, None))
+        self._ks_epilogue(D2, l, ch.data_ptr(), add0, add1, c0, c1, False)
         return c0, c1
 
     def he_rs(self, l: int, c0, c1):
@@ -262,14 +298,14 @@ class MulPlan:
         sh, lib, h = self.sh, self.sh._lib, self.sh._h
         self._unpack_c2l(0, self.xl)
         sh._ck(lib.gq_stage_ntt_dev(h, self.lo1, self.D1l, 4, self.xl.data_ptr(), 0, None))
-        sh._ck(lib.gq_stage_tensor_inv_dev(h, self.lo1, self.D1l, self.yl.data_ptr(), self.xl.data_ptr(), None))
+        sh._tensor_inv(self.lo1, self.D1l, self.D1, self.l, self.yl, self.xl)
         self._pack_l2c(1, self.yl)
 
     def _seg2(self):
         sh, lib, h = self.sh, self.sh._lib, self.sh._h
         self._unpack_l2c(1, self.rh, self.off1)
         outs = (C.c_void_p * 3)(*[self.d[k].data_ptr() for k in range(3)])
-        sh._ck(lib.gq_stage_reconstruct_dev(h, self.D1, self.l, 3, self.rh.data_ptr(), outs, sh.n_loc, None))
+        sh._reconstruct(self.D1, self.l, self.rh.data_ptr(), outs)
         arr = (C.c_void_p * 1)(self.d[2].data_ptr())
         sh._ck(lib.gq_stage_decompose_dev(h, 0, self.D2, 1, arr, sh.W, sh.n_loc, self.x2c.data_ptr(), None))
         self._pack_c2l(2, self.x2c, self.off2)
@@ -278,15 +314,14 @@ class MulPlan:
         sh, lib, h = self.sh, self.sh._lib, self.sh._h
         self._unpack_c2l(2, self.x2l)
         sh._ck(lib.gq_stage_ntt_dev(h, self.lo2, self.D2l, 1, self.x2l.data_ptr(), 0, None))
-        sh._ck(lib.gq_stage_mul_evk_inv_dev(h, self.lo2, self.D2l, self.y2l.data_ptr(), self.x2l.data_ptr(), self.rlk._h, None))
+        sh._mul_evk_inv(self.lo2, self.D2l, self.D2, self.l, self.y2l, self.x2l, self.rlk)
         self._pack_l2c(3, self.y2l)
 
     def _seg4(self):
         sh, lib, h = self.sh, self.sh._lib, self.sh._h
         self._unpack_l2c(3, self.ch, self.off2)
-        ks = lib.gq_stage_ks_epilogue_rs_dev if self.rescale else lib.gq_stage_ks_epilogue_dev     # he_rs rides in the epilogue
-        sh._ck(ks(h, self.l, self.ch.data_ptr(), self.d[0].data_ptr(), self.d[1].data_ptr(),
-                  self.out[0].data_ptr(), self.out[1].data_ptr(), sh.n_loc, None))
+        sh._ks_epilogue(self.D2, self.l, self.ch.data_ptr(), self.d[0], self.d[1], self.out[0], self.out[1],
+                        self.rescale)                # he_rs rides in the epilogue
 
     def _capture(self):
         """record each segment once; must be called with the context's stream current"""
@@ -371,6 +406,13 @@ class P2PPlan:
             return x
         self.x = [xchg(0, self.D1, self.p_xl1, self.c_off1), xchg(1, self.D1, self.p_rh, self.c_off1),
                   xchg(2, self.D2, self.p_xl2, self.c_off2), xchg(3, self.D2, self.p_ch, self.c_off2)]
+        # limb -> coefficient exchanges carry residues pre-scaled for the CRT (tensor-core CRT stages) when the
+        # library has those forms for the two bases; every rank takes the same decision (same context parameters)
+        plain = bool(os.environ.get("GPQHE_B200_SHARDED_PLAIN"))
+        self.pre1 = not plain and bool(self._lib.gq_stage_prescale_ok(self._h, self.D1, self.l, 0))
+        self.pre2 = not plain and bool(self._lib.gq_stage_prescale_ok(self._h, self.D2, self.l, 1))
+        self.x[1].pre = 1 if self.pre1 else 0
+        self.x[3].pre = 1 if self.pre2 else 0
 
     def _offsets(self, D):
         base, extra = divmod(D, self.G)
@@ -429,12 +471,16 @@ class P2PPlan:
             if self.D1l:
                 xl = self._loc("xl1")
                 self._ck(lib.gq_stage_ntt_dev(h, self.lo1, self.D1l, 4, xl, 0, None))
-                self._ck(lib.gq_stage_tensor_inv_dev(h, self.lo1, self.D1l, self.yl.data_ptr(), xl, None))
+                if self.pre1:
+                    self._ck(lib.gq_stage_tensor_inv_pre_dev(h, self.lo1, self.D1l, self.D1, self.yl.data_ptr(), xl, None))
+                else:
+                    self._ck(lib.gq_stage_tensor_inv_dev(h, self.lo1, self.D1l, self.yl.data_ptr(), xl, None))
             self._l2c(self.yl, 3, self.D1l, self.D1, self.p_rh, self.c_off1, 1)
         elif k == 2:
             self._wait(1)
             outs = (C.c_void_p * 3)(*[self.d[j].data_ptr() for j in range(3)])
-            self._ck(lib.gq_stage_reconstruct_dev(h, self.D1, self.l, 3, self._loc("rh"), outs, nl, None))
+            rec = lib.gq_stage_reconstruct_pre_dev if self.pre1 else lib.gq_stage_reconstruct_dev
+            self._ck(rec(h, self.D1, self.l, 3, self._loc("rh"), outs, nl, None))
             arr = (C.c_void_p * 1)(self.d[2].data_ptr())
             self._ck(lib.gq_stage_decompose_dev(h, 0, self.D2, 1, arr, W, nl, self.x2c.data_ptr(), None))
             self._c2l(self.x2c, 1, self.D2, self.p_xl2, self.c_off2, 2)
@@ -443,13 +489,21 @@ class P2PPlan:
             if self.D2l:
                 xl = self._loc("xl2")
                 self._ck(lib.gq_stage_ntt_dev(h, self.lo2, self.D2l, 1, xl, 0, None))
-                self._ck(lib.gq_stage_mul_evk_inv_dev(h, self.lo2, self.D2l, self.y2l.data_ptr(), xl, self.rlk._h, None))
+                if self.pre2:
+                    self._ck(lib.gq_stage_mul_evk_inv_pre_dev(h, self.lo2, self.D2l, self.D2, self.y2l.data_ptr(), xl, self.rlk._h, None))
+                else:
+                    self._ck(lib.gq_stage_mul_evk_inv_dev(h, self.lo2, self.D2l, self.y2l.data_ptr(), xl, self.rlk._h, None))
             self._l2c(self.y2l, 2, self.D2l, self.D2, self.p_ch, self.c_off2, 3)
         else:
             self._wait(3)
-            ks = lib.gq_stage_ks_epilogue_rs_dev if self.rescale else lib.gq_stage_ks_epilogue_dev
-            self._ck(ks(h, self.l, self._loc("ch"), self.d[0].data_ptr(), self.d[1].data_ptr(),
-                        self.out[0].data_ptr(), self.out[1].data_ptr(), nl, None))
+            if self.pre2:
+                self._ck(lib.gq_stage_ks_epilogue_pre_dev(h, self.l, self._loc("ch"), self.d[0].data_ptr(), self.d[1].data_ptr(),
+                                                          self.out[0].data_ptr(), self.out[1].data_ptr(), nl,
+                                                          1 if self.rescale else 0, None))
+            else:
+                ks = lib.gq_stage_ks_epilogue_rs_dev if self.rescale else lib.gq_stage_ks_epilogue_dev
+                self._ck(ks(h, self.l, self._loc("ch"), self.d[0].data_ptr(), self.d[1].data_ptr(),
+                            self.out[0].data_ptr(), self.out[1].data_ptr(), nl, None))
 
     def _seg_fused(self, k):
         """the same five segments with the exchanges inside the kernels: 16 launches per op instead of 28"""

@@ -347,6 +347,21 @@ int gq_stage_ks_epilogue_dev(gq_ctx *ctx, unsigned l, const uint64_t *chat_dev, 
                              void *stream);
 int gq_stage_rescale_dev(gq_ctx *ctx, unsigned l, uint64_t *c0_dev, uint64_t *c1_dev, int divide,
                          unsigned ncoef, void *stream);
+/* The same stages on PRE-SCALED residues, the form he_mul / he_rot use internally: the inverse transforms end with the
+   first multiplication of rns_reconstruct (src/rns.c:68-69, y_d = a_d (P/p_d)^-1 mod p_d over the basis
+   {p_0..p_(D-1)}) folded into their N^-1 scaling, and the CRT stages take such residues - which lets them run as
+   tensor-core contractions (gq_crt_tc.cu).  gq_stage_prescale_ok: 1 when these forms exist for the basis D at level l
+   (keyswitch != 0: D must be the key-switch basis of l), else use the plain entries above.  `rescale` folds he_rs in. */
+int gq_stage_prescale_ok(gq_ctx *ctx, unsigned D, unsigned l, int keyswitch);
+int gq_stage_tensor_inv_pre_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsigned D, uint64_t *y_dev,
+                                const uint64_t *x_dev, void *stream);
+int gq_stage_mul_evk_inv_pre_dev(gq_ctx *ctx, unsigned limb0, unsigned nlimbs, unsigned D, uint64_t *y_dev,
+                                 const uint64_t *x_dev, const gq_evk *evk, void *stream);
+int gq_stage_reconstruct_pre_dev(gq_ctx *ctx, unsigned D, unsigned l, unsigned npolys, const uint64_t *rhat_dev,
+                                 uint64_t *const *out_dev, unsigned ncoef, void *stream);
+int gq_stage_ks_epilogue_pre_dev(gq_ctx *ctx, unsigned l, const uint64_t *chat_dev, const uint64_t *add0_dev,
+                                 const uint64_t *add1_dev, uint64_t *c0_dev, uint64_t *c1_dev, unsigned ncoef,
+                                 int rescale, void *stream);
 
 /* ---- peer-to-peer re-layout for the sharded pipeline (gq_p2p.cu) ----------------------------
  * One receive slab per rank, exported / mapped with CUDA IPC (one process per GPU, same node).
@@ -394,6 +409,7 @@ typedef struct gq_p2p_xchg {
   const unsigned long long *epoch_dev;
   int *err_dev;
   unsigned *ticket_dev;
+  unsigned pre;   /* != 0: the residues of this exchange are pre-scaled for the basis D (gq_stage_prescale_ok) */
 } gq_p2p_xchg;
 int gq_p2p_fused_ok(gq_ctx *ctx, unsigned l);
 int gq_p2p_decompose_dev(gq_ctx *ctx, unsigned nlimbs, unsigned npolys, const uint64_t *const *in_dev, unsigned W,

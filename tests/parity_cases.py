@@ -239,6 +239,12 @@ def check_crt_edges(lib_path, logn=5, q=1 << 438, Delta=1 << 50, logqub=438):
         PB = oc.rns[D2 - 1].P
         Ph = PB // 2
         edge = [Ph - 1, Ph, Ph + 1, 0, PB - 1, 1, Ph - 5, 7]
+        # ... and the decision boundaries of T mod P over the special modulus: r = 0, P - 1 (the overflow count of the
+        # inner CRT) and r = (P -+ 1) / 2 (the rounding of T / P), for positive and negative T
+        Ps = oc.rns[ctx.dim - 1].P
+        edge += [3 * Ps + Ps // 2, 3 * Ps + Ps // 2 + 1, 9 * Ps, 9 * Ps - 1, 9 * Ps + 1, PB - 4 * Ps - Ps // 2,
+                 PB - 4 * Ps - Ps // 2 - 1, PB - 6 * Ps, PB - 6 * Ps + 1, Ps // 2, Ps // 2 + 1, Ps - 1, Ps]
+        edge = [v % PB for v in edge]
         z0 = [edge[i % len(edge)] for i in range(n)]
         z1 = [edge[(i + 3) % len(edge)] for i in range(n)]
 

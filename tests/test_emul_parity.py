@@ -186,3 +186,14 @@ def test_fused_rescale_tie_rule(emul_lib):
 def test_fused_inverse_equals_separate_kernels(emul_lib, logn, level):
     """two-kernel transforms (n = 2^13) and one-tile transforms: every loader mode of the fused inverse NTT"""
     pc.check_fused_vs_separate(emul_lib, logn, level=level)
+
+
+@pytest.mark.parametrize("logq", [500, 512, 65])
+def test_tensor_core_crt_widths(emul_lib, logq):
+    """the tensor-core reconstruction (gq_crt_tc.cu) at 8 result words (every byte column in use), at the widest
+    modulus it takes, and at 2 words (6 of 8 words are padding): product, rescale ties, edge values, fused vs separate"""
+    q, Delta = 1 << logq, 1 << (50 if logq > 100 else 20)
+    pc.check_he_vs_oracle(emul_lib, 5, q, 4, Delta, seed=logq, levels=None if logq < 100 else [9, 5, 1], logqub=logq)
+    pc.check_crt_edges(emul_lib, logn=5, q=q, Delta=Delta, logqub=logq)
+    pc.check_fused_rescale_ties(emul_lib, logn=5, q=q, Delta=Delta, logqub=logq)
+    pc.check_fused_vs_separate(emul_lib, 5, q=q, Delta=Delta, logqub=logq)

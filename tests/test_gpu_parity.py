@@ -178,3 +178,14 @@ def test_fused_rescale_tie_rule(real_lib):
 @pytest.mark.parametrize("logn", [16, 14, 12])
 def test_fused_inverse_equals_separate_kernels(real_lib, logn):
     pc.check_fused_vs_separate(real_lib, logn)
+
+
+@pytest.mark.parametrize("logq", [500, 512, 65])
+def test_tensor_core_crt_widths(real_lib, logq):
+    """the tensor-core reconstruction (gq_crt_tc.cu) at 8 result words (every byte column in use), at the widest
+    modulus it takes, and at 2 words (6 of 8 words are padding): product, rescale ties, edge values, fused vs separate"""
+    q, Delta = 1 << logq, 1 << (50 if logq > 100 else 20)
+    pc.check_he_vs_oracle(real_lib, 10, q, 4, Delta, seed=logq, levels=None if logq < 100 else [9, 5, 1], logqub=logq)
+    pc.check_crt_edges(real_lib, logn=10, q=q, Delta=Delta, logqub=logq)
+    pc.check_fused_rescale_ties(real_lib, logn=10, q=q, Delta=Delta, logqub=logq)
+    pc.check_fused_vs_separate(real_lib, 10, q=q, Delta=Delta, logqub=logq)
