@@ -472,9 +472,14 @@ def run_ours(args):
         # u8 multiply-accumulates per coefficient of the tensor-core CRT: 32 K-bytes per chunk of 4 limbs x 80 columns
         tc_mac1 = 32 * ((D1 + 3) // 4) * 80
         tc_mac2 = 32 * ((D2 + 3) // 4 + (ctx.dim + 3) // 4) * 80
+        # decomposition: the tensor-core form for coefficients of at most 7 words over pseudo-Mersenne primes (64 K-bytes x
+        # 8 byte columns per residue), else 28-bit digits on the integer pipe (15 digits x 2 multiply-adds + 4 in the fold)
+        dec_tc = W <= 7 and pre1 and not os.environ.get("GPQHE_B200_NO_TC_CRT")
+        dec_kern = "k_decompose_tc (u8 mma.sync contraction)" if dec_tc else "k_decompose28<7, pm>"
+        dec_w = 512 if dec_tc else 34.0
         stages = [
-            ("decompose x4 -> D1", "k_decompose28<7, pm>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D1, 4, in4, W, n, xc.data_ptr(), None)),
-             4 * D1 * n, 34.0, 4 * W * n * 8 + 4 * D1 * n * 8),     # 15 digits x 2 multiply-adds + 4 in the fold
+            ("decompose x4 -> D1", dec_kern, lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D1, 4, in4, W, n, xc.data_ptr(), None)),
+             4 * D1 * n, dec_w, 4 * W * n * 8 + 4 * D1 * n * 8),
             ("forward NTT, 4 x D1 limb-polys", "k_nttl_fwd_strided<4> + k_nttl_fwd_tile<12>", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D1, 4, xc.data_ptr(), 0, None)),
              4 * D1 * (n // 2) * LOGN, 8.0, 2 * 2 * 4 * D1 * n * 8),
             ("tensor product + inverse NTT, 3 x D1", "k_nttl_inv_tile<12, TENSOR> + k_nttl_inv_strided<4>",
@@ -482,8 +487,8 @@ def run_ours(args):
              3 * D1 * (n // 2) * LOGN, 8.0 + 4 * 7.0 * 2 / (3 * LOGN), (4 + 3 + 2 * 3) * D1 * n * 8),
             ("reconstruct x3 over D1", "k_crt_tc<K5> (u8 mma.sync contraction)" if pre1 else "k_reconstruct_fast<7>", reconstruct,
              3 * n, (tc_mac1 if pre1 else D1 * 38.0 + 4 * W), 3 * D1 * n * 8 + 3 * W * n * 8),
-            ("decompose d2 -> D2", "k_decompose28<7, pm>", lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D2, 1, in1, W, n, x2.data_ptr(), None)),
-             D2 * n, 34.0, W * n * 8 + D2 * n * 8),
+            ("decompose d2 -> D2", dec_kern, lambda i: ck(lib.gq_stage_decompose_dev(h, 0, D2, 1, in1, W, n, x2.data_ptr(), None)),
+             D2 * n, dec_w, W * n * 8 + D2 * n * 8),
             ("forward NTT, D2", "k_nttl_fwd_*", lambda i: ck(lib.gq_stage_ntt_dev(h, 0, D2, 1, x2.data_ptr(), 0, None)),
              D2 * (n // 2) * LOGN, 8.0, 2 * 2 * D2 * n * 8),
             ("multiply by rlk + inverse NTT, 2 x D2", "k_nttl_inv_tile<12, EVK> + k_nttl_inv_strided<4>",
@@ -503,11 +508,11 @@ def run_ours(args):
             t = timed(fn, reps, 3) / reps
             total += t
             fh = nbytes / (t * 1e-3) / 1e9 / hbm
-            if "k_crt_tc" in kern:       # tensor-core rows: the work is u8 MACs against the measured mma.sync u8 peak
+            if "_tc" in kern:            # tensor-core rows: the work is u8 MACs against the measured mma.sync u8 peak
                 ft = units * mulw / (t * 1e-3) / (imma_peak * 1e12) if imma_peak else None
                 rows.append({"stage": name, "kernel": kern, "us": t * 1e3, "units": units, "u8_mac_per_unit": mulw,
                              "algorithmic_bytes": nbytes, "frac_tensor_u8": ft, "frac_hbm": fh,
-                             "bound": "latency (carry epilogue); nearest roof: " + ("hbm" if fh >= (ft or 0) else "tensor")})
+                             "bound": "latency (integer epilogue); nearest roof: " + ("hbm" if fh >= (ft or 0) else "tensor")})
                 continue
             fi = units * mulw / (t * 1e-3) / mw_peak.value if mw_peak.value else None
             rows.append({"stage": name, "kernel": kern, "us": t * 1e3, "units": units, "mul32_per_unit": mulw,

@@ -758,6 +758,25 @@ static GqPtrs4 ptrs(const uint64_t *a, const uint64_t *b = nullptr, const uint64
   return p;
 }
 
+// B-fragment table of the tensor-core decomposition for coefficients of W words (every prime of the context), built
+// on first use and kept by the root context
+static const unsigned long long *dec_tc_table(gq_ctx *c, unsigned W) {
+  if (getenv("GPQHE_B200_NO_TC_CRT") || W == 0 || W > 7) return nullptr;
+  gq_ctx *root = c->parent ? c->parent : c;
+  const unsigned key = 0x20000u + W;
+  auto it = root->tc_tabs.find(key);
+  if (it != root->tc_tabs.end()) return (const unsigned long long *)it->second;
+  std::vector<uint64_t> p(root->dimub);
+  for (unsigned d = 0; d < root->dimub; d++) p[d] = root->primes[d].p;
+  std::vector<unsigned long long> tab(gq_dec_tc_table_words((int)root->dimub));
+  gq_dec_tc_table(tab.data(), (int)root->dimub, p.data(), (int)W);
+  uint32_t *dv = nullptr;
+  if (cudaMalloc((void **)&dv, tab.size() * 8) != cudaSuccess) return nullptr;
+  if (cudaMemcpy(dv, tab.data(), tab.size() * 8, cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(dv); return nullptr; }
+  root->tc_tabs[key] = dv;
+  return (const unsigned long long *)dv;
+}
+
 // ncoef: coefficients per polynomial in this call (0 = the whole ring); the coefficient-local
 // stages work on any slice because one thread owns one coefficient
 static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtrs4 &in, unsigned W,
@@ -772,6 +791,15 @@ static int decompose_dev(gq_ctx *c, unsigned limb0, unsigned nlimbs, const GqPtr
   // 0 = word form, 1 = 32-bit digits, 2 = 28-bit digits (at most 16 of them: carry-free column sums),
   // 3 = 28-bit digits with the pseudo-Mersenne fold
   const int digits = !dig ? 0 : (W <= 7 && !getenv("GPQHE_B200_DEC32")) ? (pm_ok(c, limb0, nlimbs) ? 3 : 2) : 1;
+  if (digits == 3) {          // pseudo-Mersenne primes, at most 7 words: the u8 tensor-core contraction (gq_crt_tc.cu)
+    const unsigned long long *tt = dec_tc_table(c, W);
+    if (tt && gq_launch_decompose_tc(tt, c->d_primes, (int)ncoef, (int)limb0, (int)nlimbs, in, (int)W, out, (int)npolys,
+                                     st, po) == 1) {
+      c->launches++;
+      GQ_CHECK_LAUNCH(c);
+      return 0;
+    }
+  }
   if (gq_launch_decompose(c->dec_tables(), (int)ncoef, (int)limb0, (int)nlimbs, in, (int)W, out,
                           (int)npolys, st, digits, po) < 0)
     GQ_FAIL(po ? "no peer-output decompose kernel for these parameters" : "no decompose kernel for this width");

@@ -321,6 +321,149 @@ k_crt_tc(TcArgs a, int n, const uint64_t *__restrict__ rhat, unsigned k, GqPtrs4
   }
 }
 
+
+// V = lo4 + hi4 2^32 (lo4, hi4 < 2^47: V < 2^79) -> canonical residue mod p = 2^s + cc, s = 32 + s32 in 33..59,
+// cc < 2^min(s - 31, 28): 2^s == -cc, so with V = Vh 2^s + Vl and t = cc Vh = th 2^s + tl (t < 2^48)
+//   V == Vl - tl + cc th,   r = Vl + p - tl + cc th  in (0, 2p + 2^31)      (the fold of k_decompose28, gq_crt.cu)
+GQ_DEV uint64_t fold_pm(uint64_t lo4, uint64_t hi4, uint64_t p, uint32_t cc, uint32_t s32) {
+  const uint32_t m1 = (1u << s32) - 1;
+  const uint64_t mid = (lo4 >> 32) + (uint32_t)hi4;           // limb 1 with its carry: below 2^33
+  const uint32_t v0 = (uint32_t)lo4, v1 = (uint32_t)mid, v2 = (uint32_t)(hi4 >> 32) + (uint32_t)(mid >> 32);
+#if defined(__CUDA_ARCH__)
+  const uint32_t vh_lo = __funnelshift_r(v1, v2, s32);
+#else
+  const uint32_t vh_lo = (uint32_t)(((((uint64_t)v2) << 32) | v1) >> s32);
+#endif
+  const uint32_t vh_hi = v2 >> s32;                           // Vh < 2^46; vh_hi * cc < 2^16
+  const uint64_t tt = gq_mad_wide(vh_lo, cc, (uint64_t)(vh_hi * cc) << 32);
+  const uint32_t th = (uint32_t)(tt >> 32) >> s32;
+  const uint64_t tl = tt & ((((uint64_t)m1) << 32) | 0xffffffffu);
+  const uint64_t vl = (((uint64_t)(v1 & m1)) << 32) | v0;
+  uint64_t r = gq_mad_wide(th, cc, vl + p - tl);
+  r = (r >= 2 * p) ? r - 2 * p : r;
+  r = (r >= p) ? r - p : r;
+  return r;
+}
+
+// ---- K4 (poly_mpi2rns, src/poly.c:96-107 over rns_decompose, src/rns.c:37-48) as the same kind of contraction --------
+// residue_d = sum_{w, a} byte_a(x_w) * (2^(64w + 8a) mod p_d)  -  sign * (2^(64W) mod p_d)        (mod p_d)
+// K = the 8 bytes of each of the W <= 7 coefficient words (word slot 7 carries the sign as a 0/1 byte against the
+// constant p - 2^(64W) mod p), N = the 8 bytes of the table entry of each limb: per group of four limbs two k-steps x
+// four n-tiles; column 2t + e of n-tile v is byte 2v + e of LIMB base + t, so lane (g, t) ends with all eight byte
+// columns of (row g, limb base + t) and (row g + 8, limb base + t): the recombination is thread-local, then one
+// pseudo-Mersenne fold (every prime 2^s + c, the shape pm_ok checks; same fold as k_decompose28 of gq_crt.cu).
+// Table: per limb 72 64-bit words (64 used: [k-chunk 2][n-tile 4][e 2][t 4]; the stride of 576 bytes keeps the four
+// limbs of a B fragment in different banks).
+#define GQ_DTC_STRIDE 72
+template <bool PEER>
+__global__ void __launch_bounds__(128)
+k_decompose_tc(const unsigned long long *__restrict__ tab, const GqPrime *__restrict__ primes, int n, int limb0,
+               int nlimbs, int W, GqPtrs4 in, uint64_t *__restrict__ out, GqPeerOut po) {
+  GQ_DYN_SMEM(unsigned long long, sT);                // [groups * 4][72], then the primes
+  const int groups = (nlimbs + 3) / 4;
+  unsigned long long *sP = sT + (size_t)groups * 4 * GQ_DTC_STRIDE, *sQ = sP + groups * 4;
+  {
+    const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(tab + (size_t)limb0 * GQ_DTC_STRIDE);
+    ulonglong2 *dst2 = reinterpret_cast<ulonglong2 *>(sT);
+    const int pieces = nlimbs * (GQ_DTC_STRIDE / 2), all = groups * 4 * (GQ_DTC_STRIDE / 2);
+    for (int j0 = threadIdx.x; j0 < all; j0 += 4 * 128) {
+      ulonglong2 tmp[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int j = j0 + u * 128;
+        tmp[u] = make_ulonglong2(0, 0);
+        if (j < pieces) tmp[u] = src[j];
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) if (j0 + u * 128 < all) dst2[j0 + u * 128] = tmp[u];
+    }
+    for (int d = threadIdx.x; d < groups * 4; d += blockDim.x) {
+      const uint64_t pd = d < nlimbs ? primes[limb0 + d].p : 0;
+      const unsigned sh = d < nlimbs ? primes[limb0 + d].bits - 1 : 33;
+      sP[d] = pd;
+      sQ[d] = ((unsigned long long)(sh - 32) << 32) | (uint32_t)(pd - (((uint64_t)1) << sh));
+    }
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3, qb = lane & ~3;
+  const int b = blockIdx.y;
+  const uint64_t *src = (b == 0) ? in.p[0] : (b == 1) ? in.p[1] : (b == 2) ? in.p[2] : in.p[3];
+  uint64_t *dst = out + (size_t)b * nlimbs * n;
+  const int stride = gridDim.x * 64;
+  const int cs = (W - 1) >> 2, ts = (W - 1) & 3;      // the top word lives in chunk cs, quad lane ts
+  // my B-fragment words: limb base + (g >> 1), e = g & 1, k-slot t
+  const unsigned long long *myB = sT + (size_t)(g >> 1) * GQ_DTC_STRIDE + (g & 1) * 4 + t;
+  uint64_t X[2][2];
+  {
+    const int i0 = (blockIdx.x * 4 + warp) * 16;
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+      const int w = 4 * c + t;
+      X[c][0] = (w < W && i0 + g < n) ? src[(size_t)w * n + i0 + g] : 0;
+      X[c][1] = (w < W && i0 + g + 8 < n) ? src[(size_t)w * n + i0 + g + 8] : 0;
+    }
+  }
+  for (int i0 = (blockIdx.x * 4 + warp) * 16; i0 < n; i0 += stride) {
+    uint32_t A[2][4];
+    {
+      const uint64_t top0 = cs ? X[1][0] : X[0][0], top1 = cs ? X[1][1] : X[0][1];
+      const uint32_t s0 = __shfl_sync(0xffffffffu, (uint32_t)(top0 >> 63), qb + ts);
+      const uint32_t s1 = __shfl_sync(0xffffffffu, (uint32_t)(top1 >> 63), qb + ts);
+#pragma unroll
+      for (int c = 0; c < 2; c++) {
+        A[c][0] = (uint32_t)X[c][0]; A[c][1] = (uint32_t)X[c][1];
+        A[c][2] = (uint32_t)(X[c][0] >> 32); A[c][3] = (uint32_t)(X[c][1] >> 32);
+      }
+      if (t == 3) { A[1][0] = s0; A[1][1] = s1; A[1][2] = 0; A[1][3] = 0; }      // word slot 7: the sign
+    }
+    {                                                 // the next step's words travel while this step's limbs are folded
+      const int j0 = i0 + stride;
+#pragma unroll
+      for (int c = 0; c < 2; c++) {
+        const int w = 4 * c + t;
+        X[c][0] = (w < W && j0 + g < n) ? src[(size_t)w * n + j0 + g] : 0;
+        X[c][1] = (w < W && j0 + g + 8 < n) ? src[(size_t)w * n + j0 + g + 8] : 0;
+      }
+    }
+    const bool live0 = i0 + g < n, live1 = i0 + g + 8 < n;
+#pragma unroll 2
+    for (int G = 0; G < groups; G++) {
+      int acc[4][4];
+#pragma unroll
+      for (int v = 0; v < 4; v++)
+#pragma unroll
+        for (int e = 0; e < 4; e++) acc[v][e] = 0;
+      const unsigned long long *gb = myB + (size_t)G * 4 * GQ_DTC_STRIDE;
+#pragma unroll
+      for (int c = 0; c < 2; c++)
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+          const unsigned long long bb = gb[(c * 4 + v) * 8];
+          mma_u8(acc[v], A[c], (uint32_t)bb, (uint32_t)(bb >> 32));
+        }
+      const int d = 4 * G + t;
+      const uint64_t p = sP[d];
+      if (d < nlimbs) {
+        const uint64_t pq = sQ[d];
+        const uint32_t cc = (uint32_t)pq, s32 = (uint32_t)(pq >> 32);       // p = 2^(32 + s32) + cc
+#pragma unroll
+        for (int row = 0; row < 2; row++) {
+          const int e0 = 2 * row;
+          const uint64_t lo4 = pack4(acc[0][e0], acc[0][e0 + 1], acc[1][e0], acc[1][e0 + 1]);     // bytes 0..3: < 2^47
+          const uint64_t hi4 = pack4(acc[2][e0], acc[2][e0 + 1], acc[3][e0], acc[3][e0 + 1]);     // bytes 4..7
+          const uint64_t r = fold_pm(lo4, hi4, p, cc, s32);
+          const int i = i0 + g + 8 * row;
+          if (row ? live1 : live0) {
+            if (PEER) *gq_peer_c2l(po, b, limb0 + d, i) = r;
+            else dst[(size_t)d * n + i] = r;
+          }
+        }
+      }
+    }
+  }
+  if (PEER) gq_peer_signal(po);
+}
+
 }  // namespace
 
 // Words (32-bit) of the table for `slots` limb slots (a multiple of 4): fragments, then the 8 words of the multiplier.
@@ -421,5 +564,59 @@ int gq_launch_ks_epilogue_tc(const GqCrtBasis &B, const GqCrtBasis &BP, const ui
   if (smem > 48 * 1024) return -1;
   if (a.ych <= 4) GQ_TC_LAUNCH(true, 4, a, n, chat, k, add, Wadd, out, Wout, fix, fix + 4, rs_j, w0);
   else GQ_TC_LAUNCH(true, 6, a, n, chat, k, add, Wadd, out, Wout, fix, fix + 4, rs_j, w0);
+  return 1;
+}
+
+// ---- K4 host side: the per-limb B fragments for coefficients of W <= 7 words, nprimes x GQ_DTC_STRIDE 64-bit words
+size_t gq_dec_tc_table_words(int nprimes) { return (size_t)nprimes * GQ_DTC_STRIDE; }
+void gq_dec_tc_table(unsigned long long *tab, int nprimes, const uint64_t *p, int W) {
+  for (int d = 0; d < nprimes; d++) {
+    uint64_t U[8][8];                                // U[w][a] = 2^(64w + 8a) mod p; slot 7: the sign constant
+    uint64_t x = 1 % p[d];
+    for (int w = 0; w < 8; w++)
+      for (int a = 0; a < 8; a++) {
+        U[w][a] = x;
+        x = (uint64_t)(((gq_u128)x * 256u) % p[d]);
+      }
+    const uint64_t tw = U[W < 8 ? W : 7][0];         // 2^(64W) mod p
+    for (int a = 0; a < 8; a++) U[7][a] = 0;
+    U[7][0] = tw ? p[d] - tw : 0;
+    for (int w = W; w < 7; w++)
+      for (int a = 0; a < 8; a++) U[w][a] = 0;
+    unsigned long long *T = tab + (size_t)d * GQ_DTC_STRIDE;
+    for (int j = 0; j < GQ_DTC_STRIDE; j++) T[j] = 0;
+    for (int c = 0; c < 2; c++)
+      for (int v = 0; v < 4; v++)
+        for (int e = 0; e < 2; e++)
+          for (int t = 0; t < 4; t++) {
+            const int w = 4 * c + t, j = 2 * v + e;  // word slot, output byte
+            uint32_t reg[2] = {0, 0};
+            for (int half = 0; half < 2; half++)
+              for (int kb = 0; kb < 4; kb++)
+                reg[half] |= (uint32_t)((U[w][4 * half + kb] >> (8 * j)) & 0xff) << (8 * kb);
+            T[((c * 4 + v) * 2 + e) * 4 + t] = ((unsigned long long)reg[1] << 32) | reg[0];
+          }
+  }
+}
+
+// Returns 1, or -1 when this form does not apply (the caller uses the integer kernels)
+int gq_launch_decompose_tc(const unsigned long long *tab, const GqPrime *primes, int n, int limb0, int nlimbs,
+                           const GqPtrs4 &in, int W, uint64_t *out, int npolys, cudaStream_t st, const GqPeerOut *po) {
+  if (!tab || W < 1 || W > 7 || nlimbs < 1 || npolys < 1 || npolys > 4) return -1;
+  const int groups = (nlimbs + 3) / 4;
+  const size_t smem = (size_t)groups * 4 * (GQ_DTC_STRIDE + 2) * 8;
+  if (smem > 48 * 1024) return -1;
+  int gx = (n + 63) / 64, cap = (GQ_NUM_SMS * 8) / npolys;
+  if (gx > cap) gx = cap;
+  if (gx < 1) gx = 1;
+  const dim3 grid(gx, npolys), block(128);
+  const GqPeerOut none = GqPeerOut();
+#ifdef GQ_EMULATE
+  if (po) gq_emul::launch_dyn(grid, block, smem, [&]() { k_decompose_tc<true>(tab, primes, n, limb0, nlimbs, W, in, out, *po); });
+  else gq_emul::launch_dyn(grid, block, smem, [&]() { k_decompose_tc<false>(tab, primes, n, limb0, nlimbs, W, in, out, none); });
+#else
+  if (po) k_decompose_tc<true><<<grid, block, smem, st>>>(tab, primes, n, limb0, nlimbs, W, in, out, *po);
+  else k_decompose_tc<false><<<grid, block, smem, st>>>(tab, primes, n, limb0, nlimbs, W, in, out, none);
+#endif
   return 1;
 }

@@ -59,6 +59,11 @@ void gq_crt_tc_table(uint32_t *tab, int slots, const uint64_t *K, const uint64_t
 int gq_launch_reconstruct_tc(const GqCrtBasis &B, const uint32_t *tab, int n, const uint64_t *rhat, unsigned k,
                              const GqPtrs4 &out, int Wout, int npolys, cudaStream_t st, int *fix, unsigned rs_j,
                              const GqWaitIn *wt);
+// K4 on the tensor cores: per-limb B fragments (coefficients of W <= 7 words, pseudo-Mersenne primes)
+size_t gq_dec_tc_table_words(int nprimes);
+void gq_dec_tc_table(unsigned long long *tab, int nprimes, const uint64_t *p, int W);
+int gq_launch_decompose_tc(const unsigned long long *tab, const GqPrime *primes, int n, int limb0, int nlimbs,
+                           const GqPtrs4 &in, int W, uint64_t *out, int npolys, cudaStream_t st, const GqPeerOut *po);
 int gq_launch_ks_epilogue_tc(const GqCrtBasis &B, const GqCrtBasis &BP, const uint32_t *tab, const GqPrime *primes,
                              const ulonglong2 *ratio, int n, const uint64_t *chat, unsigned k, const GqPtrs4 &add,
                              int Wadd, const GqPtrs4 &out, int Wout, int npolys, cudaStream_t st, int *fix,
