@@ -214,6 +214,7 @@ static int build_prescale(gq_ctx *c) {
 }
 
 // ------------------------------------------------------------------------------- create
+static void tc_prebuild(gq_ctx *c);
 extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, unsigned q_words,
                              unsigned slots, uint64_t Delta, unsigned logp, unsigned logqub,
                              int device, const uint64_t *primes_in, const uint64_t *const *zetas_in,
@@ -415,6 +416,7 @@ extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, un
     c->W = (c->q.bits() + 63) / 64;
   }
   if (build_prescale(c)) { gq_ctx_destroy(c); return 1; }
+  tc_prebuild(c);
   *out = c;
   return 0;
 }
@@ -891,6 +893,22 @@ static const uint32_t *tc_table_ks(gq_ctx *c, unsigned D2, unsigned k) {
   hb.P.store(lo, 8);
   mul_lo8(cw, lo, pinv);                           // PQ * P^-1 = Q
   return tc_upload(root, key, ys + zs, K, u, cw);
+}
+
+// The tables of the tensor-core kernels for every basis / level the HE entry points use, built with the context so
+// that no later call allocates or synchronises for them (a first use inside a stream capture would fail otherwise).
+// Best effort: a table that cannot be built leaves that shape on the integer kernels.
+static void tc_prebuild(gq_ctx *c) {
+  if (c->parent || !c->fast_crt || getenv("GPQHE_B200_NO_TC_CRT")) return;
+  for (unsigned D = 1; D <= c->dimub; D++)
+    if (c->basis[D - 1].fin_s) tc_table(c, D, 8);
+  if (!c->has_he) return;
+  for (unsigned l = 0; l <= c->L; l++) {
+    const unsigned D2 = dim_ks(c, l);
+    if (D2 <= c->dimub && c->basis[D2 - 1].ratio && c->qmod[l].dev.is_pow2 && c->qmod[l].dev.k >= 1 && c->qmod[l].dev.k <= 512)
+      tc_table_ks(c, D2, c->qmod[l].dev.k);
+  }
+  if (c->W <= 7) dec_tc_table(c, c->W);
 }
 
 // rs_j > 0: he_rs fused behind the CRT (power-of-two q and Delta; the caller checks with rs_fusable)
