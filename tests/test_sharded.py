@@ -183,6 +183,21 @@ def test_p2p_plan_fused_exchange_emulated(emul_lib, G, monkeypatch):
     _loopback_case(emul_lib, 13, 1 << 120, 1 << 40, 120, G, "cpu", expect_fused=False)
 
 
+@pytest.mark.parametrize("G,logn,fused", [(2, 6, False), (2, 13, True)])
+def test_p2p_plan_plain_and_prescaled_exchanges_emulated(emul_lib, G, logn, fused, monkeypatch):
+    """the limb -> coefficient exchanges carry residues pre-scaled for the CRT (tensor-core CRT stages) by default and
+    plain residues with GPQHE_B200_SHARDED_PLAIN=1: both forms give the bits of the single-GPU call / the oracle"""
+    import gpqhe_b200 as g
+    ctx = g.HeContext(logn, 1 << 120, 4, 1 << 40, lib_path=emul_lib, logqub=120)
+    D1, D2 = ctx.dims(ctx.L)
+    assert ctx._lib.gq_stage_prescale_ok(ctx._h, D1, ctx.L, 0) == 1 and ctx._lib.gq_stage_prescale_ok(ctx._h, D2, ctx.L, 1) == 1
+    assert ctx._lib.gq_stage_prescale_ok(ctx._h, D2 - 1, ctx.L, 1) == 0      # not the key-switch basis of this level
+    ctx.close()
+    _loopback_case(emul_lib, logn, 1 << 120, 1 << 40, 120, G, "cpu", expect_fused=fused)
+    monkeypatch.setenv("GPQHE_B200_SHARDED_PLAIN", "1")
+    _loopback_case(emul_lib, logn, 1 << 120, 1 << 40, 120, G, "cpu", expect_fused=fused)
+
+
 def test_p2p_timeout_is_sticky_and_poisons_peers(emul_lib):
     """A rank whose wait timed out (error flag set) must not let its peers consume its half-written slab: it signals
     a poison epoch, the peers' waits turn it into their own error flag, and run(check=True) raises on every rank."""
