@@ -2076,6 +2076,9 @@ static int to_peer_out(const gq_ctx *c, const gq_p2p_xchg *x, unsigned nloc, GqP
   }
   for (unsigned s = 0; s <= GQ_P2P_MAX_RANKS; s++) po->dst.off[s] = x->off[s <= x->G ? s : x->G];
   po->G = (int)x->G; po->me = (int)x->me; po->nloc = (int)nloc; po->n = (int)c->n; po->D = (int)x->D;
+  if (nloc & (nloc - 1)) GQ_FAIL("coefficient slice is not a power of two");
+  po->lg_nloc = 0;
+  while ((1u << po->lg_nloc) < nloc) po->lg_nloc++;
   po->slot = (int)x->slot; po->epoch = x->epoch_dev; po->err = x->err_dev; po->ticket = x->ticket_dev;
   return 0;
 }

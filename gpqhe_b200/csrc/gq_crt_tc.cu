@@ -362,6 +362,7 @@ k_decompose_tc(const unsigned long long *__restrict__ tab, const GqPrime *__rest
   GQ_DYN_SMEM(unsigned long long, sT);                // [groups * 4][72], then the primes
   const int groups = (nlimbs + 3) / 4;
   unsigned long long *sP = sT + (size_t)groups * 4 * GQ_DTC_STRIDE, *sQ = sP + groups * 4;
+  uint64_t **sDst = reinterpret_cast<uint64_t **>(sQ + groups * 4);     // PEER: where limb d of my slice goes
   {
     const ulonglong2 *src = reinterpret_cast<const ulonglong2 *>(tab + (size_t)limb0 * GQ_DTC_STRIDE);
     ulonglong2 *dst2 = reinterpret_cast<ulonglong2 *>(sT);
@@ -382,6 +383,7 @@ k_decompose_tc(const unsigned long long *__restrict__ tab, const GqPrime *__rest
       const unsigned sh = d < nlimbs ? primes[limb0 + d].bits - 1 : 33;
       sP[d] = pd;
       sQ[d] = ((unsigned long long)(sh - 32) << 32) | (uint32_t)(pd - (((uint64_t)1) << sh));
+      if (PEER) sDst[d] = d < nlimbs ? gq_peer_c2l(po, blockIdx.y, limb0 + d, 0) : nullptr;
     }
   }
   __syncthreads();
@@ -454,7 +456,7 @@ k_decompose_tc(const unsigned long long *__restrict__ tab, const GqPrime *__rest
           const uint64_t r = fold_pm(lo4, hi4, p, cc, s32);
           const int i = i0 + g + 8 * row;
           if (row ? live1 : live0) {
-            if (PEER) *gq_peer_c2l(po, b, limb0 + d, i) = r;
+            if (PEER) sDst[d][i] = r;
             else dst[(size_t)d * n + i] = r;
           }
         }
@@ -604,7 +606,7 @@ int gq_launch_decompose_tc(const unsigned long long *tab, const GqPrime *primes,
                            const GqPtrs4 &in, int W, uint64_t *out, int npolys, cudaStream_t st, const GqPeerOut *po) {
   if (!tab || W < 1 || W > 7 || nlimbs < 1 || npolys < 1 || npolys > 4) return -1;
   const int groups = (nlimbs + 3) / 4;
-  const size_t smem = (size_t)groups * 4 * (GQ_DTC_STRIDE + 2) * 8;
+  const size_t smem = (size_t)groups * 4 * (GQ_DTC_STRIDE + 3) * 8;
   if (smem > 48 * 1024) return -1;
   int gx = (n + 63) / 64, cap = (GQ_NUM_SMS * 8) / npolys;
   if (gx > cap) gx = cap;

@@ -390,11 +390,13 @@ __global__ void __launch_bounds__(256, GQ_STRIDED_MIN_CTAS)
 k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs, GqPeerOut po) {
   constexpr int R = 1 << SA;
   __shared__ ulonglong2 stw[R];
+  __shared__ uint64_t *sbase[GQ_P2P_MAX_RANKS];
   const int cols = tb.n >> SA;
   const int col = blockIdx.x * blockDim.x + threadIdx.x;
   const int m = blockIdx.y;
   const int d = limb0 + m % nlimbs;
   if (threadIdx.x < R) stw[threadIdx.x] = tb.tw_inv[(size_t)d * tb.n + threadIdx.x];
+  if (PEER) gq_peer_bases(po, sbase);
   __syncthreads();
   const bool live = col < cols;
   if (!PEER && !live) return;
@@ -438,8 +440,9 @@ k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
   }
   if (PEER) {
     if (live) {
+      const size_t row = (size_t)(m / nlimbs) * po.D + limb0 + m % nlimbs;
 #pragma unroll
-      for (int r = 0; r < R; r++) *gq_peer_l2c(po, m / nlimbs, m % nlimbs, col + r * cols, limb0) = v[r];
+      for (int r = 0; r < R; r++) *gq_peer_l2c_sb(po, sbase, row, col + r * cols) = v[r];
     }
     gq_peer_signal(po);
   } else {

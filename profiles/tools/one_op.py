@@ -32,6 +32,18 @@ def op():
     assert rc == 0, lib.gq_last_error()
 
 
+if "--p2p" in sys.argv:          # the peer-to-peer sharded plan with ONE virtual rank (exchanges fused into the kernels
+    from gpqhe_b200.sharded import P2PPlan      # unless GPQHE_B200_P2P_UNFUSED=1): the same launches a rank of N issues
+    ext = torch.cuda.ExternalStream(lib.gq_ctx_stream(h), device=dev)
+    with torch.cuda.stream(ext):
+        plan = P2PPlan.loopback(ctx, 1, L, evk, rescale=True, device=dev)[0]
+        for k in range(4):
+            plan.inp[k].copy_(inp[k])
+
+    def op():
+        with torch.cuda.stream(ext):
+            P2PPlan.run_lockstep([plan])
+
 for _ in range(3):
     op()
 ctx.sync()
