@@ -32,6 +32,27 @@ def op():
     assert rc == 0, lib.gq_last_error()
 
 
+if "--gemv" in sys.argv:         # configs[3]: he_gemv with slots = 16 (4 x 4 baby-step / giant-step), synthetic diagonals
+    import ctypes as C
+    import math
+    NROT = 16
+    rks = [ctx.genevk(bench.synth_evk(rng, ctx.primes, n, ctx.dimevk), bench.synth_evk(rng, ctx.primes, n, ctx.dimevk))
+           for _ in range(NROT)]
+    gdim = int((bench.LOGQ + 1 + math.log2(float(1 << bench.LOGDELTA)) + bench.LOGN) / 59 + 1)
+    gpts = torch.zeros((NROT, W, n), dtype=torch.int64, device=dev)
+    gpts[:, 0, :].random_(-(1 << bench.LOGDELTA), 1 << bench.LOGDELTA)
+    gpts[:, 1:, :] = (gpts[:, :1, :] >> 63)
+    VP = C.c_void_p * NROT
+    ptsv = VP(*[gpts.data_ptr() + k * poly for k in range(NROT)])
+    keys = VP(*[rk._h for rk in rks])
+    assert lib.gq_ctx_set_plaintext_bits(h, bench.LOGDELTA + 1) == 0
+    ctx.set_lanes(3)
+
+    def op():
+        b = inp.data_ptr()
+        rc = lib.gq_he_gemv_dev(h, L, 4, 4, gdim, out.data_ptr(), out.data_ptr() + poly, b, b + poly, ptsv, keys, None)
+        assert rc == 0, lib.gq_last_error()
+
 if "--p2p" in sys.argv:          # the peer-to-peer sharded plan with ONE virtual rank (exchanges fused into the kernels
     from gpqhe_b200.sharded import P2PPlan      # unless GPQHE_B200_P2P_UNFUSED=1): the same launches a rank of N issues
     ext = torch.cuda.ExternalStream(lib.gq_ctx_stream(h), device=dev)
