@@ -654,7 +654,7 @@ def check_fused_rescale_ties(lib_path, logn=5, q=1 << 438, Delta=1 << 50, logqub
         ctx.close()
 
 
-def check_fused_vs_separate(lib_path, logn, q=1 << 438, Delta=1 << 50, logqub=438, seed=77, level=None):
+def check_fused_vs_separate(lib_path, logn, q=1 << 438, Delta=1 << 50, logqub=438, seed=77, level=None, short=False):
     """The pointwise stage folded into the load of the inverse NTT (gq_ntt_lazy.cu, GQ_INV_*) and the CRT
     pre-multiplication folded into its final scaling, against the separate-kernel pipeline of the same library
     (GPQHE_B200_NO_FUSED_INV / GPQHE_B200_NO_PRESCALE, which the oracle pins at small sizes and the GPU tier at
@@ -682,14 +682,18 @@ def check_fused_vs_separate(lib_path, logn, q=1 << 438, Delta=1 << 50, logqub=43
                 b = g.HeCt(l, _rand_big(rr, n, W, bits), _rand_big(rr, n, W, bits), float(Delta), 1.0)
                 pt = g.HePt(_rand_big(rr, n, W, Delta.bit_length()), nu=float(Delta))
                 out = []
-                m = ctx.he_mul(a, b, k1); out += [m.c0, m.c1]
                 m = ctx.he_mul_rs(a, b, k1); out += [m.c0, m.c1]
                 m = ctx.he_mulpt(a, pt); out += [m.c0, m.c1]
                 m = ctx.he_rot(a, 3, {3: k2}); out += [m.c0, m.c1]
-                m = ctx.he_conj(b, k2); out += [m.c0, m.c1]
-                for m in ctx.he_rot_hoisted(a, [0, 1, 5], {0: k1, 1: k2, 5: k1}):
-                    out += [m.c0, m.c1]
-                out.append(ctx.poly_mul(a.c0, b.c1, ctx.dim, ctx.ql[l]))
+                if not short:            # short: one op per loader mode of the two-kernel transforms (CPU tier, n = 2^13)
+                    m = ctx.he_mul(a, b, k1); out += [m.c0, m.c1]
+                    m = ctx.he_conj(b, k2); out += [m.c0, m.c1]
+                    for m in ctx.he_rot_hoisted(a, [0, 1, 5], {0: k1, 1: k2, 5: k1}):
+                        out += [m.c0, m.c1]
+                    out.append(ctx.poly_mul(a.c0, b.c1, ctx.dim, ctx.ql[l]))
+                else:
+                    for m in ctx.he_rot_hoisted(a, [1], {1: k2}):
+                        out += [m.c0, m.c1]
                 res.append(out)
             finally:
                 ctx.close()

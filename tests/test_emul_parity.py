@@ -185,7 +185,7 @@ def test_fused_rescale_tie_rule(emul_lib):
 @pytest.mark.parametrize("logn,level", [(13, 2), (9, None)])
 def test_fused_inverse_equals_separate_kernels(emul_lib, logn, level):
     """two-kernel transforms (n = 2^13) and one-tile transforms: every loader mode of the fused inverse NTT"""
-    pc.check_fused_vs_separate(emul_lib, logn, level=level)
+    pc.check_fused_vs_separate(emul_lib, logn, level=level, short=(logn > 12))
 
 
 @pytest.mark.parametrize("logq", [500, 512, 65])

@@ -174,16 +174,19 @@ def test_p2p_plan_loopback_emulated(emul_lib, G, logn, logq, logDelta):
     _loopback_case(emul_lib, logn, 1 << logq, 1 << logDelta, logq, G, "cpu")
 
 
-@pytest.mark.parametrize("G", [2, 4])
+@pytest.mark.parametrize("G", [2])
 def test_p2p_plan_fused_exchange_emulated(emul_lib, G, monkeypatch):
     """n = 2^13: the exchanges run inside the producing / consuming kernels (gq_p2p.h); same bits as one GPU, and
     the same bits with the fusion switched off"""
     _loopback_case(emul_lib, 13, 1 << 120, 1 << 40, 120, G, "cpu", expect_fused=True)
+    monkeypatch.setenv("GPQHE_B200_SHARDED_PLAIN", "1")          # plain residues through the fused exchange
+    _loopback_case(emul_lib, 13, 1 << 120, 1 << 40, 120, G, "cpu", expect_fused=True)
+    monkeypatch.delenv("GPQHE_B200_SHARDED_PLAIN")
     monkeypatch.setenv("GPQHE_B200_P2P_UNFUSED", "1")
     _loopback_case(emul_lib, 13, 1 << 120, 1 << 40, 120, G, "cpu", expect_fused=False)
 
 
-@pytest.mark.parametrize("G,logn,fused", [(2, 6, False), (2, 13, True)])
+@pytest.mark.parametrize("G,logn,fused", [(2, 6, False)])
 def test_p2p_plan_plain_and_prescaled_exchanges_emulated(emul_lib, G, logn, fused, monkeypatch):
     """the limb -> coefficient exchanges carry residues pre-scaled for the CRT (tensor-core CRT stages) by default and
     plain residues with GPQHE_B200_SHARDED_PLAIN=1: both forms give the bits of the single-GPU call / the oracle"""
