@@ -214,6 +214,9 @@ static int build_prescale(gq_ctx *c) {
 }
 
 // ------------------------------------------------------------------------------- create
+#ifndef GQ_EMULATE
+int gq_pdl_enabled = getenv("GPQHE_B200_NO_PDL") ? 0 : 1;      // programmatic dependent launch (gq_platform.h)
+#endif
 static void tc_prebuild(gq_ctx *c);
 extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, unsigned q_words,
                              unsigned slots, uint64_t Delta, unsigned logp, unsigned logqub,

@@ -174,6 +174,8 @@ __global__ void __launch_bounds__(128)
 k_reconstruct(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
               const uint64_t *__restrict__ rhat, GqModulus q, GqPtrs4 out, int Wout,
               int *fix_count, const int *__restrict__ fix_list, unsigned rs_j, bool pre) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   __shared__ CrtShared<WT> S;
   if (fix_list) {
     const int cnt = *fix_count;
@@ -265,6 +267,8 @@ k_ks_epilogue(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pinv,
               const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
               unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout,
               int *fix_count, const int *__restrict__ fix_list, unsigned rs_j, const ulonglong2 *ratio) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   __shared__ CrtShared<WT> S;
   __shared__ CrtShared<WP> SP;
   __shared__ uint64_t sPinv[WP];
@@ -293,6 +297,8 @@ k_ks_epilogue_general(GqCrtBasis B, const uint64_t *__restrict__ Pw, int nP,
                       const uint64_t *__restrict__ Phw, const GqPrime *__restrict__ primes, int n,
                       const uint64_t *__restrict__ chat, GqModulus q, GqPtrs4 add, int Wadd,
                       GqPtrs4 out, int Wout) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   __shared__ CrtShared<WT> S;
   crt_stage<WT>(S, B, primes);
   __syncthreads();
@@ -444,6 +450,8 @@ __global__ void __launch_bounds__(256)
 k_reconstruct_fast(GqCrtBasis B, const GqPrime *__restrict__ primes, int n,
                    const uint64_t *__restrict__ rhat, unsigned k, GqPtrs4 out, int Wout,
                    int *fix_count, int *fix_list, unsigned rs_j, GqWaitIn wt) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   __shared__ CrtSharedLow<W> S;
   crt_low_stage<W>(S, B, primes);
   gq_peer_wait(wt);                   // sharded pipeline: rhat is a receive slab (gq_p2p.h); no-op otherwise
@@ -469,6 +477,8 @@ k_ks_epilogue_fast(GqCrtBasis B, GqCrtBasis BP, const uint64_t *__restrict__ Pin
                    const GqPrime *__restrict__ primes, int n, const uint64_t *__restrict__ chat,
                    unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout, int *fix_count, int *fix_list,
                    unsigned rs_j, const ulonglong2 *ratio, GqWaitIn wt) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   __shared__ CrtSharedLow<WQ> S;
   __shared__ CrtShared<WP> SP;
   __shared__ uint64_t sPinv[WQ];
@@ -541,6 +551,8 @@ GQ_DEV uint64_t reduce128(uint64_t lo, uint64_t hi, const GqPrime &P, uint64_t T
 template <int W>
 __global__ void __launch_bounds__(256)
 k_decompose32(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *__restrict__ out) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   __shared__ uint64_t sU[GQ_MAX_PRIMES * 2 * W];
   __shared__ uint64_t sC[GQ_MAX_PRIMES * 6];      // p, T1, T1sh, one_sh, TW, pad
   for (int j = threadIdx.x; j < nlimbs * 2 * W; j += blockDim.x)
@@ -605,6 +617,8 @@ k_decompose32(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t
 template <int W, bool PM, bool PEER>
 __global__ void __launch_bounds__(256)
 k_decompose28(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *__restrict__ out, GqPeerOut po) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   constexpr int J = (64 * W + 27) / 28;
   static_assert(J <= GQ_DEC28, "at most 16 digits");
   __shared__ uint64_t sU[GQ_MAX_PRIMES * J];
@@ -678,6 +692,8 @@ k_decompose28(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t
 template <int W>
 __global__ void __launch_bounds__(256)
 k_decompose(GqDecTables dt, int n, int limb0, int nlimbs, GqPtrs4 in, uint64_t *__restrict__ out) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int b = blockIdx.y;

@@ -180,6 +180,7 @@ template <bool KS, int RCH>
 __global__ void __launch_bounds__(128, 4)
 k_crt_tc(TcArgs a, int n, const uint64_t *__restrict__ rhat, unsigned k, GqPtrs4 add, int Wadd, GqPtrs4 out, int Wout,
          int *fix_count, int *fix_list, unsigned rs_j, GqWaitIn wt) {
+  GQ_PDL_TRIGGER();
   constexpr int NT = 10;
   GQ_DYN_SMEM(unsigned long long, sfrag);
   {                                                   // 2 560 bytes per chunk: 160 16-byte pieces, loads batched by 5
@@ -194,6 +195,7 @@ k_crt_tc(TcArgs a, int n, const uint64_t *__restrict__ rhat, unsigned k, GqPtrs4
       for (int u = 0; u < 5; u++) if (j0 + u * 128 < pieces) dst2[j0 + u * 128] = tmp[u];
     }
   }
+  GQ_PDL_WAIT();                                      // the table above is constant; the residues are not
   gq_peer_wait(wt);                                   // (ends with the block barrier that also publishes sfrag)
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3, qb = lane & ~3;
@@ -359,6 +361,7 @@ template <bool PEER>
 __global__ void __launch_bounds__(128)
 k_decompose_tc(const unsigned long long *__restrict__ tab, const GqPrime *__restrict__ primes, int n, int limb0,
                int nlimbs, int W, GqPtrs4 in, uint64_t *__restrict__ out, GqPeerOut po) {
+  GQ_PDL_TRIGGER();
   GQ_DYN_SMEM(unsigned long long, sT);                // [groups * 4][72], then the primes
   const int groups = (nlimbs + 3) / 4;
   unsigned long long *sP = sT + (size_t)groups * 4 * GQ_DTC_STRIDE, *sQ = sP + groups * 4;
@@ -386,6 +389,7 @@ k_decompose_tc(const unsigned long long *__restrict__ tab, const GqPrime *__rest
       if (PEER) sDst[d] = d < nlimbs ? gq_peer_c2l(po, blockIdx.y, limb0 + d, 0) : nullptr;
     }
   }
+  GQ_PDL_WAIT();                                      // tables and primes are constants; the coefficients are not
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3, qb = lane & ~3;
   const int b = blockIdx.y;
@@ -513,11 +517,7 @@ static dim3 tc_grid(int n, int npolys) {
   return dim3(gx, npolys);
 }
 
-#ifdef GQ_EMULATE
-#define GQ_TC_LAUNCH(KSV, RV, ...) gq_emul::launch_dyn(grid, block, smem, [&]() { k_crt_tc<KSV, RV>(__VA_ARGS__); })
-#else
-#define GQ_TC_LAUNCH(KSV, RV, ...) k_crt_tc<KSV, RV><<<grid, block, smem, st>>>(__VA_ARGS__)
-#endif
+#define GQ_TC_LAUNCH(KSV, RV, ...) GQ_LAUNCH_DYN((k_crt_tc<KSV, RV>), grid, block, smem, st, __VA_ARGS__)
 
 // K5.  Returns 1 (one launch; the caller follows with the exact list-mode kernel), -1 when this form does not apply.
 int gq_launch_reconstruct_tc(const GqCrtBasis &B, const uint32_t *tab, int n, const uint64_t *rhat, unsigned k,
@@ -613,12 +613,7 @@ int gq_launch_decompose_tc(const unsigned long long *tab, const GqPrime *primes,
   if (gx < 1) gx = 1;
   const dim3 grid(gx, npolys), block(128);
   const GqPeerOut none = GqPeerOut();
-#ifdef GQ_EMULATE
-  if (po) gq_emul::launch_dyn(grid, block, smem, [&]() { k_decompose_tc<true>(tab, primes, n, limb0, nlimbs, W, in, out, *po); });
-  else gq_emul::launch_dyn(grid, block, smem, [&]() { k_decompose_tc<false>(tab, primes, n, limb0, nlimbs, W, in, out, none); });
-#else
-  if (po) k_decompose_tc<true><<<grid, block, smem, st>>>(tab, primes, n, limb0, nlimbs, W, in, out, *po);
-  else k_decompose_tc<false><<<grid, block, smem, st>>>(tab, primes, n, limb0, nlimbs, W, in, out, none);
-#endif
+  if (po) GQ_LAUNCH_DYN((k_decompose_tc<true>), grid, block, smem, st, tab, primes, n, limb0, nlimbs, W, in, out, *po);
+  else GQ_LAUNCH_DYN((k_decompose_tc<false>), grid, block, smem, st, tab, primes, n, limb0, nlimbs, W, in, out, none);
   return 1;
 }

@@ -12,6 +12,8 @@ namespace {
 
 __global__ void __launch_bounds__(256)
 k_rescale_pow2(int n, int W, GqPtrs4 c, unsigned j, unsigned k) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint64_t *x = c.p[blockIdx.y] + i;
@@ -57,6 +59,8 @@ k_rescale_pow2(int n, int W, GqPtrs4 c, unsigned j, unsigned k) {
 // exact slow path: arbitrary Delta (64-bit) and arbitrary q
 __global__ void __launch_bounds__(128)
 k_rescale_general(int n, int W, GqPtrs4 c, uint64_t Delta, GqModulus q) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   uint64_t *x = c.p[blockIdx.y] + i;
@@ -135,6 +139,8 @@ k_rescale_general(int n, int W, GqPtrs4 c, uint64_t Delta, GqModulus q) {
 
 __global__ void __launch_bounds__(256)
 k_automorph(int n, int W, GqPtrs4 out, GqPtrs4 in, uint64_t g) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint64_t kk = ((uint64_t)i * g) & (uint64_t)(2 * n - 1);
@@ -157,6 +163,8 @@ k_automorph(int n, int W, GqPtrs4 out, GqPtrs4 in, uint64_t g) {
 // arithmetic is exact here because 2^k divides 2^(64W).
 __global__ void __launch_bounds__(256)
 k_linear_pow2(int n, int W, GqPtrs4 out, GqPtrs4 a, GqPtrs4 b, int op0, int op1, unsigned k) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int op = blockIdx.y ? op1 : op0;
@@ -199,6 +207,8 @@ k_linear_pow2(int n, int W, GqPtrs4 out, GqPtrs4 a, GqPtrs4 b, int op0, int op1,
 // arbitrary q: exact (W+1)-word signed result, magnitude mod q, then the centring of mpi_smod
 __global__ void __launch_bounds__(128)
 k_linear_general(int n, int W, GqPtrs4 out, GqPtrs4 a, GqPtrs4 b, int op0, int op1, GqModulus q) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int op = blockIdx.y ? op1 : op0;

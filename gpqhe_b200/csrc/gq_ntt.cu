@@ -103,6 +103,8 @@ struct TileCfg {
 template <int LOGT>
 __global__ void __launch_bounds__(TileCfg<LOGT>::NT)
 k_ntt_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   typedef TileCfg<LOGT> C;
   __shared__ uint64_t sm[C::T];
   const int t = threadIdx.x;
@@ -146,6 +148,8 @@ k_ntt_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimb
 template <int LOGT, bool WHOLE>
 __global__ void __launch_bounds__(TileCfg<LOGT>::NT)
 k_ntt_inv_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   typedef TileCfg<LOGT> C;
   __shared__ uint64_t sm[C::T];
   const int t = threadIdx.x;
@@ -189,6 +193,8 @@ k_ntt_inv_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimb
 template <int SA>
 __global__ void __launch_bounds__(256)
 k_ntt_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   constexpr int R = 1 << SA;
   const int cols = tb.n >> SA;
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -221,6 +227,8 @@ k_ntt_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nl
 template <int SA>
 __global__ void __launch_bounds__(256)
 k_ntt_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   constexpr int R = 1 << SA;
   const int cols = tb.n >> SA;
   const int c = blockIdx.x * blockDim.x + threadIdx.x;

@@ -196,6 +196,8 @@ struct TileCfg {
 template <int LOGT, bool PRE>
 __global__ void __launch_bounds__(TileCfg<LOGT>::NT, (TileCfg<LOGT>::NT >= 512 ? 2 : 1))
 k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   typedef TileCfg<LOGT> C;
   __shared__ uint64_t sm[C::T];
   const int t = threadIdx.x;
@@ -299,6 +301,8 @@ GQ_DEV uint64_t inv_load(const InvSrc &S, const GqPM &pm, int n, int logn, int n
 template <int LOGT, bool WHOLE, int MODE>
 __global__ void __launch_bounds__(TileCfg<LOGT>::NT, (TileCfg<LOGT>::NT >= 512 ? 2 : 1))
 k_nttl_inv_tile(GqNttTables tb, InvSrc src, uint64_t *__restrict__ y, int limb0, int nlimbs) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   typedef TileCfg<LOGT> C;
   __shared__ uint64_t sm[C::T];
   const int t = threadIdx.x;
@@ -350,6 +354,8 @@ k_nttl_inv_tile(GqNttTables tb, InvSrc src, uint64_t *__restrict__ y, int limb0,
 template <int SA>
 __global__ void __launch_bounds__(256, GQ_STRIDED_MIN_CTAS)
 k_nttl_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs, GqWaitIn wt) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   constexpr int R = 1 << SA;
   __shared__ ulonglong2 stw[R];
   const int cols = tb.n >> SA;
@@ -388,6 +394,8 @@ k_nttl_fwd_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int n
 template <int SA, bool PEER>
 __global__ void __launch_bounds__(256, GQ_STRIDED_MIN_CTAS)
 k_nttl_inv_strided(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs, GqPeerOut po) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   constexpr int R = 1 << SA;
   __shared__ ulonglong2 stw[R];
   __shared__ uint64_t *sbase[GQ_P2P_MAX_RANKS];

@@ -36,6 +36,8 @@ GQ_DEV void st2(uint64_t *p, ulonglong2 v) { *reinterpret_cast<ulonglong2 *>(p) 
 //   dst_s[(b*Dl_s + d - off[s]) * n + me*nloc + i]
 __global__ void __launch_bounds__(256)
 k_scatter_c2l(GqPeers pr, const uint64_t *__restrict__ src, int P, int D, int nloc, int n, int me, int G) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int half = nloc >> 1;
   const long long total = (long long)P * D * half;
   for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
@@ -56,6 +58,8 @@ k_scatter_c2l(GqPeers pr, const uint64_t *__restrict__ src, int P, int D, int nl
 //   dst_s[(b*D + off[me] + dl) * nloc + j - s*nloc]
 __global__ void __launch_bounds__(256)
 k_scatter_l2c(GqPeers pr, const uint64_t *__restrict__ src, int P, int Dl, int D, int nloc, int n, int me) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int half = n >> 1;
   const long long total = (long long)P * Dl * half;
   for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
@@ -70,7 +74,9 @@ k_scatter_l2c(GqPeers pr, const uint64_t *__restrict__ src, int P, int Dl, int D
 }
 
 // the epoch lives in device memory so that the same (graph-captured) launch works for every op
-__global__ void k_bump(unsigned long long *epoch) { if (threadIdx.x == 0) *epoch += 1; }
+__global__ void k_bump(unsigned long long *epoch) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT(); if (threadIdx.x == 0) *epoch += 1; }
 
 // A rank whose error flag is set (a wait of this or an earlier op timed out: its slab may be half written) does
 // not publish the epoch but a POISON value: it passes every peer's `flag >= epoch` test at once, and k_wait turns it
@@ -79,6 +85,8 @@ __global__ void k_bump(unsigned long long *epoch) { if (threadIdx.x == 0) *epoch
 #define GQ_P2P_POISON (~0ull)
 
 __global__ void k_signal(GqPeers flags, int slot, int G, int me, const unsigned long long *epoch_p, const int *err) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int s = threadIdx.x;
   if (s >= G) return;
   const unsigned long long epoch = (err && *err) ? GQ_P2P_POISON : *epoch_p;
@@ -94,6 +102,8 @@ __global__ void k_signal(GqPeers flags, int slot, int G, int me, const unsigned 
 // consuming kernels are ordered after the flag read on every path, not only across the kernel boundary.
 __global__ void k_wait(const uint64_t *flags, int slot, int G, const unsigned long long *epoch_p, int *err,
                        unsigned long long spin_limit) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int s = threadIdx.x;
   if (s >= G) return;
   if (*err) return;                                       // sticky: fail fast, never wait again

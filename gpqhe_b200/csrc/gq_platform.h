@@ -15,10 +15,45 @@
 #include "cuda_emul.h"   // tests/emul/cuda_emul.h (test infrastructure)
 #define GQ_LAUNCH(kernel, grid, block, stream, ...) \
   ::gq_emul::launch((grid), (block), [&]() { kernel(__VA_ARGS__); })
+#define GQ_LAUNCH_DYN(kernel, grid, block, smem, stream, ...) \
+  ::gq_emul::launch_dyn((grid), (block), (smem), [&]() { kernel(__VA_ARGS__); })
 #else
 #include <cuda_runtime.h>
-#define GQ_LAUNCH(kernel, grid, block, stream, ...) \
-  kernel<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__)
+// Programmatic dependent launch (sm_90+): every kernel of the library starts with gq_pdl_trigger() - its successor in
+// the stream may be scheduled as soon as all of this grid's blocks are resident or done - and calls gq_pdl_wait()
+// before it touches anything a predecessor wrote (or writes anything a predecessor reads): launch latency and the
+// constant-table prologues overlap the tail of the previous kernel instead of following it (one he_mul + he_rs:
+// 296 -> 267 us when replayed from a graph, profiles/tools/graph_op.py; this gets most of that without a graph).
+// gq_pdl_enabled: 1 unless GPQHE_B200_NO_PDL is set (read once, gq_api.cu); GQ_NO_PDL at compile time for libraries
+// whose kernels do not carry the two calls (profiles/probe).
+extern int gq_pdl_enabled;
+template <typename... KA, typename... A>
+static inline void gq_launch_ex(void (*kernel)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A &&...a) {
+#ifndef GQ_NO_PDL
+  if (gq_pdl_enabled) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, kernel, KA(a)...);
+    return;
+  }
+#endif
+  kernel<<<grid, block, smem, stream>>>(KA(a)...);
+}
+#define GQ_LAUNCH(kernel, grid, block, stream, ...) gq_launch_ex(kernel, (grid), (block), 0, (stream), __VA_ARGS__)
+#define GQ_LAUNCH_DYN(kernel, grid, block, smem, stream, ...) gq_launch_ex(kernel, (grid), (block), (smem), (stream), __VA_ARGS__)
+#endif
+
+// device side of the programmatic dependent launch (no-ops under emulation)
+#if defined(__CUDA_ARCH__) && !defined(GQ_NO_PDL)
+#define GQ_PDL_TRIGGER() asm volatile("griddepcontrol.launch_dependents;" ::: "memory")
+#define GQ_PDL_WAIT() asm volatile("griddepcontrol.wait;" ::: "memory")
+#else
+#define GQ_PDL_TRIGGER() ((void)0)
+#define GQ_PDL_WAIT() ((void)0)
 #endif
 
 // dynamic shared memory of a kernel launched with a byte count

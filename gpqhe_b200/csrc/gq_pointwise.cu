@@ -15,6 +15,8 @@ template <bool MUL>
 __global__ void __launch_bounds__(256)
 k_binary(const GqPrime *__restrict__ primes, int n, int limb0, int nlimbs, int npolys_total,
          uint64_t *r, const uint64_t *a, const uint64_t *b) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int half = n >> 1;
   const long long total = (long long)npolys_total * half;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -42,6 +44,8 @@ k_binary(const GqPrime *__restrict__ primes, int n, int limb0, int nlimbs, int n
 __global__ void __launch_bounds__(256)
 k_tensor(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict__ y,
          const uint64_t *__restrict__ x) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int half = n >> 1;
   const long long per = (long long)D * half;
   const size_t stride = (size_t)D * n;
@@ -71,6 +75,8 @@ __global__ void __launch_bounds__(256)
 k_mul_evk(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict__ y,
           const uint64_t *__restrict__ x, const uint64_t *__restrict__ e0,
           const uint64_t *__restrict__ e1) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int half = n >> 1;
   const long long per = (long long)D * half;
   const size_t stride = (size_t)D * n;
@@ -90,6 +96,8 @@ k_mul_evk(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict
 __global__ void __launch_bounds__(256)
 k_mul_pt(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict__ y,
          const uint64_t *__restrict__ x) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   // x[3][D][n] = NTT(c0), NTT(c1), NTT(m);  y[2][D][n] = c0*m, c1*m
   const int half = n >> 1;
   const long long per = (long long)D * half;
@@ -117,6 +125,8 @@ GQ_DEV uint64_t mul2add_pm(uint64_t a, uint64_t b, uint64_t c2, uint64_t d, cons
 __global__ void __launch_bounds__(256)
 k_tensor_pm(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict__ y,
             const uint64_t *__restrict__ x) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int half = n >> 1;
   const long long per = (long long)D * half;
   const size_t stride = (size_t)D * n;
@@ -140,6 +150,8 @@ __global__ void __launch_bounds__(256)
 k_mul_evk_pm(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict__ y,
              const uint64_t *__restrict__ x, const uint64_t *__restrict__ e0,
              const uint64_t *__restrict__ e1) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int half = n >> 1;
   const long long per = (long long)D * half;
   const size_t stride = (size_t)D * n;
@@ -158,6 +170,8 @@ k_mul_evk_pm(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restr
 __global__ void __launch_bounds__(256)
 k_mul_pt_pm(const GqPrime *__restrict__ primes, int n, int D, uint64_t *__restrict__ y,
             const uint64_t *__restrict__ x) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const int half = n >> 1;
   const long long per = (long long)D * half;
   const size_t stride = (size_t)D * n;
@@ -186,6 +200,8 @@ __global__ void __launch_bounds__(256)
 k_mul_evk_perm(const GqPrime *__restrict__ primes, int n, int logn, int D, uint64_t *__restrict__ y,
                const uint64_t *__restrict__ x, const uint64_t *__restrict__ e0,
                const uint64_t *__restrict__ e1, unsigned g) {
+  GQ_PDL_TRIGGER();
+  GQ_PDL_WAIT();
   const long long per = (long long)D * n;
   const size_t stride = (size_t)D * n;
   const unsigned mask2n = 2u * (unsigned)n - 1u;

@@ -4,6 +4,7 @@
 #pragma once
 #include <string>
 
+#define GQ_NO_PDL 1      // the probe kernels do not carry the dependent-launch calls
 #include "gq_arith.h"     // gpqhe_b200/csrc: the same arithmetic helpers as the product kernels
 
 #if defined(__GNUC__)
