@@ -665,7 +665,10 @@ def run_ours(args):
         return bool(t.item())
 
     sharded = None
+    pdl_before_sharded = None
     if not args.no_sharded:
+        pdl_before_sharded = lib.gq_set_pdl(1)          # the sharded drivers switch it off above two ranks (sharded.py)
+        lib.gq_set_pdl(pdl_before_sharded)
         from gpqhe_b200.sharded import MulPlan, ShardedHe
         with torch.cuda.stream(ext):
             sh = ShardedHe(ctx, device=dev)
@@ -769,6 +772,8 @@ def run_ours(args):
             sharded["p2p"] = p2p_leg(False)
             if sharded["p2p"].get("fused_exchange"):
                 sharded["p2p"]["unfused"] = p2p_leg(True)
+    if pdl_before_sharded is not None:
+        lib.gq_set_pdl(pdl_before_sharded)             # back to the default for the remaining legs
 
     # ---- end to end through the host C ABI: pinned host buffers, copies inside the timed region ----
     hout = torch.empty((2, W, n), dtype=torch.int64).pin_memory()

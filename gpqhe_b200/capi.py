@@ -130,6 +130,7 @@ SIGNATURES = {
     "gq_stage_ks_epilogue_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, vp]),
     "gq_stage_ks_epilogue_rs_dev": (C.c_int, [vp, C.c_uint, vp, vp, vp, vp, vp, C.c_uint, vp]),
     "gq_stage_rescale_dev": (C.c_int, [vp, C.c_uint, vp, vp, C.c_int, C.c_uint, vp]),
+    "gq_set_pdl": (C.c_int, [C.c_int]),
     "gq_stage_prescale_ok": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_int]),
     "gq_stage_tensor_inv_pre_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp]),
     "gq_stage_mul_evk_inv_pre_dev": (C.c_int, [vp, C.c_uint, C.c_uint, C.c_uint, vp, vp, vp, vp]),

@@ -217,6 +217,20 @@ static int build_prescale(gq_ctx *c) {
 #ifndef GQ_EMULATE
 int gq_pdl_enabled = getenv("GPQHE_B200_NO_PDL") ? 0 : 1;      // programmatic dependent launch (gq_platform.h)
 #endif
+// process-wide switch of the programmatic dependent launch; returns the previous setting.  On by default: it hides
+// the launch gaps of an eagerly issued op (one he_mul + he_rs: 296 -> 270 us).  The sharded plans switch it off above
+// two ranks: their per-rank kernels are a few microseconds long and already replayed from graphs, and there the early
+// launch + in-kernel wait measured SLOWER than plain graph edges (8 GPUs: 0.136 against 0.113 ms per op).
+extern "C" int gq_set_pdl(int on) {
+#ifndef GQ_EMULATE
+  const int prev = gq_pdl_enabled;
+  if (!getenv("GPQHE_B200_NO_PDL")) gq_pdl_enabled = on ? 1 : 0;
+  return prev;
+#else
+  (void)on;
+  return 0;
+#endif
+}
 static void tc_prebuild(gq_ctx *c);
 extern "C" int gq_ctx_create(gq_ctx **out, unsigned logn, const uint64_t *qw, unsigned q_words,
                              unsigned slots, uint64_t Delta, unsigned logp, unsigned logqub,

@@ -41,6 +41,10 @@ class ShardedHe:
         self.ctx, self.group = ctx, group
         self._pre_cache = {}
         self.G = dist.get_world_size(group) if dist.is_initialized() else 1
+        # above two ranks the per-rank kernels are a few microseconds long: programmatic dependent launch measured slower
+        # than plain stream / graph edges there (profiles/r02_scaling.md), so the sharded drivers switch it off
+        if self.G > 2:
+            ctx._lib.gq_set_pdl(0)
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.n, self.W = ctx.n, ctx.W
         if self.n % self.G:
@@ -408,6 +412,8 @@ class P2PPlan:
                   xchg(2, self.D2, self.p_xl2, self.c_off2), xchg(3, self.D2, self.p_ch, self.c_off2)]
         # limb -> coefficient exchanges carry residues pre-scaled for the CRT (tensor-core CRT stages) when the
         # library has those forms for the two bases; every rank takes the same decision (same context parameters)
+        if self.G > 2:                 # see ShardedHe.__init__
+            self._lib.gq_set_pdl(0)
         plain = bool(os.environ.get("GPQHE_B200_SHARDED_PLAIN"))
         self.pre1 = not plain and bool(self._lib.gq_stage_prescale_ok(self._h, self.D1, self.l, 0))
         self.pre2 = not plain and bool(self._lib.gq_stage_prescale_ok(self._h, self.D2, self.l, 1))

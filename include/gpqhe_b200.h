@@ -411,6 +411,10 @@ typedef struct gq_p2p_xchg {
   unsigned *ticket_dev;
   unsigned pre;   /* != 0: the residues of this exchange are pre-scaled for the basis D (gq_stage_prescale_ok) */
 } gq_p2p_xchg;
+/* Process-wide switch of programmatic dependent launch between the library's kernels (on by default; the environment
+   variable GPQHE_B200_NO_PDL=1 forces it off); returns the previous setting.  No reference counterpart: a launch
+   detail of this implementation. */
+int gq_set_pdl(int on);
 int gq_p2p_fused_ok(gq_ctx *ctx, unsigned l);
 int gq_p2p_decompose_dev(gq_ctx *ctx, unsigned nlimbs, unsigned npolys, const uint64_t *const *in_dev, unsigned W,
                          unsigned ncoef, const gq_p2p_xchg *send, void *stream);
