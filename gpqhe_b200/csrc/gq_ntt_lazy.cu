@@ -64,6 +64,9 @@ GQ_DEV uint64_t full_reduce(uint64_t v, uint64_t p, int sh) {
 
 // resident CTAs the strided kernels are compiled for: 3 x 256 threads (80 registers, no spills) up to 16
 // points per thread; the 32-point form (n = 2^17) needs its 200+ registers
+#ifndef GQ_TILE_CTAS
+#define GQ_TILE_CTAS 2
+#endif
 #ifndef GQ_STRIDED_CTAS
 #define GQ_STRIDED_CTAS 3
 #endif
@@ -194,7 +197,7 @@ struct TileCfg {
 // ---- forward tile kernel: 2^LOGT contiguous elements, the last LOGT stages ----------
 // PRE: inputs come from the strided kernel (up to 11p); see the range notes at the top.
 template <int LOGT, bool PRE>
-__global__ void __launch_bounds__(TileCfg<LOGT>::NT, (TileCfg<LOGT>::NT >= 512 ? 2 : 1))
+__global__ void __launch_bounds__(TileCfg<LOGT>::NT, (TileCfg<LOGT>::NT >= 512 ? GQ_TILE_CTAS : 1))
 k_nttl_fwd_tile(GqNttTables tb, uint64_t *__restrict__ data, int limb0, int nlimbs) {
   GQ_PDL_TRIGGER();
   GQ_PDL_WAIT();
@@ -299,7 +302,7 @@ GQ_DEV uint64_t inv_load(const InvSrc &S, const GqPM &pm, int n, int logn, int n
 }
 
 template <int LOGT, bool WHOLE, int MODE>
-__global__ void __launch_bounds__(TileCfg<LOGT>::NT, (TileCfg<LOGT>::NT >= 512 ? 2 : 1))
+__global__ void __launch_bounds__(TileCfg<LOGT>::NT, (TileCfg<LOGT>::NT >= 512 ? GQ_TILE_CTAS : 1))
 k_nttl_inv_tile(GqNttTables tb, InvSrc src, uint64_t *__restrict__ y, int limb0, int nlimbs) {
   GQ_PDL_TRIGGER();
   GQ_PDL_WAIT();

@@ -12,7 +12,8 @@ sys.path.insert(0, ROOT)
 import bench  # noqa: E402
 import gpqhe_b200 as g  # noqa: E402
 
-ctx = g.HeContext(bench.LOGN, 1 << bench.LOGQ, bench.SLOTS, 1 << bench.LOGDELTA, device=0)
+ctx = g.HeContext(bench.LOGN, 1 << bench.LOGQ, bench.SLOTS, 1 << bench.LOGDELTA, device=0,
+                  lib_path=os.environ.get("GQ_LIB_VARIANT"))      # A/B of a differently built library
 lib, h = ctx._lib, ctx._h
 n, W, L = ctx.n, ctx.W, ctx.L
 rng = np.random.default_rng(1)
