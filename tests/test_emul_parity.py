@@ -24,6 +24,7 @@ def test_limb_layer(emul_lib, logn, logq):
     (6, (1 << 119) + 12345, (1 << 40) + 7, None),  # arbitrary q and Delta: exact slow path
     (4, 3 ** 75, 1 << 40, None),                  # arbitrary q, power-of-two Delta
     (3, 1 << 881, 1 << 30, [29, 10, 1]),          # the reference's `cmp` ring: 47 key-switch limbs, a 2 774-bit basis
+    (3, 1 << 438, 1 << 50, [8, 1]),               # n = 8: half a 16-row step of the tensor-core CRT kernels is padding
 ])
 def test_he_ops(emul_lib, logn, q, Delta, levels):
     pc.check_he_vs_oracle(emul_lib, logn, q, 4, Delta, seed=logn, levels=levels, logqub=q.bit_length() - 1)
