@@ -57,13 +57,16 @@ if "--p2p" in sys.argv:          # the peer-to-peer sharded plan with ONE virtua
     from gpqhe_b200.sharded import P2PPlan      # unless GPQHE_B200_P2P_UNFUSED=1): the same launches a rank of N issues
     ext = torch.cuda.ExternalStream(lib.gq_ctx_stream(h), device=dev)
     with torch.cuda.stream(ext):
-        plan = P2PPlan.loopback(ctx, 1, L, evk, rescale=True, device=dev)[0]
-        for k in range(4):
-            plan.inp[k].copy_(inp[k])
+        GV = int(os.environ.get("GQ_P2P_RANKS", "1"))        # virtual ranks on this one GPU: the grids of a GV-GPU run
+        plans = P2PPlan.loopback(ctx, GV, L, evk, rescale=True, device=dev)
+        nl = n // GV
+        for r, pl in enumerate(plans):
+            for k in range(4):
+                pl.inp[k].copy_(inp[k][:, r * nl:(r + 1) * nl])
 
     def op():
         with torch.cuda.stream(ext):
-            P2PPlan.run_lockstep([plan])
+            P2PPlan.run_lockstep(plans)
 
 for _ in range(3):
     op()
